@@ -1,0 +1,264 @@
+/* ufe_b200.h -- C ABI of the B200-native UFEMISM hot path (libufe_b200.so).
+ *
+ * Drop-in boundary behind the reference's Fortran module interfaces.  Every entry
+ * point names the reference interface it replaces (paths relative to the reference repository).
+ * The Fortran side binds these with ISO_C_BINDING (ufemism2.0_b200/fortran/ufe_b200_mod.f90) and
+ * is selected by the namelist key  choice_linear_algebra_backend_config = 'B200'.
+ *
+ * Conventions (exactly what a Fortran caller owns):
+ *   - arrays are column-major; indices stored in arrays are 1-based; 0 = "none"
+ *   - a field on the a/b/c-grid is passed as the rank's owned slice (vi1:vi2), (ti1:ti2), (ei1:ei2);
+ *     3-D fields are (n_loc, nz) column-major, i.e. layer-major in memory
+ *   - mesh arrays are the full (global) arrays, which every MPI rank of the reference holds
+ *   - all calls are collective over the ranks of the handle and synchronous on return
+ *   - every function returns 0 on success; ufe_b200_last_error() describes the last failure.
+ *     Krylov non-convergence is NOT an error (iteration count == maxit), exactly like the
+ *     reference, which never checks PETSc's return codes (src/UPSY/basic/petsc_basic.f90:199-205).
+ *   - there is no CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef UFE_B200_H
+#define UFE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ufe_b200_ctx* ufe_b200_handle;
+
+/* ---- enumerations ---------------------------------------------------------------------------- */
+enum { UFE_KSP_BICGSTAB = 0, UFE_KSP_CG = 1 };                       /* north_star (b) */
+enum { UFE_PC_JACOBI = 0, UFE_PC_NONE = 1, UFE_PC_BJACOBI2 = 2, UFE_PC_NEUMANN = 3 };
+enum { UFE_BC_INFINITE = 0, UFE_BC_ZERO = 1 };                        /* C%BC_{u,v,H}_{north,east,south,west} */
+enum { UFE_SLID_NO_SLIDING = 0, UFE_SLID_WEERTMAN = 1, UFE_SLID_COULOMB = 2, UFE_SLID_BUDD = 3, UFE_SLID_TSAI2015 = 4,
+       UFE_SLID_SCHOOF2005 = 5, UFE_SLID_ZOET_IVERSON = 6, UFE_SLID_IDEALISED_SSA_ICESTREAM = 7 };
+enum { UFE_INTEGRATION_EXPLICIT = 0, UFE_INTEGRATION_SEMI_IMPLICIT = 1 };
+
+/* mesh operators, in the order calc_all_matrix_operators_mesh builds them
+ * (src/UPSY/mesh/discretisation/mesh_disc_calc_matrix_operators_2D.f90:26-59; mesh_types.f90:213-232) */
+enum { UFE_OP_DDX_A_A = 0, UFE_OP_DDY_A_A, UFE_OP_MAP_A_B, UFE_OP_DDX_A_B, UFE_OP_DDY_A_B, UFE_OP_MAP_B_A, UFE_OP_DDX_B_A,
+       UFE_OP_DDY_B_A, UFE_OP_DDX_B_B, UFE_OP_DDY_B_B, UFE_OP2_DDX_B_B, UFE_OP2_DDY_B_B, UFE_OP2_D2DX2_B_B,
+       UFE_OP2_D2DXDY_B_B, UFE_OP2_D2DY2_B_B, UFE_OP_COUNT };
+
+/* ---- the C% scalars the path reads (src/UPSY/basic/model_configuration/model_configuration_type_and_namelist.f90) */
+typedef struct ufe_b200_config {
+  double visc_it_norm_dUV_tol;              /* :306 */
+  double visc_it_relax;                     /* :308 */
+  double visc_eff_min;                      /* :309 */
+  double vel_max;                           /* :310 */
+  double stress_balance_PETSc_rtol;         /* :311 */
+  double stress_balance_PETSc_abstol;       /* :312 */
+  double Glens_flow_law_exponent;           /* :598 */
+  double Glens_flow_law_epsilon_sq_0;       /* :599 */
+  double slid_delta_v;                      /* :349 */
+  double slid_Weertman_m;                   /* :333 */
+  double slid_Budd_q_plastic;               /* :334 */
+  double slid_Budd_u_threshold;             /* :335 */
+  double slid_ZI_ut;                        /* :337 */
+  double slid_ZI_p;                         /* :336 */
+  double slid_beta_max;                     /* :348 */
+  double subgrid_friction_exponent_on_B_grid; /* :345 */
+  double Hi_min;                            /* :437 */
+  double uniform_Glens_flow_factor;         /* :603 */
+  double refgeo_idealised_SSA_icestream_Hi, refgeo_idealised_SSA_icestream_dhdx,
+         refgeo_idealised_SSA_icestream_L, refgeo_idealised_SSA_icestream_m;
+  double dHi_semiimplicit_fs;               /* :356 */
+  double dHi_PETSc_rtol, dHi_PETSc_abstol;  /* :357-358 */
+  double dt_ice_min, dt_ice_max;            /* :391-392 */
+  double ice_density, seawater_density, grav; /* src/UPSY/basic/parameters.f90:19-24 */
+  int32_t visc_it_nit;                      /* :307 */
+  int32_t do_include_SSADIVA_crossterms;    /* :275 */
+  int32_t BC_u[4], BC_v[4];                 /* north, east, south, west  (:319-326) */
+  int32_t choice_sliding_law;               /* UFE_SLID_* */
+  int32_t do_GL_subgrid_friction;           /* :340 */
+  int32_t choice_ice_integration_method;    /* UFE_INTEGRATION_* (:355) */
+  int32_t BC_H[4];                          /* :364-367 */
+  int32_t ksp_type, pc_type, ksp_maxit;     /* new keys B200_KSP_type_config / B200_PC_type_config; maxit = 2000 (petsc_basic.f90:166) */
+  int32_t write_diagnostics;                /* 1: also fill the intermediate DIVA fields that only checksum()/restart read */
+  int32_t reserved[6];
+} ufe_b200_config;
+
+/* Fill cfg with the reference's namelist defaults. */
+void ufe_b200_config_defaults(ufe_b200_config* cfg);
+
+/* ---- life cycle -------------------------------------------------------------------------------- */
+/* Replaces initialise_parallelisation + PetscInitialize for this path (src/UFEMISM/main/UFEMISM_program.f90:55-56).
+ * One rank <-> one GPU. For nranks > 1 rank 0 calls ufe_b200_get_unique_id() and broadcasts the 128 bytes with
+ * the reference's own MPI_BCAST before every rank calls ufe_b200_init().  device < 0 picks rank % device_count. */
+int ufe_b200_get_unique_id(void* id128);
+int ufe_b200_init(int device, int rank, int nranks, const void* id128, ufe_b200_handle* out);
+int ufe_b200_finalize(ufe_b200_handle h);
+const char* ufe_b200_last_error(void);
+/* number of CUDA kernels this library has launched since init (bench.py's gpu_launches claim) */
+long long ufe_b200_kernel_launches(ufe_b200_handle h);
+
+/* ---- narrow seam: linear algebra --------------------------------------------------------------- */
+/* Replaces solve_matrix_equation_CSR_PETSc( AA, bb, xx, rtol, abstol, n_Axb_its, ...)  (src/UPSY/basic/petsc_basic.f90:32-215).
+ * AA is the rank's finalised type_sparse_matrix_CSR_dp: rows i1..i1+m_loc-1 of an m_glob x m_glob matrix;
+ * ptr has m_loc+1 entries holding 1-based offsets into ind/val relative to ptr[0]; ind = global 1-based columns.
+ * xx on input is ignored (zero initial guess, petsc_basic.f90:163). */
+int ufe_b200_ksp_solve(ufe_b200_handle h, int m_glob, int m_loc, int i1, const int32_t* ptr, const int32_t* ind,
+                       const double* val, const double* bb, double* xx, double rtol, double abstol, int maxit,
+                       int ksp_type, int pc_type, int* n_Axb_its);
+
+/* Replaces multiply_CSR_matrix_with_vector_{1D,2D}_wrapper (src/UPSY/basic/CSR_matrix_algebra/CSR_matrix_vector_multiplication.f90:24,112):
+ * register a matrix once (pattern + values stay on the device), then y = A x for ncols right-hand sides
+ * laid out (n_loc, ncols) / (m_loc, ncols) column-major.  j1/n_loc give the rank's owned slice of x. */
+int ufe_b200_csr_register(ufe_b200_handle h, int id, int m_glob, int n_glob, int m_loc, int i1, int n_loc, int j1,
+                          const int32_t* ptr, const int32_t* ind, const double* val);
+int ufe_b200_csr_update_values(ufe_b200_handle h, int id, const double* val);
+int ufe_b200_spmv(ufe_b200_handle h, int id, const double* xx, double* yy, int ncols);
+int ufe_b200_csr_release(ufe_b200_handle h, int id);
+
+/* ---- wide seam: mesh --------------------------------------------------------------------------- */
+/* The members of type_mesh the path reads (src/UPSY/types/mesh_types.f90:40-131). */
+typedef struct ufe_b200_mesh_desc {
+  int32_t nV, nTri, nE, nC_mem, nz;
+  double xmin, xmax, ymin, ymax;
+  const double* V;       /* (nV,2)       */
+  const int32_t* nC;     /* (nV)         */
+  const int32_t* C;      /* (nV,nC_mem)  */
+  const int32_t* niTri;  /* (nV)         */
+  const int32_t* iTri;   /* (nV,nC_mem)  */
+  const int32_t* VBI;    /* (nV)         */
+  const int32_t* Tri;    /* (nTri,3)     */
+  const int32_t* TriC;   /* (nTri,3)     */
+  const int32_t* TriBI;  /* (nTri)       */
+  const double* TriGC;   /* (nTri,2)     */
+  const double* A;       /* (nV)         */
+  const double* Cw;      /* (nV,nC_mem)  */
+  const double* D_x;     /* (nV,nC_mem)  */
+  const double* D_y;     /* (nV,nC_mem)  */
+  const double* D;       /* (nV,nC_mem)  */
+  const int32_t* VE;     /* (nV,nC_mem)  */
+  const int32_t* ETri;   /* (nE,2)       */
+  const double* zeta;    /* (nz)         */
+} ufe_b200_mesh_desc;
+
+/* Upload the mesh (lifetime = lifetime of type_mesh; destroy on remesh, src/UFEMISM/main/UFEMISM_main_model.f90:1211).
+ * Ownership ranges follow partition_list (src/UPSY/basic/mpi_parallelisation/mpi_distributed_memory.f90:47-73). */
+int ufe_b200_mesh_create(ufe_b200_handle h, const ufe_b200_mesh_desc* mesh);
+int ufe_b200_mesh_destroy(ufe_b200_handle h);
+/* out = {vi1,vi2,ti1,ti2,ei1,ei2} (1-based, inclusive) */
+int ufe_b200_mesh_ranges(ufe_b200_handle h, int32_t* out6);
+
+/* Replaces calc_all_matrix_operators_mesh (mesh_disc_calc_matrix_operators_2D.f90:26-59): builds the 15 operator
+ * matrices on the device (patterns bit-identical to the reference's construction order). */
+int ufe_b200_calc_matrix_operators(ufe_b200_handle h);
+/* Alternatively hand over an operator the Fortran side already built (rank-local rows, as in ufe_b200_ksp_solve). */
+int ufe_b200_set_operator(ufe_b200_handle h, int op, int m_loc, const int32_t* ptr, const int32_t* ind, const double* val);
+/* Inspect an operator (parity checks): sizes first (nnz of the local rows), then the arrays. */
+int ufe_b200_get_operator_size(ufe_b200_handle h, int op, int* m_loc, int* nnz_loc);
+int ufe_b200_get_operator(ufe_b200_handle h, int op, int32_t* ptr, int32_t* ind, double* val);
+
+/* Replaces the 16 wrappers ddx/ddy/map_{a_a,a_b,b_a}_{2D,3D} (+ b_b) (src/UPSY/mesh/discretisation/mesh_disc_apply_operators.f90:18-431).
+ * d_in / d_out are the rank's owned slices, (n_loc, ncols) column-major; ncols = 1 (2D) or nz (3D). */
+int ufe_b200_apply_operator(ufe_b200_handle h, int op, const double* d_in, double* d_out, int ncols);
+
+/* ---- wide seam: stress balance ------------------------------------------------------------------ */
+/* Replaces solve_SSA_DIVA_linearised( mesh, u_b, v_b, N_b, dN_dx_b, dN_dy_b, basal_friction_coefficient_b, tau_dx_b, tau_dy_b,
+ *   u_b_prev, v_b_prev, PETSc_rtol, PETSc_abstol, n_Axb_its, BC_prescr_mask_b, BC_prescr_u_b, BC_prescr_v_b)
+ * (src/UFEMISM/ice_dynamics/conservation_of_momentum/SSA_DIVA/solve_linearised_SSA_DIVA_infinite_slab.f90:23-178).
+ * u_b_prev / v_b_prev are the rank's owned slices here (the reference gathers them globally only for the
+ * periodic / ice-stream copy BCs, which this entry point does not offer). BC_* may be NULL (no prescribed velocities). */
+int ufe_b200_solve_SSA_DIVA_linearised(ufe_b200_handle h, const ufe_b200_config* cfg, double* u_b, double* v_b,
+                                       const double* N_b, const double* dN_dx_b, const double* dN_dy_b,
+                                       const double* basal_friction_coefficient_b, const double* tau_dx_b,
+                                       const double* tau_dy_b, double* u_b_prev, double* v_b_prev, double rtol,
+                                       double abstol, int* n_Axb_its, const int32_t* BC_prescr_mask_b,
+                                       const double* BC_prescr_u_b, const double* BC_prescr_v_b);
+/* The system assembled by the last linearised solve (rank-local rows): sizes, then arrays (bit-exact ptr/ind parity). */
+int ufe_b200_get_stiffness_size(ufe_b200_handle h, int* m_loc, int* nnz_loc);
+int ufe_b200_get_stiffness(ufe_b200_handle h, int32_t* ptr, int32_t* ind, double* val, double* bb);
+
+/* Inputs of the velocity solve taken from type_ice_model / type_bed_roughness_model (owned slices). */
+typedef struct ufe_b200_ice_inputs {
+  const double* Hi;                  /* (vi1:vi2) ice%Hi */
+  const double* Hs;                  /* (vi1:vi2) ice%Hs */
+  const double* A_flow;              /* (vi1:vi2,nz) ice%A_flow after calc_ice_rheology_Glen (rheology/constitutive_equation.f90:84-163) */
+  const double* fraction_gr_b;       /* (ti1:ti2) ice%fraction_gr_b */
+  const double* till_friction_angle; /* (vi1:vi2) bed_roughness%till_friction_angle (may be NULL if the law does not use it) */
+  const double* beta_sq;             /* (vi1:vi2) bed_roughness%beta_sq   (may be NULL) */
+  const double* alpha_sq;            /* (vi1:vi2) bed_roughness%alpha_sq  (may be NULL) */
+  const double* effective_pressure;  /* (vi1:vi2) ice%effective_pressure  (may be NULL) */
+  const int32_t* mask_grounded_ice;  /* (vi1:vi2) 0/1 */
+  const int32_t* mask_icefree_land;  /* (vi1:vi2) 0/1 */
+} ufe_b200_ice_inputs;
+
+/* type_ice_velocity_solver_DIVA (src/UFEMISM/types/ice_model_types.f90:149-197): inout state + outputs.
+ * NULL members are skipped on download.  For solve_SSA, u_vav_b/v_vav_b carry SSA%u_b/SSA%v_b. */
+typedef struct ufe_b200_velocity_state {
+  double *u_vav_b, *v_vav_b;                 /* inout (ti1:ti2) */
+  double *u_base_b, *v_base_b;               /* inout */
+  double *tau_bx_b, *tau_by_b;               /* inout */
+  double *eta_3D_b;                          /* inout (ti1:ti2,nz) */
+  double *u_b_prev, *v_b_prev;               /* out   */
+  double *tau_dx_b, *tau_dy_b;               /* out   */
+  double *u_3D_b, *v_3D_b;                   /* out (ti1:ti2,nz) */
+  double *du_dx_a, *du_dy_a, *dv_dx_a, *dv_dy_a;      /* out (vi1:vi2) */
+  double *du_dz_3D_a, *dv_dz_3D_a, *eta_3D_a;         /* out (vi1:vi2,nz) */
+  double *eta_vav_a, *N_a;                   /* out */
+  double *N_b, *dN_dx_b, *dN_dy_b;           /* out */
+  double *F1_3D_a, *F2_3D_a;                 /* out (vi1:vi2,nz) */
+  double *F1_3D_b, *F2_3D_b;                 /* out (ti1:ti2,nz) */
+  double *basal_friction_coefficient_a;      /* out ice%basal_friction_coefficient */
+  double *basal_friction_coefficient_b, *beta_eff_a, *beta_eff_b; /* out */
+} ufe_b200_velocity_state;
+
+/* Replaces solve_DIVA_infinite_slab( mesh, ice, bed_roughness, DIVA, n_visc_its, n_Axb_its, BC_prescr_*)
+ * (SSA_DIVA/DIVA_solver_infinite_slab.f90:52-231) including calc_driving_stress and calc_3D_velocities. */
+int ufe_b200_solve_DIVA(ufe_b200_handle h, const ufe_b200_config* cfg, const ufe_b200_ice_inputs* ice,
+                        ufe_b200_velocity_state* DIVA, int* n_visc_its, int* n_Axb_its,
+                        const int32_t* BC_prescr_mask_b, const double* BC_prescr_u_b, const double* BC_prescr_v_b);
+/* Replaces solve_SSA (SSA_DIVA/SSA_main.f90:88-245). */
+int ufe_b200_solve_SSA(ufe_b200_handle h, const ufe_b200_config* cfg, const ufe_b200_ice_inputs* ice,
+                       ufe_b200_velocity_state* SSA, int* n_visc_its, int* n_Axb_its,
+                       const int32_t* BC_prescr_mask_b, const double* BC_prescr_u_b, const double* BC_prescr_v_b);
+
+/* Device-resident variants (inputs stay in HBM between calls; used for the time loop and by bench.py's
+ * device-timed leg): upload once, solve any number of times, download when the host needs the fields. */
+int ufe_b200_velocity_upload(ufe_b200_handle h, const ufe_b200_ice_inputs* ice, const ufe_b200_velocity_state* st);
+int ufe_b200_velocity_solve_resident(ufe_b200_handle h, const ufe_b200_config* cfg, int approximation /*0 SSA, 1 DIVA*/,
+                                     int* n_visc_its, int* n_Axb_its);
+int ufe_b200_velocity_download(ufe_b200_handle h, ufe_b200_velocity_state* st);
+
+/* ---- wide seam: ice thickness -------------------------------------------------------------------- */
+/* Replaces calc_dHi_dt( mesh, ice, Hi, Hb, SL, u_vav_b, v_vav_b, SMB, BMB, LMB, AMB, fraction_margin, mask_noice, dt,
+ *   dHi_dt, Hi_tplusdt, divQ, dHi_dt_target, BC_prescr_mask, BC_prescr_Hi)
+ * (src/UFEMISM/ice_dynamics/conservation_of_mass/conservation_of_mass_main.f90:27-119), explicit and semi-implicit.
+ * calc_and_apply_spill_over_flux (utilities/ice_thickness_safeties.f90:290) is NOT included: callers with
+ * calving-front cells set finish = 0, run the spill-over on the host and then call ufe_b200_dHi_dt_finish(). */
+typedef struct ufe_b200_thickness_io {
+  const double *Hi, *Hb, *SL;               /* (vi1:vi2) */
+  const double *u_vav_b, *v_vav_b;          /* (ti1:ti2); NULL = use the device-resident velocity state */
+  const double *SMB, *BMB, *LMB;            /* (vi1:vi2) */
+  const double *fraction_margin;            /* (vi1:vi2) */
+  const int32_t* mask_noice;                /* (vi1:vi2) 0/1 */
+  const double* dHi_dt_target;              /* (vi1:vi2) */
+  const int32_t* BC_prescr_mask;            /* (vi1:vi2) or NULL */
+  const double* BC_prescr_Hi;               /* (vi1:vi2) or NULL */
+  double *AMB, *dHi_dt, *Hi_tplusdt, *divQ; /* (vi1:vi2) out */
+} ufe_b200_thickness_io;
+int ufe_b200_calc_dHi_dt(ufe_b200_handle h, const ufe_b200_config* cfg, ufe_b200_thickness_io* io, double* dt,
+                         int finish, int* n_Axb_its);
+int ufe_b200_dHi_dt_finish(ufe_b200_handle h, const double* Hi, double* Hi_tplusdt, double dt, double* AMB,
+                           double* dHi_dt);
+
+/* ---- SIA (config 4) ------------------------------------------------------------------------------ */
+/* Replaces solve_SIA (src/UFEMISM/ice_dynamics/conservation_of_momentum/SIA/SIA_main.f90:65-158): u_3D_b, v_3D_b (ti1:ti2,nz). */
+int ufe_b200_solve_SIA(ufe_b200_handle h, const ufe_b200_config* cfg, const double* Hi, const double* Hs,
+                       const double* A_flow, double* u_3D_b, double* v_3D_b);
+
+/* ---- timing hooks for bench.py (CUDA events on the library's own stream) ----------------------- */
+/* Milliseconds spent in the named kernel class since the last reset, and its launch count.
+ * classes: "spmv_stiffness", "krylov_vec", "assembly", "column", "tri", "epilogue", "thickness", "operator_spmv" */
+int ufe_b200_timing_enable(ufe_b200_handle h, int on);
+int ufe_b200_timing_get(ufe_b200_handle h, const char* kernel_class, double* ms, long long* launches);
+int ufe_b200_timing_reset(ufe_b200_handle h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UFE_B200_H */

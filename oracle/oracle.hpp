@@ -1,0 +1,151 @@
+// TEST INFRASTRUCTURE ONLY -- CPU restatement ("oracle") of UFEMISM's stress-balance / ice-thickness
+// hot path.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg
+// may link or call this; the product (ufemism2.0_b200/csrc) never does.
+//
+// Parity status: the reference is Fortran 2018 + PETSc + MPI + NetCDF and cannot be built in this
+// image (no Fortran compiler).  The oracle is pinned against the reference's own
+// known-answer vectors that are usable as text (tests/golden/README.md): the 6x6 and two 7x7 CSR
+// systems, the partition_list table, the dummy-mesh connectivity, polynomial exactness of the
+// operators (what ct_discretisation_mapping_derivatives checks), the Laplace component test's
+// analytic solution, and the Halfar / Schoof analytic solutions.  Element-wise parity with a
+// *running* reference (PETSc KSP output) is "unpinned".
+//
+// Conventions: all arrays are the reference's own (column-major, 1-based indices, 0 = none).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace orc {
+
+// type_sparse_matrix_CSR_dp restricted to one process (CSR_sparse_matrix_type.f90:15-38)
+struct Csr {
+  int m = 0, n = 0;
+  std::vector<int> ptr;     // size m+1, 1-based offsets into ind/val (ptr[0] == 1)
+  std::vector<int> ind;     // 1-based column indices, construction order (never sorted, never merged)
+  std::vector<double> val;
+  void init(int m_, int n_, size_t nnz_est = 0) {
+    m = m_; n = n_; ptr.assign((size_t)m + 1, 1); ind.clear(); val.clear(); ind.reserve(nnz_est); val.reserve(nnz_est);
+  }
+  // add_entry_CSR_dist (CSR_matrix_basics.f90:251-277): rows must be filled in ascending order
+  void add(int i, int j, double v) { ind.push_back(j); val.push_back(v); ptr[i] = (int)ind.size() + 1; }
+  // rows that received no entry inherit the running offset (what crop/finalise leave behind)
+  void finalise() { for (int i = 1; i <= m; ++i) if (ptr[i] < ptr[i - 1]) ptr[i] = ptr[i - 1]; }
+  size_t nnz() const { return ind.size(); }
+};
+
+// y = A x  (CSR_matrix_vector_multiplication.f90:318-330)
+void spmv(const Csr& A, const double* x, double* y);
+
+struct MeshView {  // borrowed pointers to the Fortran arrays
+  int nV, nTri, nE, nC_mem, nz;
+  double xmin, xmax, ymin, ymax;
+  const double* V; const int* nC; const int* C; const int* niTri; const int* iTri; const int* VBI;
+  const int* Tri; const int* TriC; const int* TriBI; const double* TriGC;
+  const double* A; const double* Cw; const double* D_x; const double* D_y; const double* D;
+  const int* VE; const int* EV; const int* ETri; const double* zeta;
+};
+
+enum OpId {
+  OP_ddx_a_a = 0, OP_ddy_a_a, OP_map_a_b, OP_ddx_a_b, OP_ddy_a_b, OP_map_b_a, OP_ddx_b_a, OP_ddy_b_a,
+  OP_ddx_b_b, OP_ddy_b_b, OP2_ddx_b_b, OP2_ddy_b_b, OP2_d2dx2_b_b, OP2_d2dxdy_b_b, OP2_d2dy2_b_b, OP_COUNT
+};
+
+struct Operators { Csr M[OP_COUNT]; };
+
+// calc_all_matrix_operators_mesh (mesh_disc_calc_matrix_operators_2D.f90:26-59)
+void calc_all_matrix_operators(const MeshView& mesh, Operators& ops);
+
+// --- configuration scalars the path reads (model_configuration_type_and_namelist.f90) -----------------
+enum SlidingLaw { SLID_no_sliding = 0, SLID_Weertman = 1, SLID_Coulomb = 2, SLID_Budd = 3, SLID_Tsai2015 = 4,
+                  SLID_Schoof2005 = 5, SLID_ZoetIverson = 6, SLID_idealised_SSA_icestream = 7 };
+enum BC { BC_infinite = 0, BC_zero = 1 };
+enum KspType { KSP_bicgstab_jacobi = 0, KSP_gmres_ilu0 = 1 };
+
+struct Config {
+  // viscosity iteration (…type_and_namelist.f90:300-312)
+  double visc_it_norm_dUV_tol = 5e-5; int visc_it_nit = 50; double visc_it_relax = 0.2;
+  double visc_eff_min = 1e4; double vel_max = 5000.0;
+  double stress_balance_PETSc_rtol = 1e-7, stress_balance_PETSc_abstol = 1e-5;
+  double Glens_flow_law_exponent = 3.0, Glens_flow_law_epsilon_sq_0 = 1e-8;
+  int do_include_SSADIVA_crossterms = 1;
+  int BC_u[4] = {0, 0, 0, 0}, BC_v[4] = {0, 0, 0, 0};  // north, east, south, west
+  // sliding
+  int choice_sliding_law = SLID_ZoetIverson;
+  double slid_delta_v = 1e-3, slid_Weertman_m = 3.0, slid_Budd_q_plastic = 0.3, slid_Budd_u_threshold = 100.0;
+  double slid_ZI_ut = 200.0, slid_ZI_p = 5.0, slid_beta_max = 1e20;
+  int do_GL_subgrid_friction = 1; double subgrid_friction_exponent_on_B_grid = 2.0;
+  double Hi_min = 0.0;
+  // SSA_icestream idealised law (Schoof 2006)
+  double uniform_Glens_flow_factor = 1e-16;
+  double icestream_Hi = 2000.0, icestream_dhdx = -0.0003, icestream_L = 150e3, icestream_m = 1.0;
+  // thickness
+  int choice_ice_integration_method = 1;  // 0 explicit, 1 semi-implicit
+  double dHi_semiimplicit_fs = 1.5, dHi_PETSc_rtol = 1e-8, dHi_PETSc_abstol = 1e-6;
+  double dt_ice_min = 0.1;
+  int BC_H[4] = {1, 1, 1, 1};             // 0 infinite, 1 zero
+  // physical constants (parameters.f90)
+  double ice_density = 917.0, seawater_density = 1027.0, grav = 9.81;
+  // which Krylov method the oracle uses
+  int ksp_type = KSP_bicgstab_jacobi; int ksp_maxit = 2000;
+};
+
+// --- linear solvers ---------------------------------------------------------------------------------
+// Both follow PETSc semantics at the reference's call site (petsc_basic.f90:125-237): zero initial
+// guess, left preconditioning, convergence on ||B r||_2 <= max(rtol ||B b||_2, abstol), <= maxit its.
+int ksp_bicgstab_jacobi(const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int* its);
+int ksp_gmres_ilu0(const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int restart, int* its);
+
+// --- linearised SSA/DIVA (solve_linearised_SSA_DIVA_infinite_slab.f90) --------------------------------
+void assemble_SSA_DIVA(const MeshView& mesh, const Operators& ops, const Config& C,
+                       const double* N_b, const double* dN_dx_b, const double* dN_dy_b, const double* beta_b,
+                       const double* tau_dx_b, const double* tau_dy_b,
+                       const int* BC_prescr_mask_b, const double* BC_prescr_u_b, const double* BC_prescr_v_b,
+                       Csr& A, std::vector<double>& bb);
+
+struct DivaState {  // type_ice_velocity_solver_DIVA (ice_model_types.f90:149-197), fields on the path
+  std::vector<double> u_vav_b, v_vav_b, u_base_b, v_base_b, u_b_prev, v_b_prev;
+  std::vector<double> tau_dx_b, tau_dy_b, tau_bx_b, tau_by_b;
+  std::vector<double> du_dx_a, du_dy_a, dv_dx_a, dv_dy_a, du_dz_3D_a, dv_dz_3D_a;
+  std::vector<double> eta_3D_a, eta_3D_b, eta_vav_a, N_a, N_b, dN_dx_b, dN_dy_b;
+  std::vector<double> F1_3D_a, F2_3D_a, F1_3D_b, F2_3D_b;
+  std::vector<double> basal_friction_coefficient_a, basal_friction_coefficient_b, beta_eff_a, beta_eff_b;
+  std::vector<double> u_3D_b, v_3D_b;
+  void init(int nV, int nTri, int nz);
+};
+
+struct IceInputs {  // the type_ice_model / bed_roughness fields the velocity solve reads
+  const double* Hi; const double* Hs; const double* A_flow_3D;   // (nV), (nV), (nV,nz)
+  const double* fraction_gr_b;                                    // (nTri)
+  const double* till_friction_angle; const double* beta_sq; const double* alpha_sq;  // (nV) bed roughness
+  const double* effective_pressure;                               // (nV)
+  const int* mask_grounded_ice; const int* mask_icefree_land;      // (nV) 0/1
+};
+
+// solve_DIVA_infinite_slab (DIVA_solver_infinite_slab.f90:52-231); returns 0 ok
+int solve_DIVA(const MeshView& mesh, const Operators& ops, const Config& C, const IceInputs& ice, DivaState& D,
+               const int* BC_prescr_mask_b, const double* BC_prescr_u_b, const double* BC_prescr_v_b,
+               int* n_visc_its, int* n_Axb_its, int max_visc_its_override = -1);
+// solve_SSA (SSA_main.f90:88-245); uses u_vav_b/v_vav_b of D as u_b/v_b
+int solve_SSA(const MeshView& mesh, const Operators& ops, const Config& C, const IceInputs& ice, DivaState& D,
+              const int* BC_prescr_mask_b, const double* BC_prescr_u_b, const double* BC_prescr_v_b,
+              int* n_visc_its, int* n_Axb_its, int max_visc_its_override = -1);
+
+// --- ice thickness (conservation_of_mass_*.f90) -------------------------------------------------------
+struct ThicknessIO {
+  const double* Hi; const double* Hb; const double* SL; const double* u_vav_b; const double* v_vav_b;
+  const double* SMB; const double* BMB; const double* LMB; const double* fraction_margin; const int* mask_noice;
+  const double* dHi_dt_target; const int* BC_prescr_mask; const double* BC_prescr_Hi;  // may be null
+  double* AMB; double* dHi_dt; double* Hi_tplusdt; double* divQ;
+};
+int calc_dHi_dt(const MeshView& mesh, const Config& C, ThicknessIO& io, double* dt, int* n_Axb_its);
+void calc_flux_divergence_matrix_upwind(const MeshView& mesh, const double* u_vav_b, const double* v_vav_b,
+                                        const double* fraction_margin, Csr& M_divQ, std::vector<double>* u_perp = nullptr);
+
+// --- SIA (SIA_main.f90:65-158) and analytic solutions ------------------------------------------------
+void solve_SIA(const MeshView& mesh, const Operators& ops, const Config& C, const double* Hi, const double* Hs,
+               const double* A_flow_3D, double* u_3D_b, double* v_3D_b);
+double Halfar_H(double A, double n, double H0, double R0, double x, double y, double t_yr);
+void Schoof2006_icestream(double A, double n, double H, double dhdx, double L, double m, double y, double* u, double* tauc);
+
+}  // namespace orc

@@ -1,0 +1,120 @@
+"""ctypes access to oracle/liboracle.so -- TEST INFRASTRUCTURE ONLY (the CPU restatement of the reference).
+
+Nothing under ufemism2.0_b200/ imports this module.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+import ufe_b200 as ub
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_LIB = None
+KSP_BICGSTAB_JACOBI, KSP_GMRES_ILU0 = 0, 1
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        L = C.CDLL(os.path.join(ROOT, "oracle", "liboracle.so"))
+        dp, ip = ub.c_dp, ub.c_ip
+        L.orc_spmv.argtypes = [C.c_int, C.c_int, ip, ip, dp, dp, dp]
+        L.orc_ksp_solve.argtypes = [C.c_int, ip, ip, dp, dp, dp, C.c_double, C.c_double, C.c_int, C.c_int, C.POINTER(C.c_int)]
+        L.orc_mesh_create.restype = C.c_void_p
+        L.orc_mesh_create.argtypes = [C.POINTER(ub.MeshDesc)]
+        L.orc_mesh_destroy.argtypes = [C.c_void_p]
+        L.orc_calc_matrix_operators.argtypes = [C.c_void_p]
+        L.orc_get_operator_size.argtypes = [C.c_void_p, C.c_int] + [C.POINTER(C.c_int)] * 3
+        L.orc_get_operator.argtypes = [C.c_void_p, C.c_int, ip, ip, dp]
+        L.orc_apply_operator.argtypes = [C.c_void_p, C.c_int, dp, dp, C.c_int]
+        L.orc_assemble_SSA_DIVA.argtypes = [C.c_void_p, C.POINTER(ub.Config)] + [dp] * 6 + [ip, dp, dp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.orc_get_stiffness.argtypes = [C.c_void_p, ip, ip, dp, dp]
+        L.orc_solve_velocity.argtypes = [C.c_void_p, C.POINTER(ub.Config), C.c_int, C.c_int, C.POINTER(ub.IceInputs),
+                                         C.POINTER(ub.VelocityState), C.POINTER(C.c_int), C.POINTER(C.c_int), ip, dp, dp, C.c_int]
+        L.orc_calc_dHi_dt.argtypes = [C.c_void_p, C.POINTER(ub.Config), C.c_int, C.POINTER(ub.ThicknessIO), dp, C.POINTER(C.c_int)]
+        L.orc_flux_divergence_matrix.argtypes = [C.c_void_p, dp, dp, dp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.orc_get_flux_divergence_matrix.argtypes = [C.c_void_p, ip, ip, dp]
+        L.orc_Halfar_H.restype = C.c_double
+        L.orc_Halfar_H.argtypes = [C.c_double] * 7
+        L.orc_Schoof2006_icestream.argtypes = [C.c_double] * 7 + [dp, dp]
+        L.orc_solve_SIA.argtypes = [C.c_void_p, C.POINTER(ub.Config), dp, dp, dp, dp, dp]
+        _LIB = L
+    return _LIB
+
+
+def spmv(m, n, ptr, ind, val, x):
+    y = np.zeros(m)
+    lib().orc_spmv(m, n, ub.ip(ptr), ub.ip(ind), ub.dp(val), ub.dp(x), ub.dp(y))
+    return y
+
+
+def ksp_solve(ptr, ind, val, b, rtol, abstol, maxit=2000, ksp=KSP_BICGSTAB_JACOBI):
+    m = len(ptr) - 1
+    x = np.zeros(m)
+    its = C.c_int()
+    rc = lib().orc_ksp_solve(m, ub.ip(ptr), ub.ip(ind), ub.dp(val), ub.dp(b), ub.dp(x), rtol, abstol, maxit, ksp, C.byref(its))
+    return x, its.value, rc
+
+
+class OracleMesh:
+    def __init__(self, m):
+        self.m = m
+        self._d = ub.mesh_desc(m)
+        self.h = lib().orc_mesh_create(C.byref(self._d))
+        self.have_ops = False
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_mesh_destroy(self.h)
+            self.h = None
+
+    def calc_matrix_operators(self):
+        if not self.have_ops:
+            lib().orc_calc_matrix_operators(self.h)
+            self.have_ops = True
+
+    def get_operator(self, op):
+        self.calc_matrix_operators()
+        m, n, nnz = C.c_int(), C.c_int(), C.c_int()
+        lib().orc_get_operator_size(self.h, op, C.byref(m), C.byref(n), C.byref(nnz))
+        ptr = np.zeros(m.value + 1, np.int32); ind = np.zeros(nnz.value, np.int32); val = np.zeros(nnz.value)
+        lib().orc_get_operator(self.h, op, ub.ip(ptr), ub.ip(ind), ub.dp(val))
+        return ptr, ind, val, m.value, n.value
+
+    def apply_operator(self, op, x, ncols=1):
+        self.calc_matrix_operators()
+        m, n, nnz = C.c_int(), C.c_int(), C.c_int()
+        lib().orc_get_operator_size(self.h, op, C.byref(m), C.byref(n), C.byref(nnz))
+        y = np.zeros((m.value, ncols), order="F") if ncols > 1 else np.zeros(m.value)
+        lib().orc_apply_operator(self.h, op, ub.dp(x), ub.dp(y), ncols)
+        return y
+
+    def assemble(self, cfg, N_b, dN_dx_b, dN_dy_b, beta_b, tau_dx_b, tau_dy_b, BC_mask=None, BC_u=None, BC_v=None):
+        self.calc_matrix_operators()
+        m, nnz = C.c_int(), C.c_int()
+        lib().orc_assemble_SSA_DIVA(self.h, C.byref(cfg), ub.dp(N_b), ub.dp(dN_dx_b), ub.dp(dN_dy_b), ub.dp(beta_b), ub.dp(tau_dx_b),
+                                    ub.dp(tau_dy_b), ub.ip(BC_mask), ub.dp(BC_u), ub.dp(BC_v), C.byref(m), C.byref(nnz))
+        ptr = np.zeros(m.value + 1, np.int32); ind = np.zeros(nnz.value, np.int32); val = np.zeros(nnz.value); bb = np.zeros(m.value)
+        lib().orc_get_stiffness(self.h, ub.ip(ptr), ub.ip(ind), ub.dp(val), ub.dp(bb))
+        return ptr, ind, val, bb
+
+    def solve_velocity(self, cfg, approximation, ice, state, ksp=KSP_BICGSTAB_JACOBI, BC_mask=None, BC_u=None, BC_v=None, max_visc_its=-1):
+        self.calc_matrix_operators()
+        nv, na = C.c_int(), C.c_int()
+        rc = lib().orc_solve_velocity(self.h, C.byref(cfg), approximation, ksp, C.byref(ice), C.byref(state), C.byref(nv), C.byref(na),
+                                      ub.ip(BC_mask), ub.dp(BC_u), ub.dp(BC_v), max_visc_its)
+        return rc, nv.value, na.value
+
+    def calc_dHi_dt(self, cfg, io, dt, ksp=KSP_BICGSTAB_JACOBI):
+        d = C.c_double(dt)
+        its = C.c_int()
+        rc = lib().orc_calc_dHi_dt(self.h, C.byref(cfg), ksp, C.byref(io), C.cast(C.byref(d), ub.c_dp), C.byref(its))
+        return rc, d.value, its.value
+
+    def flux_divergence_matrix(self, u_b, v_b, fraction_margin):
+        m, nnz = C.c_int(), C.c_int()
+        lib().orc_flux_divergence_matrix(self.h, ub.dp(u_b), ub.dp(v_b), ub.dp(fraction_margin), C.byref(m), C.byref(nnz))
+        ptr = np.zeros(m.value + 1, np.int32); ind = np.zeros(nnz.value, np.int32); val = np.zeros(nnz.value)
+        lib().orc_get_flux_divergence_matrix(self.h, ub.ip(ptr), ub.ip(ind), ub.dp(val))
+        return ptr, ind, val

@@ -1,0 +1,307 @@
+"""ctypes binding of libufe_b200.so (include/ufe_b200.h) for tests, bench.py and smoke().
+
+This is plumbing only: every call goes straight through the C ABI the Fortran shim binds
+(ufemism2.0_b200/fortran/ufe_b200_mod.f90).  There is no fallback: if the CUDA library is
+missing or no device is present the calls raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libufe_b200.so")
+
+c_dp = C.POINTER(C.c_double)
+c_ip = C.POINTER(C.c_int32)
+
+# enumerations of include/ufe_b200.h
+KSP_BICGSTAB, KSP_CG = 0, 1
+PC_JACOBI, PC_NONE, PC_BJACOBI2, PC_NEUMANN = 0, 1, 2, 3
+BC_INFINITE, BC_ZERO = 0, 1
+(SLID_NO_SLIDING, SLID_WEERTMAN, SLID_COULOMB, SLID_BUDD, SLID_TSAI2015, SLID_SCHOOF2005, SLID_ZOET_IVERSON,
+ SLID_IDEALISED_SSA_ICESTREAM) = range(8)
+INTEGRATION_EXPLICIT, INTEGRATION_SEMI_IMPLICIT = 0, 1
+OPS = ["ddx_a_a", "ddy_a_a", "map_a_b", "ddx_a_b", "ddy_a_b", "map_b_a", "ddx_b_a", "ddy_b_a", "ddx_b_b", "ddy_b_b",
+       "M2_ddx_b_b", "M2_ddy_b_b", "M2_d2dx2_b_b", "M2_d2dxdy_b_b", "M2_d2dy2_b_b"]
+OP = {n: i for i, n in enumerate(OPS)}
+# (row grid, column grid) of each operator
+OP_GRIDS = {"ddx_a_a": "aa", "ddy_a_a": "aa", "map_a_b": "ba", "ddx_a_b": "ba", "ddy_a_b": "ba", "map_b_a": "ab",
+            "ddx_b_a": "ab", "ddy_b_a": "ab"}
+for _n in OPS[8:]:
+    OP_GRIDS[_n] = "bb"
+
+
+class Config(C.Structure):
+    _fields_ = [(n, C.c_double) for n in (
+        "visc_it_norm_dUV_tol", "visc_it_relax", "visc_eff_min", "vel_max", "stress_balance_PETSc_rtol",
+        "stress_balance_PETSc_abstol", "Glens_flow_law_exponent", "Glens_flow_law_epsilon_sq_0", "slid_delta_v",
+        "slid_Weertman_m", "slid_Budd_q_plastic", "slid_Budd_u_threshold", "slid_ZI_ut", "slid_ZI_p", "slid_beta_max",
+        "subgrid_friction_exponent_on_B_grid", "Hi_min", "uniform_Glens_flow_factor",
+        "refgeo_idealised_SSA_icestream_Hi", "refgeo_idealised_SSA_icestream_dhdx", "refgeo_idealised_SSA_icestream_L",
+        "refgeo_idealised_SSA_icestream_m", "dHi_semiimplicit_fs", "dHi_PETSc_rtol", "dHi_PETSc_abstol", "dt_ice_min",
+        "dt_ice_max", "ice_density", "seawater_density", "grav")] + [
+        ("visc_it_nit", C.c_int32), ("do_include_SSADIVA_crossterms", C.c_int32), ("BC_u", C.c_int32 * 4),
+        ("BC_v", C.c_int32 * 4), ("choice_sliding_law", C.c_int32), ("do_GL_subgrid_friction", C.c_int32),
+        ("choice_ice_integration_method", C.c_int32), ("BC_H", C.c_int32 * 4), ("ksp_type", C.c_int32),
+        ("pc_type", C.c_int32), ("ksp_maxit", C.c_int32), ("write_diagnostics", C.c_int32), ("reserved", C.c_int32 * 6)]
+
+
+def default_config():
+    """Reference namelist defaults (model_configuration_type_and_namelist.f90); mirrors ufe_b200_config_defaults."""
+    c = Config()
+    c.visc_it_norm_dUV_tol = 5e-5; c.visc_it_relax = 0.2; c.visc_eff_min = 1e4; c.vel_max = 5000.0
+    c.stress_balance_PETSc_rtol = 1e-7; c.stress_balance_PETSc_abstol = 1e-5
+    c.Glens_flow_law_exponent = 3.0; c.Glens_flow_law_epsilon_sq_0 = 1e-8
+    c.slid_delta_v = 1e-3; c.slid_Weertman_m = 3.0; c.slid_Budd_q_plastic = 0.3; c.slid_Budd_u_threshold = 100.0
+    c.slid_ZI_ut = 200.0; c.slid_ZI_p = 5.0; c.slid_beta_max = 1e20
+    c.subgrid_friction_exponent_on_B_grid = 2.0; c.Hi_min = 0.0; c.uniform_Glens_flow_factor = 1e-16
+    c.refgeo_idealised_SSA_icestream_Hi = 2000.0; c.refgeo_idealised_SSA_icestream_dhdx = -0.0003
+    c.refgeo_idealised_SSA_icestream_L = 150e3; c.refgeo_idealised_SSA_icestream_m = 1.0
+    c.dHi_semiimplicit_fs = 1.5; c.dHi_PETSc_rtol = 1e-8; c.dHi_PETSc_abstol = 1e-6
+    c.dt_ice_min = 0.1; c.dt_ice_max = 10.0
+    c.ice_density = 917.0; c.seawater_density = 1027.0; c.grav = 9.81
+    c.visc_it_nit = 50; c.do_include_SSADIVA_crossterms = 1
+    for k in range(4):
+        c.BC_u[k] = BC_INFINITE; c.BC_v[k] = BC_INFINITE; c.BC_H[k] = BC_ZERO
+    c.choice_sliding_law = SLID_ZOET_IVERSON; c.do_GL_subgrid_friction = 1
+    c.choice_ice_integration_method = INTEGRATION_SEMI_IMPLICIT
+    c.ksp_type = KSP_BICGSTAB; c.pc_type = PC_JACOBI; c.ksp_maxit = 2000; c.write_diagnostics = 1
+    return c
+
+
+class MeshDesc(C.Structure):
+    _fields_ = [("nV", C.c_int32), ("nTri", C.c_int32), ("nE", C.c_int32), ("nC_mem", C.c_int32), ("nz", C.c_int32),
+                ("xmin", C.c_double), ("xmax", C.c_double), ("ymin", C.c_double), ("ymax", C.c_double),
+                ("V", c_dp), ("nC", c_ip), ("C", c_ip), ("niTri", c_ip), ("iTri", c_ip), ("VBI", c_ip), ("Tri", c_ip),
+                ("TriC", c_ip), ("TriBI", c_ip), ("TriGC", c_dp), ("A", c_dp), ("Cw", c_dp), ("D_x", c_dp), ("D_y", c_dp),
+                ("D", c_dp), ("VE", c_ip), ("ETri", c_ip), ("zeta", c_dp)]
+
+
+class IceInputs(C.Structure):
+    _fields_ = [("Hi", c_dp), ("Hs", c_dp), ("A_flow", c_dp), ("fraction_gr_b", c_dp), ("till_friction_angle", c_dp),
+                ("beta_sq", c_dp), ("alpha_sq", c_dp), ("effective_pressure", c_dp), ("mask_grounded_ice", c_ip),
+                ("mask_icefree_land", c_ip)]
+
+
+VELOCITY_FIELDS = ["u_vav_b", "v_vav_b", "u_base_b", "v_base_b", "tau_bx_b", "tau_by_b", "eta_3D_b", "u_b_prev", "v_b_prev",
+                   "tau_dx_b", "tau_dy_b", "u_3D_b", "v_3D_b", "du_dx_a", "du_dy_a", "dv_dx_a", "dv_dy_a", "du_dz_3D_a",
+                   "dv_dz_3D_a", "eta_3D_a", "eta_vav_a", "N_a", "N_b", "dN_dx_b", "dN_dy_b", "F1_3D_a", "F2_3D_a", "F1_3D_b",
+                   "F2_3D_b", "basal_friction_coefficient_a", "basal_friction_coefficient_b", "beta_eff_a", "beta_eff_b"]
+# grid ('a' vertices / 'b' triangles) and whether the field has nz layers
+VELOCITY_SHAPES = {n: (("a" if n.endswith("_a") else "b"), "3D" in n) for n in VELOCITY_FIELDS}
+VELOCITY_SHAPES["u_b_prev"] = ("b", False); VELOCITY_SHAPES["v_b_prev"] = ("b", False)
+
+
+class VelocityState(C.Structure):
+    _fields_ = [(n, c_dp) for n in VELOCITY_FIELDS]
+
+
+class ThicknessIO(C.Structure):
+    _fields_ = [("Hi", c_dp), ("Hb", c_dp), ("SL", c_dp), ("u_vav_b", c_dp), ("v_vav_b", c_dp), ("SMB", c_dp), ("BMB", c_dp),
+                ("LMB", c_dp), ("fraction_margin", c_dp), ("mask_noice", c_ip), ("dHi_dt_target", c_dp),
+                ("BC_prescr_mask", c_ip), ("BC_prescr_Hi", c_dp), ("AMB", c_dp), ("dHi_dt", c_dp), ("Hi_tplusdt", c_dp),
+                ("divQ", c_dp)]
+
+
+def dp(a):
+    """double* of a contiguous float64 array (None -> NULL)."""
+    if a is None:
+        return None
+    assert a.dtype == np.float64 and (a.flags["F_CONTIGUOUS"] or a.flags["C_CONTIGUOUS"])
+    return a.ctypes.data_as(c_dp)
+
+
+def ip(a):
+    if a is None:
+        return None
+    assert a.dtype == np.int32 and (a.flags["F_CONTIGUOUS"] or a.flags["C_CONTIGUOUS"])
+    return a.ctypes.data_as(c_ip)
+
+
+def mesh_desc(m):
+    """MeshDesc pointing into a ufe_host.HostMesh (keeps no reference: keep `m` alive)."""
+    d = MeshDesc()
+    d.nV, d.nTri, d.nE, d.nC_mem, d.nz = m.nV, m.nTri, m.nE, m.nC_mem, m.nz
+    d.xmin, d.xmax, d.ymin, d.ymax = m.xmin, m.xmax, m.ymin, m.ymax
+    for n in ("V", "TriGC", "A", "Cw", "D_x", "D_y", "D", "zeta"):
+        setattr(d, n, dp(getattr(m, n)))
+    for n in ("nC", "C", "niTri", "iTri", "VBI", "Tri", "TriC", "TriBI", "VE", "ETri"):
+        setattr(d, n, ip(getattr(m, n)))
+    return d
+
+
+_LIB = None
+
+
+def lib():
+    """Load libufe_b200.so and declare prototypes. Raises if the library has not been built."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+    L = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+    H = C.c_void_p
+    L.ufe_b200_last_error.restype = C.c_char_p
+    L.ufe_b200_kernel_launches.restype = C.c_longlong
+    L.ufe_b200_kernel_launches.argtypes = [H]
+    L.ufe_b200_config_defaults.argtypes = [C.POINTER(Config)]
+    L.ufe_b200_get_unique_id.argtypes = [C.c_void_p]
+    L.ufe_b200_init.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(H)]
+    L.ufe_b200_finalize.argtypes = [H]
+    L.ufe_b200_ksp_solve.argtypes = [H, C.c_int, C.c_int, C.c_int, c_ip, c_ip, c_dp, c_dp, c_dp, C.c_double, C.c_double,
+                                     C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]
+    L.ufe_b200_csr_register.argtypes = [H] + [C.c_int] * 7 + [c_ip, c_ip, c_dp]
+    L.ufe_b200_csr_update_values.argtypes = [H, C.c_int, c_dp]
+    L.ufe_b200_spmv.argtypes = [H, C.c_int, c_dp, c_dp, C.c_int]
+    L.ufe_b200_csr_release.argtypes = [H, C.c_int]
+    L.ufe_b200_mesh_create.argtypes = [H, C.POINTER(MeshDesc)]
+    L.ufe_b200_mesh_destroy.argtypes = [H]
+    L.ufe_b200_mesh_ranges.argtypes = [H, c_ip]
+    L.ufe_b200_calc_matrix_operators.argtypes = [H]
+    L.ufe_b200_set_operator.argtypes = [H, C.c_int, C.c_int, c_ip, c_ip, c_dp]
+    L.ufe_b200_get_operator_size.argtypes = [H, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.ufe_b200_get_operator.argtypes = [H, C.c_int, c_ip, c_ip, c_dp]
+    L.ufe_b200_apply_operator.argtypes = [H, C.c_int, c_dp, c_dp, C.c_int]
+    L.ufe_b200_solve_SSA_DIVA_linearised.argtypes = [H, C.POINTER(Config)] + [c_dp] * 10 + [C.c_double, C.c_double,
+                                                     C.POINTER(C.c_int), c_ip, c_dp, c_dp]
+    L.ufe_b200_get_stiffness_size.argtypes = [H, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.ufe_b200_get_stiffness.argtypes = [H, c_ip, c_ip, c_dp, c_dp]
+    for fn in (L.ufe_b200_solve_DIVA, L.ufe_b200_solve_SSA):
+        fn.argtypes = [H, C.POINTER(Config), C.POINTER(IceInputs), C.POINTER(VelocityState), C.POINTER(C.c_int),
+                       C.POINTER(C.c_int), c_ip, c_dp, c_dp]
+    L.ufe_b200_velocity_upload.argtypes = [H, C.POINTER(IceInputs), C.POINTER(VelocityState)]
+    L.ufe_b200_velocity_solve_resident.argtypes = [H, C.POINTER(Config), C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.ufe_b200_velocity_download.argtypes = [H, C.POINTER(VelocityState)]
+    L.ufe_b200_calc_dHi_dt.argtypes = [H, C.POINTER(Config), C.POINTER(ThicknessIO), c_dp, C.c_int, C.POINTER(C.c_int)]
+    L.ufe_b200_dHi_dt_finish.argtypes = [H, c_dp, c_dp, C.c_double, c_dp, c_dp]
+    L.ufe_b200_solve_SIA.argtypes = [H, C.POINTER(Config), c_dp, c_dp, c_dp, c_dp, c_dp]
+    L.ufe_b200_timing_enable.argtypes = [H, C.c_int]
+    L.ufe_b200_timing_get.argtypes = [H, C.c_char_p, c_dp, C.POINTER(C.c_longlong)]
+    L.ufe_b200_timing_reset.argtypes = [H]
+    _LIB = L
+    return L
+
+
+ABI_SYMBOLS = [
+    "ufe_b200_config_defaults", "ufe_b200_get_unique_id", "ufe_b200_init", "ufe_b200_finalize", "ufe_b200_last_error",
+    "ufe_b200_kernel_launches", "ufe_b200_ksp_solve", "ufe_b200_csr_register", "ufe_b200_csr_update_values", "ufe_b200_spmv",
+    "ufe_b200_csr_release", "ufe_b200_mesh_create", "ufe_b200_mesh_destroy", "ufe_b200_mesh_ranges",
+    "ufe_b200_calc_matrix_operators", "ufe_b200_set_operator", "ufe_b200_get_operator_size", "ufe_b200_get_operator",
+    "ufe_b200_apply_operator", "ufe_b200_solve_SSA_DIVA_linearised", "ufe_b200_get_stiffness_size", "ufe_b200_get_stiffness",
+    "ufe_b200_solve_DIVA", "ufe_b200_solve_SSA", "ufe_b200_velocity_upload", "ufe_b200_velocity_solve_resident",
+    "ufe_b200_velocity_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA",
+    "ufe_b200_timing_enable", "ufe_b200_timing_get", "ufe_b200_timing_reset"]
+
+
+class UfeError(RuntimeError):
+    pass
+
+
+def check(rc):
+    if rc != 0:
+        raise UfeError(f"ufe_b200 error {rc}: {lib().ufe_b200_last_error().decode(errors='replace')}")
+
+
+class Context:
+    """One rank <-> one GPU (ufe_b200_init / ufe_b200_finalize)."""
+
+    def __init__(self, device=-1, rank=0, nranks=1, unique_id=None):
+        L = lib()
+        self.h = C.c_void_p()
+        buf = None
+        if unique_id is not None:
+            buf = C.create_string_buffer(bytes(unique_id), 128)
+        check(L.ufe_b200_init(device, rank, nranks, buf, C.byref(self.h)))
+        self.rank, self.nranks = rank, nranks
+        self._keep = []
+
+    @staticmethod
+    def unique_id():
+        buf = C.create_string_buffer(128)
+        check(lib().ufe_b200_get_unique_id(buf))
+        return buf.raw
+
+    def close(self):
+        if self.h:
+            lib().ufe_b200_finalize(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- narrow seam
+    def ksp_solve(self, m_glob, i1, ptr, ind, val, b, rtol, abstol, maxit=2000, ksp=KSP_BICGSTAB, pc=PC_JACOBI):
+        m_loc = len(ptr) - 1
+        x = np.zeros(m_loc)
+        its = C.c_int()
+        check(lib().ufe_b200_ksp_solve(self.h, m_glob, m_loc, i1, ip(ptr), ip(ind), dp(val), dp(b), dp(x), rtol, abstol, maxit,
+                                       ksp, pc, C.byref(its)))
+        return x, its.value
+
+    def csr_register(self, id_, m_glob, n_glob, i1, n_loc, j1, ptr, ind, val):
+        check(lib().ufe_b200_csr_register(self.h, id_, m_glob, n_glob, len(ptr) - 1, i1, n_loc, j1, ip(ptr), ip(ind), dp(val)))
+
+    def spmv(self, id_, x, m_loc, ncols=1):
+        y = np.zeros((m_loc, ncols), order="F") if ncols > 1 else np.zeros(m_loc)
+        check(lib().ufe_b200_spmv(self.h, id_, dp(x), dp(y), ncols))
+        return y
+
+    # -- mesh
+    def mesh_create(self, m):
+        self._keep.append(m)
+        d = mesh_desc(m)
+        check(lib().ufe_b200_mesh_create(self.h, C.byref(d)))
+        r = np.zeros(6, dtype=np.int32)
+        check(lib().ufe_b200_mesh_ranges(self.h, ip(r)))
+        self.vi1, self.vi2, self.ti1, self.ti2, self.ei1, self.ei2 = [int(v) for v in r]
+        self.nz = m.nz
+
+    def calc_matrix_operators(self):
+        check(lib().ufe_b200_calc_matrix_operators(self.h))
+
+    def get_operator(self, op):
+        m, nnz = C.c_int(), C.c_int()
+        check(lib().ufe_b200_get_operator_size(self.h, op, C.byref(m), C.byref(nnz)))
+        ptr = np.zeros(m.value + 1, np.int32); ind = np.zeros(nnz.value, np.int32); val = np.zeros(nnz.value)
+        check(lib().ufe_b200_get_operator(self.h, op, ip(ptr), ip(ind), dp(val)))
+        return ptr, ind, val
+
+    def apply_operator(self, op, x, m_loc, ncols=1):
+        y = np.zeros((m_loc, ncols), order="F") if ncols > 1 else np.zeros(m_loc)
+        check(lib().ufe_b200_apply_operator(self.h, op, dp(x), dp(y), ncols))
+        return y
+
+    def get_stiffness(self):
+        m, nnz = C.c_int(), C.c_int()
+        check(lib().ufe_b200_get_stiffness_size(self.h, C.byref(m), C.byref(nnz)))
+        ptr = np.zeros(m.value + 1, np.int32); ind = np.zeros(nnz.value, np.int32); val = np.zeros(nnz.value); bb = np.zeros(m.value)
+        check(lib().ufe_b200_get_stiffness(self.h, ip(ptr), ip(ind), dp(val), dp(bb)))
+        return ptr, ind, val, bb
+
+    def timing(self, cls):
+        ms, n = C.c_double(), C.c_longlong()
+        check(lib().ufe_b200_timing_get(self.h, cls.encode(), C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def kernel_launches(self):
+        return int(lib().ufe_b200_kernel_launches(self.h))
+
+
+def alloc_velocity_state(n_a, n_b, nz, fields=None):
+    """numpy-backed VelocityState; returns (struct, dict of arrays)."""
+    st = VelocityState()
+    arrs = {}
+    for n in VELOCITY_FIELDS:
+        if fields is not None and n not in fields:
+            continue
+        grid, is3d = VELOCITY_SHAPES[n]
+        nloc = n_a if grid == "a" else n_b
+        a = np.zeros((nloc, nz), order="F") if is3d else np.zeros(nloc)
+        arrs[n] = a
+        setattr(st, n, dp(a))
+    return st, arrs
