@@ -1,0 +1,38 @@
+"""Transcribes the reference's text known-answer vectors into golden.json (run once in the build container;
+reads only /root/reference text files to cross-check the transcription where possible)."""
+import json
+import os
+import re
+
+G = {
+    "csr6": {  # ut_petsc.f90:83-149 (both ranks' rows concatenated)
+        "m": 6, "n": 6, "ptr": [1, 2, 4, 6, 8, 9, 11], "ind": [1, 1, 2, 2, 4, 4, 5, 5, 5, 6],
+        "val": [1, 2, 3, 4, 5, 6, 7, 8, 9, 10], "x": [1, 2, 3, 4, 5, 6], "y": [1, 8, 28, 59, 40, 105]},
+    "csr7_1": {  # ut_mpi_CSR_matrix_vector_multiplication.f90:186-246
+        "m": 7, "n": 7, "ptr": [1, 2, 4, 6, 9, 11, 13, 15], "ind": [1, 2, 3, 2, 5, 3, 4, 6, 4, 5, 5, 7, 6, 7],
+        "val": [1, 2, 3, 4, 1, 2, 3, 4, 1, 2, 3, 4, 1, 2], "x": [1, 2, 3, 4, 1, 2, 3], "y": [1, 13, 9, 26, 6, 15, 8]},
+    "csr7_2": {  # ut_mpi_CSR_matrix_vector_multiplication.f90:248-318
+        "m": 7, "n": 7, "ptr": [1, 3, 6, 8, 13, 16, 19, 22],
+        "ind": [1, 5, 2, 3, 6, 2, 5, 1, 3, 4, 6, 7, 2, 4, 5, 1, 5, 7, 2, 6, 7],
+        "val": [1, 5, 2, 3, 6, 4, 1, 5, 2, 3, 4, 5, 6, 1, 2, 5, 3, 4, 6, 1, 2], "x": [1, 2, 3, 4, 1, 2, 3],
+        "y": [6, 25, 9, 46, 18, 20, 20]},
+    "partition_100_4": {"vi1": [1, 26, 51, 76], "vi2": [25, 50, 75, 100]},  # mesh_parallelisation.f90:3-36
+    "dummy5": {  # mesh_dummy_meshes.f90:67-100
+        "C": [[2, 5, 4, 0], [3, 5, 1, 0], [4, 5, 2, 0], [1, 5, 3, 0], [1, 2, 3, 4]],
+        "iTri": [[1, 4, 0, 0], [2, 1, 0, 0], [3, 2, 0, 0], [4, 3, 0, 0], [1, 2, 3, 4]],
+        "TriC": [[2, 4, 0], [3, 1, 0], [4, 2, 0], [1, 3, 0]], "nC": [3, 3, 3, 3, 4], "niTri": [2, 2, 2, 2, 4],
+        "VBI": [6, 4, 2, 8, 0]},
+    "mismip_mod_small": {"nV": 1022},
+}
+
+ref = "/root/reference/automated_testing/UFEMISM/integrated_test_MISMIP_mod_small/reference/checksum_logfile.txt"
+if os.path.exists(ref):
+    txt = open(ref).read().splitlines()
+    G["mismip_mod_small"]["petsc_version_line"] = next((l.strip() for l in txt[:12] if "PETSc" in l), "")
+    for l in txt[:200]:
+        mm = re.match(r"\s*(mask_grounded_ice|mask_floating_ice|mask_icefree_land|mask_icefree_ocean)\s*:\s*(.*)", l)
+        if mm and mm.group(1) not in G["mismip_mod_small"]:
+            G["mismip_mod_small"][mm.group(1)] = mm.group(2).strip()
+
+json.dump(G, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden.json"), "w"), indent=1)
+print("wrote golden.json")

@@ -1,0 +1,141 @@
+// Shared declarations of libufe_b200.so (sm_100a only; no CPU fallback anywhere in this directory).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/ufe_b200.h"
+
+namespace ufe {
+
+// ---- errors ------------------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+const char* get_error();
+
+#define UFE_CUDA(call)                                                                              \
+  do {                                                                                              \
+    cudaError_t e__ = (call);                                                                       \
+    if (e__ != cudaSuccess) {                                                                       \
+      ufe::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__));        \
+      return 1;                                                                                     \
+    }                                                                                               \
+  } while (0)
+
+#define UFE_CHECK(cond, ...)                                                                        \
+  do {                                                                                              \
+    if (!(cond)) { ufe::set_error(__VA_ARGS__); return 2; }                                         \
+  } while (0)
+
+#define UFE_TRY(expr)                                                                               \
+  do { int rc__ = (expr); if (rc__ != 0) return rc__; } while (0)
+
+// ---- device buffers ------------------------------------------------------------------------------
+template <typename T>
+struct DBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  int alloc(size_t count) {
+    if (count <= n && p) return 0;
+    release();
+    if (count == 0) return 0;
+    cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
+    if (e != cudaSuccess) { set_error("cudaMalloc(%zu bytes) failed: %s", count * sizeof(T), cudaGetErrorString(e)); p = nullptr; return 1; }
+    n = count;
+    return 0;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+  ~DBuf() { release(); }
+  DBuf() = default;
+  DBuf(const DBuf&) = delete;
+  DBuf& operator=(const DBuf&) = delete;
+  DBuf(DBuf&& o) noexcept : p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+  DBuf& operator=(DBuf&& o) noexcept { if (this != &o) { release(); p = o.p; n = o.n; o.p = nullptr; o.n = 0; } return *this; }
+};
+
+// ---- index ranges ---------------------------------------------------------------------------------
+// One grid (a = vertices, b = triangles, c = edges, buv = interleaved triangle u/v) on one rank.
+// Owned global indices i1..i2 (1-based); device vectors cover the extended range lo..hi (owned + halos),
+// element g lives at [g - lo].
+struct Range {
+  int n_glob = 0, i1 = 1, i2 = 0, lo = 1, hi = 0;
+  int send_l = 0, send_r = 0;  // how many of my first / last owned elements the left / right neighbour's halo needs
+  int n_loc() const { return i2 - i1 + 1; }
+  int n_ext() const { return hi - lo + 1; }
+  int off() const { return i1 - lo; }  // position of the first owned element in an extended vector
+};
+
+// ---- CSR matrix on the device -----------------------------------------------------------------------
+// Rows = the rank's owned rows (local 0..m_loc-1); ptr 0-based; ind = 0-based position in the *extended*
+// column vector (global column - col.lo).  The reference's construction order of entries is preserved.
+struct DevCsr {
+  int m_loc = 0;
+  long long nnz = 0;
+  Range rows, cols;
+  int* ptr = nullptr;  // [m_loc+1]   (may alias another matrix of the same operator group)
+  int* ind = nullptr;  // [nnz]
+  double* val = nullptr;
+  DBuf<int> ptr_buf, ind_buf;   // owning storage (empty when the pattern is shared)
+  DBuf<double> val_buf;
+  int vec_width = 4;   // lanes per row of the vector-per-row kernel (1,2,4,8,16,32)
+  bool valid = false;
+};
+
+// ---- timing classes ----------------------------------------------------------------------------------
+enum TimingClass { TC_SPMV_STIFFNESS = 0, TC_KRYLOV_VEC, TC_ASSEMBLY, TC_COLUMN, TC_TRI, TC_EPILOGUE, TC_THICKNESS, TC_OPERATOR_SPMV, TC_COUNT };
+const char* timing_class_name(int c);
+
+struct Mesh;      // mesh.cuh
+struct Velocity;  // velocity.cuh
+struct Krylov;    // krylov.cuh
+struct Thickness; // thickness.cuh
+
+struct Ctx {
+  int device = 0, rank = 0, nranks = 1;
+  cudaStream_t stream = nullptr;
+  void* nccl = nullptr;             // ncclComm_t when nranks > 1
+  long long launches = 0;
+  int sm_count = 148;
+  // timing
+  bool timing = false;
+  struct Ev { cudaEvent_t a, b; int cls; };
+  std::vector<Ev> ev_pool; size_t ev_used = 0;
+  double tc_ms[TC_COUNT] = {0}; long long tc_n[TC_COUNT] = {0};
+  // registered generic matrices (narrow seam)
+  std::map<int, DevCsr*> csr;
+  Mesh* mesh = nullptr;
+  Velocity* vel = nullptr;
+  Krylov* krylov = nullptr;
+  Thickness* thick = nullptr;
+  // pinned scratch for small D2H reads
+  double* h_pinned = nullptr;       // 64 doubles
+};
+
+// Launch bookkeeping: every kernel launch of the library goes through one of these.
+struct LaunchTimer {
+  Ctx* c; int cls; int idx = -1;
+  LaunchTimer(Ctx* c_, int cls_);
+  ~LaunchTimer();
+};
+#define UFE_LAUNCH(ctx, cls) ufe::LaunchTimer lt__((ctx), (cls))
+void timing_collect(Ctx* c);
+
+inline int grid_for(const Ctx* c, long long n, int block, int max_waves = 8) {
+  long long g = (n + block - 1) / block;
+  long long cap = (long long)c->sm_count * max_waves;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+// halo exchange of an extended vector (no-op on one rank); ncols vectors of stride r.n_ext()
+int halo_exchange(Ctx* c, const Range& r, double* v, int ncols = 1, int elems_per_index = 1);
+int allreduce_sum(Ctx* c, double* d_vals, int n);
+int allreduce_min(Ctx* c, double* d_vals, int n);
+
+}  // namespace ufe

@@ -1,0 +1,259 @@
+// Narrow seam: generic distributed CSR on the device (a1-a4, a14 of SURVEY 8a).
+//   type_sparse_matrix_CSR_dp                      src/UPSY/basic/CSR_sparse_matrix_type.f90:15-38
+//   multiply_CSR_matrix_with_vector_{1D,2D}         src/UPSY/basic/CSR_matrix_algebra/CSR_matrix_vector_multiplication.f90:199-365
+//   solve_matrix_equation_CSR_PETSc                 src/UPSY/basic/petsc_basic.f90:32-215
+#include "nccl_dl.cuh"
+
+#include <algorithm>
+
+#include "csr.cuh"
+#include "krylov_impl.cuh"
+
+namespace ufe {
+
+// Exchange (lo, hi, i1, i2) with the neighbours and derive what they need from me.
+int setup_range_halos(Ctx* c, Range& r) {
+  r.send_l = r.send_r = 0;
+  if (c->nranks == 1) return 0;
+  DBuf<int> d_all;
+  UFE_TRY(d_all.alloc((size_t)4 * c->nranks));
+  int mine[4] = {r.lo, r.hi, r.i1, r.i2};
+  UFE_CUDA(cudaMemcpyAsync(d_all.p + 4 * c->rank, mine, sizeof(mine), cudaMemcpyHostToDevice, c->stream));
+  NcclApi* N = nccl_api();
+  if (!N) return 3;
+  ncclResult_t rc = N->AllGather(d_all.p + 4 * c->rank, d_all.p, 4, ncclInt32, (ncclComm_t)c->nccl, c->stream);
+  UFE_CHECK(rc == ncclSuccess, "ncclAllGather: %s", N->GetErrorString(rc));
+  std::vector<int> all((size_t)4 * c->nranks);
+  UFE_CUDA(cudaMemcpyAsync(all.data(), d_all.p, sizeof(int) * all.size(), cudaMemcpyDeviceToHost, c->stream));
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  if (c->rank > 0) {
+    const int* L = &all[4 * (c->rank - 1)];
+    UFE_CHECK(r.lo >= L[2], "halo of rank %d reaches beyond its left neighbour (needs %d, neighbour owns from %d): too many ranks for this mesh",
+              c->rank, r.lo, L[2]);
+    r.send_l = std::max(0, L[1] - r.i1 + 1);
+    UFE_CHECK(r.send_l <= r.n_loc(), "left neighbour's halo is wider than the owned range of rank %d", c->rank);
+  } else {
+    UFE_CHECK(r.lo == r.i1 || r.lo >= 1, "bad extended range");
+  }
+  if (c->rank < c->nranks - 1) {
+    const int* Rn = &all[4 * (c->rank + 1)];
+    UFE_CHECK(r.hi <= Rn[3], "halo of rank %d reaches beyond its right neighbour: too many ranks for this mesh", c->rank);
+    r.send_r = std::max(0, r.i2 - Rn[0] + 1);
+    UFE_CHECK(r.send_r <= r.n_loc(), "right neighbour's halo is wider than the owned range of rank %d", c->rank);
+  }
+  return 0;
+}
+
+__global__ void k_csr_find_diag(int m, int row_glob0, int col_lo, const int* __restrict__ ptr, const int* __restrict__ ind,
+                                int* __restrict__ diag) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += (long long)gridDim.x * blockDim.x) {
+    const int target = row_glob0 + (int)r - col_lo;  // extended-column position of the diagonal
+    int d = -1;
+    for (int k = ptr[r]; k < ptr[r + 1]; ++k) if (ind[k] == target) { d = k; break; }
+    diag[r] = d;
+  }
+}
+
+// inverse of the (summed) diagonal; zero diagonal -> 1 (PCJacobi behaviour)
+__global__ void k_csr_dinv(int m, int row_glob0, int col_lo, const int* __restrict__ ptr, const int* __restrict__ ind,
+                           const double* __restrict__ val, double* __restrict__ dinv, int pc_none) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += (long long)gridDim.x * blockDim.x) {
+    if (pc_none) { dinv[r] = 1.0; continue; }
+    const int target = row_glob0 + (int)r - col_lo;
+    double d = 0.0;
+    for (int k = ptr[r]; k < ptr[r + 1]; ++k) if (ind[k] == target) d += val[k];
+    dinv[r] = (d != 0.0) ? 1.0 / d : 1.0;
+  }
+}
+
+// Upload rows i1..i1+m_loc-1 given in the reference's layout (1-based relative offsets, 1-based global columns).
+int csr_upload(Ctx* c, DevCsr& A, int m_glob, int n_glob, int m_loc, int i1, int n_loc, int j1, const int32_t* ptr,
+               const int32_t* ind, const double* val, bool square, const Range* force_cols) {
+  UFE_CHECK(m_loc >= 0 && ptr && (m_loc == 0 || (ind && val)), "csr_upload: NULL arrays");
+  const long long nnz = (m_loc > 0) ? (long long)ptr[m_loc] - ptr[0] : 0;
+  UFE_CHECK(nnz >= 0, "csr_upload: ptr is not ascending");
+  A.m_loc = m_loc; A.nnz = nnz;
+  A.rows.n_glob = m_glob; A.rows.i1 = i1; A.rows.i2 = i1 + m_loc - 1; A.rows.lo = i1; A.rows.hi = i1 + m_loc - 1;
+  A.cols.n_glob = n_glob; A.cols.i1 = j1; A.cols.i2 = j1 + n_loc - 1;
+  int jmin = j1, jmax = j1 + n_loc - 1;
+  for (long long k = 0; k < nnz; ++k) {
+    const int j = ind[k];
+    UFE_CHECK(j >= 1 && j <= n_glob, "csr_upload: column index %d out of range 1..%d", j, n_glob);
+    jmin = std::min(jmin, j); jmax = std::max(jmax, j);
+  }
+  if (c->nranks == 1) UFE_CHECK(jmin >= j1 && jmax <= j1 + n_loc - 1, "csr_upload: on one rank every column must lie in the owned x range");
+  if (force_cols) {
+    UFE_CHECK(jmin >= force_cols->lo && jmax <= force_cols->hi, "csr_upload: columns %d..%d outside the extended range %d..%d", jmin, jmax,
+              force_cols->lo, force_cols->hi);
+    A.cols = *force_cols;
+  } else {
+    A.cols.lo = jmin; A.cols.hi = jmax;
+    UFE_TRY(setup_range_halos(c, A.cols));
+  }
+  std::vector<int> p0((size_t)m_loc + 1), i0((size_t)nnz);
+  for (int r = 0; r <= m_loc; ++r) p0[r] = ptr[r] - ptr[0];
+  for (long long k = 0; k < nnz; ++k) i0[k] = ind[k] - A.cols.lo;
+  UFE_TRY(A.ptr_buf.alloc(m_loc + 1)); UFE_TRY(A.ind_buf.alloc(nnz)); UFE_TRY(A.val_buf.alloc(nnz));
+  A.ptr = A.ptr_buf.p; A.ind = A.ind_buf.p; A.val = A.val_buf.p;
+  UFE_CUDA(cudaMemcpyAsync(A.ptr, p0.data(), sizeof(int) * p0.size(), cudaMemcpyHostToDevice, c->stream));
+  if (nnz) {
+    UFE_CUDA(cudaMemcpyAsync(A.ind, i0.data(), sizeof(int) * nnz, cudaMemcpyHostToDevice, c->stream));
+    UFE_CUDA(cudaMemcpyAsync(A.val, val, sizeof(double) * nnz, cudaMemcpyHostToDevice, c->stream));
+  }
+  UFE_CUDA(cudaStreamSynchronize(c->stream));  // p0/i0 go out of scope
+  const double avg = m_loc > 0 ? (double)nnz / m_loc : 0.0;
+  A.vec_width = avg <= 2.5 ? 2 : avg <= 6.0 ? 4 : avg <= 14.0 ? 8 : avg <= 48.0 ? 16 : 32;
+  (void)square;
+  A.valid = true;
+  return 0;
+}
+
+template <int W>
+static void launch_spmv_plain(Ctx* c, const DevCsr& A, const double* x_ext, double* y, int tc) {
+  CsrOp<W> op{A.ptr, A.ind, A.val};
+  UFE_LAUNCH(c, tc);
+  k_spmv_fused<CsrOp<W>, 0><<<grid_for(c, (long long)A.m_loc * W, kBlock), kBlock, 0, c->stream>>>(
+      op, A.m_loc, 0, 0, x_ext, nullptr, y, nullptr, nullptr, nullptr, nullptr, nullptr);
+}
+
+int csr_spmv(Ctx* c, const DevCsr& A, const double* x_ext, double* y, int tc) {
+  if (A.m_loc == 0) return 0;
+  switch (A.vec_width) {
+    case 2: launch_spmv_plain<2>(c, A, x_ext, y, tc); break;
+    case 4: launch_spmv_plain<4>(c, A, x_ext, y, tc); break;
+    case 8: launch_spmv_plain<8>(c, A, x_ext, y, tc); break;
+    case 16: launch_spmv_plain<16>(c, A, x_ext, y, tc); break;
+    default: launch_spmv_plain<32>(c, A, x_ext, y, tc); break;
+  }
+  UFE_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// multi-column product: thread per row keeps the row in registers and streams the ncols right-hand sides
+// (K2 of SURVEY 2e: the matrix is read once instead of nz times as in CSR_matrix_vector_multiplication.f90:356-360)
+__global__ void k_spmv_multicol(int m, int n_ext, int ncols, const int* __restrict__ ptr, const int* __restrict__ ind,
+                                const double* __restrict__ val, const double* __restrict__ x, double* __restrict__ y) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += (long long)gridDim.x * blockDim.x) {
+    const int k1 = ptr[r], k2 = ptr[r + 1];
+    for (int c0 = 0; c0 < ncols; ++c0) {
+      const double* xc = x + (size_t)c0 * n_ext;
+      double s = 0.0;
+      for (int k = k1; k < k2; ++k) s += val[k] * xc[ind[k]];
+      y[(size_t)c0 * m + r] = s;
+    }
+  }
+}
+
+int csr_spmv_multicol(Ctx* c, const DevCsr& A, const double* x_ext, double* y, int ncols, int tc) {
+  if (ncols == 1) return csr_spmv(c, A, x_ext, y, tc);
+  if (A.m_loc == 0) return 0;
+  UFE_LAUNCH(c, tc);
+  k_spmv_multicol<<<grid_for(c, A.m_loc, kBlock), kBlock, 0, c->stream>>>(A.m_loc, A.cols.n_ext(), ncols, A.ptr, A.ind,
+                                                                         A.val, x_ext, y);
+  UFE_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int csr_make_dinv(Ctx* c, const DevCsr& A, double* dinv, int pc_type) {
+  UFE_LAUNCH(c, TC_KRYLOV_VEC);
+  k_csr_dinv<<<grid_for(c, A.m_loc, kBlock), kBlock, 0, c->stream>>>(A.m_loc, A.rows.i1, A.cols.lo, A.ptr, A.ind, A.val,
+                                                                    dinv, pc_type == UFE_PC_NONE ? 1 : 0);
+  UFE_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int csr_ksp_solve(Ctx* c, const DevCsr& A, const double* d_b, double* d_x_ext, const KrylovParams& kp, int tc, int* its) {
+  UFE_CHECK(kp.ksp_type == UFE_KSP_BICGSTAB, "only BiCGStab is available for general (non-symmetric) matrices");
+  UFE_CHECK(kp.pc_type == UFE_PC_JACOBI || kp.pc_type == UFE_PC_NONE, "generic CSR solve supports pc = jacobi | none");
+  if (!c->krylov) c->krylov = new Krylov();
+  UFE_TRY(c->krylov->dinv.alloc(A.m_loc));
+  UFE_TRY(csr_make_dinv(c, A, c->krylov->dinv.p, kp.pc_type));
+  const double* dinv = c->krylov->dinv.p;
+  switch (A.vec_width) {
+    case 2: return bicgstab_solve(c, CsrOp<2>{A.ptr, A.ind, A.val}, A.cols, d_b, dinv, d_x_ext, kp, tc, its);
+    case 4: return bicgstab_solve(c, CsrOp<4>{A.ptr, A.ind, A.val}, A.cols, d_b, dinv, d_x_ext, kp, tc, its);
+    case 8: return bicgstab_solve(c, CsrOp<8>{A.ptr, A.ind, A.val}, A.cols, d_b, dinv, d_x_ext, kp, tc, its);
+    case 16: return bicgstab_solve(c, CsrOp<16>{A.ptr, A.ind, A.val}, A.cols, d_b, dinv, d_x_ext, kp, tc, its);
+    default: return bicgstab_solve(c, CsrOp<32>{A.ptr, A.ind, A.val}, A.cols, d_b, dinv, d_x_ext, kp, tc, its);
+  }
+}
+
+}  // namespace ufe
+
+using namespace ufe;
+
+extern "C" {
+
+int ufe_b200_ksp_solve(ufe_b200_handle h, int m_glob, int m_loc, int i1, const int32_t* ptr, const int32_t* ind,
+                       const double* val, const double* bb, double* xx, double rtol, double abstol, int maxit, int ksp_type,
+                       int pc_type, int* n_Axb_its) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c, "NULL handle");
+  UFE_CUDA(cudaSetDevice(c->device));
+  DevCsr A;
+  UFE_TRY(csr_upload(c, A, m_glob, m_glob, m_loc, i1, m_loc, i1, ptr, ind, val, true));
+  DBuf<double> b, x;
+  UFE_TRY(b.alloc(m_loc)); UFE_TRY(x.alloc(A.cols.n_ext()));
+  UFE_CUDA(cudaMemcpyAsync(b.p, bb, sizeof(double) * m_loc, cudaMemcpyHostToDevice, c->stream));
+  UFE_CUDA(cudaMemsetAsync(x.p, 0, sizeof(double) * A.cols.n_ext(), c->stream));
+  KrylovParams kp{rtol, abstol, maxit, ksp_type, pc_type};
+  int its = 0;
+  UFE_TRY(csr_ksp_solve(c, A, b.p, x.p, kp, TC_SPMV_STIFFNESS, &its));
+  UFE_CUDA(cudaMemcpyAsync(xx, x.p + A.cols.off(), sizeof(double) * m_loc, cudaMemcpyDeviceToHost, c->stream));
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  if (n_Axb_its) *n_Axb_its = its;
+  return 0;
+}
+
+int ufe_b200_csr_register(ufe_b200_handle h, int id, int m_glob, int n_glob, int m_loc, int i1, int n_loc, int j1,
+                          const int32_t* ptr, const int32_t* ind, const double* val) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c, "NULL handle");
+  UFE_CUDA(cudaSetDevice(c->device));
+  auto it = c->csr.find(id);
+  if (it != c->csr.end()) { delete it->second; c->csr.erase(it); }
+  DevCsr* A = new DevCsr();
+  int rc = csr_upload(c, *A, m_glob, n_glob, m_loc, i1, n_loc, j1, ptr, ind, val, false);
+  if (rc) { delete A; return rc; }
+  c->csr[id] = A;
+  return 0;
+}
+
+int ufe_b200_csr_update_values(ufe_b200_handle h, int id, const double* val) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  auto it = c->csr.find(id);
+  UFE_CHECK(it != c->csr.end(), "ufe_b200_csr_update_values: matrix %d is not registered", id);
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_CUDA(cudaMemcpyAsync(it->second->val, val, sizeof(double) * it->second->nnz, cudaMemcpyHostToDevice, c->stream));
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int ufe_b200_spmv(ufe_b200_handle h, int id, const double* xx, double* yy, int ncols) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  auto it = c->csr.find(id);
+  UFE_CHECK(it != c->csr.end(), "ufe_b200_spmv: matrix %d is not registered", id);
+  UFE_CHECK(ncols >= 1, "ufe_b200_spmv: ncols must be >= 1");
+  UFE_CUDA(cudaSetDevice(c->device));
+  DevCsr& A = *it->second;
+  const int n_loc = A.cols.n_loc(), n_ext = A.cols.n_ext();
+  DBuf<double> x, y;
+  UFE_TRY(x.alloc((size_t)n_ext * ncols)); UFE_TRY(y.alloc((size_t)A.m_loc * ncols));
+  if (n_ext > n_loc) UFE_CUDA(cudaMemsetAsync(x.p, 0, sizeof(double) * n_ext * ncols, c->stream));
+  UFE_CUDA(cudaMemcpy2DAsync(x.p + A.cols.off(), sizeof(double) * n_ext, xx, sizeof(double) * n_loc, sizeof(double) * n_loc, ncols,
+                             cudaMemcpyHostToDevice, c->stream));
+  UFE_TRY(halo_exchange(c, A.cols, x.p, ncols));
+  UFE_TRY(csr_spmv_multicol(c, A, x.p, y.p, ncols, TC_OPERATOR_SPMV));
+  UFE_CUDA(cudaMemcpyAsync(yy, y.p, sizeof(double) * A.m_loc * ncols, cudaMemcpyDeviceToHost, c->stream));
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int ufe_b200_csr_release(ufe_b200_handle h, int id) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  auto it = c->csr.find(id);
+  if (it != c->csr.end()) { delete it->second; c->csr.erase(it); }
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,233 @@
+// Context life cycle, error reporting, launch/timing bookkeeping, NCCL plumbing.
+// Replaces initialise_parallelisation + PetscInitialize for this path
+// (reference: src/UFEMISM/main/UFEMISM_program.f90:55-56; src/UPSY/basic/mpi_parallelisation/mpi_basic.f90:37-76).
+#include "nccl_dl.cuh"
+#include "krylov.cuh"
+#include "mesh.cuh"
+#include "thickness.cuh"
+#include "velocity.cuh"
+
+namespace ufe {
+
+NcclApi* nccl_api() {
+  static NcclApi api;
+  if (api.ok) return &api;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* n : names) {
+    api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (api.handle) break;
+  }
+  if (!api.handle) { set_error("cannot load libnccl.so.2: %s", dlerror()); return nullptr; }
+#define UFE_SYM(field, sym)                                                                    \
+  api.field = reinterpret_cast<decltype(api.field)>(dlsym(api.handle, sym));                   \
+  if (!api.field) { set_error("libnccl lacks %s", sym); return nullptr; }
+  UFE_SYM(GetUniqueId, "ncclGetUniqueId") UFE_SYM(CommInitRank, "ncclCommInitRank") UFE_SYM(CommDestroy, "ncclCommDestroy")
+  UFE_SYM(AllReduce, "ncclAllReduce") UFE_SYM(AllGather, "ncclAllGather") UFE_SYM(Send, "ncclSend") UFE_SYM(Recv, "ncclRecv")
+  UFE_SYM(GroupStart, "ncclGroupStart") UFE_SYM(GroupEnd, "ncclGroupEnd") UFE_SYM(GetErrorString, "ncclGetErrorString")
+#undef UFE_SYM
+  api.ok = true;
+  return &api;
+}
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* get_error() { return g_err; }
+
+const char* timing_class_name(int c) {
+  static const char* names[TC_COUNT] = {"spmv_stiffness", "krylov_vec", "assembly", "column", "tri", "epilogue", "thickness", "operator_spmv"};
+  return (c >= 0 && c < TC_COUNT) ? names[c] : "?";
+}
+
+LaunchTimer::LaunchTimer(Ctx* c_, int cls_) : c(c_), cls(cls_) {
+  c->launches++;
+  if (!c->timing) return;
+  if (c->ev_used == c->ev_pool.size()) {
+    Ctx::Ev e;
+    cudaEventCreate(&e.a);
+    cudaEventCreate(&e.b);
+    c->ev_pool.push_back(e);
+  }
+  idx = (int)c->ev_used++;
+  c->ev_pool[idx].cls = cls;
+  cudaEventRecord(c->ev_pool[idx].a, c->stream);
+}
+LaunchTimer::~LaunchTimer() {
+  if (idx >= 0) cudaEventRecord(c->ev_pool[idx].b, c->stream);
+}
+
+void timing_collect(Ctx* c) {
+  if (c->ev_used == 0) return;
+  cudaStreamSynchronize(c->stream);
+  for (size_t i = 0; i < c->ev_used; ++i) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->ev_pool[i].a, c->ev_pool[i].b) == cudaSuccess) {
+      c->tc_ms[c->ev_pool[i].cls] += ms;
+      c->tc_n[c->ev_pool[i].cls] += 1;
+    }
+  }
+  c->ev_used = 0;
+}
+
+// ---- collectives (C1/C3 of SURVEY 2e): 1-D chain halos and scalar all-reduces over NCCL -----------------
+// Reference: basic_halo_exchange (src/UPSY/basic/mpi_parallelisation/halo_exchange_mod.f90:114-137) sends the
+// interior halo to the left/right neighbour and receives the exterior halo; here the ranges come from the
+// extended range of the vector (Range::lo..hi) instead of the 1-ring node ranges.
+int halo_exchange(Ctx* c, const Range& r, double* v, int ncols, int epi) {
+  if (c->nranks == 1) return 0;
+  ncclComm_t comm = (ncclComm_t)c->nccl;
+  const size_t stride = (size_t)r.n_ext() * epi;
+  const int nl = r.i1 - r.lo, nr = r.hi - r.i2;
+  NcclApi* N = nccl_api();
+  if (!N) return 3;
+  ncclResult_t rc = N->GroupStart();
+  for (int k = 0; k < ncols && rc == ncclSuccess; ++k) {
+    double* base = v + k * stride;
+    if (c->rank > 0) {
+      if (r.send_l > 0) rc = N->Send(base + (size_t)r.off() * epi, (size_t)r.send_l * epi, ncclDouble, c->rank - 1, comm, c->stream);
+      if (nl > 0 && rc == ncclSuccess) rc = N->Recv(base, (size_t)nl * epi, ncclDouble, c->rank - 1, comm, c->stream);
+    }
+    if (c->rank < c->nranks - 1 && rc == ncclSuccess) {
+      if (r.send_r > 0) rc = N->Send(base + (size_t)(r.off() + r.n_loc() - r.send_r) * epi, (size_t)r.send_r * epi, ncclDouble, c->rank + 1, comm, c->stream);
+      if (nr > 0 && rc == ncclSuccess) rc = N->Recv(base + (size_t)(r.off() + r.n_loc()) * epi, (size_t)nr * epi, ncclDouble, c->rank + 1, comm, c->stream);
+    }
+  }
+  ncclResult_t rc2 = N->GroupEnd();
+  UFE_CHECK(rc == ncclSuccess && rc2 == ncclSuccess, "halo_exchange: %s", N->GetErrorString(rc != ncclSuccess ? rc : rc2));
+  return 0;
+}
+
+int allreduce_sum(Ctx* c, double* d, int n) {
+  if (c->nranks == 1) return 0;
+  NcclApi* N = nccl_api();
+  if (!N) return 3;
+  ncclResult_t r = N->AllReduce(d, d, n, ncclDouble, ncclSum, (ncclComm_t)c->nccl, c->stream);
+  UFE_CHECK(r == ncclSuccess, "ncclAllReduce(sum): %s", N->GetErrorString(r));
+  return 0;
+}
+int allreduce_min(Ctx* c, double* d, int n) {
+  if (c->nranks == 1) return 0;
+  NcclApi* N = nccl_api();
+  if (!N) return 3;
+  ncclResult_t r = N->AllReduce(d, d, n, ncclDouble, ncclMin, (ncclComm_t)c->nccl, c->stream);
+  UFE_CHECK(r == ncclSuccess, "ncclAllReduce(min): %s", N->GetErrorString(r));
+  return 0;
+}
+
+}  // namespace ufe
+
+using namespace ufe;
+
+extern "C" {
+
+const char* ufe_b200_last_error(void) { return get_error(); }
+
+void ufe_b200_config_defaults(ufe_b200_config* c) {
+  memset(c, 0, sizeof(*c));
+  c->visc_it_norm_dUV_tol = 5e-5; c->visc_it_relax = 0.2; c->visc_eff_min = 1e4; c->vel_max = 5000.0;
+  c->stress_balance_PETSc_rtol = 1e-7; c->stress_balance_PETSc_abstol = 1e-5;
+  c->Glens_flow_law_exponent = 3.0; c->Glens_flow_law_epsilon_sq_0 = 1e-8;
+  c->slid_delta_v = 1e-3; c->slid_Weertman_m = 3.0; c->slid_Budd_q_plastic = 0.3; c->slid_Budd_u_threshold = 100.0;
+  c->slid_ZI_ut = 200.0; c->slid_ZI_p = 5.0; c->slid_beta_max = 1e20;
+  c->subgrid_friction_exponent_on_B_grid = 2.0; c->Hi_min = 0.0; c->uniform_Glens_flow_factor = 1e-16;
+  c->refgeo_idealised_SSA_icestream_Hi = 2000.0; c->refgeo_idealised_SSA_icestream_dhdx = -0.0003;
+  c->refgeo_idealised_SSA_icestream_L = 150e3; c->refgeo_idealised_SSA_icestream_m = 1.0;
+  c->dHi_semiimplicit_fs = 1.5; c->dHi_PETSc_rtol = 1e-8; c->dHi_PETSc_abstol = 1e-6;
+  c->dt_ice_min = 0.1; c->dt_ice_max = 10.0;
+  c->ice_density = 917.0; c->seawater_density = 1027.0; c->grav = 9.81;
+  c->visc_it_nit = 50; c->do_include_SSADIVA_crossterms = 1;
+  for (int k = 0; k < 4; ++k) { c->BC_u[k] = UFE_BC_INFINITE; c->BC_v[k] = UFE_BC_INFINITE; c->BC_H[k] = UFE_BC_ZERO; }
+  c->choice_sliding_law = UFE_SLID_ZOET_IVERSON; c->do_GL_subgrid_friction = 1;
+  c->choice_ice_integration_method = UFE_INTEGRATION_SEMI_IMPLICIT;
+  c->ksp_type = UFE_KSP_BICGSTAB; c->pc_type = UFE_PC_JACOBI; c->ksp_maxit = 2000; c->write_diagnostics = 1;
+}
+
+int ufe_b200_get_unique_id(void* id128) {
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is expected to be 128 bytes");
+  NcclApi* N = nccl_api();
+  if (!N) return 3;
+  ncclUniqueId id;
+  ncclResult_t r = N->GetUniqueId(&id);
+  UFE_CHECK(r == ncclSuccess, "ncclGetUniqueId: %s", N->GetErrorString(r));
+  memcpy(id128, &id, 128);
+  return 0;
+}
+
+int ufe_b200_init(int device, int rank, int nranks, const void* id128, ufe_b200_handle* out) {
+  UFE_CHECK(out != nullptr, "ufe_b200_init: out is NULL");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  UFE_CHECK(e == cudaSuccess && ndev > 0, "ufe_b200_init: no CUDA device (%s); this library has no CPU fallback",
+            e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+  UFE_CHECK(nranks >= 1 && rank >= 0 && rank < nranks, "ufe_b200_init: bad rank %d of %d", rank, nranks);
+  if (device < 0) device = rank % ndev;
+  UFE_CUDA(cudaSetDevice(device));
+  Ctx* c = new Ctx();
+  c->device = device; c->rank = rank; c->nranks = nranks;
+  cudaDeviceProp prop;
+  UFE_CUDA(cudaGetDeviceProperties(&prop, device));
+  c->sm_count = prop.multiProcessorCount;
+  UFE_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  UFE_CUDA(cudaMallocHost((void**)&c->h_pinned, 64 * sizeof(double)));
+  if (nranks > 1) {
+    UFE_CHECK(id128 != nullptr, "ufe_b200_init: nranks > 1 needs the broadcast unique id");
+    ncclUniqueId id;
+    memcpy(&id, id128, 128);
+    NcclApi* N = nccl_api();
+    if (!N) return 3;
+    ncclComm_t comm;
+    ncclResult_t r = N->CommInitRank(&comm, nranks, id, rank);
+    UFE_CHECK(r == ncclSuccess, "ncclCommInitRank: %s", N->GetErrorString(r));
+    c->nccl = comm;
+  }
+  *out = reinterpret_cast<ufe_b200_handle>(c);
+  return 0;
+}
+
+int ufe_b200_finalize(ufe_b200_handle h) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  if (!c) return 0;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  ufe_b200_mesh_destroy(h);
+  for (auto& kv : c->csr) delete kv.second;
+  c->csr.clear();
+  delete c->krylov; c->krylov = nullptr;
+  for (auto& e : c->ev_pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+  if (c->nccl && nccl_api()) nccl_api()->CommDestroy((ncclComm_t)c->nccl);
+  if (c->h_pinned) cudaFreeHost(c->h_pinned);
+  cudaStreamDestroy(c->stream);
+  delete c;
+  return 0;
+}
+
+long long ufe_b200_kernel_launches(ufe_b200_handle h) { return reinterpret_cast<Ctx*>(h)->launches; }
+
+int ufe_b200_timing_enable(ufe_b200_handle h, int on) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  timing_collect(c);
+  c->timing = on != 0;
+  return 0;
+}
+int ufe_b200_timing_get(ufe_b200_handle h, const char* cls, double* ms, long long* n) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  timing_collect(c);
+  for (int k = 0; k < TC_COUNT; ++k)
+    if (!strcmp(cls, timing_class_name(k))) { *ms = c->tc_ms[k]; *n = c->tc_n[k]; return 0; }
+  set_error("ufe_b200_timing_get: unknown kernel class '%s'", cls);
+  return 2;
+}
+int ufe_b200_timing_reset(ufe_b200_handle h) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  timing_collect(c);
+  for (int k = 0; k < TC_COUNT; ++k) { c->tc_ms[k] = 0; c->tc_n[k] = 0; }
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,92 @@
+// Host driver of the on-device BiCGStab, templated on the matrix functor (see krylov.cuh).
+#pragma once
+#include "krylov.cuh"
+
+namespace ufe {
+
+// d_b: local right-hand side (m_loc); d_dinv: local inverse diagonal (Jacobi) or ones;
+// d_x_ext: extended solution vector, owned part at [rr.off()..]; halos are NOT refreshed on return.
+template <class Op>
+int bicgstab_solve(Ctx* c, const Op& op, const Range& rr, const double* d_b, const double* d_dinv, double* d_x_ext,
+                   const KrylovParams& kp, int tc_spmv, int* its) {
+  if (!c->krylov) c->krylov = new Krylov();
+  Krylov& K = *c->krylov;
+  const int m = rr.n_loc(), off = rr.off();
+  UFE_TRY(K.ensure(c, m, rr.n_ext()));
+  cudaStream_t st = c->stream;
+  const int gv = grid_for(c, m, kBlock);                       // vector kernels
+  const int gs = grid_for(c, (long long)m * Op::W, kBlock);    // SpMV kernels
+  double* x_own = d_x_ext + off;
+  double* P_own = K.P.p + off;
+  double* S_own = K.S.p + off;
+  if (rr.n_ext() > m) {  // halos of P/S start from zero so that a missing neighbour never injects garbage
+    UFE_CUDA(cudaMemsetAsync(K.P.p, 0, sizeof(double) * rr.n_ext(), st));
+    UFE_CUDA(cudaMemsetAsync(K.S.p, 0, sizeof(double) * rr.n_ext(), st));
+  }
+  {
+    UFE_LAUNCH(c, TC_KRYLOV_VEC);
+    k_ks_init<<<gv, kBlock, 0, st>>>(m, d_b, d_dinv, K.R.p, K.RP.p, x_own, P_own, K.V.p, K.scal.p, K.partials.p, K.counter.p,
+                                     K.flags.p, kp.rtol, kp.abstol);
+  }
+  UFE_TRY(allreduce_sum(c, K.scal.p + KS_RR0, 1));
+  {
+    UFE_LAUNCH(c, TC_KRYLOV_VEC);
+    k_ks_init_finish<<<1, 1, 0, st>>>(K.scal.p);
+  }
+  int* h_flags = reinterpret_cast<int*>(c->h_pinned);
+  int iter = 0;
+  int check_every = 8;
+  bool done = false;
+  while (!done && iter < kp.maxit) {
+    const int stop_at = (iter + check_every < kp.maxit) ? iter + check_every : kp.maxit;
+    for (; iter < stop_at; ++iter) {
+      const int p = iter & 1;
+      {
+        UFE_LAUNCH(c, TC_KRYLOV_VEC);
+        k_ks_update_p<<<gv, kBlock, 0, st>>>(m, iter, K.R.p, K.V.p, P_own, K.scal.p, K.flags.p);
+      }
+      UFE_TRY(halo_exchange(c, rr, K.P.p));
+      {
+        UFE_LAUNCH(c, tc_spmv);
+        k_spmv_fused<Op, 1><<<gs, kBlock, 0, st>>>(op, m, off, iter, K.P.p, d_dinv, K.V.p, K.RP.p, K.scal.p, K.partials.p,
+                                                   K.counter.p + 1, K.flags.p);
+      }
+      UFE_TRY(allreduce_sum(c, K.scal.p + p * KS_BANK + KS_D1, 1));
+      {
+        UFE_LAUNCH(c, TC_KRYLOV_VEC);
+        k_ks_update_s<<<gv, kBlock, 0, st>>>(m, iter, K.R.p, K.V.p, S_own, K.scal.p, K.flags.p);
+      }
+      UFE_TRY(halo_exchange(c, rr, K.S.p));
+      {
+        UFE_LAUNCH(c, tc_spmv);
+        k_spmv_fused<Op, 2><<<gs, kBlock, 0, st>>>(op, m, off, iter, K.S.p, d_dinv, K.T.p, nullptr, K.scal.p, K.partials.p,
+                                                   K.counter.p + 2, K.flags.p);
+      }
+      UFE_TRY(allreduce_sum(c, K.scal.p + p * KS_BANK + KS_ST, 2));
+      {
+        UFE_LAUNCH(c, TC_KRYLOV_VEC);
+        k_ks_update_xr<<<gv, kBlock, 0, st>>>(m, iter, x_own, P_own, S_own, K.T.p, K.R.p, K.RP.p, K.scal.p, K.partials.p,
+                                              K.counter.p + 3, K.flags.p);
+      }
+      UFE_TRY(allreduce_sum(c, K.scal.p + (1 - p) * KS_BANK + KS_RHO, 2));
+    }
+    if (iter >= kp.maxit) {
+      UFE_LAUNCH(c, TC_KRYLOV_VEC);
+      k_ks_final_check<<<1, 1, 0, st>>>(iter, K.scal.p, K.flags.p);
+    } else {
+      // the convergence test of iteration `iter` runs inside its update_p; peek at it without advancing
+      UFE_LAUNCH(c, TC_KRYLOV_VEC);
+      k_ks_update_p<<<1, 32, 0, st>>>(0, iter, K.R.p, K.V.p, P_own, K.scal.p, K.flags.p);
+    }
+    UFE_CUDA(cudaMemcpyAsync(h_flags, K.flags.p, KF_COUNT * sizeof(int), cudaMemcpyDeviceToHost, st));
+    UFE_CUDA(cudaStreamSynchronize(st));
+    done = h_flags[KF_DONE] != 0;
+    if (check_every < 32) check_every *= 2;
+  }
+  UFE_CUDA(cudaGetLastError());
+  *its = h_flags[KF_ITS];
+  UFE_CHECK(h_flags[KF_REASON] != 1, "BiCGStab broke down (NaN residual) after %d iterations", *its);
+  return 0;
+}
+
+}  // namespace ufe

@@ -1,0 +1,43 @@
+// Device state of the SSA/DIVA velocity solve (type_ice_velocity_solver_DIVA / _SSA,
+// reference: src/UFEMISM/types/ice_model_types.f90:149-197).  See velocity.cu.
+#pragma once
+#include "common.cuh"
+
+namespace ufe {
+
+constexpr int kMaxNz = 32;
+
+// Every field is stored over the extended range of its grid (owned + halos): a-fields have a.n_ext() elements,
+// b-fields b.n_ext(); 3-D fields are [nz][n_ext] (the reference's (i,k) column-major layout).
+struct Velocity {
+  int nz = 0;
+  // --- inputs (type_ice_model / type_bed_roughness_model)
+  DBuf<double> Hi, Hs, A_flow, A_flow_vav, fraction_gr_b, till_friction_angle, beta_sq, alpha_sq, effective_pressure, tauc0, tauc;
+  DBuf<int> mask_grounded_ice, mask_icefree_land;
+  bool have_tfa = false, have_beta_sq = false, have_alpha_sq = false, have_neff = false;
+  int grounded_ice_exists = 1;
+  // --- state on the b-grid
+  DBuf<double> u, v, u_base, v_base, tau_bx, tau_by, eta_3D_b, u_prev, v_prev, tau_dx, tau_dy, u_3D, v_3D;
+  DBuf<double> N_b, dN_dx_b, dN_dy_b, beta_b, beta_eff_b, F1_3D_b, F2_3D_b;
+  // --- state on the a-grid
+  DBuf<double> du_dx, du_dy, dv_dx, dv_dy, du_dz_3D, dv_dz_3D, eta_3D_a, eta_vav, N_a, F1_3D_a, F2_3D_a, beta_a, beta_eff_a;
+  // --- prescribed velocities
+  DBuf<int> bc_mask;
+  DBuf<double> bc_u, bc_v;
+  bool have_bc = false;
+  // --- linear system: stiffness matrix on a pattern built once per (mesh, BC) (K3 of SURVEY 2e)
+  DevCsr A;
+  DBuf<int> row_kind;          // per matrix row: 0 free, 1 identity (prescribed / 'zero'), 2 'infinite'
+  DBuf<double> bb, uv;         // load vector (owned rows), solution (extended buv range)
+  unsigned long long pattern_key = 0;
+  bool pattern_valid = false;
+  // --- reductions
+  DBuf<double> red, partials;
+  DBuf<unsigned> counter;
+  bool uploaded = false;
+  int alloc(Ctx* c);
+};
+
+void velocity_free(Velocity* v);
+
+}  // namespace ufe

@@ -141,7 +141,7 @@ def lib():
         return _LIB
     if not os.path.exists(LIB_PATH):
         raise RuntimeError(f"{LIB_PATH} missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
-    L = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+    L = C.CDLL(LIB_PATH)
     H = C.c_void_p
     L.ufe_b200_last_error.restype = C.c_char_p
     L.ufe_b200_kernel_launches.restype = C.c_longlong
