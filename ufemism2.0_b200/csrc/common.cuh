@@ -135,6 +135,7 @@ inline int grid_for(const Ctx* c, long long n, int block, int max_waves = 8) {
 
 // halo exchange of an extended vector (no-op on one rank); ncols vectors of stride r.n_ext()
 int halo_exchange(Ctx* c, const Range& r, double* v, int ncols = 1, int elems_per_index = 1);
+int halo_exchange_int(Ctx* c, const Range& r, int* v);
 int allreduce_sum(Ctx* c, double* d_vals, int n);
 int allreduce_min(Ctx* c, double* d_vals, int n);
 

@@ -102,6 +102,26 @@ int halo_exchange(Ctx* c, const Range& r, double* v, int ncols, int epi) {
   return 0;
 }
 
+int halo_exchange_int(Ctx* c, const Range& r, int* v) {
+  if (c->nranks == 1) return 0;
+  NcclApi* N = nccl_api();
+  if (!N) return 3;
+  ncclComm_t comm = (ncclComm_t)c->nccl;
+  const int nl = r.i1 - r.lo, nr = r.hi - r.i2;
+  ncclResult_t rc = N->GroupStart();
+  if (c->rank > 0) {
+    if (r.send_l > 0 && rc == ncclSuccess) rc = N->Send(v + r.off(), r.send_l, ncclInt32, c->rank - 1, comm, c->stream);
+    if (nl > 0 && rc == ncclSuccess) rc = N->Recv(v, nl, ncclInt32, c->rank - 1, comm, c->stream);
+  }
+  if (c->rank < c->nranks - 1) {
+    if (r.send_r > 0 && rc == ncclSuccess) rc = N->Send(v + r.off() + r.n_loc() - r.send_r, r.send_r, ncclInt32, c->rank + 1, comm, c->stream);
+    if (nr > 0 && rc == ncclSuccess) rc = N->Recv(v + r.off() + r.n_loc(), nr, ncclInt32, c->rank + 1, comm, c->stream);
+  }
+  ncclResult_t rc2 = N->GroupEnd();
+  UFE_CHECK(rc == ncclSuccess && rc2 == ncclSuccess, "halo_exchange_int: %s", N->GetErrorString(rc != ncclSuccess ? rc : rc2));
+  return 0;
+}
+
 int allreduce_sum(Ctx* c, double* d, int n) {
   if (c->nranks == 1) return 0;
   NcclApi* N = nccl_api();

@@ -695,10 +695,7 @@ static int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation,
   if (coulomb_family) {
     { UFE_LAUNCH(c, TC_COLUMN); k_tauc0<<<g_a, 128, 0, st>>>(na, M.a.off(), V.effective_pressure.p, V.till_friction_angle.p, V.tauc0.p); }
     UFE_TRY(halo_exchange(c, M.a, V.tauc0.p));
-    if (c->nranks > 1) {  // the neighbour test reads mask_grounded_ice of halo vertices
-      DBuf<double> tmpm;  // masks travel as doubles to reuse the one halo routine (tiny, once per solve)
-      (void)tmpm;
-    }
+    UFE_TRY(halo_exchange_int(c, M.a, V.mask_grounded_ice.p));  // the neighbour test reads mask_grounded_ice of halo vertices
     UFE_LAUNCH(c, TC_COLUMN);
     k_tauc_extend<<<g_a, 128, 0, st>>>(na, M.a.off(), M.a.i1, M.a.lo, M.nV, M.nC.p, M.C.p, V.mask_grounded_ice.p, V.mask_icefree_land.p,
                                        V.tauc0.p, V.tauc.p, 1000.0 * cfg->ice_density * cfg->grav, cfg->Hi_min * cfg->ice_density * cfg->grav);
