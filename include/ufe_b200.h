@@ -77,7 +77,9 @@ typedef struct ufe_b200_config {
   int32_t BC_H[4];                          /* :364-367 */
   int32_t ksp_type, pc_type, ksp_maxit;     /* new keys B200_KSP_type_config / B200_PC_type_config; maxit = 2000 (petsc_basic.f90:166) */
   int32_t write_diagnostics;                /* 1: also fill the intermediate DIVA fields that only checksum()/restart read */
-  int32_t reserved[6];
+  int32_t ksp_initial_guess_nonzero;        /* 0 (default): zero initial guess, the reference's behaviour (petsc_basic.f90:163 is commented out);
+                                               1: start the Krylov solve from the current solution (= enabling KSPSetInitialGuessNonzero) */
+  int32_t reserved[5];
 } ufe_b200_config;
 
 /* Fill cfg with the reference's namelist defaults. */
@@ -246,6 +248,17 @@ int ufe_b200_calc_dHi_dt(ufe_b200_handle h, const ufe_b200_config* cfg, ufe_b200
 int ufe_b200_dHi_dt_finish(ufe_b200_handle h, const double* Hi, double* Hi_tplusdt, double dt, double* AMB,
                            double* dHi_dt);
 
+/* Device-resident time stepping: upload the thickness inputs once, then every call advances one predictor-corrector
+ * step -- calc_dHi_dt (predictor), solve_stress_balance on the predicted geometry, calc_dHi_dt (corrector) -- i.e. the
+ * three device phases of iterate_pc_timestep (src/UFEMISM/ice_dynamics/time_stepping/predictor_corrector_scheme.f90:118-233,
+ * Robinson et al. 2020 Eqs. 30-31) without any field leaving HBM.  The host-side stages the reference runs in between
+ * (alter_ice_thickness, determine_masks, calc_grounded_fractions, dt control) are not part of this path: masks and
+ * sub-grid fractions stay as uploaded; only Hs follows the thickness.  Needs ufe_b200_velocity_upload first. */
+int ufe_b200_thickness_upload(ufe_b200_handle h, const ufe_b200_thickness_io* io);
+int ufe_b200_pc_step_resident(ufe_b200_handle h, const ufe_b200_config* cfg, int approximation /*0 SSA, 1 DIVA*/, double dt,
+                              int* n_visc_its, int* n_Axb_its_velocity, int* n_Axb_its_thickness);
+int ufe_b200_thickness_download(ufe_b200_handle h, double* Hi, double* dHi_dt, double* divQ);
+
 /* ---- SIA (config 4) ------------------------------------------------------------------------------ */
 /* Replaces solve_SIA (src/UFEMISM/ice_dynamics/conservation_of_momentum/SIA/SIA_main.f90:65-158): u_3D_b, v_3D_b (ti1:ti2,nz). */
 int ufe_b200_solve_SIA(ufe_b200_handle h, const ufe_b200_config* cfg, const double* Hi, const double* Hs,
@@ -255,6 +268,13 @@ int ufe_b200_solve_SIA(ufe_b200_handle h, const ufe_b200_config* cfg, const doub
 /* Milliseconds spent in the named kernel class since the last reset, and its launch count.
  * classes: "spmv_stiffness", "krylov_vec", "assembly", "column", "tri", "epilogue", "thickness", "operator_spmv" */
 int ufe_b200_timing_enable(ufe_b200_handle h, int on);
+/* one CUDA-event stopwatch on the library's stream: start records an event, stop records another, synchronises and
+ * returns the elapsed device time in milliseconds */
+int ufe_b200_timer_start(ufe_b200_handle h);
+int ufe_b200_timer_stop(ufe_b200_handle h, double* ms);
+/* page-lock / unlock a host buffer the caller passes repeatedly (cudaHostRegister), so H2D/D2H copies run at full rate */
+int ufe_b200_host_register(void* ptr, size_t bytes);
+int ufe_b200_host_unregister(void* ptr);
 int ufe_b200_timing_get(ufe_b200_handle h, const char* kernel_class, double* ms, long long* launches);
 int ufe_b200_timing_reset(ufe_b200_handle h);
 

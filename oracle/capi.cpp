@@ -36,9 +36,10 @@ Config to_config(const ufe_b200_config* c) {
   C.icestream_L = c->refgeo_idealised_SSA_icestream_L; C.icestream_m = c->refgeo_idealised_SSA_icestream_m;
   C.choice_ice_integration_method = c->choice_ice_integration_method;
   C.dHi_semiimplicit_fs = c->dHi_semiimplicit_fs; C.dHi_PETSc_rtol = c->dHi_PETSc_rtol; C.dHi_PETSc_abstol = c->dHi_PETSc_abstol;
-  C.dt_ice_min = c->dt_ice_min;
+  C.dt_ice_min = c->dt_ice_min; C.dt_ice_max = c->dt_ice_max;
   C.ice_density = c->ice_density; C.seawater_density = c->seawater_density; C.grav = c->grav;
   C.ksp_maxit = c->ksp_maxit;
+  C.ksp_initial_guess_nonzero = c->ksp_initial_guess_nonzero;
   return C;
 }
 

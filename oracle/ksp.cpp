@@ -39,14 +39,21 @@ void get_diagonal(const Csr& A, std::vector<double>& d) {
 }
 }  // namespace
 
-int ksp_bicgstab_jacobi(const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int* its) {
+int ksp_bicgstab_jacobi(const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int* its, bool use_guess) {
   const size_t n = A.m;
   std::vector<double> dinv, R(n), RP(n), P(n, 0.0), V(n, 0.0), S(n), T(n), tmp(n);
   get_diagonal(A, dinv);
   for (size_t i = 0; i < n; ++i) dinv[i] = (dinv[i] != 0.0) ? 1.0 / dinv[i] : 1.0;  // PCJacobi: zero diagonal -> 1
-  for (size_t i = 0; i < n; ++i) { x[i] = 0.0; R[i] = dinv[i] * b[i]; }
+  for (size_t i = 0; i < n; ++i) R[i] = dinv[i] * b[i];
+  const double bnorm = std::sqrt(dot(R.data(), R.data(), n));
+  if (use_guess) {  // KSPSetInitialGuessNonzero: r0 = B (b - A x0); the default test still scales with ||B b||
+    spmv(A, x, tmp.data());
+    for (size_t i = 0; i < n; ++i) R[i] = dinv[i] * (b[i] - tmp[i]);
+  } else {
+    for (size_t i = 0; i < n; ++i) x[i] = 0.0;
+  }
   double dp = std::sqrt(dot(R.data(), R.data(), n));
-  const double ttol = std::max(rtol * dp, abstol);  // KSPConvergedDefault: rnorm0 = ||B b|| for a zero guess
+  const double ttol = std::max(rtol * bnorm, abstol);  // KSPConvergedDefault: rnorm0 = ||B b||
   *its = 0;
   if (dp <= ttol) return 0;
   RP = R;
@@ -146,7 +153,7 @@ void ilu_solve(const Aij& F, const double* r, double* z) {
 }
 }  // namespace
 
-int ksp_gmres_ilu0(const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int restart, int* its) {
+int ksp_gmres_ilu0(const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int restart, int* its, bool use_guess) {
   const size_t n = A.m;
   Aij F;
   to_aij(A, F);
@@ -154,9 +161,10 @@ int ksp_gmres_ilu0(const Csr& A, const double* b, double* x, double rtol, double
   const int m = restart;
   std::vector<std::vector<double>> Vk(m + 1, std::vector<double>(n));
   std::vector<double> H((size_t)(m + 1) * m, 0.0), cs(m), sn(m), g(m + 1), w(n), tmp(n), y(m);
-  for (size_t i = 0; i < n; ++i) x[i] = 0.0;
+  if (!use_guess) for (size_t i = 0; i < n; ++i) x[i] = 0.0;
   *its = 0;
-  double ttol = -1.0;
+  ilu_solve(F, b, w.data());
+  double ttol = std::max(rtol * std::sqrt(dot(w.data(), w.data(), n)), abstol);
   int total = 0;
   while (true) {
     // preconditioned residual z = B (b - A x)
@@ -164,7 +172,6 @@ int ksp_gmres_ilu0(const Csr& A, const double* b, double* x, double rtol, double
     for (size_t i = 0; i < n; ++i) tmp[i] = b[i] - tmp[i];
     ilu_solve(F, tmp.data(), Vk[0].data());
     double beta = std::sqrt(dot(Vk[0].data(), Vk[0].data(), n));
-    if (ttol < 0) ttol = std::max(rtol * beta, abstol);
     if (beta <= ttol || total >= maxit) { *its = total; return 0; }
     for (size_t i = 0; i < n; ++i) Vk[0][i] /= beta;
     std::fill(g.begin(), g.end(), 0.0);

@@ -82,19 +82,20 @@ struct Config {
   // thickness
   int choice_ice_integration_method = 1;  // 0 explicit, 1 semi-implicit
   double dHi_semiimplicit_fs = 1.5, dHi_PETSc_rtol = 1e-8, dHi_PETSc_abstol = 1e-6;
-  double dt_ice_min = 0.1;
+  double dt_ice_min = 0.1, dt_ice_max = 10.0;
   int BC_H[4] = {1, 1, 1, 1};             // 0 infinite, 1 zero
   // physical constants (parameters.f90)
   double ice_density = 917.0, seawater_density = 1027.0, grav = 9.81;
   // which Krylov method the oracle uses
   int ksp_type = KSP_bicgstab_jacobi; int ksp_maxit = 2000;
+  int ksp_initial_guess_nonzero = 0;  // petsc_basic.f90:163 (commented out in the reference => 0)
 };
 
 // --- linear solvers ---------------------------------------------------------------------------------
 // Both follow PETSc semantics at the reference's call site (petsc_basic.f90:125-237): zero initial
 // guess, left preconditioning, convergence on ||B r||_2 <= max(rtol ||B b||_2, abstol), <= maxit its.
-int ksp_bicgstab_jacobi(const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int* its);
-int ksp_gmres_ilu0(const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int restart, int* its);
+int ksp_bicgstab_jacobi(const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int* its, bool use_guess = false);
+int ksp_gmres_ilu0(const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int restart, int* its, bool use_guess = false);
 
 // --- linearised SSA/DIVA (solve_linearised_SSA_DIVA_infinite_slab.f90) --------------------------------
 void assemble_SSA_DIVA(const MeshView& mesh, const Operators& ops, const Config& C,

@@ -104,8 +104,9 @@ void assemble_SSA_DIVA(const MeshView& mesh, const Operators& ops, const Config&
 namespace {
 
 int linear_solve(const Config& C, const Csr& A, const double* b, double* x, double rtol, double abstol, int* its) {
-  if (C.ksp_type == KSP_gmres_ilu0) return ksp_gmres_ilu0(A, b, x, rtol, abstol, C.ksp_maxit, 30, its);
-  return ksp_bicgstab_jacobi(A, b, x, rtol, abstol, C.ksp_maxit, its);
+  const bool g = C.ksp_initial_guess_nonzero != 0;
+  if (C.ksp_type == KSP_gmres_ilu0) return ksp_gmres_ilu0(A, b, x, rtol, abstol, C.ksp_maxit, 30, its, g);
+  return ksp_bicgstab_jacobi(A, b, x, rtol, abstol, C.ksp_maxit, its, g);
 }
 
 // solve_SSA_DIVA_linearised (solve_linearised_SSA_DIVA_infinite_slab.f90:23-178)

@@ -134,7 +134,7 @@ void row_to_identity(Csr& A, int i) {  // set_diagonal_to_one_and_rest_of_row_to
 
 int calc_dHi_dt(const MeshView& mesh, const Config& C, ThicknessIO& io, double* dt, int* n_Axb_its) {
   const int nV = mesh.nV;
-  const double dt_ice_max = 10.0;  // C%dt_ice_max default (model_configuration_type_and_namelist.f90:391)
+  const double dt_ice_max = C.dt_ice_max;  // model_configuration_type_and_namelist.f90:391
   *n_Axb_its = 0;
   for (int v = 0; v < nV; ++v) io.AMB[v] = 0.0;
   ExplicitOut ex;
@@ -162,9 +162,11 @@ int calc_dHi_dt(const MeshView& mesh, const Config& C, ThicknessIO& io, double* 
     if (io.BC_prescr_mask)
       for (int vi = 1; vi <= nV; ++vi) if (io.BC_prescr_mask[vi - 1] == 1) { row_to_identity(AA, vi); bb[vi - 1] = io.BC_prescr_Hi[vi - 1]; }
     for (int vi = 1; vi <= nV; ++vi) if (io.mask_noice[vi - 1]) { row_to_identity(AA, vi); bb[vi - 1] = 0.0; }
+    const bool g = C.ksp_initial_guess_nonzero != 0;
+    if (g) for (int v = 0; v < nV; ++v) io.Hi_tplusdt[v] = ex.Hi_new[v];
     int rc = (C.ksp_type == KSP_gmres_ilu0)
-                 ? ksp_gmres_ilu0(AA, bb.data(), io.Hi_tplusdt, C.dHi_PETSc_rtol, C.dHi_PETSc_abstol, C.ksp_maxit, 30, n_Axb_its)
-                 : ksp_bicgstab_jacobi(AA, bb.data(), io.Hi_tplusdt, C.dHi_PETSc_rtol, C.dHi_PETSc_abstol, C.ksp_maxit, n_Axb_its);
+                 ? ksp_gmres_ilu0(AA, bb.data(), io.Hi_tplusdt, C.dHi_PETSc_rtol, C.dHi_PETSc_abstol, C.ksp_maxit, 30, n_Axb_its, g)
+                 : ksp_bicgstab_jacobi(AA, bb.data(), io.Hi_tplusdt, C.dHi_PETSc_rtol, C.dHi_PETSc_abstol, C.ksp_maxit, n_Axb_its, g);
     if (rc != 0) return rc;
     for (int v = 0; v < nV; ++v) { io.dHi_dt[v] = (io.Hi_tplusdt[v] - io.Hi[v]) / dts; io.AMB[v] = io.dHi_dt[v] - (io.Hi_tplusdt[v] - io.Hi[v]) / dts; }
   }

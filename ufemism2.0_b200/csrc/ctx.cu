@@ -235,6 +235,38 @@ int ufe_b200_timing_enable(ufe_b200_handle h, int on) {
   c->timing = on != 0;
   return 0;
 }
+static cudaEvent_t g_t0 = nullptr, g_t1 = nullptr;
+int ufe_b200_timer_start(ufe_b200_handle h) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CUDA(cudaSetDevice(c->device));
+  if (!g_t0) { UFE_CUDA(cudaEventCreate(&g_t0)); UFE_CUDA(cudaEventCreate(&g_t1)); }
+  UFE_CUDA(cudaEventRecord(g_t0, c->stream));
+  return 0;
+}
+int ufe_b200_timer_stop(ufe_b200_handle h, double* ms) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(g_t0 && ms, "ufe_b200_timer_stop without ufe_b200_timer_start");
+  UFE_CUDA(cudaEventRecord(g_t1, c->stream));
+  UFE_CUDA(cudaEventSynchronize(g_t1));
+  float f = 0.f;
+  UFE_CUDA(cudaEventElapsedTime(&f, g_t0, g_t1));
+  *ms = f;
+  return 0;
+}
+int ufe_b200_host_register(void* ptr, size_t bytes) {
+  cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterDefault);
+  if (e != cudaSuccess) {
+    cudaGetLastError();  // not sticky: clear it so that later launches do not report it
+    set_error("cudaHostRegister: %s", cudaGetErrorString(e));
+    return 1;
+  }
+  return 0;
+}
+int ufe_b200_host_unregister(void* ptr) {
+  cudaError_t e = cudaHostUnregister(ptr);
+  if (e != cudaSuccess) { cudaGetLastError(); set_error("cudaHostUnregister: %s", cudaGetErrorString(e)); return 1; }
+  return 0;
+}
 int ufe_b200_timing_get(ufe_b200_handle h, const char* cls, double* ms, long long* n) {
   Ctx* c = reinterpret_cast<Ctx*>(h);
   timing_collect(c);

@@ -16,27 +16,30 @@ int Krylov::ensure(Ctx* c, int m_loc, int n_ext) {
   return 0;
 }
 
-__global__ void k_ks_init(int m, const double* __restrict__ b, const double* __restrict__ dinv, double* __restrict__ R,
+__global__ void k_ks_init(int m, const double* __restrict__ b, const double* __restrict__ Ax, const double* __restrict__ dinv, double* __restrict__ R,
                           double* __restrict__ RP, double* __restrict__ x_own, double* __restrict__ P_own,
                           double* __restrict__ V, double* scal, double* partials, unsigned* counter, int* flags,
                           double rtol, double abstol) {
-  double acc[1] = {0.0};
+  double acc[2] = {0.0, 0.0};
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x) {
-    const double r = dinv[i] * b[i];
-    R[i] = r; RP[i] = r; x_own[i] = 0.0; P_own[i] = 0.0; V[i] = 0.0;
-    acc[0] += r * r;
+    const double pb = dinv[i] * b[i];
+    double r = pb;
+    if (Ax) r = dinv[i] * (b[i] - Ax[i]); else x_own[i] = 0.0;
+    R[i] = r; RP[i] = r; P_own[i] = 0.0; V[i] = 0.0;
+    acc[0] += pb * pb;
+    acc[1] += r * r;
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     flags[KF_DONE] = 0; flags[KF_ITS] = 0; flags[KF_REASON] = 0;
     scal[KS_RTOL] = rtol; scal[KS_ABSTOL] = abstol;
   }
-  grid_sum<1>(acc, partials, counter, scal + KS_RR0);
+  grid_sum<2>(acc, partials, counter, scal + KS_RR0);
 }
 
 // after the (optional) all-reduce of RR0: seed bank 0
 __global__ void k_ks_init_finish(double* scal) {
-  scal[KS_RHO] = scal[KS_RR0];
-  scal[KS_RR] = scal[KS_RR0];
+  scal[KS_RHO] = scal[KS_RINIT];
+  scal[KS_RR] = scal[KS_RINIT];
 }
 
 __device__ __forceinline__ double ks_ttol(const double* scal) {

@@ -17,7 +17,7 @@
 namespace ufe {
 
 // device scalars; two parity banks of 8 doubles + persistent slots
-enum { KS_RHO = 0, KS_RR = 1, KS_D1 = 2, KS_ST = 3, KS_TT = 4, KS_BANK = 8, KS_RR0 = 16, KS_RTOL = 17, KS_ABSTOL = 18, KS_COUNT = 24 };
+enum { KS_RHO = 0, KS_RR = 1, KS_D1 = 2, KS_ST = 3, KS_TT = 4, KS_BANK = 8, KS_RR0 = 16, KS_RINIT = 17, KS_RTOL = 18, KS_ABSTOL = 19, KS_COUNT = 24 };
 enum { KF_DONE = 0, KF_ITS = 1, KF_REASON = 2, KF_COUNT = 4 };
 
 struct Krylov {
@@ -34,12 +34,13 @@ struct Krylov {
 struct KrylovParams {
   double rtol, abstol;
   int maxit, ksp_type, pc_type;
+  int use_guess = 0;   // 1: x_ext holds the initial guess (KSPSetInitialGuessNonzero); the test still uses ||B b||
 };
 
 // ---- kernels shared by all matrix formats ------------------------------------------------------------
 
-// R = RP = B b, x = 0;  RR0 = RR[0] = RHO[0] = (R,R)
-__global__ void k_ks_init(int m, const double* __restrict__ b, const double* __restrict__ dinv, double* __restrict__ R,
+// R = RP = B (b - A x0) (Ax = nullptr: x0 = 0 and x is zeroed);  RR0 = ||B b||^2, RINIT = RR[0] = RHO[0] = (R,R)
+__global__ void k_ks_init(int m, const double* __restrict__ b, const double* __restrict__ Ax, const double* __restrict__ dinv, double* __restrict__ R,
                           double* __restrict__ RP, double* __restrict__ x_own, double* __restrict__ P_own,
                           double* __restrict__ V, double* scal, double* partials, unsigned* counter, int* flags,
                           double rtol, double abstol);

@@ -23,12 +23,19 @@ int bicgstab_solve(Ctx* c, const Op& op, const Range& rr, const double* d_b, con
     UFE_CUDA(cudaMemsetAsync(K.P.p, 0, sizeof(double) * rr.n_ext(), st));
     UFE_CUDA(cudaMemsetAsync(K.S.p, 0, sizeof(double) * rr.n_ext(), st));
   }
+  const double* d_Ax = nullptr;
+  if (kp.use_guess) {  // T = A x0 (plain product), then R = B (b - T)
+    UFE_TRY(halo_exchange(c, rr, d_x_ext));
+    UFE_LAUNCH(c, tc_spmv);
+    k_spmv_fused<Op, 0><<<gs, kBlock, 0, st>>>(op, m, off, 0, d_x_ext, nullptr, K.T.p, nullptr, nullptr, nullptr, nullptr, nullptr);
+    d_Ax = K.T.p;
+  }
   {
     UFE_LAUNCH(c, TC_KRYLOV_VEC);
-    k_ks_init<<<gv, kBlock, 0, st>>>(m, d_b, d_dinv, K.R.p, K.RP.p, x_own, P_own, K.V.p, K.scal.p, K.partials.p, K.counter.p,
+    k_ks_init<<<gv, kBlock, 0, st>>>(m, d_b, d_Ax, d_dinv, K.R.p, K.RP.p, x_own, P_own, K.V.p, K.scal.p, K.partials.p, K.counter.p,
                                      K.flags.p, kp.rtol, kp.abstol);
   }
-  UFE_TRY(allreduce_sum(c, K.scal.p + KS_RR0, 1));
+  UFE_TRY(allreduce_sum(c, K.scal.p + KS_RR0, 2));
   {
     UFE_LAUNCH(c, TC_KRYLOV_VEC);
     k_ks_init_finish<<<1, 1, 0, st>>>(K.scal.p);

@@ -22,16 +22,6 @@
 
 namespace ufe {
 
-struct Thickness {
-  // a-grid fields over the extended range
-  DBuf<double> Hi, Hb, SL, SMB, BMB, LMB, fraction_margin, target, bc_Hi, divQ, dHi_dt, AMB, Hi_new, Hi_ex, Hs, Hs_tot, bb;
-  DBuf<int> mask_noice, bc_mask, n_int;
-  DBuf<double> u_b, v_b;     // b-grid, extended (only when the caller passes velocities)
-  DevCsr M;                  // M_divQ, then AA = 1 + dt f_s M_divQ in place
-  DBuf<double> Mval0;        // M_divQ values (kept when AA overwrites M.val)
-  DBuf<unsigned long long> dtbits;
-  bool have_bc = false, pattern = false;
-};
 void thickness_free(Thickness* t) { delete t; }
 
 namespace {
@@ -246,7 +236,7 @@ __global__ void k_th_rates(int n, int off, double dt_scheme, double dt_final, in
 
 }  // namespace
 
-static int ensure_thickness(Ctx* c) {
+int ensure_thickness(Ctx* c) {
   UFE_CHECK(c->mesh && c->mesh->have_ops, "no mesh / operators: call ufe_b200_mesh_create and ufe_b200_calc_matrix_operators first");
   if (c->thick) return 0;
   Mesh& M = *c->mesh;
@@ -330,7 +320,7 @@ static int th_apply_bc(Ctx* c, const MeshV& mv, const ThPar& p, double* Hi_new) 
 }
 
 // calc_dHi_dt on device-resident inputs; u_b/v_b: extended b-grid vectors with valid halos
-static int thickness_step(Ctx* c, const ufe_b200_config* cfg, const double* u_b, const double* v_b, double* dt, int finish, int* n_Axb_its) {
+int thickness_step(Ctx* c, const ufe_b200_config* cfg, const double* u_b, const double* v_b, double* dt, int finish, int* n_Axb_its) {
   Mesh& M = *c->mesh; Thickness& T = *c->thick;
   cudaStream_t st = c->stream;
   UFE_TRY(ensure_th_pattern(c));
@@ -389,6 +379,10 @@ static int thickness_step(Ctx* c, const ufe_b200_config* cfg, const double* u_b,
     }
     KrylovParams kp{cfg->dHi_PETSc_rtol, cfg->dHi_PETSc_abstol, cfg->ksp_maxit > 0 ? cfg->ksp_maxit : 2000, UFE_KSP_BICGSTAB,
                     cfg->pc_type == UFE_PC_NONE ? UFE_PC_NONE : UFE_PC_JACOBI};
+    if (cfg->ksp_initial_guess_nonzero) {  // start from the explicit solution (the reference passes Hi + dt dHi_dt, semiimplicit.f90:152)
+      kp.use_guess = 1;
+      UFE_CUDA(cudaMemcpyAsync(T.Hi_new.p + mv.off, T.Hi_ex.p + mv.off, sizeof(double) * n, cudaMemcpyDeviceToDevice, st));
+    }
     UFE_TRY(csr_ksp_solve(c, T.M, T.bb.p, T.Hi_new.p, kp, TC_THICKNESS, n_Axb_its));
     { UFE_LAUNCH(c, TC_THICKNESS); k_th_rates<<<grid, 128, 0, st>>>(n, mv.off, dt_in, dt_final, 1, finish, T.Hi.p, T.Hi_new.p, T.dHi_dt.p, T.AMB.p); }
   }

@@ -1,0 +1,134 @@
+// Device-resident predictor-corrector time step: the unit "1 time step" = 1 velocity solve + 2 thickness solves.
+// Follows iterate_pc_timestep of run_ice_dynamics_model_pc
+//   src/UFEMISM/ice_dynamics/time_stepping/predictor_corrector_scheme.f90:118-233 (Robinson et al., 2020, Eqs. 30-31)
+// with the three device phases back to back and no field leaving HBM in between.  The host-side stages the
+// reference runs between them (alter_ice_thickness, determine_masks, calc_grounded_fractions,
+// calc_effective_thickness, truncation-error based dt control) are NOT part of this path: masks and
+// sub-grid fractions stay as uploaded, only Hs follows the predicted thickness (ice_geometry_basics.f90:33).
+#include "mesh.cuh"
+#include "thickness.cuh"
+#include "velocity.cuh"
+
+namespace ufe {
+
+struct PcState {
+  DBuf<double> dHdt_n, dHdt_nm1, Hi_prev;
+  double dt_n = 0.0;
+  bool started = false;
+};
+static PcState* g_pc = nullptr;   // one per process (one rank <-> one GPU)
+
+// Hi_star = Hi_prev + dt ((1 + zeta/2) dHdt_n - zeta/2 dHdt_nm1)  (Eq. 30), clamped at zero; Hs of the predicted geometry
+__global__ void k_pc_predict(int n, int off, double dt, double zeta, double rho_ratio, const int* __restrict__ mask_noice,
+                             const double* __restrict__ Hi_prev, double* __restrict__ dHdt_n, const double* __restrict__ dHdt_nm1,
+                             const double* __restrict__ Hb, const double* __restrict__ SL, double* __restrict__ Hi_vel,
+                             double* __restrict__ Hs_vel) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const size_t i = off + r;
+    double d = dHdt_n[i];
+    if (mask_noice[i]) d = 0.0;
+    dHdt_n[i] = d;
+    double h = Hi_prev[i] + dt * ((1.0 + zeta / 2.0) * d - (zeta / 2.0) * dHdt_nm1[i]);
+    h = fmax(0.0, h);
+    Hi_vel[i] = h;
+    Hs_vel[i] = h + fmax(SL[i] - rho_ratio * h, Hb[i]);
+  }
+}
+
+// Hi_np1 = Hi_prev + dt/2 (dHdt_n + dHdt_star)  (Eq. 31); accepted: becomes the new Hi, rates shift by one step
+__global__ void k_pc_correct(int n, int off, double dt, double rho_ratio, const int* __restrict__ mask_noice,
+                             const double* __restrict__ dHdt_n, double* __restrict__ dHdt_nm1, const double* __restrict__ dHdt_star,
+                             const double* __restrict__ Hb, const double* __restrict__ SL, double* __restrict__ Hi,
+                             double* __restrict__ Hi_vel, double* __restrict__ Hs_vel) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const size_t i = off + r;
+    double ds = dHdt_star[i];
+    if (mask_noice[i]) ds = 0.0;
+    const double h = fmax(0.0, Hi[i] + (dt / 2.0) * (dHdt_n[i] + ds));
+    Hi[i] = h;
+    dHdt_nm1[i] = dHdt_n[i];
+    Hi_vel[i] = h;
+    Hs_vel[i] = h + fmax(SL[i] - rho_ratio * h, Hb[i]);
+  }
+}
+
+}  // namespace ufe
+
+using namespace ufe;
+
+extern "C" {
+
+int ufe_b200_thickness_upload(ufe_b200_handle h, const ufe_b200_thickness_io* io) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && io, "NULL argument");
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_TRY(ensure_thickness(c));
+  Mesh& M = *c->mesh; Thickness& T = *c->thick;
+  UFE_CHECK(io->Hi && io->Hb && io->SL && io->SMB && io->BMB && io->LMB && io->fraction_margin && io->mask_noice && io->dHi_dt_target,
+            "ufe_b200_thickness_upload: Hi, Hb, SL, SMB, BMB, LMB, fraction_margin, mask_noice, dHi_dt_target are required");
+  auto up = [&](double* d, const double* s) { return cudaMemcpyAsync(d + M.a.off(), s, sizeof(double) * M.a.n_loc(), cudaMemcpyHostToDevice, c->stream); };
+  UFE_CUDA(up(T.Hi.p, io->Hi)); UFE_CUDA(up(T.Hb.p, io->Hb)); UFE_CUDA(up(T.SL.p, io->SL)); UFE_CUDA(up(T.SMB.p, io->SMB));
+  UFE_CUDA(up(T.BMB.p, io->BMB)); UFE_CUDA(up(T.LMB.p, io->LMB)); UFE_CUDA(up(T.fraction_margin.p, io->fraction_margin));
+  UFE_CUDA(up(T.target.p, io->dHi_dt_target));
+  UFE_CUDA(cudaMemcpyAsync(T.mask_noice.p + M.a.off(), io->mask_noice, sizeof(int) * M.a.n_loc(), cudaMemcpyHostToDevice, c->stream));
+  if (io->BC_prescr_mask && io->BC_prescr_Hi) {
+    UFE_CUDA(cudaMemcpyAsync(T.bc_mask.p + M.a.off(), io->BC_prescr_mask, sizeof(int) * M.a.n_loc(), cudaMemcpyHostToDevice, c->stream));
+    UFE_CUDA(up(T.bc_Hi.p, io->BC_prescr_Hi));
+    T.have_bc = true;
+  } else T.have_bc = false;
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  if (g_pc) g_pc->started = false;
+  return 0;
+}
+
+int ufe_b200_thickness_download(ufe_b200_handle h, double* Hi, double* dHi_dt, double* divQ) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && c->thick, "ufe_b200_thickness_download: nothing on the device");
+  UFE_CUDA(cudaSetDevice(c->device));
+  Mesh& M = *c->mesh; Thickness& T = *c->thick;
+  auto dn = [&](double* d, const double* s) { return d ? cudaMemcpyAsync(d, s + M.a.off(), sizeof(double) * M.a.n_loc(), cudaMemcpyDeviceToHost, c->stream) : cudaSuccess; };
+  UFE_CUDA(dn(Hi, T.Hi.p)); UFE_CUDA(dn(dHi_dt, T.dHi_dt.p)); UFE_CUDA(dn(divQ, T.divQ.p));
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int ufe_b200_pc_step_resident(ufe_b200_handle h, const ufe_b200_config* cfg, int approximation, double dt, int* n_visc_its,
+                              int* n_Axb_its_velocity, int* n_Axb_its_thickness) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && cfg && n_visc_its && n_Axb_its_velocity && n_Axb_its_thickness, "NULL argument");
+  UFE_CHECK(c->vel && c->vel->uploaded && c->thick, "ufe_b200_pc_step_resident: upload the velocity and thickness inputs first");
+  UFE_CUDA(cudaSetDevice(c->device));
+  Mesh& M = *c->mesh; Velocity& V = *c->vel; Thickness& T = *c->thick;
+  cudaStream_t st = c->stream;
+  if (!g_pc) g_pc = new PcState();
+  PcState& P = *g_pc;
+  const size_t na = M.a.n_ext();
+  const int n = M.a.n_loc(), grid = grid_for(c, n, 128, 16);
+  if (!P.started || P.dHdt_n.n < na) {
+    UFE_TRY(P.dHdt_n.alloc(na)); UFE_TRY(P.dHdt_nm1.alloc(na));
+    UFE_CUDA(cudaMemsetAsync(P.dHdt_n.p, 0, sizeof(double) * na, st)); UFE_CUDA(cudaMemsetAsync(P.dHdt_nm1.p, 0, sizeof(double) * na, st));
+    P.dt_n = dt; P.started = true;
+  }
+  const double zeta = dt / P.dt_n;
+  const double rho_ratio = cfg->ice_density / cfg->seawater_density;
+  int its_p = 0, its_c = 0;
+  double dt_p = dt, dt_c = dt;
+  // predictor: dHi_dt( Hi_n, u_n) (:129)
+  UFE_TRY(halo_exchange(c, M.b, V.u.p)); UFE_TRY(halo_exchange(c, M.b, V.v.p));
+  UFE_TRY(thickness_step(c, cfg, V.u.p, V.v.p, &dt_p, 1, &its_p));
+  UFE_CUDA(cudaMemcpyAsync(P.dHdt_n.p, T.dHi_dt.p, sizeof(double) * na, cudaMemcpyDeviceToDevice, st));
+  { UFE_LAUNCH(c, TC_THICKNESS); k_pc_predict<<<grid, 128, 0, st>>>(n, M.a.off(), dt, zeta, rho_ratio, T.mask_noice.p, T.Hi.p, P.dHdt_n.p, P.dHdt_nm1.p, T.Hb.p, T.SL.p, V.Hi.p, V.Hs.p); }
+  // velocities for the predicted geometry (:186)
+  UFE_TRY(velocity_solve(c, cfg, approximation, n_visc_its, n_Axb_its_velocity));
+  // corrector: dHi_dt( Hi_n, u_np1) (:214)
+  UFE_TRY(halo_exchange(c, M.b, V.u.p)); UFE_TRY(halo_exchange(c, M.b, V.v.p));
+  UFE_TRY(thickness_step(c, cfg, V.u.p, V.v.p, &dt_c, 1, &its_c));
+  { UFE_LAUNCH(c, TC_THICKNESS); k_pc_correct<<<grid, 128, 0, st>>>(n, M.a.off(), dt, rho_ratio, T.mask_noice.p, P.dHdt_n.p, P.dHdt_nm1.p, T.dHi_dt.p, T.Hb.p, T.SL.p, T.Hi.p, V.Hi.p, V.Hs.p); }
+  UFE_CUDA(cudaGetLastError());
+  UFE_CUDA(cudaStreamSynchronize(st));
+  P.dt_n = dt;
+  *n_Axb_its_thickness = its_p + its_c;
+  return 0;
+}
+
+}  // extern "C"

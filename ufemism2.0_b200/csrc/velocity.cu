@@ -475,6 +475,12 @@ __global__ void k_store_prev(int n, int off, const double* __restrict__ u, const
   }
 }
 
+__global__ void k_interleave(int n, int off, const double* __restrict__ u, const double* __restrict__ v, double* __restrict__ uv_own) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    uv_own[2 * r] = u[off + r]; uv_own[2 * r + 1] = v[off + r];
+  }
+}
+
 __global__ void k_deinterleave(int n, int off, const double* __restrict__ uv_own, double* __restrict__ u, double* __restrict__ v) {
   for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
     u[off + r] = uv_own[2 * r]; v[off + r] = uv_own[2 * r + 1];
@@ -500,7 +506,7 @@ __global__ void k_3D_velocities(int n, int off, int nb_ext, int nz, const double
 
 // ---- host side ---------------------------------------------------------------------------------------------------------
 
-static int ensure_velocity(Ctx* c) {
+int ensure_velocity(Ctx* c) {
   UFE_CHECK(c->mesh, "no mesh: call ufe_b200_mesh_create first");
   UFE_CHECK(c->mesh->have_ops, "no mesh operators: call ufe_b200_calc_matrix_operators first");
   if (!c->vel) {
@@ -564,6 +570,12 @@ static int ensure_pattern(Ctx* c, const VelPar& p, unsigned long long bc_version
 static int solve_linear_system(Ctx* c, const ufe_b200_config* cfg, double rtol, double abstol, int* its) {
   Velocity& V = *c->vel;
   KrylovParams kp{rtol, abstol, cfg->ksp_maxit > 0 ? cfg->ksp_maxit : 2000, cfg->ksp_type, cfg->pc_type};
+  if (cfg->ksp_initial_guess_nonzero) {  // uv_buv( tiuv2n( ti,1:2)) = u_b, v_b (solve_linearised_SSA_DIVA_infinite_slab.f90:74-84)
+    Mesh& M = *c->mesh;
+    kp.use_guess = 1;
+    UFE_LAUNCH(c, TC_EPILOGUE);
+    k_interleave<<<grid_for(c, M.b.n_loc(), 128, 16), 128, 0, c->stream>>>(M.b.n_loc(), M.b.off(), V.u.p, V.v.p, V.uv.p + M.buv.off());
+  }
   return csr_ksp_solve(c, V.A, V.bb.p, V.uv.p, kp, TC_SPMV_STIFFNESS, its);
 }
 
@@ -661,7 +673,7 @@ static int velocity_download(Ctx* c, ufe_b200_velocity_state* st) {
 }
 
 // solve_DIVA_infinite_slab (approximation = 1) / solve_SSA (approximation = 0) on device-resident fields
-static int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n_visc_its, int* n_Axb_its) {
+int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n_visc_its, int* n_Axb_its) {
   UFE_CHECK(c->vel && c->vel->uploaded, "velocity solve: call ufe_b200_velocity_upload first");
   Mesh& M = *c->mesh; Velocity& V = *c->vel;
   cudaStream_t st = c->stream;

@@ -39,5 +39,8 @@ struct Velocity {
 };
 
 void velocity_free(Velocity* v);
+int ensure_velocity(Ctx* c);
+// solve_DIVA_infinite_slab (approximation = 1) / solve_SSA (0) on device-resident fields
+int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n_visc_its, int* n_Axb_its);
 
 }  // namespace ufe

@@ -44,7 +44,7 @@ class Config(C.Structure):
         ("visc_it_nit", C.c_int32), ("do_include_SSADIVA_crossterms", C.c_int32), ("BC_u", C.c_int32 * 4),
         ("BC_v", C.c_int32 * 4), ("choice_sliding_law", C.c_int32), ("do_GL_subgrid_friction", C.c_int32),
         ("choice_ice_integration_method", C.c_int32), ("BC_H", C.c_int32 * 4), ("ksp_type", C.c_int32),
-        ("pc_type", C.c_int32), ("ksp_maxit", C.c_int32), ("write_diagnostics", C.c_int32), ("reserved", C.c_int32 * 6)]
+        ("pc_type", C.c_int32), ("ksp_maxit", C.c_int32), ("write_diagnostics", C.c_int32), ("ksp_initial_guess_nonzero", C.c_int32), ("reserved", C.c_int32 * 5)]
 
 
 def default_config():
@@ -176,10 +176,17 @@ def lib():
     L.ufe_b200_velocity_download.argtypes = [H, C.POINTER(VelocityState)]
     L.ufe_b200_calc_dHi_dt.argtypes = [H, C.POINTER(Config), C.POINTER(ThicknessIO), c_dp, C.c_int, C.POINTER(C.c_int)]
     L.ufe_b200_dHi_dt_finish.argtypes = [H, c_dp, c_dp, C.c_double, c_dp, c_dp]
+    L.ufe_b200_thickness_upload.argtypes = [H, C.POINTER(ThicknessIO)]
+    L.ufe_b200_pc_step_resident.argtypes = [H, C.POINTER(Config), C.c_int, C.c_double] + [C.POINTER(C.c_int)] * 3
+    L.ufe_b200_thickness_download.argtypes = [H, c_dp, c_dp, c_dp]
     L.ufe_b200_solve_SIA.argtypes = [H, C.POINTER(Config), c_dp, c_dp, c_dp, c_dp, c_dp]
     L.ufe_b200_timing_enable.argtypes = [H, C.c_int]
     L.ufe_b200_timing_get.argtypes = [H, C.c_char_p, c_dp, C.POINTER(C.c_longlong)]
     L.ufe_b200_timing_reset.argtypes = [H]
+    L.ufe_b200_timer_start.argtypes = [H]
+    L.ufe_b200_timer_stop.argtypes = [H, c_dp]
+    L.ufe_b200_host_register.argtypes = [C.c_void_p, C.c_size_t]
+    L.ufe_b200_host_unregister.argtypes = [C.c_void_p]
     _LIB = L
     return L
 
@@ -191,8 +198,10 @@ ABI_SYMBOLS = [
     "ufe_b200_calc_matrix_operators", "ufe_b200_set_operator", "ufe_b200_get_operator_size", "ufe_b200_get_operator",
     "ufe_b200_apply_operator", "ufe_b200_solve_SSA_DIVA_linearised", "ufe_b200_get_stiffness_size", "ufe_b200_get_stiffness",
     "ufe_b200_solve_DIVA", "ufe_b200_solve_SSA", "ufe_b200_velocity_upload", "ufe_b200_velocity_solve_resident",
-    "ufe_b200_velocity_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA",
-    "ufe_b200_timing_enable", "ufe_b200_timing_get", "ufe_b200_timing_reset"]
+    "ufe_b200_velocity_download", "ufe_b200_thickness_upload", "ufe_b200_pc_step_resident",
+    "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA",
+    "ufe_b200_timing_enable", "ufe_b200_timing_get", "ufe_b200_timing_reset", "ufe_b200_timer_start", "ufe_b200_timer_stop",
+    "ufe_b200_host_register", "ufe_b200_host_unregister"]
 
 
 class UfeError(RuntimeError):
