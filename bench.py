@@ -371,17 +371,12 @@ def run_b200(args, rank, world, rdv, log):
         except OSError:
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
-        R = 2 * m.nTri
-        ptr = ctx.get_operator(ub.OP["M2_ddx_b_b"])[0] if world == 1 else None
-        nnz_m2 = int(ptr[-1] - 1) if ptr is not None else 10 * m.nTri
-        free_rows = R - 2 * int((m.TriBI > 0).sum())
-        nnz = 4 * nnz_m2   # 2 rows x 2 columns per M2 entry (border rows are shorter; counted as stored below when single-rank)
-        if world == 1:
-            sp, si = C.c_int(), C.c_int()
-            ub.check(L.ufe_b200_get_stiffness_size(ctx.h, C.byref(sp), C.byref(si)))
-            nnz = si.value
-        rows_loc = R // world
-        B_spmv = 12 * (nnz // world if world > 1 else nnz) + 4 * (rows_loc + 1) + 8 * rows_loc + 8 * rows_loc
+        csr_b, blk_b = C.c_longlong(), C.c_longlong()
+        ub.check(L.ufe_b200_get_stiffness_storage_bytes(ctx.h, C.byref(csr_b), C.byref(blk_b)))
+        rows_loc = 2 * nb
+        # B_spmv = 12 nnz + 4 (rows + 1) + 8 rows (y) + 8 cols (x), for the rank's row block
+        B_spmv = csr_b.value + 8 * rows_loc + 8 * rows_loc
+        B_streamed = blk_b.value + 8 * rows_loc * 4   # blocks + y + x + Jacobi diagonal + dot-product operand
         avg_ms = spmv_ms / max(spmv_n, 1)
         achieved = B_spmv / (avg_ms * 1e-3) / 1e9 if spmv_n else 0.0
         res = {
@@ -397,14 +392,14 @@ def run_b200(args, rank, world, rdv, log):
             "e2e": {"value": k_e2e / e2e_s, "unit": "velocity solves/s", "h2d_bytes_per_step": bytes_in[0] // k_e2e, "d2h_bytes_per_step": bytes_out[0] // k_e2e,
                     "steps": k_e2e},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_spmv_fused<CsrOp> (stiffness-matrix SpMV inside BiCGStab)", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": "k_spmv_blk (stiffness-matrix SpMV with fused Jacobi + dot products inside BiCGStab)", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak if peak else None, "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
-                         "algorithmic_bytes_per_launch": B_spmv, "avg_launch_ms": avg_ms, "launches": spmv_n, "traffic": None,
+                         "algorithmic_bytes_per_launch": B_spmv, "streamed_bytes_per_launch": B_streamed,
+                         "streamed_GBps": B_streamed / (avg_ms * 1e-3) / 1e9 if spmv_n else 0.0, "avg_launch_ms": avg_ms, "launches": spmv_n, "traffic": None,
                          "share_of_step": spmv_ms / ms_total if ms_total else None, "frac_of_8TBs": achieved / 8000.0},
             "kernel_classes_ms": {k: v[0] for k, v in classes.items()},
             "clocks": clocks,
         }
-        _ = free_rows
     ctx.close()
     return res
 

@@ -79,7 +79,8 @@ typedef struct ufe_b200_config {
   int32_t write_diagnostics;                /* 1: also fill the intermediate DIVA fields that only checksum()/restart read */
   int32_t ksp_initial_guess_nonzero;        /* 0 (default): zero initial guess, the reference's behaviour (petsc_basic.f90:163 is commented out);
                                                1: start the Krylov solve from the current solution (= enabling KSPSetInitialGuessNonzero) */
-  int32_t reserved[5];
+  int32_t stiffness_format;                 /* storage the Krylov solver streams: 0 = 2x2-blocked sliced ELL (default), 1 = the CSR matrix itself */
+  int32_t reserved[4];
 } ufe_b200_config;
 
 /* Fill cfg with the reference's namelist defaults. */
@@ -174,6 +175,8 @@ int ufe_b200_solve_SSA_DIVA_linearised(ufe_b200_handle h, const ufe_b200_config*
 /* The system assembled by the last linearised solve (rank-local rows): sizes, then arrays (bit-exact ptr/ind parity). */
 int ufe_b200_get_stiffness_size(ufe_b200_handle h, int* m_loc, int* nnz_loc);
 int ufe_b200_get_stiffness(ufe_b200_handle h, int32_t* ptr, int32_t* ind, double* val, double* bb);
+/* bytes of matrix data one SpMV streams: the CSR arrays (12 nnz + 4 (rows+1)) and the 2x2-blocked sliced-ELL copy (36 per block slot) */
+int ufe_b200_get_stiffness_storage_bytes(ufe_b200_handle h, long long* csr_bytes, long long* blocked_bytes);
 
 /* Inputs of the velocity solve taken from type_ice_model / type_bed_roughness_model (owned slices). */
 typedef struct ufe_b200_ice_inputs {

@@ -121,6 +121,44 @@ def test_diva_converged_solve_matches_oracle_and_petsc_default(setup):
     assert abs(nv3 - nv) <= 1 and rel_l2(g2["u_vav_b"], g["u_vav_b"]) < 5e-3
 
 
+def test_blocked_and_csr_storage_agree(setup):
+    # the Krylov solver streams a 2x2-blocked sliced-ELL copy of the stiffness matrix by default; the CSR matrix itself is the
+    # other option.  Same algorithm, same reductions -> same iteration counts and (to round-off) the same solution.
+    w, ctx, o = setup
+    m = w.mesh
+    ice = w.ice_inputs()
+    res = []
+    for fmt in (0, 1):
+        cfg = wl.scaling_config()
+        cfg.stiffness_format = fmt
+        cfg.visc_it_nit = 3; cfg.visc_it_norm_dUV_tol = 1e-30
+        cfg.stress_balance_PETSc_rtol = 1e-10; cfg.stress_balance_PETSc_abstol = 1e-30
+        res.append(_solve_gpu(ctx, cfg, 1, ice, m))
+    (g0, nv0, na0), (g1, nv1, na1) = res
+    assert nv0 == nv1 and abs(na0 - na1) <= max(3, na1 // 50)
+    assert rel_l2(g0["u_vav_b"], g1["u_vav_b"]) < 1e-8 and rel_l2(g0["v_vav_b"], g1["v_vav_b"]) < 1e-8
+
+
+def test_initial_guess_option_reaches_same_solution(setup):
+    w, ctx, o = setup
+    m = w.mesh
+    ice = w.ice_inputs()
+    res = []
+    for guess in (0, 1):
+        cfg = wl.scaling_config()
+        cfg.ksp_initial_guess_nonzero = guess
+        cfg.stress_balance_PETSc_rtol = 1e-11; cfg.stress_balance_PETSc_abstol = 1e-30
+        res.append(_solve_gpu(ctx, cfg, 1, ice, m))
+    (g0, nv0, na0), (g1, nv1, na1) = res
+    assert nv0 == nv1 and na1 < na0                      # warm starts save Krylov iterations
+    assert rel_l2(g1["u_vav_b"], g0["u_vav_b"]) < 1e-6
+    st2, r = ub.alloc_velocity_state(m.nV, m.nTri, m.nz)
+    cfg.ksp_initial_guess_nonzero = 1
+    rc, nv2, na2 = o.solve_velocity(cfg, 1, ice, st2)     # the oracle implements the same option
+    assert rc == 0 and nv2 == nv1 and abs(na2 - na1) <= max(5, na2 // 20)
+    assert rel_l2(g1["u_vav_b"], r["u_vav_b"]) < 1e-7
+
+
 def test_ssa_matches_oracle(setup):
     w, ctx, o = setup
     m = w.mesh

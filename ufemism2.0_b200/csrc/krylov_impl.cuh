@@ -6,16 +6,39 @@ namespace ufe {
 
 // d_b: local right-hand side (m_loc); d_dinv: local inverse diagonal (Jacobi) or ones;
 // d_x_ext: extended solution vector, owned part at [rr.off()..]; halos are NOT refreshed on return.
+// launcher for matrices given as a per-row functor (krylov.cuh: CsrOp<W>)
+template <class Op>
+struct RowOpMat {
+  Op op;
+  void spmv(Ctx* c, int mode, int m, int off, int iter, const double* x_ext, const double* dinv, double* y, const double* rp, double* scal,
+            double* partials, unsigned* counter, const int* flags, int tc) const {
+    const int gs = grid_for(c, (long long)m * Op::W, kBlock);
+    UFE_LAUNCH(c, tc);
+    if (mode == 0) k_spmv_fused<Op, 0><<<gs, kBlock, 0, c->stream>>>(op, m, off, iter, x_ext, dinv, y, rp, scal, partials, counter, flags);
+    else if (mode == 1) k_spmv_fused<Op, 1><<<gs, kBlock, 0, c->stream>>>(op, m, off, iter, x_ext, dinv, y, rp, scal, partials, counter, flags);
+    else k_spmv_fused<Op, 2><<<gs, kBlock, 0, c->stream>>>(op, m, off, iter, x_ext, dinv, y, rp, scal, partials, counter, flags);
+  }
+};
+
+template <class Mat>
+int bicgstab_solve_mat(Ctx* c, const Mat& A, const Range& rr, const double* d_b, const double* d_dinv, double* d_x_ext,
+                       const KrylovParams& kp, int tc_spmv, int* its);
+
 template <class Op>
 int bicgstab_solve(Ctx* c, const Op& op, const Range& rr, const double* d_b, const double* d_dinv, double* d_x_ext,
                    const KrylovParams& kp, int tc_spmv, int* its) {
+  return bicgstab_solve_mat(c, RowOpMat<Op>{op}, rr, d_b, d_dinv, d_x_ext, kp, tc_spmv, its);
+}
+
+template <class Mat>
+int bicgstab_solve_mat(Ctx* c, const Mat& A, const Range& rr, const double* d_b, const double* d_dinv, double* d_x_ext,
+                       const KrylovParams& kp, int tc_spmv, int* its) {
   if (!c->krylov) c->krylov = new Krylov();
   Krylov& K = *c->krylov;
   const int m = rr.n_loc(), off = rr.off();
   UFE_TRY(K.ensure(c, m, rr.n_ext()));
   cudaStream_t st = c->stream;
   const int gv = grid_for(c, m, kBlock);                       // vector kernels
-  const int gs = grid_for(c, (long long)m * Op::W, kBlock);    // SpMV kernels
   double* x_own = d_x_ext + off;
   double* P_own = K.P.p + off;
   double* S_own = K.S.p + off;
@@ -26,8 +49,7 @@ int bicgstab_solve(Ctx* c, const Op& op, const Range& rr, const double* d_b, con
   const double* d_Ax = nullptr;
   if (kp.use_guess) {  // T = A x0 (plain product), then R = B (b - T)
     UFE_TRY(halo_exchange(c, rr, d_x_ext));
-    UFE_LAUNCH(c, tc_spmv);
-    k_spmv_fused<Op, 0><<<gs, kBlock, 0, st>>>(op, m, off, 0, d_x_ext, nullptr, K.T.p, nullptr, nullptr, nullptr, nullptr, nullptr);
+    A.spmv(c, 0, m, off, 0, d_x_ext, nullptr, K.T.p, nullptr, nullptr, nullptr, nullptr, nullptr, tc_spmv);
     d_Ax = K.T.p;
   }
   {
@@ -53,22 +75,14 @@ int bicgstab_solve(Ctx* c, const Op& op, const Range& rr, const double* d_b, con
         k_ks_update_p<<<gv, kBlock, 0, st>>>(m, iter, K.R.p, K.V.p, P_own, K.scal.p, K.flags.p);
       }
       UFE_TRY(halo_exchange(c, rr, K.P.p));
-      {
-        UFE_LAUNCH(c, tc_spmv);
-        k_spmv_fused<Op, 1><<<gs, kBlock, 0, st>>>(op, m, off, iter, K.P.p, d_dinv, K.V.p, K.RP.p, K.scal.p, K.partials.p,
-                                                   K.counter.p + 1, K.flags.p);
-      }
+      A.spmv(c, 1, m, off, iter, K.P.p, d_dinv, K.V.p, K.RP.p, K.scal.p, K.partials.p, K.counter.p + 1, K.flags.p, tc_spmv);
       UFE_TRY(allreduce_sum(c, K.scal.p + p * KS_BANK + KS_D1, 1));
       {
         UFE_LAUNCH(c, TC_KRYLOV_VEC);
         k_ks_update_s<<<gv, kBlock, 0, st>>>(m, iter, K.R.p, K.V.p, S_own, K.scal.p, K.flags.p);
       }
       UFE_TRY(halo_exchange(c, rr, K.S.p));
-      {
-        UFE_LAUNCH(c, tc_spmv);
-        k_spmv_fused<Op, 2><<<gs, kBlock, 0, st>>>(op, m, off, iter, K.S.p, d_dinv, K.T.p, nullptr, K.scal.p, K.partials.p,
-                                                   K.counter.p + 2, K.flags.p);
-      }
+      A.spmv(c, 2, m, off, iter, K.S.p, d_dinv, K.T.p, nullptr, K.scal.p, K.partials.p, K.counter.p + 2, K.flags.p, tc_spmv);
       UFE_TRY(allreduce_sum(c, K.scal.p + p * KS_BANK + KS_ST, 2));
       {
         UFE_LAUNCH(c, TC_KRYLOV_VEC);

@@ -563,6 +563,7 @@ static int ensure_pattern(Ctx* c, const VelPar& p, unsigned long long bc_version
   s = stiff_args(c);
   { UFE_LAUNCH(c, TC_ASSEMBLY); k_stiff_fill_ind<<<grid, 128, 0, c->stream>>>(s); }
   UFE_CUDA(cudaGetLastError());
+  UFE_TRY(blk_build(c, V.blk, V.A, n, M.b.off()));
   V.pattern_key = key; V.pattern_valid = true;
   return 0;
 }
@@ -576,7 +577,14 @@ static int solve_linear_system(Ctx* c, const ufe_b200_config* cfg, double rtol, 
     UFE_LAUNCH(c, TC_EPILOGUE);
     k_interleave<<<grid_for(c, M.b.n_loc(), 128, 16), 128, 0, c->stream>>>(M.b.n_loc(), M.b.off(), V.u.p, V.v.p, V.uv.p + M.buv.off());
   }
-  return csr_ksp_solve(c, V.A, V.bb.p, V.uv.p, kp, TC_SPMV_STIFFNESS, its);
+  if (cfg->stiffness_format == 1) return csr_ksp_solve(c, V.A, V.bb.p, V.uv.p, kp, TC_SPMV_STIFFNESS, its);
+  UFE_CHECK(kp.ksp_type == UFE_KSP_BICGSTAB, "only BiCGStab is available for the (non-symmetric) stiffness matrix");
+  UFE_CHECK(kp.pc_type == UFE_PC_JACOBI || kp.pc_type == UFE_PC_NONE, "stiffness solve supports pc = jacobi | none");
+  if (!c->krylov) c->krylov = new Krylov();
+  UFE_TRY(c->krylov->dinv.alloc(V.A.m_loc));
+  UFE_TRY(csr_make_dinv(c, V.A, c->krylov->dinv.p, kp.pc_type));
+  UFE_TRY(blk_update_values(c, V.blk, V.A));
+  return bicgstab_solve_mat(c, BlkLauncher{&V.blk, c->mesh->b.off()}, V.A.cols, V.bb.p, c->krylov->dinv.p, V.uv.p, kp, TC_SPMV_STIFFNESS, its);
 }
 
 template <typename T>
@@ -918,6 +926,15 @@ int ufe_b200_get_stiffness(ufe_b200_handle h, int32_t* ptr, int32_t* ind, double
   UFE_CUDA(cudaStreamSynchronize(c->stream));
   for (int r = 0; r <= A.m_loc; ++r) ptr[r] += 1;
   for (long long k = 0; k < A.nnz; ++k) ind[k] += A.cols.lo;
+  return 0;
+}
+
+int ufe_b200_get_stiffness_storage_bytes(ufe_b200_handle h, long long* csr_bytes, long long* blocked_bytes) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && c->vel && c->vel->pattern_valid, "no stiffness matrix has been assembled yet");
+  const DevCsr& A = c->vel->A;
+  *csr_bytes = 12LL * A.nnz + 4LL * (A.m_loc + 1);
+  *blocked_bytes = 36LL * c->vel->blk.n_slots + 4LL * (c->vel->blk.n_slices + 1);
   return 0;
 }
 

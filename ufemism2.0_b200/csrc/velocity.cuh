@@ -1,6 +1,7 @@
 // Device state of the SSA/DIVA velocity solve (type_ice_velocity_solver_DIVA / _SSA,
 // reference: src/UFEMISM/types/ice_model_types.f90:149-197).  See velocity.cu.
 #pragma once
+#include "blk.cuh"
 #include "common.cuh"
 
 namespace ufe {
@@ -29,6 +30,7 @@ struct Velocity {
   DevCsr A;
   DBuf<int> row_kind;          // per matrix row: 0 free, 1 identity (prescribed / 'zero'), 2 'infinite'
   DBuf<double> bb, uv;         // load vector (owned rows), solution (extended buv range)
+  BlkMat blk;                  // 2x2-blocked sliced-ELL copy of A that the Krylov solver streams
   unsigned long long pattern_key = 0;
   bool pattern_valid = false;
   // --- reductions

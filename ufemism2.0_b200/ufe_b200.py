@@ -44,7 +44,7 @@ class Config(C.Structure):
         ("visc_it_nit", C.c_int32), ("do_include_SSADIVA_crossterms", C.c_int32), ("BC_u", C.c_int32 * 4),
         ("BC_v", C.c_int32 * 4), ("choice_sliding_law", C.c_int32), ("do_GL_subgrid_friction", C.c_int32),
         ("choice_ice_integration_method", C.c_int32), ("BC_H", C.c_int32 * 4), ("ksp_type", C.c_int32),
-        ("pc_type", C.c_int32), ("ksp_maxit", C.c_int32), ("write_diagnostics", C.c_int32), ("ksp_initial_guess_nonzero", C.c_int32), ("reserved", C.c_int32 * 5)]
+        ("pc_type", C.c_int32), ("ksp_maxit", C.c_int32), ("write_diagnostics", C.c_int32), ("ksp_initial_guess_nonzero", C.c_int32), ("stiffness_format", C.c_int32), ("reserved", C.c_int32 * 4)]
 
 
 def default_config():
@@ -168,6 +168,7 @@ def lib():
                                                      C.POINTER(C.c_int), c_ip, c_dp, c_dp]
     L.ufe_b200_get_stiffness_size.argtypes = [H, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.ufe_b200_get_stiffness.argtypes = [H, c_ip, c_ip, c_dp, c_dp]
+    L.ufe_b200_get_stiffness_storage_bytes.argtypes = [H, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
     for fn in (L.ufe_b200_solve_DIVA, L.ufe_b200_solve_SSA):
         fn.argtypes = [H, C.POINTER(Config), C.POINTER(IceInputs), C.POINTER(VelocityState), C.POINTER(C.c_int),
                        C.POINTER(C.c_int), c_ip, c_dp, c_dp]
@@ -196,7 +197,7 @@ ABI_SYMBOLS = [
     "ufe_b200_kernel_launches", "ufe_b200_ksp_solve", "ufe_b200_csr_register", "ufe_b200_csr_update_values", "ufe_b200_spmv",
     "ufe_b200_csr_release", "ufe_b200_mesh_create", "ufe_b200_mesh_destroy", "ufe_b200_mesh_ranges",
     "ufe_b200_calc_matrix_operators", "ufe_b200_set_operator", "ufe_b200_get_operator_size", "ufe_b200_get_operator",
-    "ufe_b200_apply_operator", "ufe_b200_solve_SSA_DIVA_linearised", "ufe_b200_get_stiffness_size", "ufe_b200_get_stiffness",
+    "ufe_b200_apply_operator", "ufe_b200_solve_SSA_DIVA_linearised", "ufe_b200_get_stiffness_size", "ufe_b200_get_stiffness", "ufe_b200_get_stiffness_storage_bytes",
     "ufe_b200_solve_DIVA", "ufe_b200_solve_SSA", "ufe_b200_velocity_upload", "ufe_b200_velocity_solve_resident",
     "ufe_b200_velocity_download", "ufe_b200_thickness_upload", "ufe_b200_pc_step_resident",
     "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA",
