@@ -1,0 +1,279 @@
+module ufe_b200_mod
+  ! ISO_C_BINDING layer between UFEMISM's Fortran host code and libufe_b200.so (include/ufe_b200.h).
+  !
+  ! This is the reference-side binding a maintainer adds to src/UPSY/basic/ (see INTEGRATION.md).  It is written
+  ! against the reference's own types (type_sparse_matrix_CSR_dp, type_mesh, C%...) and keeps the reference's
+  ! init_routine / finalise_routine / crash conventions, so resource_tracking.nc and checksum_logfile.txt stay
+  ! comparable.  NOTE: no Fortran compiler exists in the build image (SURVEY F3); this file is syntax-reviewed only,
+  ! the runnable stand-in that exercises the same C ABI is ufemism2.0_b200/ufe_b200.py + tests/.
+  !
+  ! Selected at run time by the new namelist key
+  !     choice_linear_algebra_backend_config = 'PETSc' (default) | 'B200'
+  ! (+ B200_KSP_type_config, B200_PC_type_config, B200_use_initial_guess_config, B200_stiffness_format_config).
+
+  use, intrinsic :: iso_c_binding
+  use precisions, only: dp
+  use mpi_basic, only: par
+  use mpi_f08, only: MPI_BCAST, MPI_BYTE, MPI_COMM_WORLD
+  use call_stack_and_comp_time_tracking, only: init_routine, finalise_routine, crash
+  use model_configuration, only: C
+  use CSR_sparse_matrix_type, only: type_sparse_matrix_CSR_dp
+  use mesh_types, only: type_mesh
+
+  implicit none
+
+  private
+
+  public :: ufe_b200_initialise, ufe_b200_finalise
+  public :: solve_matrix_equation_CSR_B200
+  public :: ufe_b200_upload_mesh, ufe_b200_destroy_mesh
+  public :: ufe_b200_fill_config, ufe_b200_config
+
+  type(c_ptr), save :: handle = c_null_ptr
+
+  ! ufe_b200_config of include/ufe_b200.h (same member order)
+  type, bind(C) :: ufe_b200_config
+    real(c_double) :: visc_it_norm_dUV_tol, visc_it_relax, visc_eff_min, vel_max
+    real(c_double) :: stress_balance_PETSc_rtol, stress_balance_PETSc_abstol
+    real(c_double) :: Glens_flow_law_exponent, Glens_flow_law_epsilon_sq_0
+    real(c_double) :: slid_delta_v, slid_Weertman_m, slid_Budd_q_plastic, slid_Budd_u_threshold, slid_ZI_ut, slid_ZI_p, slid_beta_max
+    real(c_double) :: subgrid_friction_exponent_on_B_grid, Hi_min, uniform_Glens_flow_factor
+    real(c_double) :: refgeo_idealised_SSA_icestream_Hi, refgeo_idealised_SSA_icestream_dhdx
+    real(c_double) :: refgeo_idealised_SSA_icestream_L, refgeo_idealised_SSA_icestream_m
+    real(c_double) :: dHi_semiimplicit_fs, dHi_PETSc_rtol, dHi_PETSc_abstol, dt_ice_min, dt_ice_max
+    real(c_double) :: ice_density, seawater_density, grav
+    integer(c_int32_t) :: visc_it_nit, do_include_SSADIVA_crossterms
+    integer(c_int32_t) :: BC_u(4), BC_v(4)
+    integer(c_int32_t) :: choice_sliding_law, do_GL_subgrid_friction, choice_ice_integration_method
+    integer(c_int32_t) :: BC_H(4)
+    integer(c_int32_t) :: ksp_type, pc_type, ksp_maxit, write_diagnostics, ksp_initial_guess_nonzero, stiffness_format
+    integer(c_int32_t) :: reserved(4)
+  end type ufe_b200_config
+
+  ! ufe_b200_mesh_desc of include/ufe_b200.h
+  type, bind(C) :: ufe_b200_mesh_desc
+    integer(c_int32_t) :: nV, nTri, nE, nC_mem, nz
+    real(c_double)     :: xmin, xmax, ymin, ymax
+    type(c_ptr) :: V, nC, C, niTri, iTri, VBI, Tri, TriC, TriBI, TriGC, A, Cw, D_x, D_y, D, VE, ETri, zeta
+  end type ufe_b200_mesh_desc
+
+  interface
+
+    function c_ufe_b200_get_unique_id( id128) bind(C, name='ufe_b200_get_unique_id') result( ierr)
+      import :: c_int, c_char
+      character(kind=c_char), intent(inout) :: id128(128)
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_init( device, rank, nranks, id128, h) bind(C, name='ufe_b200_init') result( ierr)
+      import :: c_int, c_char, c_ptr
+      integer(c_int), value :: device, rank, nranks
+      character(kind=c_char), intent(in) :: id128(128)
+      type(c_ptr), intent(out) :: h
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_finalize( h) bind(C, name='ufe_b200_finalize') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_last_error() bind(C, name='ufe_b200_last_error') result( msg)
+      import :: c_ptr
+      type(c_ptr) :: msg
+    end function
+
+    function c_ufe_b200_ksp_solve( h, m_glob, m_loc, i1, ptr, ind, val, bb, xx, rtol, abstol, maxit, ksp_type, pc_type, n_its) &
+      bind(C, name='ufe_b200_ksp_solve') result( ierr)
+      import :: c_int, c_int32_t, c_double, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: m_glob, m_loc, i1, maxit, ksp_type, pc_type
+      integer(c_int32_t), intent(in) :: ptr(*), ind(*)
+      real(c_double), intent(in) :: val(*), bb(*)
+      real(c_double), intent(inout) :: xx(*)
+      real(c_double), value :: rtol, abstol
+      integer(c_int), intent(out) :: n_its
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_mesh_create( h, mesh) bind(C, name='ufe_b200_mesh_create') result( ierr)
+      import :: c_int, c_ptr, ufe_b200_mesh_desc
+      type(c_ptr), value :: h
+      type(ufe_b200_mesh_desc), intent(in) :: mesh
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_mesh_destroy( h) bind(C, name='ufe_b200_mesh_destroy') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_calc_matrix_operators( h) bind(C, name='ufe_b200_calc_matrix_operators') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_solve_SSA_DIVA_linearised( h, cfg, u_b, v_b, N_b, dN_dx_b, dN_dy_b, beta_b, tau_dx_b, tau_dy_b, &
+      u_b_prev, v_b_prev, rtol, abstol, n_Axb_its, BC_prescr_mask_b, BC_prescr_u_b, BC_prescr_v_b) &
+      bind(C, name='ufe_b200_solve_SSA_DIVA_linearised') result( ierr)
+      import :: c_int, c_int32_t, c_double, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      real(c_double), intent(inout) :: u_b(*), v_b(*), u_b_prev(*), v_b_prev(*)
+      real(c_double), intent(in) :: N_b(*), dN_dx_b(*), dN_dy_b(*), beta_b(*), tau_dx_b(*), tau_dy_b(*)
+      real(c_double), value :: rtol, abstol
+      integer(c_int), intent(out) :: n_Axb_its
+      integer(c_int32_t), intent(in) :: BC_prescr_mask_b(*)
+      real(c_double), intent(in) :: BC_prescr_u_b(*), BC_prescr_v_b(*)
+      integer(c_int) :: ierr
+    end function
+
+  end interface
+
+contains
+
+  subroutine check( ierr, where)
+    ! Map a non-zero status to the reference's crash() (src/UPSY/basic/crash_mod.f90:17-34)
+    integer(c_int),   intent(in) :: ierr
+    character(len=*), intent(in) :: where
+    character(len=1024) :: msg
+    character(kind=c_char), pointer :: cmsg(:)
+    integer :: i
+    if (ierr == 0) return
+    msg = ''
+    call c_f_pointer( c_ufe_b200_last_error(), cmsg, [1024])
+    do i = 1, 1024
+      if (cmsg( i) == c_null_char) exit
+      msg( i:i) = cmsg( i)
+    end do
+    call crash( trim( where) // ': ' // trim( msg))
+  end subroutine check
+
+  subroutine ufe_b200_initialise
+    ! Called once after initialise_parallelisation (src/UFEMISM/main/UFEMISM_program.f90:55): one rank <-> one GPU.
+    character(len=1024), parameter :: routine_name = 'ufe_b200_initialise'
+    character(kind=c_char) :: id128(128)
+    integer :: ierr
+    call init_routine( routine_name)
+    id128 = c_null_char
+    if (par%n > 1) then
+      if (par%primary) call check( c_ufe_b200_get_unique_id( id128), routine_name)
+      call MPI_BCAST( id128, 128, MPI_BYTE, 0, MPI_COMM_WORLD, ierr)
+    end if
+    call check( c_ufe_b200_init( -1_c_int, int( par%i, c_int), int( par%n, c_int), id128, handle), routine_name)
+    call finalise_routine( routine_name)
+  end subroutine ufe_b200_initialise
+
+  subroutine ufe_b200_finalise
+    character(len=1024), parameter :: routine_name = 'ufe_b200_finalise'
+    call init_routine( routine_name)
+    if (c_associated( handle)) call check( c_ufe_b200_finalize( handle), routine_name)
+    handle = c_null_ptr
+    call finalise_routine( routine_name)
+  end subroutine ufe_b200_finalise
+
+  subroutine solve_matrix_equation_CSR_B200( AA, bb, xx, rtol, abstol, n_Axb_its)
+    ! Drop-in for solve_matrix_equation_CSR_PETSc (src/UPSY/basic/petsc_basic.f90:32-33); same arguments, same meaning:
+    ! AA finalised, xx ignored on input (zero initial guess), n_Axb_its = iteration count, non-convergence silent.
+    type(type_sparse_matrix_CSR_dp),    intent(in   ) :: AA
+    real(dp), dimension(:),             intent(in   ) :: bb
+    real(dp), dimension(:),             intent(inout) :: xx
+    real(dp),                           intent(in   ) :: rtol, abstol
+    integer,                            intent(  out) :: n_Axb_its
+    character(len=1024), parameter :: routine_name = 'solve_matrix_equation_CSR_B200'
+    integer(c_int) :: its
+    call init_routine( routine_name)
+    if (.not. AA%is_finalised) call crash('A should be finalised before calling solve_matrix_equation_CSR_B200')
+    ! AA%ptr( AA%i1: AA%i2+1) holds 1-based offsets into the local ind/val (CSR_matrix_basics.f90:63-78)
+    call check( c_ufe_b200_ksp_solve( handle, int( AA%m, c_int), int( AA%m_loc, c_int), int( AA%i1, c_int), &
+      AA%ptr( AA%i1: AA%i2+1), AA%ind, AA%val, bb, xx, rtol, abstol, 2000_c_int, C%B200_KSP_type, C%B200_PC_type, its), routine_name)
+    n_Axb_its = int( its)
+    call finalise_routine( routine_name)
+  end subroutine solve_matrix_equation_CSR_B200
+
+  subroutine ufe_b200_upload_mesh( mesh)
+    ! Called at the end of calc_all_secondary_mesh_data / instead of calc_all_matrix_operators_mesh
+    ! (src/UPSY/mesh/mesh_secondary.f90:31-70, mesh_disc_calc_matrix_operators_2D.f90:26-59).
+    type(type_mesh), target, intent(in) :: mesh
+    character(len=1024), parameter :: routine_name = 'ufe_b200_upload_mesh'
+    type(ufe_b200_mesh_desc) :: d
+    call init_routine( routine_name)
+    d%nV = mesh%nV; d%nTri = mesh%nTri; d%nE = mesh%nE; d%nC_mem = mesh%nC_mem; d%nz = mesh%nz
+    d%xmin = mesh%xmin; d%xmax = mesh%xmax; d%ymin = mesh%ymin; d%ymax = mesh%ymax
+    d%V = c_loc( mesh%V); d%nC = c_loc( mesh%nC); d%C = c_loc( mesh%C); d%niTri = c_loc( mesh%niTri); d%iTri = c_loc( mesh%iTri)
+    d%VBI = c_loc( mesh%VBI); d%Tri = c_loc( mesh%Tri); d%TriC = c_loc( mesh%TriC); d%TriBI = c_loc( mesh%TriBI)
+    d%TriGC = c_loc( mesh%TriGC); d%A = c_loc( mesh%A); d%Cw = c_loc( mesh%Cw); d%D_x = c_loc( mesh%D_x); d%D_y = c_loc( mesh%D_y)
+    d%D = c_loc( mesh%D); d%VE = c_loc( mesh%VE); d%ETri = c_loc( mesh%ETri); d%zeta = c_loc( mesh%zeta)
+    call check( c_ufe_b200_mesh_create( handle, d), routine_name)
+    call check( c_ufe_b200_calc_matrix_operators( handle), routine_name)
+    call finalise_routine( routine_name)
+  end subroutine ufe_b200_upload_mesh
+
+  subroutine ufe_b200_destroy_mesh
+    ! Called from the mesh finaliser and before update_mesh -> remap_velocity_solver (UFEMISM_main_model.f90:1211)
+    if (c_associated( handle)) call check( c_ufe_b200_mesh_destroy( handle), 'ufe_b200_destroy_mesh')
+  end subroutine ufe_b200_destroy_mesh
+
+  subroutine ufe_b200_fill_config( cfg)
+    ! Copy the C% scalars the path reads into the plain struct that crosses the ABI
+    type(ufe_b200_config), intent(out) :: cfg
+    cfg%visc_it_norm_dUV_tol = C%visc_it_norm_dUV_tol; cfg%visc_it_relax = C%visc_it_relax; cfg%visc_eff_min = C%visc_eff_min
+    cfg%vel_max = C%vel_max; cfg%stress_balance_PETSc_rtol = C%stress_balance_PETSc_rtol
+    cfg%stress_balance_PETSc_abstol = C%stress_balance_PETSc_abstol
+    cfg%Glens_flow_law_exponent = C%Glens_flow_law_exponent; cfg%Glens_flow_law_epsilon_sq_0 = C%Glens_flow_law_epsilon_sq_0
+    cfg%slid_delta_v = C%slid_delta_v; cfg%slid_Weertman_m = C%slid_Weertman_m; cfg%slid_Budd_q_plastic = C%slid_Budd_q_plastic
+    cfg%slid_Budd_u_threshold = C%slid_Budd_u_threshold; cfg%slid_ZI_ut = C%slid_ZI_ut; cfg%slid_ZI_p = C%slid_ZI_p
+    cfg%slid_beta_max = C%slid_beta_max; cfg%subgrid_friction_exponent_on_B_grid = C%subgrid_friction_exponent_on_B_grid
+    cfg%Hi_min = C%Hi_min; cfg%uniform_Glens_flow_factor = C%uniform_Glens_flow_factor
+    cfg%refgeo_idealised_SSA_icestream_Hi = C%refgeo_idealised_SSA_icestream_Hi
+    cfg%refgeo_idealised_SSA_icestream_dhdx = C%refgeo_idealised_SSA_icestream_dhdx
+    cfg%refgeo_idealised_SSA_icestream_L = C%refgeo_idealised_SSA_icestream_L
+    cfg%refgeo_idealised_SSA_icestream_m = C%refgeo_idealised_SSA_icestream_m
+    cfg%dHi_semiimplicit_fs = C%dHi_semiimplicit_fs; cfg%dHi_PETSc_rtol = C%dHi_PETSc_rtol; cfg%dHi_PETSc_abstol = C%dHi_PETSc_abstol
+    cfg%dt_ice_min = C%dt_ice_min; cfg%dt_ice_max = C%dt_ice_max
+    cfg%ice_density = 917.0_dp; cfg%seawater_density = 1027.0_dp; cfg%grav = 9.81_dp   ! parameters.f90:19-24
+    cfg%visc_it_nit = C%visc_it_nit
+    cfg%do_include_SSADIVA_crossterms = merge( 1, 0, C%do_include_SSADIVA_crossterms)
+    cfg%BC_u = [bc_code( C%BC_u_north), bc_code( C%BC_u_east), bc_code( C%BC_u_south), bc_code( C%BC_u_west)]
+    cfg%BC_v = [bc_code( C%BC_v_north), bc_code( C%BC_v_east), bc_code( C%BC_v_south), bc_code( C%BC_v_west)]
+    cfg%BC_H = [bc_code( C%BC_H_north), bc_code( C%BC_H_east), bc_code( C%BC_H_south), bc_code( C%BC_H_west)]
+    cfg%choice_sliding_law = sliding_code( C%choice_sliding_law)
+    cfg%do_GL_subgrid_friction = merge( 1, 0, C%do_GL_subgrid_friction)
+    cfg%choice_ice_integration_method = merge( 0, 1, C%choice_ice_integration_method == 'explicit')
+    cfg%ksp_type = C%B200_KSP_type; cfg%pc_type = C%B200_PC_type; cfg%ksp_maxit = 2000
+    cfg%write_diagnostics = merge( 1, 0, C%do_write_checksum_log)
+    cfg%ksp_initial_guess_nonzero = merge( 1, 0, C%B200_use_initial_guess)
+    cfg%stiffness_format = C%B200_stiffness_format
+    cfg%reserved = 0
+  end subroutine ufe_b200_fill_config
+
+  pure function bc_code( name) result( code)
+    character(len=*), intent(in) :: name
+    integer(c_int32_t) :: code
+    select case (trim( name))
+    case ('infinite'); code = 0
+    case ('zero');     code = 1
+    case default;      code = -1   ! periodic_ISMIP-HOM / infinite_SSA_icestream are not offered by the B200 path
+    end select
+  end function bc_code
+
+  pure function sliding_code( name) result( code)
+    character(len=*), intent(in) :: name
+    integer(c_int32_t) :: code
+    select case (trim( name))
+    case ('no_sliding');   code = 0
+    case ('Weertman');     code = 1
+    case ('Coulomb');      code = 2
+    case ('Budd');         code = 3
+    case ('Tsai2015');     code = 4
+    case ('Schoof2005');   code = 5
+    case ('Zoet-Iverson'); code = 6
+    case ('idealised');    code = 7   ! SSA_icestream only
+    case default;          code = -1
+    end select
+  end function sliding_code
+
+end module ufe_b200_mod
