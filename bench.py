@@ -154,12 +154,14 @@ def h_for_vertices(nv):
     return float(np.sqrt(L * L / (nv * np.sqrt(3.0) / 2.0)))
 
 
-def make_workload(nv):
+def make_workload(nv, pc="jacobi"):
+    import ufe_b200 as ub
     import workloads as wl
     w = wl.mismip_mod(h_for_vertices(nv), half_width=HALF_WIDTH)
     cfg = w.cfg                      # config_MISMIP_8km_spinup_for_scaling.cfg physics
     cfg.write_diagnostics = 0
     cfg.ksp_initial_guess_nonzero = 1  # time stepping starts each Krylov solve from the previous solution
+    cfg.pc_type = ub.PC_MG if pc == "mg" else ub.PC_JACOBI   # the oracle ignores this key (it has its own ksp switch)
     return w
 
 
@@ -271,8 +273,10 @@ def run_b200(args, rank, world, rdv, log):
         uid = rdv.bcast(ub.Context.unique_id() if rank == 0 else None, 128)
     ctx = ub.Context(device=local_rank, rank=rank, nranks=world, unique_id=uid)
     t0 = time.time()
-    w = make_workload(args.nv)
+    w = make_workload(args.nv, args.pc)
     m, cfg = w.mesh, w.cfg
+    if args.pc == "mg":
+        ctx.set_mg_params(nu_pre=args.mg_nu, nu_post=args.mg_nu, omega=args.mg_omega, overcorr=args.mg_overcorr, w_levels=args.mg_w_levels, fp32=args.mg_fp32)
     log(f"mesh nV={m.nV} nTri={m.nTri} nE={m.nE} generated in {time.time() - t0:.1f}s")
     t0 = time.time()
     ctx.mesh_create(m)
@@ -290,6 +294,9 @@ def run_b200(args, rank, world, rdv, log):
     ub.check(L.ufe_b200_velocity_upload(ctx.h, C.byref(ice), C.byref(st)))
     ub.check(L.ufe_b200_velocity_solve_resident(ctx.h, C.byref(cfg), 1, C.byref(nv_), C.byref(na_)))
     log(f"spin-up: {nv_.value} viscosity its, {na_.value} Krylov its in {time.time() - t0:.1f}s")
+    mg_info = ctx.mg_info() if args.pc == "mg" else None
+    if mg_info:
+        log(f"multigrid hierarchy: {mg_info}")
     io, keep_io = thickness_io(w, sl_a, w.f["Hi"][sl_a])
     ub.check(L.ufe_b200_thickness_upload(ctx.h, C.byref(io)))
 
@@ -318,8 +325,12 @@ def run_b200(args, rank, world, rdv, log):
     launches = ctx.kernel_launches() - launches0
     clocks = sampler.stop() if rank == 0 else None
     L.ufe_b200_timing_enable(ctx.h, 0)
-    spmv_ms, spmv_n = ctx.timing("spmv_stiffness")
-    classes = {c: ctx.timing(c) for c in ("spmv_stiffness", "krylov_vec", "assembly", "column", "tri", "epilogue", "thickness")}
+    classes = {c: ctx.timing(c) for c in ("spmv_stiffness", "mg_fine", "mg_vec", "mg_coarse", "mg_setup", "krylov_vec", "assembly", "column", "tri",
+                                          "epilogue", "thickness")}
+    # dominant kernel family: both stream the level-0 stiffness matrix once per launch (k_spmv_blk in the Krylov recurrence,
+    # k_mg_sweep = the same pass fused with the block-Jacobi update / residual inside the multigrid cycle)
+    top = "mg_fine" if classes["mg_fine"][0] > classes["spmv_stiffness"][0] else "spmv_stiffness"
+    spmv_ms, spmv_n = classes[top]
     log("kernel classes (ms, launches): " + ", ".join(f"{k}={v[0]:.1f}/{v[1]}" for k, v in classes.items()))
 
     # ---- end-to-end leg (`e2e`): the same three phases through the host-buffer ABI calls, copies inside the timed region
@@ -377,6 +388,15 @@ def run_b200(args, rank, world, rdv, log):
         # B_spmv = 12 nnz + 4 (rows + 1) + 8 rows (y) + 8 cols (x), for the rank's row block
         B_spmv = csr_b.value + 8 * rows_loc + 8 * rows_loc
         B_streamed = blk_b.value + 8 * rows_loc * 4   # blocks + y + x + Jacobi diagonal + dot-product operand
+        if top == "mg_fine":
+            # sweeps also read the right-hand side (8 B/row); half of them the diagonal blocks (16 B/row) and the old iterate (8 B/row)
+            B_spmv += 8 * rows_loc
+            B_streamed = (mg_info["fine_bytes"] if mg_info else blk_b.value) + 8 * rows_loc * 5
+        kernel_name = ("k_mg_sweep level 0 (stiffness-matrix pass fused with block-Jacobi update / residual inside the multigrid cycle)" if top == "mg_fine"
+                       else "k_spmv_blk (stiffness-matrix SpMV with fused Jacobi + dot products inside BiCGStab)")
+        krylov_desc = ("BiCGStab + aggregation multigrid (%d levels %s, %d+%d block-Jacobi sweeps, omega %.2f, %s matrix storage in the preconditioner)"
+                       % (mg_info["levels"], mg_info["nodes"], args.mg_nu, args.mg_nu, args.mg_omega, "FP32" if args.mg_fp32 else "FP64")
+                       if mg_info else "BiCGStab + Jacobi")
         avg_ms = spmv_ms / max(spmv_n, 1)
         achieved = B_spmv / (avg_ms * 1e-3) / 1e9 if spmv_n else 0.0
         res = {
@@ -387,12 +407,12 @@ def run_b200(args, rank, world, rdv, log):
                                    f"{m.nV} vertices / {m.nTri} triangles, nz={m.nz}, dt={DT} yr, physics of config_MISMIP_8km_spinup_for_scaling.cfg",
                        "n_vertices": int(m.nV), "partition": f"{world} contiguous row blocks (partition_list)",
                        "l2_policy": "inputs larger than L2 (stiffness matrix 4 GB >> 126 MB)",
-                       "krylov": "BiCGStab + Jacobi, rtol 1e-4 / abstol 1e-3, initial guess = previous solution (ksp_initial_guess_nonzero=1)",
+                       "krylov": krylov_desc + ", rtol 1e-4 / abstol 1e-3, initial guess = previous solution (ksp_initial_guess_nonzero=1)",
                        "per_step": {"viscosity_its": tot[0] / args.steps, "krylov_its_velocity": tot[1] / args.steps, "krylov_its_thickness": tot[2] / args.steps}},
             "e2e": {"value": k_e2e / e2e_s, "unit": "velocity solves/s", "h2d_bytes_per_step": bytes_in[0] // k_e2e, "d2h_bytes_per_step": bytes_out[0] // k_e2e,
                     "steps": k_e2e},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_spmv_blk (stiffness-matrix SpMV with fused Jacobi + dot products inside BiCGStab)", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak if peak else None, "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
                          "algorithmic_bytes_per_launch": B_spmv, "streamed_bytes_per_launch": B_streamed,
                          "streamed_GBps": B_streamed / (avg_ms * 1e-3) / 1e9 if spmv_n else 0.0, "avg_launch_ms": avg_ms, "launches": spmv_n, "traffic": None,
@@ -412,6 +432,12 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--nv", type=int, default=4_000_000, help="target number of vertices (config 3: ~4M)")
     ap.add_argument("--cpu-nv", type=int, default=60_000, help="vertices of the bounded CPU sample")
+    ap.add_argument("--pc", default="jacobi", choices=["jacobi", "mg"], help="preconditioner of the stiffness-matrix solve on the device")
+    ap.add_argument("--mg-nu", type=int, default=1)
+    ap.add_argument("--mg-omega", type=float, default=0.7)
+    ap.add_argument("--mg-overcorr", type=float, default=1.0)
+    ap.add_argument("--mg-w-levels", type=int, default=3)
+    ap.add_argument("--mg-fp32", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     args = ap.parse_args()

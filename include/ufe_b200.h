@@ -30,7 +30,8 @@ typedef struct ufe_b200_ctx* ufe_b200_handle;
 
 /* ---- enumerations ---------------------------------------------------------------------------- */
 enum { UFE_KSP_BICGSTAB = 0, UFE_KSP_CG = 1 };                       /* north_star (b) */
-enum { UFE_PC_JACOBI = 0, UFE_PC_NONE = 1, UFE_PC_BJACOBI2 = 2, UFE_PC_NEUMANN = 3 };
+enum { UFE_PC_JACOBI = 0, UFE_PC_NONE = 1, UFE_PC_BJACOBI2 = 2, UFE_PC_NEUMANN = 3,
+       UFE_PC_MG = 4 };   /* aggregation multigrid, stiffness-matrix solve only (new key B200_PC_type_config = 'multigrid') */
 enum { UFE_BC_INFINITE = 0, UFE_BC_ZERO = 1 };                        /* C%BC_{u,v,H}_{north,east,south,west} */
 enum { UFE_SLID_NO_SLIDING = 0, UFE_SLID_WEERTMAN = 1, UFE_SLID_COULOMB = 2, UFE_SLID_BUDD = 3, UFE_SLID_TSAI2015 = 4,
        UFE_SLID_SCHOOF2005 = 5, UFE_SLID_ZOET_IVERSON = 6, UFE_SLID_IDEALISED_SSA_ICESTREAM = 7 };
@@ -177,6 +178,20 @@ int ufe_b200_get_stiffness_size(ufe_b200_handle h, int* m_loc, int* nnz_loc);
 int ufe_b200_get_stiffness(ufe_b200_handle h, int32_t* ptr, int32_t* ind, double* val, double* bb);
 /* bytes of matrix data one SpMV streams: the CSR arrays (12 nnz + 4 (rows+1)) and the 2x2-blocked sliced-ELL copy (36 per block slot) */
 int ufe_b200_get_stiffness_storage_bytes(ufe_b200_handle h, long long* csr_bytes, long long* blocked_bytes);
+/* Knobs of the multigrid preconditioner (pc_type = UFE_PC_MG) that replaces PETSc's one-level PC behind
+ * solve_matrix_equation_CSR_PETSc (src/UPSY/basic/petsc_basic.f90:125-129, 193) for the SSA/DIVA system: block-Jacobi sweeps before / after the
+ * coarse correction, damping, correction scaling, number of coarse levels visited twice per cycle, FP32 storage of the preconditioner's
+ * matrix values (0/1), largest coarsest level solved by a dense inverse.  Negative / NaN arguments keep the current value. */
+int ufe_b200_set_mg_params(ufe_b200_handle h, int nu_pre, int nu_post, double omega, double overcorr, int w_levels, int fp32, int dense_max);
+/* Hierarchy of the last multigrid build: number of levels, nodes per level (up to 16 entries), matrix bytes one fine-level smoothing sweep
+ * streams, total matrix bytes of all coarse levels, host seconds of the one-off pattern phase. */
+int ufe_b200_get_mg_info(ufe_b200_handle h, int* n_levels, int* nodes_per_level, long long* fine_bytes, long long* coarse_bytes, double* setup_s);
+/* Host logic of the multigrid pattern phase, exposed for the CPU test-suite (no GPU involved, no handle): one coarsening step of a 2x2-block
+ * pattern given in the solver's sliced-ELL layout (slices of 32 nodes; slice_ptr[(n+31)/32 + 1] in k-steps; col[k*32 + lane] = extended
+ * index of the neighbour node, own node = off + t).  The first call computes and reports sizes, the second copies the arrays out:
+ * agg[n], coarse_slice_ptr[(nc+31)/32 + 1], coarse_col[coarse_slots], gal_ptr[coarse_slots + 1], gal_src[gather_entries]. */
+int ufe_b200_mg_host_transfer(int n, int off, const int32_t* slice_ptr, const int32_t* col, int* nc, long long* coarse_slots, long long* gather_entries);
+int ufe_b200_mg_host_transfer_get(int32_t* agg, int32_t* coarse_slice_ptr, int32_t* coarse_col, int32_t* gal_ptr, int32_t* gal_src);
 
 /* Inputs of the velocity solve taken from type_ice_model / type_bed_roughness_model (owned slices). */
 typedef struct ufe_b200_ice_inputs {

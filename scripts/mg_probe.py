@@ -1,0 +1,56 @@
+"""Ad-hoc GPU probe: Krylov iterations and time of the first viscosity iterations of a cold DIVA solve for several preconditioner
+settings (not the bench contract).  usage: mg_probe.py NV [NVISC]"""
+import ctypes as C
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "ufemism2.0_b200")); sys.path.insert(0, ROOT)
+import numpy as np  # noqa
+import bench  # noqa
+import ufe_b200 as ub  # noqa
+
+nv = int(sys.argv[1]); nvisc = int(sys.argv[2]) if len(sys.argv) > 2 else 2
+w = bench.make_workload(nv)
+m, cfg = w.mesh, w.cfg
+ctx = ub.Context(device=0)
+ctx.mesh_create(m); ctx.calc_matrix_operators()
+cfg.visc_it_nit = nvisc - 1; cfg.visc_it_norm_dUV_tol = 1e-30; cfg.write_diagnostics = 0
+cfg.ksp_initial_guess_nonzero = 1
+ice = w.ice_inputs()
+L = ub.lib()
+print(f"mesh nV={m.nV} nTri={m.nTri}", flush=True)
+
+SETTINGS = [("jacobi", None)]
+for fp32 in (0, 1):
+    for (nu, wl_, oc) in ((1, 3, 1.0), (1, 0, 1.0), (2, 0, 1.0), (2, 3, 1.0), (1, 5, 1.0), (1, 3, 1.3), (2, 0, 1.5)):
+        SETTINGS.append((f"mg nu={nu} w_levels={wl_} overcorr={oc} fp32={fp32}", dict(nu_pre=nu, nu_post=nu, w_levels=wl_, overcorr=oc, fp32=fp32)))
+if len(sys.argv) > 3:
+    SETTINGS = [s for s in SETTINGS if any(k in s[0] for k in sys.argv[3].split(","))]
+
+ref = None
+for name, prm in SETTINGS:
+    st, arrs = ub.alloc_velocity_state(m.nV, m.nTri, m.nz, fields=["u_vav_b", "v_vav_b"])
+    ub.check(L.ufe_b200_velocity_upload(ctx.h, C.byref(ice), C.byref(st)))
+    cfg.pc_type = ub.PC_JACOBI if prm is None else ub.PC_MG
+    if prm:
+        ctx.set_mg_params(**prm)
+    L.ufe_b200_timing_reset(ctx.h); L.ufe_b200_timing_enable(ctx.h, 1)
+    a, b = C.c_int(), C.c_int()
+    l0 = ctx.kernel_launches()
+    t0 = time.time()
+    ub.check(L.ufe_b200_velocity_solve_resident(ctx.h, C.byref(cfg), 1, C.byref(a), C.byref(b)))
+    dt = time.time() - t0
+    L.ufe_b200_timing_enable(ctx.h, 0)
+    ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
+    u = arrs["u_vav_b"].copy()
+    if ref is None:
+        ref = u
+    cls = {c: ctx.timing(c) for c in ("spmv_stiffness", "mg_fine", "mg_vec", "mg_coarse", "mg_setup", "krylov_vec")}
+    info = ctx.mg_info() if prm else {}
+    print(f"{name:48s}: {a.value} visc its, {b.value:5d} Krylov its, {dt:8.3f} s, launches {ctx.kernel_launches() - l0:7d}, "
+          f"rel diff vs first {np.linalg.norm(u - ref) / np.linalg.norm(ref):.2e}  "
+          + " ".join(f"{k}={v[0]:.0f}ms/{v[1]}" for k, v in cls.items() if v[1])
+          + (f"  levels={info['nodes']} setup_host={info['setup_s']:.2f}s" if info else ""), flush=True)
+ctx.close()

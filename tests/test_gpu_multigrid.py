@@ -1,0 +1,112 @@
+"""GPU: aggregation-multigrid preconditioned BiCGStab (pc_type = UFE_PC_MG) on the SSA/DIVA stiffness matrix, through the C ABI.
+The oracle solves the same linear systems with the reference's default PETSc configuration (GMRES(30) + ILU(0)); at tight
+tolerance every Krylov method converges to A^-1 b, so the multigrid path is held to the same 1e-6 relative L2 as the Jacobi path."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+import ufe_b200 as ub
+import workloads as wl
+from test_gpu_velocity import _linearised, _solve_gpu, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def setup():
+    w = wl.mismip_mod(2.0e4)
+    ctx = ub.Context(device=0)
+    ctx.mesh_create(w.mesh)
+    ctx.calc_matrix_operators()
+    o = ol.OracleMesh(w.mesh)
+    o.calc_matrix_operators()
+    yield w, ctx, o
+    ctx.close()
+
+
+def _coefficients(m, seed=3):
+    rng = np.random.default_rng(seed)
+    N_b = 1e10 * (1 + 0.5 * rng.random(m.nTri)); dNx = 1e3 * rng.standard_normal(m.nTri); dNy = 1e3 * rng.standard_normal(m.nTri)
+    beta = 1e3 * rng.random(m.nTri) * (rng.random(m.nTri) < 0.6)      # 40 % floating triangles (no basal friction)
+    tdx = 1e4 * rng.standard_normal(m.nTri); tdy = 1e4 * rng.standard_normal(m.nTri)
+    return N_b, dNx, dNy, beta, tdx, tdy
+
+
+@pytest.mark.parametrize("variant", ["fp64", "fp32_storage", "bc_zero", "prescribed", "v22"])
+def test_linearised_solve_with_multigrid(setup, variant):
+    w, ctx, o = setup
+    m = w.mesh
+    co = _coefficients(m)
+    cfg = wl.scaling_config()
+    bc = None
+    ctx.set_mg_params(nu_pre=1, nu_post=1, omega=0.7, overcorr=1.0, w_levels=3, fp32=0)
+    if variant == "fp32_storage":
+        ctx.set_mg_params(fp32=1)
+    if variant == "v22":
+        ctx.set_mg_params(nu_pre=2, nu_post=2, w_levels=0)
+    if variant == "bc_zero":
+        cfg.BC_u[0] = ub.BC_ZERO; cfg.BC_v[1] = ub.BC_ZERO; cfg.BC_u[3] = ub.BC_ZERO
+    if variant == "prescribed":
+        rng = np.random.default_rng(9)
+        bm = (rng.random(m.nTri) < 0.05).astype(np.int32)
+        bc = (bm, 10.0 * rng.standard_normal(m.nTri), 10.0 * rng.standard_normal(m.nTri))
+    cfg.pc_type = ub.PC_JACOBI
+    uj, vj, its_j = _linearised(ctx, cfg, m, *co, 1e-12, 1e-30, bc)
+    cfg.pc_type = ub.PC_MG
+    u, v, its = _linearised(ctx, cfg, m, *co, 1e-12, 1e-30, bc)
+    info = ctx.mg_info()
+    assert info["levels"] >= 3 and all(a > 2 * b for a, b in zip(info["nodes"], info["nodes"][1:])), info
+    optr, oind, oval, obb = o.assemble(cfg, *co, *(bc or (None, None, None)))
+    xo, its_o, rc = ol.ksp_solve(optr, oind, oval, obb, 1e-12, 1e-30, ksp=ol.KSP_GMRES_ILU0)
+    assert rc == 0
+    uv = np.empty(2 * m.nTri); uv[0::2] = u; uv[1::2] = v
+    assert rel_l2(uv, xo) < 1e-6, (variant, its, its_o, rel_l2(uv, xo))          # north_star tolerance, against the reference's default KSP
+    assert rel_l2(u, uj) < 1e-7 and rel_l2(v, vj) < 1e-7
+    assert 0 < its < its_j / 3, (its, its_j)                                      # the point of the preconditioner
+    ctx.set_mg_params(nu_pre=1, nu_post=1, omega=0.7, overcorr=1.0, w_levels=3, fp32=0)
+
+
+def test_diva_solve_with_multigrid_matches_oracle(setup):
+    w, ctx, o = setup
+    m = w.mesh
+    cfg = wl.scaling_config()
+    cfg.pc_type = ub.PC_MG
+    cfg.stress_balance_PETSc_rtol = 1e-12; cfg.stress_balance_PETSc_abstol = 1e-30
+    ice = w.ice_inputs()
+    g, nv, na = _solve_gpu(ctx, cfg, 1, ice, m)
+    st2, r = ub.alloc_velocity_state(m.nV, m.nTri, m.nz)
+    cfg_o = wl.scaling_config()
+    cfg_o.stress_balance_PETSc_rtol = 1e-12; cfg_o.stress_balance_PETSc_abstol = 1e-30
+    rc, nv2, na2 = o.solve_velocity(cfg_o, 1, ice, st2, ksp=ol.KSP_GMRES_ILU0)
+    assert rc == 0 and nv == nv2
+    for f in ("u_vav_b", "v_vav_b", "u_3D_b", "tau_bx_b", "eta_3D_b"):
+        assert rel_l2(g[f], r[f]) < 1e-6, (f, rel_l2(g[f], r[f]))
+
+
+def test_multigrid_with_initial_guess_and_config_tolerance(setup):
+    """the bench configuration: rtol 1e-4, warm start; the nonlinear solve lands on the same velocity field"""
+    w, ctx, o = setup
+    m = w.mesh
+    ice = w.ice_inputs()
+    res = []
+    for pc in (ub.PC_JACOBI, ub.PC_MG):
+        cfg = wl.scaling_config()
+        cfg.pc_type = pc
+        cfg.ksp_initial_guess_nonzero = 1
+        res.append(_solve_gpu(ctx, cfg, 1, ice, m))
+    (gj, nvj, naj), (gm, nvm, nam) = res
+    assert abs(nvj - nvm) <= 1 and nam < naj / 3
+    assert rel_l2(gm["u_vav_b"], gj["u_vav_b"]) < 5e-3       # two preconditioners at rtol 1e-4
+
+
+def test_multigrid_is_deterministic(setup):
+    w, ctx, o = setup
+    m = w.mesh
+    co = _coefficients(m, seed=4)
+    cfg = wl.scaling_config()
+    cfg.pc_type = ub.PC_MG
+    a = _linearised(ctx, cfg, m, *co, 1e-10, 1e-30)
+    b = _linearised(ctx, cfg, m, *co, 1e-10, 1e-30)
+    assert a[2] == b[2] and np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])

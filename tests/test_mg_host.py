@@ -1,0 +1,114 @@
+"""CPU: host logic of the multigrid pattern phase (ufemism2.0_b200/csrc/mg.cu: aggregation, coarse sliced-ELL pattern,
+Galerkin gather lists), checked against a dense P^T A P in numpy.  No GPU, no oracle involved."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import ufe_b200 as ub
+
+
+def sliced_ell(n, off, nbrs):
+    """nbrs[t] = list of extended column indices (own node = off + t first). Returns slice_ptr, col in the solver's layout."""
+    nsl = (n + 31) // 32
+    sp = np.zeros(nsl + 1, np.int32)
+    for s in range(nsl):
+        sp[s + 1] = sp[s] + max(len(nbrs[t]) for t in range(s * 32, min(n, s * 32 + 32)))
+    col = np.zeros(int(sp[-1]) * 32, np.int32)
+    for s in range(nsl):
+        for lane in range(32):
+            t = s * 32 + lane
+            for k in range(sp[s], sp[s + 1]):
+                j = k - sp[s]
+                if t < n:
+                    col[k * 32 + lane] = nbrs[t][j] if j < len(nbrs[t]) else off + t
+    return sp, col
+
+
+def host_transfer(n, off, sp, col):
+    L = ub.lib()
+    nc, cs, ge = C.c_int(), C.c_longlong(), C.c_longlong()
+    ub.check(L.ufe_b200_mg_host_transfer(n, off, ub.ip(sp), ub.ip(col), C.byref(nc), C.byref(cs), C.byref(ge)))
+    agg = np.zeros(n, np.int32); csp = np.zeros((nc.value + 31) // 32 + 1, np.int32); ccol = np.zeros(cs.value, np.int32)
+    gp = np.zeros(cs.value + 1, np.int32); gs = np.zeros(ge.value, np.int32)
+    ub.check(L.ufe_b200_mg_host_transfer_get(ub.ip(agg), ub.ip(csp), ub.ip(ccol), ub.ip(gp), ub.ip(gs)))
+    return nc.value, agg, csp, ccol, gp, gs
+
+
+def grid_pattern(nx, ny, rng, halo=0):
+    """5-point + one random extra neighbour per node on an nx x ny grid; `halo` extra extended columns on each side."""
+    n = nx * ny
+    off = halo
+    nbrs = []
+    for t in range(n):
+        i, j = divmod(t, ny)
+        l = [off + t]
+        for di, dj in ((1, 0), (-1, 0), (0, 1), (0, -1)):
+            a, b = i + di, j + dj
+            if 0 <= a < nx and 0 <= b < ny:
+                l.append(off + a * ny + b)
+        extra = int(rng.integers(0, n))
+        if off + extra not in l:
+            l.append(off + extra)
+        if halo and (i == 0 or i == nx - 1):           # couplings to halo columns, dropped by the preconditioner
+            l.append(int(rng.integers(0, halo)) if i == 0 else off + n + int(rng.integers(0, halo)))
+        nbrs.append(l)
+    return n, off, nbrs
+
+
+def dense_from_ell(n, off, sp, col, val, n_ext):
+    """val[(k*4 + q)*32 + lane]; returns the dense (2n x 2n_ext) matrix, duplicates added."""
+    A = np.zeros((2 * n, 2 * n_ext))
+    for t in range(n):
+        s, lane = divmod(t, 32)
+        for k in range(sp[s], sp[s + 1]):
+            c = col[k * 32 + lane]
+            v = [val[(k * 4 + q) * 32 + lane] for q in range(4)]
+            A[2 * t, 2 * c] += v[0]; A[2 * t, 2 * c + 1] += v[1]; A[2 * t + 1, 2 * c] += v[2]; A[2 * t + 1, 2 * c + 1] += v[3]
+    return A
+
+
+@pytest.mark.parametrize("halo", [0, 7])
+def test_transfer_is_galerkin_product(halo):
+    rng = np.random.default_rng(5)
+    n, off, nbrs = grid_pattern(23, 17, rng, halo)
+    sp, col = sliced_ell(n, off, nbrs)
+    nc, agg, csp, ccol, gp, gs = host_transfer(n, off, sp, col)
+    # a partition into fewer, non-empty aggregates
+    assert 0 < nc < n / 2
+    assert agg.min() == 0 and agg.max() == nc - 1 and len(np.unique(agg)) == nc
+    # values: random in the real slots, zero in the padding
+    n_slots = int(sp[-1]) * 32
+    val = np.zeros(n_slots * 4)
+    for t in range(n):
+        s, lane = divmod(t, 32)
+        for j in range(len(nbrs[t])):
+            for q in range(4):
+                val[((sp[s] + j) * 4 + q) * 32 + lane] = rng.standard_normal()
+    # the device kernel's sum, restated: coarse slot value = sum of its listed fine slots
+    cval = np.zeros(len(ccol) * 4)
+    for cs in range(len(ccol)):
+        for fs in gs[gp[cs]:gp[cs + 1]]:
+            for q in range(4):
+                cval[((cs >> 5) * 4 + q) * 32 + (cs & 31)] += val[((fs >> 5) * 4 + q) * 32 + (fs & 31)]
+    # every in-range fine slot is gathered exactly once
+    in_range = sum(1 for t in range(n) for k in range(sp[t >> 5], sp[(t >> 5) + 1]) if 0 <= col[k * 32 + (t & 31)] - off < n)
+    assert len(gs) == in_range and len(np.unique(gs)) == len(gs)
+    A = dense_from_ell(n, off, sp, col, val, n + 2 * halo)[:, 2 * off:2 * (off + n)]      # owned columns only
+    P = np.zeros((2 * n, 2 * nc))
+    for t in range(n):
+        P[2 * t, 2 * agg[t]] = 1.0; P[2 * t + 1, 2 * agg[t] + 1] = 1.0
+    Ac = dense_from_ell(nc, 0, csp, ccol, cval, nc)
+    np.testing.assert_allclose(Ac, P.T @ A @ P, rtol=1e-12, atol=1e-12)
+    # coarse rows start with their own node (the diagonal block) and padding points at the own node
+    for I in range(nc):
+        assert ccol[csp[I >> 5] * 32 + (I & 31)] == I
+
+
+def test_isolated_nodes_are_grouped():
+    """identity rows nobody references (e.g. prescribed velocities in an ice-free corner) must not stall the coarsening"""
+    n = 100
+    nbrs = [[t] for t in range(n)]
+    sp, col = sliced_ell(n, 0, nbrs)
+    nc, agg, *_ = host_transfer(n, 0, sp, col)
+    assert nc == 13 and np.bincount(agg).max() == 8

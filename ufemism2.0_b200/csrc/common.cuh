@@ -87,13 +87,26 @@ struct DevCsr {
 };
 
 // ---- timing classes ----------------------------------------------------------------------------------
-enum TimingClass { TC_SPMV_STIFFNESS = 0, TC_KRYLOV_VEC, TC_ASSEMBLY, TC_COLUMN, TC_TRI, TC_EPILOGUE, TC_THICKNESS, TC_OPERATOR_SPMV, TC_COUNT };
+enum TimingClass { TC_SPMV_STIFFNESS = 0, TC_KRYLOV_VEC, TC_ASSEMBLY, TC_COLUMN, TC_TRI, TC_EPILOGUE, TC_THICKNESS, TC_OPERATOR_SPMV,
+                   TC_MG_FINE, TC_MG_VEC, TC_MG_COARSE, TC_MG_SETUP, TC_COUNT };
 const char* timing_class_name(int c);
 
 struct Mesh;      // mesh.cuh
 struct Velocity;  // velocity.cuh
 struct Krylov;    // krylov.cuh
 struct Thickness; // thickness.cuh
+
+// multigrid preconditioner knobs (mg.cuh); set through ufe_b200_set_mg_params
+struct MgParams {
+  int nu_pre = 1, nu_post = 1;   // block-Jacobi sweeps before / after the coarse-grid correction
+  double omega = 0.7;            // damping
+  double overcorr = 1.0;         // scaling of the coarse-grid correction
+  int w_levels = 3;              // coarse levels 1..w_levels are visited twice per cycle (W-cycle on top, V-cycle below)
+  int dense_max = 128;           // coarsest level: at most this many nodes -> dense inverse; otherwise `coarse_sweeps` sweeps
+  int coarse_sweeps = 8;
+  int max_levels = 12;
+  int fp32 = 0;                  // 1: matrix values of the preconditioner stored as float
+};
 
 struct Ctx {
   int device = 0, rank = 0, nranks = 1;
@@ -112,6 +125,7 @@ struct Ctx {
   Velocity* vel = nullptr;
   Krylov* krylov = nullptr;
   Thickness* thick = nullptr;
+  MgParams mg_params;
   // pinned scratch for small D2H reads
   double* h_pinned = nullptr;       // 64 doubles
 };

@@ -42,7 +42,8 @@ void set_error(const char* fmt, ...) {
 const char* get_error() { return g_err; }
 
 const char* timing_class_name(int c) {
-  static const char* names[TC_COUNT] = {"spmv_stiffness", "krylov_vec", "assembly", "column", "tri", "epilogue", "thickness", "operator_spmv"};
+  static const char* names[TC_COUNT] = {"spmv_stiffness", "krylov_vec", "assembly", "column", "tri", "epilogue", "thickness", "operator_spmv",
+                                          "mg_fine", "mg_vec", "mg_coarse", "mg_setup"};
   return (c >= 0 && c < TC_COUNT) ? names[c] : "?";
 }
 

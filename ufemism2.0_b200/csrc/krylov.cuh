@@ -23,6 +23,7 @@ enum { KF_DONE = 0, KF_ITS = 1, KF_REASON = 2, KF_COUNT = 4 };
 struct Krylov {
   DBuf<double> R, RP, V, T, dinv;   // local (m_loc)
   DBuf<double> P, S;                // extended (inputs of the SpMV)
+  DBuf<double> W1, W2;              // local work vectors of the multigrid-preconditioned variant (mg.cu)
   DBuf<double> binv;                // 2x2 block-Jacobi inverse blocks [4][m_loc/2]
   DBuf<double> scal, partials;
   DBuf<unsigned> counter;

@@ -1,0 +1,773 @@
+// Aggregation multigrid preconditioner of the stiffness-matrix solve (see mg.cuh for the design and its reference context).
+#include "mg.cuh"
+
+#include <algorithm>
+#include <chrono>
+
+#include "krylov_impl.cuh"
+
+namespace ufe {
+
+namespace {
+
+// =====================================================================================================================
+// host: hierarchy (pattern) construction
+// =====================================================================================================================
+struct HostLevel {
+  int n = 0, off = 0;
+  std::vector<int> slice_ptr, col;   // sliced-ELL block pattern, as BlkMat
+};
+
+// adjacency of G u G^T restricted to owned nodes, no self loops, no duplicates
+void build_sym_graph(const HostLevel& H, std::vector<size_t>& ptr, std::vector<int>& adj) {
+  const int n = H.n;
+  std::vector<int> deg(n, 0);
+  auto for_each_edge = [&](auto&& f) {
+    for (int t = 0; t < n; ++t) {
+      const int s = t >> 5, lane = t & 31;
+      for (int k = H.slice_ptr[s]; k < H.slice_ptr[s + 1]; ++k) {
+        const int cj = H.col[(size_t)k * 32 + lane] - H.off;
+        if (cj < 0 || cj >= n || cj == t) continue;
+        f(t, cj);
+      }
+    }
+  };
+  for_each_edge([&](int i, int j) { deg[i]++; deg[j]++; });
+  std::vector<size_t> p0(n + 1, 0);
+  for (int i = 0; i < n; ++i) p0[i + 1] = p0[i] + deg[i];
+  std::vector<int> raw(p0[n]);
+  std::vector<size_t> fill(p0.begin(), p0.end() - 1);
+  for_each_edge([&](int i, int j) { raw[fill[i]++] = j; raw[fill[j]++] = i; });
+  // dedupe (keeps first occurrence, i.e. out-edges in pattern order first)
+  std::vector<int> stamp(n, -1);
+  ptr.assign(n + 1, 0);
+  adj.clear();
+  adj.reserve(raw.size() / 2 + n);
+  for (int i = 0; i < n; ++i) {
+    for (size_t k = p0[i]; k < p0[i + 1]; ++k) {
+      const int j = raw[k];
+      if (stamp[j] != i) { stamp[j] = i; adj.push_back(j); }
+    }
+    ptr[i + 1] = adj.size();
+  }
+}
+
+// greedy neighbourhood aggregation; returns the number of aggregates
+int aggregate(int n, const std::vector<size_t>& ptr, const std::vector<int>& adj, std::vector<int>& agg) {
+  agg.assign(n, -1);
+  int na = 0;
+  // pass 1: a node whose whole neighbourhood is still free becomes a root and takes the neighbourhood
+  for (int i = 0; i < n; ++i) {
+    if (agg[i] >= 0 || ptr[i + 1] == ptr[i]) continue;
+    bool is_free = true;
+    for (size_t k = ptr[i]; k < ptr[i + 1]; ++k) if (agg[adj[k]] >= 0) { is_free = false; break; }
+    if (!is_free) continue;
+    agg[i] = na;
+    for (size_t k = ptr[i]; k < ptr[i + 1]; ++k) agg[adj[k]] = na;
+    ++na;
+  }
+  // pass 2: leftovers join the aggregate most of their neighbours belong to (pass-1 state, so no chains form)
+  std::vector<int> agg1(agg);
+  for (int i = 0; i < n; ++i) {
+    if (agg1[i] >= 0) continue;
+    int best = -1, best_cnt = 0;
+    for (size_t k = ptr[i]; k < ptr[i + 1]; ++k) {
+      const int a = agg1[adj[k]];
+      if (a < 0 || a == best) continue;
+      int cnt = 0;
+      for (size_t k2 = ptr[i]; k2 < ptr[i + 1]; ++k2) cnt += (agg1[adj[k2]] == a);
+      if (cnt > best_cnt || (cnt == best_cnt && a < best)) { best = a; best_cnt = cnt; }
+    }
+    if (best >= 0) agg[i] = best;
+  }
+  // pass 3: anything still free (cannot happen on a symmetric graph, kept for safety) starts an aggregate with its free neighbours
+  for (int i = 0; i < n; ++i) {
+    if (agg[i] >= 0 || ptr[i + 1] == ptr[i]) continue;
+    agg[i] = na;
+    for (size_t k = ptr[i]; k < ptr[i + 1]; ++k) if (agg[adj[k]] < 0) agg[adj[k]] = na;
+    ++na;
+  }
+  // pass 4: isolated nodes (rows that only hold their diagonal and that nobody references) are grouped 8 at a time
+  int in_group = 0;
+  for (int i = 0; i < n; ++i) {
+    if (agg[i] >= 0) continue;
+    if (in_group == 0) ++na;
+    agg[i] = na - 1;
+    in_group = (in_group + 1) & 7;
+  }
+  return na;
+}
+
+struct HostTransfer {
+  int nc = 0;
+  std::vector<int> agg, mem_ptr, mem, gal_ptr, gal_src;
+  HostLevel coarse;
+  long long coarse_slots = 0;
+};
+
+void build_transfer(const HostLevel& F, HostTransfer& T) {
+  const int n = F.n;
+  std::vector<size_t> gptr;
+  std::vector<int> gadj;
+  build_sym_graph(F, gptr, gadj);
+  T.nc = aggregate(n, gptr, gadj, T.agg);
+  std::vector<size_t>().swap(gptr);
+  std::vector<int>().swap(gadj);
+  const int nc = T.nc;
+  // members (ascending fine index inside an aggregate)
+  T.mem_ptr.assign(nc + 1, 0);
+  for (int i = 0; i < n; ++i) T.mem_ptr[T.agg[i] + 1]++;
+  for (int I = 0; I < nc; ++I) T.mem_ptr[I + 1] += T.mem_ptr[I];
+  T.mem.resize(n);
+  {
+    std::vector<int> fill(T.mem_ptr.begin(), T.mem_ptr.end() - 1);
+    for (int i = 0; i < n; ++i) T.mem[fill[T.agg[i]]++] = i;
+  }
+  // coarse block rows: own aggregate first, then neighbours in order of first appearance
+  const size_t fine_slots = F.col.size();
+  std::vector<int> slotpos(fine_slots, -1);
+  std::vector<int> stamp(nc, -1), posn(nc, 0);
+  std::vector<int> cptr(nc + 1, 0), ccol;
+  ccol.reserve((size_t)nc * 10);
+  for (int I = 0; I < nc; ++I) {
+    const int start = (int)ccol.size();
+    stamp[I] = I; posn[I] = 0; ccol.push_back(I);
+    for (int m = T.mem_ptr[I]; m < T.mem_ptr[I + 1]; ++m) {
+      const int i = T.mem[m], s = i >> 5, lane = i & 31;
+      for (int k = F.slice_ptr[s]; k < F.slice_ptr[s + 1]; ++k) {
+        const size_t fs = (size_t)k * 32 + lane;
+        const int cj = F.col[fs] - F.off;
+        if (cj < 0 || cj >= n) continue;   // halo triangle: dropped inside the preconditioner
+        const int J = T.agg[cj];
+        if (stamp[J] != I) { stamp[J] = I; posn[J] = (int)ccol.size() - start; ccol.push_back(J); }
+        slotpos[fs] = posn[J];
+      }
+    }
+    cptr[I + 1] = (int)ccol.size();
+  }
+  // coarse sliced-ELL pattern
+  HostLevel& C = T.coarse;
+  C.n = nc; C.off = 0;
+  const int nsl = (nc + 31) / 32;
+  C.slice_ptr.assign(nsl + 1, 0);
+  for (int s = 0; s < nsl; ++s) {
+    int w = 0;
+    for (int I = s * 32; I < std::min(nc, s * 32 + 32); ++I) w = std::max(w, cptr[I + 1] - cptr[I]);
+    C.slice_ptr[s + 1] = C.slice_ptr[s] + w;
+  }
+  T.coarse_slots = (long long)C.slice_ptr[nsl] * 32;
+  C.col.assign((size_t)T.coarse_slots, 0);
+  for (int s = 0; s < nsl; ++s)
+    for (int lane = 0; lane < 32; ++lane) {
+      const int I = s * 32 + lane;
+      const int len = I < nc ? cptr[I + 1] - cptr[I] : 0;
+      const int pad = I < nc ? I : 0;
+      for (int k = C.slice_ptr[s]; k < C.slice_ptr[s + 1]; ++k) {
+        const int j = k - C.slice_ptr[s];
+        C.col[(size_t)k * 32 + lane] = j < len ? ccol[cptr[I] + j] : pad;
+      }
+    }
+  // Galerkin gather lists: coarse slot -> fine slots (ascending fine slot order: deterministic sums)
+  T.gal_ptr.assign((size_t)T.coarse_slots + 1, 0);
+  auto coarse_slot = [&](int i, size_t fs) -> long long {
+    const int I = T.agg[i];
+    return ((long long)C.slice_ptr[I >> 5] + slotpos[fs]) * 32 + (I & 31);
+  };
+  for (int i = 0; i < n; ++i) {
+    const int s = i >> 5, lane = i & 31;
+    for (int k = F.slice_ptr[s]; k < F.slice_ptr[s + 1]; ++k) {
+      const size_t fs = (size_t)k * 32 + lane;
+      if (slotpos[fs] >= 0) T.gal_ptr[coarse_slot(i, fs) + 1]++;
+    }
+  }
+  for (long long q = 0; q < T.coarse_slots; ++q) T.gal_ptr[q + 1] += T.gal_ptr[q];
+  T.gal_src.resize((size_t)T.gal_ptr[T.coarse_slots]);
+  {
+    std::vector<int> fill(T.gal_ptr.begin(), T.gal_ptr.end() - 1);
+    // fine slots in ascending slot order: iterate k-steps of a slice, lanes inside
+    const int nslf = (n + 31) / 32;
+    for (int s = 0; s < nslf; ++s)
+      for (int k = F.slice_ptr[s]; k < F.slice_ptr[s + 1]; ++k)
+        for (int lane = 0; lane < 32; ++lane) {
+          const int i = s * 32 + lane;
+          if (i >= n) break;
+          const size_t fs = (size_t)k * 32 + lane;
+          if (slotpos[fs] >= 0) T.gal_src[fill[coarse_slot(i, fs)]++] = (int)fs;
+        }
+  }
+}
+
+template <typename T>
+int upload(Ctx* c, DBuf<T>& d, const std::vector<T>& h) {
+  UFE_TRY(d.alloc(h.size() ? h.size() : 1));
+  if (!h.empty()) UFE_CUDA(cudaMemcpyAsync(d.p, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice, c->stream));
+  return 0;
+}
+
+// =====================================================================================================================
+// device kernels
+// =====================================================================================================================
+
+// MODE 0: out = x + Dw (b - A x)   (damped block-Jacobi sweep; Dw = omega * inverse diagonal block)
+// MODE 1: out = b - A x            (residual)
+// x_ext: iterate over the extended range (node t at x2[off + t]); out, b: node t at [t]
+template <typename VT, int MODE>
+__global__ void __launch_bounds__(kBlock) k_mg_sweep(int n, int off, const int* __restrict__ slice_ptr, const int* __restrict__ col,
+                                                     const VT* __restrict__ val, const double* __restrict__ x_ext, const double* __restrict__ b,
+                                                     const double* __restrict__ dblk, double* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int warps_per_block = kBlock / 32;
+  const int n_slices = (n + 31) >> 5;
+  const double2* __restrict__ x2 = reinterpret_cast<const double2*>(x_ext);
+  for (int s = blockIdx.x * warps_per_block + (threadIdx.x >> 5); s < n_slices; s += gridDim.x * warps_per_block) {
+    const int t = (s << 5) + lane;
+    const int k0 = slice_ptr[s], k1 = slice_ptr[s + 1];
+    double yu = 0.0, yv = 0.0;
+    const int* __restrict__ cp = col + (size_t)k0 * 32 + lane;
+    const VT* __restrict__ vp = val + (size_t)k0 * 128 + lane;
+#pragma unroll 2
+    for (int k = k0; k < k1; ++k, cp += 32, vp += 128) {
+      const int tj = *cp;
+      const double a0 = (double)vp[0], a1 = (double)vp[32], a2 = (double)vp[64], a3 = (double)vp[96];
+      const double2 xv = x2[tj];
+      yu += a0 * xv.x + a1 * xv.y;
+      yv += a2 * xv.x + a3 * xv.y;
+    }
+    if (t < n) {
+      const double2 bv = reinterpret_cast<const double2*>(b)[t];
+      const double ru = bv.x - yu, rv = bv.y - yv;
+      if (MODE == 1) {
+        reinterpret_cast<double2*>(out)[t] = make_double2(ru, rv);
+      } else {
+        const double2 xo = x2[off + t];
+        const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
+        reinterpret_cast<double2*>(out)[t] = make_double2(xo.x + d01.x * ru + d01.y * rv, xo.y + d23.x * ru + d23.y * rv);
+      }
+    }
+  }
+}
+
+// x = Dw b  (first sweep from a zero iterate)
+__global__ void k_mg_smooth0(int n, const double* __restrict__ b, const double* __restrict__ dblk, double* __restrict__ x_own) {
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+    const double2 bv = reinterpret_cast<const double2*>(b)[t];
+    const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
+    reinterpret_cast<double2*>(x_own)[t] = make_double2(d01.x * bv.x + d01.y * bv.y, d23.x * bv.x + d23.y * bv.y);
+  }
+}
+
+// bc_I = sum of r over the members of aggregate I (fixed order)
+__global__ void k_mg_restrict(int nc, const int* __restrict__ mem_ptr, const int* __restrict__ mem, const double* __restrict__ r, double* __restrict__ bc) {
+  for (int I = blockIdx.x * blockDim.x + threadIdx.x; I < nc; I += gridDim.x * blockDim.x) {
+    double su = 0.0, sv = 0.0;
+    for (int k = mem_ptr[I]; k < mem_ptr[I + 1]; ++k) {
+      const double2 v = reinterpret_cast<const double2*>(r)[mem[k]];
+      su += v.x; sv += v.y;
+    }
+    reinterpret_cast<double2*>(bc)[I] = make_double2(su, sv);
+  }
+}
+
+// x_i += w * ec_agg(i)
+__global__ void k_mg_prolong(int n, const int* __restrict__ agg, const double* __restrict__ ec, double w, double* __restrict__ x_own) {
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+    const double2 e = reinterpret_cast<const double2*>(ec)[agg[t]];
+    double2 x = reinterpret_cast<double2*>(x_own)[t];
+    x.x += w * e.x; x.y += w * e.y;
+    reinterpret_cast<double2*>(x_own)[t] = x;
+  }
+}
+
+__global__ void k_mg_axpy(int n2, const double* __restrict__ a, double* __restrict__ y) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += gridDim.x * blockDim.x) y[i] += a[i];
+}
+
+// coarse block values: sum of the fine blocks listed for the slot
+template <typename VTI, typename VTO>
+__global__ void k_mg_galerkin(long long n_cslots, const int* __restrict__ gal_ptr, const int* __restrict__ gal_src, const VTI* __restrict__ fv,
+                              VTO* __restrict__ cv) {
+  for (long long cs = (long long)blockIdx.x * blockDim.x + threadIdx.x; cs < n_cslots; cs += (long long)gridDim.x * blockDim.x) {
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    for (int k = gal_ptr[cs]; k < gal_ptr[cs + 1]; ++k) {
+      const int fs = gal_src[k];
+      const VTI* p = fv + ((size_t)(fs >> 5) * 128) + (fs & 31);
+      a0 += (double)p[0]; a1 += (double)p[32]; a2 += (double)p[64]; a3 += (double)p[96];
+    }
+    VTO* q = cv + ((size_t)(cs >> 5) * 128) + (cs & 31);
+    q[0] = (VTO)a0; q[32] = (VTO)a1; q[64] = (VTO)a2; q[96] = (VTO)a3;
+  }
+}
+
+// FP32 copy of the level-0 values straight from the CSR matrix through the block scatter map
+__global__ void k_mg_scatter_f32(long long nnz, const int* __restrict__ map, const double* __restrict__ v, float* __restrict__ out) {
+  for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += (long long)gridDim.x * blockDim.x) out[map[k]] = (float)v[k];
+}
+
+// Dw = omega * inverse of the diagonal 2x2 block (sum of every slot that points at the own node; padding holds zeros)
+template <typename VT>
+__global__ void k_mg_diag(int n, int off, const int* __restrict__ slice_ptr, const int* __restrict__ col, const VT* __restrict__ val, double omega,
+                          double* __restrict__ dblk) {
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+    const int s = t >> 5, lane = t & 31;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    for (int k = slice_ptr[s]; k < slice_ptr[s + 1]; ++k) {
+      if (col[(size_t)k * 32 + lane] != off + t) continue;
+      const VT* p = val + (size_t)k * 128 + lane;
+      a0 += (double)p[0]; a1 += (double)p[32]; a2 += (double)p[64]; a3 += (double)p[96];
+    }
+    const double det = a0 * a3 - a1 * a2;
+    double i0, i1, i2, i3;
+    if (det != 0.0 && fabs(det) > 1e-14 * (fabs(a0 * a3) + fabs(a1 * a2))) {
+      const double id = omega / det;
+      i0 = a3 * id; i1 = -a1 * id; i2 = -a2 * id; i3 = a0 * id;
+    } else {  // singular block: plain Jacobi on whatever diagonal exists
+      i0 = a0 != 0.0 ? omega / a0 : omega; i3 = a3 != 0.0 ? omega / a3 : omega; i1 = i2 = 0.0;
+    }
+    reinterpret_cast<double2*>(dblk)[2 * t] = make_double2(i0, i1);
+    reinterpret_cast<double2*>(dblk)[2 * t + 1] = make_double2(i2, i3);
+  }
+}
+
+// dense copy of the coarsest matrix into the left half of the Gauss-Jordan workspace W[N][2N]; right half = identity
+template <typename VT>
+__global__ void k_mg_dense_fill(int n, const int* __restrict__ slice_ptr, const int* __restrict__ col, const VT* __restrict__ val, double* __restrict__ W) {
+  const int N = 2 * n;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+    const int s = t >> 5, lane = t & 31;
+    double* ru = W + (size_t)(2 * t) * 2 * N;
+    double* rv = ru + 2 * N;
+    for (int k = slice_ptr[s]; k < slice_ptr[s + 1]; ++k) {
+      const int cj = col[(size_t)k * 32 + lane];
+      const VT* p = val + (size_t)k * 128 + lane;
+      ru[2 * cj] += (double)p[0]; ru[2 * cj + 1] += (double)p[32];
+      rv[2 * cj] += (double)p[64]; rv[2 * cj + 1] += (double)p[96];
+    }
+    ru[N + 2 * t] = 1.0; rv[N + 2 * t + 1] = 1.0;
+  }
+}
+
+// single-block Gauss-Jordan with partial pivoting on W[N][2N]; writes the inverse column-major: inv[j*N + i] = (A^-1)(i,j)
+__global__ void __launch_bounds__(1024) k_mg_dense_invert(int N, double* __restrict__ W, double* __restrict__ inv) {
+  extern __shared__ double sh[];   // N factors + reduction scratch
+  double* fac = sh;
+  __shared__ double s_max[32];
+  __shared__ int s_arg[32];
+  __shared__ int s_piv;
+  __shared__ double s_pval;
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
+  const int ld = 2 * N;
+  for (int p = 0; p < N; ++p) {
+    // pivot search in column p, rows p..N-1
+    double best = -1.0; int arg = p;
+    for (int i = p + tid; i < N; i += nt) {
+      const double a = fabs(W[(size_t)i * ld + p]);
+      if (a > best) { best = a; arg = i; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+      if (ob > best || (ob == best && oa < arg)) { best = ob; arg = oa; }
+    }
+    if (lane == 0) { s_max[warp] = best; s_arg[warp] = arg; }
+    __syncthreads();
+    if (tid == 0) {
+      double bb = s_max[0]; int aa = s_arg[0];
+      for (int w = 1; w < (nt + 31) / 32; ++w)
+        if (s_max[w] > bb || (s_max[w] == bb && s_arg[w] < aa)) { bb = s_max[w]; aa = s_arg[w]; }
+      s_piv = aa;
+      const double pv = W[(size_t)aa * ld + p];
+      s_pval = (pv != 0.0) ? pv : 1.0;
+    }
+    __syncthreads();
+    const int piv = s_piv;
+    const double ipv = 1.0 / s_pval;
+    // swap rows p <-> piv and scale the pivot row
+    for (int j = tid; j < ld; j += nt) {
+      const double a = W[(size_t)piv * ld + j];
+      if (piv != p) W[(size_t)piv * ld + j] = W[(size_t)p * ld + j];
+      W[(size_t)p * ld + j] = a * ipv;
+    }
+    __syncthreads();
+    for (int i = tid; i < N; i += nt) fac[i] = (i == p) ? 0.0 : W[(size_t)i * ld + p];
+    __syncthreads();
+    // eliminate column p from every other row; columns < p of the left half are already unit vectors
+    const int j0 = p, ncol = ld - j0;
+    for (long long e = tid; e < (long long)N * ncol; e += nt) {
+      const int i = (int)(e / ncol), j = j0 + (int)(e % ncol);
+      const double f = fac[i];
+      if (f != 0.0) W[(size_t)i * ld + j] -= f * W[(size_t)p * ld + j];
+    }
+    __syncthreads();
+  }
+  for (long long e = tid; e < (long long)N * N; e += nt) {
+    const int i = (int)(e / N), j = (int)(e % N);
+    inv[(size_t)j * N + i] = W[(size_t)i * ld + N + j];
+  }
+}
+
+// x = A^-1 b on the coarsest level (one block)
+__global__ void __launch_bounds__(1024) k_mg_dense_solve(int N, const double* __restrict__ inv, const double* __restrict__ b, double* __restrict__ x) {
+  extern __shared__ double sb[];
+  for (int j = threadIdx.x; j < N; j += blockDim.x) sb[j] = b[j];
+  __syncthreads();
+  for (int i = threadIdx.x; i < N; i += blockDim.x) {
+    double s = 0.0;
+    for (int j = 0; j < N; ++j) s += inv[(size_t)j * N + i] * sb[j];
+    x[i] = s;
+  }
+}
+
+// ---- BiCGStab pieces that differ from the Jacobi path (the preconditioner is no longer fused into the SpMV) ----------
+
+// Bb = M^-1 b, Br = M^-1 (b - A x0) (Br == Bb and x zeroed when there is no initial guess)
+__global__ void k_ksmg_init(int m, const double* __restrict__ Bb, const double* __restrict__ Br, int zero_x, double* __restrict__ R,
+                            double* __restrict__ RP, double* __restrict__ x_own, double* __restrict__ P_own, double* __restrict__ V, double* scal,
+                            double* partials, unsigned* counter, int* flags, double rtol, double abstol) {
+  double acc[2] = {0.0, 0.0};
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x) {
+    const double pb = Bb[i], r = Br[i];
+    if (zero_x) x_own[i] = 0.0;
+    R[i] = r; RP[i] = r; P_own[i] = 0.0; V[i] = 0.0;
+    acc[0] += pb * pb;
+    acc[1] += r * r;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    flags[KF_DONE] = 0; flags[KF_ITS] = 0; flags[KF_REASON] = 0;
+    scal[KS_RTOL] = rtol; scal[KS_ABSTOL] = abstol;
+  }
+  grid_sum<2>(acc, partials, counter, scal + KS_RR0);
+}
+
+__global__ void k_ksmg_sub(int m, const double* __restrict__ b, const double* __restrict__ Ax, double* __restrict__ out) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x) out[i] = b[i] - Ax[i];
+}
+
+// D1 = (v, rp)
+__global__ void k_ksmg_dot1(int m, int iter, const double* __restrict__ v, const double* __restrict__ rp, double* scal, double* partials,
+                            unsigned* counter, const int* flags) {
+  if (flags[KF_DONE]) return;
+  double acc[1] = {0.0};
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x) acc[0] += v[i] * rp[i];
+  grid_sum<1>(acc, partials, counter, scal + (iter & 1) * KS_BANK + KS_D1);
+}
+// ST = (s, t), TT = (t, t)
+__global__ void k_ksmg_dot2(int m, int iter, const double* __restrict__ s, const double* __restrict__ t, double* scal, double* partials,
+                            unsigned* counter, const int* flags) {
+  if (flags[KF_DONE]) return;
+  double acc[2] = {0.0, 0.0};
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x) {
+    const double tv = t[i];
+    acc[0] += s[i] * tv; acc[1] += tv * tv;
+  }
+  grid_sum<2>(acc, partials, counter, scal + (iter & 1) * KS_BANK + KS_ST);
+}
+
+// =====================================================================================================================
+// host: cycle
+// =====================================================================================================================
+template <typename VT>
+const VT* level_values(const MgLevel& L);
+template <>
+const double* level_values<double>(const MgLevel& L) { return L.val; }
+template <>
+const float* level_values<float>(const MgLevel& L) { return L.valf.p; }
+
+template <typename VT, int MODE>
+void launch_sweep(Ctx* c, const MgLevel& L, int level, const double* x_ext, const double* b, double* out) {
+  const int grid = grid_for(c, (long long)L.n_slices * 32, kBlock);
+  UFE_LAUNCH(c, level == 0 ? TC_MG_FINE : TC_MG_COARSE);
+  k_mg_sweep<VT, MODE><<<grid, kBlock, 0, c->stream>>>(L.n, L.off, L.slice_ptr, L.col, level_values<VT>(L), x_ext, b, L.dblk.p, out);
+}
+
+// solves (approximately) A_l x = b;  the result is written to `out` (node t at out[2t..2t+1])
+template <typename VT>
+int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out) {
+  MgLevel& L = G.lv[l];
+  const MgParams& P = G.p;
+  cudaStream_t st = c->stream;
+  const int last = (int)G.lv.size() - 1;
+  const int gv = grid_for(c, L.n, kBlock);
+  double* xa = L.xa.p;
+  double* xb = L.xb.p;
+  if (l == last) {
+    if (G.dense_n > 0) {
+      UFE_LAUNCH(c, TC_MG_COARSE);
+      k_mg_dense_solve<<<1, std::min(1024, ((G.dense_n + 31) / 32) * 32), sizeof(double) * G.dense_n, st>>>(G.dense_n, G.dense_inv.p, b, out);
+      return 0;
+    }
+    { UFE_LAUNCH(c, TC_MG_COARSE); k_mg_smooth0<<<gv, kBlock, 0, st>>>(L.n, b, L.dblk.p, xa + 2 * L.off); }
+    for (int s = 0; s < P.coarse_sweeps; ++s) {
+      double* dst = (s == P.coarse_sweeps - 1) ? out : xb + 2 * L.off;
+      launch_sweep<VT, 0>(c, L, l, xa, b, dst);
+      std::swap(xa, xb);
+    }
+    return 0;
+  }
+  MgLevel& Cn = G.lv[l + 1];
+  { UFE_LAUNCH(c, l == 0 ? TC_MG_VEC : TC_MG_COARSE); k_mg_smooth0<<<gv, kBlock, 0, st>>>(L.n, b, L.dblk.p, xa + 2 * L.off); }
+  for (int s = 1; s < P.nu_pre; ++s) {
+    launch_sweep<VT, 0>(c, L, l, xa, b, xb + 2 * L.off);
+    std::swap(xa, xb);
+  }
+  launch_sweep<VT, 1>(c, L, l, xa, b, L.r.p);
+  {
+    UFE_LAUNCH(c, l == 0 ? TC_MG_VEC : TC_MG_COARSE);
+    k_mg_restrict<<<grid_for(c, L.nc, kBlock), kBlock, 0, st>>>(L.nc, L.mem_ptr.p, L.mem.p, L.r.p, Cn.b.p);
+  }
+  UFE_TRY(mg_cycle<VT>(c, G, l + 1, Cn.b.p, Cn.sol.p));
+  if (l + 1 < last && l + 1 <= P.w_levels) {   // second visit of the coarse level: e += cycle(b_c - A_c e)
+    launch_sweep<VT, 1>(c, Cn, l + 1, Cn.sol.p, Cn.b.p, Cn.b2.p);
+    UFE_TRY(mg_cycle<VT>(c, G, l + 1, Cn.b2.p, Cn.sol2.p));
+    UFE_LAUNCH(c, TC_MG_COARSE);
+    k_mg_axpy<<<grid_for(c, 2 * Cn.n, kBlock), kBlock, 0, st>>>(2 * Cn.n, Cn.sol2.p, Cn.sol.p);
+  }
+  {
+    UFE_LAUNCH(c, l == 0 ? TC_MG_VEC : TC_MG_COARSE);
+    k_mg_prolong<<<gv, kBlock, 0, st>>>(L.n, L.agg.p, Cn.sol.p, P.overcorr, xa + 2 * L.off);
+  }
+  for (int s = 0; s < P.nu_post; ++s) {
+    double* dst = (s == P.nu_post - 1) ? out : xb + 2 * L.off;
+    launch_sweep<VT, 0>(c, L, l, xa, b, dst);
+    std::swap(xa, xb);
+  }
+  return 0;
+}
+
+template <typename VT>
+int mg_numeric(Ctx* c, Mg& G) {
+  cudaStream_t st = c->stream;
+  const int nl = (int)G.lv.size();
+  for (int l = 0; l < nl; ++l) {
+    MgLevel& L = G.lv[l];
+    {
+      UFE_LAUNCH(c, TC_MG_SETUP);
+      k_mg_diag<VT><<<grid_for(c, L.n, kBlock), kBlock, 0, st>>>(L.n, L.off, L.slice_ptr, L.col, level_values<VT>(L), G.p.omega, L.dblk.p);
+    }
+    if (l + 1 < nl) {
+      MgLevel& Cn = G.lv[l + 1];
+      VT* cv = const_cast<VT*>(level_values<VT>(Cn));
+      UFE_LAUNCH(c, TC_MG_SETUP);
+      k_mg_galerkin<VT, VT><<<grid_for(c, Cn.n_slots, kBlock), kBlock, 0, st>>>(Cn.n_slots, L.gal_ptr.p, L.gal_src.p, level_values<VT>(L), cv);
+    }
+  }
+  if (G.dense_n > 0) {
+    MgLevel& L = G.lv[nl - 1];
+    const int N = G.dense_n;
+    UFE_CUDA(cudaMemsetAsync(G.dense_w.p, 0, sizeof(double) * (size_t)N * 2 * N, st));
+    { UFE_LAUNCH(c, TC_MG_SETUP); k_mg_dense_fill<VT><<<grid_for(c, L.n, 128), 128, 0, st>>>(L.n, L.slice_ptr, L.col, level_values<VT>(L), G.dense_w.p); }
+    { UFE_LAUNCH(c, TC_MG_SETUP); k_mg_dense_invert<<<1, 1024, sizeof(double) * N, st>>>(N, G.dense_w.p, G.dense_inv.p); }
+  }
+  UFE_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+// =====================================================================================================================
+// public entry points
+// =====================================================================================================================
+int mg_build(Ctx* c, Mg& G, const BlkMat& B, int off_tri, int n_ext_tri) {
+  const auto t_start = std::chrono::steady_clock::now();
+  G.valid = false;
+  G.lv.clear();
+  G.lv.reserve(G.p.max_levels + 1);
+  G.gather_entries = 0;
+  // level 0 = the Krylov solver's own matrix
+  HostLevel H;
+  H.n = B.n_tri; H.off = off_tri;
+  H.slice_ptr.resize((size_t)B.n_slices + 1);
+  H.col.resize((size_t)B.n_slots);
+  UFE_CUDA(cudaMemcpyAsync(H.slice_ptr.data(), B.slice_ptr.p, sizeof(int) * H.slice_ptr.size(), cudaMemcpyDeviceToHost, c->stream));
+  UFE_CUDA(cudaMemcpyAsync(H.col.data(), B.col.p, sizeof(int) * H.col.size(), cudaMemcpyDeviceToHost, c->stream));
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  {
+    G.lv.emplace_back();
+    MgLevel& L = G.lv.back();
+    L.n = B.n_tri; L.n_ext = n_ext_tri; L.off = off_tri; L.n_slices = B.n_slices; L.n_slots = B.n_slots;
+    L.slice_ptr = B.slice_ptr.p; L.col = B.col.p; L.val = B.val.p;
+  }
+  while (true) {
+    MgLevel& L = G.lv.back();
+    const bool small = L.n <= G.p.dense_max;
+    if (small || (int)G.lv.size() >= G.p.max_levels) break;
+    HostTransfer T;
+    build_transfer(H, T);
+    if (T.nc >= L.n || T.nc * 10 > L.n * 9) break;   // coarsening stalled: stop here, smooth on this level
+    L.nc = T.nc;
+    UFE_TRY(upload(c, L.agg, T.agg)); UFE_TRY(upload(c, L.mem_ptr, T.mem_ptr)); UFE_TRY(upload(c, L.mem, T.mem));
+    UFE_TRY(upload(c, L.gal_ptr, T.gal_ptr)); UFE_TRY(upload(c, L.gal_src, T.gal_src));
+    G.gather_entries += (long long)T.gal_src.size();
+    UFE_CHECK(T.coarse_slots * 4 < 2147483647LL, "mg_build: coarse level too large for 32-bit value offsets");
+    G.lv.emplace_back();
+    MgLevel& Cn = G.lv.back();
+    Cn.n = T.nc; Cn.n_ext = T.nc; Cn.off = 0; Cn.n_slices = (T.nc + 31) / 32; Cn.n_slots = T.coarse_slots;
+    UFE_TRY(upload(c, Cn.slice_ptr_buf, T.coarse.slice_ptr)); UFE_TRY(upload(c, Cn.col_buf, T.coarse.col));
+    Cn.slice_ptr = Cn.slice_ptr_buf.p; Cn.col = Cn.col_buf.p;
+    UFE_CUDA(cudaStreamSynchronize(c->stream));   // the host vectors of T die at the end of this iteration
+    H = std::move(T.coarse);
+  }
+  // work vectors and value storage
+  for (size_t l = 0; l < G.lv.size(); ++l) {
+    MgLevel& L = G.lv[l];
+    const size_t ne = 2 * (size_t)L.n_ext, no = 2 * (size_t)L.n;
+    UFE_TRY(L.dblk.alloc(4 * (size_t)L.n));
+    UFE_TRY(L.xa.alloc(ne)); UFE_TRY(L.xb.alloc(ne)); UFE_TRY(L.r.alloc(no));
+    UFE_CUDA(cudaMemsetAsync(L.xa.p, 0, sizeof(double) * ne, c->stream));   // halo entries stay zero for ever
+    UFE_CUDA(cudaMemsetAsync(L.xb.p, 0, sizeof(double) * ne, c->stream));
+    if (l > 0) {
+      UFE_TRY(L.b.alloc(no)); UFE_TRY(L.b2.alloc(no)); UFE_TRY(L.sol.alloc(no)); UFE_TRY(L.sol2.alloc(no));
+      if (G.p.fp32) {
+        UFE_TRY(L.valf.alloc((size_t)L.n_slots * 4));
+        UFE_CUDA(cudaMemsetAsync(L.valf.p, 0, sizeof(float) * (size_t)L.n_slots * 4, c->stream));
+      } else {
+        UFE_TRY(L.val_buf.alloc((size_t)L.n_slots * 4));
+        UFE_CUDA(cudaMemsetAsync(L.val_buf.p, 0, sizeof(double) * (size_t)L.n_slots * 4, c->stream));
+        L.val = L.val_buf.p;
+      }
+    } else if (G.p.fp32) {
+      UFE_TRY(L.valf.alloc((size_t)L.n_slots * 4));
+      UFE_CUDA(cudaMemsetAsync(L.valf.p, 0, sizeof(float) * (size_t)L.n_slots * 4, c->stream));
+    }
+  }
+  MgLevel& Lc = G.lv.back();
+  G.dense_n = 0;
+  if (Lc.n <= G.p.dense_max && 2 * (size_t)Lc.n * sizeof(double) <= 40 * 1024) {
+    G.dense_n = 2 * Lc.n;
+    UFE_TRY(G.dense_w.alloc((size_t)G.dense_n * 2 * G.dense_n));
+    UFE_TRY(G.dense_inv.alloc((size_t)G.dense_n * G.dense_n));
+  }
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  G.setup_host_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
+  G.valid = true;
+  return 0;
+}
+
+int mg_update_values(Ctx* c, Mg& G, const BlkMat& B, const DevCsr& A) {
+  UFE_CHECK(G.valid, "mg_update_values: hierarchy not built");
+  if (G.p.fp32) {
+    {
+      UFE_LAUNCH(c, TC_MG_SETUP);
+      k_mg_scatter_f32<<<grid_for(c, A.nnz, 256), 256, 0, c->stream>>>(A.nnz, B.map.p, A.val, G.lv[0].valf.p);
+    }
+    return mg_numeric<float>(c, G);
+  }
+  G.lv[0].val = B.val.p;
+  return mg_numeric<double>(c, G);
+}
+
+int mg_apply(Ctx* c, Mg& G, const double* r, double* z) {
+  return G.p.fp32 ? mg_cycle<float>(c, G, 0, r, z) : mg_cycle<double>(c, G, 0, r, z);
+}
+
+int bicgstab_solve_mg(Ctx* c, Mg& G, const BlkLauncher& A, const Range& rr, const double* d_b, double* d_x_ext, const KrylovParams& kp, int* its) {
+  if (!c->krylov) c->krylov = new Krylov();
+  Krylov& K = *c->krylov;
+  const int m = rr.n_loc(), off = rr.off();
+  UFE_TRY(K.ensure(c, m, rr.n_ext()));
+  UFE_TRY(K.W1.alloc(m)); UFE_TRY(K.W2.alloc(m));
+  cudaStream_t st = c->stream;
+  const int gv = grid_for(c, m, kBlock);
+  double* x_own = d_x_ext + off;
+  double* P_own = K.P.p + off;
+  double* S_own = K.S.p + off;
+  if (rr.n_ext() > m) {
+    UFE_CUDA(cudaMemsetAsync(K.P.p, 0, sizeof(double) * rr.n_ext(), st));
+    UFE_CUDA(cudaMemsetAsync(K.S.p, 0, sizeof(double) * rr.n_ext(), st));
+  }
+  auto spmv_plain = [&](const double* x_ext, double* y) {
+    A.spmv(c, 0, m, off, 0, x_ext, nullptr, y, nullptr, nullptr, nullptr, nullptr, nullptr, TC_SPMV_STIFFNESS);
+  };
+  // W1 = M^-1 b;  W2 = M^-1 (b - A x0) when an initial guess is given
+  UFE_TRY(mg_apply(c, G, d_b, K.W1.p));
+  const double* Br = K.W1.p;
+  if (kp.use_guess) {
+    UFE_TRY(halo_exchange(c, rr, d_x_ext));
+    spmv_plain(d_x_ext, K.T.p);
+    { UFE_LAUNCH(c, TC_KRYLOV_VEC); k_ksmg_sub<<<gv, kBlock, 0, st>>>(m, d_b, K.T.p, K.V.p); }
+    UFE_TRY(mg_apply(c, G, K.V.p, K.W2.p));
+    Br = K.W2.p;
+  }
+  {
+    UFE_LAUNCH(c, TC_KRYLOV_VEC);
+    k_ksmg_init<<<gv, kBlock, 0, st>>>(m, K.W1.p, Br, kp.use_guess ? 0 : 1, K.R.p, K.RP.p, x_own, P_own, K.V.p, K.scal.p, K.partials.p,
+                                       K.counter.p, K.flags.p, kp.rtol, kp.abstol);
+  }
+  UFE_TRY(allreduce_sum(c, K.scal.p + KS_RR0, 2));
+  { UFE_LAUNCH(c, TC_KRYLOV_VEC); k_ks_init_finish<<<1, 1, 0, st>>>(K.scal.p); }
+  int* h_flags = reinterpret_cast<int*>(c->h_pinned);
+  int iter = 0;
+  int check_every = 2;
+  bool done = false;
+  while (!done && iter < kp.maxit) {
+    const int stop_at = (iter + check_every < kp.maxit) ? iter + check_every : kp.maxit;
+    for (; iter < stop_at; ++iter) {
+      const int p = iter & 1;
+      { UFE_LAUNCH(c, TC_KRYLOV_VEC); k_ks_update_p<<<gv, kBlock, 0, st>>>(m, iter, K.R.p, K.V.p, P_own, K.scal.p, K.flags.p); }
+      UFE_TRY(halo_exchange(c, rr, K.P.p));
+      spmv_plain(K.P.p, K.W1.p);
+      UFE_TRY(mg_apply(c, G, K.W1.p, K.V.p));
+      { UFE_LAUNCH(c, TC_KRYLOV_VEC); k_ksmg_dot1<<<gv, kBlock, 0, st>>>(m, iter, K.V.p, K.RP.p, K.scal.p, K.partials.p, K.counter.p + 1, K.flags.p); }
+      UFE_TRY(allreduce_sum(c, K.scal.p + p * KS_BANK + KS_D1, 1));
+      { UFE_LAUNCH(c, TC_KRYLOV_VEC); k_ks_update_s<<<gv, kBlock, 0, st>>>(m, iter, K.R.p, K.V.p, S_own, K.scal.p, K.flags.p); }
+      UFE_TRY(halo_exchange(c, rr, K.S.p));
+      spmv_plain(K.S.p, K.W1.p);
+      UFE_TRY(mg_apply(c, G, K.W1.p, K.T.p));
+      { UFE_LAUNCH(c, TC_KRYLOV_VEC); k_ksmg_dot2<<<gv, kBlock, 0, st>>>(m, iter, S_own, K.T.p, K.scal.p, K.partials.p, K.counter.p + 2, K.flags.p); }
+      UFE_TRY(allreduce_sum(c, K.scal.p + p * KS_BANK + KS_ST, 2));
+      {
+        UFE_LAUNCH(c, TC_KRYLOV_VEC);
+        k_ks_update_xr<<<gv, kBlock, 0, st>>>(m, iter, x_own, P_own, S_own, K.T.p, K.R.p, K.RP.p, K.scal.p, K.partials.p, K.counter.p + 3, K.flags.p);
+      }
+      UFE_TRY(allreduce_sum(c, K.scal.p + (1 - p) * KS_BANK + KS_RHO, 2));
+    }
+    if (iter >= kp.maxit) {
+      UFE_LAUNCH(c, TC_KRYLOV_VEC);
+      k_ks_final_check<<<1, 1, 0, st>>>(iter, K.scal.p, K.flags.p);
+    } else {
+      UFE_LAUNCH(c, TC_KRYLOV_VEC);
+      k_ks_update_p<<<1, 32, 0, st>>>(0, iter, K.R.p, K.V.p, P_own, K.scal.p, K.flags.p);
+    }
+    UFE_CUDA(cudaMemcpyAsync(h_flags, K.flags.p, KF_COUNT * sizeof(int), cudaMemcpyDeviceToHost, st));
+    UFE_CUDA(cudaStreamSynchronize(st));
+    done = h_flags[KF_DONE] != 0;
+    if (check_every < 8) check_every *= 2;
+  }
+  UFE_CUDA(cudaGetLastError());
+  *its = h_flags[KF_ITS];
+  UFE_CHECK(h_flags[KF_REASON] != 1, "BiCGStab (multigrid) broke down (NaN residual) after %d iterations", *its);
+  return 0;
+}
+
+}  // namespace ufe
+
+// ---- host-logic hooks (no GPU involved): the pattern phase of one level, for the CPU test-suite ------------------------------------
+static thread_local ufe::HostTransfer* g_host_transfer = nullptr;
+
+extern "C" int ufe_b200_mg_host_transfer(int n, int off, const int32_t* slice_ptr, const int32_t* col, int* nc, long long* coarse_slots,
+                                         long long* gather_entries) {
+  using namespace ufe;
+  UFE_CHECK(n > 0 && slice_ptr && col, "ufe_b200_mg_host_transfer: empty pattern");
+  HostLevel F;
+  F.n = n; F.off = off;
+  const int nsl = (n + 31) / 32;
+  F.slice_ptr.assign(slice_ptr, slice_ptr + nsl + 1);
+  F.col.assign(col, col + (size_t)F.slice_ptr[nsl] * 32);
+  delete g_host_transfer;
+  g_host_transfer = new HostTransfer();
+  build_transfer(F, *g_host_transfer);
+  if (nc) *nc = g_host_transfer->nc;
+  if (coarse_slots) *coarse_slots = g_host_transfer->coarse_slots;
+  if (gather_entries) *gather_entries = (long long)g_host_transfer->gal_src.size();
+  return 0;
+}
+
+extern "C" int ufe_b200_mg_host_transfer_get(int32_t* agg, int32_t* coarse_slice_ptr, int32_t* coarse_col, int32_t* gal_ptr, int32_t* gal_src) {
+  using namespace ufe;
+  UFE_CHECK(g_host_transfer != nullptr, "ufe_b200_mg_host_transfer_get: call ufe_b200_mg_host_transfer first");
+  const HostTransfer& T = *g_host_transfer;
+  auto copy = [](int32_t* dst, const std::vector<int>& v) { if (dst && !v.empty()) std::memcpy(dst, v.data(), sizeof(int) * v.size()); };
+  copy(agg, T.agg); copy(coarse_slice_ptr, T.coarse.slice_ptr); copy(coarse_col, T.coarse.col); copy(gal_ptr, T.gal_ptr); copy(gal_src, T.gal_src);
+  delete g_host_transfer;
+  g_host_transfer = nullptr;
+  return 0;
+}

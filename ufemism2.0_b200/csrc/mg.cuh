@@ -1,0 +1,67 @@
+// Aggregation multigrid preconditioner for the SSA/DIVA stiffness matrix (pc_type = UFE_PC_MG).
+//
+// Why: the reference hands the linearised system to PETSc (solve_matrix_equation_CSR_PETSc, src/UPSY/basic/petsc_basic.f90:32-242),
+// whose default one-level preconditioners (block-Jacobi/ILU(0), or Jacobi as north_star prescribes) need O(1/h) Krylov iterations:
+// ~270 at 60 k vertices, ~610 at 250 k and more than the reference's 2000-iteration cap (:166) at 4 M.  A multilevel
+// preconditioner keeps the count nearly mesh-independent, so the solve stays a few dozen streamed passes over the matrix.
+//
+// What: plain (unsmoothed) aggregation on the graph of 2x2 triangle blocks.
+//   * hierarchy (pattern) built once per (mesh, BC) on the host from the blocked sliced-ELL pattern: greedy neighbourhood
+//     aggregation (root + all free neighbours, leftovers join the most common neighbouring aggregate), coarse patterns in the same
+//     sliced-ELL layout, and per coarse block the list of fine blocks it sums ("Galerkin gather list");
+//   * values rebuilt on the device every viscosity iteration, deterministically (no atomics): A_c = P^T A P with piecewise-constant
+//     P per velocity component, i.e. coarse block (I,J) = sum of the fine blocks (i,j), i in I, j in J;
+//   * cycle: damped 2x2-block-Jacobi smoothing, V-cycle with an optional second coarse visit on the first `w_levels` coarse levels,
+//     dense inverse (Gauss-Jordan on the device) on the coarsest level;
+//   * optional FP32 storage of the matrix values inside the preconditioner (the outer BiCGStab, its residuals and the convergence
+//     test stay FP64, so the solution meets the same tolerance).
+// Multi-GPU: aggregates never cross ranks and couplings to halo triangles are dropped inside the preconditioner, i.e. the
+// preconditioner is block-diagonal over ranks exactly like PETSc's default block-Jacobi; the Krylov SpMV keeps its halo exchange.
+#pragma once
+#include "blk.cuh"
+#include "common.cuh"
+
+namespace ufe {
+
+
+struct MgLevel {
+  int n = 0, n_ext = 0, off = 0;          // nodes, size of the extended vector (level 0: owned + halo triangles), offset of node 0
+  int n_slices = 0;
+  long long n_slots = 0;
+  const int* slice_ptr = nullptr;         // views of the pattern (level 0: the Krylov solver's BlkMat)
+  const int* col = nullptr;
+  const double* val = nullptr;            // FP64 values (level 0: BlkMat::val)
+  DBuf<int> slice_ptr_buf, col_buf;
+  DBuf<double> val_buf;
+  DBuf<float> valf;                       // FP32 copy (fp32 = 1)
+  DBuf<double> dblk;                      // [n][4] omega * inverse of the diagonal 2x2 block
+  // transfer to the next coarser level
+  int nc = 0;
+  DBuf<int> agg;                          // [n] coarse node of each node
+  DBuf<int> mem_ptr, mem;                 // coarse node -> member nodes
+  DBuf<int> gal_ptr, gal_src;             // coarse block slot -> fine block slots
+  // work vectors (2 doubles per node)
+  DBuf<double> xa, xb;                    // ping-pong iterates over the extended range
+  DBuf<double> b, b2, r, sol, sol2;       // restricted right-hand sides, residual, coarse solutions (levels >= 1)
+};
+
+struct Mg {
+  std::vector<MgLevel> lv;
+  DBuf<double> dense_w, dense_inv;        // Gauss-Jordan workspace [N][2N], inverse (column-major) [N][N]
+  int dense_n = 0;                        // unknowns of the dense coarsest solve (0: smoothing only)
+  MgParams p;
+  bool valid = false;
+  long long gather_entries = 0;
+  double setup_host_s = 0.0;
+};
+
+// pattern phase (once per stiffness pattern); B is the level-0 matrix the Krylov solver streams
+int mg_build(Ctx* c, Mg& G, const BlkMat& B, int off_tri, int n_ext_tri);
+// numeric phase (every viscosity iteration, after blk_update_values)
+int mg_update_values(Ctx* c, Mg& G, const BlkMat& B, const DevCsr& A);
+// z = M^-1 r for owned rows (r, z: 2 doubles per owned triangle)
+int mg_apply(Ctx* c, Mg& G, const double* r, double* z);
+// left-preconditioned BiCGStab (same recurrence, stopping rule and scalars as bicgstab_solve_mat) with M^-1 = one multigrid cycle
+int bicgstab_solve_mg(Ctx* c, Mg& G, const BlkLauncher& A, const Range& rr, const double* d_b, double* d_x_ext, const KrylovParams& kp, int* its);
+
+}  // namespace ufe

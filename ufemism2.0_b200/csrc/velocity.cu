@@ -564,6 +564,7 @@ static int ensure_pattern(Ctx* c, const VelPar& p, unsigned long long bc_version
   { UFE_LAUNCH(c, TC_ASSEMBLY); k_stiff_fill_ind<<<grid, 128, 0, c->stream>>>(s); }
   UFE_CUDA(cudaGetLastError());
   UFE_TRY(blk_build(c, V.blk, V.A, n, M.b.off()));
+  V.mg.valid = false;
   V.pattern_key = key; V.pattern_valid = true;
   return 0;
 }
@@ -579,7 +580,14 @@ static int solve_linear_system(Ctx* c, const ufe_b200_config* cfg, double rtol, 
   }
   if (cfg->stiffness_format == 1) return csr_ksp_solve(c, V.A, V.bb.p, V.uv.p, kp, TC_SPMV_STIFFNESS, its);
   UFE_CHECK(kp.ksp_type == UFE_KSP_BICGSTAB, "only BiCGStab is available for the (non-symmetric) stiffness matrix");
-  UFE_CHECK(kp.pc_type == UFE_PC_JACOBI || kp.pc_type == UFE_PC_NONE, "stiffness solve supports pc = jacobi | none");
+  if (kp.pc_type == UFE_PC_MG) {
+    Mesh& M = *c->mesh;
+    if (!V.mg.valid) { V.mg.p = c->mg_params; UFE_TRY(mg_build(c, V.mg, V.blk, M.b.off(), M.b.n_ext())); }
+    UFE_TRY(blk_update_values(c, V.blk, V.A));
+    UFE_TRY(mg_update_values(c, V.mg, V.blk, V.A));
+    return bicgstab_solve_mg(c, V.mg, BlkLauncher{&V.blk, M.b.off()}, V.A.cols, V.bb.p, V.uv.p, kp, its);
+  }
+  UFE_CHECK(kp.pc_type == UFE_PC_JACOBI || kp.pc_type == UFE_PC_NONE, "stiffness solve supports pc = jacobi | none | multigrid");
   if (!c->krylov) c->krylov = new Krylov();
   UFE_TRY(c->krylov->dinv.alloc(V.A.m_loc));
   UFE_TRY(csr_make_dinv(c, V.A, c->krylov->dinv.p, kp.pc_type));
@@ -926,6 +934,38 @@ int ufe_b200_get_stiffness(ufe_b200_handle h, int32_t* ptr, int32_t* ind, double
   UFE_CUDA(cudaStreamSynchronize(c->stream));
   for (int r = 0; r <= A.m_loc; ++r) ptr[r] += 1;
   for (long long k = 0; k < A.nnz; ++k) ind[k] += A.cols.lo;
+  return 0;
+}
+
+int ufe_b200_set_mg_params(ufe_b200_handle h, int nu_pre, int nu_post, double omega, double overcorr, int w_levels, int fp32, int dense_max) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c != nullptr, "ufe_b200_set_mg_params: null handle");
+  MgParams& p = c->mg_params;
+  if (nu_pre >= 1) p.nu_pre = nu_pre;
+  if (nu_post >= 1) p.nu_post = nu_post;
+  if (omega > 0.0) p.omega = omega;
+  if (overcorr > 0.0) p.overcorr = overcorr;
+  if (w_levels >= 0) p.w_levels = w_levels;
+  if (fp32 >= 0) p.fp32 = fp32 != 0;
+  if (dense_max >= 1) p.dense_max = dense_max < 128 ? dense_max : 128;
+  if (c->vel) c->vel->mg.valid = false;   // storage precision / depth are fixed at build time
+  return 0;
+}
+
+int ufe_b200_get_mg_info(ufe_b200_handle h, int* n_levels, int* nodes_per_level, long long* fine_bytes, long long* coarse_bytes, double* setup_s) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && c->vel && c->vel->mg.valid, "ufe_b200_get_mg_info: no multigrid hierarchy has been built");
+  const Mg& G = c->vel->mg;
+  const long long vb = G.p.fp32 ? 4 : 8;
+  if (n_levels) *n_levels = (int)G.lv.size();
+  long long cb = 0;
+  for (size_t l = 0; l < G.lv.size(); ++l) {
+    if (nodes_per_level && l < 16) nodes_per_level[l] = G.lv[l].n;
+    const long long b = G.lv[l].n_slots * (4 + 4 * vb) + 4LL * (G.lv[l].n_slices + 1);
+    if (l == 0) { if (fine_bytes) *fine_bytes = b; } else cb += b;
+  }
+  if (coarse_bytes) *coarse_bytes = cb;
+  if (setup_s) *setup_s = G.setup_host_s;
   return 0;
 }
 

@@ -17,7 +17,7 @@ c_ip = C.POINTER(C.c_int32)
 
 # enumerations of include/ufe_b200.h
 KSP_BICGSTAB, KSP_CG = 0, 1
-PC_JACOBI, PC_NONE, PC_BJACOBI2, PC_NEUMANN = 0, 1, 2, 3
+PC_JACOBI, PC_NONE, PC_BJACOBI2, PC_NEUMANN, PC_MG = 0, 1, 2, 3, 4
 BC_INFINITE, BC_ZERO = 0, 1
 (SLID_NO_SLIDING, SLID_WEERTMAN, SLID_COULOMB, SLID_BUDD, SLID_TSAI2015, SLID_SCHOOF2005, SLID_ZOET_IVERSON,
  SLID_IDEALISED_SSA_ICESTREAM) = range(8)
@@ -169,6 +169,10 @@ def lib():
     L.ufe_b200_get_stiffness_size.argtypes = [H, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.ufe_b200_get_stiffness.argtypes = [H, c_ip, c_ip, c_dp, c_dp]
     L.ufe_b200_get_stiffness_storage_bytes.argtypes = [H, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
+    L.ufe_b200_set_mg_params.argtypes = [H, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, C.c_int, C.c_int]
+    L.ufe_b200_get_mg_info.argtypes = [H, C.POINTER(C.c_int), c_ip, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), c_dp]
+    L.ufe_b200_mg_host_transfer.argtypes = [C.c_int, C.c_int, c_ip, c_ip, C.POINTER(C.c_int), C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
+    L.ufe_b200_mg_host_transfer_get.argtypes = [c_ip] * 5
     for fn in (L.ufe_b200_solve_DIVA, L.ufe_b200_solve_SSA):
         fn.argtypes = [H, C.POINTER(Config), C.POINTER(IceInputs), C.POINTER(VelocityState), C.POINTER(C.c_int),
                        C.POINTER(C.c_int), c_ip, c_dp, c_dp]
@@ -198,6 +202,7 @@ ABI_SYMBOLS = [
     "ufe_b200_csr_release", "ufe_b200_mesh_create", "ufe_b200_mesh_destroy", "ufe_b200_mesh_ranges",
     "ufe_b200_calc_matrix_operators", "ufe_b200_set_operator", "ufe_b200_get_operator_size", "ufe_b200_get_operator",
     "ufe_b200_apply_operator", "ufe_b200_solve_SSA_DIVA_linearised", "ufe_b200_get_stiffness_size", "ufe_b200_get_stiffness", "ufe_b200_get_stiffness_storage_bytes",
+    "ufe_b200_set_mg_params", "ufe_b200_get_mg_info", "ufe_b200_mg_host_transfer", "ufe_b200_mg_host_transfer_get",
     "ufe_b200_solve_DIVA", "ufe_b200_solve_SSA", "ufe_b200_velocity_upload", "ufe_b200_velocity_solve_resident",
     "ufe_b200_velocity_download", "ufe_b200_thickness_upload", "ufe_b200_pc_step_resident",
     "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA",
@@ -292,6 +297,14 @@ class Context:
         ptr = np.zeros(m.value + 1, np.int32); ind = np.zeros(nnz.value, np.int32); val = np.zeros(nnz.value); bb = np.zeros(m.value)
         check(lib().ufe_b200_get_stiffness(self.h, ip(ptr), ip(ind), dp(val), dp(bb)))
         return ptr, ind, val, bb
+
+    def set_mg_params(self, nu_pre=-1, nu_post=-1, omega=-1.0, overcorr=-1.0, w_levels=-1, fp32=-1, dense_max=-1):
+        check(lib().ufe_b200_set_mg_params(self.h, nu_pre, nu_post, omega, overcorr, w_levels, fp32, dense_max))
+
+    def mg_info(self):
+        nl = C.c_int(); nodes = np.zeros(16, np.int32); fb = C.c_longlong(); cb = C.c_longlong(); ss = C.c_double()
+        check(lib().ufe_b200_get_mg_info(self.h, C.byref(nl), ip(nodes), C.byref(fb), C.byref(cb), C.cast(C.byref(ss), c_dp)))
+        return dict(levels=nl.value, nodes=[int(x) for x in nodes[:nl.value]], fine_bytes=fb.value, coarse_bytes=cb.value, setup_s=ss.value)
 
     def timing(self, cls):
         ms, n = C.c_double(), C.c_longlong()
