@@ -12,8 +12,15 @@ import bench  # noqa
 import ufe_b200 as ub  # noqa
 
 nv = int(sys.argv[1]); nvisc = int(sys.argv[2]) if len(sys.argv) > 2 else 2
-w = bench.make_workload(nv)
+wname = os.environ.get("PROBE_WORKLOAD", "mismip_mod")
+if wname == "mismip_plus":
+    import workloads as wl
+    w = wl.mismip_plus(float(np.sqrt(800e3 * 80e3 / (nv * np.sqrt(3.0) / 2.0))))
+    w.cfg.ksp_initial_guess_nonzero = 1
+else:
+    w = bench.make_workload(nv)
 m, cfg = w.mesh, w.cfg
+approx = w.approximation
 ctx = ub.Context(device=0)
 ctx.mesh_create(m); ctx.calc_matrix_operators()
 cfg.visc_it_nit = nvisc - 1; cfg.visc_it_norm_dUV_tol = 1e-30; cfg.write_diagnostics = 0
@@ -22,12 +29,16 @@ ice = w.ice_inputs()
 L = ub.lib()
 print(f"mesh nV={m.nV} nTri={m.nTri}", flush=True)
 
-SETTINGS = [("jacobi", None)]
-for fp32 in (0, 1):
-    for (nu, wl_, oc) in ((1, 3, 1.0), (1, 0, 1.0), (2, 0, 1.0), (2, 3, 1.0), (1, 5, 1.0), (1, 3, 1.3), (2, 0, 1.5)):
-        SETTINGS.append((f"mg nu={nu} w_levels={wl_} overcorr={oc} fp32={fp32}", dict(nu_pre=nu, nu_post=nu, w_levels=wl_, overcorr=oc, fp32=fp32)))
-if len(sys.argv) > 3:
-    SETTINGS = [s for s in SETTINGS if any(k in s[0] for k in sys.argv[3].split(","))]
+# settings: "jacobi" or "nu,w_levels,overcorr,omega,fp32" separated by ';' in argv[3]
+spec = sys.argv[3] if len(sys.argv) > 3 else "jacobi;1,3,1.0,0.7,0;1,3,1.3,0.7,0"
+SETTINGS = []
+for tok in spec.split(";"):
+    if tok == "jacobi":
+        SETTINGS.append(("jacobi", None))
+    else:
+        nu, wl_, oc, om, fp = tok.split(",")
+        SETTINGS.append((f"mg nu={nu} w={wl_} oc={oc} om={om} fp32={fp}", dict(nu_pre=int(nu), nu_post=int(nu), w_levels=int(wl_), overcorr=float(oc), omega=float(om), fp32=int(fp))))
+timing = int(os.environ.get("PROBE_TIMING", "1"))
 
 ref = None
 for name, prm in SETTINGS:
@@ -36,11 +47,11 @@ for name, prm in SETTINGS:
     cfg.pc_type = ub.PC_JACOBI if prm is None else ub.PC_MG
     if prm:
         ctx.set_mg_params(**prm)
-    L.ufe_b200_timing_reset(ctx.h); L.ufe_b200_timing_enable(ctx.h, 1)
+    L.ufe_b200_timing_reset(ctx.h); L.ufe_b200_timing_enable(ctx.h, timing)
     a, b = C.c_int(), C.c_int()
     l0 = ctx.kernel_launches()
     t0 = time.time()
-    ub.check(L.ufe_b200_velocity_solve_resident(ctx.h, C.byref(cfg), 1, C.byref(a), C.byref(b)))
+    ub.check(L.ufe_b200_velocity_solve_resident(ctx.h, C.byref(cfg), approx, C.byref(a), C.byref(b)))
     dt = time.time() - t0
     L.ufe_b200_timing_enable(ctx.h, 0)
     ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))

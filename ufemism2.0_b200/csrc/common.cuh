@@ -88,7 +88,7 @@ struct DevCsr {
 
 // ---- timing classes ----------------------------------------------------------------------------------
 enum TimingClass { TC_SPMV_STIFFNESS = 0, TC_KRYLOV_VEC, TC_ASSEMBLY, TC_COLUMN, TC_TRI, TC_EPILOGUE, TC_THICKNESS, TC_OPERATOR_SPMV,
-                   TC_MG_FINE, TC_MG_VEC, TC_MG_COARSE, TC_MG_SETUP, TC_COUNT };
+                   TC_MG_FINE, TC_MG_VEC, TC_MG_COARSE, TC_MG_SETUP, TC_H2D, TC_D2H, TC_COUNT };
 const char* timing_class_name(int c);
 
 struct Mesh;      // mesh.cuh
@@ -99,13 +99,14 @@ struct Thickness; // thickness.cuh
 // multigrid preconditioner knobs (mg.cuh); set through ufe_b200_set_mg_params
 struct MgParams {
   int nu_pre = 1, nu_post = 1;   // block-Jacobi sweeps before / after the coarse-grid correction
-  double omega = 0.7;            // damping
-  double overcorr = 1.0;         // scaling of the coarse-grid correction
+  double omega = 0.8;            // damping
+  double overcorr = 1.5;         // scaling of the coarse-grid correction (plain aggregation under-corrects; > 1.7 is not robust)
   int w_levels = 3;              // coarse levels 1..w_levels are visited twice per cycle (W-cycle on top, V-cycle below)
   int dense_max = 128;           // coarsest level: at most this many nodes -> dense inverse; otherwise `coarse_sweeps` sweeps
   int coarse_sweeps = 8;
   int max_levels = 12;
   int fp32 = 0;                  // 1: matrix values of the preconditioner stored as float
+  int use_graph = 1;             // replay the coarse-grid correction (levels >= 1) as one CUDA graph
 };
 
 struct Ctx {
@@ -116,6 +117,8 @@ struct Ctx {
   int sm_count = 148;
   // timing
   bool timing = false;
+  int timing_level = 1;             // 1: every launch; 2: only the host<->device transfer regions (TC_H2D / TC_D2H)
+  int timing_suppress = 0;          // > 0: launches are counted but not individually timed (inside a timed region / graph capture)
   struct Ev { cudaEvent_t a, b; int cls; };
   std::vector<Ev> ev_pool; size_t ev_used = 0;
   double tc_ms[TC_COUNT] = {0}; long long tc_n[TC_COUNT] = {0};
@@ -133,10 +136,11 @@ struct Ctx {
 // Launch bookkeeping: every kernel launch of the library goes through one of these.
 struct LaunchTimer {
   Ctx* c; int cls; int idx = -1;
-  LaunchTimer(Ctx* c_, int cls_);
+  LaunchTimer(Ctx* c_, int cls_, bool count = true);   // count = false: a timed region around launches that count themselves
   ~LaunchTimer();
 };
 #define UFE_LAUNCH(ctx, cls) ufe::LaunchTimer lt__((ctx), (cls))
+#define UFE_REGION(ctx, cls) ufe::LaunchTimer region__((ctx), (cls), false)
 void timing_collect(Ctx* c);
 
 inline int grid_for(const Ctx* c, long long n, int block, int max_waves = 8) {

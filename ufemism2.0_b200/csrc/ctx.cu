@@ -43,13 +43,13 @@ const char* get_error() { return g_err; }
 
 const char* timing_class_name(int c) {
   static const char* names[TC_COUNT] = {"spmv_stiffness", "krylov_vec", "assembly", "column", "tri", "epilogue", "thickness", "operator_spmv",
-                                          "mg_fine", "mg_vec", "mg_coarse", "mg_setup"};
+                                          "mg_fine", "mg_vec", "mg_coarse", "mg_setup", "h2d", "d2h"};
   return (c >= 0 && c < TC_COUNT) ? names[c] : "?";
 }
 
-LaunchTimer::LaunchTimer(Ctx* c_, int cls_) : c(c_), cls(cls_) {
-  c->launches++;
-  if (!c->timing) return;
+LaunchTimer::LaunchTimer(Ctx* c_, int cls_, bool count) : c(c_), cls(cls_) {
+  if (count) c->launches++;
+  if (!c->timing || c->timing_suppress > 0 || (c->timing_level == 2 && cls != TC_H2D && cls != TC_D2H)) return;
   if (c->ev_used == c->ev_pool.size()) {
     Ctx::Ev e;
     cudaEventCreate(&e.a);
@@ -236,8 +236,9 @@ int ufe_b200_timing_enable(ufe_b200_handle h, int on) {
   Ctx* c = reinterpret_cast<Ctx*>(h);
   timing_collect(c);
   c->timing = on != 0;
+  c->timing_level = on == 2 ? 2 : 1;   // 2: time only the host<->device transfer regions (no per-kernel events)
   // lets `ncu --profile-from-start off` capture exactly the region bench.py times
-  if (on) cudaProfilerStart(); else cudaProfilerStop();
+  if (on == 1) cudaProfilerStart(); else cudaProfilerStop();
   return 0;
 }
 static cudaEvent_t g_t0 = nullptr, g_t1 = nullptr;

@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdlib>
 
 #include "krylov_impl.cuh"
 
@@ -479,6 +480,61 @@ void launch_sweep(Ctx* c, const MgLevel& L, int level, const double* x_ext, cons
   k_mg_sweep<VT, MODE><<<grid, kBlock, 0, c->stream>>>(L.n, L.off, L.slice_ptr, L.col, level_values<VT>(L), x_ext, b, L.dblk.p, out);
 }
 
+template <typename VT>
+int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out);
+
+// coarse-grid correction of level l: lv[l+1].sol ~= A_{l+1}^-1 lv[l+1].b, with a second visit on the first w_levels coarse levels
+template <typename VT>
+int mg_coarse_correction(Ctx* c, Mg& G, int l) {
+  MgLevel& Cn = G.lv[l + 1];
+  const int last = (int)G.lv.size() - 1;
+  UFE_TRY(mg_cycle<VT>(c, G, l + 1, Cn.b.p, Cn.sol.p));
+  if (l + 1 < last && l + 1 <= G.p.w_levels) {   // e += cycle(b_c - A_c e)
+    launch_sweep<VT, 1>(c, Cn, l + 1, Cn.sol.p, Cn.b.p, Cn.b2.p);
+    UFE_TRY(mg_cycle<VT>(c, G, l + 1, Cn.b2.p, Cn.sol2.p));
+    UFE_LAUNCH(c, TC_MG_COARSE);
+    k_mg_axpy<<<grid_for(c, 2 * Cn.n, kBlock), kBlock, 0, c->stream>>>(2 * Cn.n, Cn.sol2.p, Cn.sol.p);
+  }
+  return 0;
+}
+
+// The same, entered from the fine level: every launch on levels >= 1 is a small, latency-bound kernel, so the whole correction is
+// captured once as a CUDA graph and replayed (one timed region of class mg_coarse instead of ~100 individually timed launches).
+template <typename VT>
+int mg_coarse_from_fine(Ctx* c, Mg& G) {
+  cudaStream_t st = c->stream;
+  LaunchTimer region(c, TC_MG_COARSE, false);
+  c->timing_suppress++;
+  int rc = 0;
+  if (!G.p.use_graph) {
+    rc = mg_coarse_correction<VT>(c, G, 0);
+  } else {
+    if (!G.graph_exec) {
+      const long long l0 = c->launches;
+      cudaError_t e = cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal);
+      if (e == cudaSuccess) {
+        rc = mg_coarse_correction<VT>(c, G, 0);
+        cudaError_t e2 = cudaStreamEndCapture(st, &G.graph);
+        if (rc == 0 && e2 == cudaSuccess) e2 = cudaGraphInstantiate(&G.graph_exec, G.graph, 0);
+        if (e2 != cudaSuccess) e = e2;
+      }
+      G.graph_launches = c->launches - l0;
+      c->launches = l0;
+      if (e != cudaSuccess || rc != 0) {
+        c->timing_suppress--;
+        G.drop_graph();
+        if (rc == 0) { set_error("multigrid: CUDA graph capture of the coarse-grid correction failed: %s", cudaGetErrorString(e)); rc = 1; }
+        return rc;
+      }
+    }
+    cudaError_t e = cudaGraphLaunch(G.graph_exec, st);
+    c->launches += G.graph_launches;
+    if (e != cudaSuccess) { set_error("multigrid: cudaGraphLaunch failed: %s", cudaGetErrorString(e)); rc = 1; }
+  }
+  c->timing_suppress--;
+  return rc;
+}
+
 // solves (approximately) A_l x = b;  the result is written to `out` (node t at out[2t..2t+1])
 template <typename VT>
 int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out) {
@@ -514,13 +570,8 @@ int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out) {
     UFE_LAUNCH(c, l == 0 ? TC_MG_VEC : TC_MG_COARSE);
     k_mg_restrict<<<grid_for(c, L.nc, kBlock), kBlock, 0, st>>>(L.nc, L.mem_ptr.p, L.mem.p, L.r.p, Cn.b.p);
   }
-  UFE_TRY(mg_cycle<VT>(c, G, l + 1, Cn.b.p, Cn.sol.p));
-  if (l + 1 < last && l + 1 <= P.w_levels) {   // second visit of the coarse level: e += cycle(b_c - A_c e)
-    launch_sweep<VT, 1>(c, Cn, l + 1, Cn.sol.p, Cn.b.p, Cn.b2.p);
-    UFE_TRY(mg_cycle<VT>(c, G, l + 1, Cn.b2.p, Cn.sol2.p));
-    UFE_LAUNCH(c, TC_MG_COARSE);
-    k_mg_axpy<<<grid_for(c, 2 * Cn.n, kBlock), kBlock, 0, st>>>(2 * Cn.n, Cn.sol2.p, Cn.sol.p);
-  }
+  if (l == 0) UFE_TRY(mg_coarse_from_fine<VT>(c, G));
+  else UFE_TRY(mg_coarse_correction<VT>(c, G, l));
   {
     UFE_LAUNCH(c, l == 0 ? TC_MG_VEC : TC_MG_COARSE);
     k_mg_prolong<<<gv, kBlock, 0, st>>>(L.n, L.agg.p, Cn.sol.p, P.overcorr, xa + 2 * L.off);
@@ -569,6 +620,8 @@ int mg_numeric(Ctx* c, Mg& G) {
 int mg_build(Ctx* c, Mg& G, const BlkMat& B, int off_tri, int n_ext_tri) {
   const auto t_start = std::chrono::steady_clock::now();
   G.valid = false;
+  G.drop_graph();
+  if (const char* e = getenv("UFE_B200_MG_GRAPH")) G.p.use_graph = atoi(e);   // debugging aid: 0 = plain launches
   G.lv.clear();
   G.lv.reserve(G.p.max_levels + 1);
   G.gather_entries = 0;
@@ -696,7 +749,9 @@ int bicgstab_solve_mg(Ctx* c, Mg& G, const BlkLauncher& A, const Range& rr, cons
   { UFE_LAUNCH(c, TC_KRYLOV_VEC); k_ks_init_finish<<<1, 1, 0, st>>>(K.scal.p); }
   int* h_flags = reinterpret_cast<int*>(c->h_pinned);
   int iter = 0;
-  int check_every = 2;
+  // one multigrid-preconditioned iteration is milliseconds of device work and its kernels do not test the done flag, so the host
+  // looks at the convergence flag after every iteration (the Jacobi path batches 8-32 sub-millisecond iterations instead)
+  const int check_every = 1;
   bool done = false;
   while (!done && iter < kp.maxit) {
     const int stop_at = (iter + check_every < kp.maxit) ? iter + check_every : kp.maxit;
@@ -730,7 +785,6 @@ int bicgstab_solve_mg(Ctx* c, Mg& G, const BlkLauncher& A, const Range& rr, cons
     UFE_CUDA(cudaMemcpyAsync(h_flags, K.flags.p, KF_COUNT * sizeof(int), cudaMemcpyDeviceToHost, st));
     UFE_CUDA(cudaStreamSynchronize(st));
     done = h_flags[KF_DONE] != 0;
-    if (check_every < 8) check_every *= 2;
   }
   UFE_CUDA(cudaGetLastError());
   *its = h_flags[KF_ITS];

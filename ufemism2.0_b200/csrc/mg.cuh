@@ -46,10 +46,20 @@ struct MgLevel {
 };
 
 struct Mg {
+  ~Mg() { drop_graph(); }
+  void drop_graph() {
+    if (graph_exec) cudaGraphExecDestroy(graph_exec);
+    if (graph) cudaGraphDestroy(graph);
+    graph_exec = nullptr; graph = nullptr; graph_launches = 0;
+  }
   std::vector<MgLevel> lv;
   DBuf<double> dense_w, dense_inv;        // Gauss-Jordan workspace [N][2N], inverse (column-major) [N][N]
   int dense_n = 0;                        // unknowns of the dense coarsest solve (0: smoothing only)
   MgParams p;
+  // the coarse-grid correction (every launch on levels >= 1) captured once as a CUDA graph and replayed per cycle
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t graph_exec = nullptr;
+  long long graph_launches = 0;
   bool valid = false;
   long long gather_entries = 0;
   double setup_host_s = 0.0;

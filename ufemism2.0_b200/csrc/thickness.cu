@@ -404,6 +404,9 @@ int ufe_b200_calc_dHi_dt(ufe_b200_handle h, const ufe_b200_config* cfg, ufe_b200
   Mesh& M = *c->mesh; Thickness& T = *c->thick;
   UFE_CHECK(io->Hi && io->Hb && io->SL && io->SMB && io->BMB && io->LMB && io->fraction_margin && io->mask_noice && io->dHi_dt_target,
             "ufe_b200_calc_dHi_dt: Hi, Hb, SL, SMB, BMB, LMB, fraction_margin, mask_noice, dHi_dt_target are required");
+  const double *u_b, *v_b;
+  {
+  UFE_REGION(c, TC_H2D);
   UFE_TRY(th_h2d(c, T.Hi.p, M.a, io->Hi)); UFE_TRY(th_h2d(c, T.Hb.p, M.a, io->Hb)); UFE_TRY(th_h2d(c, T.SL.p, M.a, io->SL));
   UFE_TRY(th_h2d(c, T.SMB.p, M.a, io->SMB)); UFE_TRY(th_h2d(c, T.BMB.p, M.a, io->BMB)); UFE_TRY(th_h2d(c, T.LMB.p, M.a, io->LMB));
   UFE_TRY(th_h2d(c, T.fraction_margin.p, M.a, io->fraction_margin)); UFE_TRY(th_h2d(c, T.target.p, M.a, io->dHi_dt_target));
@@ -413,9 +416,9 @@ int ufe_b200_calc_dHi_dt(ufe_b200_handle h, const ufe_b200_config* cfg, ufe_b200
     UFE_TRY(th_h2d(c, T.bc_mask.p, M.a, io->BC_prescr_mask)); UFE_TRY(th_h2d(c, T.bc_Hi.p, M.a, io->BC_prescr_Hi));
     T.have_bc = true;
   } else T.have_bc = false;
-  const double *u_b, *v_b;
+  if (io->u_vav_b && io->v_vav_b) { UFE_TRY(th_h2d(c, T.u_b.p, M.b, io->u_vav_b)); UFE_TRY(th_h2d(c, T.v_b.p, M.b, io->v_vav_b)); }
+  }
   if (io->u_vav_b && io->v_vav_b) {
-    UFE_TRY(th_h2d(c, T.u_b.p, M.b, io->u_vav_b)); UFE_TRY(th_h2d(c, T.v_b.p, M.b, io->v_vav_b));
     UFE_TRY(halo_exchange(c, M.b, T.u_b.p)); UFE_TRY(halo_exchange(c, M.b, T.v_b.p));
     u_b = T.u_b.p; v_b = T.v_b.p;
   } else {
@@ -425,8 +428,11 @@ int ufe_b200_calc_dHi_dt(ufe_b200_handle h, const ufe_b200_config* cfg, ufe_b200
   }
   int its = 0;
   UFE_TRY(thickness_step(c, cfg, u_b, v_b, dt, finish, &its));
-  UFE_TRY(th_d2h(c, io->AMB, T.AMB.p, M.a)); UFE_TRY(th_d2h(c, io->dHi_dt, T.dHi_dt.p, M.a));
-  UFE_TRY(th_d2h(c, io->Hi_tplusdt, T.Hi_new.p, M.a)); UFE_TRY(th_d2h(c, io->divQ, T.divQ.p, M.a));
+  {
+    UFE_REGION(c, TC_D2H);
+    UFE_TRY(th_d2h(c, io->AMB, T.AMB.p, M.a)); UFE_TRY(th_d2h(c, io->dHi_dt, T.dHi_dt.p, M.a));
+    UFE_TRY(th_d2h(c, io->Hi_tplusdt, T.Hi_new.p, M.a)); UFE_TRY(th_d2h(c, io->divQ, T.divQ.p, M.a));
+  }
   UFE_CUDA(cudaStreamSynchronize(c->stream));
   if (n_Axb_its) *n_Axb_its = its;
   return 0;

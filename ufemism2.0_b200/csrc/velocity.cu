@@ -630,6 +630,7 @@ static int velocity_upload(Ctx* c, const ufe_b200_ice_inputs* ice, const ufe_b20
   UFE_TRY(ensure_velocity(c));
   Mesh& M = *c->mesh; Velocity& V = *c->vel;
   const int nz = M.nz;
+  UFE_REGION(c, TC_H2D);
   if (ice) {
     UFE_CHECK(ice->Hi && ice->Hs && ice->A_flow && ice->fraction_gr_b && ice->mask_grounded_ice, "ice inputs: Hi, Hs, A_flow, fraction_gr_b, mask_grounded_ice are required");
     UFE_TRY(h2d_field(c, V.Hi.p, M.a, ice->Hi)); UFE_TRY(h2d_field(c, V.Hs.p, M.a, ice->Hs));
@@ -666,6 +667,8 @@ static int velocity_download(Ctx* c, ufe_b200_velocity_state* st) {
   UFE_CHECK(c->vel && c->vel->uploaded, "velocity_download: nothing on the device");
   Mesh& M = *c->mesh; Velocity& V = *c->vel;
   const int nz = M.nz;
+  {
+  UFE_REGION(c, TC_D2H);
   UFE_TRY(d2h_field(c, st->u_vav_b, V.u.p, M.b)); UFE_TRY(d2h_field(c, st->v_vav_b, V.v.p, M.b));
   UFE_TRY(d2h_field(c, st->u_base_b, V.u_base.p, M.b)); UFE_TRY(d2h_field(c, st->v_base_b, V.v_base.p, M.b));
   UFE_TRY(d2h_field(c, st->tau_bx_b, V.tau_bx.p, M.b)); UFE_TRY(d2h_field(c, st->tau_by_b, V.tau_by.p, M.b));
@@ -684,6 +687,7 @@ static int velocity_download(Ctx* c, ufe_b200_velocity_state* st) {
   UFE_TRY(d2h_field(c, st->basal_friction_coefficient_a, V.beta_a.p, M.a));
   UFE_TRY(d2h_field(c, st->basal_friction_coefficient_b, V.beta_b.p, M.b));
   UFE_TRY(d2h_field(c, st->beta_eff_a, V.beta_eff_a.p, M.a)); UFE_TRY(d2h_field(c, st->beta_eff_b, V.beta_eff_b.p, M.b));
+  }
   UFE_CUDA(cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -941,6 +945,7 @@ int ufe_b200_set_mg_params(ufe_b200_handle h, int nu_pre, int nu_post, double om
   Ctx* c = reinterpret_cast<Ctx*>(h);
   UFE_CHECK(c != nullptr, "ufe_b200_set_mg_params: null handle");
   MgParams& p = c->mg_params;
+  const int old_fp32 = p.fp32, old_dense = p.dense_max;
   if (nu_pre >= 1) p.nu_pre = nu_pre;
   if (nu_post >= 1) p.nu_post = nu_post;
   if (omega > 0.0) p.omega = omega;
@@ -948,7 +953,12 @@ int ufe_b200_set_mg_params(ufe_b200_handle h, int nu_pre, int nu_post, double om
   if (w_levels >= 0) p.w_levels = w_levels;
   if (fp32 >= 0) p.fp32 = fp32 != 0;
   if (dense_max >= 1) p.dense_max = dense_max < 128 ? dense_max : 128;
-  if (c->vel) c->vel->mg.valid = false;   // storage precision / depth are fixed at build time
+  if (c->vel) {
+    Mg& G = c->vel->mg;
+    G.drop_graph();                                   // the captured launch sequence depends on the cycle shape
+    if (p.fp32 != old_fp32 || p.dense_max != old_dense) G.valid = false;   // storage precision / depth are fixed at build time
+    else if (G.valid) { const int ug = G.p.use_graph; G.p = p; G.p.use_graph = ug; }
+  }
   return 0;
 }
 
