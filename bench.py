@@ -333,50 +333,44 @@ def run_b200(args, rank, world, rdv, log):
     spmv_ms, spmv_n = classes[top]
     log("kernel classes (ms, launches): " + ", ".join(f"{k}={v[0]:.1f}/{v[1]}" for k, v in classes.items()))
 
-    # ---- end-to-end leg (`e2e`): the same three phases through the host-buffer ABI calls, copies inside the timed region
-    S = dict(Hi=np.zeros(na), dHdt_nm1=np.zeros(na), dt_n=DT, u=A["u_vav_b"], v=A["v_vav_b"])
-    ub.check(L.ufe_b200_thickness_download(ctx.h, ub.dp(S["Hi"]), None, None))
+    # ---- end-to-end leg (`e2e`): the same step through the host-buffer entry ufe_b200_pc_step -- every input the host model owns goes up
+    # from page-locked host arrays and every result (thickness, rates, the whole velocity state incl. the 3-D fields) comes back, per step
+    S_Hi = np.zeros(na); dH_nm1 = np.zeros(na)
+    ub.check(L.ufe_b200_thickness_download(ctx.h, ub.dp(S_Hi), ub.dp(dH_nm1), None))
     ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
     out = {k: np.zeros(na) for k in ("AMB", "dHi_dt", "Hi_tplusdt", "divQ")}
-    pinned = list(A.values()) + list(out.values()) + [v for v in w._keep.values()] + [v for v in keep_io.values()]
+    keep_io["Hi"][:] = S_Hi
+    io2, _k = thickness_io(w, sl_a, keep_io["Hi"], out=out)
+    for k in ("Hb", "SL", "SMB", "BMB", "LMB", "fraction_margin", "mask_noice", "dHi_dt_target"):   # the arrays that get page-locked below
+        a = keep_io[k]
+        setattr(io2, k, ub.ip(a) if a.dtype == np.int32 else ub.dp(a))
+    io2.Hi = ub.dp(keep_io["Hi"])
+    pinned = list(A.values()) + list(out.values()) + [v for v in w._keep.values()] + [v for v in keep_io.values()] + [dH_nm1]
     registered = [a for a in pinned if a.nbytes >= (1 << 16) and L.ufe_b200_host_register(a.ctypes.data_as(C.c_void_p), a.nbytes) == 0]
-    bytes_in, bytes_out = [0], [0]
+    ice_in = [k for k in w._keep if k not in ("Hi", "Hs")]
+    bytes_in = (sum(keep_io[k].nbytes for k in ("Hi", "Hb", "SL", "SMB", "BMB", "LMB", "fraction_margin", "mask_noice", "dHi_dt_target")) + dH_nm1.nbytes
+                + sum(w._keep[k].nbytes for k in ice_in) + sum(A[k].nbytes for k in STATE_FIELDS[:7]))
+    bytes_out = sum(a.nbytes for a in A.values()) + sum(a.nbytes for a in out.values()) + dH_nm1.nbytes
 
-    def calc(Hi, u, v, dt):
-        Hi = np.ascontiguousarray(Hi)
-        keep_io["Hi"][:] = Hi
-        io2, _k = thickness_io(w, sl_a, keep_io["Hi"], u, v, out)
-        for k in ("Hb", "SL", "SMB", "BMB", "LMB", "fraction_margin", "mask_noice", "dHi_dt_target"):   # reuse the page-locked inputs
-            a = keep_io[k]
-            setattr(io2, k, ub.ip(a) if a.dtype == np.int32 else ub.dp(a))
-        io2.Hi = ub.dp(keep_io["Hi"])
-        d = C.c_double(dt); its = C.c_int()
-        ub.check(L.ufe_b200_calc_dHi_dt(ctx.h, C.byref(cfg), C.byref(io2), C.cast(C.byref(d), ub.c_dp), 1, C.byref(its)))
-        bytes_in[0] += 8 * 8 * na + 4 * na + 2 * 8 * nb
-        bytes_out[0] += 4 * 8 * na
-        return out["dHi_dt"].copy(), its.value
+    def step_e2e():
+        ub.check(L.ufe_b200_pc_step(ctx.h, C.byref(cfg), 1, DT, DT, C.byref(ice), C.byref(st), C.byref(io2), ub.dp(dH_nm1),
+                                    C.byref(nv_), C.byref(na_), C.byref(nt_)))
+        keep_io["Hi"][:] = out["Hi_tplusdt"]      # the host model accepts the step: Hi_n := Hi_np1
 
-    def solve(Hi, Hs):
-        w._keep["Hi"][:] = Hi; w._keep["Hs"][:] = Hs
-        ub.check(L.ufe_b200_solve_DIVA(ctx.h, C.byref(cfg), C.byref(ice), C.byref(st), C.byref(nv_), C.byref(na_), None, None, None))
-        bytes_in[0] += sum(a.nbytes for a in w._keep.values()) + sum(A[k].nbytes for k in STATE_FIELDS[:7])
-        bytes_out[0] += sum(a.nbytes for a in A.values())
-        return nv_.value, na_.value
-
-    pc_step_host(calc, solve, w, cfg, sl_a, S, DT)   # one untimed pass (allocations, page-locking)
-    bytes_in[0] = bytes_out[0] = 0
-    k_e2e = max(1, min(args.steps, 3))
+    step_e2e()   # one untimed pass (stream creation, page faults)
+    k_e2e = max(1, min(args.steps, 5))
     L.ufe_b200_timing_reset(ctx.h)
-    L.ufe_b200_timing_enable(ctx.h, 2)      # times only the host<->device transfer regions (two event pairs per ABI call)
+    L.ufe_b200_timing_enable(ctx.h, 2)      # times only the host<->device transfer regions
     rdv.barrier()
     t0 = time.perf_counter()
     for _ in range(k_e2e):
-        pc_step_host(calc, solve, w, cfg, sl_a, S, DT)
+        step_e2e()
     e2e_s = rdv.allreduce_max(time.perf_counter() - t0)
     L.ufe_b200_timing_enable(ctx.h, 0)
     h2d_ms, d2h_ms = ctx.timing("h2d")[0] / k_e2e, ctx.timing("d2h")[0] / k_e2e
     for a in registered:
         L.ufe_b200_host_unregister(a.ctypes.data_as(C.c_void_p))
+    bytes_in, bytes_out = [bytes_in * k_e2e], [bytes_out * k_e2e]
 
     res = None
     if rank == 0:
@@ -414,7 +408,8 @@ def run_b200(args, rank, world, rdv, log):
                        "krylov": krylov_desc + ", rtol 1e-4 / abstol 1e-3, initial guess = previous solution (ksp_initial_guess_nonzero=1)",
                        "per_step": {"viscosity_its": tot[0] / args.steps, "krylov_its_velocity": tot[1] / args.steps, "krylov_its_thickness": tot[2] / args.steps}},
             "e2e": {"value": k_e2e / e2e_s, "unit": "velocity solves/s", "h2d_bytes_per_step": bytes_in[0] // k_e2e, "d2h_bytes_per_step": bytes_out[0] // k_e2e,
-                    "steps": k_e2e, "ms_per_step": 1e3 * e2e_s / k_e2e, "h2d_ms_per_step": h2d_ms, "d2h_ms_per_step": d2h_ms},
+                    "steps": k_e2e, "ms_per_step": 1e3 * e2e_s / k_e2e, "h2d_ms_per_step": h2d_ms, "d2h_ms_per_step": d2h_ms,
+                    "call": "ufe_b200_pc_step (host buffers; transfers overlap the thickness solves on a second stream)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak if peak else None, "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",

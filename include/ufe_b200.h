@@ -276,6 +276,17 @@ int ufe_b200_thickness_upload(ufe_b200_handle h, const ufe_b200_thickness_io* io
 int ufe_b200_pc_step_resident(ufe_b200_handle h, const ufe_b200_config* cfg, int approximation /*0 SSA, 1 DIVA*/, double dt,
                               int* n_visc_its, int* n_Axb_its_velocity, int* n_Axb_its_thickness);
 int ufe_b200_thickness_download(ufe_b200_handle h, double* Hi, double* dHi_dt, double* divQ);
+/* The same step through HOST buffers -- the widest seam: the device phases of one iterate_pc_timestep pass of run_ice_dynamics_model_pc
+ * (src/UFEMISM/ice_dynamics/time_stepping/predictor_corrector_scheme.f90:118-233) in one call.
+ *   in : io->Hi (= Hi_n), Hb, SL, SMB, BMB, LMB, fraction_margin, mask_noice, dHi_dt_target [, BC_prescr_*]; ice inputs except Hi/Hs (the
+ *        velocity solve sees the predicted geometry); state (u_vav_b, v_vav_b, u_base_b, v_base_b, tau_bx_b, tau_by_b, eta_3D_b);
+ *        dHi_dt_nm1 = pc%dHi_dt_Hnm1_unm1 (vi1:vi2); dt_prev = pc%dt_n (<= 0: first step).
+ *   out: io->Hi_tplusdt (= Hi_np1, Eq. 31), io->dHi_dt / divQ / AMB of the corrector, dHi_dt_nm1 = pc%dHi_dt_Hn_un, every non-NULL state field.
+ * Transfers the next phase does not depend on run on a second stream: the ice inputs and the 3-D state go up while the predictor runs, the
+ * velocity state comes back while the corrector runs. */
+int ufe_b200_pc_step(ufe_b200_handle h, const ufe_b200_config* cfg, int approximation /*0 SSA, 1 DIVA*/, double dt, double dt_prev,
+                     const ufe_b200_ice_inputs* ice, ufe_b200_velocity_state* state, const ufe_b200_thickness_io* io, double* dHi_dt_nm1,
+                     int* n_visc_its, int* n_Axb_its_velocity, int* n_Axb_its_thickness);
 
 /* ---- SIA (config 4) ------------------------------------------------------------------------------ */
 /* Replaces solve_SIA (src/UFEMISM/ice_dynamics/conservation_of_momentum/SIA/SIA_main.f90:65-158): u_3D_b, v_3D_b (ti1:ti2,nz). */

@@ -1,0 +1,133 @@
+"""GPU: the predictor-corrector time step (device phases of run_ice_dynamics_model_pc, predictor_corrector_scheme.f90:118-233).
+(1) the device-resident step vs the same call sequence driven on the host with the CPU oracle;
+(2) the host-buffer entry ufe_b200_pc_step (overlapped transfers) vs the resident step."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import bench
+import oracle_lib as ol
+import ufe_b200 as ub
+import workloads as wl
+
+pytestmark = pytest.mark.gpu
+DT = 0.2
+FIELDS = bench.STATE_FIELDS + ["u_b_prev", "v_b_prev"]
+
+
+def rel_l2(a, b):
+    n = np.linalg.norm(b)
+    return np.linalg.norm(a - b) / (n if n > 0 else 1.0)
+
+
+def _workload():
+    w = wl.mismip_mod(2.5e4)
+    cfg = w.cfg
+    cfg.write_diagnostics = 0
+    cfg.stress_balance_PETSc_rtol = 1e-11; cfg.stress_balance_PETSc_abstol = 1e-30
+    cfg.dHi_PETSc_rtol = 1e-12; cfg.dHi_PETSc_abstol = 1e-30
+    cfg.visc_it_norm_dUV_tol = 1e-7
+    return w
+
+
+def _spin_up(ctx, w):
+    m, cfg = w.mesh, w.cfg
+    L = ub.lib()
+    ice = w.ice_inputs()
+    st, A = ub.alloc_velocity_state(m.nV, m.nTri, m.nz, fields=FIELDS)
+    nv, na = C.c_int(), C.c_int()
+    ub.check(L.ufe_b200_velocity_upload(ctx.h, C.byref(ice), C.byref(st)))
+    ub.check(L.ufe_b200_velocity_solve_resident(ctx.h, C.byref(cfg), 1, C.byref(nv), C.byref(na)))
+    ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
+    return ice, st, A
+
+
+@pytest.mark.parametrize("pc", [ub.PC_JACOBI, ub.PC_MG])
+def test_resident_pc_steps_match_oracle_sequence(pc):
+    w = _workload()
+    m, cfg = w.mesh, w.cfg
+    cfg.pc_type = pc
+    L = ub.lib()
+    ctx = ub.Context(device=0)
+    ctx.mesh_create(m); ctx.calc_matrix_operators()
+    ice, st, A = _spin_up(ctx, w)
+    io, keep = bench.thickness_io(w, slice(None), w.f["Hi"].copy())
+    ub.check(L.ufe_b200_thickness_upload(ctx.h, C.byref(io)))
+    nv, na, nt = C.c_int(), C.c_int(), C.c_int()
+    for _ in range(2):
+        ub.check(L.ufe_b200_pc_step_resident(ctx.h, C.byref(cfg), 1, DT, C.byref(nv), C.byref(na), C.byref(nt)))
+    Hi_g = np.zeros(m.nV); dH_g = np.zeros(m.nV)
+    ub.check(L.ufe_b200_thickness_download(ctx.h, ub.dp(Hi_g), ub.dp(dH_g), None))
+    ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
+    u_g = A["u_vav_b"].copy()
+    ctx.close()
+
+    # the same two steps with the oracle behind the host call sequence (what bench.py's CPU arm times)
+    o = ol.OracleMesh(m)
+    w2 = _workload()
+    cfg2 = w2.cfg
+    st2, A2 = ub.alloc_velocity_state(m.nV, m.nTri, m.nz, fields=FIELDS)
+    out = {k: np.zeros(m.nV) for k in ("AMB", "dHi_dt", "Hi_tplusdt", "divQ")}
+
+    def calc(Hi, u, v, dt):
+        io2, _k = bench.thickness_io(w2, slice(None), Hi, u, v, out)
+        rc, _dt, its = o.calc_dHi_dt(cfg2, io2, dt)
+        assert rc == 0
+        return out["dHi_dt"].copy(), its
+
+    def solve(Hi, Hs):
+        w2.f["Hi"], w2.f["Hs"] = Hi, Hs
+        rc, a, b = o.solve_velocity(cfg2, 1, w2.ice_inputs(), st2)
+        assert rc == 0
+        return a, b
+
+    rc, _a, _b = o.solve_velocity(cfg2, 1, w2.ice_inputs(), st2)
+    assert rc == 0
+    S = dict(Hi=w2.f["Hi"].copy(), dHdt_nm1=np.zeros(m.nV), dt_n=DT, u=A2["u_vav_b"], v=A2["v_vav_b"])
+    for _ in range(2):
+        bench.pc_step_host(calc, solve, w2, cfg2, slice(None), S, DT)
+    assert rel_l2(Hi_g, S["Hi"]) < 1e-9, rel_l2(Hi_g, S["Hi"])
+    assert rel_l2(u_g, A2["u_vav_b"]) < 1e-6, rel_l2(u_g, A2["u_vav_b"])
+
+
+def test_host_buffer_pc_step_equals_resident():
+    w = _workload()
+    m, cfg = w.mesh, w.cfg
+    cfg.pc_type = ub.PC_MG
+    L = ub.lib()
+    nv, na, nt = C.c_int(), C.c_int(), C.c_int()
+    # resident
+    ctx = ub.Context(device=0)
+    ctx.mesh_create(m); ctx.calc_matrix_operators()
+    ice, st, A = _spin_up(ctx, w)
+    A0 = {k: v.copy() for k, v in A.items()}
+    io, keep = bench.thickness_io(w, slice(None), w.f["Hi"].copy())
+    ub.check(L.ufe_b200_thickness_upload(ctx.h, C.byref(io)))
+    for _ in range(2):
+        ub.check(L.ufe_b200_pc_step_resident(ctx.h, C.byref(cfg), 1, DT, C.byref(nv), C.byref(na), C.byref(nt)))
+    Hi_r = np.zeros(m.nV)
+    ub.check(L.ufe_b200_thickness_download(ctx.h, ub.dp(Hi_r), None, None))
+    ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
+    res = {k: v.copy() for k, v in A.items()}
+    its_r = (nv.value, na.value, nt.value)
+    ctx.close()
+    # host buffers: everything goes up and comes back every step
+    ctx = ub.Context(device=0)
+    ctx.mesh_create(m); ctx.calc_matrix_operators()
+    for k in A:
+        A[k][...] = A0[k]
+    out = {k: np.zeros(m.nV) for k in ("AMB", "dHi_dt", "Hi_tplusdt", "divQ")}
+    io2, keep2 = bench.thickness_io(w, slice(None), w.f["Hi"].copy(), out=out)
+    dH_nm1 = np.zeros(m.nV)
+    dt_prev = 0.0
+    for _ in range(2):
+        ub.check(L.ufe_b200_pc_step(ctx.h, C.byref(cfg), 1, DT, dt_prev, C.byref(ice), C.byref(st), C.byref(io2), ub.dp(dH_nm1),
+                                    C.byref(nv), C.byref(na), C.byref(nt)))
+        keep2["Hi"][:] = out["Hi_tplusdt"]       # the host accepts the step
+        dt_prev = DT
+    ctx.close()
+    assert (nv.value, na.value, nt.value) == its_r
+    assert np.array_equal(out["Hi_tplusdt"], Hi_r)
+    for k in ("u_vav_b", "v_vav_b", "u_3D_b", "eta_3D_b", "tau_bx_b"):
+        assert np.array_equal(A[k], res[k]), k

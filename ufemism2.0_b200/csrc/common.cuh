@@ -112,6 +112,8 @@ struct MgParams {
 struct Ctx {
   int device = 0, rank = 0, nranks = 1;
   cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream = nullptr;   // host<->device transfers that overlap compute (ufe_b200_pc_step)
+  cudaEvent_t ev_copy_a = nullptr, ev_copy_b = nullptr;
   void* nccl = nullptr;             // ncclComm_t when nranks > 1
   long long launches = 0;
   int sm_count = 148;

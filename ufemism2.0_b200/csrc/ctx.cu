@@ -225,6 +225,7 @@ int ufe_b200_finalize(ufe_b200_handle h) {
   for (auto& e : c->ev_pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
   if (c->nccl && nccl_api()) nccl_api()->CommDestroy((ncclComm_t)c->nccl);
   if (c->h_pinned) cudaFreeHost(c->h_pinned);
+  if (c->copy_stream) { cudaStreamDestroy(c->copy_stream); cudaEventDestroy(c->ev_copy_a); cudaEventDestroy(c->ev_copy_b); }
   cudaStreamDestroy(c->stream);
   delete c;
   return 0;

@@ -89,14 +89,21 @@ __global__ void k_ks_update_xr(int m, int iter, double* __restrict__ x_own, cons
   const double* cur = scal + p * KS_BANK;
   const double alpha = cur[KS_RHO] / cur[KS_D1];
   const double omega = (cur[KS_TT] == 0.0) ? 0.0 : cur[KS_ST] / cur[KS_TT];
+  // breakdown (rho, (v, r~) or (t, t) vanished): leave x at the last finite iterate and hand a NaN residual norm to the next
+  // convergence test, which stops the iteration with reason 1; the host restarts from x (krylov_impl.cuh)
+  const bool bad = !(isfinite(alpha) && isfinite(omega));
   double acc[2] = {0.0, 0.0};  // RHO, RR of the next iteration (adjacent slots)
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x) {
-    const double s = S_own[i];
-    x_own[i] += alpha * P_own[i] + omega * s;
-    const double r = s - omega * T[i];
-    R[i] = r;
-    acc[0] += r * RP[i];
-    acc[1] += r * r;
+  if (!bad) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x) {
+      const double s = S_own[i];
+      x_own[i] += alpha * P_own[i] + omega * s;
+      const double r = s - omega * T[i];
+      R[i] = r;
+      acc[0] += r * RP[i];
+      acc[1] += r * r;
+    }
+  } else {
+    acc[0] = acc[1] = nan("");
   }
   grid_sum<2>(acc, partials, counter, scal + (1 - p) * KS_BANK + KS_RHO);
 }

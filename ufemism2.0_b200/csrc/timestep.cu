@@ -52,6 +52,51 @@ __global__ void k_pc_correct(int n, int off, double dt, double rho_ratio, const 
   }
 }
 
+// the three device phases of one predictor-corrector step; `before_velocity` / `after_velocity` let the host-buffer entry
+// overlap its transfers with the thickness solves
+template <class F1, class F2>
+static int pc_step_core(Ctx* c, const ufe_b200_config* cfg, int approximation, double dt, int* n_visc_its, int* n_Axb_its_velocity,
+                        int* n_Axb_its_thickness, F1&& before_velocity, F2&& after_velocity) {
+  Mesh& M = *c->mesh; Velocity& V = *c->vel; Thickness& T = *c->thick;
+  cudaStream_t st = c->stream;
+  PcState& P = *g_pc;
+  const size_t na = M.a.n_ext();
+  const int n = M.a.n_loc(), grid = grid_for(c, n, 128, 16);
+  const double zeta = dt / P.dt_n;
+  const double rho_ratio = cfg->ice_density / cfg->seawater_density;
+  int its_p = 0, its_c = 0;
+  double dt_p = dt, dt_c = dt;
+  // predictor: dHi_dt( Hi_n, u_n) (:129)
+  UFE_TRY(halo_exchange(c, M.b, V.u.p)); UFE_TRY(halo_exchange(c, M.b, V.v.p));
+  UFE_TRY(thickness_step(c, cfg, V.u.p, V.v.p, &dt_p, 1, &its_p));
+  UFE_CUDA(cudaMemcpyAsync(P.dHdt_n.p, T.dHi_dt.p, sizeof(double) * na, cudaMemcpyDeviceToDevice, st));
+  { UFE_LAUNCH(c, TC_THICKNESS); k_pc_predict<<<grid, 128, 0, st>>>(n, M.a.off(), dt, zeta, rho_ratio, T.mask_noice.p, T.Hi.p, P.dHdt_n.p, P.dHdt_nm1.p, T.Hb.p, T.SL.p, V.Hi.p, V.Hs.p); }
+  // velocities for the predicted geometry (:186)
+  UFE_TRY(before_velocity());
+  UFE_TRY(velocity_solve(c, cfg, approximation, n_visc_its, n_Axb_its_velocity));
+  UFE_TRY(after_velocity());
+  // corrector: dHi_dt( Hi_n, u_np1) (:214)
+  UFE_TRY(halo_exchange(c, M.b, V.u.p)); UFE_TRY(halo_exchange(c, M.b, V.v.p));
+  UFE_TRY(thickness_step(c, cfg, V.u.p, V.v.p, &dt_c, 1, &its_c));
+  { UFE_LAUNCH(c, TC_THICKNESS); k_pc_correct<<<grid, 128, 0, st>>>(n, M.a.off(), dt, rho_ratio, T.mask_noice.p, P.dHdt_n.p, P.dHdt_nm1.p, T.dHi_dt.p, T.Hb.p, T.SL.p, T.Hi.p, V.Hi.p, V.Hs.p); }
+  UFE_CUDA(cudaGetLastError());
+  *n_Axb_its_thickness = its_p + its_c;
+  return 0;
+}
+
+static int pc_state_ensure(Ctx* c, double dt, bool reset) {
+  Mesh& M = *c->mesh;
+  if (!g_pc) g_pc = new PcState();
+  PcState& P = *g_pc;
+  const size_t na = M.a.n_ext();
+  if (reset || !P.started || P.dHdt_n.n < na) {
+    UFE_TRY(P.dHdt_n.alloc(na)); UFE_TRY(P.dHdt_nm1.alloc(na));
+    UFE_CUDA(cudaMemsetAsync(P.dHdt_n.p, 0, sizeof(double) * na, c->stream)); UFE_CUDA(cudaMemsetAsync(P.dHdt_nm1.p, 0, sizeof(double) * na, c->stream));
+    P.dt_n = dt; P.started = true;
+  }
+  return 0;
+}
+
 }  // namespace ufe
 
 using namespace ufe;
@@ -98,36 +143,82 @@ int ufe_b200_pc_step_resident(ufe_b200_handle h, const ufe_b200_config* cfg, int
   UFE_CHECK(c && cfg && n_visc_its && n_Axb_its_velocity && n_Axb_its_thickness, "NULL argument");
   UFE_CHECK(c->vel && c->vel->uploaded && c->thick, "ufe_b200_pc_step_resident: upload the velocity and thickness inputs first");
   UFE_CUDA(cudaSetDevice(c->device));
-  Mesh& M = *c->mesh; Velocity& V = *c->vel; Thickness& T = *c->thick;
-  cudaStream_t st = c->stream;
-  if (!g_pc) g_pc = new PcState();
-  PcState& P = *g_pc;
-  const size_t na = M.a.n_ext();
-  const int n = M.a.n_loc(), grid = grid_for(c, n, 128, 16);
-  if (!P.started || P.dHdt_n.n < na) {
-    UFE_TRY(P.dHdt_n.alloc(na)); UFE_TRY(P.dHdt_nm1.alloc(na));
-    UFE_CUDA(cudaMemsetAsync(P.dHdt_n.p, 0, sizeof(double) * na, st)); UFE_CUDA(cudaMemsetAsync(P.dHdt_nm1.p, 0, sizeof(double) * na, st));
-    P.dt_n = dt; P.started = true;
+  UFE_TRY(pc_state_ensure(c, dt, false));
+  auto nop = []() { return 0; };
+  UFE_TRY(pc_step_core(c, cfg, approximation, dt, n_visc_its, n_Axb_its_velocity, n_Axb_its_thickness, nop, nop));
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  g_pc->dt_n = dt;
+  return 0;
+}
+
+// Host-buffer variant.  Transfers that the next phase does not depend on go through a second stream:
+//   copy stream : [H2D ice inputs + rest of the velocity state]                [D2H velocity state (3-D fields ...)]
+//   main stream : H2D thickness fields, u, v -> predictor -> (wait) velocity solve (record) -> corrector -> D2H thickness results
+int ufe_b200_pc_step(ufe_b200_handle h, const ufe_b200_config* cfg, int approximation, double dt, double dt_prev,
+                     const ufe_b200_ice_inputs* ice, ufe_b200_velocity_state* state, const ufe_b200_thickness_io* io, double* dHi_dt_nm1,
+                     int* n_visc_its, int* n_Axb_its_velocity, int* n_Axb_its_thickness) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && cfg && ice && state && io && dHi_dt_nm1 && n_visc_its && n_Axb_its_velocity && n_Axb_its_thickness, "NULL argument");
+  UFE_CHECK(io->Hi && io->Hb && io->SL && io->SMB && io->BMB && io->LMB && io->fraction_margin && io->mask_noice && io->dHi_dt_target,
+            "ufe_b200_pc_step: Hi, Hb, SL, SMB, BMB, LMB, fraction_margin, mask_noice, dHi_dt_target are required");
+  UFE_CHECK(state->u_vav_b && state->v_vav_b, "ufe_b200_pc_step: the velocity state needs u_vav_b and v_vav_b");
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_TRY(ensure_thickness(c));
+  UFE_TRY(ensure_velocity(c));
+  Mesh& M = *c->mesh; Thickness& T = *c->thick;
+  cudaStream_t main_st = c->stream;
+  if (!c->copy_stream) {
+    UFE_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    UFE_CUDA(cudaEventCreateWithFlags(&c->ev_copy_a, cudaEventDisableTiming));
+    UFE_CUDA(cudaEventCreateWithFlags(&c->ev_copy_b, cudaEventDisableTiming));
   }
-  const double zeta = dt / P.dt_n;
-  const double rho_ratio = cfg->ice_density / cfg->seawater_density;
-  int its_p = 0, its_c = 0;
-  double dt_p = dt, dt_c = dt;
-  // predictor: dHi_dt( Hi_n, u_n) (:129)
-  UFE_TRY(halo_exchange(c, M.b, V.u.p)); UFE_TRY(halo_exchange(c, M.b, V.v.p));
-  UFE_TRY(thickness_step(c, cfg, V.u.p, V.v.p, &dt_p, 1, &its_p));
-  UFE_CUDA(cudaMemcpyAsync(P.dHdt_n.p, T.dHi_dt.p, sizeof(double) * na, cudaMemcpyDeviceToDevice, st));
-  { UFE_LAUNCH(c, TC_THICKNESS); k_pc_predict<<<grid, 128, 0, st>>>(n, M.a.off(), dt, zeta, rho_ratio, T.mask_noice.p, T.Hi.p, P.dHdt_n.p, P.dHdt_nm1.p, T.Hb.p, T.SL.p, V.Hi.p, V.Hs.p); }
-  // velocities for the predicted geometry (:186)
-  UFE_TRY(velocity_solve(c, cfg, approximation, n_visc_its, n_Axb_its_velocity));
-  // corrector: dHi_dt( Hi_n, u_np1) (:214)
-  UFE_TRY(halo_exchange(c, M.b, V.u.p)); UFE_TRY(halo_exchange(c, M.b, V.v.p));
-  UFE_TRY(thickness_step(c, cfg, V.u.p, V.v.p, &dt_c, 1, &its_c));
-  { UFE_LAUNCH(c, TC_THICKNESS); k_pc_correct<<<grid, 128, 0, st>>>(n, M.a.off(), dt, rho_ratio, T.mask_noice.p, P.dHdt_n.p, P.dHdt_nm1.p, T.dHi_dt.p, T.Hb.p, T.SL.p, T.Hi.p, V.Hi.p, V.Hs.p); }
-  UFE_CUDA(cudaGetLastError());
-  UFE_CUDA(cudaStreamSynchronize(st));
+  UFE_TRY(pc_state_ensure(c, dt_prev, false));
+  PcState& P = *g_pc;
+  P.dt_n = dt_prev > 0.0 ? dt_prev : dt;
+  const size_t nb_a = sizeof(double) * M.a.n_loc();
+  {  // what the predictor needs, on the main stream
+    UFE_REGION(c, TC_H2D);
+    auto up = [&](double* d, const double* s) { return cudaMemcpyAsync(d + M.a.off(), s, nb_a, cudaMemcpyHostToDevice, main_st); };
+    UFE_CUDA(up(T.Hi.p, io->Hi)); UFE_CUDA(up(T.Hb.p, io->Hb)); UFE_CUDA(up(T.SL.p, io->SL)); UFE_CUDA(up(T.SMB.p, io->SMB));
+    UFE_CUDA(up(T.BMB.p, io->BMB)); UFE_CUDA(up(T.LMB.p, io->LMB)); UFE_CUDA(up(T.fraction_margin.p, io->fraction_margin));
+    UFE_CUDA(up(T.target.p, io->dHi_dt_target)); UFE_CUDA(up(P.dHdt_nm1.p, dHi_dt_nm1));
+    UFE_CUDA(cudaMemcpyAsync(T.mask_noice.p + M.a.off(), io->mask_noice, sizeof(int) * M.a.n_loc(), cudaMemcpyHostToDevice, main_st));
+    if (io->BC_prescr_mask && io->BC_prescr_Hi) {
+      UFE_CUDA(cudaMemcpyAsync(T.bc_mask.p + M.a.off(), io->BC_prescr_mask, sizeof(int) * M.a.n_loc(), cudaMemcpyHostToDevice, main_st));
+      UFE_CUDA(up(T.bc_Hi.p, io->BC_prescr_Hi));
+      T.have_bc = true;
+    } else T.have_bc = false;
+    UFE_TRY(velocity_upload(c, nullptr, state, VU_STATE_UV));
+  }
+  {  // everything else the velocity solve needs, on the copy stream, while the predictor runs
+    c->stream = c->copy_stream;
+    int rc;
+    { UFE_REGION(c, TC_H2D); rc = velocity_upload(c, ice, state, VU_STATE_REST | VU_SKIP_GEOMETRY); }
+    cudaError_t e = cudaEventRecord(c->ev_copy_a, c->copy_stream);
+    c->stream = main_st;
+    UFE_TRY(rc);
+    UFE_CUDA(e);
+  }
+  auto before_velocity = [&]() -> int { UFE_CUDA(cudaStreamWaitEvent(main_st, c->ev_copy_a, 0)); return 0; };
+  auto after_velocity = [&]() -> int {   // the velocity state is final: start bringing it back while the corrector runs
+    UFE_CUDA(cudaEventRecord(c->ev_copy_b, main_st));
+    UFE_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_copy_b, 0));
+    c->stream = c->copy_stream;
+    int rc;
+    { UFE_REGION(c, TC_D2H); rc = velocity_download(c, state, false); }
+    c->stream = main_st;
+    return rc;
+  };
+  UFE_TRY(pc_step_core(c, cfg, approximation, dt, n_visc_its, n_Axb_its_velocity, n_Axb_its_thickness, before_velocity, after_velocity));
+  {
+    UFE_REGION(c, TC_D2H);
+    auto dn = [&](double* d, const double* s) { return d ? cudaMemcpyAsync(d, s + M.a.off(), nb_a, cudaMemcpyDeviceToHost, main_st) : cudaSuccess; };
+    UFE_CUDA(dn(io->Hi_tplusdt, T.Hi.p)); UFE_CUDA(dn(io->dHi_dt, T.dHi_dt.p)); UFE_CUDA(dn(io->divQ, T.divQ.p)); UFE_CUDA(dn(io->AMB, T.AMB.p));
+    UFE_CUDA(dn(dHi_dt_nm1, P.dHdt_nm1.p));
+  }
+  UFE_CUDA(cudaStreamSynchronize(main_st));
+  UFE_CUDA(cudaStreamSynchronize(c->copy_stream));
   P.dt_n = dt;
-  *n_Axb_its_thickness = its_p + its_c;
   return 0;
 }
 

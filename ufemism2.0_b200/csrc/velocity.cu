@@ -626,14 +626,15 @@ static int upload_bc(Ctx* c, const int32_t* mask, const double* bu, const double
   return 0;
 }
 
-static int velocity_upload(Ctx* c, const ufe_b200_ice_inputs* ice, const ufe_b200_velocity_state* st) {
+int velocity_upload(Ctx* c, const ufe_b200_ice_inputs* ice, const ufe_b200_velocity_state* st, int flags) {
   UFE_TRY(ensure_velocity(c));
   Mesh& M = *c->mesh; Velocity& V = *c->vel;
   const int nz = M.nz;
   UFE_REGION(c, TC_H2D);
   if (ice) {
-    UFE_CHECK(ice->Hi && ice->Hs && ice->A_flow && ice->fraction_gr_b && ice->mask_grounded_ice, "ice inputs: Hi, Hs, A_flow, fraction_gr_b, mask_grounded_ice are required");
-    UFE_TRY(h2d_field(c, V.Hi.p, M.a, ice->Hi)); UFE_TRY(h2d_field(c, V.Hs.p, M.a, ice->Hs));
+    UFE_CHECK(((ice->Hi && ice->Hs) || (flags & VU_SKIP_GEOMETRY)) && ice->A_flow && ice->fraction_gr_b && ice->mask_grounded_ice,
+              "ice inputs: Hi, Hs, A_flow, fraction_gr_b, mask_grounded_ice are required");
+    if (!(flags & VU_SKIP_GEOMETRY)) { UFE_TRY(h2d_field(c, V.Hi.p, M.a, ice->Hi)); UFE_TRY(h2d_field(c, V.Hs.p, M.a, ice->Hs)); }
     UFE_TRY(h2d_field(c, V.A_flow.p, M.a, ice->A_flow, nz)); UFE_TRY(h2d_field(c, V.fraction_gr_b.p, M.b, ice->fraction_gr_b));
     UFE_TRY(h2d_field(c, V.till_friction_angle.p, M.a, ice->till_friction_angle)); UFE_TRY(h2d_field(c, V.beta_sq.p, M.a, ice->beta_sq));
     UFE_TRY(h2d_field(c, V.alpha_sq.p, M.a, ice->alpha_sq)); UFE_TRY(h2d_field(c, V.effective_pressure.p, M.a, ice->effective_pressure));
@@ -653,8 +654,10 @@ static int velocity_upload(Ctx* c, const ufe_b200_ice_inputs* ice, const ufe_b20
       V.grounded_ice_exists = f > 0.0;
     }
   }
-  if (st) {
+  if (st && (flags & VU_STATE_UV)) {
     UFE_TRY(h2d_field(c, V.u.p, M.b, (const double*)st->u_vav_b)); UFE_TRY(h2d_field(c, V.v.p, M.b, (const double*)st->v_vav_b));
+  }
+  if (st && (flags & VU_STATE_REST)) {
     UFE_TRY(h2d_field(c, V.u_base.p, M.b, (const double*)st->u_base_b)); UFE_TRY(h2d_field(c, V.v_base.p, M.b, (const double*)st->v_base_b));
     UFE_TRY(h2d_field(c, V.tau_bx.p, M.b, (const double*)st->tau_bx_b)); UFE_TRY(h2d_field(c, V.tau_by.p, M.b, (const double*)st->tau_by_b));
     UFE_TRY(h2d_field(c, V.eta_3D_b.p, M.b, (const double*)st->eta_3D_b, nz));
@@ -663,7 +666,7 @@ static int velocity_upload(Ctx* c, const ufe_b200_ice_inputs* ice, const ufe_b20
   return 0;
 }
 
-static int velocity_download(Ctx* c, ufe_b200_velocity_state* st) {
+int velocity_download(Ctx* c, ufe_b200_velocity_state* st, bool sync) {
   UFE_CHECK(c->vel && c->vel->uploaded, "velocity_download: nothing on the device");
   Mesh& M = *c->mesh; Velocity& V = *c->vel;
   const int nz = M.nz;
@@ -688,7 +691,7 @@ static int velocity_download(Ctx* c, ufe_b200_velocity_state* st) {
   UFE_TRY(d2h_field(c, st->basal_friction_coefficient_b, V.beta_b.p, M.b));
   UFE_TRY(d2h_field(c, st->beta_eff_a, V.beta_eff_a.p, M.a)); UFE_TRY(d2h_field(c, st->beta_eff_b, V.beta_eff_b.p, M.b));
   }
-  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  if (sync) UFE_CUDA(cudaStreamSynchronize(c->stream));
   return 0;
 }
 

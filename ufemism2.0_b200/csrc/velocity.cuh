@@ -43,6 +43,11 @@ struct Velocity {
 };
 
 void velocity_free(Velocity* v);
+// host -> device copies of the velocity solve's inputs on c->stream (no synchronisation); flags select what is copied
+enum { VU_STATE_UV = 1, VU_STATE_REST = 2, VU_SKIP_GEOMETRY = 4, VU_ALL = VU_STATE_UV | VU_STATE_REST };
+int velocity_upload(Ctx* c, const ufe_b200_ice_inputs* ice, const ufe_b200_velocity_state* st, int flags = VU_ALL);
+// device -> host copies of every non-NULL field of st on c->stream, then (sync) a synchronise of that stream
+int velocity_download(Ctx* c, ufe_b200_velocity_state* st, bool sync = true);
 int ensure_velocity(Ctx* c);
 // solve_DIVA_infinite_slab (approximation = 1) / solve_SSA (0) on device-resident fields
 int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n_visc_its, int* n_Axb_its);

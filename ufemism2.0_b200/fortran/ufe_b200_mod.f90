@@ -131,6 +131,30 @@ module ufe_b200_mod
       integer(c_int) :: ierr
     end function
 
+    ! multigrid preconditioner of the SSA/DIVA solve (C%B200_PC_type_config = 'multigrid' -> cfg%pc_type = 4)
+    function c_ufe_b200_set_mg_params( h, nu_pre, nu_post, omega, overcorr, w_levels, fp32, dense_max) &
+      bind(C, name='ufe_b200_set_mg_params') result( ierr)
+      import :: c_int, c_double, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: nu_pre, nu_post, w_levels, fp32, dense_max
+      real(c_double), value :: omega, overcorr
+      integer(c_int) :: ierr
+    end function
+
+    ! one predictor-corrector step through host arrays (device phases of run_ice_dynamics_model_pc, predictor_corrector_scheme.f90:118-233)
+    function c_ufe_b200_pc_step( h, cfg, approximation, dt, dt_prev, ice, state, io, dHi_dt_nm1, n_visc_its, n_Axb_its_velocity, &
+      n_Axb_its_thickness) bind(C, name='ufe_b200_pc_step') result( ierr)
+      import :: c_int, c_double, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      integer(c_int), value :: approximation
+      real(c_double), value :: dt, dt_prev
+      type(c_ptr), value :: ice, state, io            ! c_loc of ufe_b200_ice_inputs / _velocity_state / _thickness_io filled with c_loc of the model arrays
+      real(c_double), intent(inout) :: dHi_dt_nm1(*)  ! region%ice%pc%dHi_dt_Hnm1_unm1( vi1:vi2) in, %dHi_dt_Hn_un out
+      integer(c_int), intent(out) :: n_visc_its, n_Axb_its_velocity, n_Axb_its_thickness
+      integer(c_int) :: ierr
+    end function
+
   end interface
 
 contains

@@ -184,6 +184,8 @@ def lib():
     L.ufe_b200_thickness_upload.argtypes = [H, C.POINTER(ThicknessIO)]
     L.ufe_b200_pc_step_resident.argtypes = [H, C.POINTER(Config), C.c_int, C.c_double] + [C.POINTER(C.c_int)] * 3
     L.ufe_b200_thickness_download.argtypes = [H, c_dp, c_dp, c_dp]
+    L.ufe_b200_pc_step.argtypes = [H, C.POINTER(Config), C.c_int, C.c_double, C.c_double, C.POINTER(IceInputs), C.POINTER(VelocityState),
+                                   C.POINTER(ThicknessIO), c_dp] + [C.POINTER(C.c_int)] * 3
     L.ufe_b200_solve_SIA.argtypes = [H, C.POINTER(Config), c_dp, c_dp, c_dp, c_dp, c_dp]
     L.ufe_b200_timing_enable.argtypes = [H, C.c_int]
     L.ufe_b200_timing_get.argtypes = [H, C.c_char_p, c_dp, C.POINTER(C.c_longlong)]
@@ -204,7 +206,7 @@ ABI_SYMBOLS = [
     "ufe_b200_apply_operator", "ufe_b200_solve_SSA_DIVA_linearised", "ufe_b200_get_stiffness_size", "ufe_b200_get_stiffness", "ufe_b200_get_stiffness_storage_bytes",
     "ufe_b200_set_mg_params", "ufe_b200_get_mg_info", "ufe_b200_mg_host_transfer", "ufe_b200_mg_host_transfer_get",
     "ufe_b200_solve_DIVA", "ufe_b200_solve_SSA", "ufe_b200_velocity_upload", "ufe_b200_velocity_solve_resident",
-    "ufe_b200_velocity_download", "ufe_b200_thickness_upload", "ufe_b200_pc_step_resident",
+    "ufe_b200_velocity_download", "ufe_b200_thickness_upload", "ufe_b200_pc_step_resident", "ufe_b200_pc_step",
     "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA",
     "ufe_b200_timing_enable", "ufe_b200_timing_get", "ufe_b200_timing_reset", "ufe_b200_timer_start", "ufe_b200_timer_stop",
     "ufe_b200_host_register", "ufe_b200_host_unregister"]
