@@ -192,6 +192,14 @@ int ufe_b200_get_mg_info(ufe_b200_handle h, int* n_levels, int* nodes_per_level,
  * agg[n], coarse_slice_ptr[(nc+31)/32 + 1], coarse_col[coarse_slots], gal_ptr[coarse_slots + 1], gal_src[gather_entries]. */
 int ufe_b200_mg_host_transfer(int n, int off, const int32_t* slice_ptr, const int32_t* col, int* nc, long long* coarse_slots, long long* gather_entries);
 int ufe_b200_mg_host_transfer_get(int32_t* agg, int32_t* coarse_slice_ptr, int32_t* coarse_col, int32_t* gal_ptr, int32_t* gal_src);
+/* The same for rows split into nparts row blocks (= ranks), emulated in one process with the exchanges replaced by copies: part p owns nodes
+ * off[p] .. off[p]+n[p]-1 of one global numbering of n_total nodes (col holds global ids), its pattern starts at slice_ptr[sp_start[p]] /
+ * col[col_start[p]].  Outputs: agg_glob[n_total] (global coarse ids), the assembled coarse pattern, and per part a gather list over the
+ * assembled coarse slots: gal_ptr[nparts * (coarse_slots + 1)], gal_src (part p at gal_src_start[p] .. gal_src_start[p+1]). */
+int ufe_b200_mg_host_transfer_parts(int nparts, int n_total, const int32_t* n, const int32_t* off, const int32_t* sp_start, const int32_t* col_start,
+                                    const int32_t* slice_ptr, const int32_t* col, int* nc, long long* coarse_slots, long long* gather_entries);
+int ufe_b200_mg_host_transfer_parts_get(int32_t* agg_glob, int32_t* coarse_slice_ptr, int32_t* coarse_col, int32_t* gal_ptr, int32_t* gal_src,
+                                        int32_t* gal_src_start);
 
 /* Inputs of the velocity solve taken from type_ice_model / type_bed_roughness_model (owned slices). */
 typedef struct ufe_b200_ice_inputs {

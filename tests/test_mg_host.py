@@ -112,3 +112,53 @@ def test_isolated_nodes_are_grouped():
     sp, col = sliced_ell(n, 0, nbrs)
     nc, agg, *_ = host_transfer(n, 0, sp, col)
     assert nc == 13 and np.bincount(agg).max() == 8
+
+
+@pytest.mark.parametrize("nparts", [2, 3])
+def test_split_rows_assemble_the_global_galerkin_product(nparts):
+    """rows split over ranks (emulated): every part coarsens its own block, the coarse level is assembled from all parts and the sum of the
+    parts' Galerkin gathers (= the all-reduce on the device) is P^T A P of the WHOLE matrix, couplings across the cuts included"""
+    rng = np.random.default_rng(11)
+    n, _off, nbrs = grid_pattern(29, 13, rng, halo=0)      # global ids
+    cuts = [0] + sorted(int(x) for x in rng.choice(np.arange(40, n - 40), nparts - 1, replace=False)) + [n]
+    sps, cols, sp_start, col_start, ns, offs = [], [], [], [], [], []
+    for p in range(nparts):
+        a, b = cuts[p], cuts[p + 1]
+        sp, col = sliced_ell(b - a, a, nbrs[a:b])
+        sp_start.append(sum(len(x) for x in sps)); col_start.append(sum(len(x) for x in cols))
+        sps.append(sp); cols.append(col); ns.append(b - a); offs.append(a)
+    i32 = lambda x: np.ascontiguousarray(x, np.int32)
+    SP, COL = i32(np.concatenate(sps)), i32(np.concatenate(cols))
+    L = ub.lib()
+    nc, cs, ge = C.c_int(), C.c_longlong(), C.c_longlong()
+    ub.check(L.ufe_b200_mg_host_transfer_parts(nparts, n, ub.ip(i32(ns)), ub.ip(i32(offs)), ub.ip(i32(sp_start)), ub.ip(i32(col_start)), ub.ip(SP),
+                                               ub.ip(COL), C.byref(nc), C.byref(cs), C.byref(ge)))
+    agg = np.zeros(n, np.int32); csp = np.zeros((nc.value + 31) // 32 + 1, np.int32); ccol = np.zeros(cs.value, np.int32)
+    gp = np.zeros(nparts * (cs.value + 1), np.int32); gs = np.zeros(ge.value, np.int32); gstart = np.zeros(nparts + 1, np.int32)
+    ub.check(L.ufe_b200_mg_host_transfer_parts_get(ub.ip(agg), ub.ip(csp), ub.ip(ccol), ub.ip(gp), ub.ip(gs), ub.ip(gstart)))
+    assert agg.min() == 0 and agg.max() == nc.value - 1
+    # aggregates never cross a cut and are numbered part after part
+    for p in range(nparts - 1):
+        assert agg[cuts[p]:cuts[p + 1]].max() < agg[cuts[p + 1]:cuts[p + 2]].min()
+    # per-part values, per-part gathers, then the sum over parts
+    A = np.zeros((2 * n, 2 * n)); cval = np.zeros(len(ccol) * 4)
+    for p in range(nparts):
+        a, b = cuts[p], cuts[p + 1]
+        sp, col = sps[p], cols[p]
+        val = np.zeros(int(sp[-1]) * 32 * 4)
+        for t in range(b - a):
+            s, lane = divmod(t, 32)
+            for j in range(len(nbrs[a + t])):
+                for q in range(4):
+                    val[((sp[s] + j) * 4 + q) * 32 + lane] = rng.standard_normal()
+        A[2 * a:2 * b, :] = dense_from_ell(b - a, a, sp, col, val, n)
+        gpp = gp[p * (cs.value + 1):(p + 1) * (cs.value + 1)]; gsp = gs[gstart[p]:gstart[p + 1]]
+        for c_ in range(len(ccol)):
+            for fs in gsp[gpp[c_]:gpp[c_ + 1]]:
+                for q in range(4):
+                    cval[((c_ >> 5) * 4 + q) * 32 + (c_ & 31)] += val[((fs >> 5) * 4 + q) * 32 + (fs & 31)]
+    P = np.zeros((2 * n, 2 * nc.value))
+    for t in range(n):
+        P[2 * t, 2 * agg[t]] = 1.0; P[2 * t + 1, 2 * agg[t] + 1] = 1.0
+    Ac = dense_from_ell(nc.value, 0, csp, ccol, cval, nc.value)
+    np.testing.assert_allclose(Ac, P.T @ A @ P, rtol=1e-12, atol=1e-12)

@@ -158,5 +158,8 @@ int halo_exchange(Ctx* c, const Range& r, double* v, int ncols = 1, int elems_pe
 int halo_exchange_int(Ctx* c, const Range& r, int* v);
 int allreduce_sum(Ctx* c, double* d_vals, int n);
 int allreduce_min(Ctx* c, double* d_vals, int n);
+int allreduce_sum_large(Ctx* c, void* d_vals, size_t n, bool is_float);   // in place, double or float
+// all-gather of variable-length int lists through device buffers (setup paths only): counts[r], concatenation in rank order
+int allgatherv_int(Ctx* c, const std::vector<int>& mine, std::vector<int>& counts, std::vector<int>& all);
 
 }  // namespace ufe

@@ -3,6 +3,8 @@
 // (reference: src/UFEMISM/main/UFEMISM_program.f90:55-56; src/UPSY/basic/mpi_parallelisation/mpi_basic.f90:37-76).
 #include <cuda_profiler_api.h>
 
+#include <algorithm>
+
 #include "nccl_dl.cuh"
 #include "krylov.cuh"
 #include "mesh.cuh"
@@ -131,6 +133,43 @@ int allreduce_sum(Ctx* c, double* d, int n) {
   if (!N) return 3;
   ncclResult_t r = N->AllReduce(d, d, n, ncclDouble, ncclSum, (ncclComm_t)c->nccl, c->stream);
   UFE_CHECK(r == ncclSuccess, "ncclAllReduce(sum): %s", N->GetErrorString(r));
+  return 0;
+}
+int allreduce_sum_large(Ctx* c, void* d, size_t n, bool is_float) {
+  if (c->nranks == 1) return 0;
+  NcclApi* N = nccl_api();
+  if (!N) return 3;
+  ncclResult_t r = N->AllReduce(d, d, n, is_float ? ncclFloat : ncclDouble, ncclSum, (ncclComm_t)c->nccl, c->stream);
+  UFE_CHECK(r == ncclSuccess, "ncclAllReduce(sum): %s", N->GetErrorString(r));
+  return 0;
+}
+int allgatherv_int(Ctx* c, const std::vector<int>& mine, std::vector<int>& counts, std::vector<int>& all) {
+  counts.assign(c->nranks, 0);
+  if (c->nranks == 1) { counts[0] = (int)mine.size(); all = mine; return 0; }
+  NcclApi* N = nccl_api();
+  if (!N) return 3;
+  ncclComm_t comm = (ncclComm_t)c->nccl;
+  DBuf<int> d_cnt;
+  UFE_TRY(d_cnt.alloc(c->nranks));
+  const int my = (int)mine.size();
+  UFE_CUDA(cudaMemcpyAsync(d_cnt.p + c->rank, &my, sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  ncclResult_t r = N->AllGather(d_cnt.p + c->rank, d_cnt.p, 1, ncclInt32, comm, c->stream);
+  UFE_CHECK(r == ncclSuccess, "ncclAllGather(counts): %s", N->GetErrorString(r));
+  UFE_CUDA(cudaMemcpyAsync(counts.data(), d_cnt.p, sizeof(int) * c->nranks, cudaMemcpyDeviceToHost, c->stream));
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  size_t maxc = 1, total = 0;
+  for (int q : counts) { maxc = std::max(maxc, (size_t)q); total += q; }
+  DBuf<int> d_buf;
+  UFE_TRY(d_buf.alloc(maxc * c->nranks));
+  if (my > 0) UFE_CUDA(cudaMemcpyAsync(d_buf.p + maxc * c->rank, mine.data(), sizeof(int) * my, cudaMemcpyHostToDevice, c->stream));
+  r = N->AllGather(d_buf.p + maxc * c->rank, d_buf.p, maxc, ncclInt32, comm, c->stream);
+  UFE_CHECK(r == ncclSuccess, "ncclAllGather(data): %s", N->GetErrorString(r));
+  std::vector<int> padded(maxc * c->nranks);
+  UFE_CUDA(cudaMemcpyAsync(padded.data(), d_buf.p, sizeof(int) * padded.size(), cudaMemcpyDeviceToHost, c->stream));
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  all.clear();
+  all.reserve(total);
+  for (int q = 0; q < c->nranks; ++q) all.insert(all.end(), padded.begin() + maxc * q, padded.begin() + maxc * q + counts[q]);
   return 0;
 }
 int allreduce_min(Ctx* c, double* d, int n) {

@@ -99,55 +99,64 @@ int aggregate(int n, const std::vector<size_t>& ptr, const std::vector<int>& adj
   return na;
 }
 
-struct HostTransfer {
-  int nc = 0;
-  std::vector<int> agg, mem_ptr, mem, gal_ptr, gal_src;
-  HostLevel coarse;
-  long long coarse_slots = 0;
+// ---- one coarsening step, written so that the row blocks of several ranks can be coarsened independently and then assembled into
+// ---- one coarse level that every rank holds (single rank: one part) ------------------------------------------------------------
+
+// aggregation of one rank's own nodes: agg = local aggregate ids 0..nc_loc-1, members in ascending fine order
+struct LocalAgg {
+  int nc_loc = 0;
+  std::vector<int> agg, mem_ptr, mem;
 };
 
-void build_transfer(const HostLevel& F, HostTransfer& T) {
-  const int n = F.n;
+void aggregate_part(const HostLevel& F, LocalAgg& A) {
   std::vector<size_t> gptr;
   std::vector<int> gadj;
   build_sym_graph(F, gptr, gadj);
-  T.nc = aggregate(n, gptr, gadj, T.agg);
-  std::vector<size_t>().swap(gptr);
-  std::vector<int>().swap(gadj);
-  const int nc = T.nc;
-  // members (ascending fine index inside an aggregate)
-  T.mem_ptr.assign(nc + 1, 0);
-  for (int i = 0; i < n; ++i) T.mem_ptr[T.agg[i] + 1]++;
-  for (int I = 0; I < nc; ++I) T.mem_ptr[I + 1] += T.mem_ptr[I];
-  T.mem.resize(n);
-  {
-    std::vector<int> fill(T.mem_ptr.begin(), T.mem_ptr.end() - 1);
-    for (int i = 0; i < n; ++i) T.mem[fill[T.agg[i]]++] = i;
-  }
-  // coarse block rows: own aggregate first, then neighbours in order of first appearance
-  const size_t fine_slots = F.col.size();
-  std::vector<int> slotpos(fine_slots, -1);
-  std::vector<int> stamp(nc, -1), posn(nc, 0);
-  std::vector<int> cptr(nc + 1, 0), ccol;
-  ccol.reserve((size_t)nc * 10);
-  for (int I = 0; I < nc; ++I) {
-    const int start = (int)ccol.size();
-    stamp[I] = I; posn[I] = 0; ccol.push_back(I);
-    for (int m = T.mem_ptr[I]; m < T.mem_ptr[I + 1]; ++m) {
-      const int i = T.mem[m], s = i >> 5, lane = i & 31;
+  A.nc_loc = aggregate(F.n, gptr, gadj, A.agg);
+  A.mem_ptr.assign(A.nc_loc + 1, 0);
+  for (int i = 0; i < F.n; ++i) A.mem_ptr[A.agg[i] + 1]++;
+  for (int I = 0; I < A.nc_loc; ++I) A.mem_ptr[I + 1] += A.mem_ptr[I];
+  A.mem.resize(F.n);
+  std::vector<int> fill(A.mem_ptr.begin(), A.mem_ptr.end() - 1);
+  for (int i = 0; i < F.n; ++i) A.mem[fill[A.agg[i]]++] = i;
+}
+
+// coarse block rows of this part's aggregates with GLOBAL coarse column ids: own aggregate first, then neighbours in order of first
+// appearance.  agg_ext[c] = global coarse id of extended node c (own nodes: offset + local id; halo nodes: the neighbour rank's id;
+// -1: unknown, the coupling is dropped).  slotpos[fine slot] = position of its coarse block inside the row (-1: dropped).
+struct LocalRows {
+  std::vector<int> cptr, ccol, slotpos;
+};
+
+void build_local_rows(const HostLevel& F, const LocalAgg& A, const std::vector<int>& agg_ext, int offset, int nc_glob, LocalRows& R) {
+  R.slotpos.assign(F.col.size(), -1);
+  std::vector<int> stamp(nc_glob, -1), posn(nc_glob, 0);
+  R.cptr.assign(A.nc_loc + 1, 0);
+  R.ccol.clear();
+  R.ccol.reserve((size_t)A.nc_loc * 10);
+  const int n_ext = (int)agg_ext.size();
+  for (int I = 0; I < A.nc_loc; ++I) {
+    const int Ig = offset + I;
+    const int start = (int)R.ccol.size();
+    stamp[Ig] = Ig; posn[Ig] = 0; R.ccol.push_back(Ig);
+    for (int m = A.mem_ptr[I]; m < A.mem_ptr[I + 1]; ++m) {
+      const int i = A.mem[m], s = i >> 5, lane = i & 31;
       for (int k = F.slice_ptr[s]; k < F.slice_ptr[s + 1]; ++k) {
         const size_t fs = (size_t)k * 32 + lane;
-        const int cj = F.col[fs] - F.off;
-        if (cj < 0 || cj >= n) continue;   // halo triangle: dropped inside the preconditioner
-        const int J = T.agg[cj];
-        if (stamp[J] != I) { stamp[J] = I; posn[J] = (int)ccol.size() - start; ccol.push_back(J); }
-        slotpos[fs] = posn[J];
+        const int ce = F.col[fs];
+        if (ce < 0 || ce >= n_ext) continue;
+        const int J = agg_ext[ce];
+        if (J < 0) continue;
+        if (stamp[J] != Ig) { stamp[J] = Ig; posn[J] = (int)R.ccol.size() - start; R.ccol.push_back(J); }
+        R.slotpos[fs] = posn[J];
       }
     }
-    cptr[I + 1] = (int)ccol.size();
+    R.cptr[I + 1] = (int)R.ccol.size();
   }
-  // coarse sliced-ELL pattern
-  HostLevel& C = T.coarse;
+}
+
+// sliced-ELL pattern of the assembled coarse level from its rows (cptr/ccol over all nc coarse nodes, global ids)
+void ell_from_rows(int nc, const std::vector<int>& cptr, const std::vector<int>& ccol, HostLevel& C) {
   C.n = nc; C.off = 0;
   const int nsl = (nc + 31) / 32;
   C.slice_ptr.assign(nsl + 1, 0);
@@ -156,8 +165,7 @@ void build_transfer(const HostLevel& F, HostTransfer& T) {
     for (int I = s * 32; I < std::min(nc, s * 32 + 32); ++I) w = std::max(w, cptr[I + 1] - cptr[I]);
     C.slice_ptr[s + 1] = C.slice_ptr[s] + w;
   }
-  T.coarse_slots = (long long)C.slice_ptr[nsl] * 32;
-  C.col.assign((size_t)T.coarse_slots, 0);
+  C.col.assign((size_t)C.slice_ptr[nsl] * 32, 0);
   for (int s = 0; s < nsl; ++s)
     for (int lane = 0; lane < 32; ++lane) {
       const int I = s * 32 + lane;
@@ -168,40 +176,114 @@ void build_transfer(const HostLevel& F, HostTransfer& T) {
         C.col[(size_t)k * 32 + lane] = j < len ? ccol[cptr[I] + j] : pad;
       }
     }
-  // Galerkin gather lists: coarse slot -> fine slots (ascending fine slot order: deterministic sums)
-  T.gal_ptr.assign((size_t)T.coarse_slots + 1, 0);
-  auto coarse_slot = [&](int i, size_t fs) -> long long {
-    const int I = T.agg[i];
-    return ((long long)C.slice_ptr[I >> 5] + slotpos[fs]) * 32 + (I & 31);
+}
+
+// Galerkin gather lists of this part: coarse slot (of the assembled level) -> this part's fine slots, ascending (deterministic sums)
+void build_gather(const HostLevel& F, const LocalAgg& A, int offset, const LocalRows& R, const HostLevel& C, std::vector<int>& gal_ptr,
+                  std::vector<int>& gal_src) {
+  const size_t coarse_slots = C.col.size();
+  gal_ptr.assign(coarse_slots + 1, 0);
+  auto coarse_slot = [&](int i, size_t fs) -> size_t {
+    const int Ig = offset + A.agg[i];
+    return ((size_t)C.slice_ptr[Ig >> 5] + R.slotpos[fs]) * 32 + (Ig & 31);
   };
+  const int n = F.n, nslf = (n + 31) / 32;
   for (int i = 0; i < n; ++i) {
     const int s = i >> 5, lane = i & 31;
     for (int k = F.slice_ptr[s]; k < F.slice_ptr[s + 1]; ++k) {
       const size_t fs = (size_t)k * 32 + lane;
-      if (slotpos[fs] >= 0) T.gal_ptr[coarse_slot(i, fs) + 1]++;
+      if (R.slotpos[fs] >= 0) gal_ptr[coarse_slot(i, fs) + 1]++;
     }
   }
-  for (long long q = 0; q < T.coarse_slots; ++q) T.gal_ptr[q + 1] += T.gal_ptr[q];
-  T.gal_src.resize((size_t)T.gal_ptr[T.coarse_slots]);
+  for (size_t q = 0; q < coarse_slots; ++q) gal_ptr[q + 1] += gal_ptr[q];
+  gal_src.resize((size_t)gal_ptr[coarse_slots]);
+  std::vector<int> fill(gal_ptr.begin(), gal_ptr.end() - 1);
+  for (int s = 0; s < nslf; ++s)
+    for (int k = F.slice_ptr[s]; k < F.slice_ptr[s + 1]; ++k)
+      for (int lane = 0; lane < 32; ++lane) {
+        const int i = s * 32 + lane;
+        if (i >= n) break;
+        const size_t fs = (size_t)k * 32 + lane;
+        if (R.slotpos[fs] >= 0) gal_src[fill[coarse_slot(i, fs)]++] = (int)fs;
+      }
+}
+
+struct HostTransfer {
+  int nc = 0;                 // coarse nodes of the assembled level (all parts)
+  int nc_loc = 0, offset = 0; // this part's aggregates are the coarse nodes offset .. offset + nc_loc - 1
+  std::vector<int> agg;       // GLOBAL coarse id of each own node
+  std::vector<int> mem_ptr, mem, gal_ptr, gal_src;
+  HostLevel coarse;
+  long long coarse_slots = 0;
+};
+
+// single part (one rank, and every level >= 1): the extended range holds nothing but the own nodes' aggregates
+void build_transfer(const HostLevel& F, HostTransfer& T) {
+  LocalAgg A;
+  aggregate_part(F, A);
+  std::vector<int> agg_ext;
   {
-    std::vector<int> fill(T.gal_ptr.begin(), T.gal_ptr.end() - 1);
-    // fine slots in ascending slot order: iterate k-steps of a slice, lanes inside
-    const int nslf = (n + 31) / 32;
-    for (int s = 0; s < nslf; ++s)
-      for (int k = F.slice_ptr[s]; k < F.slice_ptr[s + 1]; ++k)
-        for (int lane = 0; lane < 32; ++lane) {
-          const int i = s * 32 + lane;
-          if (i >= n) break;
-          const size_t fs = (size_t)k * 32 + lane;
-          if (slotpos[fs] >= 0) T.gal_src[fill[coarse_slot(i, fs)]++] = (int)fs;
-        }
+    int n_ext = F.off + F.n;
+    for (int v : F.col) n_ext = std::max(n_ext, v + 1);
+    agg_ext.assign(n_ext, -1);                      // halo triangles (other ranks' rows) are dropped
+    for (int i = 0; i < F.n; ++i) agg_ext[F.off + i] = A.agg[i];
   }
+  LocalRows R;
+  build_local_rows(F, A, agg_ext, 0, A.nc_loc, R);
+  ell_from_rows(A.nc_loc, R.cptr, R.ccol, T.coarse);
+  build_gather(F, A, 0, R, T.coarse, T.gal_ptr, T.gal_src);
+  T.nc = T.nc_loc = A.nc_loc; T.offset = 0;
+  T.coarse_slots = (long long)T.coarse.col.size();
+  T.agg = std::move(A.agg); T.mem_ptr = std::move(A.mem_ptr); T.mem = std::move(A.mem);
+}
+
+// assembled coarse rows of all parts: lens (one per coarse node, rank order) and the concatenated global column ids
+void rows_from_parts(const std::vector<int>& all_lens, std::vector<int>& cptr) {
+  cptr.assign(all_lens.size() + 1, 0);
+  for (size_t I = 0; I < all_lens.size(); ++I) cptr[I + 1] = cptr[I] + all_lens[I];
 }
 
 template <typename T>
 int upload(Ctx* c, DBuf<T>& d, const std::vector<T>& h) {
   UFE_TRY(d.alloc(h.size() ? h.size() : 1));
   if (!h.empty()) UFE_CUDA(cudaMemcpyAsync(d.p, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice, c->stream));
+  return 0;
+}
+
+// level 0 -> 1 when the matrix rows are split over ranks: aggregate the own block, exchange the aggregate ids of the halo triangles, build
+// the own coarse rows with global column ids, all-gather the rows and assemble the (replicated) level 1
+int build_transfer_distributed(Ctx* c, const HostLevel& F, const Range& rb, HostTransfer& T) {
+  LocalAgg A;
+  aggregate_part(F, A);
+  std::vector<int> counts, dummy;
+  UFE_TRY(allgatherv_int(c, std::vector<int>{A.nc_loc}, counts, dummy));
+  int offset = 0, nc_glob = 0;
+  for (int q = 0; q < c->nranks; ++q) { if (q < c->rank) offset += dummy[q]; nc_glob += dummy[q]; }
+  // global aggregate id of every triangle of the extended range
+  std::vector<int> agg_ext(rb.n_ext(), -1);
+  for (int i = 0; i < F.n; ++i) agg_ext[F.off + i] = offset + A.agg[i];
+  {
+    DBuf<int> d_ext;
+    UFE_TRY(upload(c, d_ext, agg_ext));
+    UFE_TRY(halo_exchange_int(c, rb, d_ext.p));
+    UFE_CUDA(cudaMemcpyAsync(agg_ext.data(), d_ext.p, sizeof(int) * agg_ext.size(), cudaMemcpyDeviceToHost, c->stream));
+    UFE_CUDA(cudaStreamSynchronize(c->stream));
+  }
+  LocalRows R;
+  build_local_rows(F, A, agg_ext, offset, nc_glob, R);
+  std::vector<int> lens(A.nc_loc), all_lens, all_cols, cptr;
+  for (int I = 0; I < A.nc_loc; ++I) lens[I] = R.cptr[I + 1] - R.cptr[I];
+  UFE_TRY(allgatherv_int(c, lens, counts, all_lens));
+  UFE_TRY(allgatherv_int(c, R.ccol, counts, all_cols));
+  UFE_CHECK((int)all_lens.size() == nc_glob, "multigrid: assembled %zu coarse rows, expected %d", all_lens.size(), nc_glob);
+  rows_from_parts(all_lens, cptr);
+  ell_from_rows(nc_glob, cptr, all_cols, T.coarse);
+  build_gather(F, A, offset, R, T.coarse, T.gal_ptr, T.gal_src);
+  T.nc = nc_glob; T.nc_loc = A.nc_loc; T.offset = offset;
+  T.coarse_slots = (long long)T.coarse.col.size();
+  T.agg.resize(F.n);
+  for (int i = 0; i < F.n; ++i) T.agg[i] = offset + A.agg[i];
+  T.mem_ptr = std::move(A.mem_ptr); T.mem = std::move(A.mem);
   return 0;
 }
 
@@ -560,16 +642,21 @@ int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out) {
     return 0;
   }
   MgLevel& Cn = G.lv[l + 1];
+  const bool split = l == 0 && G.distributed;   // level 0 is a row block: its iterates need the neighbours' halo before every matrix pass
   { UFE_LAUNCH(c, l == 0 ? TC_MG_VEC : TC_MG_COARSE); k_mg_smooth0<<<gv, kBlock, 0, st>>>(L.n, b, L.dblk.p, xa + 2 * L.off); }
   for (int s = 1; s < P.nu_pre; ++s) {
+    if (split) UFE_TRY(halo_exchange(c, G.rb, xa, 1, 2));
     launch_sweep<VT, 0>(c, L, l, xa, b, xb + 2 * L.off);
     std::swap(xa, xb);
   }
+  if (split) UFE_TRY(halo_exchange(c, G.rb, xa, 1, 2));
   launch_sweep<VT, 1>(c, L, l, xa, b, L.r.p);
+  if (split) UFE_CUDA(cudaMemsetAsync(Cn.b.p, 0, sizeof(double) * 2 * (size_t)Cn.n, st));
   {
     UFE_LAUNCH(c, l == 0 ? TC_MG_VEC : TC_MG_COARSE);
-    k_mg_restrict<<<grid_for(c, L.nc, kBlock), kBlock, 0, st>>>(L.nc, L.mem_ptr.p, L.mem.p, L.r.p, Cn.b.p);
+    k_mg_restrict<<<grid_for(c, L.nc_loc, kBlock), kBlock, 0, st>>>(L.nc_loc, L.mem_ptr.p, L.mem.p, L.r.p, Cn.b.p + 2 * (size_t)L.c_offset);
   }
+  if (split) UFE_TRY(allreduce_sum_large(c, Cn.b.p, 2 * (size_t)Cn.n, false));   // every rank now holds the whole level-1 right-hand side
   if (l == 0) UFE_TRY(mg_coarse_from_fine<VT>(c, G));
   else UFE_TRY(mg_coarse_correction<VT>(c, G, l));
   {
@@ -578,6 +665,7 @@ int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out) {
   }
   for (int s = 0; s < P.nu_post; ++s) {
     double* dst = (s == P.nu_post - 1) ? out : xb + 2 * L.off;
+    if (split) UFE_TRY(halo_exchange(c, G.rb, xa, 1, 2));
     launch_sweep<VT, 0>(c, L, l, xa, b, dst);
     std::swap(xa, xb);
   }
@@ -600,6 +688,10 @@ int mg_numeric(Ctx* c, Mg& G) {
       UFE_LAUNCH(c, TC_MG_SETUP);
       k_mg_galerkin<VT, VT><<<grid_for(c, Cn.n_slots, kBlock), kBlock, 0, st>>>(Cn.n_slots, L.gal_ptr.p, L.gal_src.p, level_values<VT>(L), cv);
     }
+    if (l == 0 && G.distributed && nl > 1) {   // each rank summed the blocks of its own coarse rows (zeros elsewhere): complete the replicated level 1
+      VT* cv = const_cast<VT*>(level_values<VT>(G.lv[1]));
+      UFE_TRY(allreduce_sum_large(c, cv, (size_t)G.lv[1].n_slots * 4, sizeof(VT) == 4));
+    }
   }
   if (G.dense_n > 0) {
     MgLevel& L = G.lv[nl - 1];
@@ -617,7 +709,10 @@ int mg_numeric(Ctx* c, Mg& G) {
 // =====================================================================================================================
 // public entry points
 // =====================================================================================================================
-int mg_build(Ctx* c, Mg& G, const BlkMat& B, int off_tri, int n_ext_tri) {
+int mg_build(Ctx* c, Mg& G, const BlkMat& B, const Range& rb) {
+  const int off_tri = rb.off(), n_ext_tri = rb.n_ext();
+  G.distributed = c->nranks > 1;
+  G.rb = rb;
   const auto t_start = std::chrono::steady_clock::now();
   G.valid = false;
   G.drop_graph();
@@ -641,12 +736,14 @@ int mg_build(Ctx* c, Mg& G, const BlkMat& B, int off_tri, int n_ext_tri) {
   }
   while (true) {
     MgLevel& L = G.lv.back();
-    const bool small = L.n <= G.p.dense_max;
+    const bool small = L.n <= G.p.dense_max && !(G.distributed && G.lv.size() == 1);   // a split level 0 is never the coarsest
     if (small || (int)G.lv.size() >= G.p.max_levels) break;
     HostTransfer T;
-    build_transfer(H, T);
-    if (T.nc >= L.n || T.nc * 10 > L.n * 9) break;   // coarsening stalled: stop here, smooth on this level
-    L.nc = T.nc;
+    const bool split = G.distributed && G.lv.size() == 1;
+    if (split) UFE_TRY(build_transfer_distributed(c, H, rb, T));
+    else build_transfer(H, T);
+    if (!split && (T.nc >= L.n || T.nc * 10 > L.n * 9)) break;   // coarsening stalled: stop here, smooth on this level
+    L.nc = T.nc; L.nc_loc = T.nc_loc; L.c_offset = T.offset;
     UFE_TRY(upload(c, L.agg, T.agg)); UFE_TRY(upload(c, L.mem_ptr, T.mem_ptr)); UFE_TRY(upload(c, L.mem, T.mem));
     UFE_TRY(upload(c, L.gal_ptr, T.gal_ptr)); UFE_TRY(upload(c, L.gal_src, T.gal_src));
     G.gather_entries += (long long)T.gal_src.size();
@@ -842,5 +939,73 @@ extern "C" int ufe_b200_mg_host_transfer_get(int32_t* agg, int32_t* coarse_slice
   copy(agg, T.agg); copy(coarse_slice_ptr, T.coarse.slice_ptr); copy(coarse_col, T.coarse.col); copy(gal_ptr, T.gal_ptr); copy(gal_src, T.gal_src);
   delete g_host_transfer;
   g_host_transfer = nullptr;
+  return 0;
+}
+
+// the same pattern phase for a matrix whose rows are split into parts (= ranks), emulated in one process: part p owns the nodes
+// off[p] .. off[p] + n[p] - 1 of one global numbering (its extended range is the whole range), its sliced-ELL pattern starts at
+// slice_ptr[sp_start[p]] / col[col_start[p]].  Exactly the code path of build_transfer_distributed with the exchanges replaced by copies.
+struct HostPartsResult {
+  std::vector<int> agg_glob, gal_ptr, gal_src, gal_src_start;
+  ufe::HostLevel coarse;
+};
+static thread_local HostPartsResult* g_host_parts = nullptr;
+
+extern "C" int ufe_b200_mg_host_transfer_parts(int nparts, int n_total, const int32_t* n, const int32_t* off, const int32_t* sp_start,
+                                               const int32_t* col_start, const int32_t* slice_ptr, const int32_t* col, int* nc,
+                                               long long* coarse_slots, long long* gather_entries) {
+  using namespace ufe;
+  UFE_CHECK(nparts > 0 && n && off && sp_start && col_start && slice_ptr && col, "ufe_b200_mg_host_transfer_parts: NULL argument");
+  std::vector<HostLevel> F(nparts);
+  std::vector<LocalAgg> A(nparts);
+  std::vector<int> offset(nparts + 1, 0);
+  for (int p = 0; p < nparts; ++p) {
+    F[p].n = n[p]; F[p].off = off[p];
+    const int nsl = (n[p] + 31) / 32;
+    F[p].slice_ptr.assign(slice_ptr + sp_start[p], slice_ptr + sp_start[p] + nsl + 1);
+    F[p].col.assign(col + col_start[p], col + col_start[p] + (size_t)F[p].slice_ptr[nsl] * 32);
+    aggregate_part(F[p], A[p]);
+    offset[p + 1] = offset[p] + A[p].nc_loc;
+  }
+  const int nc_glob = offset[nparts];
+  delete g_host_parts;
+  g_host_parts = new HostPartsResult();
+  HostPartsResult& Rs = *g_host_parts;
+  Rs.agg_glob.assign(n_total, -1);
+  for (int p = 0; p < nparts; ++p)
+    for (int i = 0; i < n[p]; ++i) Rs.agg_glob[off[p] + i] = offset[p] + A[p].agg[i];
+  std::vector<LocalRows> R(nparts);
+  std::vector<int> all_lens, all_cols, cptr;
+  for (int p = 0; p < nparts; ++p) {
+    build_local_rows(F[p], A[p], Rs.agg_glob, offset[p], nc_glob, R[p]);
+    for (int I = 0; I < A[p].nc_loc; ++I) all_lens.push_back(R[p].cptr[I + 1] - R[p].cptr[I]);
+    all_cols.insert(all_cols.end(), R[p].ccol.begin(), R[p].ccol.end());
+  }
+  rows_from_parts(all_lens, cptr);
+  ell_from_rows(nc_glob, cptr, all_cols, Rs.coarse);
+  for (int p = 0; p < nparts; ++p) {
+    std::vector<int> gp, gs;
+    build_gather(F[p], A[p], offset[p], R[p], Rs.coarse, gp, gs);
+    Rs.gal_src_start.push_back((int)Rs.gal_src.size());
+    Rs.gal_ptr.insert(Rs.gal_ptr.end(), gp.begin(), gp.end());
+    Rs.gal_src.insert(Rs.gal_src.end(), gs.begin(), gs.end());
+  }
+  Rs.gal_src_start.push_back((int)Rs.gal_src.size());
+  if (nc) *nc = nc_glob;
+  if (coarse_slots) *coarse_slots = (long long)Rs.coarse.col.size();
+  if (gather_entries) *gather_entries = (long long)Rs.gal_src.size();
+  return 0;
+}
+
+extern "C" int ufe_b200_mg_host_transfer_parts_get(int32_t* agg_glob, int32_t* coarse_slice_ptr, int32_t* coarse_col, int32_t* gal_ptr, int32_t* gal_src,
+                                                   int32_t* gal_src_start) {
+  using namespace ufe;
+  UFE_CHECK(g_host_parts != nullptr, "ufe_b200_mg_host_transfer_parts_get: call ufe_b200_mg_host_transfer_parts first");
+  const HostPartsResult& T = *g_host_parts;
+  auto copy = [](int32_t* dst, const std::vector<int>& v) { if (dst && !v.empty()) std::memcpy(dst, v.data(), sizeof(int) * v.size()); };
+  copy(agg_glob, T.agg_glob); copy(coarse_slice_ptr, T.coarse.slice_ptr); copy(coarse_col, T.coarse.col); copy(gal_ptr, T.gal_ptr);
+  copy(gal_src, T.gal_src); copy(gal_src_start, T.gal_src_start);
+  delete g_host_parts;
+  g_host_parts = nullptr;
   return 0;
 }

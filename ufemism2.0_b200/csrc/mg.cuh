@@ -15,8 +15,11 @@
 //     dense inverse (Gauss-Jordan on the device) on the coarsest level;
 //   * optional FP32 storage of the matrix values inside the preconditioner (the outer BiCGStab, its residuals and the convergence
 //     test stay FP64, so the solution meets the same tolerance).
-// Multi-GPU: aggregates never cross ranks and couplings to halo triangles are dropped inside the preconditioner, i.e. the
-// preconditioner is block-diagonal over ranks exactly like PETSc's default block-Jacobi; the Krylov SpMV keeps its halo exchange.
+// Multi-GPU: level 0 is the rank's row block (smoothing sweeps exchange halos like the Krylov SpMV); aggregates never cross ranks, but the
+// coarse levels are global: every rank coarsens its own block, the coarse block rows are all-gathered once per pattern, and levels >= 1 are
+// replicated -- each rank restricts its residual into its slice of the level-1 right-hand side, one all-reduce completes it, and every rank
+// runs the same (latency-bound, graph-replayed) coarse correction redundantly.  Level-1 values are completed by one all-reduce per
+// viscosity iteration.  The iteration count therefore does not depend on the number of ranks beyond the aggregate boundaries.
 #pragma once
 #include "blk.cuh"
 #include "common.cuh"
@@ -36,8 +39,9 @@ struct MgLevel {
   DBuf<float> valf;                       // FP32 copy (fp32 = 1)
   DBuf<double> dblk;                      // [n][4] omega * inverse of the diagonal 2x2 block
   // transfer to the next coarser level
-  int nc = 0;
-  DBuf<int> agg;                          // [n] coarse node of each node
+  int nc = 0;                             // nodes of the next level (all ranks)
+  int nc_loc = 0, c_offset = 0;           // this rank's aggregates are the coarse nodes c_offset .. c_offset + nc_loc - 1 (level 0 only; else all)
+  DBuf<int> agg;                          // [n] coarse node (global id) of each node
   DBuf<int> mem_ptr, mem;                 // coarse node -> member nodes
   DBuf<int> gal_ptr, gal_src;             // coarse block slot -> fine block slots
   // work vectors (2 doubles per node)
@@ -56,6 +60,8 @@ struct Mg {
   DBuf<double> dense_w, dense_inv;        // Gauss-Jordan workspace [N][2N], inverse (column-major) [N][N]
   int dense_n = 0;                        // unknowns of the dense coarsest solve (0: smoothing only)
   MgParams p;
+  bool distributed = false;               // nranks > 1: level 0 is this rank's row block, levels >= 1 are replicated on every rank
+  Range rb;                               // triangle range of level 0 (halo exchange of the level-0 iterates)
   // the coarse-grid correction (every launch on levels >= 1) captured once as a CUDA graph and replayed per cycle
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t graph_exec = nullptr;
@@ -66,7 +72,7 @@ struct Mg {
 };
 
 // pattern phase (once per stiffness pattern); B is the level-0 matrix the Krylov solver streams
-int mg_build(Ctx* c, Mg& G, const BlkMat& B, int off_tri, int n_ext_tri);
+int mg_build(Ctx* c, Mg& G, const BlkMat& B, const Range& rb);
 // numeric phase (every viscosity iteration, after blk_update_values)
 int mg_update_values(Ctx* c, Mg& G, const BlkMat& B, const DevCsr& A);
 // z = M^-1 r for owned rows (r, z: 2 doubles per owned triangle)

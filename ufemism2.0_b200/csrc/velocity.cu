@@ -582,7 +582,7 @@ static int solve_linear_system(Ctx* c, const ufe_b200_config* cfg, double rtol, 
   UFE_CHECK(kp.ksp_type == UFE_KSP_BICGSTAB, "only BiCGStab is available for the (non-symmetric) stiffness matrix");
   if (kp.pc_type == UFE_PC_MG) {
     Mesh& M = *c->mesh;
-    if (!V.mg.valid) { V.mg.p = c->mg_params; UFE_TRY(mg_build(c, V.mg, V.blk, M.b.off(), M.b.n_ext())); }
+    if (!V.mg.valid) { V.mg.p = c->mg_params; UFE_TRY(mg_build(c, V.mg, V.blk, M.b)); }
     UFE_TRY(blk_update_values(c, V.blk, V.A));
     UFE_TRY(mg_update_values(c, V.mg, V.blk, V.A));
     return bicgstab_solve_mg(c, V.mg, BlkLauncher{&V.blk, M.b.off()}, V.A.cols, V.bb.p, V.uv.p, kp, its);

@@ -173,6 +173,8 @@ def lib():
     L.ufe_b200_get_mg_info.argtypes = [H, C.POINTER(C.c_int), c_ip, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), c_dp]
     L.ufe_b200_mg_host_transfer.argtypes = [C.c_int, C.c_int, c_ip, c_ip, C.POINTER(C.c_int), C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
     L.ufe_b200_mg_host_transfer_get.argtypes = [c_ip] * 5
+    L.ufe_b200_mg_host_transfer_parts.argtypes = [C.c_int, C.c_int] + [c_ip] * 6 + [C.POINTER(C.c_int), C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
+    L.ufe_b200_mg_host_transfer_parts_get.argtypes = [c_ip] * 6
     for fn in (L.ufe_b200_solve_DIVA, L.ufe_b200_solve_SSA):
         fn.argtypes = [H, C.POINTER(Config), C.POINTER(IceInputs), C.POINTER(VelocityState), C.POINTER(C.c_int),
                        C.POINTER(C.c_int), c_ip, c_dp, c_dp]
@@ -204,7 +206,7 @@ ABI_SYMBOLS = [
     "ufe_b200_csr_release", "ufe_b200_mesh_create", "ufe_b200_mesh_destroy", "ufe_b200_mesh_ranges",
     "ufe_b200_calc_matrix_operators", "ufe_b200_set_operator", "ufe_b200_get_operator_size", "ufe_b200_get_operator",
     "ufe_b200_apply_operator", "ufe_b200_solve_SSA_DIVA_linearised", "ufe_b200_get_stiffness_size", "ufe_b200_get_stiffness", "ufe_b200_get_stiffness_storage_bytes",
-    "ufe_b200_set_mg_params", "ufe_b200_get_mg_info", "ufe_b200_mg_host_transfer", "ufe_b200_mg_host_transfer_get",
+    "ufe_b200_set_mg_params", "ufe_b200_get_mg_info", "ufe_b200_mg_host_transfer", "ufe_b200_mg_host_transfer_get", "ufe_b200_mg_host_transfer_parts", "ufe_b200_mg_host_transfer_parts_get",
     "ufe_b200_solve_DIVA", "ufe_b200_solve_SSA", "ufe_b200_velocity_upload", "ufe_b200_velocity_solve_resident",
     "ufe_b200_velocity_download", "ufe_b200_thickness_upload", "ufe_b200_pc_step_resident", "ufe_b200_pc_step",
     "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA",
