@@ -106,7 +106,8 @@ struct MgParams {
   int coarse_sweeps = 8;
   int max_levels = 12;
   int fp32 = 0;                  // 1: matrix values of the preconditioner stored as float
-  int use_graph = 1;             // replay the coarse-grid correction (levels >= 1) as one CUDA graph
+  int use_graph = 1;             // coarse-grid correction (levels >= 1): 0 plain launches, 1 one CUDA graph (default), 2 one persistent
+                                 // cooperative kernel (measured slower than the graph on B200: profiles/r01_mg_probe_modes.log)
 };
 
 struct Ctx {

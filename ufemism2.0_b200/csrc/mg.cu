@@ -5,6 +5,8 @@
 #include <chrono>
 #include <cstdlib>
 
+#include <cooperative_groups.h>
+
 #include "krylov_impl.cuh"
 
 namespace ufe {
@@ -291,18 +293,21 @@ int build_transfer_distributed(Ctx* c, const HostLevel& F, const Range& rb, Host
 // device kernels
 // =====================================================================================================================
 
+// Every cycle operation is a __device__ function over (block id, number of blocks), so that the same code runs as a stand-alone kernel
+// (level 0, and levels >= 1 in launch / graph mode) and as one step of the persistent coarse-level program (k_mg_program).
+
 // MODE 0: out = x + Dw (b - A x)   (damped block-Jacobi sweep; Dw = omega * inverse diagonal block)
 // MODE 1: out = b - A x            (residual)
 // x_ext: iterate over the extended range (node t at x2[off + t]); out, b: node t at [t]
 template <typename VT, int MODE>
-__global__ void __launch_bounds__(kBlock) k_mg_sweep(int n, int off, const int* __restrict__ slice_ptr, const int* __restrict__ col,
-                                                     const VT* __restrict__ val, const double* __restrict__ x_ext, const double* __restrict__ b,
-                                                     const double* __restrict__ dblk, double* __restrict__ out) {
+__device__ __forceinline__ void d_mg_sweep(int n, int off, const int* __restrict__ slice_ptr, const int* __restrict__ col, const VT* __restrict__ val,
+                                           const double* __restrict__ x_ext, const double* __restrict__ b, const double* __restrict__ dblk,
+                                           double* __restrict__ out, int bid, int nb) {
   const int lane = threadIdx.x & 31;
   const int warps_per_block = kBlock / 32;
   const int n_slices = (n + 31) >> 5;
   const double2* __restrict__ x2 = reinterpret_cast<const double2*>(x_ext);
-  for (int s = blockIdx.x * warps_per_block + (threadIdx.x >> 5); s < n_slices; s += gridDim.x * warps_per_block) {
+  for (int s = bid * warps_per_block + (threadIdx.x >> 5); s < n_slices; s += nb * warps_per_block) {
     const int t = (s << 5) + lane;
     const int k0 = slice_ptr[s], k1 = slice_ptr[s + 1];
     double yu = 0.0, yv = 0.0;
@@ -329,19 +334,29 @@ __global__ void __launch_bounds__(kBlock) k_mg_sweep(int n, int off, const int* 
     }
   }
 }
+template <typename VT, int MODE>
+__global__ void __launch_bounds__(kBlock) k_mg_sweep(int n, int off, const int* __restrict__ slice_ptr, const int* __restrict__ col,
+                                                     const VT* __restrict__ val, const double* __restrict__ x_ext, const double* __restrict__ b,
+                                                     const double* __restrict__ dblk, double* __restrict__ out) {
+  d_mg_sweep<VT, MODE>(n, off, slice_ptr, col, val, x_ext, b, dblk, out, blockIdx.x, gridDim.x);
+}
 
 // x = Dw b  (first sweep from a zero iterate)
-__global__ void k_mg_smooth0(int n, const double* __restrict__ b, const double* __restrict__ dblk, double* __restrict__ x_own) {
-  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+__device__ __forceinline__ void d_mg_smooth0(int n, const double* __restrict__ b, const double* __restrict__ dblk, double* __restrict__ x_own, int bid, int nb) {
+  for (int t = bid * blockDim.x + threadIdx.x; t < n; t += nb * blockDim.x) {
     const double2 bv = reinterpret_cast<const double2*>(b)[t];
     const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
     reinterpret_cast<double2*>(x_own)[t] = make_double2(d01.x * bv.x + d01.y * bv.y, d23.x * bv.x + d23.y * bv.y);
   }
 }
+__global__ void k_mg_smooth0(int n, const double* __restrict__ b, const double* __restrict__ dblk, double* __restrict__ x_own) {
+  d_mg_smooth0(n, b, dblk, x_own, blockIdx.x, gridDim.x);
+}
 
 // bc_I = sum of r over the members of aggregate I (fixed order)
-__global__ void k_mg_restrict(int nc, const int* __restrict__ mem_ptr, const int* __restrict__ mem, const double* __restrict__ r, double* __restrict__ bc) {
-  for (int I = blockIdx.x * blockDim.x + threadIdx.x; I < nc; I += gridDim.x * blockDim.x) {
+__device__ __forceinline__ void d_mg_restrict(int nc, const int* __restrict__ mem_ptr, const int* __restrict__ mem, const double* __restrict__ r,
+                                              double* __restrict__ bc, int bid, int nb) {
+  for (int I = bid * blockDim.x + threadIdx.x; I < nc; I += nb * blockDim.x) {
     double su = 0.0, sv = 0.0;
     for (int k = mem_ptr[I]; k < mem_ptr[I + 1]; ++k) {
       const double2 v = reinterpret_cast<const double2*>(r)[mem[k]];
@@ -350,20 +365,28 @@ __global__ void k_mg_restrict(int nc, const int* __restrict__ mem_ptr, const int
     reinterpret_cast<double2*>(bc)[I] = make_double2(su, sv);
   }
 }
+__global__ void k_mg_restrict(int nc, const int* __restrict__ mem_ptr, const int* __restrict__ mem, const double* __restrict__ r, double* __restrict__ bc) {
+  d_mg_restrict(nc, mem_ptr, mem, r, bc, blockIdx.x, gridDim.x);
+}
 
 // x_i += w * ec_agg(i)
-__global__ void k_mg_prolong(int n, const int* __restrict__ agg, const double* __restrict__ ec, double w, double* __restrict__ x_own) {
-  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+__device__ __forceinline__ void d_mg_prolong(int n, const int* __restrict__ agg, const double* __restrict__ ec, double w, double* __restrict__ x_own,
+                                             int bid, int nb) {
+  for (int t = bid * blockDim.x + threadIdx.x; t < n; t += nb * blockDim.x) {
     const double2 e = reinterpret_cast<const double2*>(ec)[agg[t]];
     double2 x = reinterpret_cast<double2*>(x_own)[t];
     x.x += w * e.x; x.y += w * e.y;
     reinterpret_cast<double2*>(x_own)[t] = x;
   }
 }
-
-__global__ void k_mg_axpy(int n2, const double* __restrict__ a, double* __restrict__ y) {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += gridDim.x * blockDim.x) y[i] += a[i];
+__global__ void k_mg_prolong(int n, const int* __restrict__ agg, const double* __restrict__ ec, double w, double* __restrict__ x_own) {
+  d_mg_prolong(n, agg, ec, w, x_own, blockIdx.x, gridDim.x);
 }
+
+__device__ __forceinline__ void d_mg_axpy(int n2, const double* __restrict__ a, double* __restrict__ y, int bid, int nb) {
+  for (int i = bid * blockDim.x + threadIdx.x; i < n2; i += nb * blockDim.x) y[i] += a[i];
+}
+__global__ void k_mg_axpy(int n2, const double* __restrict__ a, double* __restrict__ y) { d_mg_axpy(n2, a, y, blockIdx.x, gridDim.x); }
 
 // coarse block values: sum of the fine blocks listed for the slot
 template <typename VTI, typename VTO>
@@ -488,15 +511,45 @@ __global__ void __launch_bounds__(1024) k_mg_dense_invert(int N, double* __restr
   }
 }
 
-// x = A^-1 b on the coarsest level (one block)
-__global__ void __launch_bounds__(1024) k_mg_dense_solve(int N, const double* __restrict__ inv, const double* __restrict__ b, double* __restrict__ x) {
-  extern __shared__ double sb[];
+// x = A^-1 b on the coarsest level (one block; sb: N doubles of shared memory)
+__device__ __forceinline__ void d_mg_dense_solve(int N, const double* __restrict__ inv, const double* __restrict__ b, double* __restrict__ x, double* sb) {
   for (int j = threadIdx.x; j < N; j += blockDim.x) sb[j] = b[j];
   __syncthreads();
   for (int i = threadIdx.x; i < N; i += blockDim.x) {
     double s = 0.0;
     for (int j = 0; j < N; ++j) s += inv[(size_t)j * N + i] * sb[j];
     x[i] = s;
+  }
+}
+__global__ void __launch_bounds__(1024) k_mg_dense_solve(int N, const double* __restrict__ inv, const double* __restrict__ b, double* __restrict__ x) {
+  extern __shared__ double sb[];
+  d_mg_dense_solve(N, inv, b, x, sb);
+}
+
+// ---- the coarse-grid correction as ONE persistent cooperative kernel ------------------------------------------------------------------
+// Levels >= 1 are a fixed sequence of ~170 small dependent operations per cycle (W-cycle on top, V below): a few microseconds of work each,
+// so stream launches and even CUDA-graph nodes are dominated by launch/drain latency.  k_mg_program keeps one grid resident (a few CTAs per
+// SM, cooperative launch) and walks the recorded step list, separating steps by a grid-wide barrier instead of a kernel boundary.
+// Measured on B200 at 4 M vertices (profiles/r01_mg_probe_modes.log): 0.91 ms per cycle with 4 CTAs/SM, 0.98 with 2, 1.27 with 1, against
+// 0.74 ms for the CUDA graph -- cooperative_groups' grid.sync() across 148 SMs on two dies costs more than a graph-node boundary.  The graph
+// stays the default (MgParams::use_graph = 1); this path is kept selectable (UFE_B200_MG_GRAPH=2) and is covered by the same tests.
+template <typename VT>
+__global__ void __launch_bounds__(kBlock) k_mg_program(const MgStep* __restrict__ steps, int nsteps) {
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  __shared__ double sb[2 * 128];   // dense coarsest solve: at most 128 nodes (MgParams::dense_max)
+  const int bid = blockIdx.x, nb = gridDim.x;
+  for (int s = 0; s < nsteps; ++s) {
+    const MgStep st = steps[s];
+    switch (st.op) {
+      case MG_OP_SMOOTH0: d_mg_smooth0(st.n, st.b, st.d, st.out, bid, nb); break;
+      case MG_OP_SWEEP: d_mg_sweep<VT, 0>(st.n, st.off, st.ip0, st.ip1, static_cast<const VT*>(st.val), st.x, st.b, st.d, st.out, bid, nb); break;
+      case MG_OP_RESID: d_mg_sweep<VT, 1>(st.n, st.off, st.ip0, st.ip1, static_cast<const VT*>(st.val), st.x, st.b, st.d, st.out, bid, nb); break;
+      case MG_OP_RESTRICT: d_mg_restrict(st.n, st.ip0, st.ip1, st.x, st.out, bid, nb); break;
+      case MG_OP_PROLONG: d_mg_prolong(st.n, st.ip0, st.x, st.w, st.out, bid, nb); break;
+      case MG_OP_AXPY: d_mg_axpy(st.n, st.x, st.out, bid, nb); break;
+      case MG_OP_DENSE: if (bid == 0) d_mg_dense_solve(st.n, static_cast<const double*>(st.val), st.b, st.out, sb); break;
+    }
+    if (s + 1 < nsteps) grid.sync();
   }
 }
 
@@ -555,11 +608,41 @@ const double* level_values<double>(const MgLevel& L) { return L.val; }
 template <>
 const float* level_values<float>(const MgLevel& L) { return L.valf.p; }
 
+// Host side of the cycle operations: launch the kernel, or -- while the coarse-level program is being recorded -- append a step.
 template <typename VT, int MODE>
-void launch_sweep(Ctx* c, const MgLevel& L, int level, const double* x_ext, const double* b, double* out) {
+void launch_sweep(Ctx* c, Mg& G, const MgLevel& L, int level, const double* x_ext, const double* b, double* out) {
+  if (G.rec) {
+    G.rec->push_back(MgStep{MODE == 0 ? MG_OP_SWEEP : MG_OP_RESID, L.n, L.off, 0, L.slice_ptr, L.col, level_values<VT>(L), x_ext, b, L.dblk.p, out, 0.0});
+    return;
+  }
   const int grid = grid_for(c, (long long)L.n_slices * 32, kBlock);
   UFE_LAUNCH(c, level == 0 ? TC_MG_FINE : TC_MG_COARSE);
   k_mg_sweep<VT, MODE><<<grid, kBlock, 0, c->stream>>>(L.n, L.off, L.slice_ptr, L.col, level_values<VT>(L), x_ext, b, L.dblk.p, out);
+}
+inline void op_smooth0(Ctx* c, Mg& G, int level, int n, const double* b, const double* dblk, double* x_own) {
+  if (G.rec) { G.rec->push_back(MgStep{MG_OP_SMOOTH0, n, 0, 0, nullptr, nullptr, nullptr, nullptr, b, dblk, x_own, 0.0}); return; }
+  UFE_LAUNCH(c, level == 0 ? TC_MG_VEC : TC_MG_COARSE);
+  k_mg_smooth0<<<grid_for(c, n, kBlock), kBlock, 0, c->stream>>>(n, b, dblk, x_own);
+}
+inline void op_restrict(Ctx* c, Mg& G, int level, int nc, const int* mem_ptr, const int* mem, const double* r, double* bc) {
+  if (G.rec) { G.rec->push_back(MgStep{MG_OP_RESTRICT, nc, 0, 0, mem_ptr, mem, nullptr, r, nullptr, nullptr, bc, 0.0}); return; }
+  UFE_LAUNCH(c, level == 0 ? TC_MG_VEC : TC_MG_COARSE);
+  k_mg_restrict<<<grid_for(c, nc, kBlock), kBlock, 0, c->stream>>>(nc, mem_ptr, mem, r, bc);
+}
+inline void op_prolong(Ctx* c, Mg& G, int level, int n, const int* agg, const double* ec, double w, double* x_own) {
+  if (G.rec) { G.rec->push_back(MgStep{MG_OP_PROLONG, n, 0, 0, agg, nullptr, nullptr, ec, nullptr, nullptr, x_own, w}); return; }
+  UFE_LAUNCH(c, level == 0 ? TC_MG_VEC : TC_MG_COARSE);
+  k_mg_prolong<<<grid_for(c, n, kBlock), kBlock, 0, c->stream>>>(n, agg, ec, w, x_own);
+}
+inline void op_axpy(Ctx* c, Mg& G, int n2, const double* a, double* y) {
+  if (G.rec) { G.rec->push_back(MgStep{MG_OP_AXPY, n2, 0, 0, nullptr, nullptr, nullptr, a, nullptr, nullptr, y, 0.0}); return; }
+  UFE_LAUNCH(c, TC_MG_COARSE);
+  k_mg_axpy<<<grid_for(c, n2, kBlock), kBlock, 0, c->stream>>>(n2, a, y);
+}
+inline void op_dense(Ctx* c, Mg& G, const double* b, double* x) {
+  if (G.rec) { G.rec->push_back(MgStep{MG_OP_DENSE, G.dense_n, 0, 0, nullptr, nullptr, G.dense_inv.p, nullptr, b, nullptr, x, 0.0}); return; }
+  UFE_LAUNCH(c, TC_MG_COARSE);
+  k_mg_dense_solve<<<1, std::min(1024, ((G.dense_n + 31) / 32) * 32), sizeof(double) * G.dense_n, c->stream>>>(G.dense_n, G.dense_inv.p, b, x);
 }
 
 template <typename VT>
@@ -572,10 +655,9 @@ int mg_coarse_correction(Ctx* c, Mg& G, int l) {
   const int last = (int)G.lv.size() - 1;
   UFE_TRY(mg_cycle<VT>(c, G, l + 1, Cn.b.p, Cn.sol.p));
   if (l + 1 < last && l + 1 <= G.p.w_levels) {   // e += cycle(b_c - A_c e)
-    launch_sweep<VT, 1>(c, Cn, l + 1, Cn.sol.p, Cn.b.p, Cn.b2.p);
+    launch_sweep<VT, 1>(c, G, Cn, l + 1, Cn.sol.p, Cn.b.p, Cn.b2.p);
     UFE_TRY(mg_cycle<VT>(c, G, l + 1, Cn.b2.p, Cn.sol2.p));
-    UFE_LAUNCH(c, TC_MG_COARSE);
-    k_mg_axpy<<<grid_for(c, 2 * Cn.n, kBlock), kBlock, 0, c->stream>>>(2 * Cn.n, Cn.sol2.p, Cn.sol.p);
+    op_axpy(c, G, 2 * Cn.n, Cn.sol2.p, Cn.sol.p);
   }
   return 0;
 }
@@ -590,6 +672,33 @@ int mg_coarse_from_fine(Ctx* c, Mg& G) {
   int rc = 0;
   if (!G.p.use_graph) {
     rc = mg_coarse_correction<VT>(c, G, 0);
+  } else if (G.p.use_graph == 2) {   // one persistent cooperative kernel walks the recorded step list
+    if (G.program_n == 0) {
+      std::vector<MgStep> steps;
+      G.rec = &steps;
+      rc = mg_coarse_correction<VT>(c, G, 0);
+      G.rec = nullptr;
+      int occ = 0;
+      cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_mg_program<VT>, kBlock, 0);
+      if (rc == 0 && (e != cudaSuccess || occ < 1)) { set_error("multigrid: persistent coarse kernel cannot be made resident (%s)", cudaGetErrorString(e)); rc = 1; }
+      if (rc == 0) {
+        int bps = 2;
+        if (const char* ev = getenv("UFE_B200_MG_BPS")) bps = atoi(ev);
+        G.program_grid = c->sm_count * std::max(1, std::min(occ, bps));
+        if (G.program.alloc(steps.size() * sizeof(MgStep)) != 0) rc = 1;
+        else if (cudaMemcpyAsync(G.program.p, steps.data(), steps.size() * sizeof(MgStep), cudaMemcpyHostToDevice, st) != cudaSuccess ||
+                 cudaStreamSynchronize(st) != cudaSuccess) { set_error("multigrid: upload of the coarse-level program failed"); rc = 1; }
+        else G.program_n = (int)steps.size();
+      }
+    }
+    if (rc == 0) {
+      const MgStep* d_steps = reinterpret_cast<const MgStep*>(G.program.p);
+      int nsteps = G.program_n;
+      void* args[] = {(void*)&d_steps, (void*)&nsteps};
+      cudaError_t e = cudaLaunchCooperativeKernel((void*)k_mg_program<VT>, dim3(G.program_grid), dim3(kBlock), args, 0, st);
+      c->launches += 1;
+      if (e != cudaSuccess) { set_error("multigrid: cooperative launch of the coarse-level program failed: %s", cudaGetErrorString(e)); rc = 1; }
+    }
   } else {
     if (!G.graph_exec) {
       const long long l0 = c->launches;
@@ -624,49 +733,41 @@ int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out) {
   const MgParams& P = G.p;
   cudaStream_t st = c->stream;
   const int last = (int)G.lv.size() - 1;
-  const int gv = grid_for(c, L.n, kBlock);
   double* xa = L.xa.p;
   double* xb = L.xb.p;
   if (l == last) {
     if (G.dense_n > 0) {
-      UFE_LAUNCH(c, TC_MG_COARSE);
-      k_mg_dense_solve<<<1, std::min(1024, ((G.dense_n + 31) / 32) * 32), sizeof(double) * G.dense_n, st>>>(G.dense_n, G.dense_inv.p, b, out);
+      op_dense(c, G, b, out);
       return 0;
     }
-    { UFE_LAUNCH(c, TC_MG_COARSE); k_mg_smooth0<<<gv, kBlock, 0, st>>>(L.n, b, L.dblk.p, xa + 2 * L.off); }
+    op_smooth0(c, G, l, L.n, b, L.dblk.p, xa + 2 * L.off);
     for (int s = 0; s < P.coarse_sweeps; ++s) {
       double* dst = (s == P.coarse_sweeps - 1) ? out : xb + 2 * L.off;
-      launch_sweep<VT, 0>(c, L, l, xa, b, dst);
+      launch_sweep<VT, 0>(c, G, L, l, xa, b, dst);
       std::swap(xa, xb);
     }
     return 0;
   }
   MgLevel& Cn = G.lv[l + 1];
   const bool split = l == 0 && G.distributed;   // level 0 is a row block: its iterates need the neighbours' halo before every matrix pass
-  { UFE_LAUNCH(c, l == 0 ? TC_MG_VEC : TC_MG_COARSE); k_mg_smooth0<<<gv, kBlock, 0, st>>>(L.n, b, L.dblk.p, xa + 2 * L.off); }
+  op_smooth0(c, G, l, L.n, b, L.dblk.p, xa + 2 * L.off);
   for (int s = 1; s < P.nu_pre; ++s) {
     if (split) UFE_TRY(halo_exchange(c, G.rb, xa, 1, 2));
-    launch_sweep<VT, 0>(c, L, l, xa, b, xb + 2 * L.off);
+    launch_sweep<VT, 0>(c, G, L, l, xa, b, xb + 2 * L.off);
     std::swap(xa, xb);
   }
   if (split) UFE_TRY(halo_exchange(c, G.rb, xa, 1, 2));
-  launch_sweep<VT, 1>(c, L, l, xa, b, L.r.p);
+  launch_sweep<VT, 1>(c, G, L, l, xa, b, L.r.p);
   if (split) UFE_CUDA(cudaMemsetAsync(Cn.b.p, 0, sizeof(double) * 2 * (size_t)Cn.n, st));
-  {
-    UFE_LAUNCH(c, l == 0 ? TC_MG_VEC : TC_MG_COARSE);
-    k_mg_restrict<<<grid_for(c, L.nc_loc, kBlock), kBlock, 0, st>>>(L.nc_loc, L.mem_ptr.p, L.mem.p, L.r.p, Cn.b.p + 2 * (size_t)L.c_offset);
-  }
+  op_restrict(c, G, l, L.nc_loc, L.mem_ptr.p, L.mem.p, L.r.p, Cn.b.p + 2 * (size_t)L.c_offset);
   if (split) UFE_TRY(allreduce_sum_large(c, Cn.b.p, 2 * (size_t)Cn.n, false));   // every rank now holds the whole level-1 right-hand side
   if (l == 0) UFE_TRY(mg_coarse_from_fine<VT>(c, G));
   else UFE_TRY(mg_coarse_correction<VT>(c, G, l));
-  {
-    UFE_LAUNCH(c, l == 0 ? TC_MG_VEC : TC_MG_COARSE);
-    k_mg_prolong<<<gv, kBlock, 0, st>>>(L.n, L.agg.p, Cn.sol.p, P.overcorr, xa + 2 * L.off);
-  }
+  op_prolong(c, G, l, L.n, L.agg.p, Cn.sol.p, P.overcorr, xa + 2 * L.off);
   for (int s = 0; s < P.nu_post; ++s) {
     double* dst = (s == P.nu_post - 1) ? out : xb + 2 * L.off;
     if (split) UFE_TRY(halo_exchange(c, G.rb, xa, 1, 2));
-    launch_sweep<VT, 0>(c, L, l, xa, b, dst);
+    launch_sweep<VT, 0>(c, G, L, l, xa, b, dst);
     std::swap(xa, xb);
   }
   return 0;

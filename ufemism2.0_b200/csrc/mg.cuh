@@ -26,6 +26,20 @@
 
 namespace ufe {
 
+// one step of the recorded coarse-level program (mg.cu: k_mg_program)
+enum MgOp { MG_OP_SMOOTH0 = 0, MG_OP_SWEEP = 1, MG_OP_RESID = 2, MG_OP_RESTRICT = 3, MG_OP_PROLONG = 4, MG_OP_AXPY = 5, MG_OP_DENSE = 6 };
+struct MgStep {
+  int op, n, off, pad;
+  const int* ip0;      // slice_ptr | mem_ptr | agg
+  const int* ip1;      // col | mem
+  const void* val;     // matrix values | dense inverse
+  const double* x;     // iterate (extended) | residual to restrict | coarse solution | axpy operand
+  const double* b;     // right-hand side
+  const double* d;     // inverse diagonal blocks
+  double* out;
+  double w;
+};
+
 
 struct MgLevel {
   int n = 0, n_ext = 0, off = 0;          // nodes, size of the extended vector (level 0: owned + halo triangles), offset of node 0
@@ -54,7 +68,7 @@ struct Mg {
   void drop_graph() {
     if (graph_exec) cudaGraphExecDestroy(graph_exec);
     if (graph) cudaGraphDestroy(graph);
-    graph_exec = nullptr; graph = nullptr; graph_launches = 0;
+    graph_exec = nullptr; graph = nullptr; graph_launches = 0; program_n = 0;
   }
   std::vector<MgLevel> lv;
   DBuf<double> dense_w, dense_inv;        // Gauss-Jordan workspace [N][2N], inverse (column-major) [N][N]
@@ -66,6 +80,10 @@ struct Mg {
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t graph_exec = nullptr;
   long long graph_launches = 0;
+  // ... or, use_graph = 2, recorded as a step list that one persistent cooperative kernel walks (mg.cu: k_mg_program)
+  std::vector<MgStep>* rec = nullptr;   // non-null while recording
+  DBuf<char> program;
+  int program_n = 0, program_grid = 0;
   bool valid = false;
   long long gather_entries = 0;
   double setup_host_s = 0.0;
