@@ -297,9 +297,12 @@ int ufe_b200_pc_step(ufe_b200_handle h, const ufe_b200_config* cfg, int approxim
                      int* n_visc_its, int* n_Axb_its_velocity, int* n_Axb_its_thickness);
 
 /* ---- SIA (config 4) ------------------------------------------------------------------------------ */
-/* Replaces solve_SIA (src/UFEMISM/ice_dynamics/conservation_of_momentum/SIA/SIA_main.f90:65-158): u_3D_b, v_3D_b (ti1:ti2,nz). */
-int ufe_b200_solve_SIA(ufe_b200_handle h, const ufe_b200_config* cfg, const double* Hi, const double* Hs,
-                       const double* A_flow, double* u_3D_b, double* v_3D_b);
+/* Replaces solve_SIA( mesh, ice, SIA) (src/UFEMISM/ice_dynamics/conservation_of_momentum/SIA/SIA_main.f90:65-158), the analytical SIA
+ * solution with Glen's flow law: in ice%Hi, ice%Hs (vi1:vi2), ice%A_flow (vi1:vi2,nz) after calc_ice_rheology_Glen, C%SIA_maximum_diffusivity
+ * (model_configuration_type_and_namelist.f90:305, default 1e5); out SIA%u_3D_b, SIA%v_3D_b, SIA%D_3D_b (ti1:ti2,nz) and SIA%du_dz_3D, SIA%dv_dz_3D
+ * (vi1:vi2,nz).  NULL outputs are skipped (u_3D_b and v_3D_b are required). */
+int ufe_b200_solve_SIA(ufe_b200_handle h, const ufe_b200_config* cfg, double SIA_maximum_diffusivity, const double* Hi, const double* Hs,
+                       const double* A_flow, double* u_3D_b, double* v_3D_b, double* D_3D_b, double* du_dz_3D_a, double* dv_dz_3D_a);
 
 /* ---- timing hooks for bench.py (CUDA events on the library's own stream) ----------------------- */
 /* Milliseconds spent in the named kernel class since the last reset, and its launch count.

@@ -190,8 +190,8 @@ void orc_Schoof2006_icestream(double A, double n, double H, double dhdx, double 
 
 }  // extern "C"
 
-extern "C" void orc_solve_SIA(void* h, const ufe_b200_config* cfg, const double* Hi, const double* Hs, const double* A_flow,
-                              double* u_3D_b, double* v_3D_b) {
+extern "C" void orc_solve_SIA(void* h, const ufe_b200_config* cfg, double SIA_maximum_diffusivity, const double* Hi, const double* Hs,
+                              const double* A_flow, double* u_3D_b, double* v_3D_b, double* D_3D_b, double* du_dz_3D_a, double* dv_dz_3D_a) {
   auto* o = static_cast<OracleMesh*>(h);
-  solve_SIA(o->mv, o->ops, to_config(cfg), Hi, Hs, A_flow, u_3D_b, v_3D_b);
+  solve_SIA(o->mv, o->ops, to_config(cfg), SIA_maximum_diffusivity, Hi, Hs, A_flow, u_3D_b, v_3D_b, D_3D_b, du_dz_3D_a, dv_dz_3D_a);
 }

@@ -144,8 +144,8 @@ void calc_flux_divergence_matrix_upwind(const MeshView& mesh, const double* u_va
                                         const double* fraction_margin, Csr& M_divQ, std::vector<double>* u_perp = nullptr);
 
 // --- SIA (SIA_main.f90:65-158) and analytic solutions ------------------------------------------------
-void solve_SIA(const MeshView& mesh, const Operators& ops, const Config& C, const double* Hi, const double* Hs,
-               const double* A_flow_3D, double* u_3D_b, double* v_3D_b);
+void solve_SIA(const MeshView& mesh, const Operators& ops, const Config& C, double SIA_maximum_diffusivity, const double* Hi, const double* Hs,
+               const double* A_flow_3D, double* u_3D_b, double* v_3D_b, double* D_3D_b, double* du_dz_3D_a, double* dv_dz_3D_a);
 double Halfar_H(double A, double n, double H0, double R0, double x, double y, double t_yr);
 void Schoof2006_icestream(double A, double n, double H, double dhdx, double L, double m, double y, double* u, double* tauc);
 

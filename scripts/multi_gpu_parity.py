@@ -58,7 +58,7 @@ for pc, name in CASES:
         w.cfg.write_diagnostics = 0
         w.cfg.stress_balance_PETSc_rtol = 1e-11; w.cfg.stress_balance_PETSc_abstol = 1e-30
         w.cfg.dHi_PETSc_rtol = 1e-12; w.cfg.dHi_PETSc_abstol = 1e-30
-        w.cfg.visc_it_norm_dUV_tol = 1e-7
+        w.cfg.visc_it_norm_dUV_tol = 1e-7; w.cfg.visc_it_nit = 12
         return w
     ctx1 = ub.Context(device=local)                                  # alone
     single = run(ctx1, workload(), pc, 2)

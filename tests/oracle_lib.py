@@ -38,7 +38,7 @@ def lib():
         L.orc_Halfar_H.restype = C.c_double
         L.orc_Halfar_H.argtypes = [C.c_double] * 7
         L.orc_Schoof2006_icestream.argtypes = [C.c_double] * 7 + [dp, dp]
-        L.orc_solve_SIA.argtypes = [C.c_void_p, C.POINTER(ub.Config), dp, dp, dp, dp, dp]
+        L.orc_solve_SIA.argtypes = [C.c_void_p, C.POINTER(ub.Config), C.c_double] + [dp] * 8
         _LIB = L
     return _LIB
 
@@ -111,6 +111,15 @@ class OracleMesh:
         its = C.c_int()
         rc = lib().orc_calc_dHi_dt(self.h, C.byref(cfg), ksp, C.byref(io), C.cast(C.byref(d), ub.c_dp), C.byref(its))
         return rc, d.value, its.value
+
+    def solve_SIA(self, cfg, Hi, Hs, A_flow, max_diffusivity=1e5):
+        self.calc_matrix_operators()
+        m = self.m
+        out = dict(u_3D_b=np.zeros((m.nTri, m.nz), order="F"), v_3D_b=np.zeros((m.nTri, m.nz), order="F"), D_3D_b=np.zeros((m.nTri, m.nz), order="F"),
+                   du_dz_3D_a=np.zeros((m.nV, m.nz), order="F"), dv_dz_3D_a=np.zeros((m.nV, m.nz), order="F"))
+        lib().orc_solve_SIA(self.h, C.byref(cfg), max_diffusivity, ub.dp(Hi), ub.dp(Hs), ub.dp(A_flow), *(ub.dp(out[k]) for k in
+                            ("u_3D_b", "v_3D_b", "D_3D_b", "du_dz_3D_a", "dv_dz_3D_a")))
+        return out
 
     def flux_divergence_matrix(self, u_b, v_b, fraction_margin):
         m, nnz = C.c_int(), C.c_int()

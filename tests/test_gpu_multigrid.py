@@ -110,3 +110,25 @@ def test_multigrid_is_deterministic(setup):
     a = _linearised(ctx, cfg, m, *co, 1e-10, 1e-30)
     b = _linearised(ctx, cfg, m, *co, 1e-10, 1e-30)
     assert a[2] == b[2] and np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+@pytest.mark.parametrize("pc", [ub.PC_JACOBI, ub.PC_MG])
+def test_config2_mismip_plus_ssa_on_graded_mesh(pc):
+    """BASELINE.json configs[1]: MISMIP+ bed, SSA, Schoof2005 sliding, resolution graded towards the grounding line"""
+    w = wl.mismip_plus(4.0e3)
+    m = w.mesh
+    ctx = ub.Context(device=0)
+    ctx.mesh_create(m); ctx.calc_matrix_operators()
+    cfg = w.cfg
+    cfg.pc_type = pc
+    cfg.stress_balance_PETSc_rtol = 1e-12; cfg.stress_balance_PETSc_abstol = 1e-30
+    ice = w.ice_inputs()
+    g, nv, na = _solve_gpu(ctx, cfg, 0, ice, m)
+    ctx.close()
+    o = ol.OracleMesh(m)
+    st2, r = ub.alloc_velocity_state(m.nV, m.nTri, m.nz)
+    rc, nv2, na2 = o.solve_velocity(cfg, 0, ice, st2, ksp=ol.KSP_GMRES_ILU0)
+    assert rc == 0 and nv == nv2
+    for f in ("u_vav_b", "v_vav_b", "N_b", "basal_friction_coefficient_b"):
+        assert rel_l2(g[f], r[f]) < 1e-6, (f, rel_l2(g[f], r[f]))
+    assert np.abs(g["u_vav_b"]).max() > 10.0        # a flowing ice stream, not the trivial solution

@@ -991,9 +991,4 @@ int ufe_b200_get_stiffness_storage_bytes(ufe_b200_handle h, long long* csr_bytes
   return 0;
 }
 
-int ufe_b200_solve_SIA(ufe_b200_handle, const ufe_b200_config*, const double*, const double*, const double*, double*, double*) {
-  set_error("solve_SIA: not implemented yet");
-  return 9;
-}
-
 }  // extern "C"

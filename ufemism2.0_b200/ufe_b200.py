@@ -188,7 +188,7 @@ def lib():
     L.ufe_b200_thickness_download.argtypes = [H, c_dp, c_dp, c_dp]
     L.ufe_b200_pc_step.argtypes = [H, C.POINTER(Config), C.c_int, C.c_double, C.c_double, C.POINTER(IceInputs), C.POINTER(VelocityState),
                                    C.POINTER(ThicknessIO), c_dp] + [C.POINTER(C.c_int)] * 3
-    L.ufe_b200_solve_SIA.argtypes = [H, C.POINTER(Config), c_dp, c_dp, c_dp, c_dp, c_dp]
+    L.ufe_b200_solve_SIA.argtypes = [H, C.POINTER(Config), C.c_double] + [c_dp] * 8
     L.ufe_b200_timing_enable.argtypes = [H, C.c_int]
     L.ufe_b200_timing_get.argtypes = [H, C.c_char_p, c_dp, C.POINTER(C.c_longlong)]
     L.ufe_b200_timing_reset.argtypes = [H]
