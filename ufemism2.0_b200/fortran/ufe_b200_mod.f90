@@ -131,6 +131,18 @@ module ufe_b200_mod
       integer(c_int) :: ierr
     end function
 
+    ! solve_SIA (SIA_main.f90:65-158)
+    function c_ufe_b200_solve_SIA( h, cfg, SIA_maximum_diffusivity, Hi, Hs, A_flow, u_3D_b, v_3D_b, D_3D_b, du_dz_3D, dv_dz_3D) &
+      bind(C, name='ufe_b200_solve_SIA') result( ierr)
+      import :: c_int, c_double, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      real(c_double), value :: SIA_maximum_diffusivity
+      real(c_double), intent(in) :: Hi(*), Hs(*), A_flow(*)
+      real(c_double), intent(out) :: u_3D_b(*), v_3D_b(*), D_3D_b(*), du_dz_3D(*), dv_dz_3D(*)
+      integer(c_int) :: ierr
+    end function
+
     ! multigrid preconditioner of the SSA/DIVA solve (C%B200_PC_type_config = 'multigrid' -> cfg%pc_type = 4)
     function c_ufe_b200_set_mg_params( h, nu_pre, nu_post, omega, overcorr, w_levels, fp32, dense_max) &
       bind(C, name='ufe_b200_set_mg_params') result( ierr)
