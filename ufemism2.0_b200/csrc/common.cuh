@@ -105,6 +105,9 @@ struct MgParams {
   int dense_max = 128;           // coarsest level: at most this many nodes -> dense inverse; otherwise `coarse_sweeps` sweeps
   int coarse_sweeps = 8;
   int max_levels = 12;
+  int fuse = 0;                  // 1: fuse neighbouring operations on the coarse levels (3 launches per level visit instead of 5); measured no
+                                 // gain on B200 (the fused kernels have longer dependent-load chains: profiles/r01_mg_probe_fuse.log)
+  int double_from = 0;           // > 0: transfers from this level on aggregate twice (ratio ~60): fewer latency-bound coarse levels
   int fp32 = 0;                  // 1: matrix values of the preconditioner stored as float
   int use_graph = 1;             // coarse-grid correction (levels >= 1): 0 plain launches, 1 one CUDA graph (default), 2 one persistent
                                  // cooperative kernel (measured slower than the graph on B200: profiles/r01_mg_probe_modes.log)

@@ -219,19 +219,36 @@ struct HostTransfer {
   long long coarse_slots = 0;
 };
 
-// single part (one rank, and every level >= 1): the extended range holds nothing but the own nodes' aggregates
-void build_transfer(const HostLevel& F, HostTransfer& T) {
+// single part (one rank, and every level >= 1): the extended range holds nothing but the own nodes' aggregates.
+// passes = 2 aggregates the aggregates once more (coarsening ratio ~60 instead of ~8): fewer, latency-bound coarse levels.
+void build_transfer(const HostLevel& F, HostTransfer& T, int passes = 1) {
   LocalAgg A;
   aggregate_part(F, A);
-  std::vector<int> agg_ext;
-  {
+  auto own_agg_ext = [&](const LocalAgg& a) {
     int n_ext = F.off + F.n;
     for (int v : F.col) n_ext = std::max(n_ext, v + 1);
-    agg_ext.assign(n_ext, -1);                      // halo triangles (other ranks' rows) are dropped
-    for (int i = 0; i < F.n; ++i) agg_ext[F.off + i] = A.agg[i];
+    std::vector<int> e(n_ext, -1);                      // halo triangles (other ranks' rows) are dropped
+    for (int i = 0; i < F.n; ++i) e[F.off + i] = a.agg[i];
+    return e;
+  };
+  for (int pass = 1; pass < passes && A.nc_loc > 1; ++pass) {
+    // pattern of the intermediate level, aggregated again; the two maps are composed and the intermediate level is dropped
+    LocalRows R1;
+    HostLevel C1;
+    build_local_rows(F, A, own_agg_ext(A), 0, A.nc_loc, R1);
+    ell_from_rows(A.nc_loc, R1.cptr, R1.ccol, C1);
+    LocalAgg A2;
+    aggregate_part(C1, A2);
+    for (int i = 0; i < F.n; ++i) A.agg[i] = A2.agg[A.agg[i]];
+    A.nc_loc = A2.nc_loc;
+    A.mem_ptr.assign(A.nc_loc + 1, 0);
+    for (int i = 0; i < F.n; ++i) A.mem_ptr[A.agg[i] + 1]++;
+    for (int I = 0; I < A.nc_loc; ++I) A.mem_ptr[I + 1] += A.mem_ptr[I];
+    std::vector<int> fill(A.mem_ptr.begin(), A.mem_ptr.end() - 1);
+    for (int i = 0; i < F.n; ++i) A.mem[fill[A.agg[i]]++] = i;
   }
   LocalRows R;
-  build_local_rows(F, A, agg_ext, 0, A.nc_loc, R);
+  build_local_rows(F, A, own_agg_ext(A), 0, A.nc_loc, R);
   ell_from_rows(A.nc_loc, R.cptr, R.ccol, T.coarse);
   build_gather(F, A, 0, R, T.coarse, T.gal_ptr, T.gal_src);
   T.nc = T.nc_loc = A.nc_loc; T.offset = 0;
@@ -296,17 +313,22 @@ int build_transfer_distributed(Ctx* c, const HostLevel& F, const Range& rb, Host
 // Every cycle operation is a __device__ function over (block id, number of blocks), so that the same code runs as a stand-alone kernel
 // (level 0, and levels >= 1 in launch / graph mode) and as one step of the persistent coarse-level program (k_mg_program).
 
-// MODE 0: out = x + Dw (b - A x)   (damped block-Jacobi sweep; Dw = omega * inverse diagonal block)
-// MODE 1: out = b - A x            (residual)
-// x_ext: iterate over the extended range (node t at x2[off + t]); out, b: node t at [t]
+// MODE 0: out = x + Dw (b - A x)            (damped block-Jacobi sweep; Dw = omega * inverse diagonal block)
+// MODE 1: out = b - A x                     (residual)
+// MODE 2: out = b - A x, out2 = Dw out      (residual that becomes the right-hand side of a second coarse visit + its first sweep)
+// MODE 3: x' = x + w P e, out = x' + Dw (b - A x')   (coarse-grid correction fused into the first post-smoothing sweep; the
+//         neighbours' corrections are gathered through agg, so the prolongated iterate is never written; coarse levels only)
+// x_ext: iterate over the extended range (node t at x2[off + t]); out, out2, b: node t at [t]
 template <typename VT, int MODE>
 __device__ __forceinline__ void d_mg_sweep(int n, int off, const int* __restrict__ slice_ptr, const int* __restrict__ col, const VT* __restrict__ val,
                                            const double* __restrict__ x_ext, const double* __restrict__ b, const double* __restrict__ dblk,
-                                           double* __restrict__ out, int bid, int nb) {
+                                           double* __restrict__ out, int bid, int nb, double* __restrict__ out2 = nullptr,
+                                           const int* __restrict__ agg = nullptr, const double* __restrict__ ec = nullptr, double w = 0.0) {
   const int lane = threadIdx.x & 31;
-  const int warps_per_block = kBlock / 32;
+  const int warps_per_block = blockDim.x >> 5;
   const int n_slices = (n + 31) >> 5;
   const double2* __restrict__ x2 = reinterpret_cast<const double2*>(x_ext);
+  const double2* __restrict__ e2 = reinterpret_cast<const double2*>(ec);
   for (int s = bid * warps_per_block + (threadIdx.x >> 5); s < n_slices; s += nb * warps_per_block) {
     const int t = (s << 5) + lane;
     const int k0 = slice_ptr[s], k1 = slice_ptr[s + 1];
@@ -317,19 +339,22 @@ __device__ __forceinline__ void d_mg_sweep(int n, int off, const int* __restrict
     for (int k = k0; k < k1; ++k, cp += 32, vp += 128) {
       const int tj = *cp;
       const double a0 = (double)vp[0], a1 = (double)vp[32], a2 = (double)vp[64], a3 = (double)vp[96];
-      const double2 xv = x2[tj];
+      double2 xv = x2[tj];
+      if (MODE == 3) { const double2 ev = e2[agg[tj]]; xv.x += w * ev.x; xv.y += w * ev.y; }
       yu += a0 * xv.x + a1 * xv.y;
       yv += a2 * xv.x + a3 * xv.y;
     }
     if (t < n) {
       const double2 bv = reinterpret_cast<const double2*>(b)[t];
       const double ru = bv.x - yu, rv = bv.y - yv;
-      if (MODE == 1) {
-        reinterpret_cast<double2*>(out)[t] = make_double2(ru, rv);
-      } else {
-        const double2 xo = x2[off + t];
+      if (MODE == 1 || MODE == 2) reinterpret_cast<double2*>(out)[t] = make_double2(ru, rv);
+      if (MODE != 1) {
         const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
-        reinterpret_cast<double2*>(out)[t] = make_double2(xo.x + d01.x * ru + d01.y * rv, xo.y + d23.x * ru + d23.y * rv);
+        double2 xo = make_double2(0.0, 0.0);
+        if (MODE == 0 || MODE == 3) xo = x2[off + t];
+        if (MODE == 3) { const double2 ev = e2[agg[off + t]]; xo.x += w * ev.x; xo.y += w * ev.y; }
+        double* dst = (MODE == 2) ? out2 : out;
+        reinterpret_cast<double2*>(dst)[t] = make_double2(xo.x + d01.x * ru + d01.y * rv, xo.y + d23.x * ru + d23.y * rv);
       }
     }
   }
@@ -337,8 +362,9 @@ __device__ __forceinline__ void d_mg_sweep(int n, int off, const int* __restrict
 template <typename VT, int MODE>
 __global__ void __launch_bounds__(kBlock) k_mg_sweep(int n, int off, const int* __restrict__ slice_ptr, const int* __restrict__ col,
                                                      const VT* __restrict__ val, const double* __restrict__ x_ext, const double* __restrict__ b,
-                                                     const double* __restrict__ dblk, double* __restrict__ out) {
-  d_mg_sweep<VT, MODE>(n, off, slice_ptr, col, val, x_ext, b, dblk, out, blockIdx.x, gridDim.x);
+                                                     const double* __restrict__ dblk, double* __restrict__ out, double* __restrict__ out2,
+                                                     const int* __restrict__ agg, const double* __restrict__ ec, double w) {
+  d_mg_sweep<VT, MODE>(n, off, slice_ptr, col, val, x_ext, b, dblk, out, blockIdx.x, gridDim.x, out2, agg, ec, w);
 }
 
 // x = Dw b  (first sweep from a zero iterate)
@@ -353,9 +379,10 @@ __global__ void k_mg_smooth0(int n, const double* __restrict__ b, const double* 
   d_mg_smooth0(n, b, dblk, x_own, blockIdx.x, gridDim.x);
 }
 
-// bc_I = sum of r over the members of aggregate I (fixed order)
+// bc_I = sum of r over the members of aggregate I (fixed order); with dblk_c also the coarse level's first sweep x_I = Dw_I bc_I
 __device__ __forceinline__ void d_mg_restrict(int nc, const int* __restrict__ mem_ptr, const int* __restrict__ mem, const double* __restrict__ r,
-                                              double* __restrict__ bc, int bid, int nb) {
+                                              double* __restrict__ bc, int bid, int nb, const double* __restrict__ dblk_c = nullptr,
+                                              double* __restrict__ xc = nullptr) {
   for (int I = bid * blockDim.x + threadIdx.x; I < nc; I += nb * blockDim.x) {
     double su = 0.0, sv = 0.0;
     for (int k = mem_ptr[I]; k < mem_ptr[I + 1]; ++k) {
@@ -363,10 +390,15 @@ __device__ __forceinline__ void d_mg_restrict(int nc, const int* __restrict__ me
       su += v.x; sv += v.y;
     }
     reinterpret_cast<double2*>(bc)[I] = make_double2(su, sv);
+    if (dblk_c) {
+      const double2 d01 = reinterpret_cast<const double2*>(dblk_c)[2 * I], d23 = reinterpret_cast<const double2*>(dblk_c)[2 * I + 1];
+      reinterpret_cast<double2*>(xc)[I] = make_double2(d01.x * su + d01.y * sv, d23.x * su + d23.y * sv);
+    }
   }
 }
-__global__ void k_mg_restrict(int nc, const int* __restrict__ mem_ptr, const int* __restrict__ mem, const double* __restrict__ r, double* __restrict__ bc) {
-  d_mg_restrict(nc, mem_ptr, mem, r, bc, blockIdx.x, gridDim.x);
+__global__ void k_mg_restrict(int nc, const int* __restrict__ mem_ptr, const int* __restrict__ mem, const double* __restrict__ r, double* __restrict__ bc,
+                              const double* __restrict__ dblk_c, double* __restrict__ xc) {
+  d_mg_restrict(nc, mem_ptr, mem, r, bc, blockIdx.x, gridDim.x, dblk_c, xc);
 }
 
 // x_i += w * ec_agg(i)
@@ -610,24 +642,26 @@ const float* level_values<float>(const MgLevel& L) { return L.valf.p; }
 
 // Host side of the cycle operations: launch the kernel, or -- while the coarse-level program is being recorded -- append a step.
 template <typename VT, int MODE>
-void launch_sweep(Ctx* c, Mg& G, const MgLevel& L, int level, const double* x_ext, const double* b, double* out) {
-  if (G.rec) {
+void launch_sweep(Ctx* c, Mg& G, const MgLevel& L, int level, const double* x_ext, const double* b, double* out, double* out2 = nullptr,
+                  const int* agg = nullptr, const double* ec = nullptr, double w = 0.0) {
+  if (G.rec) {   // the recorded program only knows the unfused operations (mg_cycle does not fuse while recording)
     G.rec->push_back(MgStep{MODE == 0 ? MG_OP_SWEEP : MG_OP_RESID, L.n, L.off, 0, L.slice_ptr, L.col, level_values<VT>(L), x_ext, b, L.dblk.p, out, 0.0});
     return;
   }
   const int grid = grid_for(c, (long long)L.n_slices * 32, kBlock);
   UFE_LAUNCH(c, level == 0 ? TC_MG_FINE : TC_MG_COARSE);
-  k_mg_sweep<VT, MODE><<<grid, kBlock, 0, c->stream>>>(L.n, L.off, L.slice_ptr, L.col, level_values<VT>(L), x_ext, b, L.dblk.p, out);
+  k_mg_sweep<VT, MODE><<<grid, kBlock, 0, c->stream>>>(L.n, L.off, L.slice_ptr, L.col, level_values<VT>(L), x_ext, b, L.dblk.p, out, out2, agg, ec, w);
 }
 inline void op_smooth0(Ctx* c, Mg& G, int level, int n, const double* b, const double* dblk, double* x_own) {
   if (G.rec) { G.rec->push_back(MgStep{MG_OP_SMOOTH0, n, 0, 0, nullptr, nullptr, nullptr, nullptr, b, dblk, x_own, 0.0}); return; }
   UFE_LAUNCH(c, level == 0 ? TC_MG_VEC : TC_MG_COARSE);
   k_mg_smooth0<<<grid_for(c, n, kBlock), kBlock, 0, c->stream>>>(n, b, dblk, x_own);
 }
-inline void op_restrict(Ctx* c, Mg& G, int level, int nc, const int* mem_ptr, const int* mem, const double* r, double* bc) {
+inline void op_restrict(Ctx* c, Mg& G, int level, int nc, const int* mem_ptr, const int* mem, const double* r, double* bc,
+                        const double* dblk_c = nullptr, double* xc = nullptr) {
   if (G.rec) { G.rec->push_back(MgStep{MG_OP_RESTRICT, nc, 0, 0, mem_ptr, mem, nullptr, r, nullptr, nullptr, bc, 0.0}); return; }
   UFE_LAUNCH(c, level == 0 ? TC_MG_VEC : TC_MG_COARSE);
-  k_mg_restrict<<<grid_for(c, nc, kBlock), kBlock, 0, c->stream>>>(nc, mem_ptr, mem, r, bc);
+  k_mg_restrict<<<grid_for(c, nc, kBlock), kBlock, 0, c->stream>>>(nc, mem_ptr, mem, r, bc, dblk_c, xc);
 }
 inline void op_prolong(Ctx* c, Mg& G, int level, int n, const int* agg, const double* ec, double w, double* x_own) {
   if (G.rec) { G.rec->push_back(MgStep{MG_OP_PROLONG, n, 0, 0, agg, nullptr, nullptr, ec, nullptr, nullptr, x_own, w}); return; }
@@ -646,17 +680,28 @@ inline void op_dense(Ctx* c, Mg& G, const double* b, double* x) {
 }
 
 template <typename VT>
-int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out);
+int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out, bool x1_ready = false);
+
+// Levels >= 1 are latency-bound, so neighbouring operations are fused there whenever the data flow allows (three launches per level visit
+// instead of five): restriction + the coarse level's first sweep, second-visit residual + its first sweep, prolongation + first post-sweep.
+// Not while recording the persistent program (it only knows the unfused operations).
+inline bool mg_fuse(const Mg& G) { return G.p.fuse != 0 && G.rec == nullptr; }
 
 // coarse-grid correction of level l: lv[l+1].sol ~= A_{l+1}^-1 lv[l+1].b, with a second visit on the first w_levels coarse levels
+// (x1_ready: the producer of lv[l+1].b already wrote the first sweep Dw b into lv[l+1].xa)
 template <typename VT>
-int mg_coarse_correction(Ctx* c, Mg& G, int l) {
+int mg_coarse_correction(Ctx* c, Mg& G, int l, bool x1_ready = false) {
   MgLevel& Cn = G.lv[l + 1];
   const int last = (int)G.lv.size() - 1;
-  UFE_TRY(mg_cycle<VT>(c, G, l + 1, Cn.b.p, Cn.sol.p));
+  UFE_TRY(mg_cycle<VT>(c, G, l + 1, Cn.b.p, Cn.sol.p, x1_ready));
   if (l + 1 < last && l + 1 <= G.p.w_levels) {   // e += cycle(b_c - A_c e)
-    launch_sweep<VT, 1>(c, G, Cn, l + 1, Cn.sol.p, Cn.b.p, Cn.b2.p);
-    UFE_TRY(mg_cycle<VT>(c, G, l + 1, Cn.b2.p, Cn.sol2.p));
+    if (mg_fuse(G)) {   // the residual kernel also does the first sweep of the second visit
+      launch_sweep<VT, 2>(c, G, Cn, l + 1, Cn.sol.p, Cn.b.p, Cn.b2.p, Cn.xa.p + 2 * Cn.off);
+      UFE_TRY(mg_cycle<VT>(c, G, l + 1, Cn.b2.p, Cn.sol2.p, true));
+    } else {
+      launch_sweep<VT, 1>(c, G, Cn, l + 1, Cn.sol.p, Cn.b.p, Cn.b2.p);
+      UFE_TRY(mg_cycle<VT>(c, G, l + 1, Cn.b2.p, Cn.sol2.p));
+    }
     op_axpy(c, G, 2 * Cn.n, Cn.sol2.p, Cn.sol.p);
   }
   return 0;
@@ -728,7 +773,7 @@ int mg_coarse_from_fine(Ctx* c, Mg& G) {
 
 // solves (approximately) A_l x = b;  the result is written to `out` (node t at out[2t..2t+1])
 template <typename VT>
-int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out) {
+int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out, bool x1_ready) {
   MgLevel& L = G.lv[l];
   const MgParams& P = G.p;
   cudaStream_t st = c->stream;
@@ -750,7 +795,7 @@ int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out) {
   }
   MgLevel& Cn = G.lv[l + 1];
   const bool split = l == 0 && G.distributed;   // level 0 is a row block: its iterates need the neighbours' halo before every matrix pass
-  op_smooth0(c, G, l, L.n, b, L.dblk.p, xa + 2 * L.off);
+  if (!x1_ready) op_smooth0(c, G, l, L.n, b, L.dblk.p, xa + 2 * L.off);
   for (int s = 1; s < P.nu_pre; ++s) {
     if (split) UFE_TRY(halo_exchange(c, G.rb, xa, 1, 2));
     launch_sweep<VT, 0>(c, G, L, l, xa, b, xb + 2 * L.off);
@@ -759,12 +804,24 @@ int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out) {
   if (split) UFE_TRY(halo_exchange(c, G.rb, xa, 1, 2));
   launch_sweep<VT, 1>(c, G, L, l, xa, b, L.r.p);
   if (split) UFE_CUDA(cudaMemsetAsync(Cn.b.p, 0, sizeof(double) * 2 * (size_t)Cn.n, st));
-  op_restrict(c, G, l, L.nc_loc, L.mem_ptr.p, L.mem.p, L.r.p, Cn.b.p + 2 * (size_t)L.c_offset);
+  // the child's first sweep rides on the restriction unless the child is solved directly or its right-hand side still needs the all-reduce
+  const bool child_smooths = !(l + 1 == last && G.dense_n > 0);
+  const bool fuse_down = mg_fuse(G) && !split && child_smooths && l >= 1;
+  if (fuse_down) op_restrict(c, G, l, L.nc_loc, L.mem_ptr.p, L.mem.p, L.r.p, Cn.b.p + 2 * (size_t)L.c_offset, Cn.dblk.p, Cn.xa.p + 2 * Cn.off);
+  else op_restrict(c, G, l, L.nc_loc, L.mem_ptr.p, L.mem.p, L.r.p, Cn.b.p + 2 * (size_t)L.c_offset);
   if (split) UFE_TRY(allreduce_sum_large(c, Cn.b.p, 2 * (size_t)Cn.n, false));   // every rank now holds the whole level-1 right-hand side
   if (l == 0) UFE_TRY(mg_coarse_from_fine<VT>(c, G));
-  else UFE_TRY(mg_coarse_correction<VT>(c, G, l));
-  op_prolong(c, G, l, L.n, L.agg.p, Cn.sol.p, P.overcorr, xa + 2 * L.off);
-  for (int s = 0; s < P.nu_post; ++s) {
+  else UFE_TRY(mg_coarse_correction<VT>(c, G, l, fuse_down));
+  int s0 = 0;
+  if (mg_fuse(G) && l >= 1 && P.nu_post >= 1) {   // prolongation fused into the first post-sweep (levels >= 1: off = 0, agg covers the whole level)
+    double* dst = (P.nu_post == 1) ? out : xb + 2 * L.off;
+    launch_sweep<VT, 3>(c, G, L, l, xa, b, dst, nullptr, L.agg.p, Cn.sol.p, P.overcorr);
+    std::swap(xa, xb);
+    s0 = 1;
+  } else {
+    op_prolong(c, G, l, L.n, L.agg.p, Cn.sol.p, P.overcorr, xa + 2 * L.off);
+  }
+  for (int s = s0; s < P.nu_post; ++s) {
     double* dst = (s == P.nu_post - 1) ? out : xb + 2 * L.off;
     if (split) UFE_TRY(halo_exchange(c, G.rb, xa, 1, 2));
     launch_sweep<VT, 0>(c, G, L, l, xa, b, dst);
@@ -818,6 +875,8 @@ int mg_build(Ctx* c, Mg& G, const BlkMat& B, const Range& rb) {
   G.valid = false;
   G.drop_graph();
   if (const char* e = getenv("UFE_B200_MG_GRAPH")) G.p.use_graph = atoi(e);   // debugging aid: 0 = plain launches
+  if (const char* e = getenv("UFE_B200_MG_DOUBLE")) G.p.double_from = atoi(e);
+  if (const char* e = getenv("UFE_B200_MG_FUSE")) G.p.fuse = atoi(e);
   G.lv.clear();
   G.lv.reserve(G.p.max_levels + 1);
   G.gather_entries = 0;
@@ -842,7 +901,7 @@ int mg_build(Ctx* c, Mg& G, const BlkMat& B, const Range& rb) {
     HostTransfer T;
     const bool split = G.distributed && G.lv.size() == 1;
     if (split) UFE_TRY(build_transfer_distributed(c, H, rb, T));
-    else build_transfer(H, T);
+    else build_transfer(H, T, (G.p.double_from > 0 && (int)G.lv.size() - 1 >= G.p.double_from) ? 2 : 1);
     if (!split && (T.nc >= L.n || T.nc * 10 > L.n * 9)) break;   // coarsening stalled: stop here, smooth on this level
     L.nc = T.nc; L.nc_loc = T.nc_loc; L.c_offset = T.offset;
     UFE_TRY(upload(c, L.agg, T.agg)); UFE_TRY(upload(c, L.mem_ptr, T.mem_ptr)); UFE_TRY(upload(c, L.mem, T.mem));
