@@ -304,6 +304,30 @@ int ufe_b200_pc_step(ufe_b200_handle h, const ufe_b200_config* cfg, int approxim
 int ufe_b200_solve_SIA(ufe_b200_handle h, const ufe_b200_config* cfg, double SIA_maximum_diffusivity, const double* Hi, const double* Hs,
                        const double* A_flow, double* u_3D_b, double* v_3D_b, double* D_3D_b, double* du_dz_3D_a, double* dv_dz_3D_a);
 
+/* ---- secondary velocities ------------------------------------------------------------ */
+/* Outputs of calc_secondary_velocities( mesh, ice) (src/UFEMISM/ice_dynamics/conservation_of_momentum/conservation_of_momentum_main.f90:177-246):
+ * the ice%... members of the same names; b-grid fields (ti1:ti2), a-grid fields (vi1:vi2[,nz]).  NULL pointers are skipped. */
+typedef struct ufe_b200_secondary_velocities {
+  double *u_surf_b, *v_surf_b, *uabs_surf_b, *u_base_b, *v_base_b, *uabs_base_b, *u_vav_b, *v_vav_b, *uabs_vav_b;
+  double *u_3D, *v_3D;
+  double *u_surf, *v_surf, *u_base, *v_base, *u_vav, *v_vav, *uabs_surf, *uabs_base, *uabs_vav, *R_shear;
+} ufe_b200_secondary_velocities;
+/* u_3D_b, v_3D_b (ti1:ti2,nz): ice%u_3D_b, ice%v_3D_b; pass NULL for both to use the fields the last velocity solve / solve_SIA left on the device. */
+int ufe_b200_calc_secondary_velocities(ufe_b200_handle h, const double* u_3D_b, const double* v_3D_b, const ufe_b200_secondary_velocities* out);
+
+/* Replaces calc_vertical_velocities( mesh, ice, BMB) (src/UFEMISM/ice_dynamics/conservation_of_mass/vertical_velocities.f90:23-196) and
+ * calc_dw_dz (:198-243): w from conservation of mass in every 3-D Voronoi cell, integrated from the ice base upwards.  In: ice%Hi, ice%Hs,
+ * ice%Hib, ice%dHb_dt, ice%dHi_dt, BMB, ice%mask_grounded_ice, ice%mask_floating_ice (vi1:vi2); the zeta gradients dzeta_d{x,y,z}_ak are formed
+ * from Hi and Hs as calc_zeta_gradients does (utilities/zeta_gradients.f90:88-115).  The horizontal velocities are the ones on the device:
+ * u_3D_b, v_3D_b of the last velocity solve and u_3D, v_3D of the last ufe_b200_calc_secondary_velocities (call that first, as the reference
+ * does).  Out: ice%w_3D and (if not NULL) ice%dw_dz_3D (vi1:vi2,nz); dw_dz_3D is NaN where there is no ice, like the reference. */
+typedef struct ufe_b200_vertical_velocity_io {
+  const double *Hi, *Hs, *Hib, *dHb_dt, *dHi_dt, *BMB;
+  const int32_t *mask_grounded_ice, *mask_floating_ice;
+  double *w_3D, *dw_dz_3D;
+} ufe_b200_vertical_velocity_io;
+int ufe_b200_calc_vertical_velocities(ufe_b200_handle h, const ufe_b200_config* cfg, const ufe_b200_vertical_velocity_io* io);
+
 /* ---- timing hooks for bench.py (CUDA events on the library's own stream) ----------------------- */
 /* Milliseconds spent in the named kernel class since the last reset, and its launch count.
  * classes: "spmv_stiffness", "krylov_vec", "assembly", "column", "tri", "epilogue", "thickness", "operator_spmv" */

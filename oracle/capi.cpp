@@ -195,3 +195,20 @@ extern "C" void orc_solve_SIA(void* h, const ufe_b200_config* cfg, double SIA_ma
   auto* o = static_cast<OracleMesh*>(h);
   solve_SIA(o->mv, o->ops, to_config(cfg), SIA_maximum_diffusivity, Hi, Hs, A_flow, u_3D_b, v_3D_b, D_3D_b, du_dz_3D_a, dv_dz_3D_a);
 }
+
+extern "C" void orc_calc_secondary_velocities(void* h, const double* u_3D_b, const double* v_3D_b, const ufe_b200_secondary_velocities* out) {
+  auto* o = static_cast<OracleMesh*>(h);
+  static_assert(sizeof(SecondaryVelocities) == sizeof(ufe_b200_secondary_velocities), "the two structs list the same 21 pointers in the same order");
+  SecondaryVelocities S;
+  std::memcpy(&S, out, sizeof(S));
+  calc_secondary_velocities(o->mv, o->ops, u_3D_b, v_3D_b, S);
+}
+
+extern "C" void orc_calc_vertical_velocities(void* h, const ufe_b200_config* cfg, const ufe_b200_vertical_velocity_io* io, const double* u_3D_b,
+                                             const double* v_3D_b, const double* u_3D, const double* v_3D) {
+  auto* o = static_cast<OracleMesh*>(h);
+  static_assert(sizeof(VerticalVelocityIO) == sizeof(ufe_b200_vertical_velocity_io), "same 10 pointers in the same order");
+  VerticalVelocityIO V;
+  std::memcpy(&V, io, sizeof(V));
+  calc_vertical_velocities(o->mv, o->ops, to_config(cfg), V, u_3D_b, v_3D_b, u_3D, v_3D);
+}

@@ -143,6 +143,24 @@ int calc_dHi_dt(const MeshView& mesh, const Config& C, ThicknessIO& io, double* 
 void calc_flux_divergence_matrix_upwind(const MeshView& mesh, const double* u_vav_b, const double* v_vav_b,
                                         const double* fraction_margin, Csr& M_divQ, std::vector<double>* u_perp = nullptr);
 
+// --- secondary velocities (conservation_of_momentum_main.f90:177-246): every pointer is an output the caller owns
+struct SecondaryVelocities {
+  double *u_surf_b, *v_surf_b, *uabs_surf_b, *u_base_b, *v_base_b, *uabs_base_b, *u_vav_b, *v_vav_b, *uabs_vav_b;   // (nTri)
+  double *u_3D, *v_3D;                                                                                             // (nV,nz)
+  double *u_surf, *v_surf, *u_base, *v_base, *u_vav, *v_vav, *uabs_surf, *uabs_base, *uabs_vav, *R_shear;           // (nV)
+};
+void calc_secondary_velocities(const MeshView& mesh, const Operators& ops, const double* u_3D_b, const double* v_3D_b, SecondaryVelocities& S);
+
+// --- vertical velocities (conservation_of_mass/vertical_velocities.f90:23-243); the zeta gradients follow zeta_gradients.f90:88-115
+struct VerticalVelocityIO {
+  const double *Hi, *Hs, *Hib, *dHb_dt, *dHi_dt, *BMB;     // (nV)
+  const int *mask_grounded_ice, *mask_floating_ice;         // (nV)
+  double *w_3D, *dw_dz_3D;                                  // (nV,nz) out (dw_dz_3D may be null)
+};
+void calc_vertical_velocities(const MeshView& mesh, const Operators& ops, const Config& C, const VerticalVelocityIO& io, const double* u_3D_b,
+                              const double* v_3D_b, const double* u_3D, const double* v_3D);
+void ddzeta_operator(const double* zeta, int nz, std::vector<int>& nb, std::vector<double>& coef);
+
 // --- SIA (SIA_main.f90:65-158) and analytic solutions ------------------------------------------------
 void solve_SIA(const MeshView& mesh, const Operators& ops, const Config& C, double SIA_maximum_diffusivity, const double* Hi, const double* Hs,
                const double* A_flow_3D, double* u_3D_b, double* v_3D_b, double* D_3D_b, double* du_dz_3D_a, double* dv_dz_3D_a);

@@ -39,6 +39,8 @@ def lib():
         L.orc_Halfar_H.argtypes = [C.c_double] * 7
         L.orc_Schoof2006_icestream.argtypes = [C.c_double] * 7 + [dp, dp]
         L.orc_solve_SIA.argtypes = [C.c_void_p, C.POINTER(ub.Config), C.c_double] + [dp] * 8
+        L.orc_calc_secondary_velocities.argtypes = [C.c_void_p, dp, dp, C.POINTER(ub.SecondaryVelocities)]
+        L.orc_calc_vertical_velocities.argtypes = [C.c_void_p, C.POINTER(ub.Config), C.POINTER(ub.VerticalVelocityIO), dp, dp, dp, dp]
         _LIB = L
     return _LIB
 
@@ -120,6 +122,16 @@ class OracleMesh:
         lib().orc_solve_SIA(self.h, C.byref(cfg), max_diffusivity, ub.dp(Hi), ub.dp(Hs), ub.dp(A_flow), *(ub.dp(out[k]) for k in
                             ("u_3D_b", "v_3D_b", "D_3D_b", "du_dz_3D_a", "dv_dz_3D_a")))
         return out
+
+    def calc_secondary_velocities(self, u_3D_b, v_3D_b):
+        self.calc_matrix_operators()
+        s, arrs = ub.alloc_secondary(self.m.nV, self.m.nTri, self.m.nz)
+        lib().orc_calc_secondary_velocities(self.h, ub.dp(u_3D_b), ub.dp(v_3D_b), C.byref(s))
+        return arrs
+
+    def calc_vertical_velocities(self, cfg, io, u_3D_b, v_3D_b, u_3D, v_3D):
+        self.calc_matrix_operators()
+        lib().orc_calc_vertical_velocities(self.h, C.byref(cfg), C.byref(io), ub.dp(u_3D_b), ub.dp(v_3D_b), ub.dp(u_3D), ub.dp(v_3D))
 
     def flux_divergence_matrix(self, u_b, v_b, fraction_margin):
         m, nnz = C.c_int(), C.c_int()

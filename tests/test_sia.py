@@ -153,3 +153,125 @@ def test_gpu_halfar_dome_evolution():
     ana, ana0 = _halfar_analytic(m, dt * nsteps), _halfar_analytic(m, 0.0)
     rmse = np.sqrt(np.mean((Hi_gpu - ana) ** 2)); moved = np.sqrt(np.mean((ana - ana0) ** 2))
     assert moved > 50.0 and rmse < 20.0 and rmse < 0.2 * moved, (rmse, moved)
+
+
+def _random_3D_velocities(m, seed=5):
+    rng = np.random.default_rng(seed)
+    prof = np.linspace(1.0, 0.3, m.nz) ** 2
+    u = np.asfortranarray(200.0 * rng.standard_normal((m.nTri, 1)) * prof + rng.standard_normal((m.nTri, m.nz)))
+    v = np.asfortranarray(150.0 * rng.standard_normal((m.nTri, 1)) * prof + rng.standard_normal((m.nTri, m.nz)))
+    return u, v
+
+
+def test_oracle_secondary_velocities_definitions():
+    """calc_secondary_velocities (conservation_of_momentum_main.f90:177-246) against its definitions in numpy"""
+    w = wl.halfar(4.0e4)
+    m = w.mesh
+    o = ol.OracleMesh(m)
+    u, v = _random_3D_velocities(m)
+    r = o.calc_secondary_velocities(u, v)
+    zeta = np.asarray(m.zeta, float)
+    np.testing.assert_array_equal(r["u_surf_b"], u[:, 0]); np.testing.assert_array_equal(r["v_base_b"], v[:, -1])
+    np.testing.assert_allclose(r["u_vav_b"], vertical_average(zeta, u), rtol=1e-13, atol=1e-12)
+    np.testing.assert_allclose(r["uabs_vav_b"], np.hypot(r["u_vav_b"], r["v_vav_b"]), rtol=1e-14)
+    np.testing.assert_allclose(r["u_3D"], o.apply_operator(ub.OP["map_b_a"], u, m.nz), rtol=1e-14, atol=1e-12)
+    np.testing.assert_allclose(r["v_vav"], o.apply_operator(ub.OP["map_b_a"], r["v_vav_b"]), rtol=1e-14, atol=1e-12)
+    np.testing.assert_allclose(r["R_shear"], (np.hypot(r["u_base"], r["v_base"]) + 0.1) / (np.hypot(r["u_surf"], r["v_surf"]) + 0.1), rtol=1e-14)
+
+
+@pytest.mark.gpu
+def test_gpu_secondary_velocities_match_oracle():
+    w = wl.halfar(2.0e4)
+    m = w.mesh
+    o = ol.OracleMesh(m)
+    u, v = _random_3D_velocities(m)
+    ref = o.calc_secondary_velocities(u, v)
+    ctx = ub.Context(device=0)
+    ctx.mesh_create(m); ctx.calc_matrix_operators()
+    s, out = ub.alloc_secondary(m.nV, m.nTri, m.nz)
+    ub.check(ub.lib().ufe_b200_calc_secondary_velocities(ctx.h, ub.dp(u), ub.dp(v), C.byref(s)))
+    # second call on the resident fields (what follows a velocity solve): same result
+    s2, out2 = ub.alloc_secondary(m.nV, m.nTri, m.nz)
+    ub.check(ub.lib().ufe_b200_calc_secondary_velocities(ctx.h, None, None, C.byref(s2)))
+    ctx.close()
+    for k in ub.SECONDARY_FIELDS:
+        assert rel_l2(out[k], ref[k]) < 1e-13, (k, rel_l2(out[k], ref[k]))
+        assert np.array_equal(out[k], out2[k]), k
+    np.testing.assert_array_equal(out["u_surf_b"], u[:, 0])
+
+
+def _vertical_io(m, Hi, Hs, Hib, dHb_dt, dHi_dt, BMB, mg, mf):
+    keep = [np.ascontiguousarray(a, float) for a in (Hi, Hs, Hib, dHb_dt, dHi_dt, BMB)] + [np.ascontiguousarray(a, np.int32) for a in (mg, mf)]
+    w, dw = np.zeros((m.nV, m.nz), order="F"), np.zeros((m.nV, m.nz), order="F")
+    io = ub.VerticalVelocityIO(*[ub.dp(a) for a in keep[:6]], ub.ip(keep[6]), ub.ip(keep[7]), ub.dp(w), ub.dp(dw))
+    io._keep = keep
+    return io, w, dw
+
+
+def test_oracle_vertical_velocities_of_a_linear_flow():
+    """calc_vertical_velocities (vertical_velocities.f90:23-196) + calc_dw_dz: for u = a x, v = b y, uniform in z, on a flat slab the Voronoi
+    flux integral is exact, so dw/dz = -(a + b) and w = w_base - (a + b) Hi (1 - zeta) on every interior column"""
+    w_ = wl.halfar(4.0e4)
+    m = w_.mesh
+    o = ol.OracleMesh(m)
+    a, b, H = 2.0e-3, -0.5e-3, 1500.0
+    gc = np.asarray(m.Tricc, float)                      # Voronoi vertices
+    u_b = np.asfortranarray(np.repeat((a * gc[:, 0])[:, None], m.nz, 1)); v_b = np.asfortranarray(np.repeat((b * gc[:, 1])[:, None], m.nz, 1))
+    u_a = np.asfortranarray(np.repeat((a * m.V[:, 0])[:, None], m.nz, 1)); v_a = np.asfortranarray(np.repeat((b * m.V[:, 1])[:, None], m.nz, 1))
+    one, zero = np.ones(m.nV), np.zeros(m.nV)
+    io, w, dw = _vertical_io(m, H * one, H * one, zero, zero, zero, zero, one, zero)
+    o.calc_vertical_velocities(w_.cfg, io, u_b, v_b, u_a, v_a)
+    zeta = np.asarray(m.zeta, float)
+    interior = np.asarray(m.VBI) == 0
+    for vi in np.nonzero(~interior)[0]:                  # also drop the ring next to the border (modified Voronoi cells there)
+        interior[np.asarray(m.C)[vi, : m.nC[vi]] - 1] = False
+    assert interior.sum() > m.nV // 2
+    want = -(a + b) * H * (1.0 - zeta)
+    np.testing.assert_allclose(w[interior], np.repeat(want[None, :], interior.sum(), 0), rtol=1e-9, atol=1e-9)
+    np.testing.assert_allclose(dw[interior], -(a + b), rtol=1e-8)
+    # ice-free columns: w = 0, dw_dz = NaN; thin ice: the basal value everywhere
+    io, w, dw = _vertical_io(m, np.where(np.arange(m.nV) % 3 == 0, 5.0, H), H * one, zero, 0.3 * one, zero, -0.2 * one, np.arange(m.nV) % 2, zero)
+    o.calc_vertical_velocities(w_.cfg, io, u_b, v_b, u_a, v_a)
+    noice = np.arange(m.nV) % 2 == 0
+    assert np.all(w[noice] == 0.0) and np.all(np.isnan(dw[noice]))
+    thin = ~noice & (np.arange(m.nV) % 3 == 0)
+    assert thin.any() and np.all(w[thin] == w[thin][:, -1:]) and np.allclose(w[thin][:, -1], 0.3 - 0.2)
+
+
+def _vertical_case(m, seed=11):
+    rng = np.random.default_rng(seed)
+    x, y = m.V[:, 0], m.V[:, 1]
+    L = m.xmax - m.xmin
+    Hi = np.maximum(0.0, 2500.0 * np.cos(1.3 * np.pi * x / L) * np.cos(1.1 * np.pi * y / L) + 30.0 * rng.standard_normal(m.nV))
+    Hi[rng.random(m.nV) < 0.02] = 4.0                      # some thin-ice columns
+    Hb = -300.0 + 400.0 * np.sin(3.0 * x / L) + 20.0 * rng.standard_normal(m.nV)
+    Hib = np.maximum(Hb, -0.9 * Hi)
+    Hs = Hib + Hi
+    mg = ((Hi > 0) & (Hib <= Hb)).astype(np.int32); mf = ((Hi > 0) & (Hib > Hb)).astype(np.int32)
+    return Hi, Hs, Hib, 1e-3 * rng.standard_normal(m.nV), 0.5 * rng.standard_normal(m.nV), rng.standard_normal(m.nV), mg, mf
+
+
+@pytest.mark.gpu
+def test_gpu_vertical_velocities_match_oracle():
+    w_ = wl.halfar(2.0e4)
+    m = w_.mesh
+    o = ol.OracleMesh(m)
+    u, v = _random_3D_velocities(m)
+    sec = o.calc_secondary_velocities(u, v)
+    case = _vertical_case(m)
+    assert case[6].sum() > 100 and case[7].sum() > 100 and (case[0] == 0).sum() > 100
+    io, w_ref, dw_ref = _vertical_io(m, *case)
+    cfg = w_.cfg
+    o.calc_vertical_velocities(cfg, io, u, v, sec["u_3D"], sec["v_3D"])
+    ctx = ub.Context(device=0)
+    ctx.mesh_create(m); ctx.calc_matrix_operators()
+    io2, w_gpu, dw_gpu = _vertical_io(m, *case)
+    assert ub.lib().ufe_b200_calc_vertical_velocities(ctx.h, C.byref(cfg), C.byref(io2)) != 0     # needs the a-grid velocities first
+    s, out = ub.alloc_secondary(m.nV, m.nTri, m.nz)
+    ub.check(ub.lib().ufe_b200_calc_secondary_velocities(ctx.h, ub.dp(u), ub.dp(v), C.byref(s)))
+    ub.check(ub.lib().ufe_b200_calc_vertical_velocities(ctx.h, C.byref(cfg), C.byref(io2)))
+    ctx.close()
+    assert rel_l2(w_gpu, w_ref) < 1e-12, rel_l2(w_gpu, w_ref)
+    ice = (case[6] + case[7]) > 0
+    assert np.all(np.isnan(dw_gpu[~ice])) and np.all(np.isnan(dw_ref[~ice])) and np.all(w_gpu[~ice] == 0.0)
+    assert rel_l2(dw_gpu[ice], dw_ref[ice]) < 1e-12, rel_l2(dw_gpu[ice], dw_ref[ice])

@@ -95,6 +95,8 @@ struct Mesh;      // mesh.cuh
 struct Velocity;  // velocity.cuh
 struct Krylov;    // krylov.cuh
 struct Thickness; // thickness.cuh
+struct Secondary; // secondary.cu
+void secondary_free(Secondary* s);
 
 // multigrid preconditioner knobs (mg.cuh); set through ufe_b200_set_mg_params
 struct MgParams {
@@ -134,6 +136,7 @@ struct Ctx {
   Velocity* vel = nullptr;
   Krylov* krylov = nullptr;
   Thickness* thick = nullptr;
+  Secondary* sec = nullptr;
   MgParams mg_params;
   // pinned scratch for small D2H reads
   double* h_pinned = nullptr;       // 64 doubles

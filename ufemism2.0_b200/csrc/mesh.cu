@@ -148,6 +148,7 @@ int ufe_b200_mesh_destroy(ufe_b200_handle h) {
   cudaStreamSynchronize(c->stream);
   velocity_free(c->vel); c->vel = nullptr;
   thickness_free(c->thick); c->thick = nullptr;
+  secondary_free(c->sec); c->sec = nullptr;
   delete c->mesh; c->mesh = nullptr;
   return 0;
 }

@@ -167,6 +167,24 @@ module ufe_b200_mod
       integer(c_int) :: ierr
     end function
 
+    ! calc_secondary_velocities (conservation_of_momentum_main.f90:177-246); out = c_loc of a ufe_b200_secondary_velocities
+    function c_ufe_b200_calc_secondary_velocities( h, u_3D_b, v_3D_b, out) bind(C, name='ufe_b200_calc_secondary_velocities') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h
+      type(c_ptr), value :: u_3D_b, v_3D_b            ! c_loc( ice%u_3D_b) / c_null_ptr to use the fields of the last device solve
+      type(c_ptr), value :: out                       ! 21 c_loc's in the order of include/ufe_b200.h
+      integer(c_int) :: ierr
+    end function
+
+    ! calc_vertical_velocities + calc_dw_dz (conservation_of_mass/vertical_velocities.f90:23-243); io = c_loc of a ufe_b200_vertical_velocity_io
+    function c_ufe_b200_calc_vertical_velocities( h, cfg, io) bind(C, name='ufe_b200_calc_vertical_velocities') result( ierr)
+      import :: c_int, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      type(c_ptr), value :: io
+      integer(c_int) :: ierr
+    end function
+
   end interface
 
 contains

@@ -97,6 +97,29 @@ class VelocityState(C.Structure):
     _fields_ = [(n, c_dp) for n in VELOCITY_FIELDS]
 
 
+SECONDARY_FIELDS = ["u_surf_b", "v_surf_b", "uabs_surf_b", "u_base_b", "v_base_b", "uabs_base_b", "u_vav_b", "v_vav_b", "uabs_vav_b", "u_3D", "v_3D",
+                    "u_surf", "v_surf", "u_base", "v_base", "u_vav", "v_vav", "uabs_surf", "uabs_base", "uabs_vav", "R_shear"]
+
+
+class SecondaryVelocities(C.Structure):
+    _fields_ = [(n, c_dp) for n in SECONDARY_FIELDS]
+
+
+def alloc_secondary(n_a, n_b, nz):
+    s = SecondaryVelocities()
+    arrs = {}
+    for n in SECONDARY_FIELDS:
+        a = np.zeros(n_b) if n.endswith("_b") else (np.zeros((n_a, nz), order="F") if n in ("u_3D", "v_3D") else np.zeros(n_a))
+        arrs[n] = a
+        setattr(s, n, dp(a))
+    return s, arrs
+
+
+class VerticalVelocityIO(C.Structure):
+    _fields_ = [(n, c_dp) for n in ("Hi", "Hs", "Hib", "dHb_dt", "dHi_dt", "BMB")] + [("mask_grounded_ice", c_ip), ("mask_floating_ice", c_ip),
+                                                                                      ("w_3D", c_dp), ("dw_dz_3D", c_dp)]
+
+
 class ThicknessIO(C.Structure):
     _fields_ = [("Hi", c_dp), ("Hb", c_dp), ("SL", c_dp), ("u_vav_b", c_dp), ("v_vav_b", c_dp), ("SMB", c_dp), ("BMB", c_dp),
                 ("LMB", c_dp), ("fraction_margin", c_dp), ("mask_noice", c_ip), ("dHi_dt_target", c_dp),
@@ -189,6 +212,8 @@ def lib():
     L.ufe_b200_pc_step.argtypes = [H, C.POINTER(Config), C.c_int, C.c_double, C.c_double, C.POINTER(IceInputs), C.POINTER(VelocityState),
                                    C.POINTER(ThicknessIO), c_dp] + [C.POINTER(C.c_int)] * 3
     L.ufe_b200_solve_SIA.argtypes = [H, C.POINTER(Config), C.c_double] + [c_dp] * 8
+    L.ufe_b200_calc_secondary_velocities.argtypes = [H, c_dp, c_dp, C.POINTER(SecondaryVelocities)]
+    L.ufe_b200_calc_vertical_velocities.argtypes = [H, C.POINTER(Config), C.POINTER(VerticalVelocityIO)]
     L.ufe_b200_timing_enable.argtypes = [H, C.c_int]
     L.ufe_b200_timing_get.argtypes = [H, C.c_char_p, c_dp, C.POINTER(C.c_longlong)]
     L.ufe_b200_timing_reset.argtypes = [H]
@@ -209,7 +234,7 @@ ABI_SYMBOLS = [
     "ufe_b200_set_mg_params", "ufe_b200_get_mg_info", "ufe_b200_mg_host_transfer", "ufe_b200_mg_host_transfer_get", "ufe_b200_mg_host_transfer_parts", "ufe_b200_mg_host_transfer_parts_get",
     "ufe_b200_solve_DIVA", "ufe_b200_solve_SSA", "ufe_b200_velocity_upload", "ufe_b200_velocity_solve_resident",
     "ufe_b200_velocity_download", "ufe_b200_thickness_upload", "ufe_b200_pc_step_resident", "ufe_b200_pc_step",
-    "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA",
+    "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA", "ufe_b200_calc_secondary_velocities", "ufe_b200_calc_vertical_velocities",
     "ufe_b200_timing_enable", "ufe_b200_timing_get", "ufe_b200_timing_reset", "ufe_b200_timer_start", "ufe_b200_timer_stop",
     "ufe_b200_host_register", "ufe_b200_host_unregister"]
 
