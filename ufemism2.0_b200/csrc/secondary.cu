@@ -201,7 +201,7 @@ extern "C" int ufe_b200_calc_secondary_velocities(ufe_b200_handle h, const doubl
   UFE_CUDA(cudaSetDevice(c->device));
   UFE_TRY(ensure_velocity(c));
   Mesh& M = *c->mesh; Velocity& V = *c->vel;
-  UFE_CHECK(u_3D_b || V.uploaded, "ufe_b200_calc_secondary_velocities: no 3-D velocities given and none resident on the device");
+  UFE_CHECK(u_3D_b || V.uploaded || (c->sec && c->sec->have_3D), "ufe_b200_calc_secondary_velocities: no 3-D velocities given and none resident on the device");
   cudaStream_t st = c->stream;
   const int nz = M.nz, na = M.a.n_loc(), nb = M.b.n_loc();
   const size_t na_ext = M.a.n_ext(), nb_ext = M.b.n_ext();
