@@ -356,15 +356,24 @@ def run_b200(args, rank, world, rdv, log):
         a = keep_io[k]
         setattr(io2, k, ub.ip(a) if a.dtype == np.int32 else ub.dp(a))
     io2.Hi = ub.dp(keep_io["Hi"])
-    pinned = list(A.values()) + list(out.values()) + [v for v in w._keep.values()] + [v for v in keep_io.values()] + [dH_nm1]
+    resident_state = args.e2e_state == "resident"
+    st_e2e, A_e2e = st, A
+    if resident_state:
+        # the solver state (warm-start velocities, basal fields, eta_3D_b) stays on the device between calls, as the reference keeps it inside
+        # its solver object; per step the host sends what it owns (geometry, mass balance, flow factor, friction inputs) and reads the results
+        ub.check(L.ufe_b200_set_state_resident(ctx.h, 1))
+        st_e2e, A_e2e = ub.alloc_velocity_state(na, nb, m.nz, fields=[k for k in STATE_FIELDS if k != "eta_3D_b"])
+        for k in A_e2e:
+            A_e2e[k][...] = A[k]
+    pinned = list(A_e2e.values()) + list(out.values()) + [v for v in w._keep.values()] + [v for v in keep_io.values()] + [dH_nm1]
     registered = [a for a in pinned if a.nbytes >= (1 << 16) and L.ufe_b200_host_register(a.ctypes.data_as(C.c_void_p), a.nbytes) == 0]
     ice_in = [k for k in w._keep if k not in ("Hi", "Hs")]
     bytes_in = (sum(keep_io[k].nbytes for k in ("Hi", "Hb", "SL", "SMB", "BMB", "LMB", "fraction_margin", "mask_noice", "dHi_dt_target")) + dH_nm1.nbytes
-                + sum(w._keep[k].nbytes for k in ice_in) + sum(A[k].nbytes for k in STATE_FIELDS[:7]))
-    bytes_out = sum(a.nbytes for a in A.values()) + sum(a.nbytes for a in out.values()) + dH_nm1.nbytes
+                + sum(w._keep[k].nbytes for k in ice_in) + (0 if resident_state else sum(A[k].nbytes for k in STATE_FIELDS[:7])))
+    bytes_out = sum(a.nbytes for a in A_e2e.values()) + sum(a.nbytes for a in out.values()) + dH_nm1.nbytes
 
     def step_e2e():
-        ub.check(L.ufe_b200_pc_step(ctx.h, C.byref(cfg), 1, DT, DT, C.byref(ice), C.byref(st), C.byref(io2), ub.dp(dH_nm1),
+        ub.check(L.ufe_b200_pc_step(ctx.h, C.byref(cfg), 1, DT, DT, C.byref(ice), C.byref(st_e2e), C.byref(io2), ub.dp(dH_nm1),
                                     C.byref(nv_), C.byref(na_), C.byref(nt_)))
         keep_io["Hi"][:] = out["Hi_tplusdt"]      # the host model accepts the step: Hi_n := Hi_np1
 
@@ -420,7 +429,10 @@ def run_b200(args, rank, world, rdv, log):
                        "per_step": {"viscosity_its": tot[0] / args.steps, "krylov_its_velocity": tot[1] / args.steps, "krylov_its_thickness": tot[2] / args.steps}},
             "e2e": {"value": k_e2e / e2e_s, "unit": "velocity solves/s", "h2d_bytes_per_step": bytes_in[0] // k_e2e, "d2h_bytes_per_step": bytes_out[0] // k_e2e,
                     "steps": k_e2e, "ms_per_step": 1e3 * e2e_s / k_e2e, "h2d_ms_per_step": h2d_ms, "d2h_ms_per_step": d2h_ms,
-                    "call": "ufe_b200_pc_step (host buffers; transfers overlap the thickness solves on a second stream)"},
+                    "call": "ufe_b200_pc_step (host buffers; transfers overlap the thickness solves on a second stream)",
+                    "state": ("solver state resident on the device (ufe_b200_set_state_resident); per step in: geometry, mass balance, flow factor, "
+                              "friction inputs; out: Hi(t+dt), rates, u/v_3D_b, depth-averaged and basal velocities, basal stresses")
+                    if args.e2e_state == "resident" else "whole solver state (incl. eta_3D_b) uploaded and downloaded every step"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak if peak else None, "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
@@ -448,6 +460,8 @@ def main():
     ap.add_argument("--mg-overcorr", type=float, default=1.5)
     ap.add_argument("--mg-w-levels", type=int, default=3)
     ap.add_argument("--mg-fp32", type=int, default=0)
+    ap.add_argument("--e2e-state", choices=["resident", "roundtrip"], default="resident",
+                    help="e2e leg: solver state kept on the device between calls (default) or uploaded and downloaded every step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     args = ap.parse_args()

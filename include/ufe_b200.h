@@ -295,6 +295,11 @@ int ufe_b200_thickness_download(ufe_b200_handle h, double* Hi, double* dHi_dt, d
 int ufe_b200_pc_step(ufe_b200_handle h, const ufe_b200_config* cfg, int approximation /*0 SSA, 1 DIVA*/, double dt, double dt_prev,
                      const ufe_b200_ice_inputs* ice, ufe_b200_velocity_state* state, const ufe_b200_thickness_io* io, double* dHi_dt_nm1,
                      int* n_visc_its, int* n_Axb_its_velocity, int* n_Axb_its_thickness);
+/* on = 1: the host does not modify the velocity solver's state between ufe_b200_pc_step calls (the reference keeps it inside the solver
+ * object, type_ice_velocity_solver_DIVA, src/UFEMISM/types/ice_model_types.f90:149-197): after the first call the state fields are no
+ * longer copied to the device, and `state` only selects which results are copied back (NULL members are skipped).  Call with 0 after the
+ * host changed the state itself (e.g. remapping to a new mesh). */
+int ufe_b200_set_state_resident(ufe_b200_handle h, int on);
 
 /* ---- SIA (config 4) ------------------------------------------------------------------------------ */
 /* Replaces solve_SIA( mesh, ice, SIA) (src/UFEMISM/ice_dynamics/conservation_of_momentum/SIA/SIA_main.f90:65-158), the analytical SIA

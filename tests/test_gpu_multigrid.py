@@ -132,3 +132,25 @@ def test_config2_mismip_plus_ssa_on_graded_mesh(pc):
     for f in ("u_vav_b", "v_vav_b", "N_b", "basal_friction_coefficient_b"):
         assert rel_l2(g[f], r[f]) < 1e-6, (f, rel_l2(g[f], r[f]))
     assert np.abs(g["u_vav_b"]).max() > 10.0        # a flowing ice stream, not the trivial solution
+
+
+def test_single_cta_tail_equals_separate_launches():
+    """the small levels run as one single-CTA kernel per visit (k_mg_tail); same arithmetic as the stand-alone kernels, so the same bits"""
+    import os
+    w = wl.mismip_mod(2.0e4)
+    m = w.mesh
+    co = _coefficients(m, seed=6)
+    cfg = wl.scaling_config()
+    cfg.pc_type = ub.PC_MG
+    res = []
+    try:
+        for tail in ("0", "4096"):
+            os.environ["UFE_B200_MG_TAIL"] = tail
+            ctx = ub.Context(device=0)
+            ctx.mesh_create(m); ctx.calc_matrix_operators()
+            res.append(_linearised(ctx, cfg, m, *co, 1e-10, 1e-30))
+            assert ctx.mg_info()["levels"] >= 4
+            ctx.close()
+    finally:
+        os.environ.pop("UFE_B200_MG_TAIL", None)
+    assert res[0][2] == res[1][2] and np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1])

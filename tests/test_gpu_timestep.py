@@ -131,3 +131,34 @@ def test_host_buffer_pc_step_equals_resident():
     assert np.array_equal(out["Hi_tplusdt"], Hi_r)
     for k in ("u_vav_b", "v_vav_b", "u_3D_b", "eta_3D_b", "tau_bx_b"):
         assert np.array_equal(A[k], res[k]), k
+
+
+def test_host_buffer_pc_step_with_resident_solver_state():
+    """ufe_b200_set_state_resident: the state is uploaded once; later calls ignore the host copies of it and only bring results back"""
+    w = _workload()
+    m, cfg = w.mesh, w.cfg
+    cfg.pc_type = ub.PC_MG
+    L = ub.lib()
+    nv, na, nt = C.c_int(), C.c_int(), C.c_int()
+    results = []
+    for resident in (0, 1):
+        ctx = ub.Context(device=0)
+        ctx.mesh_create(m); ctx.calc_matrix_operators()
+        ice, st, A = _spin_up(ctx, w)
+        ub.check(L.ufe_b200_set_state_resident(ctx.h, resident))
+        out = {k: np.zeros(m.nV) for k in ("AMB", "dHi_dt", "Hi_tplusdt", "divQ")}
+        io2, keep2 = bench.thickness_io(w, slice(None), w.f["Hi"].copy(), out=out)
+        dH_nm1 = np.zeros(m.nV)
+        dt_prev = 0.0
+        for it in range(3):
+            ub.check(L.ufe_b200_pc_step(ctx.h, C.byref(cfg), 1, DT, dt_prev, C.byref(ice), C.byref(st), C.byref(io2), ub.dp(dH_nm1),
+                                        C.byref(nv), C.byref(na), C.byref(nt)))
+            keep2["Hi"][:] = out["Hi_tplusdt"]
+            dt_prev = DT
+            if resident and it == 0:
+                A["eta_3D_b"][...] = np.nan; A["u_base_b"][...] = np.nan     # must not be read again
+        results.append((out["Hi_tplusdt"].copy(), A["u_vav_b"].copy(), A["u_3D_b"].copy(), (nv.value, na.value, nt.value)))
+        ctx.close()
+    assert results[0][3] == results[1][3]
+    for a, b in zip(results[0][:3], results[1][:3]):
+        assert np.array_equal(a, b)

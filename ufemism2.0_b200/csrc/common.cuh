@@ -106,6 +106,10 @@ struct MgParams {
   int w_levels = 3;              // coarse levels 1..w_levels are visited twice per cycle (W-cycle on top, V-cycle below)
   int dense_max = 128;           // coarsest level: at most this many nodes -> dense inverse; otherwise `coarse_sweeps` sweeps
   int coarse_sweeps = 8;
+  int tail_max = 0;              // > 0: levels from the first one with <= tail_max nodes down run as one single-CTA kernel per visit (k_mg_tail).
+                                 // Measured slower than graph nodes on B200 at 4 M vertices (0.82 vs 0.72 ms per cycle with 2048, 1.98 ms with
+                                 // 16384: one SM's L2 bandwidth and latency cost more than ~80 kernel boundaries save;
+                                 // profiles/r01_mg_probe_tail.log), so off by default; UFE_B200_MG_TAIL=<nodes> enables it
   int max_levels = 12;
   int fuse = 0;                  // 1: fuse neighbouring operations on the coarse levels (3 launches per level visit instead of 5); measured no
                                  // gain on B200 (the fused kernels have longer dependent-load chains: profiles/r01_mg_probe_fuse.log)
@@ -137,6 +141,7 @@ struct Ctx {
   Krylov* krylov = nullptr;
   Thickness* thick = nullptr;
   Secondary* sec = nullptr;
+  int state_resident = 0;        // ufe_b200_set_state_resident: ufe_b200_pc_step keeps the solver state on the device between calls
   MgParams mg_params;
   // pinned scratch for small D2H reads
   double* h_pinned = nullptr;       // 64 doubles

@@ -319,30 +319,74 @@ int build_transfer_distributed(Ctx* c, const HostLevel& F, const Range& rb, Host
 // MODE 3: x' = x + w P e, out = x' + Dw (b - A x')   (coarse-grid correction fused into the first post-smoothing sweep; the
 //         neighbours' corrections are gathered through agg, so the prolongated iterate is never written; coarse levels only)
 // x_ext: iterate over the extended range (node t at x2[off + t]); out, out2, b: node t at [t]
-template <typename VT, int MODE>
+// Pointer flavours of the cycle operations.  R = true: stand-alone kernels -- inputs are read-only for the whole launch (__restrict__, so the
+// compiler may use the non-coherent load path).  R = false: inside k_mg_tail one launch runs many operations and an operation reads what an
+// earlier one wrote, so every vector goes through ordinary coherent loads (one CTA: the SM's L1 plus __syncthreads order them).
+template <bool R> struct MgPtr {
+  typedef const double* __restrict__ cd; typedef double* __restrict__ d; typedef const double2* __restrict__ cd2;
+};
+template <> struct MgPtr<false> {
+  typedef const double* cd; typedef double* d; typedef const double2* cd2;
+};
+
+// U: slots of a row in flight at once.  Level 0 streams gigabytes and is bandwidth-bound (U = 2 keeps its registers low); the coarse levels are a
+// chain of dependent loads (column -> iterate) with only a few warps per SM, so their time is load latency x chain length: U = 8 issues the
+// columns, values and gathers of 8 slots before the first use and shortens the chain ~4x.  The summation order is the same for every U.
+template <typename VT, int MODE, int U = 2, bool R = true>
 __device__ __forceinline__ void d_mg_sweep(int n, int off, const int* __restrict__ slice_ptr, const int* __restrict__ col, const VT* __restrict__ val,
-                                           const double* __restrict__ x_ext, const double* __restrict__ b, const double* __restrict__ dblk,
-                                           double* __restrict__ out, int bid, int nb, double* __restrict__ out2 = nullptr,
-                                           const int* __restrict__ agg = nullptr, const double* __restrict__ ec = nullptr, double w = 0.0) {
+                                           typename MgPtr<R>::cd x_ext, typename MgPtr<R>::cd b, const double* __restrict__ dblk,
+                                           typename MgPtr<R>::d out, int bid, int nb, typename MgPtr<R>::d out2 = nullptr,
+                                           const int* __restrict__ agg = nullptr, typename MgPtr<R>::cd ec = nullptr, double w = 0.0) {
   const int lane = threadIdx.x & 31;
   const int warps_per_block = blockDim.x >> 5;
   const int n_slices = (n + 31) >> 5;
-  const double2* __restrict__ x2 = reinterpret_cast<const double2*>(x_ext);
-  const double2* __restrict__ e2 = reinterpret_cast<const double2*>(ec);
+  typename MgPtr<R>::cd2 x2 = reinterpret_cast<const double2*>(x_ext);
+  typename MgPtr<R>::cd2 e2 = reinterpret_cast<const double2*>(ec);
   for (int s = bid * warps_per_block + (threadIdx.x >> 5); s < n_slices; s += nb * warps_per_block) {
     const int t = (s << 5) + lane;
     const int k0 = slice_ptr[s], k1 = slice_ptr[s + 1];
     double yu = 0.0, yv = 0.0;
     const int* __restrict__ cp = col + (size_t)k0 * 32 + lane;
     const VT* __restrict__ vp = val + (size_t)k0 * 128 + lane;
+    if (U <= 2) {
 #pragma unroll 2
-    for (int k = k0; k < k1; ++k, cp += 32, vp += 128) {
-      const int tj = *cp;
-      const double a0 = (double)vp[0], a1 = (double)vp[32], a2 = (double)vp[64], a3 = (double)vp[96];
-      double2 xv = x2[tj];
-      if (MODE == 3) { const double2 ev = e2[agg[tj]]; xv.x += w * ev.x; xv.y += w * ev.y; }
-      yu += a0 * xv.x + a1 * xv.y;
-      yv += a2 * xv.x + a3 * xv.y;
+      for (int k = k0; k < k1; ++k, cp += 32, vp += 128) {
+        const int tj = *cp;
+        const double a0 = (double)vp[0], a1 = (double)vp[32], a2 = (double)vp[64], a3 = (double)vp[96];
+        double2 xv = x2[tj];
+        if (MODE == 3) { const double2 ev = e2[agg[tj]]; xv.x += w * ev.x; xv.y += w * ev.y; }
+        yu += a0 * xv.x + a1 * xv.y;
+        yv += a2 * xv.x + a3 * xv.y;
+      }
+    } else {
+      for (int k = k0; k < k1; k += U, cp += U * 32, vp += U * 128) {
+        int tj[U], ta[U];
+        VT a[U][4];
+        double2 xv[U], ev[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) tj[u] = (k + u < k1) ? cp[u * 32] : -1;
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (tj[u] >= 0) { a[u][0] = vp[u * 128]; a[u][1] = vp[u * 128 + 32]; a[u][2] = vp[u * 128 + 64]; a[u][3] = vp[u * 128 + 96]; }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          if (tj[u] >= 0) xv[u] = x2[tj[u]];
+          if (MODE == 3 && tj[u] >= 0) ta[u] = agg[tj[u]];
+        }
+        if (MODE == 3) {
+#pragma unroll
+          for (int u = 0; u < U; ++u)
+            if (tj[u] >= 0) ev[u] = e2[ta[u]];
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (tj[u] >= 0) {
+            double2 x = xv[u];
+            if (MODE == 3) { x.x += w * ev[u].x; x.y += w * ev[u].y; }
+            yu += (double)a[u][0] * x.x + (double)a[u][1] * x.y;
+            yv += (double)a[u][2] * x.x + (double)a[u][3] * x.y;
+          }
+      }
     }
     if (t < n) {
       const double2 bv = reinterpret_cast<const double2*>(b)[t];
@@ -352,23 +396,24 @@ __device__ __forceinline__ void d_mg_sweep(int n, int off, const int* __restrict
         const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
         double2 xo = make_double2(0.0, 0.0);
         if (MODE == 0 || MODE == 3) xo = x2[off + t];
-        if (MODE == 3) { const double2 ev = e2[agg[off + t]]; xo.x += w * ev.x; xo.y += w * ev.y; }
+        if (MODE == 3) { const double2 e = e2[agg[off + t]]; xo.x += w * e.x; xo.y += w * e.y; }
         double* dst = (MODE == 2) ? out2 : out;
         reinterpret_cast<double2*>(dst)[t] = make_double2(xo.x + d01.x * ru + d01.y * rv, xo.y + d23.x * ru + d23.y * rv);
       }
     }
   }
 }
-template <typename VT, int MODE>
+template <typename VT, int MODE, int U>
 __global__ void __launch_bounds__(kBlock) k_mg_sweep(int n, int off, const int* __restrict__ slice_ptr, const int* __restrict__ col,
                                                      const VT* __restrict__ val, const double* __restrict__ x_ext, const double* __restrict__ b,
                                                      const double* __restrict__ dblk, double* __restrict__ out, double* __restrict__ out2,
                                                      const int* __restrict__ agg, const double* __restrict__ ec, double w) {
-  d_mg_sweep<VT, MODE>(n, off, slice_ptr, col, val, x_ext, b, dblk, out, blockIdx.x, gridDim.x, out2, agg, ec, w);
+  d_mg_sweep<VT, MODE, U>(n, off, slice_ptr, col, val, x_ext, b, dblk, out, blockIdx.x, gridDim.x, out2, agg, ec, w);
 }
 
 // x = Dw b  (first sweep from a zero iterate)
-__device__ __forceinline__ void d_mg_smooth0(int n, const double* __restrict__ b, const double* __restrict__ dblk, double* __restrict__ x_own, int bid, int nb) {
+template <bool R = true>
+__device__ __forceinline__ void d_mg_smooth0(int n, typename MgPtr<R>::cd b, const double* __restrict__ dblk, typename MgPtr<R>::d x_own, int bid, int nb) {
   for (int t = bid * blockDim.x + threadIdx.x; t < n; t += nb * blockDim.x) {
     const double2 bv = reinterpret_cast<const double2*>(b)[t];
     const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
@@ -380,14 +425,25 @@ __global__ void k_mg_smooth0(int n, const double* __restrict__ b, const double* 
 }
 
 // bc_I = sum of r over the members of aggregate I (fixed order); with dblk_c also the coarse level's first sweep x_I = Dw_I bc_I
-__device__ __forceinline__ void d_mg_restrict(int nc, const int* __restrict__ mem_ptr, const int* __restrict__ mem, const double* __restrict__ r,
-                                              double* __restrict__ bc, int bid, int nb, const double* __restrict__ dblk_c = nullptr,
-                                              double* __restrict__ xc = nullptr) {
+template <bool R = true>
+__device__ __forceinline__ void d_mg_restrict(int nc, const int* __restrict__ mem_ptr, const int* __restrict__ mem, typename MgPtr<R>::cd r,
+                                              typename MgPtr<R>::d bc, int bid, int nb, const double* __restrict__ dblk_c = nullptr,
+                                              typename MgPtr<R>::d xc = nullptr) {
+  constexpr int U = 8;   // members in flight (same order of summation; see d_mg_sweep)
   for (int I = bid * blockDim.x + threadIdx.x; I < nc; I += nb * blockDim.x) {
     double su = 0.0, sv = 0.0;
-    for (int k = mem_ptr[I]; k < mem_ptr[I + 1]; ++k) {
-      const double2 v = reinterpret_cast<const double2*>(r)[mem[k]];
-      su += v.x; sv += v.y;
+    const int k1 = mem_ptr[I + 1];
+    for (int k = mem_ptr[I]; k < k1; k += U) {
+      int mj[U];
+      double2 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) mj[u] = (k + u < k1) ? mem[k + u] : -1;
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (mj[u] >= 0) v[u] = reinterpret_cast<const double2*>(r)[mj[u]];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (mj[u] >= 0) { su += v[u].x; sv += v[u].y; }
     }
     reinterpret_cast<double2*>(bc)[I] = make_double2(su, sv);
     if (dblk_c) {
@@ -402,7 +458,8 @@ __global__ void k_mg_restrict(int nc, const int* __restrict__ mem_ptr, const int
 }
 
 // x_i += w * ec_agg(i)
-__device__ __forceinline__ void d_mg_prolong(int n, const int* __restrict__ agg, const double* __restrict__ ec, double w, double* __restrict__ x_own,
+template <bool R = true>
+__device__ __forceinline__ void d_mg_prolong(int n, const int* __restrict__ agg, typename MgPtr<R>::cd ec, double w, typename MgPtr<R>::d x_own,
                                              int bid, int nb) {
   for (int t = bid * blockDim.x + threadIdx.x; t < n; t += nb * blockDim.x) {
     const double2 e = reinterpret_cast<const double2*>(ec)[agg[t]];
@@ -415,7 +472,8 @@ __global__ void k_mg_prolong(int n, const int* __restrict__ agg, const double* _
   d_mg_prolong(n, agg, ec, w, x_own, blockIdx.x, gridDim.x);
 }
 
-__device__ __forceinline__ void d_mg_axpy(int n2, const double* __restrict__ a, double* __restrict__ y, int bid, int nb) {
+template <bool R = true>
+__device__ __forceinline__ void d_mg_axpy(int n2, typename MgPtr<R>::cd a, typename MgPtr<R>::d y, int bid, int nb) {
   for (int i = bid * blockDim.x + threadIdx.x; i < n2; i += nb * blockDim.x) y[i] += a[i];
 }
 __global__ void k_mg_axpy(int n2, const double* __restrict__ a, double* __restrict__ y) { d_mg_axpy(n2, a, y, blockIdx.x, gridDim.x); }
@@ -544,7 +602,8 @@ __global__ void __launch_bounds__(1024) k_mg_dense_invert(int N, double* __restr
 }
 
 // x = A^-1 b on the coarsest level (one block; sb: N doubles of shared memory)
-__device__ __forceinline__ void d_mg_dense_solve(int N, const double* __restrict__ inv, const double* __restrict__ b, double* __restrict__ x, double* sb) {
+template <bool R = true>
+__device__ __forceinline__ void d_mg_dense_solve(int N, const double* __restrict__ inv, typename MgPtr<R>::cd b, typename MgPtr<R>::d x, double* sb) {
   for (int j = threadIdx.x; j < N; j += blockDim.x) sb[j] = b[j];
   __syncthreads();
   for (int i = threadIdx.x; i < N; i += blockDim.x) {
@@ -574,14 +633,42 @@ __global__ void __launch_bounds__(kBlock) k_mg_program(const MgStep* __restrict_
     const MgStep st = steps[s];
     switch (st.op) {
       case MG_OP_SMOOTH0: d_mg_smooth0(st.n, st.b, st.d, st.out, bid, nb); break;
-      case MG_OP_SWEEP: d_mg_sweep<VT, 0>(st.n, st.off, st.ip0, st.ip1, static_cast<const VT*>(st.val), st.x, st.b, st.d, st.out, bid, nb); break;
-      case MG_OP_RESID: d_mg_sweep<VT, 1>(st.n, st.off, st.ip0, st.ip1, static_cast<const VT*>(st.val), st.x, st.b, st.d, st.out, bid, nb); break;
+      case MG_OP_SWEEP: d_mg_sweep<VT, 0, 8>(st.n, st.off, st.ip0, st.ip1, static_cast<const VT*>(st.val), st.x, st.b, st.d, st.out, bid, nb); break;
+      case MG_OP_RESID: d_mg_sweep<VT, 1, 8>(st.n, st.off, st.ip0, st.ip1, static_cast<const VT*>(st.val), st.x, st.b, st.d, st.out, bid, nb); break;
       case MG_OP_RESTRICT: d_mg_restrict(st.n, st.ip0, st.ip1, st.x, st.out, bid, nb); break;
       case MG_OP_PROLONG: d_mg_prolong(st.n, st.ip0, st.x, st.w, st.out, bid, nb); break;
       case MG_OP_AXPY: d_mg_axpy(st.n, st.x, st.out, bid, nb); break;
       case MG_OP_DENSE: if (bid == 0) d_mg_dense_solve(st.n, static_cast<const double*>(st.val), st.b, st.out, sb); break;
     }
     if (s + 1 < nsteps) grid.sync();
+  }
+}
+
+// ---- the small levels at the bottom of the hierarchy as ONE single-CTA kernel per visit ----------------------------------------------------
+// From the first level with at most MgParams::tail_max nodes downwards a level visit is ~13 dependent operations on a few hundred to a few
+// thousand nodes; as graph nodes each costs a kernel boundary (~2 us) plus its own load-latency chain, and with a W-cycle above them these
+// levels are visited 8 times per cycle -- about half of the coarse-grid time at 4 M vertices.  One CTA of 512 threads walks the recorded
+// operations of the whole sub-cycle instead, separated by __syncthreads(): no kernel boundaries, the matrices stay in this SM's L1/L2, and
+// the arithmetic (hence every result bit) is the same as in the stand-alone kernels.
+// Measured on B200 at 4 M vertices (profiles/r01_mg_probe_tail.log): 0.82 ms per cycle against 0.72 ms with plain graph nodes -- a kernel
+// boundary inside a graph is cheaper than one SM streaming a 0.4 MB level from L2 three times per visit.  Kept selectable
+// (MgParams::tail_max / UFE_B200_MG_TAIL, default off) and covered by tests/test_gpu_multigrid.py.
+constexpr int kTailBlock = 512, kTailU = 4;
+template <typename VT>
+__global__ void __launch_bounds__(kTailBlock, 1) k_mg_tail(const MgStep* __restrict__ steps, int nsteps) {
+  __shared__ double sb[2 * 128];   // dense coarsest solve: at most 128 nodes (MgParams::dense_max)
+  for (int s = 0; s < nsteps; ++s) {
+    const MgStep st = steps[s];
+    switch (st.op) {
+      case MG_OP_SMOOTH0: d_mg_smooth0<false>(st.n, st.b, st.d, st.out, 0, 1); break;
+      case MG_OP_SWEEP: d_mg_sweep<VT, 0, kTailU, false>(st.n, st.off, st.ip0, st.ip1, static_cast<const VT*>(st.val), st.x, st.b, st.d, st.out, 0, 1); break;
+      case MG_OP_RESID: d_mg_sweep<VT, 1, kTailU, false>(st.n, st.off, st.ip0, st.ip1, static_cast<const VT*>(st.val), st.x, st.b, st.d, st.out, 0, 1); break;
+      case MG_OP_RESTRICT: d_mg_restrict<false>(st.n, st.ip0, st.ip1, st.x, st.out, 0, 1); break;
+      case MG_OP_PROLONG: d_mg_prolong<false>(st.n, st.ip0, st.x, st.w, st.out, 0, 1); break;
+      case MG_OP_AXPY: d_mg_axpy<false>(st.n, st.x, st.out, 0, 1); break;
+      case MG_OP_DENSE: d_mg_dense_solve<false>(st.n, static_cast<const double*>(st.val), st.b, st.out, sb); break;
+    }
+    __syncthreads();
   }
 }
 
@@ -650,7 +737,8 @@ void launch_sweep(Ctx* c, Mg& G, const MgLevel& L, int level, const double* x_ex
   }
   const int grid = grid_for(c, (long long)L.n_slices * 32, kBlock);
   UFE_LAUNCH(c, level == 0 ? TC_MG_FINE : TC_MG_COARSE);
-  k_mg_sweep<VT, MODE><<<grid, kBlock, 0, c->stream>>>(L.n, L.off, L.slice_ptr, L.col, level_values<VT>(L), x_ext, b, L.dblk.p, out, out2, agg, ec, w);
+  if (level == 0) k_mg_sweep<VT, MODE, 2><<<grid, kBlock, 0, c->stream>>>(L.n, L.off, L.slice_ptr, L.col, level_values<VT>(L), x_ext, b, L.dblk.p, out, out2, agg, ec, w);
+  else k_mg_sweep<VT, MODE, 8><<<grid, kBlock, 0, c->stream>>>(L.n, L.off, L.slice_ptr, L.col, level_values<VT>(L), x_ext, b, L.dblk.p, out, out2, agg, ec, w);
 }
 inline void op_smooth0(Ctx* c, Mg& G, int level, int n, const double* b, const double* dblk, double* x_own) {
   if (G.rec) { G.rec->push_back(MgStep{MG_OP_SMOOTH0, n, 0, 0, nullptr, nullptr, nullptr, nullptr, b, dblk, x_own, 0.0}); return; }
@@ -707,6 +795,30 @@ int mg_coarse_correction(Ctx* c, Mg& G, int l, bool x1_ready = false) {
   return 0;
 }
 
+// records the sub-cycle of the tail level for both (right-hand side, solution) pairs its parent uses and uploads the step lists
+template <typename VT>
+int mg_tail_build(Ctx* c, Mg& G) {
+  G.tail_len[0] = G.tail_len[1] = 0;
+  const int t = G.tail_level;
+  if (t <= 0 || t >= (int)G.lv.size()) return 0;
+  MgLevel& L = G.lv[t];
+  std::vector<MgStep> all, steps;
+  for (int which = 0; which < 2; ++which) {
+    steps.clear();
+    G.rec = &steps;
+    const int rc = mg_cycle<VT>(c, G, t, which ? L.b2.p : L.b.p, which ? L.sol2.p : L.sol.p, false);
+    G.rec = nullptr;
+    if (rc) return rc;
+    G.tail_off[which] = (int)all.size();
+    all.insert(all.end(), steps.begin(), steps.end());
+  }
+  UFE_TRY(G.tail_prog.alloc(all.size() * sizeof(MgStep)));
+  UFE_CUDA(cudaMemcpyAsync(G.tail_prog.p, all.data(), all.size() * sizeof(MgStep), cudaMemcpyHostToDevice, c->stream));
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  G.tail_len[0] = G.tail_off[1]; G.tail_len[1] = (int)all.size() - G.tail_off[1];
+  return 0;
+}
+
 // The same, entered from the fine level: every launch on levels >= 1 is a small, latency-bound kernel, so the whole correction is
 // captured once as a CUDA graph and replayed (one timed region of class mg_coarse instead of ~100 individually timed launches).
 template <typename VT>
@@ -715,6 +827,7 @@ int mg_coarse_from_fine(Ctx* c, Mg& G) {
   LaunchTimer region(c, TC_MG_COARSE, false);
   c->timing_suppress++;
   int rc = 0;
+  if (G.tail_level > 0 && G.tail_len[0] == 0 && (rc = mg_tail_build<VT>(c, G)) != 0) { c->timing_suppress--; return rc; }
   if (!G.p.use_graph) {
     rc = mg_coarse_correction<VT>(c, G, 0);
   } else if (G.p.use_graph == 2) {   // one persistent cooperative kernel walks the recorded step list
@@ -778,6 +891,14 @@ int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out, bool x1_ready) 
   const MgParams& P = G.p;
   cudaStream_t st = c->stream;
   const int last = (int)G.lv.size() - 1;
+  if (l == G.tail_level && l > 0 && !G.rec && G.tail_len[0] > 0) {   // this level and everything below it: one single-CTA kernel
+    const int which = (b == L.b.p && out == L.sol.p) ? 0 : (b == L.b2.p && out == L.sol2.p) ? 1 : -1;
+    if (which >= 0) {
+      UFE_LAUNCH(c, TC_MG_COARSE);
+      k_mg_tail<VT><<<1, kTailBlock, 0, st>>>(reinterpret_cast<const MgStep*>(G.tail_prog.p) + G.tail_off[which], G.tail_len[which]);
+      return 0;
+    }
+  }
   double* xa = L.xa.p;
   double* xb = L.xb.p;
   if (l == last) {
@@ -939,6 +1060,11 @@ int mg_build(Ctx* c, Mg& G, const BlkMat& B, const Range& rb) {
       UFE_CUDA(cudaMemsetAsync(L.valf.p, 0, sizeof(float) * (size_t)L.n_slots * 4, c->stream));
     }
   }
+  // the first coarse level small enough for one CTA (never level 1: its right-hand side comes from the fine level / the all-reduce)
+  G.tail_level = 0;
+  if (const char* e = getenv("UFE_B200_MG_TAIL")) G.p.tail_max = atoi(e);
+  for (int l = 2; l < (int)G.lv.size() && G.p.tail_max > 0; ++l)
+    if (G.lv[l].n <= G.p.tail_max) { G.tail_level = l; break; }
   MgLevel& Lc = G.lv.back();
   G.dense_n = 0;
   if (Lc.n <= G.p.dense_max && 2 * (size_t)Lc.n * sizeof(double) <= 40 * 1024) {

@@ -68,7 +68,7 @@ struct Mg {
   void drop_graph() {
     if (graph_exec) cudaGraphExecDestroy(graph_exec);
     if (graph) cudaGraphDestroy(graph);
-    graph_exec = nullptr; graph = nullptr; graph_launches = 0; program_n = 0;
+    graph_exec = nullptr; graph = nullptr; graph_launches = 0; program_n = 0; tail_len[0] = tail_len[1] = 0;
   }
   std::vector<MgLevel> lv;
   DBuf<double> dense_w, dense_inv;        // Gauss-Jordan workspace [N][2N], inverse (column-major) [N][N]
@@ -84,6 +84,9 @@ struct Mg {
   std::vector<MgStep>* rec = nullptr;   // non-null while recording
   DBuf<char> program;
   int program_n = 0, program_grid = 0;
+  // the levels from tail_level down run as one single-CTA kernel per visit (mg.cu: k_mg_tail); two step lists: (b, sol) and (b2, sol2)
+  int tail_level = 0, tail_off[2] = {0, 0}, tail_len[2] = {0, 0};
+  DBuf<char> tail_prog;
   bool valid = false;
   long long gather_entries = 0;
   double setup_host_s = 0.0;

@@ -175,6 +175,9 @@ int ufe_b200_pc_step(ufe_b200_handle h, const ufe_b200_config* cfg, int approxim
   UFE_TRY(pc_state_ensure(c, dt_prev, false));
   PcState& P = *g_pc;
   P.dt_n = dt_prev > 0.0 ? dt_prev : dt;
+  // ufe_b200_set_state_resident: after the first call the solver state (u, v, basal velocities and stresses, eta_3D_b) stays on the device,
+  // like the reference's DIVA%... fields stay inside the solver object; `state` then only says which results come back
+  const bool keep_state = c->state_resident && c->vel->uploaded;
   const size_t nb_a = sizeof(double) * M.a.n_loc();
   {  // what the predictor needs, on the main stream
     UFE_REGION(c, TC_H2D);
@@ -188,12 +191,12 @@ int ufe_b200_pc_step(ufe_b200_handle h, const ufe_b200_config* cfg, int approxim
       UFE_CUDA(up(T.bc_Hi.p, io->BC_prescr_Hi));
       T.have_bc = true;
     } else T.have_bc = false;
-    UFE_TRY(velocity_upload(c, nullptr, state, VU_STATE_UV));
+    if (!keep_state) UFE_TRY(velocity_upload(c, nullptr, state, VU_STATE_UV));
   }
   {  // everything else the velocity solve needs, on the copy stream, while the predictor runs
     c->stream = c->copy_stream;
     int rc;
-    { UFE_REGION(c, TC_H2D); rc = velocity_upload(c, ice, state, VU_STATE_REST | VU_SKIP_GEOMETRY); }
+    { UFE_REGION(c, TC_H2D); rc = velocity_upload(c, ice, keep_state ? nullptr : state, VU_STATE_REST | VU_SKIP_GEOMETRY); }
     cudaError_t e = cudaEventRecord(c->ev_copy_a, c->copy_stream);
     c->stream = main_st;
     UFE_TRY(rc);
@@ -219,6 +222,13 @@ int ufe_b200_pc_step(ufe_b200_handle h, const ufe_b200_config* cfg, int approxim
   UFE_CUDA(cudaStreamSynchronize(main_st));
   UFE_CUDA(cudaStreamSynchronize(c->copy_stream));
   P.dt_n = dt;
+  return 0;
+}
+
+int ufe_b200_set_state_resident(ufe_b200_handle h, int on) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c, "NULL handle");
+  c->state_resident = on ? 1 : 0;
   return 0;
 }
 

@@ -598,12 +598,20 @@ static int solve_linear_system(Ctx* c, const ufe_b200_config* cfg, double rtol, 
 template <typename T>
 static int h2d_field(Ctx* c, T* d_ext, const Range& r, const T* h, int ncols = 1) {
   if (!h) return 0;
+  if (r.n_ext() == r.n_loc()) {   // no halo: one contiguous copy
+    UFE_CUDA(cudaMemcpyAsync(d_ext, h, sizeof(T) * (size_t)r.n_loc() * ncols, cudaMemcpyHostToDevice, c->stream));
+    return 0;
+  }
   UFE_CUDA(cudaMemcpy2DAsync(d_ext + r.off(), sizeof(T) * r.n_ext(), h, sizeof(T) * r.n_loc(), sizeof(T) * r.n_loc(), ncols,
                              cudaMemcpyHostToDevice, c->stream));
   return 0;
 }
 static int d2h_field(Ctx* c, double* h, const double* d_ext, const Range& r, int ncols = 1) {
   if (!h) return 0;
+  if (r.n_ext() == r.n_loc()) {
+    UFE_CUDA(cudaMemcpyAsync(h, d_ext, sizeof(double) * (size_t)r.n_loc() * ncols, cudaMemcpyDeviceToHost, c->stream));
+    return 0;
+  }
   UFE_CUDA(cudaMemcpy2DAsync(h, sizeof(double) * r.n_loc(), d_ext + r.off(), sizeof(double) * r.n_ext(), sizeof(double) * r.n_loc(), ncols,
                              cudaMemcpyDeviceToHost, c->stream));
   return 0;

@@ -167,6 +167,13 @@ module ufe_b200_mod
       integer(c_int) :: ierr
     end function
 
+    function c_ufe_b200_set_state_resident( h, on) bind(C, name='ufe_b200_set_state_resident') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: on
+      integer(c_int) :: ierr
+    end function
+
     ! calc_secondary_velocities (conservation_of_momentum_main.f90:177-246); out = c_loc of a ufe_b200_secondary_velocities
     function c_ufe_b200_calc_secondary_velocities( h, u_3D_b, v_3D_b, out) bind(C, name='ufe_b200_calc_secondary_velocities') result( ierr)
       import :: c_int, c_ptr
