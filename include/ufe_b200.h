@@ -139,6 +139,7 @@ typedef struct ufe_b200_mesh_desc {
   const int32_t* VE;     /* (nV,nC_mem)  */
   const int32_t* ETri;   /* (nE,2)       */
   const double* zeta;    /* (nz)         */
+  const double* Tricc;   /* (nTri,2) circumcentres = Voronoi vertices (mesh%Tricc); may be NULL unless ufe_b200_calc_grounded_fractions is used */
 } ufe_b200_mesh_desc;
 
 /* Upload the mesh (lifetime = lifetime of type_mesh; destroy on remesh, src/UFEMISM/main/UFEMISM_main_model.f90:1211).
@@ -332,6 +333,36 @@ typedef struct ufe_b200_vertical_velocity_io {
   double *w_3D, *dw_dz_3D;
 } ufe_b200_vertical_velocity_io;
 int ufe_b200_calc_vertical_velocities(ufe_b200_handle h, const ufe_b200_config* cfg, const ufe_b200_vertical_velocity_io* io);
+
+/* ---- geometry / mask / sub-grid stage between the thickness and velocity solves --------------------------------------------
+ * All fields are the rank's owned slices; logical masks travel as int32 (0/1), as everywhere in this ABI. */
+
+/* Replaces determine_masks( mesh, Hi, Hb, SL, mask, mask_icefree_land, ...) (src/UFEMISM/ice_dynamics/utilities/masks_mod.f90:25-217).
+ * `mask` holds C%type_icefree_land .. C%type_coastline = 1 .. 10 (model_configuration_type_and_namelist.f90:4526-4535).  NULL members are skipped. */
+typedef struct ufe_b200_masks {
+  int32_t *mask, *mask_icefree_land, *mask_icefree_ocean, *mask_grounded_ice, *mask_floating_ice, *mask_margin, *mask_gl_gr, *mask_gl_fl,
+          *mask_cf_gr, *mask_cf_fl, *mask_coastline;
+} ufe_b200_masks;
+int ufe_b200_determine_masks(ufe_b200_handle h, const ufe_b200_config* cfg, const double* Hi, const double* Hb, const double* SL,
+                             const ufe_b200_masks* out);
+
+/* Replaces calc_effective_thickness( mesh, Hi, Hb, SL, Hi_eff, fraction_margin) (utilities/subgrid_ice_margin.f90:19-158). */
+int ufe_b200_calc_effective_thickness(ufe_b200_handle h, const ufe_b200_config* cfg, const double* Hi, const double* Hb, const double* SL,
+                                      double* Hi_eff, double* fraction_margin);
+
+/* Replaces calc_grounded_fractions( mesh, Hi, Hb, SL, dHb, fraction_gr, fraction_gr_b, mask_floating_ice, bedrock_cdf, bedrock_cdf_b)
+ * (utilities/subgrid_grounded_fractions_main.f90:22-120 with ..._bilin_TAF.f90 and ..._bedrock_CDF.f90).  choice = C%choice_subgrid_grounded_fraction,
+ * nbins = C%subgrid_bedrock_cdf_nbins; bedrock_cdf (vi1:vi2,nbins), bedrock_cdf_b (ti1:ti2,nbins) may be NULL for UFE_GF_BILIN_INTERP_TAF. */
+enum { UFE_GF_BILIN_INTERP_TAF = 0, UFE_GF_BEDROCK_CDF = 1, UFE_GF_BILIN_INTERP_TAF_PLUS_BEDROCK_CDF = 2 };
+int ufe_b200_calc_grounded_fractions(ufe_b200_handle h, const ufe_b200_config* cfg, int choice, int nbins, const double* Hi, const double* Hb,
+                                     const double* SL, const double* dHb, const int32_t* mask_floating_ice, const double* bedrock_cdf,
+                                     const double* bedrock_cdf_b, double* fraction_gr, double* fraction_gr_b);
+
+/* Replace calc_critical_timestep_adv / _SIA( mesh, ice, dt_crit) (utilities/time_step_criteria.f90:80-141, 20-78); the result is the global
+ * minimum (the reference's MPI_ALLREDUCE( MPI_MIN)).  u_vav_b, v_vav_b NULL = the velocities of the last device solve. */
+int ufe_b200_calc_critical_timestep_adv(ufe_b200_handle h, const ufe_b200_config* cfg, int do_grounded_only_adv_dt, const double* Hi,
+                                        const int32_t* mask_floating_ice, const double* u_vav_b, const double* v_vav_b, double* dt_crit_adv);
+int ufe_b200_calc_critical_timestep_SIA(ufe_b200_handle h, const ufe_b200_config* cfg, const double* Hi, const double* D_3D_b, double* dt_crit_SIA);
 
 /* ---- timing hooks for bench.py (CUDA events on the library's own stream) ----------------------- */
 /* Milliseconds spent in the named kernel class since the last reset, and its launch count.

@@ -75,7 +75,7 @@ void* orc_mesh_create(const ufe_b200_mesh_desc* d) {
   m.xmin = d->xmin; m.xmax = d->xmax; m.ymin = d->ymin; m.ymax = d->ymax;
   m.V = d->V; m.nC = d->nC; m.C = d->C; m.niTri = d->niTri; m.iTri = d->iTri; m.VBI = d->VBI; m.Tri = d->Tri; m.TriC = d->TriC;
   m.TriBI = d->TriBI; m.TriGC = d->TriGC; m.A = d->A; m.Cw = d->Cw; m.D_x = d->D_x; m.D_y = d->D_y; m.D = d->D; m.VE = d->VE;
-  m.EV = nullptr; m.ETri = d->ETri; m.zeta = d->zeta;
+  m.EV = nullptr; m.ETri = d->ETri; m.zeta = d->zeta; m.Tricc = d->Tricc;
   return o;
 }
 void orc_mesh_destroy(void* h) { delete static_cast<OracleMesh*>(h); }
@@ -211,4 +211,35 @@ extern "C" void orc_calc_vertical_velocities(void* h, const ufe_b200_config* cfg
   VerticalVelocityIO V;
   std::memcpy(&V, io, sizeof(V));
   calc_vertical_velocities(o->mv, o->ops, to_config(cfg), V, u_3D_b, v_3D_b, u_3D, v_3D);
+}
+
+extern "C" void orc_determine_masks(void* h, const ufe_b200_config* cfg, const double* Hi, const double* Hb, const double* SL, const ufe_b200_masks* out) {
+  auto* o = static_cast<OracleMesh*>(h);
+  static_assert(sizeof(MaskSet) == sizeof(ufe_b200_masks), "same 11 pointers in the same order");
+  MaskSet M;
+  std::memcpy(&M, out, sizeof(M));
+  determine_masks(o->mv, to_config(cfg), Hi, Hb, SL, M);
+}
+extern "C" void orc_calc_effective_thickness(void* h, const ufe_b200_config* cfg, const double* Hi, const double* Hb, const double* SL, double* Hi_eff,
+                                             double* fraction_margin) {
+  auto* o = static_cast<OracleMesh*>(h);
+  calc_effective_thickness(o->mv, to_config(cfg), Hi, Hb, SL, Hi_eff, fraction_margin);
+}
+extern "C" int orc_calc_grounded_fractions(void* h, const ufe_b200_config* cfg, int choice, int nbins, const double* Hi, const double* Hb, const double* SL,
+                                           const double* dHb, const int* mask_floating_ice, const double* cdf, const double* cdf_b, double* fr,
+                                           double* fr_b) {
+  auto* o = static_cast<OracleMesh*>(h);
+  try {
+    calc_grounded_fractions(o->mv, o->ops, to_config(cfg), choice, nbins, Hi, Hb, SL, dHb, mask_floating_ice, cdf, cdf_b, fr, fr_b);
+  } catch (const std::exception&) { return 1; }
+  return 0;
+}
+extern "C" double orc_calc_critical_timestep_adv(void* h, const ufe_b200_config* cfg, int grounded_only, const double* Hi, const int* mask_floating_ice,
+                                                 const double* u_vav_b, const double* v_vav_b) {
+  auto* o = static_cast<OracleMesh*>(h);
+  return calc_critical_timestep_adv(o->mv, to_config(cfg), grounded_only, Hi, mask_floating_ice, u_vav_b, v_vav_b);
+}
+extern "C" double orc_calc_critical_timestep_SIA(void* h, const ufe_b200_config* cfg, const double* Hi, const double* D_3D_b) {
+  auto* o = static_cast<OracleMesh*>(h);
+  return calc_critical_timestep_SIA(o->mv, to_config(cfg), Hi, D_3D_b);
 }

@@ -44,6 +44,7 @@ struct MeshView {  // borrowed pointers to the Fortran arrays
   const int* Tri; const int* TriC; const int* TriBI; const double* TriGC;
   const double* A; const double* Cw; const double* D_x; const double* D_y; const double* D;
   const int* VE; const int* EV; const int* ETri; const double* zeta;
+  const double* Tricc = nullptr;   // (nTri,2) circumcentres (Voronoi vertices); only the grounded fractions need them
 };
 
 enum OpId {
@@ -150,6 +151,19 @@ struct SecondaryVelocities {
   double *u_surf, *v_surf, *u_base, *v_base, *u_vav, *v_vav, *uabs_surf, *uabs_base, *uabs_vav, *R_shear;           // (nV)
 };
 void calc_secondary_velocities(const MeshView& mesh, const Operators& ops, const double* u_3D_b, const double* v_3D_b, SecondaryVelocities& S);
+
+// --- geometry / mask / sub-grid stage between the device phases (geometry.cpp)
+struct MaskSet { int *mask, *icefree_land, *icefree_ocean, *grounded_ice, *floating_ice, *margin, *gl_gr, *gl_fl, *cf_gr, *cf_fl, *coastline; };
+enum GroundedFractionChoice { GF_bilin_interp_TAF = 0, GF_bedrock_CDF = 1, GF_bilin_interp_TAF_plus_bedrock_CDF = 2 };
+void determine_masks(const MeshView& mesh, const Config& C, const double* Hi, const double* Hb, const double* SL, const MaskSet& out);
+void calc_effective_thickness(const MeshView& mesh, const Config& C, const double* Hi, const double* Hb, const double* SL, double* Hi_eff,
+                              double* fraction_margin);
+void calc_grounded_fractions(const MeshView& mesh, const Operators& ops, const Config& C, int choice, int nbins, const double* Hi, const double* Hb,
+                             const double* SL, const double* dHb, const int* mask_floating_ice, const double* bedrock_cdf,
+                             const double* bedrock_cdf_b, double* fraction_gr, double* fraction_gr_b);
+double calc_critical_timestep_SIA(const MeshView& mesh, const Config& C, const double* Hi, const double* D_3D_b);
+double calc_critical_timestep_adv(const MeshView& mesh, const Config& C, int do_grounded_only_adv_dt, const double* Hi, const int* mask_floating_ice,
+                                  const double* u_vav_b, const double* v_vav_b);
 
 // --- vertical velocities (conservation_of_mass/vertical_velocities.f90:23-243); the zeta gradients follow zeta_gradients.f90:88-115
 struct VerticalVelocityIO {

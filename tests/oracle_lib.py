@@ -41,6 +41,14 @@ def lib():
         L.orc_solve_SIA.argtypes = [C.c_void_p, C.POINTER(ub.Config), C.c_double] + [dp] * 8
         L.orc_calc_secondary_velocities.argtypes = [C.c_void_p, dp, dp, C.POINTER(ub.SecondaryVelocities)]
         L.orc_calc_vertical_velocities.argtypes = [C.c_void_p, C.POINTER(ub.Config), C.POINTER(ub.VerticalVelocityIO), dp, dp, dp, dp]
+        PC = C.POINTER(ub.Config)
+        L.orc_determine_masks.argtypes = [C.c_void_p, PC, dp, dp, dp, C.POINTER(ub.Masks)]
+        L.orc_calc_effective_thickness.argtypes = [C.c_void_p, PC, dp, dp, dp, dp, dp]
+        L.orc_calc_grounded_fractions.argtypes = [C.c_void_p, PC, C.c_int, C.c_int, dp, dp, dp, dp, ip, dp, dp, dp, dp]
+        L.orc_calc_critical_timestep_adv.restype = C.c_double
+        L.orc_calc_critical_timestep_adv.argtypes = [C.c_void_p, PC, C.c_int, dp, ip, dp, dp]
+        L.orc_calc_critical_timestep_SIA.restype = C.c_double
+        L.orc_calc_critical_timestep_SIA.argtypes = [C.c_void_p, PC, dp, dp]
         _LIB = L
     return _LIB
 
@@ -132,6 +140,30 @@ class OracleMesh:
     def calc_vertical_velocities(self, cfg, io, u_3D_b, v_3D_b, u_3D, v_3D):
         self.calc_matrix_operators()
         lib().orc_calc_vertical_velocities(self.h, C.byref(cfg), C.byref(io), ub.dp(u_3D_b), ub.dp(v_3D_b), ub.dp(u_3D), ub.dp(v_3D))
+
+    def determine_masks(self, cfg, Hi, Hb, SL):
+        s, arrs = ub.alloc_masks(self.m.nV)
+        lib().orc_determine_masks(self.h, C.byref(cfg), ub.dp(Hi), ub.dp(Hb), ub.dp(SL), C.byref(s))
+        return arrs
+
+    def calc_effective_thickness(self, cfg, Hi, Hb, SL):
+        Hi_eff, fm = np.zeros(self.m.nV), np.zeros(self.m.nV)
+        lib().orc_calc_effective_thickness(self.h, C.byref(cfg), ub.dp(Hi), ub.dp(Hb), ub.dp(SL), ub.dp(Hi_eff), ub.dp(fm))
+        return Hi_eff, fm
+
+    def calc_grounded_fractions(self, cfg, choice, nbins, Hi, Hb, SL, dHb, mask_floating_ice, cdf, cdf_b):
+        self.calc_matrix_operators()
+        fr, fr_b = np.zeros(self.m.nV), np.zeros(self.m.nTri)
+        rc = lib().orc_calc_grounded_fractions(self.h, C.byref(cfg), choice, nbins, ub.dp(Hi), ub.dp(Hb), ub.dp(SL), ub.dp(dHb), ub.ip(mask_floating_ice),
+                                               ub.dp(cdf), ub.dp(cdf_b), ub.dp(fr), ub.dp(fr_b))
+        assert rc == 0
+        return fr, fr_b
+
+    def calc_critical_timestep_adv(self, cfg, grounded_only, Hi, mask_floating_ice, u_vav_b, v_vav_b):
+        return lib().orc_calc_critical_timestep_adv(self.h, C.byref(cfg), grounded_only, ub.dp(Hi), ub.ip(mask_floating_ice), ub.dp(u_vav_b), ub.dp(v_vav_b))
+
+    def calc_critical_timestep_SIA(self, cfg, Hi, D_3D_b):
+        return lib().orc_calc_critical_timestep_SIA(self.h, C.byref(cfg), ub.dp(Hi), ub.dp(D_3D_b))
 
     def flux_divergence_matrix(self, u_b, v_b, fraction_margin):
         m, nnz = C.c_int(), C.c_int()

@@ -97,6 +97,8 @@ struct Krylov;    // krylov.cuh
 struct Thickness; // thickness.cuh
 struct Secondary; // secondary.cu
 void secondary_free(Secondary* s);
+struct Geometry;  // geometry.cu
+void geometry_free(Geometry* g);
 
 // multigrid preconditioner knobs (mg.cuh); set through ufe_b200_set_mg_params
 struct MgParams {
@@ -141,6 +143,7 @@ struct Ctx {
   Krylov* krylov = nullptr;
   Thickness* thick = nullptr;
   Secondary* sec = nullptr;
+  Geometry* geo = nullptr;
   int state_resident = 0;        // ufe_b200_set_state_resident: ufe_b200_pc_step keeps the solver state on the device between calls
   MgParams mg_params;
   // pinned scratch for small D2H reads

@@ -1,0 +1,523 @@
+// Geometry / mask / sub-grid stage between the thickness and velocity solves, on the device.
+// Reference (src/UFEMISM/ice_dynamics/utilities/):
+//   determine_masks                               masks_mod.f90:25-217
+//   calc_effective_thickness                      subgrid_ice_margin.f90:19-158
+//   calc_grounded_fractions                       subgrid_grounded_fractions_main.f90:22-120
+//   ..._bilin_interp_TAF_{a,b}, calc_grounded_area_triangle*    subgrid_grounded_fractions_bilin_TAF.f90:20-369
+//   ..._bedrock_CDF_{a,b}                         subgrid_grounded_fractions_bedrock_CDF.f90:22-181
+//   calc_critical_timestep_{SIA,adv}              time_step_criteria.f90:20-141
+//   is_floating, thickness_above_floatation       src/UPSY/basic/math_utilities/ice_geometry_basics.f90:20-64
+// The reference gathers every field to every process (15 gather_to_all over these routines); here one halo exchange per field that a
+// neighbour stencil reads, and each routine is one or two passes over the vertices / triangles.
+#include "mesh.cuh"
+#include "velocity.cuh"
+
+namespace ufe {
+
+struct Geometry {
+  DBuf<double> a[8];       // vertex fields over the extended a range: Hi, Hb, SL, dHb, TAF, out0, out1, scratch
+  DBuf<double> b[3];       // triangle fields over the extended b range: TAF_b, fraction_gr_b, scratch
+  DBuf<int> ia[3];         // kind (1..4) / margin flag / floating flag over the extended a range
+  DBuf<int> masks;         // [11][n_loc] results of determine_masks
+  DBuf<double> cdf, cdf_b; // (n_loc, nbins)
+  DBuf<double> u, v;       // host-given velocities (extended b range)
+  DBuf<double> D3;         // SIA diffusivity (nz, extended b range)
+  DBuf<unsigned long long> dtbits;
+};
+void geometry_free(Geometry* g) { delete g; }
+
+namespace {
+
+struct GeoMesh {
+  int nV, nTri, nE, a_lo, b_lo, vi1, ti1;
+  const int *nC, *C, *niTri, *iTri, *VBI, *Tri, *TriBI, *VE, *ETri;
+  const double *V, *Tricc;
+};
+GeoMesh geo_mesh(const Mesh& M) {
+  return GeoMesh{M.nV, M.nTri, M.nE, M.a.lo, M.b.lo, M.a.i1, M.b.i1, M.nC.p, M.C.p, M.niTri.p, M.iTri.p, M.VBI.p, M.Tri.p, M.TriBI.p, M.VE.p,
+                 M.ETri.p, M.V.p, M.Tricc.p};
+}
+
+__device__ __forceinline__ bool is_floating(double rw_over_ri, double Hi, double Hb, double SL) { return Hi < (SL - Hb) * rw_over_ri; }
+
+// basic masks as one code per vertex: 1 ice-free land, 2 ice-free ocean, 3 grounded ice, 4 floating ice (masks_mod.f90:63-103), and the TAF
+__global__ void k_geo_kind(int n, int off, double rw_over_ri, const double* __restrict__ Hi, const double* __restrict__ Hb,
+                           const double* __restrict__ SL, int* __restrict__ kind, double* __restrict__ TAF) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const size_t i = off + r;
+    const bool fl = is_floating(rw_over_ri, Hi[i], Hb[i], SL[i]);
+    kind[i] = fl ? (Hi[i] > 0.0 ? 4 : 2) : (Hi[i] > 0.0 ? 3 : 1);
+    if (TAF) TAF[i] = Hi[i] - fmax(0.0, (SL[i] - Hb[i]) * rw_over_ri);
+  }
+}
+
+// transitional masks (masks_mod.f90:121-203); out = [11][n]: mask, land, ocean, grounded, floating, margin, gl_gr, gl_fl, cf_gr, cf_fl, coastline
+__global__ void k_geo_masks(GeoMesh m, int n, int off, const int* __restrict__ kind, int* __restrict__ out) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const int vi = m.vi1 + (int)r;
+    const int k = kind[off + r];
+    bool nb_noice = false, nb_fl = false, nb_gr = false, nb_oc = false;
+    for (int ci = 0; ci < m.nC[vi - 1]; ++ci) {
+      const int kj = kind[m.C[(size_t)ci * m.nV + vi - 1] - m.a_lo];
+      nb_noice |= kj <= 2; nb_fl |= kj == 4; nb_gr |= kj == 3; nb_oc |= kj == 2;
+    }
+    const bool margin = k >= 3 && nb_noice, gl_gr = k == 3 && nb_fl, gl_fl = k == 4 && nb_gr, cf_gr = k == 3 && nb_oc, cf_fl = k == 4 && nb_oc,
+               coast = k == 1 && nb_oc;
+    int mask = k;                          // the reference overwrites in this order, so the last true test wins
+    if (margin) mask = 9;
+    if (gl_gr) mask = 5;
+    if (gl_fl) mask = 6;
+    if (cf_gr) mask = 7;
+    if (cf_fl) mask = 8;
+    if (coast) mask = 10;
+    const int v[11] = {mask, k == 1, k == 2, k == 3, k == 4, margin, gl_gr, gl_fl, cf_gr, cf_fl, coast};
+#pragma unroll
+    for (int q = 0; q < 11; ++q) out[(size_t)q * n + r] = v[q];
+  }
+}
+
+// calc_effective_thickness, first pass: margin flag (subgrid_ice_margin.f90:53-61)
+__global__ void k_geo_margin(GeoMesh m, int n, int off, const double* __restrict__ Hi, int* __restrict__ margin) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const int vi = m.vi1 + (int)r;
+    bool mg = false;
+    if (Hi[off + r] > 0.0)
+      for (int ci = 0; ci < m.nC[vi - 1]; ++ci) mg |= Hi[m.C[(size_t)ci * m.nV + vi - 1] - m.a_lo] == 0.0;
+    margin[off + r] = mg;
+  }
+}
+// second pass (:87-146)
+__global__ void k_geo_hi_eff(GeoMesh m, int n, int off, double rw_over_ri, const double* __restrict__ Hi, const double* __restrict__ Hb,
+                             const double* __restrict__ SL, const int* __restrict__ margin, double* __restrict__ Hi_eff,
+                             double* __restrict__ fraction_margin) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const int vi = m.vi1 + (int)r;
+    const size_t i = off + r;
+    const double H = Hi[i];
+    const bool fl = is_floating(rw_over_ri, H, Hb[i], SL[i]);
+    double he = H, fm = 1.0;
+    if (fl && !(H > 0.0)) { he = 0.0; fm = 0.0; }
+    if (margin[i] && fl) {
+      double hmax = 0.0;
+      for (int ci = 0; ci < m.nC[vi - 1]; ++ci) {
+        const int j = m.C[(size_t)ci * m.nV + vi - 1] - m.a_lo;
+        if (!margin[j]) hmax = fmax(hmax, Hi[j]);
+      }
+      if (hmax > H) { he = hmax; fm = H / hmax; }
+    }
+    Hi_eff[i] = he; fraction_margin[i] = fm;
+  }
+}
+
+struct P2 { double x, y; };
+__device__ __forceinline__ double tri_area(P2 p, P2 q, P2 r) { return fabs((q.x - p.x) * (r.y - p.y) - (q.y - p.y) * (r.x - p.x)) / 2.0; }
+__device__ __forceinline__ double corner_area(P2 va, P2 vb, P2 vc, double ta, double tb, double tc) {
+  const double lab = ta / (ta - tb), lac = ta / (ta - tc);
+  const P2 pab{(va.x * (1.0 - lab)) + (vb.x * lab), (va.y * (1.0 - lab)) + (vb.y * lab)};
+  const P2 pac{(va.x * (1.0 - lac)) + (vc.x * lac), (va.y * (1.0 - lac)) + (vc.y * lac)};
+  return tri_area(va, pab, pac);
+}
+// calc_grounded_area_triangle (bilin_TAF.f90:244-321)
+__device__ void grounded_area(P2 va, P2 vb, P2 vc, double TAFa, double TAFb, double TAFc, double& A_tot, double& A_grnd) {
+  const double tol = 1e-9;
+  A_tot = tri_area(va, vb, vc);
+  const double a = TAFa >= 0.0 ? fmax(tol, TAFa) : fmin(-tol, TAFa);
+  const double b = TAFb >= 0.0 ? fmax(tol, TAFb) : fmin(-tol, TAFb);
+  const double c = TAFc >= 0.0 ? fmax(tol, TAFc) : fmin(-tol, TAFc);
+  if (a >= 0 && b >= 0 && c >= 0) A_grnd = A_tot;
+  else if (a <= 0 && b <= 0 && c <= 0) A_grnd = 0.0;
+  else if (a >= 0 && b <= 0 && c <= 0) A_grnd = corner_area(va, vb, vc, a, b, c);
+  else if (a <= 0 && b >= 0 && c <= 0) A_grnd = corner_area(vb, vc, va, b, c, a);
+  else if (a <= 0 && b <= 0 && c >= 0) A_grnd = corner_area(vc, va, vb, c, a, b);
+  else if (a <= 0 && b >= 0 && c >= 0) A_grnd = A_tot - corner_area(va, vb, vc, a, b, c);
+  else if (a >= 0 && b <= 0 && c >= 0) A_grnd = A_tot - corner_area(vb, vc, va, b, c, a);
+  else A_grnd = A_tot - corner_area(vc, va, vb, c, a, b);
+}
+__device__ __forceinline__ P2 vert(const GeoMesh& m, int vi) { return P2{m.V[vi - 1], m.V[(size_t)m.nV + vi - 1]}; }
+__device__ __forceinline__ P2 tricc(const GeoMesh& m, int ti) { return P2{m.Tricc[ti - 1], m.Tricc[(size_t)m.nTri + ti - 1]}; }
+
+// bedrock CDF lookup (bedrock_CDF.f90:49-81); cdf[(bin) * stride]
+__device__ double cdf_fraction(const double* __restrict__ cdf, size_t stride, int nbins, double Hb_float) {
+  if (Hb_float <= cdf[0]) return 1.0;
+  if (Hb_float >= cdf[(size_t)(nbins - 1) * stride]) return 0.0;
+  int iu = 1;
+  while (cdf[(size_t)(iu - 1) * stride] < Hb_float) iu = iu + 1;
+  const int il = iu - 1;
+  const double cu = cdf[(size_t)(iu - 1) * stride], cl = cdf[(size_t)(il - 1) * stride];
+  const double wl = (cu - Hb_float) / (cu - cl), wu = 1.0 - wl;
+  const double f = 1.0 - ((double)(il - 1) * wl + (double)(iu - 1) * wu) / (double)(nbins - 1);
+  return fmin(1.0, fmax(0.0, f));
+}
+
+// triangles: TAF_b = map_a_b TAF (for the vertex pass), the TAF fraction of the triangle itself, the CDF fraction, and their combination
+__global__ void k_geo_frac_b(GeoMesh m, int n, int off, int choice, int nbins, double ri_over_rw, const int* __restrict__ ptr,
+                             const int* __restrict__ ind, const double* __restrict__ w_map, const double* __restrict__ TAF,
+                             const double* __restrict__ Hi, const double* __restrict__ SL, const double* __restrict__ dHb,
+                             const int* __restrict__ kind, const double* __restrict__ cdf_b, double* __restrict__ TAF_b,
+                             double* __restrict__ fraction_gr_b) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const int ti = m.ti1 + (int)r;
+    double tb = 0.0, Hi_b = 0.0, SL_b = 0.0, dHb_b = 0.0;
+    for (int k = ptr[r]; k < ptr[r + 1]; ++k) {
+      const int j = ind[k];
+      const double wk = w_map[k];
+      tb += wk * TAF[j];
+      if (choice != UFE_GF_BILIN_INTERP_TAF) { Hi_b += wk * Hi[j]; SL_b += wk * SL[j]; dHb_b += wk * dHb[j]; }
+    }
+    TAF_b[off + r] = tb;
+    const int via = m.Tri[ti - 1], vib = m.Tri[(size_t)m.nTri + ti - 1], vic = m.Tri[2 * (size_t)m.nTri + ti - 1];
+    const double a = TAF[via - m.a_lo], b = TAF[vib - m.a_lo], c = TAF[vic - m.a_lo];
+    double f_taf = 0.0, f_cdf = 0.0;
+    if (choice != UFE_GF_BEDROCK_CDF) {
+      const double tmax = fmax(a, fmax(b, c)), tmin = fmin(a, fmin(b, c));
+      if (tmin >= 0.0) f_taf = 1.0;
+      else if (tmax <= 0.0) f_taf = 0.0;
+      else {
+        double At, Ag;
+        grounded_area(vert(m, via), vert(m, vib), vert(m, vic), a, b, c, At, Ag);
+        f_taf = fmin(1.0, fmax(0.0, Ag / At));
+      }
+    }
+    if (choice != UFE_GF_BILIN_INTERP_TAF) {
+      if (m.TriBI[ti - 1] > 0) f_cdf = (a > 0.0 || b > 0.0 || c > 0.0) ? 1.0 : 0.0;
+      else f_cdf = cdf_fraction(cdf_b + r, (size_t)n, nbins, SL_b - Hi_b * ri_over_rw - dHb_b);
+    }
+    double f = f_taf;
+    if (choice == UFE_GF_BEDROCK_CDF) f = f_cdf;
+    else if (choice == UFE_GF_BILIN_INTERP_TAF_PLUS_BEDROCK_CDF) {
+      const bool gl = kind[via - m.a_lo] == 4 || kind[vib - m.a_lo] == 4 || kind[vic - m.a_lo] == 4;   // mask_floating_ice of a corner
+      f = gl ? f_taf : f_cdf;
+    }
+    fraction_gr_b[off + r] = f;
+  }
+}
+
+// vertices: TAF fraction of the Voronoi cell (bilin_TAF.f90:49-168), CDF fraction, combination (main.f90:76-88)
+__global__ void k_geo_frac_a(GeoMesh m, int n, int off, int choice, int nbins, double ri_over_rw, const double* __restrict__ TAF,
+                             const double* __restrict__ TAF_b, const double* __restrict__ Hi, const double* __restrict__ SL,
+                             const double* __restrict__ dHb, const double* __restrict__ cdf, double* __restrict__ fraction_gr) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const int vi = m.vi1 + (int)r;
+    const size_t i = off + r;
+    double f_taf = 0.0, f_cdf = 0.0;
+    if (choice != UFE_GF_BEDROCK_CDF) {
+      const double TAFa = TAF[i];
+      double tmax = fmax(-1e6, TAFa), tmin = fmin(1e6, TAFa);
+      const int nc = m.nC[vi - 1];
+      for (int ci = 0; ci < nc; ++ci) {
+        const double t = TAF[m.C[(size_t)ci * m.nV + vi - 1] - m.a_lo];
+        tmax = fmax(tmax, t); tmin = fmin(tmin, t);
+      }
+      if (tmin >= 0.0) f_taf = 1.0;
+      else if (tmax <= 0.0) f_taf = 0.0;
+      else {
+        double A_vor = 0.0, A_grnd = 0.0, At, Ag;
+        const P2 va = vert(m, vi);
+        const int nt = m.niTri[vi - 1];
+        auto itri = [&](int k) { return m.iTri[(size_t)k * m.nV + vi - 1]; };
+        if (m.VBI[vi - 1] == 0) {
+          for (int k1 = 0; k1 < nt; ++k1) {
+            const int t1 = itri(k1), t2 = itri(k1 + 1 == nt ? 0 : k1 + 1);
+            grounded_area(va, tricc(m, t1), tricc(m, t2), TAFa, TAF_b[t1 - m.b_lo], TAF_b[t2 - m.b_lo], At, Ag);
+            A_vor = A_vor + At; A_grnd = A_grnd + Ag;
+          }
+        } else {
+          int vj = m.C[vi - 1];
+          P2 pj = vert(m, vj);
+          int t = itri(0);
+          grounded_area(va, P2{0.5 * (va.x + pj.x), 0.5 * (va.y + pj.y)}, tricc(m, t), TAFa, 0.5 * (TAFa + TAF[vj - m.a_lo]), TAF_b[t - m.b_lo], At, Ag);
+          A_vor = A_vor + At; A_grnd = A_grnd + Ag;
+          for (int k1 = 0; k1 < nt - 1; ++k1) {
+            const int t1 = itri(k1), t2 = itri(k1 + 1);
+            grounded_area(va, tricc(m, t1), tricc(m, t2), TAFa, TAF_b[t1 - m.b_lo], TAF_b[t2 - m.b_lo], At, Ag);
+            A_vor = A_vor + At; A_grnd = A_grnd + Ag;
+          }
+          t = itri(nt - 1);
+          vj = m.C[(size_t)(nc - 1) * m.nV + vi - 1];
+          pj = vert(m, vj);
+          grounded_area(va, tricc(m, t), P2{0.5 * (va.x + pj.x), 0.5 * (va.y + pj.y)}, TAFa, TAF_b[t - m.b_lo], 0.5 * (TAFa + TAF[vj - m.a_lo]), At, Ag);
+          A_vor = A_vor + At; A_grnd = A_grnd + Ag;
+        }
+        f_taf = fmin(1.0, fmax(0.0, A_grnd / A_vor));
+      }
+    }
+    if (choice != UFE_GF_BILIN_INTERP_TAF) f_cdf = cdf_fraction(cdf + r, (size_t)n, nbins, SL[i] - Hi[i] * ri_over_rw - dHb[i]);
+    fraction_gr[i] = choice == UFE_GF_BILIN_INTERP_TAF ? f_taf : choice == UFE_GF_BEDROCK_CDF ? f_cdf : fmin(f_taf, f_cdf);
+  }
+}
+
+__device__ __forceinline__ void block_min_to(double v, unsigned long long* dtbits) {
+  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+  if ((threadIdx.x & 31) == 0) atomicMin(dtbits, (unsigned long long)__double_as_longlong(v));   // v > 0: bit order = value order
+}
+
+// calc_critical_timestep_adv (time_step_criteria.f90:113-131): every edge is seen from the vertex (or two) that owns an end of it
+__global__ void k_geo_dt_adv(GeoMesh m, int n, int off, int grounded_only, double dt_max, const double* __restrict__ Hi, const int* __restrict__ fl,
+                             const double* __restrict__ u_b, const double* __restrict__ v_b, unsigned long long* dtbits) {
+  double best = dt_max;
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const int vi = m.vi1 + (int)r;
+    if (Hi[off + r] == 0.0 || (grounded_only && fl[off + r])) continue;
+    const P2 pi = vert(m, vi);
+    for (int ci = 0; ci < m.nC[vi - 1]; ++ci) {
+      const size_t k = (size_t)ci * m.nV + vi - 1;
+      const int vj = m.C[k], ei = m.VE[k];
+      if (Hi[vj - m.a_lo] == 0.0 || (grounded_only && fl[vj - m.a_lo])) continue;
+      const int til = m.ETri[ei - 1], tir = m.ETri[(size_t)m.nE + ei - 1];
+      double uc, vc;
+      if (til == 0) { uc = u_b[tir - m.b_lo]; vc = v_b[tir - m.b_lo]; }
+      else if (tir == 0) { uc = u_b[til - m.b_lo]; vc = v_b[til - m.b_lo]; }
+      else { uc = (u_b[til - m.b_lo] + u_b[tir - m.b_lo]) / 2.0; vc = (v_b[til - m.b_lo] + v_b[tir - m.b_lo]) / 2.0; }
+      const P2 pj = vert(m, vj);
+      const double dx = pi.x - pj.x, dy = pi.y - pj.y;
+      best = fmin(best, sqrt(dx * dx + dy * dy) / fmax(0.1, fabs(uc) + fabs(vc)) * 0.9);
+    }
+  }
+  block_min_to(best, dtbits);
+}
+
+// calc_critical_timestep_SIA (:46-72)
+__global__ void k_geo_dt_sia(GeoMesh m, int n, int off, int nb_ext, int nz, double dt_max, const double* __restrict__ Hi, const double* __restrict__ D_3D_b,
+                             unsigned long long* dtbits) {
+  double best = dt_max;
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const int ti = m.ti1 + (int)r;
+    const int via = m.Tri[ti - 1], vib = m.Tri[(size_t)m.nTri + ti - 1], vic = m.Tri[2 * (size_t)m.nTri + ti - 1];
+    const P2 a = vert(m, via), b = vert(m, vib), c = vert(m, vic);
+    auto dist = [](P2 p, P2 q) { return sqrt((q.x - p.x) * (q.x - p.x) + (q.y - p.y) * (q.y - p.y)); };
+    const double d_min = fmin(dist(a, b), fmin(dist(b, c), dist(c, a)));
+    double Dm = 0.0;
+    for (int k = 0; k < nz; ++k) Dm = fmax(Dm, fabs(D_3D_b[(size_t)k * nb_ext + off + r]));
+    const double H = fmax(fmax(0.1, Hi[via - m.a_lo]), fmax(Hi[vib - m.a_lo], Hi[vic - m.a_lo]));
+    best = fmin(best, d_min * d_min / (6.0 * H * fmax(1e2, Dm)) * 0.9);
+  }
+  block_min_to(best, dtbits);
+}
+
+int ensure_geometry(Ctx* c) {
+  UFE_CHECK(c->mesh && c->mesh->have_ops, "the geometry stage needs the mesh and its operators (ufe_b200_calc_matrix_operators)");
+  Mesh& M = *c->mesh;
+  if (!c->geo) c->geo = new Geometry();
+  Geometry& G = *c->geo;
+  for (auto& x : G.a) UFE_TRY(x.alloc(M.a.n_ext()));
+  for (auto& x : G.b) UFE_TRY(x.alloc(M.b.n_ext()));
+  for (auto& x : G.ia) UFE_TRY(x.alloc(M.a.n_ext()));
+  UFE_TRY(G.masks.alloc((size_t)11 * M.a.n_loc()));
+  UFE_TRY(G.dtbits.alloc(1));
+  return 0;
+}
+
+int up_a(Ctx* c, double* d, const double* h) {
+  Mesh& M = *c->mesh;
+  UFE_CUDA(cudaMemcpyAsync(d + M.a.off(), h, sizeof(double) * M.a.n_loc(), cudaMemcpyHostToDevice, c->stream));
+  return 0;
+}
+int down_a(Ctx* c, double* h, const double* d) {
+  Mesh& M = *c->mesh;
+  if (h) UFE_CUDA(cudaMemcpyAsync(h, d + M.a.off(), sizeof(double) * M.a.n_loc(), cudaMemcpyDeviceToHost, c->stream));
+  return 0;
+}
+
+int finish_dt(Ctx* c, Geometry& G, double dt_ice_max, double* out) {
+  cudaStream_t st = c->stream;
+  unsigned long long bits = 0;
+  UFE_CUDA(cudaMemcpyAsync(&bits, G.dtbits.p, sizeof(bits), cudaMemcpyDeviceToHost, st));
+  UFE_CUDA(cudaStreamSynchronize(st));
+  double dt = __builtin_bit_cast(double, bits);
+  if (c->nranks > 1) {   // MPI_ALLREDUCE( ..., MPI_MIN, ...) (time_step_criteria.f90:74,133)
+    UFE_CUDA(cudaMemcpyAsync(G.a[7].p, &dt, sizeof(double), cudaMemcpyHostToDevice, st));
+    UFE_TRY(allreduce_min(c, G.a[7].p, 1));
+    UFE_CUDA(cudaMemcpyAsync(&dt, G.a[7].p, sizeof(double), cudaMemcpyDeviceToHost, st));
+    UFE_CUDA(cudaStreamSynchronize(st));
+  }
+  *out = dt < dt_ice_max ? dt : dt_ice_max;
+  return 0;
+}
+
+}  // namespace
+
+}  // namespace ufe
+
+using namespace ufe;
+
+extern "C" {
+
+int ufe_b200_determine_masks(ufe_b200_handle h, const ufe_b200_config* cfg, const double* Hi, const double* Hb, const double* SL,
+                             const ufe_b200_masks* out) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && cfg && Hi && Hb && SL && out, "ufe_b200_determine_masks: NULL argument");
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_TRY(ensure_geometry(c));
+  Mesh& M = *c->mesh; Geometry& G = *c->geo;
+  cudaStream_t st = c->stream;
+  const int na = M.a.n_loc(), off = M.a.off();
+  { UFE_REGION(c, TC_H2D); UFE_TRY(up_a(c, G.a[0].p, Hi)); UFE_TRY(up_a(c, G.a[1].p, Hb)); UFE_TRY(up_a(c, G.a[2].p, SL)); }
+  const GeoMesh m = geo_mesh(M);
+  const int grid = grid_for(c, na, 128, 16);
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_kind<<<grid, 128, 0, st>>>(na, off, cfg->seawater_density / cfg->ice_density, G.a[0].p, G.a[1].p, G.a[2].p, G.ia[0].p, nullptr); }
+  UFE_TRY(halo_exchange_int(c, M.a, G.ia[0].p));
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_masks<<<grid, 128, 0, st>>>(m, na, off, G.ia[0].p, G.masks.p); }
+  UFE_CUDA(cudaGetLastError());
+  {
+    UFE_REGION(c, TC_D2H);
+    int32_t* const dst[11] = {out->mask, out->mask_icefree_land, out->mask_icefree_ocean, out->mask_grounded_ice, out->mask_floating_ice, out->mask_margin,
+                              out->mask_gl_gr, out->mask_gl_fl, out->mask_cf_gr, out->mask_cf_fl, out->mask_coastline};
+    for (int q = 0; q < 11; ++q)
+      if (dst[q]) UFE_CUDA(cudaMemcpyAsync(dst[q], G.masks.p + (size_t)q * na, sizeof(int) * na, cudaMemcpyDeviceToHost, st));
+  }
+  UFE_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int ufe_b200_calc_effective_thickness(ufe_b200_handle h, const ufe_b200_config* cfg, const double* Hi, const double* Hb, const double* SL,
+                                      double* Hi_eff, double* fraction_margin) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && cfg && Hi && Hb && SL && Hi_eff && fraction_margin, "ufe_b200_calc_effective_thickness: NULL argument");
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_TRY(ensure_geometry(c));
+  Mesh& M = *c->mesh; Geometry& G = *c->geo;
+  cudaStream_t st = c->stream;
+  const int na = M.a.n_loc(), off = M.a.off();
+  { UFE_REGION(c, TC_H2D); UFE_TRY(up_a(c, G.a[0].p, Hi)); UFE_TRY(up_a(c, G.a[1].p, Hb)); UFE_TRY(up_a(c, G.a[2].p, SL)); }
+  UFE_TRY(halo_exchange(c, M.a, G.a[0].p));
+  const GeoMesh m = geo_mesh(M);
+  const int grid = grid_for(c, na, 128, 16);
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_margin<<<grid, 128, 0, st>>>(m, na, off, G.a[0].p, G.ia[1].p); }
+  UFE_TRY(halo_exchange_int(c, M.a, G.ia[1].p));
+  {
+    UFE_LAUNCH(c, TC_COLUMN);
+    k_geo_hi_eff<<<grid, 128, 0, st>>>(m, na, off, cfg->seawater_density / cfg->ice_density, G.a[0].p, G.a[1].p, G.a[2].p, G.ia[1].p, G.a[5].p, G.a[6].p);
+  }
+  UFE_CUDA(cudaGetLastError());
+  { UFE_REGION(c, TC_D2H); UFE_TRY(down_a(c, Hi_eff, G.a[5].p)); UFE_TRY(down_a(c, fraction_margin, G.a[6].p)); }
+  UFE_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int ufe_b200_calc_grounded_fractions(ufe_b200_handle h, const ufe_b200_config* cfg, int choice, int nbins, const double* Hi, const double* Hb,
+                                     const double* SL, const double* dHb, const int32_t* mask_floating_ice, const double* bedrock_cdf,
+                                     const double* bedrock_cdf_b, double* fraction_gr, double* fraction_gr_b) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && cfg && Hi && Hb && SL && fraction_gr && fraction_gr_b, "ufe_b200_calc_grounded_fractions: NULL argument");
+  UFE_CHECK(choice >= UFE_GF_BILIN_INTERP_TAF && choice <= UFE_GF_BILIN_INTERP_TAF_PLUS_BEDROCK_CDF,
+            "unknown choice_subgrid_grounded_fraction %d", choice);                                        // main.f90:58-60
+  const bool need_cdf = choice != UFE_GF_BILIN_INTERP_TAF;
+  UFE_CHECK(!need_cdf || (dHb && bedrock_cdf && bedrock_cdf_b && nbins >= 2), "ufe_b200_calc_grounded_fractions: the bedrock CDFs and dHb are required");
+  UFE_CHECK(choice != UFE_GF_BILIN_INTERP_TAF_PLUS_BEDROCK_CDF || mask_floating_ice, "ufe_b200_calc_grounded_fractions: mask_floating_ice is required");
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_TRY(ensure_geometry(c));
+  Mesh& M = *c->mesh; Geometry& G = *c->geo;
+  UFE_CHECK(choice == UFE_GF_BEDROCK_CDF || M.Tricc.p, "ufe_b200_calc_grounded_fractions: bilin_interp_TAF needs mesh%%Tricc (ufe_b200_mesh_desc.Tricc)");
+  cudaStream_t st = c->stream;
+  const int na = M.a.n_loc(), nb = M.b.n_loc(), off = M.a.off();
+  {
+    UFE_REGION(c, TC_H2D);
+    UFE_TRY(up_a(c, G.a[0].p, Hi)); UFE_TRY(up_a(c, G.a[1].p, Hb)); UFE_TRY(up_a(c, G.a[2].p, SL));
+    if (need_cdf) {
+      UFE_TRY(up_a(c, G.a[3].p, dHb));
+      UFE_TRY(G.cdf.alloc((size_t)na * nbins)); UFE_TRY(G.cdf_b.alloc((size_t)nb * nbins));
+      UFE_CUDA(cudaMemcpyAsync(G.cdf.p, bedrock_cdf, sizeof(double) * na * nbins, cudaMemcpyHostToDevice, st));
+      UFE_CUDA(cudaMemcpyAsync(G.cdf_b.p, bedrock_cdf_b, sizeof(double) * nb * nbins, cudaMemcpyHostToDevice, st));
+    }
+  }
+  const GeoMesh m = geo_mesh(M);
+  const double rw_ri = cfg->seawater_density / cfg->ice_density, ri_rw = cfg->ice_density / cfg->seawater_density;
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_kind<<<grid_for(c, na, 128, 16), 128, 0, st>>>(na, off, rw_ri, G.a[0].p, G.a[1].p, G.a[2].p, G.ia[0].p, G.a[4].p); }
+  if (mask_floating_ice && choice == UFE_GF_BILIN_INTERP_TAF_PLUS_BEDROCK_CDF) {
+    // the caller's mask decides which triangles touch the grounding line (main.f90:91-104); 4 = floating ice, 0 = anything else
+    std::vector<int> k(na);
+    for (int i = 0; i < na; ++i) k[i] = mask_floating_ice[i] ? 4 : 0;
+    UFE_CUDA(cudaMemcpyAsync(G.ia[0].p + off, k.data(), sizeof(int) * na, cudaMemcpyHostToDevice, st));
+    UFE_CUDA(cudaStreamSynchronize(st));
+  }
+  UFE_TRY(halo_exchange(c, M.a, G.a[4].p)); UFE_TRY(halo_exchange_int(c, M.a, G.ia[0].p));
+  if (need_cdf) { UFE_TRY(halo_exchange(c, M.a, G.a[0].p)); UFE_TRY(halo_exchange(c, M.a, G.a[2].p)); UFE_TRY(halo_exchange(c, M.a, G.a[3].p)); }
+  const Mesh::OpGroup& gab = M.grp[Mesh::G_AB];
+  {
+    UFE_LAUNCH(c, TC_TRI);
+    k_geo_frac_b<<<grid_for(c, nb, 128, 16), 128, 0, st>>>(m, nb, M.b.off(), choice, nbins, ri_rw, gab.ptr.p, gab.ind.p, gab.val[0].p, G.a[4].p, G.a[0].p,
+                                                            G.a[2].p, G.a[3].p, G.ia[0].p, G.cdf_b.p, G.b[0].p, G.b[1].p);
+  }
+  UFE_TRY(halo_exchange(c, M.b, G.b[0].p));
+  {
+    UFE_LAUNCH(c, TC_COLUMN);
+    k_geo_frac_a<<<grid_for(c, na, 128, 16), 128, 0, st>>>(m, na, off, choice, nbins, ri_rw, G.a[4].p, G.b[0].p, G.a[0].p, G.a[2].p, G.a[3].p, G.cdf.p,
+                                                            G.a[5].p);
+  }
+  UFE_CUDA(cudaGetLastError());
+  {
+    UFE_REGION(c, TC_D2H);
+    UFE_TRY(down_a(c, fraction_gr, G.a[5].p));
+    UFE_CUDA(cudaMemcpyAsync(fraction_gr_b, G.b[1].p + M.b.off(), sizeof(double) * nb, cudaMemcpyDeviceToHost, st));
+  }
+  UFE_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int ufe_b200_calc_critical_timestep_adv(ufe_b200_handle h, const ufe_b200_config* cfg, int do_grounded_only_adv_dt, const double* Hi,
+                                        const int32_t* mask_floating_ice, const double* u_vav_b, const double* v_vav_b, double* dt_crit_adv) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && cfg && Hi && dt_crit_adv, "ufe_b200_calc_critical_timestep_adv: NULL argument");
+  UFE_CHECK(!do_grounded_only_adv_dt || mask_floating_ice, "ufe_b200_calc_critical_timestep_adv: mask_floating_ice is required");
+  UFE_CHECK((u_vav_b == nullptr) == (v_vav_b == nullptr), "ufe_b200_calc_critical_timestep_adv: give both velocities or neither");
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_TRY(ensure_geometry(c));
+  Mesh& M = *c->mesh; Geometry& G = *c->geo;
+  cudaStream_t st = c->stream;
+  const int na = M.a.n_loc(), nb = M.b.n_loc();
+  const double* d_u; const double* d_v;
+  {
+    UFE_REGION(c, TC_H2D);
+    UFE_TRY(up_a(c, G.a[0].p, Hi));
+    if (mask_floating_ice) UFE_CUDA(cudaMemcpyAsync(G.ia[2].p + M.a.off(), mask_floating_ice, sizeof(int) * na, cudaMemcpyHostToDevice, st));
+    else UFE_CUDA(cudaMemsetAsync(G.ia[2].p, 0, sizeof(int) * M.a.n_ext(), st));
+    if (u_vav_b) {
+      UFE_TRY(G.u.alloc(M.b.n_ext())); UFE_TRY(G.v.alloc(M.b.n_ext()));
+      UFE_CUDA(cudaMemcpyAsync(G.u.p + M.b.off(), u_vav_b, sizeof(double) * nb, cudaMemcpyHostToDevice, st));
+      UFE_CUDA(cudaMemcpyAsync(G.v.p + M.b.off(), v_vav_b, sizeof(double) * nb, cudaMemcpyHostToDevice, st));
+      d_u = G.u.p; d_v = G.v.p;
+    } else {
+      UFE_CHECK(c->vel && c->vel->uploaded, "ufe_b200_calc_critical_timestep_adv: no velocities given and none resident on the device");
+      d_u = c->vel->u.p; d_v = c->vel->v.p;
+    }
+  }
+  UFE_TRY(halo_exchange(c, M.a, G.a[0].p)); UFE_TRY(halo_exchange_int(c, M.a, G.ia[2].p));
+  UFE_TRY(halo_exchange(c, M.b, const_cast<double*>(d_u))); UFE_TRY(halo_exchange(c, M.b, const_cast<double*>(d_v)));
+  const unsigned long long init = (unsigned long long)__builtin_bit_cast(long long, cfg->dt_ice_max);
+  UFE_CUDA(cudaMemcpyAsync(G.dtbits.p, &init, sizeof(init), cudaMemcpyHostToDevice, st));
+  {
+    UFE_LAUNCH(c, TC_COLUMN);
+    k_geo_dt_adv<<<grid_for(c, na, 128, 16), 128, 0, st>>>(geo_mesh(M), na, M.a.off(), do_grounded_only_adv_dt, cfg->dt_ice_max, G.a[0].p, G.ia[2].p, d_u, d_v,
+                                                            G.dtbits.p);
+  }
+  UFE_CUDA(cudaGetLastError());
+  return finish_dt(c, G, cfg->dt_ice_max, dt_crit_adv);
+}
+
+int ufe_b200_calc_critical_timestep_SIA(ufe_b200_handle h, const ufe_b200_config* cfg, const double* Hi, const double* D_3D_b, double* dt_crit_SIA) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && cfg && Hi && D_3D_b && dt_crit_SIA, "ufe_b200_calc_critical_timestep_SIA: NULL argument");
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_TRY(ensure_geometry(c));
+  Mesh& M = *c->mesh; Geometry& G = *c->geo;
+  cudaStream_t st = c->stream;
+  const int nb = M.b.n_loc(), nz = M.nz;
+  const size_t nb_ext = M.b.n_ext();
+  {
+    UFE_REGION(c, TC_H2D);
+    UFE_TRY(up_a(c, G.a[0].p, Hi));
+    UFE_TRY(G.D3.alloc(nb_ext * nz));
+    UFE_CUDA(cudaMemcpy2DAsync(G.D3.p + M.b.off(), sizeof(double) * nb_ext, D_3D_b, sizeof(double) * nb, sizeof(double) * nb, nz, cudaMemcpyHostToDevice, st));
+  }
+  UFE_TRY(halo_exchange(c, M.a, G.a[0].p));
+  const unsigned long long init = (unsigned long long)__builtin_bit_cast(long long, cfg->dt_ice_max);
+  UFE_CUDA(cudaMemcpyAsync(G.dtbits.p, &init, sizeof(init), cudaMemcpyHostToDevice, st));
+  {
+    UFE_LAUNCH(c, TC_TRI);
+    k_geo_dt_sia<<<grid_for(c, nb, 128, 16), 128, 0, st>>>(geo_mesh(M), nb, M.b.off(), (int)nb_ext, nz, cfg->dt_ice_max, G.a[0].p, G.D3.p, G.dtbits.p);
+  }
+  UFE_CUDA(cudaGetLastError());
+  return finish_dt(c, G, cfg->dt_ice_max, dt_crit_SIA);
+}
+
+}  // extern "C"

@@ -129,6 +129,7 @@ int ufe_b200_mesh_create(ufe_b200_handle h, const ufe_b200_mesh_desc* d) {
   UFE_TRY(up(c, M->A, d->A, nV, "A")); UFE_TRY(up(c, M->Cw, d->Cw, nV * ncm, "Cw")); UFE_TRY(up(c, M->D_x, d->D_x, nV * ncm, "D_x"));
   UFE_TRY(up(c, M->D_y, d->D_y, nV * ncm, "D_y")); UFE_TRY(up(c, M->D, d->D, nV * ncm, "D")); UFE_TRY(up(c, M->VE, d->VE, nV * ncm, "VE"));
   UFE_TRY(up(c, M->ETri, d->ETri, nE * 2, "ETri")); UFE_TRY(up(c, M->zeta, d->zeta, (size_t)d->nz, "zeta"));
+  if (d->Tricc) UFE_TRY(up(c, M->Tricc, d->Tricc, nTri * 2, "Tricc"));
   M->h_zeta.assign(d->zeta, d->zeta + d->nz);
   auto setr = [&](Range& r, int n) {
     r.n_glob = n;
@@ -149,6 +150,7 @@ int ufe_b200_mesh_destroy(ufe_b200_handle h) {
   velocity_free(c->vel); c->vel = nullptr;
   thickness_free(c->thick); c->thick = nullptr;
   secondary_free(c->sec); c->sec = nullptr;
+  geometry_free(c->geo); c->geo = nullptr;
   delete c->mesh; c->mesh = nullptr;
   return 0;
 }

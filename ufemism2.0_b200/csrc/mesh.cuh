@@ -9,7 +9,7 @@ namespace ufe {
 struct Mesh {
   int nV = 0, nTri = 0, nE = 0, nC_mem = 0, nz = 0;
   double xmin = 0, xmax = 0, ymin = 0, ymax = 0;
-  DBuf<double> V, TriGC, A, Cw, D_x, D_y, D, zeta;
+  DBuf<double> V, TriGC, Tricc, A, Cw, D_x, D_y, D, zeta;
   DBuf<int> nC, C, niTri, iTri, VBI, Tri, TriC, TriBI, VE, ETri;
   std::vector<double> h_zeta;
   Range a, b, c, buv;     // vertices, triangles, edges, interleaved (u,v) unknowns on triangles

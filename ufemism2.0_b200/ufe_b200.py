@@ -75,7 +75,7 @@ class MeshDesc(C.Structure):
                 ("xmin", C.c_double), ("xmax", C.c_double), ("ymin", C.c_double), ("ymax", C.c_double),
                 ("V", c_dp), ("nC", c_ip), ("C", c_ip), ("niTri", c_ip), ("iTri", c_ip), ("VBI", c_ip), ("Tri", c_ip),
                 ("TriC", c_ip), ("TriBI", c_ip), ("TriGC", c_dp), ("A", c_dp), ("Cw", c_dp), ("D_x", c_dp), ("D_y", c_dp),
-                ("D", c_dp), ("VE", c_ip), ("ETri", c_ip), ("zeta", c_dp)]
+                ("D", c_dp), ("VE", c_ip), ("ETri", c_ip), ("zeta", c_dp), ("Tricc", c_dp)]
 
 
 class IceInputs(C.Structure):
@@ -115,6 +115,20 @@ def alloc_secondary(n_a, n_b, nz):
     return s, arrs
 
 
+MASK_FIELDS = ["mask", "mask_icefree_land", "mask_icefree_ocean", "mask_grounded_ice", "mask_floating_ice", "mask_margin", "mask_gl_gr", "mask_gl_fl",
+               "mask_cf_gr", "mask_cf_fl", "mask_coastline"]
+GF_BILIN_INTERP_TAF, GF_BEDROCK_CDF, GF_BILIN_INTERP_TAF_PLUS_BEDROCK_CDF = 0, 1, 2
+
+
+class Masks(C.Structure):
+    _fields_ = [(n, c_ip) for n in MASK_FIELDS]
+
+
+def alloc_masks(n):
+    arrs = {k: np.zeros(n, np.int32) for k in MASK_FIELDS}
+    return Masks(*[ip(arrs[k]) for k in MASK_FIELDS]), arrs
+
+
 class VerticalVelocityIO(C.Structure):
     _fields_ = [(n, c_dp) for n in ("Hi", "Hs", "Hib", "dHb_dt", "dHi_dt", "BMB")] + [("mask_grounded_ice", c_ip), ("mask_floating_ice", c_ip),
                                                                                       ("w_3D", c_dp), ("dw_dz_3D", c_dp)]
@@ -147,7 +161,7 @@ def mesh_desc(m):
     d = MeshDesc()
     d.nV, d.nTri, d.nE, d.nC_mem, d.nz = m.nV, m.nTri, m.nE, m.nC_mem, m.nz
     d.xmin, d.xmax, d.ymin, d.ymax = m.xmin, m.xmax, m.ymin, m.ymax
-    for n in ("V", "TriGC", "A", "Cw", "D_x", "D_y", "D", "zeta"):
+    for n in ("V", "TriGC", "A", "Cw", "D_x", "D_y", "D", "zeta", "Tricc"):
         setattr(d, n, dp(getattr(m, n)))
     for n in ("nC", "C", "niTri", "iTri", "VBI", "Tri", "TriC", "TriBI", "VE", "ETri"):
         setattr(d, n, ip(getattr(m, n)))
@@ -214,6 +228,12 @@ def lib():
     L.ufe_b200_solve_SIA.argtypes = [H, C.POINTER(Config), C.c_double] + [c_dp] * 8
     L.ufe_b200_calc_secondary_velocities.argtypes = [H, c_dp, c_dp, C.POINTER(SecondaryVelocities)]
     L.ufe_b200_set_state_resident.argtypes = [H, C.c_int]
+    PC = C.POINTER(Config)
+    L.ufe_b200_determine_masks.argtypes = [H, PC, c_dp, c_dp, c_dp, C.POINTER(Masks)]
+    L.ufe_b200_calc_effective_thickness.argtypes = [H, PC, c_dp, c_dp, c_dp, c_dp, c_dp]
+    L.ufe_b200_calc_grounded_fractions.argtypes = [H, PC, C.c_int, C.c_int, c_dp, c_dp, c_dp, c_dp, c_ip, c_dp, c_dp, c_dp, c_dp]
+    L.ufe_b200_calc_critical_timestep_adv.argtypes = [H, PC, C.c_int, c_dp, c_ip, c_dp, c_dp, C.POINTER(C.c_double)]
+    L.ufe_b200_calc_critical_timestep_SIA.argtypes = [H, PC, c_dp, c_dp, C.POINTER(C.c_double)]
     L.ufe_b200_calc_vertical_velocities.argtypes = [H, C.POINTER(Config), C.POINTER(VerticalVelocityIO)]
     L.ufe_b200_timing_enable.argtypes = [H, C.c_int]
     L.ufe_b200_timing_get.argtypes = [H, C.c_char_p, c_dp, C.POINTER(C.c_longlong)]
@@ -235,7 +255,8 @@ ABI_SYMBOLS = [
     "ufe_b200_set_mg_params", "ufe_b200_get_mg_info", "ufe_b200_mg_host_transfer", "ufe_b200_mg_host_transfer_get", "ufe_b200_mg_host_transfer_parts", "ufe_b200_mg_host_transfer_parts_get",
     "ufe_b200_solve_DIVA", "ufe_b200_solve_SSA", "ufe_b200_velocity_upload", "ufe_b200_velocity_solve_resident",
     "ufe_b200_velocity_download", "ufe_b200_thickness_upload", "ufe_b200_pc_step_resident", "ufe_b200_pc_step",
-    "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA", "ufe_b200_calc_secondary_velocities", "ufe_b200_calc_vertical_velocities", "ufe_b200_set_state_resident",
+    "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA", "ufe_b200_calc_secondary_velocities", "ufe_b200_calc_vertical_velocities", "ufe_b200_set_state_resident", "ufe_b200_determine_masks", "ufe_b200_calc_effective_thickness",
+               "ufe_b200_calc_grounded_fractions", "ufe_b200_calc_critical_timestep_adv", "ufe_b200_calc_critical_timestep_SIA",
     "ufe_b200_timing_enable", "ufe_b200_timing_get", "ufe_b200_timing_reset", "ufe_b200_timer_start", "ufe_b200_timer_stop",
     "ufe_b200_host_register", "ufe_b200_host_unregister"]
 
