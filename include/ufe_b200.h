@@ -364,6 +364,38 @@ int ufe_b200_calc_critical_timestep_adv(ufe_b200_handle h, const ufe_b200_config
                                         const int32_t* mask_floating_ice, const double* u_vav_b, const double* v_vav_b, double* dt_crit_adv);
 int ufe_b200_calc_critical_timestep_SIA(ufe_b200_handle h, const ufe_b200_config* cfg, const double* Hi, const double* D_3D_b, double* dt_crit_SIA);
 
+/* Replaces alter_ice_thickness( mesh, ice, Hi_old, Hb, SL, Hi_new, refgeo, time) (utilities/ice_thickness_safeties.f90:26-288): the would-be
+ * effective thickness, mask protection, thin-ice / calving / shelf removal, fixiness, limitness, modiness.  The C% scalars it reads, with the
+ * defaults of model_configuration_type_and_namelist.f90:424-469 (ufe_b200_alter_params_defaults). */
+enum { UFE_MODINESS_NONE = 0, UFE_MODINESS_TI_HOM = 1, UFE_MODINESS_TI_HOM_UP = 2, UFE_MODINESS_TI_HOM_DOWN = 3, UFE_MODINESS_NO_THICK_INLAND = 4,
+       UFE_MODINESS_NO_THIN_INLAND = 5 };
+typedef struct ufe_b200_alter_params {
+  int32_t do_protect_grounded_mask; double protect_grounded_mask_t_end;
+  double Hi_min;
+  int32_t calving_law_threshold_thickness; double calving_threshold_thickness_shelf;   /* C%choice_calving_law == 'threshold_thickness' */
+  int32_t remove_ice_absent_at_PD, do_remove_shelves, remove_shelves_larger_than_PD, continental_shelf_calving;
+  double continental_shelf_min_height;
+  double fixiness_t_start, fixiness_t_end; int32_t do_fixiness_before_start;
+  double limitness_t_start, limitness_t_end; int32_t do_limitness_before_start;
+  int32_t modiness_H_style; double modiness_T_hom_ref;
+  double fixiness_H_gl_gr, fixiness_H_gl_fl, fixiness_H_grounded, fixiness_H_floating;
+  int32_t fixiness_H_freeland, fixiness_H_freeocean;
+  double limitness_H_gl_gr, limitness_H_gl_fl, limitness_H_grounded, limitness_H_floating;
+} ufe_b200_alter_params;
+void ufe_b200_alter_params_defaults(ufe_b200_alter_params* p);
+/* masks: ice%mask_* of the current geometry (only icefree_land, icefree_ocean, grounded_ice, floating_ice, gl_gr, gl_fl are read);
+ * refgeo_Hi, refgeo_Hb: refgeo%Hi, refgeo%Hb; Ti_hom: ice%Ti_hom (may be NULL unless a Ti_hom modiness style is chosen); Hi_new is in/out. */
+int ufe_b200_alter_ice_thickness(ufe_b200_handle h, const ufe_b200_config* cfg, const ufe_b200_alter_params* prm, double time, const ufe_b200_masks* masks,
+                                 const double* Hi_old, const double* Hb, const double* SL, const double* refgeo_Hi, const double* refgeo_Hb,
+                                 const double* Ti_hom, double* Hi_new);
+
+/* Replaces calc_and_apply_spill_over_flux( mesh, ice, Hi_new, dt) (utilities/ice_thickness_safeties.f90:290-437): ice above the upstream
+ * thickness at calving-front vertices is handed to the neighbouring ice-free ocean vertices, weighted by the outflow velocity.
+ * In: ice%mask_icefree_ocean, mask_cf_gr, mask_cf_fl (from `masks`), ice%Hi_eff, u_vav_b, v_vav_b (NULL = the last device solve; ice%u_perp is
+ * formed from them as calc_ice_flux_divergence_matrix_upwind does).  In/out Hi_new; out ice%Qspill (may be NULL). */
+int ufe_b200_calc_and_apply_spill_over_flux(ufe_b200_handle h, const ufe_b200_masks* masks, const double* Hi_eff, const double* u_vav_b,
+                                            const double* v_vav_b, double dt, double* Hi_new, double* Qspill);
+
 /* ---- timing hooks for bench.py (CUDA events on the library's own stream) ----------------------- */
 /* Milliseconds spent in the named kernel class since the last reset, and its launch count.
  * classes: "spmv_stiffness", "krylov_vec", "assembly", "column", "tri", "epilogue", "thickness", "operator_spmv" */

@@ -243,3 +243,33 @@ extern "C" double orc_calc_critical_timestep_SIA(void* h, const ufe_b200_config*
   auto* o = static_cast<OracleMesh*>(h);
   return calc_critical_timestep_SIA(o->mv, to_config(cfg), Hi, D_3D_b);
 }
+
+extern "C" int orc_alter_ice_thickness(void* h, const ufe_b200_config* cfg, const ufe_b200_alter_params* prm, double time, const ufe_b200_masks* masks,
+                                       const double* Hi_old, const double* Hb, const double* SL, const double* refgeo_Hi, const double* refgeo_Hb,
+                                       const double* Ti_hom, double* Hi_new) {
+  auto* o = static_cast<OracleMesh*>(h);
+  MaskSet M; std::memcpy(&M, masks, sizeof(M));
+  AlterParams P;
+  P.do_protect_grounded_mask = prm->do_protect_grounded_mask; P.protect_grounded_mask_t_end = prm->protect_grounded_mask_t_end; P.Hi_min = prm->Hi_min;
+  P.calving_law_threshold_thickness = prm->calving_law_threshold_thickness; P.calving_threshold_thickness_shelf = prm->calving_threshold_thickness_shelf;
+  P.remove_ice_absent_at_PD = prm->remove_ice_absent_at_PD; P.do_remove_shelves = prm->do_remove_shelves;
+  P.remove_shelves_larger_than_PD = prm->remove_shelves_larger_than_PD; P.continental_shelf_calving = prm->continental_shelf_calving;
+  P.continental_shelf_min_height = prm->continental_shelf_min_height;
+  P.fixiness_t_start = prm->fixiness_t_start; P.fixiness_t_end = prm->fixiness_t_end; P.do_fixiness_before_start = prm->do_fixiness_before_start;
+  P.limitness_t_start = prm->limitness_t_start; P.limitness_t_end = prm->limitness_t_end; P.do_limitness_before_start = prm->do_limitness_before_start;
+  P.modiness_H_style = prm->modiness_H_style; P.modiness_T_hom_ref = prm->modiness_T_hom_ref;
+  P.fixiness_H_gl_gr = prm->fixiness_H_gl_gr; P.fixiness_H_gl_fl = prm->fixiness_H_gl_fl; P.fixiness_H_grounded = prm->fixiness_H_grounded;
+  P.fixiness_H_floating = prm->fixiness_H_floating; P.fixiness_H_freeland = prm->fixiness_H_freeland; P.fixiness_H_freeocean = prm->fixiness_H_freeocean;
+  P.limitness_H_gl_gr = prm->limitness_H_gl_gr; P.limitness_H_gl_fl = prm->limitness_H_gl_fl; P.limitness_H_grounded = prm->limitness_H_grounded;
+  P.limitness_H_floating = prm->limitness_H_floating;
+  try {
+    alter_ice_thickness(o->mv, to_config(cfg), P, time, M, Hi_old, Hb, SL, refgeo_Hi, refgeo_Hb, Ti_hom, Hi_new);
+  } catch (const std::exception&) { return 1; }
+  return 0;
+}
+extern "C" void orc_calc_and_apply_spill_over_flux(void* h, const ufe_b200_masks* masks, const double* Hi_eff, const double* u_vav_b, const double* v_vav_b,
+                                                   double dt, double* Hi_new, double* Qspill) {
+  auto* o = static_cast<OracleMesh*>(h);
+  MaskSet M; std::memcpy(&M, masks, sizeof(M));
+  calc_and_apply_spill_over_flux(o->mv, M, Hi_eff, u_vav_b, v_vav_b, dt, Hi_new, Qspill);
+}

@@ -10,6 +10,7 @@
 //   triangle_area                             src/UPSY/basic/math_utilities/plane_geometry.f90:322-330
 #include <algorithm>
 #include <cmath>
+#include <limits>
 #include <stdexcept>
 
 #include "oracle.hpp"
@@ -259,6 +260,122 @@ double calc_critical_timestep_adv(const MeshView& mesh, const Config& C, int do_
       dt_crit = std::min(dt_crit, dt);
     }
   return std::min(C.dt_ice_max, dt_crit);
+}
+
+
+// decaying weight shared by fixiness and limitness (ice_thickness_safeties.f90:118-172)
+static double decay_weight(double time, double t_start, double t_end, int before_start) {
+  double f = 1.0;
+  if (t_start >= t_end) f = 0.0;
+  else if (time <= t_start) f = before_start ? 1.0 : 0.0;
+  else if (time >= t_end) f = 0.0;
+  else f = 1.0 - (time - t_start) / (t_end - t_start);
+  return std::min(1.0, std::max(0.0, f));
+}
+
+void alter_ice_thickness(const MeshView& mesh, const Config& C, const AlterParams& P, double time, const MaskSet& M, const double* Hi_old,
+                         const double* Hb, const double* SL, const double* refgeo_Hi, const double* refgeo_Hb, const double* Ti_hom, double* Hi_new) {
+  const int nV = mesh.nV;
+  std::vector<double> Hi_eff(nV), fm(nV);
+  calc_effective_thickness(mesh, C, Hi_new, Hb, SL, Hi_eff.data(), fm.data());   // :55
+  if (P.do_protect_grounded_mask && time <= P.protect_grounded_mask_t_end)
+    for (int vi = 0; vi < nV; ++vi)
+      if (M.grounded_ice[vi]) Hi_new[vi] = std::max(Hi_new[vi], (SL[vi] - Hb[vi]) * C.seawater_density / C.ice_density + 0.1);
+  for (int vi = 0; vi < nV; ++vi) {   // :72-119, in the reference's order
+    if (Hi_eff[vi] < P.Hi_min) Hi_new[vi] = 0.0;
+    const bool fl = is_floating(C, Hi_eff[vi], Hb[vi], SL[vi]);
+    if (P.calving_law_threshold_thickness && fl && Hi_eff[vi] < P.calving_threshold_thickness_shelf) Hi_new[vi] = 0.0;
+    if (P.remove_ice_absent_at_PD && refgeo_Hi[vi] == 0.0) Hi_new[vi] = 0.0;
+    if (P.do_remove_shelves && fl) Hi_new[vi] = 0.0;
+    if (P.remove_shelves_larger_than_PD && refgeo_Hi[vi] == 0.0 && refgeo_Hb[vi] < 0.0) Hi_new[vi] = 0.0;
+    if (P.continental_shelf_calving && refgeo_Hi[vi] == 0.0 && refgeo_Hb[vi] < P.continental_shelf_min_height) Hi_new[vi] = 0.0;
+  }
+  const double fixiness = decay_weight(time, P.fixiness_t_start, P.fixiness_t_end, P.do_fixiness_before_start);
+  const double limitness = decay_weight(time, P.limitness_t_start, P.limitness_t_end, P.do_limitness_before_start);
+  for (int vi = 0; vi < nV; ++vi) {
+    double up = 0.0, down = 0.0;   // modiness :177-219
+    const bool inland = M.grounded_ice[vi] && !M.gl_gr[vi];
+    switch (P.modiness_H_style) {
+      case 0: break;
+      case 1: up = down = 1.0 - std::exp(Ti_hom[vi] / P.modiness_T_hom_ref); break;
+      case 2: up = 1.0 - std::exp(Ti_hom[vi] / P.modiness_T_hom_ref); break;
+      case 3: down = 1.0 - std::exp(Ti_hom[vi] / P.modiness_T_hom_ref); break;
+      case 4: if (inland) up = 1.0; break;
+      case 5: if (inland) down = 1.0; break;
+      default: throw std::runtime_error("unknown modiness_H_choice");
+    }
+    up = std::min(1.0, std::max(0.0, up)); down = std::min(1.0, std::max(0.0, down));
+    double fix = 0.0, lim = 0.0;   // :224-262
+    if (M.gl_gr[vi]) { fix = P.fixiness_H_gl_gr * fixiness; lim = P.limitness_H_gl_gr * limitness; }
+    else if (M.gl_fl[vi]) { fix = P.fixiness_H_gl_fl * fixiness; lim = P.limitness_H_gl_fl * limitness; }
+    else if (M.grounded_ice[vi]) { fix = P.fixiness_H_grounded * fixiness; lim = P.limitness_H_grounded * limitness; }
+    else if (M.floating_ice[vi]) { fix = P.fixiness_H_floating * fixiness; lim = P.limitness_H_floating * limitness; }
+    else if (M.icefree_land[vi]) { if (P.fixiness_H_freeland && fixiness > 0.0) fix = 1.0; lim = P.limitness_H_grounded * limitness; }
+    else if (M.icefree_ocean[vi]) { if (P.fixiness_H_freeocean && fixiness > 0.0) fix = 1.0; lim = P.limitness_H_floating * limitness; }
+    else throw std::runtime_error("vertex neither grounded, floating, nor ice-free?");
+    double H = Hi_old[vi] * fix + Hi_new[vi] * (1.0 - fix);
+    H = std::min(H, refgeo_Hi[vi] + (1.0 - up) * lim + (1.0 - limitness) * (H - refgeo_Hi[vi]));
+    H = std::max(H, refgeo_Hi[vi] - (1.0 - down) * lim - (1.0 - limitness) * (refgeo_Hi[vi] - H));
+    Hi_new[vi] = H;
+  }
+}
+
+void calc_and_apply_spill_over_flux(const MeshView& mesh, const MaskSet& M, const double* Hi_eff, const double* u_vav_b, const double* v_vav_b,
+                                    double dt, double* Hi_new, double* Qspill) {
+  const int nV = mesh.nV, nE = mesh.nE, ncm = mesh.nC_mem;
+  const double w_eps = (double)1.e-2f;   // `real(dp) :: w_eps = 1.e-2`: a default-real literal (:309)
+  // ice%u_perp as calc_ice_flux_divergence_matrix_upwind leaves it (conservation_of_mass_utilities.f90:78-99)
+  std::vector<double> u_perp((size_t)nV * ncm, 0.0), relweight((size_t)nV * ncm, 0.0), Q_src(nV, 0.0), Q_dst(nV, 0.0);
+  for (int vi = 0; vi < nV; ++vi)
+    for (int ci = 0; ci < mesh.nC[vi]; ++ci) {
+      const size_t k = vi + (size_t)ci * nV;
+      const int ei = mesh.VE[k] - 1, til = mesh.ETri[ei], tir = mesh.ETri[ei + nE];
+      double uc, vc;
+      if (til == 0) { uc = u_vav_b[tir - 1]; vc = v_vav_b[tir - 1]; }
+      else if (tir == 0) { uc = u_vav_b[til - 1]; vc = v_vav_b[til - 1]; }
+      else { uc = (u_vav_b[til - 1] + u_vav_b[tir - 1]) / 2.0; vc = (v_vav_b[til - 1] + v_vav_b[tir - 1]) / 2.0; }
+      u_perp[k] = uc * mesh.D_x[k] / mesh.D[k] + vc * mesh.D_y[k] / mesh.D[k];
+    }
+  for (int vi = 0; vi < nV; ++vi) {   // sources :323-392
+    const bool cf = M.cf_fl[vi] || M.cf_gr[vi];
+    double Hi_ups;
+    if (cf) {
+      int cm = -1; double umin = std::numeric_limits<double>::max();
+      for (int ci = 0; ci < mesh.nC[vi]; ++ci)
+        if (u_perp[vi + (size_t)ci * nV] < umin) { umin = u_perp[vi + (size_t)ci * nV]; cm = ci; }
+      const int vj = mesh.C[vi + (size_t)cm * nV] - 1;
+      if (Hi_new[vj] == 0.0) continue;
+      Hi_ups = Hi_new[vj];
+    } else {
+      Hi_ups = Hi_eff[vi];
+    }
+    if (cf && Hi_new[vi] > Hi_ups) {
+      Q_src[vi] = -(Hi_new[vi] - Hi_ups) * mesh.A[vi] / dt;
+      std::vector<double> weight(ncm, 0.0);
+      for (int ci = 0; ci < mesh.nC[vi]; ++ci) {
+        const int vj = mesh.C[vi + (size_t)ci * nV] - 1;
+        if (M.icefree_ocean[vj]) weight[ci] = std::max(0.0, u_perp[vi + (size_t)ci * nV]) + w_eps;
+      }
+      double sw = 0.0;
+      for (int ci = 0; ci < ncm; ++ci) sw += weight[ci];   // sum( weight) over all nC_mem entries
+      if (sw < w_eps) Q_src[vi] = 0.0;
+      else for (int ci = 0; ci < mesh.nC[vi]; ++ci) relweight[vi + (size_t)ci * nV] = weight[ci] / sw;
+    }
+  }
+  for (int vi = 0; vi < nV; ++vi) {   // destinations :398-424
+    if (!M.icefree_ocean[vi]) continue;
+    for (int ci = 0; ci < mesh.nC[vi]; ++ci) {
+      const int vj = mesh.C[vi + (size_t)ci * nV] - 1;
+      for (int cj = 0; cj < mesh.nC[vj]; ++cj)
+        if (mesh.C[vj + (size_t)cj * nV] - 1 == vi)
+          if (Q_src[vj] < -1.e-2 && relweight[vj + (size_t)cj * nV] > 1.e-6) Q_dst[vi] = Q_dst[vi] - Q_src[vj] * relweight[vj + (size_t)cj * nV];
+    }
+  }
+  for (int vi = 0; vi < nV; ++vi) {
+    const double q = (Q_src[vi] + Q_dst[vi]) / mesh.A[vi];
+    if (Qspill) Qspill[vi] = q;
+    Hi_new[vi] = Hi_new[vi] + q * dt;
+  }
 }
 
 }  // namespace orc

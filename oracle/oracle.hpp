@@ -161,6 +161,25 @@ void calc_effective_thickness(const MeshView& mesh, const Config& C, const doubl
 void calc_grounded_fractions(const MeshView& mesh, const Operators& ops, const Config& C, int choice, int nbins, const double* Hi, const double* Hb,
                              const double* SL, const double* dHb, const int* mask_floating_ice, const double* bedrock_cdf,
                              const double* bedrock_cdf_b, double* fraction_gr, double* fraction_gr_b);
+// alter_ice_thickness / calc_and_apply_spill_over_flux (ice_thickness_safeties.f90:26-437); AlterParams = the C% scalars (same members as
+// ufe_b200_alter_params, include/ufe_b200.h)
+struct AlterParams {
+  int do_protect_grounded_mask; double protect_grounded_mask_t_end;
+  double Hi_min;
+  int calving_law_threshold_thickness; double calving_threshold_thickness_shelf;
+  int remove_ice_absent_at_PD, do_remove_shelves, remove_shelves_larger_than_PD, continental_shelf_calving;
+  double continental_shelf_min_height;
+  double fixiness_t_start, fixiness_t_end; int do_fixiness_before_start;
+  double limitness_t_start, limitness_t_end; int do_limitness_before_start;
+  int modiness_H_style; double modiness_T_hom_ref;
+  double fixiness_H_gl_gr, fixiness_H_gl_fl, fixiness_H_grounded, fixiness_H_floating;
+  int fixiness_H_freeland, fixiness_H_freeocean;
+  double limitness_H_gl_gr, limitness_H_gl_fl, limitness_H_grounded, limitness_H_floating;
+};
+void alter_ice_thickness(const MeshView& mesh, const Config& C, const AlterParams& P, double time, const MaskSet& masks, const double* Hi_old,
+                         const double* Hb, const double* SL, const double* refgeo_Hi, const double* refgeo_Hb, const double* Ti_hom, double* Hi_new);
+void calc_and_apply_spill_over_flux(const MeshView& mesh, const MaskSet& masks, const double* Hi_eff, const double* u_vav_b, const double* v_vav_b,
+                                    double dt, double* Hi_new, double* Qspill);
 double calc_critical_timestep_SIA(const MeshView& mesh, const Config& C, const double* Hi, const double* D_3D_b);
 double calc_critical_timestep_adv(const MeshView& mesh, const Config& C, int do_grounded_only_adv_dt, const double* Hi, const int* mask_floating_ice,
                                   const double* u_vav_b, const double* v_vav_b);

@@ -49,6 +49,8 @@ def lib():
         L.orc_calc_critical_timestep_adv.argtypes = [C.c_void_p, PC, C.c_int, dp, ip, dp, dp]
         L.orc_calc_critical_timestep_SIA.restype = C.c_double
         L.orc_calc_critical_timestep_SIA.argtypes = [C.c_void_p, PC, dp, dp]
+        L.orc_alter_ice_thickness.argtypes = [C.c_void_p, PC, C.POINTER(ub.AlterParams), C.c_double, C.POINTER(ub.Masks), dp, dp, dp, dp, dp, dp, dp]
+        L.orc_calc_and_apply_spill_over_flux.argtypes = [C.c_void_p, C.POINTER(ub.Masks), dp, dp, dp, C.c_double, dp, dp]
         _LIB = L
     return _LIB
 
@@ -164,6 +166,20 @@ class OracleMesh:
 
     def calc_critical_timestep_SIA(self, cfg, Hi, D_3D_b):
         return lib().orc_calc_critical_timestep_SIA(self.h, C.byref(cfg), ub.dp(Hi), ub.dp(D_3D_b))
+
+    def alter_ice_thickness(self, cfg, prm, time, masks, Hi_old, Hb, SL, ref_Hi, ref_Hb, Ti_hom, Hi_new):
+        out = Hi_new.copy()
+        ms = ub.masks_struct(masks)
+        rc = lib().orc_alter_ice_thickness(self.h, C.byref(cfg), C.byref(prm), time, C.byref(ms), ub.dp(Hi_old), ub.dp(Hb), ub.dp(SL), ub.dp(ref_Hi),
+                                           ub.dp(ref_Hb), ub.dp(Ti_hom), ub.dp(out))
+        assert rc == 0
+        return out
+
+    def calc_and_apply_spill_over_flux(self, masks, Hi_eff, u_vav_b, v_vav_b, dt, Hi_new):
+        out, q = Hi_new.copy(), np.zeros(self.m.nV)
+        ms = ub.masks_struct(masks)
+        lib().orc_calc_and_apply_spill_over_flux(self.h, C.byref(ms), ub.dp(Hi_eff), ub.dp(u_vav_b), ub.dp(v_vav_b), dt, ub.dp(out), ub.dp(q))
+        return out, q
 
     def flux_divergence_matrix(self, u_b, v_b, fraction_margin):
         m, nnz = C.c_int(), C.c_int()

@@ -242,3 +242,120 @@ def test_gpu_geometry_stage_matches_oracle():
     want = o.calc_critical_timestep_SIA(cfg, Hi, D)
     assert abs(dt.value - want) <= 1e-14 * want and want < cfg.dt_ice_max, (dt.value, want)
     ctx.close()
+
+
+def _alter_case(seed=12):
+    w, m, Hi, Hb, SL = _case(h=3.0e4)
+    o = ol.OracleMesh(m)
+    rng = np.random.default_rng(seed)
+    masks = o.determine_masks(w.cfg, Hi, Hb, SL)
+    Hi_new = np.maximum(0.0, Hi + 40.0 * rng.standard_normal(m.nV) * (Hi > 0))
+    ref_Hi = np.maximum(0.0, Hi + 100.0 * rng.standard_normal(m.nV) * (Hi > 0)); ref_Hi[rng.random(m.nV) < 0.1] = 0.0
+    ref_Hb = Hb + 5.0 * rng.standard_normal(m.nV)
+    Ti_hom = -30.0 * rng.random(m.nV)
+    return w, m, o, masks, Hi, Hb, SL, Hi_new, ref_Hi, ref_Hb, Ti_hom
+
+
+def _alter_variants():
+    P = []
+    p = ub.alter_params_defaults(); P.append(("defaults", p, 0.0))
+    p = ub.alter_params_defaults(); p.Hi_min = 30.0; p.do_protect_grounded_mask = 1; p.protect_grounded_mask_t_end = 100.0; p.remove_ice_absent_at_PD = 1
+    P.append(("protect+Hi_min+PD", p, 50.0))
+    p = ub.alter_params_defaults(); p.do_remove_shelves = 1; P.append(("no_shelves", p, 0.0))
+    p = ub.alter_params_defaults(); p.remove_shelves_larger_than_PD = 1; p.continental_shelf_calving = 1; p.continental_shelf_min_height = -300.0
+    P.append(("PD_front+shelf_edge", p, 0.0))
+    p = ub.alter_params_defaults(); p.fixiness_t_start, p.fixiness_t_end = 0.0, 100.0
+    p.fixiness_H_gl_gr, p.fixiness_H_gl_fl, p.fixiness_H_grounded, p.fixiness_H_floating = 1.0, 0.5, 0.8, 0.2
+    p.fixiness_H_freeland = 1; p.fixiness_H_freeocean = 1
+    P.append(("fixiness", p, 25.0))
+    p = ub.alter_params_defaults(); p.limitness_t_start, p.limitness_t_end = 0.0, 100.0; p.do_limitness_before_start = 1
+    p.limitness_H_gl_gr, p.limitness_H_gl_fl, p.limitness_H_grounded, p.limitness_H_floating = 10.0, 20.0, 30.0, 40.0
+    p.modiness_H_style = 1
+    P.append(("limitness+Ti_hom", p, -5.0))
+    p = ub.alter_params_defaults(); p.limitness_t_start, p.limitness_t_end = 0.0, 100.0; p.limitness_H_grounded = 15.0; p.limitness_H_gl_gr = 15.0
+    p.limitness_H_gl_fl = p.limitness_H_floating = 25.0; p.modiness_H_style = 4
+    P.append(("limitness_decaying+no_thick_inland", p, 60.0))
+    return P
+
+
+def test_oracle_alter_ice_thickness_properties():
+    w, m, o, masks, Hi, Hb, SL, Hi_new, ref_Hi, ref_Hb, Ti_hom = _alter_case()
+    V = dict((n, (p, t)) for n, p, t in _alter_variants())
+    he, fm = o.calc_effective_thickness(w.cfg, Hi_new, Hb, SL)
+    fl = he < (SL - Hb) * RHO_W / RHO_I
+    # defaults: only the thickness-threshold calving law acts
+    p, t = V["defaults"]
+    out = o.alter_ice_thickness(w.cfg, p, t, masks, Hi, Hb, SL, ref_Hi, ref_Hb, Ti_hom, Hi_new)
+    calved = fl & (he < 100.0)
+    assert calved.sum() > 10 and (out[calved] == 0).all()
+    np.testing.assert_allclose(out[~calved], Hi_new[~calved], rtol=1e-13)      # ref + (H - ref) is H up to rounding (limitness 0)
+    p, t = V["no_shelves"]
+    out = o.alter_ice_thickness(w.cfg, p, t, masks, Hi, Hb, SL, ref_Hi, ref_Hb, Ti_hom, Hi_new)
+    assert (out[fl] == 0).all()
+    np.testing.assert_allclose(out[~fl], Hi_new[~fl], rtol=1e-13)
+    # full fixiness at the grounded side of the grounding line, before the interval starts it is off
+    p, t = V["fixiness"]
+    out = o.alter_ice_thickness(w.cfg, p, t, masks, Hi, Hb, SL, ref_Hi, ref_Hb, Ti_hom, Hi_new)
+    keep = ~calved
+    g = masks["mask_gl_gr"].astype(bool) & keep
+    np.testing.assert_allclose(out[g], Hi[g] * 0.75 + Hi_new[g] * 0.25, rtol=1e-13)
+    inl = masks["mask_grounded_ice"].astype(bool) & ~masks["mask_gl_gr"].astype(bool) & keep
+    np.testing.assert_allclose(out[inl], Hi[inl] * 0.6 + Hi_new[inl] * 0.4, rtol=1e-13)
+    # peak limitness: within the allowed departure from the reference thickness (modiness widens nothing: it only tightens)
+    p, t = V["limitness+Ti_hom"]
+    out = o.alter_ice_thickness(w.cfg, p, t, masks, Hi, Hb, SL, ref_Hi, ref_Hb, Ti_hom, Hi_new)
+    lim = np.select([masks["mask_gl_gr"] > 0, masks["mask_gl_fl"] > 0, masks["mask_grounded_ice"] > 0, masks["mask_floating_ice"] > 0,
+                     masks["mask_icefree_land"] > 0], [10.0, 20.0, 30.0, 40.0, 30.0], 40.0)
+    assert (np.abs(out - ref_Hi) <= lim + 1e-9).all() and (np.abs(out - ref_Hi) > 0.5 * lim).sum() > 10
+
+
+def test_oracle_spill_over_flux_conserves_mass():
+    w, m, o, masks, Hi, Hb, SL, Hi_new, ref_Hi, ref_Hb, Ti_hom = _alter_case()
+    rng = np.random.default_rng(3)
+    r = np.hypot(m.V[:, 0], m.V[:, 1])
+    Tri = np.asarray(m.Tri) - 1
+    rc = m.V[Tri].mean(axis=1)
+    u = 400.0 * rc[:, 0] / 1e6 + 20.0 * rng.standard_normal(m.nTri); v = 400.0 * rc[:, 1] / 1e6 + 20.0 * rng.standard_normal(m.nTri)   # outward flow
+    cf = (masks["mask_cf_fl"] + masks["mask_cf_gr"]) > 0
+    H = Hi.copy(); H[cf] *= 1.0 + rng.random(cf.sum())                  # calving-front vertices thicker than their upstream neighbours
+    he, fm = o.calc_effective_thickness(w.cfg, H, Hb, SL)
+    out, q = o.calc_and_apply_spill_over_flux(masks, he, u, v, 0.5, H)
+    A = np.asarray(m.A)
+    src, dst = q < 0, q > 0
+    assert src.sum() > 10 and dst.sum() > 10 and cf[src].all() and (masks["mask_icefree_ocean"][dst] > 0).all()
+    assert abs(np.sum(q * A)) < 1e-9 * np.sum(np.abs(q) * A)           # what leaves the front arrives in the ocean cells
+    np.testing.assert_allclose(out, H + q * 0.5, rtol=0, atol=1e-9)
+    assert (out[src] < H[src]).all() and (out[dst] > 0).all()
+
+
+@pytest.mark.gpu
+def test_gpu_alter_ice_thickness_and_spill_over_match_oracle():
+    w, m, o, masks, Hi, Hb, SL, Hi_new, ref_Hi, ref_Hb, Ti_hom = _alter_case()
+    cfg = w.cfg
+    ctx = ub.Context(device=0)
+    ctx.mesh_create(m); ctx.calc_matrix_operators()
+    L = ub.lib()
+    ms = ub.masks_struct(masks)
+    for name, p, t in _alter_variants():
+        want = o.alter_ice_thickness(cfg, p, t, masks, Hi, Hb, SL, ref_Hi, ref_Hb, Ti_hom, Hi_new)
+        got = Hi_new.copy()
+        ub.check(L.ufe_b200_alter_ice_thickness(ctx.h, C.byref(cfg), C.byref(p), t, C.byref(ms), ub.dp(Hi), ub.dp(Hb), ub.dp(SL), ub.dp(ref_Hi), ub.dp(ref_Hb),
+                                                ub.dp(Ti_hom), ub.dp(got)))
+        assert np.max(np.abs(got - want)) <= 1e-11 * np.max(np.abs(want)), (name, np.max(np.abs(got - want)))
+        assert not np.array_equal(want, Hi_new), name
+    p = ub.alter_params_defaults(); p.modiness_H_style = 9
+    assert L.ufe_b200_alter_ice_thickness(ctx.h, C.byref(cfg), C.byref(p), 0.0, C.byref(ms), ub.dp(Hi), ub.dp(Hb), ub.dp(SL), ub.dp(ref_Hi), ub.dp(ref_Hb),
+                                          ub.dp(Ti_hom), ub.dp(Hi_new.copy())) != 0
+    rng = np.random.default_rng(3)
+    Tri = np.asarray(m.Tri) - 1
+    rc = m.V[Tri].mean(axis=1)
+    u = 400.0 * rc[:, 0] / 1e6 + 20.0 * rng.standard_normal(m.nTri); v = 400.0 * rc[:, 1] / 1e6 + 20.0 * rng.standard_normal(m.nTri)
+    cf = (masks["mask_cf_fl"] + masks["mask_cf_gr"]) > 0
+    H = Hi.copy(); H[cf] *= 1.0 + rng.random(cf.sum())
+    he, fm = o.calc_effective_thickness(cfg, H, Hb, SL)
+    want, q_want = o.calc_and_apply_spill_over_flux(masks, he, u, v, 0.5, H)
+    got, q = H.copy(), np.zeros(m.nV)
+    ub.check(L.ufe_b200_calc_and_apply_spill_over_flux(ctx.h, C.byref(ms), ub.dp(he), ub.dp(u), ub.dp(v), 0.5, ub.dp(got), ub.dp(q)))
+    ctx.close()
+    assert (q_want != 0).sum() > 20
+    assert np.max(np.abs(q - q_want)) <= 1e-11 * np.max(np.abs(q_want)) and np.max(np.abs(got - want)) <= 1e-11 * np.max(want)

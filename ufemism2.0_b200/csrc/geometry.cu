@@ -15,7 +15,7 @@
 namespace ufe {
 
 struct Geometry {
-  DBuf<double> a[8];       // vertex fields over the extended a range: Hi, Hb, SL, dHb, TAF, out0, out1, scratch
+  DBuf<double> a[10];      // vertex fields over the extended a range: Hi, Hb, SL, dHb, TAF, out0, out1, scratch, ...
   DBuf<double> b[3];       // triangle fields over the extended b range: TAF_b, fraction_gr_b, scratch
   DBuf<int> ia[3];         // kind (1..4) / margin flag / floating flag over the extended a range
   DBuf<int> masks;         // [11][n_loc] results of determine_masks
@@ -294,6 +294,144 @@ __global__ void k_geo_dt_sia(GeoMesh m, int n, int off, int nb_ext, int nz, doub
   block_min_to(best, dtbits);
 }
 
+// ---- alter_ice_thickness (ice_thickness_safeties.f90:26-288), after the two effective-thickness passes on Hi_new ------------------------------
+enum { MB_LAND = 1, MB_OCEAN = 2, MB_GROUNDED = 4, MB_FLOATING = 8, MB_GL_GR = 16, MB_GL_FL = 32, MB_CF_GR = 64, MB_CF_FL = 128 };
+struct AlterDev {
+  ufe_b200_alter_params p;
+  double rw_over_ri, fixiness, limitness;
+  int protect;
+};
+__global__ void k_geo_alter(int n, int off, AlterDev a, const int* __restrict__ bits, const double* __restrict__ Hi_old, const double* __restrict__ Hb,
+                            const double* __restrict__ SL, const double* __restrict__ Hi_eff, const double* __restrict__ ref_Hi,
+                            const double* __restrict__ ref_Hb, const double* __restrict__ Ti_hom, double* __restrict__ Hi_new, int* err) {
+  const ufe_b200_alter_params& P = a.p;
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const size_t i = off + r;
+    const int mb = bits[i];
+    double H = Hi_new[i];
+    if (a.protect && (mb & MB_GROUNDED)) H = fmax(H, (SL[i] - Hb[i]) * a.rw_over_ri + 0.1);
+    const double he = Hi_eff[i];
+    const bool fl = is_floating(a.rw_over_ri, he, Hb[i], SL[i]);
+    if (he < P.Hi_min) H = 0.0;
+    if (P.calving_law_threshold_thickness && fl && he < P.calving_threshold_thickness_shelf) H = 0.0;
+    if (P.remove_ice_absent_at_PD && ref_Hi[i] == 0.0) H = 0.0;
+    if (P.do_remove_shelves && fl) H = 0.0;
+    if (P.remove_shelves_larger_than_PD && ref_Hi[i] == 0.0 && ref_Hb[i] < 0.0) H = 0.0;
+    if (P.continental_shelf_calving && ref_Hi[i] == 0.0 && ref_Hb[i] < P.continental_shelf_min_height) H = 0.0;
+    double up = 0.0, down = 0.0;
+    const bool inland = (mb & MB_GROUNDED) && !(mb & MB_GL_GR);
+    switch (P.modiness_H_style) {
+      case UFE_MODINESS_TI_HOM: up = down = 1.0 - exp(Ti_hom[i] / P.modiness_T_hom_ref); break;
+      case UFE_MODINESS_TI_HOM_UP: up = 1.0 - exp(Ti_hom[i] / P.modiness_T_hom_ref); break;
+      case UFE_MODINESS_TI_HOM_DOWN: down = 1.0 - exp(Ti_hom[i] / P.modiness_T_hom_ref); break;
+      case UFE_MODINESS_NO_THICK_INLAND: if (inland) up = 1.0; break;
+      case UFE_MODINESS_NO_THIN_INLAND: if (inland) down = 1.0; break;
+      default: break;
+    }
+    up = fmin(1.0, fmax(0.0, up)); down = fmin(1.0, fmax(0.0, down));
+    double fix = 0.0, lim = 0.0;
+    if (mb & MB_GL_GR) { fix = P.fixiness_H_gl_gr * a.fixiness; lim = P.limitness_H_gl_gr * a.limitness; }
+    else if (mb & MB_GL_FL) { fix = P.fixiness_H_gl_fl * a.fixiness; lim = P.limitness_H_gl_fl * a.limitness; }
+    else if (mb & MB_GROUNDED) { fix = P.fixiness_H_grounded * a.fixiness; lim = P.limitness_H_grounded * a.limitness; }
+    else if (mb & MB_FLOATING) { fix = P.fixiness_H_floating * a.fixiness; lim = P.limitness_H_floating * a.limitness; }
+    else if (mb & MB_LAND) { if (P.fixiness_H_freeland && a.fixiness > 0.0) fix = 1.0; lim = P.limitness_H_grounded * a.limitness; }
+    else if (mb & MB_OCEAN) { if (P.fixiness_H_freeocean && a.fixiness > 0.0) fix = 1.0; lim = P.limitness_H_floating * a.limitness; }
+    else { *err = 1; }   // 'vertex neither grounded, floating, nor ice-free?' (:259)
+    H = Hi_old[i] * fix + H * (1.0 - fix);
+    H = fmin(H, ref_Hi[i] + (1.0 - up) * lim + (1.0 - a.limitness) * (H - ref_Hi[i]));
+    H = fmax(H, ref_Hi[i] - (1.0 - down) * lim - (1.0 - a.limitness) * (ref_Hi[i] - H));
+    Hi_new[i] = H;
+  }
+}
+
+// ---- calc_and_apply_spill_over_flux (ice_thickness_safeties.f90:290-437) -------------------------------------------------------------------
+struct SpillMesh { const double *A, *D_x, *D_y, *D; };
+__device__ __forceinline__ double u_perp_of(const GeoMesh& m, const SpillMesh& g, int vi, int ci, const double* __restrict__ u_b, const double* __restrict__ v_b) {
+  const size_t k = (size_t)ci * m.nV + vi - 1;
+  const int ei = m.VE[k];
+  const int til = m.ETri[ei - 1], tir = m.ETri[(size_t)m.nE + ei - 1];
+  double uc, vc;
+  if (til == 0) { uc = u_b[tir - m.b_lo]; vc = v_b[tir - m.b_lo]; }
+  else if (tir == 0) { uc = u_b[til - m.b_lo]; vc = v_b[til - m.b_lo]; }
+  else { uc = (u_b[til - m.b_lo] + u_b[tir - m.b_lo]) / 2.0; vc = (v_b[til - m.b_lo] + v_b[tir - m.b_lo]) / 2.0; }
+  return uc * g.D_x[k] / g.D[k] + vc * g.D_y[k] / g.D[k];
+}
+// sources: Q_src and the sum of the outflow weights of every calving-front vertex (:323-392); the relative weights are re-formed by the receiver
+__global__ void k_geo_spill_src(GeoMesh m, SpillMesh g, int n, int off, double dt, double w_eps, const int* __restrict__ bits, const double* __restrict__ Hi_new,
+                                const double* __restrict__ u_b, const double* __restrict__ v_b, double* __restrict__ Q_src, double* __restrict__ sumw) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const int vi = m.vi1 + (int)r;
+    const size_t i = off + r;
+    double q = 0.0, sw = 0.0;
+    if (bits[i] & (MB_CF_GR | MB_CF_FL)) {
+      const int nc = m.nC[vi - 1];
+      int cm = 0; double umin = 1.7976931348623157e308;
+      for (int ci = 0; ci < nc; ++ci) {
+        const double up = u_perp_of(m, g, vi, ci, u_b, v_b);
+        if (up < umin) { umin = up; cm = ci; }
+      }
+      const double Hi_ups = Hi_new[m.C[(size_t)cm * m.nV + vi - 1] - m.a_lo];
+      if (Hi_ups != 0.0 && Hi_new[i] > Hi_ups) {
+        q = -(Hi_new[i] - Hi_ups) * g.A[vi - 1] / dt;
+        for (int ci = 0; ci < nc; ++ci)
+          if (bits[m.C[(size_t)ci * m.nV + vi - 1] - m.a_lo] & MB_OCEAN) sw += fmax(0.0, u_perp_of(m, g, vi, ci, u_b, v_b)) + w_eps;
+        if (sw < w_eps) q = 0.0;
+      }
+    }
+    Q_src[i] = q; sumw[i] = sw;
+  }
+}
+// destinations (:398-424) and the update (:427-435)
+__global__ void k_geo_spill_dst(GeoMesh m, SpillMesh g, int n, int off, double dt, double w_eps, const int* __restrict__ bits, const double* __restrict__ u_b,
+                                const double* __restrict__ v_b, const double* __restrict__ Q_src, const double* __restrict__ sumw, double* __restrict__ Hi_new,
+                                double* __restrict__ Qspill) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const int vi = m.vi1 + (int)r;
+    const size_t i = off + r;
+    double qd = 0.0;
+    if (bits[i] & MB_OCEAN) {
+      for (int ci = 0; ci < m.nC[vi - 1]; ++ci) {
+        const int vj = m.C[(size_t)ci * m.nV + vi - 1];
+        const double qs = Q_src[vj - m.a_lo];
+        if (!(qs < -1.e-2)) continue;
+        for (int cj = 0; cj < m.nC[vj - 1]; ++cj)
+          if (m.C[(size_t)cj * m.nV + vj - 1] == vi) {
+            const double rel = (fmax(0.0, u_perp_of(m, g, vj, cj, u_b, v_b)) + w_eps) / sumw[vj - m.a_lo];
+            if (rel > 1.e-6) qd = qd - qs * rel;
+          }
+      }
+    }
+    const double q = (Q_src[i] + qd) / g.A[vi - 1];
+    Qspill[i] = q;
+    Hi_new[i] = Hi_new[i] + q * dt;
+  }
+}
+
+int pack_mask_bits(Ctx* c, Geometry& G, const ufe_b200_masks* mk, int which) {   // which: MB_* bits the caller needs; missing pointers are an error
+  Mesh& M = *c->mesh;
+  const int na = M.a.n_loc();
+  const int32_t* src[8] = {mk->mask_icefree_land, mk->mask_icefree_ocean, mk->mask_grounded_ice, mk->mask_floating_ice, mk->mask_gl_gr, mk->mask_gl_fl,
+                           mk->mask_cf_gr, mk->mask_cf_fl};
+  std::vector<int> bits(na, 0);
+  for (int q = 0; q < 8; ++q) {
+    if (!(which & (1 << q))) continue;
+    UFE_CHECK(src[q], "a required mask is NULL (bit %d of land, ocean, grounded, floating, gl_gr, gl_fl, cf_gr, cf_fl)", q);
+    for (int i = 0; i < na; ++i) bits[i] |= src[q][i] ? (1 << q) : 0;
+  }
+  UFE_CUDA(cudaMemcpyAsync(G.ia[2].p + M.a.off(), bits.data(), sizeof(int) * na, cudaMemcpyHostToDevice, c->stream));
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+double decay_weight(double time, double t0, double t1, int before_start) {   // ice_thickness_safeties.f90:118-172
+  double f = 1.0;
+  if (t0 >= t1) f = 0.0;
+  else if (time <= t0) f = before_start ? 1.0 : 0.0;
+  else if (time >= t1) f = 0.0;
+  else f = 1.0 - (time - t0) / (t1 - t0);
+  return f < 0.0 ? 0.0 : (f > 1.0 ? 1.0 : f);
+}
+
 int ensure_geometry(Ctx* c) {
   UFE_CHECK(c->mesh && c->mesh->have_ops, "the geometry stage needs the mesh and its operators (ufe_b200_calc_matrix_operators)");
   Mesh& M = *c->mesh;
@@ -450,6 +588,105 @@ int ufe_b200_calc_grounded_fractions(ufe_b200_handle h, const ufe_b200_config* c
     UFE_TRY(down_a(c, fraction_gr, G.a[5].p));
     UFE_CUDA(cudaMemcpyAsync(fraction_gr_b, G.b[1].p + M.b.off(), sizeof(double) * nb, cudaMemcpyDeviceToHost, st));
   }
+  UFE_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+void ufe_b200_alter_params_defaults(ufe_b200_alter_params* p) {   // model_configuration_type_and_namelist.f90:424-469
+  if (!p) return;
+  *p = ufe_b200_alter_params{};
+  p->protect_grounded_mask_t_end = -9.9e9;
+  p->calving_law_threshold_thickness = 1; p->calving_threshold_thickness_shelf = 100.0;
+  p->continental_shelf_min_height = -2000.0;
+  p->fixiness_t_start = p->fixiness_t_end = 9.9e9; p->limitness_t_start = p->limitness_t_end = 9.9e9;
+  p->modiness_H_style = UFE_MODINESS_NONE; p->modiness_T_hom_ref = 20.0;
+  p->limitness_H_gl_gr = p->limitness_H_gl_fl = p->limitness_H_grounded = p->limitness_H_floating = 9.9e9;
+}
+
+int ufe_b200_alter_ice_thickness(ufe_b200_handle h, const ufe_b200_config* cfg, const ufe_b200_alter_params* prm, double time, const ufe_b200_masks* masks,
+                                 const double* Hi_old, const double* Hb, const double* SL, const double* refgeo_Hi, const double* refgeo_Hb,
+                                 const double* Ti_hom, double* Hi_new) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && cfg && prm && masks && Hi_old && Hb && SL && refgeo_Hi && refgeo_Hb && Hi_new, "ufe_b200_alter_ice_thickness: NULL argument");
+  UFE_CHECK(prm->modiness_H_style >= UFE_MODINESS_NONE && prm->modiness_H_style <= UFE_MODINESS_NO_THIN_INLAND, "unknown modiness_H_choice %d",
+            prm->modiness_H_style);                                                                   // :180-181
+  const bool need_T = prm->modiness_H_style >= UFE_MODINESS_TI_HOM && prm->modiness_H_style <= UFE_MODINESS_TI_HOM_DOWN;
+  UFE_CHECK(!need_T || Ti_hom, "ufe_b200_alter_ice_thickness: this modiness style needs Ti_hom");
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_TRY(ensure_geometry(c));
+  Mesh& M = *c->mesh; Geometry& G = *c->geo;
+  cudaStream_t st = c->stream;
+  const int na = M.a.n_loc(), off = M.a.off();
+  {
+    UFE_REGION(c, TC_H2D);
+    UFE_TRY(up_a(c, G.a[0].p, Hi_new)); UFE_TRY(up_a(c, G.a[1].p, Hb)); UFE_TRY(up_a(c, G.a[2].p, SL)); UFE_TRY(up_a(c, G.a[3].p, Hi_old));
+    UFE_TRY(up_a(c, G.a[4].p, refgeo_Hi)); UFE_TRY(up_a(c, G.a[7].p, refgeo_Hb));
+    if (need_T) UFE_TRY(up_a(c, G.a[8].p, Ti_hom));
+    UFE_TRY(pack_mask_bits(c, G, masks, MB_LAND | MB_OCEAN | MB_GROUNDED | MB_FLOATING | MB_GL_GR | MB_GL_FL));
+  }
+  // the would-be effective thickness of Hi_new (:55)
+  UFE_TRY(halo_exchange(c, M.a, G.a[0].p));
+  const GeoMesh m = geo_mesh(M);
+  const int grid = grid_for(c, na, 128, 16);
+  const double rw_ri = cfg->seawater_density / cfg->ice_density;
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_margin<<<grid, 128, 0, st>>>(m, na, off, G.a[0].p, G.ia[1].p); }
+  UFE_TRY(halo_exchange_int(c, M.a, G.ia[1].p));
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_hi_eff<<<grid, 128, 0, st>>>(m, na, off, rw_ri, G.a[0].p, G.a[1].p, G.a[2].p, G.ia[1].p, G.a[5].p, G.a[6].p); }
+  AlterDev a;
+  a.p = *prm; a.rw_over_ri = rw_ri;
+  a.fixiness = decay_weight(time, prm->fixiness_t_start, prm->fixiness_t_end, prm->do_fixiness_before_start);
+  a.limitness = decay_weight(time, prm->limitness_t_start, prm->limitness_t_end, prm->do_limitness_before_start);
+  a.protect = prm->do_protect_grounded_mask && time <= prm->protect_grounded_mask_t_end;
+  UFE_CUDA(cudaMemsetAsync(G.ia[0].p, 0, sizeof(int), st));
+  {
+    UFE_LAUNCH(c, TC_COLUMN);
+    k_geo_alter<<<grid, 128, 0, st>>>(na, off, a, G.ia[2].p, G.a[3].p, G.a[1].p, G.a[2].p, G.a[5].p, G.a[4].p, G.a[7].p, G.a[8].p, G.a[0].p, G.ia[0].p);
+  }
+  UFE_CUDA(cudaGetLastError());
+  int err = 0;
+  { UFE_REGION(c, TC_D2H); UFE_TRY(down_a(c, Hi_new, G.a[0].p)); UFE_CUDA(cudaMemcpyAsync(&err, G.ia[0].p, sizeof(int), cudaMemcpyDeviceToHost, st)); }
+  UFE_CUDA(cudaStreamSynchronize(st));
+  UFE_CHECK(!err, "vertex neither grounded, floating, nor ice-free?");
+  return 0;
+}
+
+int ufe_b200_calc_and_apply_spill_over_flux(ufe_b200_handle h, const ufe_b200_masks* masks, const double* Hi_eff, const double* u_vav_b,
+                                            const double* v_vav_b, double dt, double* Hi_new, double* Qspill) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && masks && Hi_eff && Hi_new && dt > 0.0, "ufe_b200_calc_and_apply_spill_over_flux: NULL argument or dt <= 0");
+  UFE_CHECK((u_vav_b == nullptr) == (v_vav_b == nullptr), "ufe_b200_calc_and_apply_spill_over_flux: give both velocities or neither");
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_TRY(ensure_geometry(c));
+  Mesh& M = *c->mesh; Geometry& G = *c->geo;
+  cudaStream_t st = c->stream;
+  const int na = M.a.n_loc(), nb = M.b.n_loc(), off = M.a.off();
+  const double* d_u; const double* d_v;
+  {
+    UFE_REGION(c, TC_H2D);
+    UFE_TRY(up_a(c, G.a[0].p, Hi_new));
+    UFE_TRY(pack_mask_bits(c, G, masks, MB_OCEAN | MB_CF_GR | MB_CF_FL));
+    if (u_vav_b) {
+      UFE_TRY(G.u.alloc(M.b.n_ext())); UFE_TRY(G.v.alloc(M.b.n_ext()));
+      UFE_CUDA(cudaMemcpyAsync(G.u.p + M.b.off(), u_vav_b, sizeof(double) * nb, cudaMemcpyHostToDevice, st));
+      UFE_CUDA(cudaMemcpyAsync(G.v.p + M.b.off(), v_vav_b, sizeof(double) * nb, cudaMemcpyHostToDevice, st));
+      d_u = G.u.p; d_v = G.v.p;
+    } else {
+      UFE_CHECK(c->vel && c->vel->uploaded, "ufe_b200_calc_and_apply_spill_over_flux: no velocities given and none resident on the device");
+      d_u = c->vel->u.p; d_v = c->vel->v.p;
+    }
+  }
+  (void)Hi_eff;   // ice%Hi_eff only feeds the non-calving-front branch of Hi_ups, which never produces a source (:349-356)
+  UFE_TRY(halo_exchange(c, M.a, G.a[0].p)); UFE_TRY(halo_exchange_int(c, M.a, G.ia[2].p));
+  UFE_TRY(halo_exchange(c, M.b, const_cast<double*>(d_u))); UFE_TRY(halo_exchange(c, M.b, const_cast<double*>(d_v)));
+  const GeoMesh m = geo_mesh(M);
+  const SpillMesh g{M.A.p, M.D_x.p, M.D_y.p, M.D.p};
+  const double w_eps = (double)1.e-2f;   // `real(dp) :: w_eps = 1.e-2`, a default-real literal (:309)
+  const int grid = grid_for(c, na, 128, 16);
+  { UFE_LAUNCH(c, TC_THICKNESS); k_geo_spill_src<<<grid, 128, 0, st>>>(m, g, na, off, dt, w_eps, G.ia[2].p, G.a[0].p, d_u, d_v, G.a[5].p, G.a[6].p); }
+  UFE_TRY(halo_exchange(c, M.a, G.a[5].p)); UFE_TRY(halo_exchange(c, M.a, G.a[6].p));
+  { UFE_LAUNCH(c, TC_THICKNESS); k_geo_spill_dst<<<grid, 128, 0, st>>>(m, g, na, off, dt, w_eps, G.ia[2].p, d_u, d_v, G.a[5].p, G.a[6].p, G.a[0].p, G.a[7].p); }
+  UFE_CUDA(cudaGetLastError());
+  { UFE_REGION(c, TC_D2H); UFE_TRY(down_a(c, Hi_new, G.a[0].p)); UFE_TRY(down_a(c, Qspill, G.a[7].p)); }
   UFE_CUDA(cudaStreamSynchronize(st));
   return 0;
 }

@@ -129,6 +129,31 @@ def alloc_masks(n):
     return Masks(*[ip(arrs[k]) for k in MASK_FIELDS]), arrs
 
 
+class AlterParams(C.Structure):
+    """C% scalars of alter_ice_thickness (include/ufe_b200.h: ufe_b200_alter_params)"""
+    _fields_ = [("do_protect_grounded_mask", C.c_int32), ("protect_grounded_mask_t_end", C.c_double), ("Hi_min", C.c_double),
+                ("calving_law_threshold_thickness", C.c_int32), ("calving_threshold_thickness_shelf", C.c_double),
+                ("remove_ice_absent_at_PD", C.c_int32), ("do_remove_shelves", C.c_int32), ("remove_shelves_larger_than_PD", C.c_int32),
+                ("continental_shelf_calving", C.c_int32), ("continental_shelf_min_height", C.c_double),
+                ("fixiness_t_start", C.c_double), ("fixiness_t_end", C.c_double), ("do_fixiness_before_start", C.c_int32),
+                ("limitness_t_start", C.c_double), ("limitness_t_end", C.c_double), ("do_limitness_before_start", C.c_int32),
+                ("modiness_H_style", C.c_int32), ("modiness_T_hom_ref", C.c_double),
+                ("fixiness_H_gl_gr", C.c_double), ("fixiness_H_gl_fl", C.c_double), ("fixiness_H_grounded", C.c_double), ("fixiness_H_floating", C.c_double),
+                ("fixiness_H_freeland", C.c_int32), ("fixiness_H_freeocean", C.c_int32),
+                ("limitness_H_gl_gr", C.c_double), ("limitness_H_gl_fl", C.c_double), ("limitness_H_grounded", C.c_double), ("limitness_H_floating", C.c_double)]
+
+
+def alter_params_defaults():
+    p = AlterParams()
+    lib().ufe_b200_alter_params_defaults(C.byref(p))
+    return p
+
+
+def masks_struct(arrs):
+    """Masks pointing into a dict of int32 arrays (missing keys -> NULL)"""
+    return Masks(*[ip(arrs.get(k)) for k in MASK_FIELDS])
+
+
 class VerticalVelocityIO(C.Structure):
     _fields_ = [(n, c_dp) for n in ("Hi", "Hs", "Hib", "dHb_dt", "dHi_dt", "BMB")] + [("mask_grounded_ice", c_ip), ("mask_floating_ice", c_ip),
                                                                                       ("w_3D", c_dp), ("dw_dz_3D", c_dp)]
@@ -234,6 +259,10 @@ def lib():
     L.ufe_b200_calc_grounded_fractions.argtypes = [H, PC, C.c_int, C.c_int, c_dp, c_dp, c_dp, c_dp, c_ip, c_dp, c_dp, c_dp, c_dp]
     L.ufe_b200_calc_critical_timestep_adv.argtypes = [H, PC, C.c_int, c_dp, c_ip, c_dp, c_dp, C.POINTER(C.c_double)]
     L.ufe_b200_calc_critical_timestep_SIA.argtypes = [H, PC, c_dp, c_dp, C.POINTER(C.c_double)]
+    L.ufe_b200_alter_params_defaults.restype = None
+    L.ufe_b200_alter_params_defaults.argtypes = [C.POINTER(AlterParams)]
+    L.ufe_b200_alter_ice_thickness.argtypes = [H, PC, C.POINTER(AlterParams), C.c_double, C.POINTER(Masks), c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]
+    L.ufe_b200_calc_and_apply_spill_over_flux.argtypes = [H, C.POINTER(Masks), c_dp, c_dp, c_dp, C.c_double, c_dp, c_dp]
     L.ufe_b200_calc_vertical_velocities.argtypes = [H, C.POINTER(Config), C.POINTER(VerticalVelocityIO)]
     L.ufe_b200_timing_enable.argtypes = [H, C.c_int]
     L.ufe_b200_timing_get.argtypes = [H, C.c_char_p, c_dp, C.POINTER(C.c_longlong)]
@@ -256,7 +285,8 @@ ABI_SYMBOLS = [
     "ufe_b200_solve_DIVA", "ufe_b200_solve_SSA", "ufe_b200_velocity_upload", "ufe_b200_velocity_solve_resident",
     "ufe_b200_velocity_download", "ufe_b200_thickness_upload", "ufe_b200_pc_step_resident", "ufe_b200_pc_step",
     "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA", "ufe_b200_calc_secondary_velocities", "ufe_b200_calc_vertical_velocities", "ufe_b200_set_state_resident", "ufe_b200_determine_masks", "ufe_b200_calc_effective_thickness",
-               "ufe_b200_calc_grounded_fractions", "ufe_b200_calc_critical_timestep_adv", "ufe_b200_calc_critical_timestep_SIA",
+               "ufe_b200_calc_grounded_fractions", "ufe_b200_calc_critical_timestep_adv", "ufe_b200_calc_critical_timestep_SIA", "ufe_b200_alter_params_defaults", "ufe_b200_alter_ice_thickness",
+               "ufe_b200_calc_and_apply_spill_over_flux",
     "ufe_b200_timing_enable", "ufe_b200_timing_get", "ufe_b200_timing_reset", "ufe_b200_timer_start", "ufe_b200_timer_stop",
     "ufe_b200_host_register", "ufe_b200_host_unregister"]
 
