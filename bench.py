@@ -199,17 +199,25 @@ def surf(Hi, Hb, SL, cfg):
     return Hi + np.maximum(SL - cfg.ice_density / cfg.seawater_density * Hi, Hb)
 
 
-def pc_step_host(calc_dHi_dt, solve_velocity, w, cfg, sl_a, S, dt):
+def pc_step_host(calc_dHi_dt, solve_velocity, w, cfg, sl_a, S, dt, geometry=None):
     """One predictor-corrector step through host buffers (the call sequence of predictor_corrector_scheme.f90:118-233).
     S: dict with Hi, dHdt_nm1, dt_n, ice (IceInputs builder), velocity state arrays.  Used by the e2e leg (GPU C ABI)
-    and by the CPU reference arm (oracle) alike; only `calc_dHi_dt` / `solve_velocity` differ."""
+    and by the CPU reference arm (oracle) alike; only `calc_dHi_dt` / `solve_velocity` differ.
+    geometry( Hi, for_velocity): optional geometry/mask/sub-grid stage (determine_masks, calc_grounded_fractions, calc_effective_thickness;
+    :95-107, :172-179, :198-211); it updates the masks / fractions in w.f that the two callbacks read."""
     f = w.f
     Hb, SL, noice = f["Hb"][sl_a], f["SL"][sl_a], f["mask_noice"][sl_a]
     zeta = dt / S["dt_n"]
+    if geometry:
+        geometry(S["Hi"], False)
     d_n, its_p = calc_dHi_dt(S["Hi"], S["u"], S["v"], dt)                      # predictor (:129)
     d_n = np.where(noice == 1, 0.0, d_n)
     Hi_star = np.maximum(0.0, S["Hi"] + dt * ((1 + zeta / 2) * d_n - (zeta / 2) * S["dHdt_nm1"]))   # Eq. 30
+    if geometry:
+        geometry(Hi_star, True)
     nv, na = solve_velocity(Hi_star, surf(Hi_star, Hb, SL, cfg))                  # (:186) updates S["u"], S["v"], ...
+    if geometry:
+        geometry(S["Hi"], False)
     d_s, its_c = calc_dHi_dt(S["Hi"], S["u"], S["v"], dt)                      # corrector (:214)
     d_s = np.where(noice == 1, 0.0, d_s)
     S["Hi"] = np.maximum(0.0, S["Hi"] + (dt / 2) * (d_n + d_s))                  # Eq. 31

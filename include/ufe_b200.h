@@ -358,6 +358,13 @@ int ufe_b200_calc_grounded_fractions(ufe_b200_handle h, const ufe_b200_config* c
                                      const double* SL, const double* dHb, const int32_t* mask_floating_ice, const double* bedrock_cdf,
                                      const double* bedrock_cdf_b, double* fraction_gr, double* fraction_gr_b);
 
+/* Keep the geometry stage on the device inside the predictor-corrector step: after this call ufe_b200_pc_step_resident and ufe_b200_pc_step
+ * update, as run_ice_dynamics_model_pc does (time_stepping/predictor_corrector_scheme.f90:95-107, 161-183, 198-211), the masks and grounded
+ * fractions the velocity solve reads (for the predicted geometry) and fraction_margin of the thickness solves (for the current geometry)
+ * themselves instead of using the uploaded ones.  dHb, bedrock_cdf, bedrock_cdf_b as in ufe_b200_calc_grounded_fractions (NULL for
+ * UFE_GF_BILIN_INTERP_TAF); choice < 0 switches the behaviour off again. */
+int ufe_b200_geometry_resident(ufe_b200_handle h, int choice, int nbins, const double* dHb, const double* bedrock_cdf, const double* bedrock_cdf_b);
+
 /* Replace calc_critical_timestep_adv / _SIA( mesh, ice, dt_crit) (utilities/time_step_criteria.f90:80-141, 20-78); the result is the global
  * minimum (the reference's MPI_ALLREDUCE( MPI_MIN)).  u_vav_b, v_vav_b NULL = the velocities of the last device solve. */
 int ufe_b200_calc_critical_timestep_adv(ufe_b200_handle h, const ufe_b200_config* cfg, int do_grounded_only_adv_dt, const double* Hi,

@@ -162,3 +162,77 @@ def test_host_buffer_pc_step_with_resident_solver_state():
     assert results[0][3] == results[1][3]
     for a, b in zip(results[0][:3], results[1][:3]):
         assert np.array_equal(a, b)
+
+
+def test_resident_pc_steps_with_the_geometry_stage_on_the_device():
+    """ufe_b200_geometry_resident: masks, grounded fractions and margin fractions follow the evolving thickness inside the resident step;
+    the oracle runs determine_masks / calc_grounded_fractions / calc_effective_thickness between its phases as run_ice_dynamics_model_pc does"""
+    w = _workload()
+    m, cfg = w.mesh, w.cfg
+    cfg.pc_type = ub.PC_MG
+    rng = np.random.default_rng(17)
+    nbins = 11
+    dHb = 2.0 * np.sin(m.V[:, 0] / 3e5)
+    Tri = np.asarray(m.Tri) - 1
+    bins = np.linspace(-1.0, 1.0, nbins)[None, :] ** 3
+    cdf = np.asfortranarray(w.f["Hb"][:, None] + (30.0 + 40.0 * rng.random(m.nV))[:, None] * bins)
+    cdf_b = np.asfortranarray(w.f["Hb"][Tri].mean(axis=1)[:, None] + (30.0 + 40.0 * rng.random(m.nTri))[:, None] * bins)
+    choice = ub.GF_BILIN_INTERP_TAF_PLUS_BEDROCK_CDF
+    NSTEP, DTL = 3, 1.0
+    L = ub.lib()
+    ctx = ub.Context(device=0)
+    ctx.mesh_create(m); ctx.calc_matrix_operators()
+    ice, st, A = _spin_up(ctx, w)
+    io, keep = bench.thickness_io(w, slice(None), w.f["Hi"].copy())
+    ub.check(L.ufe_b200_thickness_upload(ctx.h, C.byref(io)))
+    ub.check(L.ufe_b200_geometry_resident(ctx.h, choice, nbins, ub.dp(dHb), ub.dp(cdf), ub.dp(cdf_b)))
+    nv, na, nt = C.c_int(), C.c_int(), C.c_int()
+    for _ in range(NSTEP):
+        ub.check(L.ufe_b200_pc_step_resident(ctx.h, C.byref(cfg), 1, DTL, C.byref(nv), C.byref(na), C.byref(nt)))
+    Hi_g = np.zeros(m.nV)
+    ub.check(L.ufe_b200_thickness_download(ctx.h, ub.dp(Hi_g), None, None))
+    ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
+    u_g = A["u_vav_b"].copy()
+    # the same steps with the geometry stage switched off again: the evolving masks must matter for this to be a test
+    ctx.close()
+
+    o = ol.OracleMesh(m)
+    w2 = _workload()
+    cfg2 = w2.cfg
+    st2, A2 = ub.alloc_velocity_state(m.nV, m.nTri, m.nz, fields=FIELDS)
+    out = {k: np.zeros(m.nV) for k in ("AMB", "dHi_dt", "Hi_tplusdt", "divQ")}
+    changed = []
+
+    def geometry(Hi, for_velocity):
+        f = w2.f
+        if for_velocity:
+            mk = o.determine_masks(cfg2, Hi, f["Hb"], f["SL"])
+            changed.append(int((mk["mask_grounded_ice"] != f["mask_grounded_ice"]).sum()))
+            f["mask_grounded_ice"], f["mask_icefree_land"] = mk["mask_grounded_ice"], mk["mask_icefree_land"]
+            fr, fr_b = o.calc_grounded_fractions(cfg2, choice, nbins, Hi, f["Hb"], f["SL"], dHb, mk["mask_floating_ice"], cdf, cdf_b)
+            f["fraction_gr_b"] = fr_b
+        else:
+            he, fm = o.calc_effective_thickness(cfg2, Hi, f["Hb"], f["SL"])
+            f["fraction_margin"] = fm
+
+    def calc(Hi, u, v, dt):
+        io2, _k = bench.thickness_io(w2, slice(None), Hi, u, v, out)
+        rc, _dt, its = o.calc_dHi_dt(cfg2, io2, dt)
+        assert rc == 0
+        return out["dHi_dt"].copy(), its
+
+    def solve(Hi, Hs):
+        w2.f["Hi"], w2.f["Hs"] = Hi, Hs
+        rc, a, b = o.solve_velocity(cfg2, 1, w2.ice_inputs(), st2)
+        assert rc == 0
+        return a, b
+
+    rc, _a, _b = o.solve_velocity(cfg2, 1, w2.ice_inputs(), st2)
+    assert rc == 0
+    S = dict(Hi=w2.f["Hi"].copy(), dHdt_nm1=np.zeros(m.nV), dt_n=DTL, u=A2["u_vav_b"], v=A2["v_vav_b"])
+    fgb0 = w2.f["fraction_gr_b"].copy()
+    for _ in range(NSTEP):
+        bench.pc_step_host(calc, solve, w2, cfg2, slice(None), S, DTL, geometry=geometry)
+    assert rel_l2(w2.f["fraction_gr_b"], fgb0) > 1e-3          # the stage did change what the velocity solve sees
+    assert rel_l2(Hi_g, S["Hi"]) < 1e-9, rel_l2(Hi_g, S["Hi"])
+    assert rel_l2(u_g, A2["u_vav_b"]) < 1e-6, rel_l2(u_g, A2["u_vav_b"])

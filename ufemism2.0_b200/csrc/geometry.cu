@@ -9,6 +9,7 @@
 //   is_floating, thickness_above_floatation       src/UPSY/basic/math_utilities/ice_geometry_basics.f90:20-64
 // The reference gathers every field to every process (15 gather_to_all over these routines); here one halo exchange per field that a
 // neighbour stencil reads, and each routine is one or two passes over the vertices / triangles.
+#include "geometry.cuh"
 #include "mesh.cuh"
 #include "velocity.cuh"
 
@@ -23,6 +24,11 @@ struct Geometry {
   DBuf<double> u, v;       // host-given velocities (extended b range)
   DBuf<double> D3;         // SIA diffusivity (nz, extended b range)
   DBuf<unsigned long long> dtbits;
+  // ufe_b200_geometry_resident: inputs that stay on the device for the resident time step
+  bool dynamic = false;
+  int choice = 0, nbins = 0;
+  DBuf<double> dHb_res, cdf_res, cdf_b_res;
+  DBuf<int> flag;
 };
 void geometry_free(Geometry* g) { delete g; }
 
@@ -472,13 +478,96 @@ int finish_dt(Ctx* c, Geometry& G, double dt_ice_max, double* out) {
   return 0;
 }
 
+// velocity-solve masks from the basic mask code
+__global__ void k_geo_vel_masks(int n, int off, const int* __restrict__ kind, int* __restrict__ mask_grounded_ice, int* __restrict__ mask_icefree_land,
+                                int* any_grounded) {
+  int any = 0;
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const int k = kind[off + r];
+    mask_grounded_ice[off + r] = k == 3; mask_icefree_land[off + r] = k == 1;
+    any |= k == 3;
+  }
+  if (__any_sync(0xffffffffu, any) && (threadIdx.x & 31) == 0) atomicOr(any_grounded, 1);
+}
+
 }  // namespace
+
+bool geometry_dynamic(const Ctx* c) { return c->geo && c->geo->dynamic; }
+
+int geometry_for_velocity(Ctx* c, const ufe_b200_config* cfg, double* Hi, const double* Hb, double* SL, int* mask_grounded_ice, int* mask_icefree_land,
+                          double* fraction_gr_b, int* any_grounded) {
+  UFE_TRY(ensure_geometry(c));
+  Mesh& M = *c->mesh; Geometry& G = *c->geo;
+  cudaStream_t st = c->stream;
+  const int na = M.a.n_loc(), nb = M.b.n_loc(), off = M.a.off();
+  const GeoMesh m = geo_mesh(M);
+  const double rw_ri = cfg->seawater_density / cfg->ice_density, ri_rw = cfg->ice_density / cfg->seawater_density;
+  UFE_TRY(G.flag.alloc(1));
+  UFE_CUDA(cudaMemsetAsync(G.flag.p, 0, sizeof(int), st));
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_kind<<<grid_for(c, na, 128, 16), 128, 0, st>>>(na, off, rw_ri, Hi, Hb, SL, G.ia[0].p, G.a[4].p); }
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_vel_masks<<<grid_for(c, na, 128, 16), 128, 0, st>>>(na, off, G.ia[0].p, mask_grounded_ice, mask_icefree_land, G.flag.p); }
+  UFE_TRY(halo_exchange(c, M.a, G.a[4].p)); UFE_TRY(halo_exchange_int(c, M.a, G.ia[0].p));
+  const bool need_cdf = G.choice != UFE_GF_BILIN_INTERP_TAF;
+  if (need_cdf) { UFE_TRY(halo_exchange(c, M.a, Hi)); UFE_TRY(halo_exchange(c, M.a, SL)); }
+  const Mesh::OpGroup& gab = M.grp[Mesh::G_AB];
+  {   // only the b-grid fraction feeds the velocity solve (basal friction); TAF_b is a by-product
+    UFE_LAUNCH(c, TC_TRI);
+    k_geo_frac_b<<<grid_for(c, nb, 128, 16), 128, 0, st>>>(m, nb, M.b.off(), G.choice, G.nbins, ri_rw, gab.ptr.p, gab.ind.p, gab.val[0].p, G.a[4].p, Hi, SL,
+                                                            G.dHb_res.p, G.ia[0].p, G.cdf_b_res.p, G.b[0].p, fraction_gr_b);
+  }
+  UFE_CUDA(cudaGetLastError());
+  UFE_CUDA(cudaMemcpyAsync(any_grounded, G.flag.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+  UFE_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int geometry_for_thickness(Ctx* c, const ufe_b200_config* cfg, double* Hi, const double* Hb, const double* SL, double* fraction_margin) {
+  UFE_TRY(ensure_geometry(c));
+  Mesh& M = *c->mesh; Geometry& G = *c->geo;
+  cudaStream_t st = c->stream;
+  const int na = M.a.n_loc(), off = M.a.off();
+  const GeoMesh m = geo_mesh(M);
+  const int grid = grid_for(c, na, 128, 16);
+  UFE_TRY(halo_exchange(c, M.a, Hi));
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_margin<<<grid, 128, 0, st>>>(m, na, off, Hi, G.ia[1].p); }
+  UFE_TRY(halo_exchange_int(c, M.a, G.ia[1].p));
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_hi_eff<<<grid, 128, 0, st>>>(m, na, off, cfg->seawater_density / cfg->ice_density, Hi, Hb, SL, G.ia[1].p, G.a[5].p, fraction_margin); }
+  UFE_CUDA(cudaGetLastError());
+  return 0;
+}
 
 }  // namespace ufe
 
 using namespace ufe;
 
 extern "C" {
+
+int ufe_b200_geometry_resident(ufe_b200_handle h, int choice, int nbins, const double* dHb, const double* bedrock_cdf, const double* bedrock_cdf_b) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c, "NULL handle");
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_TRY(ensure_geometry(c));
+  Mesh& M = *c->mesh; Geometry& G = *c->geo;
+  if (choice < 0) { G.dynamic = false; return 0; }
+  UFE_CHECK(choice <= UFE_GF_BILIN_INTERP_TAF_PLUS_BEDROCK_CDF, "unknown choice_subgrid_grounded_fraction %d", choice);
+  const bool need_cdf = choice != UFE_GF_BILIN_INTERP_TAF;
+  UFE_CHECK(!need_cdf || (dHb && bedrock_cdf && bedrock_cdf_b && nbins >= 2), "ufe_b200_geometry_resident: the bedrock CDFs and dHb are required");
+  UFE_CHECK(choice == UFE_GF_BEDROCK_CDF || M.Tricc.p, "ufe_b200_geometry_resident: bilin_interp_TAF needs mesh%%Tricc (ufe_b200_mesh_desc.Tricc)");
+  const int na = M.a.n_loc(), nb = M.b.n_loc();
+  cudaStream_t st = c->stream;
+  UFE_TRY(G.dHb_res.alloc(M.a.n_ext()));
+  UFE_CUDA(cudaMemsetAsync(G.dHb_res.p, 0, sizeof(double) * M.a.n_ext(), st));
+  if (need_cdf) {
+    UFE_TRY(G.cdf_res.alloc((size_t)na * nbins)); UFE_TRY(G.cdf_b_res.alloc((size_t)nb * nbins));
+    UFE_CUDA(cudaMemcpyAsync(G.dHb_res.p + M.a.off(), dHb, sizeof(double) * na, cudaMemcpyHostToDevice, st));
+    UFE_CUDA(cudaMemcpyAsync(G.cdf_res.p, bedrock_cdf, sizeof(double) * na * nbins, cudaMemcpyHostToDevice, st));
+    UFE_CUDA(cudaMemcpyAsync(G.cdf_b_res.p, bedrock_cdf_b, sizeof(double) * nb * nbins, cudaMemcpyHostToDevice, st));
+    UFE_TRY(halo_exchange(c, M.a, G.dHb_res.p));
+  }
+  UFE_CUDA(cudaStreamSynchronize(st));
+  G.choice = choice; G.nbins = nbins; G.dynamic = true;
+  return 0;
+}
 
 int ufe_b200_determine_masks(ufe_b200_handle h, const ufe_b200_config* cfg, const double* Hi, const double* Hb, const double* SL,
                              const ufe_b200_masks* out) {

@@ -3,8 +3,11 @@
 //   src/UFEMISM/ice_dynamics/time_stepping/predictor_corrector_scheme.f90:118-233 (Robinson et al., 2020, Eqs. 30-31)
 // with the three device phases back to back and no field leaving HBM in between.  The host-side stages the
 // reference runs between them (alter_ice_thickness, determine_masks, calc_grounded_fractions,
-// calc_effective_thickness, truncation-error based dt control) are NOT part of this path: masks and
-// sub-grid fractions stay as uploaded, only Hs follows the predicted thickness (ice_geometry_basics.f90:33).
+// calc_effective_thickness) run on the device too once ufe_b200_geometry_resident switched them on: masks and grounded
+// fractions of the predicted geometry for the velocity solve, fraction_margin of the current geometry for the two thickness solves
+// (geometry.cu).  Otherwise masks and sub-grid fractions stay as uploaded and only Hs follows the predicted thickness
+// (ice_geometry_basics.f90:33).  alter_ice_thickness and the truncation-error based dt control stay with the host.
+#include "geometry.cuh"
 #include "mesh.cuh"
 #include "thickness.cuh"
 #include "velocity.cuh"
@@ -66,6 +69,9 @@ static int pc_step_core(Ctx* c, const ufe_b200_config* cfg, int approximation, d
   const double rho_ratio = cfg->ice_density / cfg->seawater_density;
   int its_p = 0, its_c = 0;
   double dt_p = dt, dt_c = dt;
+  const bool dynamic = geometry_dynamic(c);
+  // effective thickness / margin fraction of the current geometry (:107; the same values serve the corrector, :211)
+  if (dynamic) UFE_TRY(geometry_for_thickness(c, cfg, T.Hi.p, T.Hb.p, T.SL.p, T.fraction_margin.p));
   // predictor: dHi_dt( Hi_n, u_n) (:129)
   UFE_TRY(halo_exchange(c, M.b, V.u.p)); UFE_TRY(halo_exchange(c, M.b, V.v.p));
   UFE_TRY(thickness_step(c, cfg, V.u.p, V.v.p, &dt_p, 1, &its_p));
@@ -73,6 +79,19 @@ static int pc_step_core(Ctx* c, const ufe_b200_config* cfg, int approximation, d
   { UFE_LAUNCH(c, TC_THICKNESS); k_pc_predict<<<grid, 128, 0, st>>>(n, M.a.off(), dt, zeta, rho_ratio, T.mask_noice.p, T.Hi.p, P.dHdt_n.p, P.dHdt_nm1.p, T.Hb.p, T.SL.p, V.Hi.p, V.Hs.p); }
   // velocities for the predicted geometry (:186)
   UFE_TRY(before_velocity());
+  if (dynamic) {   // masks and grounded fractions of the predicted geometry (:172-179)
+    int any = 0;
+    UFE_TRY(geometry_for_velocity(c, cfg, V.Hi.p, T.Hb.p, T.SL.p, V.mask_grounded_ice.p, V.mask_icefree_land.p, V.fraction_gr_b.p, &any));
+    if (c->nranks > 1) {   // MPI_ALLREDUCE( ..., MPI_LOR, ...) (DIVA_solver_infinite_slab.f90:88)
+      double f = any;
+      UFE_CUDA(cudaMemcpyAsync(V.red.p + 4, &f, sizeof(double), cudaMemcpyHostToDevice, st));
+      UFE_TRY(allreduce_sum(c, V.red.p + 4, 1));
+      UFE_CUDA(cudaMemcpyAsync(&f, V.red.p + 4, sizeof(double), cudaMemcpyDeviceToHost, st));
+      UFE_CUDA(cudaStreamSynchronize(st));
+      any = f > 0.0;
+    }
+    V.grounded_ice_exists = any;
+  }
   UFE_TRY(velocity_solve(c, cfg, approximation, n_visc_its, n_Axb_its_velocity));
   UFE_TRY(after_velocity());
   // corrector: dHi_dt( Hi_n, u_np1) (:214)

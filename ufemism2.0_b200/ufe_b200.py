@@ -259,6 +259,7 @@ def lib():
     L.ufe_b200_calc_grounded_fractions.argtypes = [H, PC, C.c_int, C.c_int, c_dp, c_dp, c_dp, c_dp, c_ip, c_dp, c_dp, c_dp, c_dp]
     L.ufe_b200_calc_critical_timestep_adv.argtypes = [H, PC, C.c_int, c_dp, c_ip, c_dp, c_dp, C.POINTER(C.c_double)]
     L.ufe_b200_calc_critical_timestep_SIA.argtypes = [H, PC, c_dp, c_dp, C.POINTER(C.c_double)]
+    L.ufe_b200_geometry_resident.argtypes = [H, C.c_int, C.c_int, c_dp, c_dp, c_dp]
     L.ufe_b200_alter_params_defaults.restype = None
     L.ufe_b200_alter_params_defaults.argtypes = [C.POINTER(AlterParams)]
     L.ufe_b200_alter_ice_thickness.argtypes = [H, PC, C.POINTER(AlterParams), C.c_double, C.POINTER(Masks), c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]
@@ -285,7 +286,7 @@ ABI_SYMBOLS = [
     "ufe_b200_solve_DIVA", "ufe_b200_solve_SSA", "ufe_b200_velocity_upload", "ufe_b200_velocity_solve_resident",
     "ufe_b200_velocity_download", "ufe_b200_thickness_upload", "ufe_b200_pc_step_resident", "ufe_b200_pc_step",
     "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA", "ufe_b200_calc_secondary_velocities", "ufe_b200_calc_vertical_velocities", "ufe_b200_set_state_resident", "ufe_b200_determine_masks", "ufe_b200_calc_effective_thickness",
-               "ufe_b200_calc_grounded_fractions", "ufe_b200_calc_critical_timestep_adv", "ufe_b200_calc_critical_timestep_SIA", "ufe_b200_alter_params_defaults", "ufe_b200_alter_ice_thickness",
+               "ufe_b200_calc_grounded_fractions", "ufe_b200_calc_critical_timestep_adv", "ufe_b200_calc_critical_timestep_SIA", "ufe_b200_alter_params_defaults", "ufe_b200_geometry_resident", "ufe_b200_alter_ice_thickness",
                "ufe_b200_calc_and_apply_spill_over_flux",
     "ufe_b200_timing_enable", "ufe_b200_timing_get", "ufe_b200_timing_reset", "ufe_b200_timer_start", "ufe_b200_timer_stop",
     "ufe_b200_host_register", "ufe_b200_host_unregister"]
