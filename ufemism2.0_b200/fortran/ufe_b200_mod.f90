@@ -54,7 +54,7 @@ module ufe_b200_mod
   type, bind(C) :: ufe_b200_mesh_desc
     integer(c_int32_t) :: nV, nTri, nE, nC_mem, nz
     real(c_double)     :: xmin, xmax, ymin, ymax
-    type(c_ptr) :: V, nC, C, niTri, iTri, VBI, Tri, TriC, TriBI, TriGC, A, Cw, D_x, D_y, D, VE, ETri, zeta
+    type(c_ptr) :: V, nC, C, niTri, iTri, VBI, Tri, TriC, TriBI, TriGC, A, Cw, D_x, D_y, D, VE, ETri, zeta, Tricc
   end type ufe_b200_mesh_desc
 
   interface
@@ -167,6 +167,90 @@ module ufe_b200_mod
       integer(c_int) :: ierr
     end function
 
+    ! geometry / mask / sub-grid stage (SURVEY 8f-1); logical masks travel as integer(c_int32_t) 0/1 arrays, the structs as c_loc
+    function c_ufe_b200_determine_masks( h, cfg, Hi, Hb, SL, masks) bind(C, name='ufe_b200_determine_masks') result( ierr)
+      import :: c_int, c_double, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      real(c_double), intent(in) :: Hi(*), Hb(*), SL(*)
+      type(c_ptr), value :: masks                     ! c_loc of 11 c_ptr: mask, icefree_land, icefree_ocean, grounded_ice, floating_ice, margin, gl_gr, gl_fl, cf_gr, cf_fl, coastline
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_calc_effective_thickness( h, cfg, Hi, Hb, SL, Hi_eff, fraction_margin) bind(C, name='ufe_b200_calc_effective_thickness') result( ierr)
+      import :: c_int, c_double, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      real(c_double), intent(in) :: Hi(*), Hb(*), SL(*)
+      real(c_double), intent(out) :: Hi_eff(*), fraction_margin(*)
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_calc_grounded_fractions( h, cfg, choice, nbins, Hi, Hb, SL, dHb, mask_floating_ice, bedrock_cdf, bedrock_cdf_b, &
+      fraction_gr, fraction_gr_b) bind(C, name='ufe_b200_calc_grounded_fractions') result( ierr)
+      import :: c_int, c_int32_t, c_double, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      integer(c_int), value :: choice, nbins          ! 0 'bilin_interp_TAF', 1 'bedrock_CDF', 2 'bilin_interp_TAF+bedrock_CDF'; C%subgrid_bedrock_cdf_nbins
+      real(c_double), intent(in) :: Hi(*), Hb(*), SL(*), dHb(*), bedrock_cdf(*), bedrock_cdf_b(*)
+      integer(c_int32_t), intent(in) :: mask_floating_ice(*)
+      real(c_double), intent(out) :: fraction_gr(*), fraction_gr_b(*)
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_geometry_resident( h, choice, nbins, dHb, bedrock_cdf, bedrock_cdf_b) bind(C, name='ufe_b200_geometry_resident') result( ierr)
+      import :: c_int, c_double, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: choice, nbins
+      real(c_double), intent(in) :: dHb(*), bedrock_cdf(*), bedrock_cdf_b(*)
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_calc_critical_timestep_adv( h, cfg, do_grounded_only_adv_dt, Hi, mask_floating_ice, u_vav_b, v_vav_b, dt_crit_adv) &
+      bind(C, name='ufe_b200_calc_critical_timestep_adv') result( ierr)
+      import :: c_int, c_int32_t, c_double, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      integer(c_int), value :: do_grounded_only_adv_dt
+      real(c_double), intent(in) :: Hi(*)
+      integer(c_int32_t), intent(in) :: mask_floating_ice(*)
+      type(c_ptr), value :: u_vav_b, v_vav_b          ! c_loc( ice%u_vav_b) / c_null_ptr = the velocities of the last device solve
+      real(c_double), intent(out) :: dt_crit_adv
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_calc_critical_timestep_SIA( h, cfg, Hi, D_3D_b, dt_crit_SIA) bind(C, name='ufe_b200_calc_critical_timestep_SIA') result( ierr)
+      import :: c_int, c_double, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      real(c_double), intent(in) :: Hi(*), D_3D_b(*)
+      real(c_double), intent(out) :: dt_crit_SIA
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_alter_ice_thickness( h, cfg, prm, time, masks, Hi_old, Hb, SL, refgeo_Hi, refgeo_Hb, Ti_hom, Hi_new) &
+      bind(C, name='ufe_b200_alter_ice_thickness') result( ierr)
+      import :: c_int, c_double, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      type(c_ptr), value :: prm, masks                ! c_loc of a ufe_b200_alter_params / ufe_b200_masks mirror
+      real(c_double), value :: time
+      real(c_double), intent(in) :: Hi_old(*), Hb(*), SL(*), refgeo_Hi(*), refgeo_Hb(*), Ti_hom(*)
+      real(c_double), intent(inout) :: Hi_new(*)
+      integer(c_int) :: ierr
+    end function
+
+    function c_ufe_b200_calc_and_apply_spill_over_flux( h, masks, Hi_eff, u_vav_b, v_vav_b, dt, Hi_new, Qspill) &
+      bind(C, name='ufe_b200_calc_and_apply_spill_over_flux') result( ierr)
+      import :: c_int, c_double, c_ptr
+      type(c_ptr), value :: h, masks, u_vav_b, v_vav_b
+      real(c_double), intent(in) :: Hi_eff(*)
+      real(c_double), value :: dt
+      real(c_double), intent(inout) :: Hi_new(*)
+      real(c_double), intent(out) :: Qspill(*)
+      integer(c_int) :: ierr
+    end function
+
     function c_ufe_b200_set_state_resident( h, on) bind(C, name='ufe_b200_set_state_resident') result( ierr)
       import :: c_int, c_ptr
       type(c_ptr), value :: h
@@ -268,6 +352,7 @@ contains
     d%VBI = c_loc( mesh%VBI); d%Tri = c_loc( mesh%Tri); d%TriC = c_loc( mesh%TriC); d%TriBI = c_loc( mesh%TriBI)
     d%TriGC = c_loc( mesh%TriGC); d%A = c_loc( mesh%A); d%Cw = c_loc( mesh%Cw); d%D_x = c_loc( mesh%D_x); d%D_y = c_loc( mesh%D_y)
     d%D = c_loc( mesh%D); d%VE = c_loc( mesh%VE); d%ETri = c_loc( mesh%ETri); d%zeta = c_loc( mesh%zeta)
+    d%Tricc = c_loc( mesh%Tricc)
     call check( c_ufe_b200_mesh_create( handle, d), routine_name)
     call check( c_ufe_b200_calc_matrix_operators( handle), routine_name)
     call finalise_routine( routine_name)
