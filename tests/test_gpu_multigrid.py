@@ -154,3 +154,31 @@ def test_single_cta_tail_equals_separate_launches():
     finally:
         os.environ.pop("UFE_B200_MG_TAIL", None)
     assert res[0][2] == res[1][2] and np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1])
+
+
+def test_assembly_writes_the_blocked_matrix_directly():
+    """the assembly kernels fill the blocked sliced-ELL copy in the same pass; UFE_B200_BLK_SCATTER=1 forces the separate scatter pass -- same bits"""
+    import os
+    w = wl.mismip_mod(2.0e4)
+    m = w.mesh
+    co = _coefficients(m, seed=8)
+    cfg = wl.scaling_config()
+    res = []
+    try:
+        for scatter in (True, False):
+            if scatter:
+                os.environ["UFE_B200_BLK_SCATTER"] = "1"
+            else:
+                os.environ.pop("UFE_B200_BLK_SCATTER", None)
+            ctx = ub.Context(device=0)
+            ctx.mesh_create(m); ctx.calc_matrix_operators()
+            for pc in (ub.PC_JACOBI, ub.PC_MG):
+                cfg.pc_type = pc
+                res.append(_linearised(ctx, cfg, m, *co, 1e-10, 1e-30))
+                res.append(_linearised(ctx, cfg, m, *[1.1 * a for a in co], 1e-10, 1e-30))      # second assembly on the existing pattern
+            ctx.close()
+    finally:
+        os.environ.pop("UFE_B200_BLK_SCATTER", None)
+    n = len(res) // 2
+    for a, b in zip(res[:n], res[n:]):
+        assert a[2] == b[2] and np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])

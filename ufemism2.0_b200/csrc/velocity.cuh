@@ -32,6 +32,7 @@ struct Velocity {
   DBuf<int> row_kind;          // per matrix row: 0 free, 1 identity (prescribed / 'zero'), 2 'infinite'
   DBuf<double> bb, uv;         // load vector (owned rows), solution (extended buv range)
   BlkMat blk;                  // 2x2-blocked sliced-ELL copy of A that the Krylov solver streams
+  bool blk_filled = false;     // the last assembly wrote blk.val itself (no scatter pass needed)
   Mg mg;                       // multigrid preconditioner on the pattern of blk (pc_type = UFE_PC_MG)
   unsigned long long pattern_key = 0;
   bool pattern_valid = false;
