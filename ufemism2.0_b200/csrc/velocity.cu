@@ -270,7 +270,7 @@ struct StiffArgs {
   int* A_ptr; int* A_ind; double* A_val; int* row_kind; double* bb;
   // when the blocked sliced-ELL copy exists the assembly writes it in the same pass (blk.cu: map = CSR position -> slot), which saves the
   // separate scatter pass over both formats (6 ms per viscosity iteration at 4 M vertices)
-  double* blk_val; const int* blk_map;
+  double* blk_val; const int* blk_map; const int* blk_slice_ptr;
 };
 
 __device__ __forceinline__ void put(const StiffArgs& s, int k, double v) {
@@ -348,6 +348,10 @@ __device__ __forceinline__ void assemble_triangle(const StiffArgs& s, const VelP
       put(s, k, -1.0 * (double)nn);
       s.bb[row] = 0.0;
     } else {
+      // both rows of the triangle free (almost all): the blocked copy lists the neighbours in the order of this loop (blk.cu: order of first
+      // appearance), so the slot follows from q alone and the 32 triangles of a slice write 32 consecutive doubles -- no map lookup
+      const bool direct = s.blk_map && s.row_kind[2 * r] == 0 && s.row_kind[2 * r + 1] == 0;
+      double* bslot = direct ? s.blk_val + ((size_t)s.blk_slice_ptr[r >> 5] * 4 + uv * 2) * 32 + (r & 31) : nullptr;
       for (int q = s.m2_ptr[r]; q < s.m2_ptr[r + 1]; ++q) {
         const bool is_self = (s.m2_ind[q] == self);
         const double ddx = s.m2_ddx[q], ddy = s.m2_ddy[q], dxx = s.m2_dxx[q], dxy = s.m2_dxy[q], dyy = s.m2_dyy[q];
@@ -366,8 +370,8 @@ __device__ __forceinline__ void assemble_triangle(const StiffArgs& s, const VelP
           if (uv == 0) { Au = 4.0 * dxx + dyy; if (is_self) Au = Au - beta / N; Av = 3.0 * dxy; }
           else { Av = 4.0 * dyy + dxx; if (is_self) Av = Av - beta / N; Au = 3.0 * dxy; }
         }
-        put(s, k++, Au);
-        put(s, k++, Av);
+        if (direct) { s.A_val[k++] = Au; s.A_val[k++] = Av; bslot[0] = Au; bslot[32] = Av; bslot += 128; }
+        else { put(s, k++, Au); put(s, k++, Av); }
       }
       const double tau = (uv == 0) ? tdx : tdy;
       s.bb[row] = p.crossterms ? -tau : -tau / N;
@@ -535,7 +539,7 @@ static StiffArgs stiff_args(Ctx* c) {
   s.m2_ddx = g.val[0].p; s.m2_ddy = g.val[1].p; s.m2_dxx = g.val[2].p; s.m2_dxy = g.val[3].p; s.m2_dyy = g.val[4].p;
   s.A_ptr = V.A.ptr; s.A_ind = V.A.ind; s.A_val = V.A.val; s.row_kind = V.row_kind.p; s.bb = V.bb.p;
   const bool direct = V.blk.valid && V.blk.map.p && V.blk.val.p && !getenv("UFE_B200_BLK_SCATTER");
-  s.blk_val = direct ? V.blk.val.p : nullptr; s.blk_map = direct ? V.blk.map.p : nullptr;
+  s.blk_val = direct ? V.blk.val.p : nullptr; s.blk_map = direct ? V.blk.map.p : nullptr; s.blk_slice_ptr = V.blk.slice_ptr.p;
   return s;
 }
 
