@@ -274,7 +274,7 @@ struct StiffArgs {
 };
 
 __device__ __forceinline__ void put(const StiffArgs& s, int k, double v) {
-  s.A_val[k] = v;
+  if (s.A_val) s.A_val[k] = v;
   if (s.blk_map) s.blk_val[s.blk_map[k]] = v;
 }
 
@@ -370,7 +370,10 @@ __device__ __forceinline__ void assemble_triangle(const StiffArgs& s, const VelP
           if (uv == 0) { Au = 4.0 * dxx + dyy; if (is_self) Au = Au - beta / N; Av = 3.0 * dxy; }
           else { Av = 4.0 * dyy + dxx; if (is_self) Av = Av - beta / N; Au = 3.0 * dxy; }
         }
-        if (direct) { s.A_val[k++] = Au; s.A_val[k++] = Av; bslot[0] = Au; bslot[32] = Av; bslot += 128; }
+        if (direct) {
+          if (s.A_val) { s.A_val[k] = Au; s.A_val[k + 1] = Av; }
+          k += 2; bslot[0] = Au; bslot[32] = Av; bslot += 128;
+        }
         else { put(s, k++, Au); put(s, k++, Av); }
       }
       const double tau = (uv == 0) ? tdx : tdy;
@@ -529,7 +532,8 @@ int ensure_velocity(Ctx* c) {
   return 0;
 }
 
-static StiffArgs stiff_args(Ctx* c) {
+// skip_csr: only the blocked copy is wanted (FP64 multigrid solve); the CSR values are re-formed on demand (ensure_csr_values)
+static StiffArgs stiff_args(Ctx* c, bool skip_csr = false) {
   Mesh& M = *c->mesh; Velocity& V = *c->vel;
   StiffArgs s;
   s.n = M.b.n_loc(); s.off = M.b.off(); s.ti1 = M.b.i1; s.b_lo = M.b.lo; s.nTri = M.nTri;
@@ -540,7 +544,26 @@ static StiffArgs stiff_args(Ctx* c) {
   s.A_ptr = V.A.ptr; s.A_ind = V.A.ind; s.A_val = V.A.val; s.row_kind = V.row_kind.p; s.bb = V.bb.p;
   const bool direct = V.blk.valid && V.blk.map.p && V.blk.val.p && !getenv("UFE_B200_BLK_SCATTER");
   s.blk_val = direct ? V.blk.val.p : nullptr; s.blk_map = direct ? V.blk.map.p : nullptr; s.blk_slice_ptr = V.blk.slice_ptr.p;
+  if (skip_csr && direct) s.A_val = nullptr;
   return s;
+}
+
+// The CSR values are only read by the CSR / Jacobi solves, the FP32 multigrid storage and ufe_b200_get_stiffness; the default FP64 multigrid
+// solve streams the blocked copy alone, so the assembly then leaves the (uncoalesced) CSR value writes out.
+static bool csr_values_unneeded(Ctx* c, const ufe_b200_config* cfg) {
+  return cfg->pc_type == UFE_PC_MG && cfg->stiffness_format != 1 && !c->mg_params.fp32 && !getenv("UFE_B200_BLK_SCATTER");
+}
+__global__ void k_blk_gather(long long nnz, const int* __restrict__ map, const double* __restrict__ bv, double* __restrict__ v) {
+  for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += (long long)gridDim.x * blockDim.x) v[k] = bv[map[k]];
+}
+static int ensure_csr_values(Ctx* c) {
+  Velocity& V = *c->vel;
+  if (!V.csr_stale) return 0;
+  UFE_LAUNCH(c, TC_ASSEMBLY);
+  k_blk_gather<<<grid_for(c, V.A.nnz, 256), 256, 0, c->stream>>>(V.A.nnz, V.blk.map.p, V.blk.val.p, V.A.val);
+  UFE_CUDA(cudaGetLastError());
+  V.csr_stale = false;
+  return 0;
 }
 
 // The sparsity pattern is a pure function of the mesh, the BC choices and the prescribed-velocity mask:
@@ -592,6 +615,7 @@ static int solve_linear_system(Ctx* c, const ufe_b200_config* cfg, double rtol, 
     UFE_LAUNCH(c, TC_EPILOGUE);
     k_interleave<<<grid_for(c, M.b.n_loc(), 128, 16), 128, 0, c->stream>>>(M.b.n_loc(), M.b.off(), V.u.p, V.v.p, V.uv.p + M.buv.off());
   }
+  if (cfg->stiffness_format == 1 || kp.pc_type != UFE_PC_MG || c->mg_params.fp32) UFE_TRY(ensure_csr_values(c));   // no-op unless the assembly skipped them
   if (cfg->stiffness_format == 1) return csr_ksp_solve(c, V.A, V.bb.p, V.uv.p, kp, TC_SPMV_STIFFNESS, its);
   UFE_CHECK(kp.ksp_type == UFE_KSP_BICGSTAB, "only BiCGStab is available for the (non-symmetric) stiffness matrix");
   if (kp.pc_type == UFE_PC_MG) {
@@ -784,7 +808,7 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
   ta.fraction_gr_b = V.fraction_gr_b.p; ta.tau_dx = V.tau_dx.p; ta.tau_dy = V.tau_dy.p;
   ta.N_b = V.N_b.p; ta.dN_dx_b = V.dN_dx_b.p; ta.dN_dy_b = V.dN_dy_b.p; ta.beta_b = V.beta_b.p; ta.beta_eff_b = V.beta_eff_b.p;
   ta.eta_3D_b = V.eta_3D_b.p; ta.F1_3D_b = V.F1_3D_b.p; ta.F2_3D_b = V.F2_3D_b.p;
-  StiffArgs sa = stiff_args(c);
+  StiffArgs sa = stiff_args(c, csr_values_unneeded(c, cfg));
 
   // adaptive relaxation (DIVA_solver_infinite_slab.f90:121-131)
   double L2_uv = 1e9, relax = cfg->visc_it_relax, eps0 = cfg->Glens_flow_law_epsilon_sq_0;
@@ -814,7 +838,7 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
     {
       UFE_LAUNCH(c, TC_ASSEMBLY);
       if (DIVA) k_tri_assemble<true><<<g_b, 128, 0, st>>>(ta, sa, p); else k_tri_assemble<false><<<g_b, 128, 0, st>>>(ta, sa, p);
-      V.blk_filled = sa.blk_map != nullptr;
+      V.blk_filled = sa.blk_map != nullptr; V.csr_stale = sa.A_val == nullptr; V.csr_stale = sa.A_val == nullptr;
     }
     { UFE_LAUNCH(c, TC_EPILOGUE); k_store_prev<<<g_b, 128, 0, st>>>(nb, M.b.off(), V.u.p, V.v.p, V.u_prev.p, V.v_prev.p); }
     int its = 0;
@@ -929,11 +953,11 @@ int ufe_b200_solve_SSA_DIVA_linearised(ufe_b200_handle h, const ufe_b200_config*
   V.uploaded = true;
   VelPar p = make_par(cfg);
   UFE_TRY(ensure_pattern(c, p, g_bc_version));
-  StiffArgs sa = stiff_args(c);
+  StiffArgs sa = stiff_args(c, csr_values_unneeded(c, cfg));
   const int g_b = grid_for(c, nb, 128, 16);
   { UFE_LAUNCH(c, TC_EPILOGUE); k_store_prev<<<g_b, 128, 0, st>>>(nb, M.b.off(), V.u.p, V.v.p, V.u_prev.p, V.v_prev.p); }
   { UFE_LAUNCH(c, TC_ASSEMBLY); k_assemble<<<g_b, 128, 0, st>>>(sa, p, V.N_b.p, V.dN_dx_b.p, V.dN_dy_b.p, V.beta_eff_b.p, V.tau_dx.p, V.tau_dy.p); }
-  V.blk_filled = sa.blk_map != nullptr;
+  V.blk_filled = sa.blk_map != nullptr; V.csr_stale = sa.A_val == nullptr;
   int its = 0;
   UFE_TRY(solve_linear_system(c, cfg, rtol, abstol, &its));
   { UFE_LAUNCH(c, TC_EPILOGUE); k_deinterleave<<<g_b, 128, 0, st>>>(nb, M.b.off(), V.uv.p + M.buv.off(), V.u.p, V.v.p); }
@@ -957,6 +981,7 @@ int ufe_b200_get_stiffness(ufe_b200_handle h, int32_t* ptr, int32_t* ind, double
   Ctx* c = reinterpret_cast<Ctx*>(h);
   UFE_CHECK(c && c->vel && c->vel->pattern_valid, "no stiffness matrix has been assembled yet");
   UFE_CUDA(cudaSetDevice(c->device));
+  UFE_TRY(ensure_csr_values(c));
   const DevCsr& A = c->vel->A;
   UFE_CUDA(cudaMemcpyAsync(ptr, A.ptr, sizeof(int) * (A.m_loc + 1), cudaMemcpyDeviceToHost, c->stream));
   UFE_CUDA(cudaMemcpyAsync(ind, A.ind, sizeof(int) * A.nnz, cudaMemcpyDeviceToHost, c->stream));

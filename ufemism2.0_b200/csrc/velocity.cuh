@@ -33,6 +33,7 @@ struct Velocity {
   DBuf<double> bb, uv;         // load vector (owned rows), solution (extended buv range)
   BlkMat blk;                  // 2x2-blocked sliced-ELL copy of A that the Krylov solver streams
   bool blk_filled = false;     // the last assembly wrote blk.val itself (no scatter pass needed)
+  bool csr_stale = false;      // ... and skipped the CSR values (re-formed from blk.val on demand)
   Mg mg;                       // multigrid preconditioner on the pattern of blk (pc_type = UFE_PC_MG)
   unsigned long long pattern_key = 0;
   bool pattern_valid = false;
