@@ -197,3 +197,24 @@ def test_resident_solve_equals_host_solve(setup):
     ub.check(L.ufe_b200_velocity_solve_resident(ctx.h, C.byref(cfg), 1, C.byref(a), C.byref(b)))
     ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
     assert (a.value, b.value) == (nv, na) and np.array_equal(arrs["u_vav_b"], g["u_vav_b"])   # deterministic reductions
+
+
+@pytest.mark.parametrize("nz", [8, 10])
+def test_diva_stages_with_other_layer_counts(nz):
+    """k_vertex_diva is specialised for nz = 8, 12, 16 (register-resident columns) with a generic fallback: one specialised and one generic count"""
+    w = wl.mismip_mod(3.0e4, nz=nz)
+    m = w.mesh
+    ctx = ub.Context(device=0)
+    ctx.mesh_create(m); ctx.calc_matrix_operators()
+    o = ol.OracleMesh(m)
+    cfg = wl.scaling_config()
+    cfg.stress_balance_PETSc_rtol = 1e-13; cfg.stress_balance_PETSc_abstol = 1e-30
+    cfg.visc_it_nit = 2; cfg.visc_it_norm_dUV_tol = 1e-30
+    ice = w.ice_inputs()
+    g, nv, na = _solve_gpu(ctx, cfg, 1, ice, m)
+    ctx.close()
+    st2, r = ub.alloc_velocity_state(m.nV, m.nTri, m.nz)
+    rc, nv2, na2 = o.solve_velocity(cfg, 1, ice, st2)
+    assert rc == 0 and nv == nv2 == 3
+    for f in _FIELDS:
+        assert rel_l2(g[f], r[f]) < 1e-8, (f, rel_l2(g[f], r[f]))

@@ -185,12 +185,17 @@ struct VertexArgs {
 // DIVA: calc_horizontal_strain_rates, calc_vertical_shear_strain_rates, calc_effective_viscosity (a-grid part),
 // calc_F_integrals (a-grid part), calc_effective_basal_friction_coefficient (a-grid part)
 // (DIVA_solver_infinite_slab.f90:138-151, 235-457)
+// NZ > 0: the number of layers is a compile-time constant, every layer loop unrolls and the three per-column arrays live in registers; with a
+// run-time nz (NZ = 0) they are local memory (3 x 256 B per thread), which no longer fits in L1 at full occupancy.  Same operations, same order.
+template <int NZ>
 __global__ void __launch_bounds__(128) k_vertex_diva(VertexArgs a, VelPar p) {
-  double dzu[kMaxNz], dzv[kMaxNz], eta[kMaxNz];
+  constexpr int kCap = NZ > 0 ? NZ : kMaxNz;
+  double dzu[kCap], dzv[kCap], eta[kCap];
   for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < a.n; r += (long long)gridDim.x * blockDim.x) {
     const size_t i = a.off + r;
-    const int nz = a.nz;
+    const int nz = NZ > 0 ? NZ : a.nz;
     double du_dx = 0, du_dy = 0, dv_dx = 0, dv_dy = 0, ub = 0, vb = 0;
+#pragma unroll
     for (int k = 0; k < nz; ++k) { dzu[k] = 0.0; dzv[k] = 0.0; }
     for (int q = a.ptr[r]; q < a.ptr[r + 1]; ++q) {
       const int tj = a.ind[q];
@@ -199,6 +204,7 @@ __global__ void __launch_bounds__(128) k_vertex_diva(VertexArgs a, VelPar p) {
       du_dx += wx * uj; du_dy += wy * uj; dv_dx += wx * vj; dv_dy += wy * vj;
       ub += wm * a.u_base[tj]; vb += wm * a.v_base[tj];
       const double tbx = a.tau_bx[tj], tby = a.tau_by[tj];
+#pragma unroll
       for (int k = 0; k < nz; ++k) {
         const double e = fmax(p.visc_eff_min, a.eta_3D_b[(size_t)k * a.nb_ext + tj]);
         dzu[k] += wm * (tbx * a.zeta[k] / e);
@@ -206,6 +212,7 @@ __global__ void __launch_bounds__(128) k_vertex_diva(VertexArgs a, VelPar p) {
       }
     }
     const double hs = du_dx * du_dx + dv_dy * dv_dy + du_dx * dv_dy + 0.25 * (du_dy + dv_dx) * (du_dy + dv_dx);
+#pragma unroll
     for (int k = 0; k < nz; ++k) {
       const double eps_sq = hs + 0.25 * (dzu[k] * dzu[k] + dzv[k] * dzv[k]) + p.eps0;
       const double e = fmin(fmax(glen_eta(a.A_flow[(size_t)k * a.n_ext + i], eps_sq, p.n_glen), p.visc_eff_min), p.eta_max);
@@ -213,6 +220,7 @@ __global__ void __launch_bounds__(128) k_vertex_diva(VertexArgs a, VelPar p) {
       a.eta_3D_a[(size_t)k * a.n_ext + i] = e;
     }
     double vav = 0.0;
+#pragma unroll
     for (int k = 0; k < nz - 1; ++k) vav = vav + 0.5 * (eta[k + 1] + eta[k]) * (a.zeta[k + 1] - a.zeta[k]);
     const double Hi = a.Hi[i];
     a.N_a[i] = vav * fmax((double)0.1f, Hi);   // max( 0.1, Hi) with a default-real literal (DIVA_solver_infinite_slab.f90:341)
@@ -221,6 +229,7 @@ __global__ void __launch_bounds__(128) k_vertex_diva(VertexArgs a, VelPar p) {
     double i1 = 0.0, i2 = 0.0;
     a.F1_3D_a[(size_t)(nz - 1) * a.n_ext + i] = Hc * 0.0;
     a.F2_3D_a[(size_t)(nz - 1) * a.n_ext + i] = Hc * 0.0;
+#pragma unroll
     for (int k = nz - 2; k >= 0; --k) {
       const double z0 = a.zeta[k], z1 = a.zeta[k + 1];
       i1 = i1 - 0.5 * ((z1 / eta[k + 1]) + (z0 / eta[k])) * (z1 - z0);
@@ -234,6 +243,7 @@ __global__ void __launch_bounds__(128) k_vertex_diva(VertexArgs a, VelPar p) {
     a.beta_eff_a[i] = (p.sliding_law == UFE_SLID_NO_SLIDING) ? 1.0 / F2_surf : beta / (1.0 + beta * F2_surf);
     if (p.diagnostics) {
       a.du_dx[i] = du_dx; a.du_dy[i] = du_dy; a.dv_dx[i] = dv_dx; a.dv_dy[i] = dv_dy; a.eta_vav[i] = vav;
+#pragma unroll
       for (int k = 0; k < nz; ++k) { a.du_dz_3D[(size_t)k * a.n_ext + i] = dzu[k]; a.dv_dz_3D[(size_t)k * a.n_ext + i] = dzv[k]; }
     }
   }
@@ -828,7 +838,11 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
     }
     {
       UFE_LAUNCH(c, TC_COLUMN);
-      if (DIVA) k_vertex_diva<<<g_a, 128, 0, st>>>(va, p); else k_vertex_ssa<<<g_a, 128, 0, st>>>(va, p);
+      if (!DIVA) k_vertex_ssa<<<g_a, 128, 0, st>>>(va, p);
+      else if (nz == 12) k_vertex_diva<12><<<g_a, 128, 0, st>>>(va, p);   // C%nz of every shipped configuration
+      else if (nz == 8) k_vertex_diva<8><<<g_a, 128, 0, st>>>(va, p);
+      else if (nz == 16) k_vertex_diva<16><<<g_a, 128, 0, st>>>(va, p);
+      else k_vertex_diva<0><<<g_a, 128, 0, st>>>(va, p);
     }
     UFE_TRY(halo_exchange(c, M.a, V.N_a.p)); UFE_TRY(halo_exchange(c, M.a, V.beta_a.p));
     if (DIVA) {
