@@ -201,7 +201,7 @@ def test_resident_solve_equals_host_solve(setup):
 
 @pytest.mark.parametrize("nz", [8, 10])
 def test_diva_stages_with_other_layer_counts(nz):
-    """k_vertex_diva is specialised for nz = 8, 12, 16 (register-resident columns) with a generic fallback: one specialised and one generic count"""
+    """the column kernels take the number of layers at run time: layer counts other than the configurations' 12"""
     w = wl.mismip_mod(3.0e4, nz=nz)
     m = w.mesh
     ctx = ub.Context(device=0)

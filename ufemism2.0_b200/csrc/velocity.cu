@@ -185,8 +185,10 @@ struct VertexArgs {
 // DIVA: calc_horizontal_strain_rates, calc_vertical_shear_strain_rates, calc_effective_viscosity (a-grid part),
 // calc_F_integrals (a-grid part), calc_effective_basal_friction_coefficient (a-grid part)
 // (DIVA_solver_infinite_slab.f90:138-151, 235-457)
-// NZ > 0: the number of layers is a compile-time constant, every layer loop unrolls and the three per-column arrays live in registers; with a
-// run-time nz (NZ = 0) they are local memory (3 x 256 B per thread), which no longer fits in L1 at full occupancy.  Same operations, same order.
+// NZ > 0: the number of layers is a compile-time constant, every layer loop unrolls and the three per-column arrays live in registers (168
+// registers per thread); NZ = 0: run-time nz, the arrays are local memory (128 registers + 784 B of stack).  Same operations, same order.
+// Measured at 4 M vertices: 6.4 ms for NZ = 12 against 5.8 ms for NZ = 0 -- the kernel is bound by the latency of the triangle-column
+// gathers, and the register version runs fewer warps per SM; so NZ = 0 is what runs (UFE_B200_VERTEX_NZ12 selects the other for profiling).
 template <int NZ>
 __global__ void __launch_bounds__(128) k_vertex_diva(VertexArgs a, VelPar p) {
   constexpr int kCap = NZ > 0 ? NZ : kMaxNz;
@@ -839,9 +841,7 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
     {
       UFE_LAUNCH(c, TC_COLUMN);
       if (!DIVA) k_vertex_ssa<<<g_a, 128, 0, st>>>(va, p);
-      else if (nz == 12) k_vertex_diva<12><<<g_a, 128, 0, st>>>(va, p);   // C%nz of every shipped configuration
-      else if (nz == 8) k_vertex_diva<8><<<g_a, 128, 0, st>>>(va, p);
-      else if (nz == 16) k_vertex_diva<16><<<g_a, 128, 0, st>>>(va, p);
+      else if (nz == 12 && getenv("UFE_B200_VERTEX_NZ12")) k_vertex_diva<12><<<g_a, 128, 0, st>>>(va, p);
       else k_vertex_diva<0><<<g_a, 128, 0, st>>>(va, p);
     }
     UFE_TRY(halo_exchange(c, M.a, V.N_a.p)); UFE_TRY(halo_exchange(c, M.a, V.beta_a.p));
