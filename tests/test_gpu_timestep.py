@@ -236,3 +236,48 @@ def test_resident_pc_steps_with_the_geometry_stage_on_the_device():
     assert rel_l2(w2.f["fraction_gr_b"], fgb0) > 1e-3          # the stage did change what the velocity solve sees
     assert rel_l2(Hi_g, S["Hi"]) < 1e-9, rel_l2(Hi_g, S["Hi"])
     assert rel_l2(u_g, A2["u_vav_b"]) < 1e-6, rel_l2(u_g, A2["u_vav_b"])
+
+
+def test_host_buffer_pc_step_with_the_geometry_stage_equals_resident():
+    """ufe_b200_pc_step uploads the host's masks / fractions on the copy stream; with ufe_b200_geometry_resident the device's own values
+    (computed after that upload has landed) are the ones the solves use, exactly as in the resident step"""
+    w = _workload()
+    m, cfg = w.mesh, w.cfg
+    cfg.pc_type = ub.PC_MG
+    L = ub.lib()
+    nv, na, nt = C.c_int(), C.c_int(), C.c_int()
+    choice, DTL = ub.GF_BILIN_INTERP_TAF, 1.0
+    # resident
+    ctx = ub.Context(device=0)
+    ctx.mesh_create(m); ctx.calc_matrix_operators()
+    ice, st, A = _spin_up(ctx, w)
+    A0 = {k: v.copy() for k, v in A.items()}
+    io, keep = bench.thickness_io(w, slice(None), w.f["Hi"].copy())
+    ub.check(L.ufe_b200_thickness_upload(ctx.h, C.byref(io)))
+    ub.check(L.ufe_b200_geometry_resident(ctx.h, choice, 0, None, None, None))
+    for _ in range(2):
+        ub.check(L.ufe_b200_pc_step_resident(ctx.h, C.byref(cfg), 1, DTL, C.byref(nv), C.byref(na), C.byref(nt)))
+    Hi_r = np.zeros(m.nV)
+    ub.check(L.ufe_b200_thickness_download(ctx.h, ub.dp(Hi_r), None, None))
+    ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
+    u_r = A["u_vav_b"].copy()
+    its_r = (nv.value, na.value, nt.value)
+    ctx.close()
+    # host buffers; the host's own (stale) masks and fractions go up every step and must be overridden on the device
+    ctx = ub.Context(device=0)
+    ctx.mesh_create(m); ctx.calc_matrix_operators()
+    for k in A:
+        A[k][...] = A0[k]
+    ub.check(L.ufe_b200_geometry_resident(ctx.h, choice, 0, None, None, None))
+    out = {k: np.zeros(m.nV) for k in ("AMB", "dHi_dt", "Hi_tplusdt", "divQ")}
+    io2, keep2 = bench.thickness_io(w, slice(None), w.f["Hi"].copy(), out=out)
+    dH_nm1 = np.zeros(m.nV)
+    dt_prev = 0.0
+    for _ in range(2):
+        ub.check(L.ufe_b200_pc_step(ctx.h, C.byref(cfg), 1, DTL, dt_prev, C.byref(ice), C.byref(st), C.byref(io2), ub.dp(dH_nm1),
+                                    C.byref(nv), C.byref(na), C.byref(nt)))
+        keep2["Hi"][:] = out["Hi_tplusdt"]
+        dt_prev = DTL
+    ctx.close()
+    assert (nv.value, na.value, nt.value) == its_r
+    assert np.array_equal(out["Hi_tplusdt"], Hi_r) and np.array_equal(A["u_vav_b"], u_r)
