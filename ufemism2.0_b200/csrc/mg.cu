@@ -482,12 +482,24 @@ __global__ void k_mg_axpy(int n2, const double* __restrict__ a, double* __restri
 template <typename VTI, typename VTO>
 __global__ void k_mg_galerkin(long long n_cslots, const int* __restrict__ gal_ptr, const int* __restrict__ gal_src, const VTI* __restrict__ fv,
                               VTO* __restrict__ cv) {
+  constexpr int U = 4;   // source slots in flight: indices first, then their 4 x U values (same order of summation)
   for (long long cs = (long long)blockIdx.x * blockDim.x + threadIdx.x; cs < n_cslots; cs += (long long)gridDim.x * blockDim.x) {
     double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-    for (int k = gal_ptr[cs]; k < gal_ptr[cs + 1]; ++k) {
-      const int fs = gal_src[k];
-      const VTI* p = fv + ((size_t)(fs >> 5) * 128) + (fs & 31);
-      a0 += (double)p[0]; a1 += (double)p[32]; a2 += (double)p[64]; a3 += (double)p[96];
+    const int k1 = gal_ptr[cs + 1];
+    for (int k = gal_ptr[cs]; k < k1; k += U) {
+      int fs[U];
+      VTI v[U][4];
+#pragma unroll
+      for (int u = 0; u < U; ++u) fs[u] = (k + u < k1) ? gal_src[k + u] : -1;
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (fs[u] >= 0) {
+          const VTI* p = fv + ((size_t)(fs[u] >> 5) * 128) + (fs[u] & 31);
+          v[u][0] = p[0]; v[u][1] = p[32]; v[u][2] = p[64]; v[u][3] = p[96];
+        }
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (fs[u] >= 0) { a0 += (double)v[u][0]; a1 += (double)v[u][1]; a2 += (double)v[u][2]; a3 += (double)v[u][3]; }
     }
     VTO* q = cv + ((size_t)(cs >> 5) * 128) + (cs & 31);
     q[0] = (VTO)a0; q[32] = (VTO)a1; q[64] = (VTO)a2; q[96] = (VTO)a3;

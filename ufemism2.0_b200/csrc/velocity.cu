@@ -189,8 +189,8 @@ struct VertexArgs {
 // registers per thread); NZ = 0: run-time nz, the arrays are local memory (128 registers + 784 B of stack).  Same operations, same order.
 // Measured at 4 M vertices: 6.4 ms for NZ = 12 against 5.8 ms for NZ = 0 -- the kernel is bound by the latency of the triangle-column
 // gathers, and the register version runs fewer warps per SM; so NZ = 0 is what runs (UFE_B200_VERTEX_NZ12 selects the other for profiling).
-template <int NZ>
-__global__ void __launch_bounds__(128) k_vertex_diva(VertexArgs a, VelPar p) {
+template <int NZ, int MB = 6>
+__global__ void __launch_bounds__(128, MB) k_vertex_diva(VertexArgs a, VelPar p) {
   constexpr int kCap = NZ > 0 ? NZ : kMaxNz;
   double dzu[kCap], dzv[kCap], eta[kCap];
   for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < a.n; r += (long long)gridDim.x * blockDim.x) {
@@ -842,7 +842,14 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
       UFE_LAUNCH(c, TC_COLUMN);
       if (!DIVA) k_vertex_ssa<<<g_a, 128, 0, st>>>(va, p);
       else if (nz == 12 && getenv("UFE_B200_VERTEX_NZ12")) k_vertex_diva<12><<<g_a, 128, 0, st>>>(va, p);
-      else k_vertex_diva<0><<<g_a, 128, 0, st>>>(va, p);
+      else {
+        // registers capped for 6 resident blocks per SM (80 registers): the kernel is bound by gather latency, more warps beat fewer spills
+        // (column class per step at 4 M vertices: 6.5 ms with 4 blocks / 128 registers, 5.25 ms with 6, 5.4 ms with 8)
+        static const int mb = getenv("UFE_B200_VERTEX_MB") ? atoi(getenv("UFE_B200_VERTEX_MB")) : 6;
+        if (mb >= 8) k_vertex_diva<0, 8><<<g_a, 128, 0, st>>>(va, p);
+        else if (mb >= 6) k_vertex_diva<0, 6><<<g_a, 128, 0, st>>>(va, p);
+        else k_vertex_diva<0, 4><<<g_a, 128, 0, st>>>(va, p);
+      }
     }
     UFE_TRY(halo_exchange(c, M.a, V.N_a.p)); UFE_TRY(halo_exchange(c, M.a, V.beta_a.p));
     if (DIVA) {
