@@ -32,7 +32,9 @@ typedef struct ufe_b200_ctx* ufe_b200_handle;
 enum { UFE_KSP_BICGSTAB = 0, UFE_KSP_CG = 1 };                       /* north_star (b) */
 enum { UFE_PC_JACOBI = 0, UFE_PC_NONE = 1, UFE_PC_BJACOBI2 = 2, UFE_PC_NEUMANN = 3,
        UFE_PC_MG = 4 };   /* aggregation multigrid, stiffness-matrix solve only (new key B200_PC_type_config = 'multigrid') */
-enum { UFE_BC_INFINITE = 0, UFE_BC_ZERO = 1 };                        /* C%BC_{u,v,H}_{north,east,south,west} */
+enum { UFE_BC_INFINITE = 0, UFE_BC_ZERO = 1,                          /* C%BC_{u,v,H}_{north,east,south,west} */
+       UFE_BC_PERIODIC_ISMIP_HOM = 2, UFE_BC_INFINITE_SSA_ICESTREAM = 3 }; /* BC_u / BC_v only: the copy rows of
+       calc_SSA_DIVA_stiffness_matrix_row_BC (solve_linearised_SSA_DIVA_infinite_slab.f90:547-579, 618-636) */
 enum { UFE_SLID_NO_SLIDING = 0, UFE_SLID_WEERTMAN = 1, UFE_SLID_COULOMB = 2, UFE_SLID_BUDD = 3, UFE_SLID_TSAI2015 = 4,
        UFE_SLID_SCHOOF2005 = 5, UFE_SLID_ZOET_IVERSON = 6, UFE_SLID_IDEALISED_SSA_ICESTREAM = 7 };
 enum { UFE_INTEGRATION_EXPLICIT = 0, UFE_INTEGRATION_SEMI_IMPLICIT = 1 };
@@ -65,6 +67,7 @@ typedef struct ufe_b200_config {
   double uniform_Glens_flow_factor;         /* :603 */
   double refgeo_idealised_SSA_icestream_Hi, refgeo_idealised_SSA_icestream_dhdx,
          refgeo_idealised_SSA_icestream_L, refgeo_idealised_SSA_icestream_m;
+  double refgeo_idealised_ISMIP_HOM_L;      /* period of BC 'periodic_ISMIP-HOM' (mesh_utilities.f90:2620-2675) */
   double dHi_semiimplicit_fs;               /* :356 */
   double dHi_PETSc_rtol, dHi_PETSc_abstol;  /* :357-358 */
   double dt_ice_min, dt_ice_max;            /* :391-392 */

@@ -34,6 +34,7 @@ Config to_config(const ufe_b200_config* c) {
   C.uniform_Glens_flow_factor = c->uniform_Glens_flow_factor;
   C.icestream_Hi = c->refgeo_idealised_SSA_icestream_Hi; C.icestream_dhdx = c->refgeo_idealised_SSA_icestream_dhdx;
   C.icestream_L = c->refgeo_idealised_SSA_icestream_L; C.icestream_m = c->refgeo_idealised_SSA_icestream_m;
+  C.ISMIP_HOM_L = c->refgeo_idealised_ISMIP_HOM_L;
   C.choice_ice_integration_method = c->choice_ice_integration_method;
   C.dHi_semiimplicit_fs = c->dHi_semiimplicit_fs; C.dHi_PETSc_rtol = c->dHi_PETSc_rtol; C.dHi_PETSc_abstol = c->dHi_PETSc_abstol;
   C.dt_ice_min = c->dt_ice_min; C.dt_ice_max = c->dt_ice_max;
@@ -106,6 +107,18 @@ void orc_assemble_SSA_DIVA(void* h, const ufe_b200_config* cfg, const double* N_
   auto* o = static_cast<OracleMesh*>(h);
   assemble_SSA_DIVA(o->mv, o->ops, to_config(cfg), N_b, dN_dx_b, dN_dy_b, beta_b, tau_dx_b, tau_dy_b, BC_mask, BC_u, BC_v, o->A, o->bb);
   *m = o->A.m; *nnz = (int)o->A.nnz();
+}
+// same with the previous solution the copy rows ('periodic_ISMIP-HOM', 'infinite_SSA_icestream') read
+void orc_assemble_SSA_DIVA_prev(void* h, const ufe_b200_config* cfg, const double* N_b, const double* dN_dx_b, const double* dN_dy_b,
+                                const double* beta_b, const double* tau_dx_b, const double* tau_dy_b, const int* BC_mask,
+                                const double* BC_u, const double* BC_v, const double* u_b_prev, const double* v_b_prev, int* m, int* nnz) {
+  auto* o = static_cast<OracleMesh*>(h);
+  assemble_SSA_DIVA(o->mv, o->ops, to_config(cfg), N_b, dN_dx_b, dN_dy_b, beta_b, tau_dx_b, tau_dy_b, BC_mask, BC_u, BC_v, o->A, o->bb,
+                    u_b_prev, v_b_prev);
+  *m = o->A.m; *nnz = (int)o->A.nnz();
+}
+void orc_find_ti_copy(void* h, int choice, double L, int ti, int* ti_copy, double* wti_copy) {
+  find_ti_copy(static_cast<OracleMesh*>(h)->mv, choice, L, ti, ti_copy, wti_copy);
 }
 void orc_get_stiffness(void* h, int* ptr, int* ind, double* val, double* bb) {
   auto* o = static_cast<OracleMesh*>(h);

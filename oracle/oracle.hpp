@@ -60,7 +60,7 @@ void calc_all_matrix_operators(const MeshView& mesh, Operators& ops);
 // --- configuration scalars the path reads (model_configuration_type_and_namelist.f90) -----------------
 enum SlidingLaw { SLID_no_sliding = 0, SLID_Weertman = 1, SLID_Coulomb = 2, SLID_Budd = 3, SLID_Tsai2015 = 4,
                   SLID_Schoof2005 = 5, SLID_ZoetIverson = 6, SLID_idealised_SSA_icestream = 7 };
-enum BC { BC_infinite = 0, BC_zero = 1 };
+enum BC { BC_infinite = 0, BC_zero = 1, BC_periodic_ISMIP_HOM = 2, BC_infinite_SSA_icestream = 3 };
 enum KspType { KSP_bicgstab_jacobi = 0, KSP_gmres_ilu0 = 1 };
 
 struct Config {
@@ -80,6 +80,7 @@ struct Config {
   // SSA_icestream idealised law (Schoof 2006)
   double uniform_Glens_flow_factor = 1e-16;
   double icestream_Hi = 2000.0, icestream_dhdx = -0.0003, icestream_L = 150e3, icestream_m = 1.0;
+  double ISMIP_HOM_L = 0.0;  // refgeo_idealised_ISMIP_HOM_L: period of the 'periodic_ISMIP-HOM' copy rows
   // thickness
   int choice_ice_integration_method = 1;  // 0 explicit, 1 semi-implicit
   double dHi_semiimplicit_fs = 1.5, dHi_PETSc_rtol = 1e-8, dHi_PETSc_abstol = 1e-6;
@@ -103,7 +104,10 @@ void assemble_SSA_DIVA(const MeshView& mesh, const Operators& ops, const Config&
                        const double* N_b, const double* dN_dx_b, const double* dN_dy_b, const double* beta_b,
                        const double* tau_dx_b, const double* tau_dy_b,
                        const int* BC_prescr_mask_b, const double* BC_prescr_u_b, const double* BC_prescr_v_b,
-                       Csr& A, std::vector<double>& bb);
+                       Csr& A, std::vector<double>& bb, const double* u_b_prev = nullptr, const double* v_b_prev = nullptr);
+// find_containing_vertex (mesh_utilities.f90:1368), find_ti_copy_{ISMIP_HOM_periodic,SSA_icestream_infinite} (:2620, :2681)
+int find_containing_vertex(const MeshView& mesh, const double p[2], int vi);
+void find_ti_copy(const MeshView& mesh, int choice, double L, int ti, int* ti_copy, double* wti_copy);
 
 struct DivaState {  // type_ice_velocity_solver_DIVA (ice_model_types.f90:149-197), fields on the path
   std::vector<double> u_vav_b, v_vav_b, u_base_b, v_base_b, u_b_prev, v_b_prev;

@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 
 #include "oracle.hpp"
 
@@ -27,14 +28,65 @@ void DivaState::init(int nV, int nTri, int nz) {
 }
 
 // ---------------------------------------------------------------------------------------------------
+// Copy rows of the ISMIP-HOM / SSA_icestream experiments
+// ---------------------------------------------------------------------------------------------------
+// find_containing_vertex (mesh_utilities.f90:1368-1416): greedy walk to the vertex nearest to p
+int find_containing_vertex(const MeshView& mesh, const double p[2], int vi) {
+  const int nV = mesh.nV;
+  auto dist = [&](int v) { const double dx = mesh.V[v - 1] - p[0], dy = mesh.V[(size_t)nV + v - 1] - p[1]; return std::sqrt(dx * dx + dy * dy); };
+  int vi_prev = vi;
+  for (;;) {
+    const double d = dist(vi);
+    double dcmin = d + 10.0; int vcmin = 0;
+    for (int ci = 1; ci <= mesh.nC[vi - 1]; ++ci) {
+      const int vc = mesh.C[(size_t)(ci - 1) * nV + vi - 1];
+      if (vc == vi_prev) continue;  // the neighbour we just came from
+      const double dc = dist(vc);
+      if (dc < dcmin) { dcmin = dc; vcmin = vc; }
+    }
+    if (dcmin < d) { vi_prev = vi; vi = vcmin; } else return vi;
+  }
+}
+
+// find_ti_copy_ISMIP_HOM_periodic (mesh_utilities.f90:2620-2677) and find_ti_copy_SSA_icestream_infinite (:2681-2730):
+// the point the previous solution is copied from, the vertex whose Voronoi cell holds it, inverse-square-distance weights
+// over that vertex's triangles.  ti_copy / wti_copy hold nC_mem entries (0 = unused).
+void find_ti_copy(const MeshView& mesh, int choice, double L, int ti, int* ti_copy, double* wti_copy) {
+  const int nV = mesh.nV, nTri = mesh.nTri;
+  const double gc[2] = {mesh.TriGC[ti - 1], mesh.TriGC[(size_t)nTri + ti - 1]};
+  double p[2];
+  if (choice == BC_periodic_ISMIP_HOM) {
+    p[0] = (gc[0] > 0.0) ? gc[0] - L / 2.0 : gc[0] + L / 2.0;
+    p[1] = (gc[1] > 0.0) ? gc[1] - L / 2.0 : gc[1] + L / 2.0;
+  } else {
+    p[1] = gc[1];
+    p[0] = (gc[0] < 0.0) ? mesh.xmin + (mesh.xmax - mesh.xmin) * 1.0 / 3.0 : mesh.xmin + (mesh.xmax - mesh.xmin) * 2.0 / 3.0;
+  }
+  const int vi = find_containing_vertex(mesh, p, 5);
+  for (int n = 0; n < mesh.nC_mem; ++n) { ti_copy[n] = 0; wti_copy[n] = 0.0; }
+  const int nt = mesh.niTri[vi - 1];
+  double wsum = 0.0;
+  for (int iti = 1; iti <= nt; ++iti) {
+    const int tj = mesh.iTri[(size_t)(iti - 1) * nV + vi - 1];
+    const double dx = p[0] - mesh.TriGC[tj - 1], dy = p[1] - mesh.TriGC[(size_t)nTri + tj - 1];
+    const double dist = std::sqrt(dx * dx + dy * dy);
+    ti_copy[iti - 1] = tj;
+    wti_copy[iti - 1] = 1.0 / (dist * dist);
+    wsum += wti_copy[iti - 1];
+  }
+  for (int iti = 0; iti < nt; ++iti) wti_copy[iti] = wti_copy[iti] / wsum;
+}
+
+// ---------------------------------------------------------------------------------------------------
 // Assembly of the linearised SSA/DIVA (solve_linearised_SSA_DIVA_infinite_slab.f90:61-153)
 // ---------------------------------------------------------------------------------------------------
 void assemble_SSA_DIVA(const MeshView& mesh, const Operators& ops, const Config& C,
                        const double* N_b, const double* dN_dx_b, const double* dN_dy_b, const double* beta_b,
                        const double* tau_dx_b, const double* tau_dy_b,
                        const int* BC_mask, const double* BC_u, const double* BC_v,
-                       Csr& A, std::vector<double>& bb) {
+                       Csr& A, std::vector<double>& bb, const double* u_b_prev, const double* v_b_prev) {
   const int nTri = mesh.nTri, R = 2 * nTri;
+  std::vector<int> ti_copy(mesh.nC_mem); std::vector<double> wti_copy(mesh.nC_mem);
   const Csr& Mx = ops.M[OP2_ddx_b_b]; const Csr& My = ops.M[OP2_ddy_b_b];
   const Csr& Mxx = ops.M[OP2_d2dx2_b_b]; const Csr& Mxy = ops.M[OP2_d2dxdy_b_b]; const Csr& Myy = ops.M[OP2_d2dy2_b_b];
   A.init(R, R, Mx.nnz() * 4);
@@ -59,6 +111,22 @@ void assemble_SSA_DIVA(const MeshView& mesh, const Operators& ops, const Config&
         }
         A.add(row, row, -1.0 * (double)n_neighbours);
         bb[row - 1] = 0.0;
+      } else if (choice == BC_periodic_ISMIP_HOM || (choice == BC_infinite_SSA_icestream && uv == 1)) {
+        // value at ti = relaxed, weighted previous solution around the displaced point (:547-581, :618-636)
+        if (!u_b_prev || !v_b_prev) { std::fprintf(stderr, "oracle: copy BC rows need u_b_prev, v_b_prev\n"); std::abort(); }
+        const double* prev = (uv == 1) ? u_b_prev : v_b_prev;
+        find_ti_copy(mesh, choice, C.ISMIP_HOM_L, ti, ti_copy.data(), wti_copy.data());
+        A.add(row, row, 1.0);
+        double fixed = 0.0;
+        for (int n = 0; n < mesh.nC_mem; ++n) {
+          const int tj = ti_copy[n];
+          if (tj == 0) continue;
+          fixed = fixed + wti_copy[n] * prev[tj - 1];
+        }
+        fixed = (C.visc_it_relax * fixed) + ((1.0 - C.visc_it_relax) * prev[ti - 1]);
+        bb[row - 1] = fixed;
+      } else if (choice != BC_zero) {  // crash('unknown choice_BC_u/v') in the reference
+        std::fprintf(stderr, "oracle: unknown choice_BC_%c %d\n", uv == 1 ? 'u' : 'v', choice); std::abort();
       } else {  // 'zero'
         A.add(row, row, 1.0);
         bb[row - 1] = 0.0;
@@ -117,7 +185,7 @@ void solve_linearised(const MeshView& mesh, const Operators& ops, const Config& 
   const int nTri = mesh.nTri;
   for (int t = 0; t < nTri; ++t) { u_b_prev[t] = u_b[t]; v_b_prev[t] = v_b[t]; }
   Csr A; std::vector<double> bb, uv(2 * (size_t)nTri);
-  assemble_SSA_DIVA(mesh, ops, C, N_b, dN_dx_b, dN_dy_b, beta_b, tau_dx_b, tau_dy_b, BC_mask, BC_u, BC_v, A, bb);
+  assemble_SSA_DIVA(mesh, ops, C, N_b, dN_dx_b, dN_dy_b, beta_b, tau_dx_b, tau_dy_b, BC_mask, BC_u, BC_v, A, bb, u_b_prev, v_b_prev);
   for (int t = 0; t < nTri; ++t) { uv[2 * t] = u_b[t]; uv[2 * t + 1] = v_b[t]; }
   linear_solve(C, A, bb.data(), uv.data(), C.stress_balance_PETSc_rtol, C.stress_balance_PETSc_abstol, n_Axb_its);
   for (int t = 0; t < nTri; ++t) { u_b[t] = uv[2 * t]; v_b[t] = uv[2 * t + 1]; }

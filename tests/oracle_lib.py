@@ -29,6 +29,8 @@ def lib():
         L.orc_get_operator.argtypes = [C.c_void_p, C.c_int, ip, ip, dp]
         L.orc_apply_operator.argtypes = [C.c_void_p, C.c_int, dp, dp, C.c_int]
         L.orc_assemble_SSA_DIVA.argtypes = [C.c_void_p, C.POINTER(ub.Config)] + [dp] * 6 + [ip, dp, dp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.orc_assemble_SSA_DIVA_prev.argtypes = [C.c_void_p, C.POINTER(ub.Config)] + [dp] * 6 + [ip, dp, dp, dp, dp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.orc_find_ti_copy.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, ip, dp]
         L.orc_get_stiffness.argtypes = [C.c_void_p, ip, ip, dp, dp]
         L.orc_solve_velocity.argtypes = [C.c_void_p, C.POINTER(ub.Config), C.c_int, C.c_int, C.POINTER(ub.IceInputs),
                                          C.POINTER(ub.VelocityState), C.POINTER(C.c_int), C.POINTER(C.c_int), ip, dp, dp, C.c_int]
@@ -102,11 +104,22 @@ class OracleMesh:
         lib().orc_apply_operator(self.h, op, ub.dp(x), ub.dp(y), ncols)
         return y
 
-    def assemble(self, cfg, N_b, dN_dx_b, dN_dy_b, beta_b, tau_dx_b, tau_dy_b, BC_mask=None, BC_u=None, BC_v=None):
+    def find_ti_copy(self, choice, L, ti):
+        """find_ti_copy_ISMIP_HOM_periodic (choice 2) / find_ti_copy_SSA_icestream_infinite (choice 3) for the 1-based triangle ti"""
+        tj = np.zeros(self.m.nC_mem, np.int32); w = np.zeros(self.m.nC_mem)
+        lib().orc_find_ti_copy(self.h, choice, L, ti, ub.ip(tj), ub.dp(w))
+        return tj, w
+
+    def assemble(self, cfg, N_b, dN_dx_b, dN_dy_b, beta_b, tau_dx_b, tau_dy_b, BC_mask=None, BC_u=None, BC_v=None, u_b_prev=None, v_b_prev=None):
         self.calc_matrix_operators()
         m, nnz = C.c_int(), C.c_int()
-        lib().orc_assemble_SSA_DIVA(self.h, C.byref(cfg), ub.dp(N_b), ub.dp(dN_dx_b), ub.dp(dN_dy_b), ub.dp(beta_b), ub.dp(tau_dx_b),
-                                    ub.dp(tau_dy_b), ub.ip(BC_mask), ub.dp(BC_u), ub.dp(BC_v), C.byref(m), C.byref(nnz))
+        if u_b_prev is not None:
+            lib().orc_assemble_SSA_DIVA_prev(self.h, C.byref(cfg), ub.dp(N_b), ub.dp(dN_dx_b), ub.dp(dN_dy_b), ub.dp(beta_b), ub.dp(tau_dx_b),
+                                             ub.dp(tau_dy_b), ub.ip(BC_mask), ub.dp(BC_u), ub.dp(BC_v), ub.dp(u_b_prev), ub.dp(v_b_prev),
+                                             C.byref(m), C.byref(nnz))
+        else:
+            lib().orc_assemble_SSA_DIVA(self.h, C.byref(cfg), ub.dp(N_b), ub.dp(dN_dx_b), ub.dp(dN_dy_b), ub.dp(beta_b), ub.dp(tau_dx_b),
+                                        ub.dp(tau_dy_b), ub.ip(BC_mask), ub.dp(BC_u), ub.dp(BC_v), C.byref(m), C.byref(nnz))
         ptr = np.zeros(m.value + 1, np.int32); ind = np.zeros(nnz.value, np.int32); val = np.zeros(nnz.value); bb = np.zeros(m.value)
         lib().orc_get_stiffness(self.h, ub.ip(ptr), ub.ip(ind), ub.dp(val), ub.dp(bb))
         return ptr, ind, val, bb

@@ -199,6 +199,7 @@ void ufe_b200_config_defaults(ufe_b200_config* c) {
   c->subgrid_friction_exponent_on_B_grid = 2.0; c->Hi_min = 0.0; c->uniform_Glens_flow_factor = 1e-16;
   c->refgeo_idealised_SSA_icestream_Hi = 2000.0; c->refgeo_idealised_SSA_icestream_dhdx = -0.0003;
   c->refgeo_idealised_SSA_icestream_L = 150e3; c->refgeo_idealised_SSA_icestream_m = 1.0;
+  c->refgeo_idealised_ISMIP_HOM_L = 0.0;
   c->dHi_semiimplicit_fs = 1.5; c->dHi_PETSc_rtol = 1e-8; c->dHi_PETSc_abstol = 1e-6;
   c->dt_ice_min = 0.1; c->dt_ice_max = 10.0;
   c->ice_density = 917.0; c->seawater_density = 1027.0; c->grav = 9.81;

@@ -18,6 +18,7 @@
 #include "velocity.cuh"
 
 #include <cub/device/device_scan.cuh>
+#include <cstring>
 
 #include "csr.cuh"
 #include "krylov_impl.cuh"
@@ -63,6 +64,7 @@ struct VelPar {
   double slid_delta_v, slid_Weertman_m, slid_Budd_q, slid_Budd_u, slid_ZI_ut, slid_ZI_p, slid_beta_max, subgrid_exp, Hi_min;
   double A_uniform, is_Hi, is_dhdx, is_L, is_m;
   double ice_density, grav;
+  double relax_cfg, ismip_hom_L;   // C%visc_it_relax itself (relax above is the adaptive one) and the period of the ISMIP-HOM copy rows
   int sliding_law, do_subgrid, crossterms, BC_u[4], BC_v[4], diagnostics;
 };
 
@@ -76,6 +78,7 @@ static VelPar make_par(const ufe_b200_config* C) {
   p.A_uniform = C->uniform_Glens_flow_factor; p.is_Hi = C->refgeo_idealised_SSA_icestream_Hi; p.is_dhdx = C->refgeo_idealised_SSA_icestream_dhdx;
   p.is_L = C->refgeo_idealised_SSA_icestream_L; p.is_m = C->refgeo_idealised_SSA_icestream_m;
   p.ice_density = C->ice_density; p.grav = C->grav;
+  p.relax_cfg = C->visc_it_relax; p.ismip_hom_L = C->refgeo_idealised_ISMIP_HOM_L;
   p.sliding_law = C->choice_sliding_law; p.do_subgrid = C->do_GL_subgrid_friction; p.crossterms = C->do_include_SSADIVA_crossterms;
   for (int k = 0; k < 4; ++k) { p.BC_u[k] = C->BC_u[k]; p.BC_v[k] = C->BC_v[k]; }
   p.diagnostics = C->write_diagnostics;
@@ -394,6 +397,102 @@ __device__ __forceinline__ void assemble_triangle(const StiffArgs& s, const VelP
   }
 }
 
+// ---- copy rows: BC 'periodic_ISMIP-HOM' and 'infinite_SSA_icestream' (calc_SSA_DIVA_stiffness_matrix_row_BC :547-581, :618-636) ----------
+// The matrix row is the identity row k_stiff_count already makes of every choice that is not 'infinite'; what differs is the load vector.
+__device__ __forceinline__ bool is_copy_choice(int choice) { return choice == UFE_BC_PERIODIC_ISMIP_HOM || choice == UFE_BC_INFINITE_SSA_ICESTREAM; }
+
+// compact list of the owned copy rows (out_row == nullptr: count only)
+__global__ void k_copy_bc_list(StiffArgs s, VelPar p, int* __restrict__ count, int* __restrict__ out_row, int* __restrict__ out_choice) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < s.n; r += (long long)gridDim.x * blockDim.x) {
+    const int ti = s.ti1 + (int)r;
+    const int bi = s.TriBI[ti - 1];
+    if (bi <= 0 || s.bc_mask[s.off + r] == 1) continue;
+    const int side = bc_side(bi);
+    for (int uv = 0; uv < 2; ++uv) {
+      const int choice = (uv == 0) ? p.BC_u[side] : p.BC_v[side];
+      if (!is_copy_choice(choice)) continue;
+      const int e = atomicAdd(count, 1);
+      if (out_row) { out_row[e] = 2 * (int)r + uv; out_choice[e] = choice; }
+    }
+  }
+}
+
+// the point the previous solution is copied from (find_ti_copy_ISMIP_HOM_periodic, mesh_utilities.f90:2645-2658;
+// find_ti_copy_SSA_icestream_infinite, :2704-2710)
+__device__ __forceinline__ void copy_bc_point(int choice, double gcx, double gcy, double L, double xmin, double xmax, double& px, double& py) {
+  if (choice == UFE_BC_PERIODIC_ISMIP_HOM) {
+    px = (gcx > 0.0) ? gcx - L / 2.0 : gcx + L / 2.0;
+    py = (gcy > 0.0) ? gcy - L / 2.0 : gcy + L / 2.0;
+  } else {
+    py = gcy;
+    px = (gcx < 0.0) ? xmin + (xmax - xmin) * 1.0 / 3.0 : xmin + (xmax - xmin) * 2.0 / 3.0;
+  }
+}
+
+// find_containing_vertex (mesh_utilities.f90:1368-1416) from the reference's start vertex 5: one greedy walk per copy row, once per pattern
+__global__ void k_copy_bc_find(int n_copy, const int* __restrict__ row, const int* __restrict__ choice, int* __restrict__ out_vi, int ti1,
+                               int nV, int nTri, const double* __restrict__ V, const int* __restrict__ nC, const int* __restrict__ Cn,
+                               const double* __restrict__ TriGC, double L, double xmin, double xmax) {
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n_copy; e += gridDim.x * blockDim.x) {
+    const int ti = ti1 + (row[e] >> 1);
+    double px, py;
+    copy_bc_point(choice[e], TriGC[ti - 1], TriGC[(size_t)nTri + ti - 1], L, xmin, xmax, px, py);
+    int vi = 5, vi_prev = 5;
+    for (;;) {
+      double dx = V[vi - 1] - px, dy = V[(size_t)nV + vi - 1] - py;
+      const double d = sqrt(dx * dx + dy * dy);
+      double dcmin = d + 10.0; int vcmin = 0;
+      const int nc = nC[vi - 1];
+      for (int ci = 0; ci < nc; ++ci) {
+        const int vc = Cn[(size_t)ci * nV + vi - 1];
+        if (vc == vi_prev) continue;
+        dx = V[vc - 1] - px; dy = V[(size_t)nV + vc - 1] - py;
+        const double dc = sqrt(dx * dx + dy * dy);
+        if (dc < dcmin) { dcmin = dc; vcmin = vc; }
+      }
+      if (dcmin < d) { vi_prev = vi; vi = vcmin; } else break;
+    }
+    out_vi[e] = vi;
+  }
+}
+
+// nranks > 1: own slice of the previous solution into the global vectors (zero elsewhere; completed by one all-reduce)
+__global__ void k_copy_bc_scatter(int n, int off, int ti1, int nTri, const double* __restrict__ u, const double* __restrict__ v, double* __restrict__ g) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    g[ti1 - 1 + r] = u[off + r]; g[(size_t)nTri + ti1 - 1 + r] = v[off + r];
+  }
+}
+
+// load vector of the copy rows: inverse-square-distance weights over the triangles of the containing vertex (normalised first, as the
+// reference does), then the relaxation with C%visc_it_relax.  src_u/src_v[tj - src_lo] = previous solution on triangle tj.
+__global__ void k_copy_bc_rhs(int n_copy, const int* __restrict__ row, const int* __restrict__ choice, const int* __restrict__ cvi, int ti1,
+                              int nV, int nTri, const int* __restrict__ niTri, const int* __restrict__ iTri, const double* __restrict__ TriGC,
+                              double L, double xmin, double xmax, double relax, const double* __restrict__ src_u,
+                              const double* __restrict__ src_v, int src_lo, double* __restrict__ bb) {
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n_copy; e += gridDim.x * blockDim.x) {
+    const int rw = row[e], ti = ti1 + (rw >> 1), vi = cvi[e];
+    const double* __restrict__ prev = (rw & 1) ? src_v : src_u;
+    double px, py;
+    copy_bc_point(choice[e], TriGC[ti - 1], TriGC[(size_t)nTri + ti - 1], L, xmin, xmax, px, py);
+    const int nt = niTri[vi - 1];
+    double wsum = 0.0;
+    for (int it = 0; it < nt; ++it) {
+      const int tj = iTri[(size_t)it * nV + vi - 1];
+      const double dx = px - TriGC[tj - 1], dy = py - TriGC[(size_t)nTri + tj - 1];
+      const double dist = sqrt(dx * dx + dy * dy);
+      wsum += 1.0 / (dist * dist);
+    }
+    double fixed = 0.0;
+    for (int it = 0; it < nt; ++it) {
+      const int tj = iTri[(size_t)it * nV + vi - 1];
+      const double dx = px - TriGC[tj - 1], dy = py - TriGC[(size_t)nTri + tj - 1];
+      const double dist = sqrt(dx * dx + dy * dy);
+      fixed = fixed + ((1.0 / (dist * dist)) / wsum) * prev[tj - src_lo];
+    }
+    bb[rw] = (relax * fixed) + ((1.0 - relax) * prev[ti - src_lo]);
+  }
+}
+
 // standalone assembly from given b-grid coefficients (the solve_SSA_DIVA_linearised entry point)
 __global__ void __launch_bounds__(128) k_assemble(StiffArgs s, VelPar p, const double* __restrict__ N_b, const double* __restrict__ dNx,
                                                   const double* __restrict__ dNy, const double* __restrict__ beta,
@@ -584,8 +683,16 @@ static int ensure_pattern(Ctx* c, const VelPar& p, unsigned long long bc_version
   Mesh& M = *c->mesh; Velocity& V = *c->vel;
   unsigned long long key = 1469598103934665603ull;
   auto mix = [&](unsigned long long x) { key = (key ^ x) * 1099511628211ull; };
-  for (int k = 0; k < 4; ++k) { mix(p.BC_u[k] + 1); mix(p.BC_v[k] + 7); }
+  bool any_copy = false;
+  for (int k = 0; k < 4; ++k) {
+    mix(p.BC_u[k] + 1); mix(p.BC_v[k] + 7);
+    // crash('unknown choice_BC_u/v ...') in the reference (solve_linearised_SSA_DIVA_infinite_slab.f90:510, 586); 'infinite_SSA_icestream' exists for u only
+    UFE_CHECK(p.BC_u[k] >= UFE_BC_INFINITE && p.BC_u[k] <= UFE_BC_INFINITE_SSA_ICESTREAM, "unknown choice_BC_u %d", p.BC_u[k]);
+    UFE_CHECK(p.BC_v[k] >= UFE_BC_INFINITE && p.BC_v[k] <= UFE_BC_PERIODIC_ISMIP_HOM, "unknown choice_BC_v %d", p.BC_v[k]);
+    any_copy = any_copy || p.BC_u[k] >= UFE_BC_PERIODIC_ISMIP_HOM || p.BC_v[k] >= UFE_BC_PERIODIC_ISMIP_HOM;
+  }
   mix(bc_version);
+  if (any_copy) { unsigned long long lb; memcpy(&lb, &p.ismip_hom_L, sizeof(lb)); mix(lb); }
   if (V.pattern_valid && V.pattern_key == key) return 0;
   const int n = M.b.n_loc(), rows = 2 * n;
   UFE_TRY(V.A.ptr_buf.alloc((size_t)rows + 1)); UFE_TRY(V.row_kind.alloc(rows));
@@ -614,7 +721,51 @@ static int ensure_pattern(Ctx* c, const VelPar& p, unsigned long long bc_version
   UFE_CUDA(cudaGetLastError());
   UFE_TRY(blk_build(c, V.blk, V.A, n, M.b.off()));
   V.mg.valid = false;
+  V.n_copy = 0; V.copy_any = any_copy;
+  if (any_copy) {   // the copy rows and, once per pattern, the vertex each one copies around
+    UFE_CHECK(M.nV >= 5, "copy boundary conditions need a mesh of at least 5 vertices");
+    UFE_TRY(V.copy_count.alloc(1));
+    UFE_CUDA(cudaMemsetAsync(V.copy_count.p, 0, sizeof(int), c->stream));
+    { UFE_LAUNCH(c, TC_ASSEMBLY); k_copy_bc_list<<<grid, 128, 0, c->stream>>>(s, p, V.copy_count.p, nullptr, nullptr); }
+    int nc = 0;
+    UFE_CUDA(cudaMemcpyAsync(&nc, V.copy_count.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    UFE_CUDA(cudaStreamSynchronize(c->stream));
+    if (nc > 0) {
+      UFE_TRY(V.copy_row.alloc(nc)); UFE_TRY(V.copy_choice.alloc(nc)); UFE_TRY(V.copy_vi.alloc(nc));
+      UFE_CUDA(cudaMemsetAsync(V.copy_count.p, 0, sizeof(int), c->stream));
+      { UFE_LAUNCH(c, TC_ASSEMBLY); k_copy_bc_list<<<grid, 128, 0, c->stream>>>(s, p, V.copy_count.p, V.copy_row.p, V.copy_choice.p); }
+      UFE_LAUNCH(c, TC_ASSEMBLY);
+      k_copy_bc_find<<<grid_for(c, nc, 128), 128, 0, c->stream>>>(nc, V.copy_row.p, V.copy_choice.p, V.copy_vi.p, M.b.i1, M.nV, M.nTri, M.V.p,
+                                                                  M.nC.p, M.C.p, M.TriGC.p, p.ismip_hom_L, M.xmin, M.xmax);
+      UFE_CUDA(cudaGetLastError());
+    }
+    V.n_copy = nc;
+    if (c->nranks > 1) UFE_TRY(V.uv_glob.alloc(2 * (size_t)M.nTri));
+  }
   V.pattern_key = key; V.pattern_valid = true;
+  return 0;
+}
+
+// Load vector of the copy rows from the previous solution (= V.u, V.v at assembly time); call after the assembly kernel.
+// Collective when nranks > 1 (every rank of a pattern with copy choices calls it, whether it owns copy rows or not).
+static int copy_bc_rhs(Ctx* c, const VelPar& p) {
+  Mesh& M = *c->mesh; Velocity& V = *c->vel;
+  if (!V.copy_any) return 0;
+  const double* src_u = V.u.p; const double* src_v = V.v.p; int src_lo = M.b.lo;
+  if (c->nranks > 1) {
+    UFE_CUDA(cudaMemsetAsync(V.uv_glob.p, 0, sizeof(double) * 2 * (size_t)M.nTri, c->stream));
+    { UFE_LAUNCH(c, TC_ASSEMBLY);
+      k_copy_bc_scatter<<<grid_for(c, M.b.n_loc(), 256), 256, 0, c->stream>>>(M.b.n_loc(), M.b.off(), M.b.i1, M.nTri, V.u.p, V.v.p, V.uv_glob.p); }
+    UFE_TRY(allreduce_sum_large(c, V.uv_glob.p, 2 * (size_t)M.nTri, false));
+    src_u = V.uv_glob.p; src_v = V.uv_glob.p + M.nTri; src_lo = 1;
+  }
+  if (V.n_copy > 0) {
+    UFE_LAUNCH(c, TC_ASSEMBLY);
+    k_copy_bc_rhs<<<grid_for(c, V.n_copy, 128), 128, 0, c->stream>>>(V.n_copy, V.copy_row.p, V.copy_choice.p, V.copy_vi.p, M.b.i1, M.nV, M.nTri,
+                                                                    M.niTri.p, M.iTri.p, M.TriGC.p, p.ismip_hom_L, M.xmin, M.xmax, p.relax_cfg,
+                                                                    src_u, src_v, src_lo, V.bb.p);
+    UFE_CUDA(cudaGetLastError());
+  }
   return 0;
 }
 
@@ -859,8 +1010,9 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
     {
       UFE_LAUNCH(c, TC_ASSEMBLY);
       if (DIVA) k_tri_assemble<true><<<g_b, 128, 0, st>>>(ta, sa, p); else k_tri_assemble<false><<<g_b, 128, 0, st>>>(ta, sa, p);
-      V.blk_filled = sa.blk_map != nullptr; V.csr_stale = sa.A_val == nullptr; V.csr_stale = sa.A_val == nullptr;
+      V.blk_filled = sa.blk_map != nullptr; V.csr_stale = sa.A_val == nullptr;
     }
+    UFE_TRY(copy_bc_rhs(c, p));   // u, v still hold the previous solution here (k_store_prev below copies the same values)
     { UFE_LAUNCH(c, TC_EPILOGUE); k_store_prev<<<g_b, 128, 0, st>>>(nb, M.b.off(), V.u.p, V.v.p, V.u_prev.p, V.v_prev.p); }
     int its = 0;
     UFE_TRY(solve_linear_system(c, cfg, cfg->stress_balance_PETSc_rtol, cfg->stress_balance_PETSc_abstol, &its));
@@ -979,6 +1131,7 @@ int ufe_b200_solve_SSA_DIVA_linearised(ufe_b200_handle h, const ufe_b200_config*
   { UFE_LAUNCH(c, TC_EPILOGUE); k_store_prev<<<g_b, 128, 0, st>>>(nb, M.b.off(), V.u.p, V.v.p, V.u_prev.p, V.v_prev.p); }
   { UFE_LAUNCH(c, TC_ASSEMBLY); k_assemble<<<g_b, 128, 0, st>>>(sa, p, V.N_b.p, V.dN_dx_b.p, V.dN_dy_b.p, V.beta_eff_b.p, V.tau_dx.p, V.tau_dy.p); }
   V.blk_filled = sa.blk_map != nullptr; V.csr_stale = sa.A_val == nullptr;
+  UFE_TRY(copy_bc_rhs(c, p));
   int its = 0;
   UFE_TRY(solve_linear_system(c, cfg, rtol, abstol, &its));
   { UFE_LAUNCH(c, TC_EPILOGUE); k_deinterleave<<<g_b, 128, 0, st>>>(nb, M.b.off(), V.uv.p + M.buv.off(), V.u.p, V.v.p); }

@@ -31,6 +31,12 @@ struct Velocity {
   DevCsr A;
   DBuf<int> row_kind;          // per matrix row: 0 free, 1 identity (prescribed / 'zero'), 2 'infinite'
   DBuf<double> bb, uv;         // load vector (owned rows), solution (extended buv range)
+  // copy rows of BC 'periodic_ISMIP-HOM' / 'infinite_SSA_icestream' (identity rows whose load vector is the previous solution around a
+  // displaced point): compact list built with the pattern -- owned matrix row, BC choice, vertex whose Voronoi cell holds the point
+  DBuf<int> copy_row, copy_choice, copy_vi, copy_count;
+  int n_copy = 0;              // owned copy rows
+  bool copy_any = false;       // the BC choices of the current pattern contain a copy choice (on any rank)
+  DBuf<double> uv_glob;        // nranks > 1 only: the previous solution on all triangles (the reference gathers u_b_prev globally too)
   BlkMat blk;                  // 2x2-blocked sliced-ELL copy of A that the Krylov solver streams
   bool blk_filled = false;     // the last assembly wrote blk.val itself (no scatter pass needed)
   bool csr_stale = false;      // ... and skipped the CSR values (re-formed from blk.val on demand)

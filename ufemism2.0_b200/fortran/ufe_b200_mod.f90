@@ -40,6 +40,7 @@ module ufe_b200_mod
     real(c_double) :: subgrid_friction_exponent_on_B_grid, Hi_min, uniform_Glens_flow_factor
     real(c_double) :: refgeo_idealised_SSA_icestream_Hi, refgeo_idealised_SSA_icestream_dhdx
     real(c_double) :: refgeo_idealised_SSA_icestream_L, refgeo_idealised_SSA_icestream_m
+    real(c_double) :: refgeo_idealised_ISMIP_HOM_L
     real(c_double) :: dHi_semiimplicit_fs, dHi_PETSc_rtol, dHi_PETSc_abstol, dt_ice_min, dt_ice_max
     real(c_double) :: ice_density, seawater_density, grav
     integer(c_int32_t) :: visc_it_nit, do_include_SSADIVA_crossterms
@@ -378,6 +379,7 @@ contains
     cfg%refgeo_idealised_SSA_icestream_dhdx = C%refgeo_idealised_SSA_icestream_dhdx
     cfg%refgeo_idealised_SSA_icestream_L = C%refgeo_idealised_SSA_icestream_L
     cfg%refgeo_idealised_SSA_icestream_m = C%refgeo_idealised_SSA_icestream_m
+    cfg%refgeo_idealised_ISMIP_HOM_L = C%refgeo_idealised_ISMIP_HOM_L
     cfg%dHi_semiimplicit_fs = C%dHi_semiimplicit_fs; cfg%dHi_PETSc_rtol = C%dHi_PETSc_rtol; cfg%dHi_PETSc_abstol = C%dHi_PETSc_abstol
     cfg%dt_ice_min = C%dt_ice_min; cfg%dt_ice_max = C%dt_ice_max
     cfg%ice_density = 917.0_dp; cfg%seawater_density = 1027.0_dp; cfg%grav = 9.81_dp   ! parameters.f90:19-24
@@ -402,7 +404,9 @@ contains
     select case (trim( name))
     case ('infinite'); code = 0
     case ('zero');     code = 1
-    case default;      code = -1   ! periodic_ISMIP-HOM / infinite_SSA_icestream are not offered by the B200 path
+    case ('periodic_ISMIP-HOM');     code = 2   ! BC_u / BC_v only (copy rows, solve_linearised_SSA_DIVA_infinite_slab.f90:547-563)
+    case ('infinite_SSA_icestream'); code = 3   ! BC_u only in the reference (:565-581)
+    case default;      code = -1   ! rejected by the library with the reference's own 'unknown choice_BC' message
     end select
   end function bc_code
 

@@ -18,7 +18,7 @@ c_ip = C.POINTER(C.c_int32)
 # enumerations of include/ufe_b200.h
 KSP_BICGSTAB, KSP_CG = 0, 1
 PC_JACOBI, PC_NONE, PC_BJACOBI2, PC_NEUMANN, PC_MG = 0, 1, 2, 3, 4
-BC_INFINITE, BC_ZERO = 0, 1
+BC_INFINITE, BC_ZERO, BC_PERIODIC_ISMIP_HOM, BC_INFINITE_SSA_ICESTREAM = 0, 1, 2, 3
 (SLID_NO_SLIDING, SLID_WEERTMAN, SLID_COULOMB, SLID_BUDD, SLID_TSAI2015, SLID_SCHOOF2005, SLID_ZOET_IVERSON,
  SLID_IDEALISED_SSA_ICESTREAM) = range(8)
 INTEGRATION_EXPLICIT, INTEGRATION_SEMI_IMPLICIT = 0, 1
@@ -39,7 +39,7 @@ class Config(C.Structure):
         "slid_Weertman_m", "slid_Budd_q_plastic", "slid_Budd_u_threshold", "slid_ZI_ut", "slid_ZI_p", "slid_beta_max",
         "subgrid_friction_exponent_on_B_grid", "Hi_min", "uniform_Glens_flow_factor",
         "refgeo_idealised_SSA_icestream_Hi", "refgeo_idealised_SSA_icestream_dhdx", "refgeo_idealised_SSA_icestream_L",
-        "refgeo_idealised_SSA_icestream_m", "dHi_semiimplicit_fs", "dHi_PETSc_rtol", "dHi_PETSc_abstol", "dt_ice_min",
+        "refgeo_idealised_SSA_icestream_m", "refgeo_idealised_ISMIP_HOM_L", "dHi_semiimplicit_fs", "dHi_PETSc_rtol", "dHi_PETSc_abstol", "dt_ice_min",
         "dt_ice_max", "ice_density", "seawater_density", "grav")] + [
         ("visc_it_nit", C.c_int32), ("do_include_SSADIVA_crossterms", C.c_int32), ("BC_u", C.c_int32 * 4),
         ("BC_v", C.c_int32 * 4), ("choice_sliding_law", C.c_int32), ("do_GL_subgrid_friction", C.c_int32),
@@ -58,6 +58,7 @@ def default_config():
     c.subgrid_friction_exponent_on_B_grid = 2.0; c.Hi_min = 0.0; c.uniform_Glens_flow_factor = 1e-16
     c.refgeo_idealised_SSA_icestream_Hi = 2000.0; c.refgeo_idealised_SSA_icestream_dhdx = -0.0003
     c.refgeo_idealised_SSA_icestream_L = 150e3; c.refgeo_idealised_SSA_icestream_m = 1.0
+    c.refgeo_idealised_ISMIP_HOM_L = 0.0
     c.dHi_semiimplicit_fs = 1.5; c.dHi_PETSc_rtol = 1e-8; c.dHi_PETSc_abstol = 1e-6
     c.dt_ice_min = 0.1; c.dt_ice_max = 10.0
     c.ice_density = 917.0; c.seawater_density = 1027.0; c.grav = 9.81

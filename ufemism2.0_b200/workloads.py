@@ -139,3 +139,26 @@ def halfar(h, half_width=800e3, nz=12, seed=20261104, jitter=0.2, H0=3000.0, R0=
     cfg = scaling_config()
     cfg.choice_sliding_law = ub.SLID_NO_SLIDING
     return Workload(mesh, cfg, f, approximation=2, name="Halfar")
+
+
+def ssa_icestream(h, nz=12, seed=20261104, jitter=0.2):
+    """The reference's integrated test idealised/SSA_icestream (automated_testing/integrated_tests/idealised/SSA_icestream/config_0*_*km.cfg):
+    a 2000 m slab on a bed sloping in x (idealised_geometries.f90:186-212), till yield stress of Schoof (2006), SSA, u copied from the interior
+    at the west / east borders ('infinite_SSA_icestream'), zero elsewhere.  Analytic solution: Schoof_SSA_solution.f90."""
+    mesh = uh.HostMesh.synthetic(-400e3, 400e3, -400e3, 400e3, h, jitter=jitter, seed=seed, nz=nz)
+    x = mesh.V[:, 0]
+    Hi = np.full(mesh.nV, 2000.0)
+    Hb = -0.0003 * x
+    f = _common_fields(mesh, Hi, Hb, np.full(mesh.nV, -10000.0), A_uniform=1e-18)
+    f["SMB"] = np.zeros(mesh.nV)
+    cfg = ub.default_config()
+    cfg.visc_it_norm_dUV_tol = 5e-8; cfg.visc_it_nit = 5000; cfg.visc_it_relax = 0.3; cfg.visc_eff_min = 1e4; cfg.vel_max = 5000.0
+    cfg.stress_balance_PETSc_rtol = 1e-7; cfg.stress_balance_PETSc_abstol = 1e-5
+    cfg.Glens_flow_law_exponent = 3.0; cfg.Glens_flow_law_epsilon_sq_0 = 1e-10; cfg.uniform_Glens_flow_factor = 1e-18
+    cfg.choice_sliding_law = ub.SLID_IDEALISED_SSA_ICESTREAM
+    cfg.refgeo_idealised_SSA_icestream_Hi = 2000.0; cfg.refgeo_idealised_SSA_icestream_dhdx = -0.0003
+    cfg.refgeo_idealised_SSA_icestream_L = 150e3; cfg.refgeo_idealised_SSA_icestream_m = 1.0
+    for k, (bu, bv) in enumerate([(ub.BC_ZERO, ub.BC_ZERO), (ub.BC_INFINITE_SSA_ICESTREAM, ub.BC_ZERO),
+                                  (ub.BC_ZERO, ub.BC_ZERO), (ub.BC_INFINITE_SSA_ICESTREAM, ub.BC_ZERO)]):   # north, east, south, west
+        cfg.BC_u[k] = bu; cfg.BC_v[k] = bv
+    return Workload(mesh, cfg, f, approximation=0, name="SSA_icestream")
