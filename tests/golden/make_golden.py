@@ -34,5 +34,32 @@ if os.path.exists(ref):
         if mm and mm.group(1) not in G["mismip_mod_small"]:
             G["mismip_mod_small"][mm.group(1)] = mm.group(2).strip()
 
+# Output of the reference itself: the checksum log of integrated_test_SSA_icestream_small (16 km, SSA, BC 'infinite_SSA_icestream').  Its first
+# stress-balance solve logs (sum, sum|.|, min, max) of u_b / v_b after every relaxed viscosity iteration: 520 iterations, all kept.
+def _nums(line):
+    return [float(x.replace("-.", "-0.")) for x in re.findall(r"=\s*(-?[0-9]*\.[0-9]+E[+-][0-9]+)", line)]
+
+
+ref = "/root/reference/automated_testing/UFEMISM/integrated_test_SSA_icestream_small/reference/checksum_logfile.txt"
+if os.path.exists(ref):
+    S = {"source": "automated_testing/UFEMISM/integrated_test_SSA_icestream_small/reference/checksum_logfile.txt",
+         "columns": ["sum", "sum_abs", "min", "max"], "u_b_relaxed": [], "v_b_relaxed": [], "u_b_limited": []}
+    for l in open(ref):
+        if l.startswith(" mask_grounded_ice:") and "nV" not in S:
+            S["nV"] = int(re.search(r"sum = (\d+)", l).group(1))          # every vertex is grounded ice in this experiment
+        elif l.startswith(" fraction_gr_b:") and "nTri" not in S:
+            S["nTri"] = int(round(_nums(l)[0]))                            # fraction_gr_b = 1 on every triangle
+        elif l.startswith(" tau_dx_b:") and "tau_dx_b" not in S:
+            S["tau_dx_b"] = _nums(l)
+        elif l.startswith(" ice%Hi:") and "Hi" not in S:
+            S["Hi"] = _nums(l)
+        elif "/solve_SSA/relax_viscosity_iterations]" in l and l.startswith(" u_b:"):
+            S["u_b_relaxed"].append(_nums(l))
+        elif "/solve_SSA/relax_viscosity_iterations]" in l and l.startswith(" v_b:"):
+            S["v_b_relaxed"].append(_nums(l))
+        elif "/solve_SSA/apply_velocity_limits]" in l and l.startswith(" u_b:"):
+            S["u_b_limited"].append(_nums(l))
+    json.dump(S, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "ssa_icestream_small.json"), "w"))   # compact: 520 x 3 rows
+
 json.dump(G, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden.json"), "w"), indent=1)
 print("wrote golden.json")

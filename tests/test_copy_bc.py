@@ -117,3 +117,47 @@ def test_ssa_icestream_matches_schoof_2006(stream):
         assert np.abs(v).max() < 0.1 * ua.max()
         assert 0.6 * ua.max() < u.max() < 1.15 * ua.max()
     assert rmse[32e3] < 700.0 and rmse[22e3] < 0.6 * rmse[32e3], rmse
+
+
+def reference_sequence():
+    import json, os
+    return json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ssa_icestream_small.json")))
+
+
+def check_against_reference_log(seq, nTri, first=1, last=12):
+    """seq[k] = (sum, max) of u_b after relaxed viscosity iteration k+1 on a mesh of nTri triangles; the reference's log holds the same
+    statistics for its own 7936-triangle mesh (tests/golden/README.md), so sums are compared per triangle."""
+    g = reference_sequence()
+    for k in range(first - 1, last):
+        ref_mean, ref_max = g["u_b_relaxed"][k][0] / g["nTri"], g["u_b_relaxed"][k][3]
+        mean, mx = seq[k][0] / nTri, seq[k][1]
+        tol = 0.10 if k == 0 else 0.04      # the first iterate's maximum sits on a single border triangle and depends on the mesh
+        assert abs(mean - ref_mean) <= tol * ref_mean and abs(mx - ref_max) <= tol * ref_max, (k + 1, mean, ref_mean, mx, ref_max)
+
+
+def test_reference_log_is_self_consistent():
+    g = reference_sequence()
+    assert g["nV"] == 4097 and g["nTri"] == 7936 and len(g["u_b_relaxed"]) == len(g["u_b_limited"]) == 520
+    # relax_viscosity_iterations: u = 0.3 u_new + 0.7 u_prev, so the sums obey the same recurrence (no velocity limit is hit here)
+    s_rel = np.array(g["u_b_relaxed"])[:, 0]; s_lim = np.array(g["u_b_limited"])[:, 0]
+    prev = np.concatenate(([0.0], s_rel[:-1]))
+    assert np.allclose(s_rel, 0.3 * s_lim + 0.7 * prev, rtol=1e-11)
+
+
+def test_oracle_follows_the_reference_checksum_log():
+    """Output of the reference itself (integrated_test_SSA_icestream_small, 16 km): mean and maximum of u_b after each of the first 12 viscosity
+    iterations, on a mesh of our generator with the reference's triangle count (7936 +- 1 %)."""
+    g = reference_sequence()
+    w = wl.ssa_icestream(13.7e3)
+    m = w.mesh
+    assert abs(m.nTri - g["nTri"]) < 0.01 * g["nTri"] and abs(m.nV - g["nV"]) < 0.01 * g["nV"]
+    o = ol.OracleMesh(m)
+    st, f = ub.alloc_velocity_state(m.nV, m.nTri, m.nz)
+    cfg = w.cfg
+    cfg.visc_it_nit = 0            # one viscosity iteration per call; the state carries u_b, v_b to the next one
+    seq = []
+    for k in range(12):
+        rc, nv, na = o.solve_velocity(cfg, 0, w.ice_inputs(), st)
+        assert rc == 0 and nv == 1
+        seq.append((f["u_vav_b"].sum(), f["u_vav_b"].max()))
+    check_against_reference_log(seq, m.nTri)

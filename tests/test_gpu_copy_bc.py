@@ -108,3 +108,35 @@ def test_unknown_bc_choice_is_an_error(setup):
     ice = w.ice_inputs()
     rc = ub.lib().ufe_b200_solve_SSA(ctx.h, C.byref(cfg), C.byref(ice), C.byref(st), C.byref(nv), C.byref(na), None, None, None)
     assert rc != 0 and b"unknown choice_BC_v" in ub.lib().ufe_b200_last_error()
+
+
+def test_gpu_follows_the_reference_checksum_log():
+    """The device path against output of the reference itself (tests/golden/ssa_icestream_small.json): mean and maximum of u_b after each of the
+    first 12 relaxed viscosity iterations of integrated_test_SSA_icestream_small, and the same sequence against the oracle."""
+    from test_copy_bc import check_against_reference_log, reference_sequence
+    g = reference_sequence()
+    w = wl.ssa_icestream(13.7e3)
+    m = w.mesh
+    assert abs(m.nTri - g["nTri"]) < 0.01 * g["nTri"]
+    ctx = ub.Context(device=0)
+    try:
+        ctx.mesh_create(m)
+        ctx.calc_matrix_operators()
+        o = ol.OracleMesh(m)
+        cfg = w.cfg
+        cfg.visc_it_nit = 0        # one viscosity iteration per call; the state carries u_b, v_b to the next one
+        cfg.stress_balance_PETSc_rtol = 1e-11; cfg.stress_balance_PETSc_abstol = 1e-30   # tight, so device and oracle can be compared closely
+        st, f = ub.alloc_velocity_state(m.nV, m.nTri, m.nz)
+        st_o, f_o = ub.alloc_velocity_state(m.nV, m.nTri, m.nz)
+        ice = w.ice_inputs()
+        nv, na = C.c_int(), C.c_int()
+        seq = []
+        for k in range(12):
+            ub.check(ub.lib().ufe_b200_solve_SSA(ctx.h, C.byref(cfg), C.byref(ice), C.byref(st), C.byref(nv), C.byref(na), None, None, None))
+            rc, nv_o, na_o = o.solve_velocity(cfg, 0, ice, st_o)
+            assert rc == 0 and nv.value == nv_o == 1
+            assert np.abs(f["u_vav_b"] - f_o["u_vav_b"]).max() <= 1e-7 * np.abs(f_o["u_vav_b"]).max(), k
+            seq.append((f["u_vav_b"].sum(), f["u_vav_b"].max()))
+        check_against_reference_log(seq, m.nTri)
+    finally:
+        ctx.close()
