@@ -33,6 +33,9 @@ if os.path.exists(ref):
         mm = re.match(r"\s*(mask_grounded_ice|mask_floating_ice|mask_icefree_land|mask_icefree_ocean)\s*:\s*(.*)", l)
         if mm and mm.group(1) not in G["mismip_mod_small"]:
             G["mismip_mod_small"][mm.group(1)] = mm.group(2).strip()
+    # output of the reference itself: (sum, sum|.|, min, max) of u_b after each of the first 20 relaxed DIVA viscosity iterations of the first solve
+    rows = [l for l in txt if l.startswith(" u_b:") and "/solve_DIVA_infinite_slab/relax_viscosity_iterations]" in l][:20]
+    G["mismip_mod_small"]["u_b_relaxed"] = [[float(x.replace("-.", "-0.")) for x in re.findall(r"=\s*(-?[0-9]*\.[0-9]+E[+-][0-9]+)", l)] for l in rows]
 
 # Output of the reference itself: the checksum log of integrated_test_SSA_icestream_small (16 km, SSA, BC 'infinite_SSA_icestream').  Its first
 # stress-balance solve logs (sum, sum|.|, min, max) of u_b / v_b after every relaxed viscosity iteration: 520 iterations, all kept.
