@@ -420,6 +420,15 @@ def run_b200(args, rank, world, rdv, log):
             B_streamed = (mg_info["fine_bytes"] if mg_info else blk_b.value) + 8 * rows_loc * 5
         kernel_name = ("k_mg_sweep level 0 (stiffness-matrix pass fused with block-Jacobi update / residual inside the multigrid cycle)" if top == "mg_fine"
                        else "k_spmv_blk (stiffness-matrix SpMV with fused Jacobi + dot products inside BiCGStab)")
+        # roofline.traffic: DRAM bytes per launch of that kernel from the committed `ncu --set full` capture (profiles/r01_ncu_traffic.json), valid
+        # for the mesh the capture was taken on (one rank, same triangle count); null otherwise
+        traffic, traffic_src = None, None
+        try:
+            cap = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))["k_mg_sweep_level0" if top == "mg_fine" else "k_spmv_blk"]
+            if world == 1 and cap.get("n_triangles") == int(m.nTri) and "dram_bytes_read" in cap:
+                traffic, traffic_src = int(cap["dram_bytes_read"]) + int(cap["dram_bytes_write"]), cap["report"]
+        except (OSError, KeyError, ValueError):
+            pass
         krylov_desc = ("BiCGStab + aggregation multigrid (%d levels %s, %d+%d block-Jacobi sweeps, omega %.2f, %s matrix storage in the preconditioner)"
                        % (mg_info["levels"], mg_info["nodes"], args.mg_nu, args.mg_nu, args.mg_omega, "FP32" if args.mg_fp32 else "FP64")
                        if mg_info else "BiCGStab + Jacobi")
@@ -445,7 +454,7 @@ def run_b200(args, rank, world, rdv, log):
             "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak if peak else None, "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
                          "algorithmic_bytes_per_launch": B_spmv, "streamed_bytes_per_launch": B_streamed,
-                         "streamed_GBps": B_streamed / (avg_ms * 1e-3) / 1e9 if spmv_n else 0.0, "avg_launch_ms": avg_ms, "launches": spmv_n, "traffic": None,
+                         "streamed_GBps": B_streamed / (avg_ms * 1e-3) / 1e9 if spmv_n else 0.0, "avg_launch_ms": avg_ms, "launches": spmv_n, "traffic": traffic, "traffic_source": traffic_src,
                          "share_of_step": spmv_ms / ms_total if ms_total else None, "frac_of_8TBs": achieved / 8000.0},
             "kernel_classes_ms": {k: v[0] for k, v in classes.items()},
             "clocks": clocks,
