@@ -170,7 +170,8 @@ int ufe_b200_apply_operator(ufe_b200_handle h, int op, const double* d_in, doubl
  *   u_b_prev, v_b_prev, PETSc_rtol, PETSc_abstol, n_Axb_its, BC_prescr_mask_b, BC_prescr_u_b, BC_prescr_v_b)
  * (src/UFEMISM/ice_dynamics/conservation_of_momentum/SSA_DIVA/solve_linearised_SSA_DIVA_infinite_slab.f90:23-178).
  * u_b_prev / v_b_prev are the rank's owned slices here (the reference gathers them globally only for the
- * periodic / ice-stream copy BCs, which this entry point does not offer). BC_* may be NULL (no prescribed velocities). */
+ * periodic / ice-stream copy BCs; the library completes the previous solution across ranks itself when cfg selects
+ * UFE_BC_PERIODIC_ISMIP_HOM / UFE_BC_INFINITE_SSA_ICESTREAM). BC_* may be NULL (no prescribed velocities). */
 int ufe_b200_solve_SSA_DIVA_linearised(ufe_b200_handle h, const ufe_b200_config* cfg, double* u_b, double* v_b,
                                        const double* N_b, const double* dN_dx_b, const double* dN_dy_b,
                                        const double* basal_friction_coefficient_b, const double* tau_dx_b,
