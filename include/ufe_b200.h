@@ -314,6 +314,23 @@ int ufe_b200_set_state_resident(ufe_b200_handle h, int on);
 int ufe_b200_solve_SIA(ufe_b200_handle h, const ufe_b200_config* cfg, double SIA_maximum_diffusivity, const double* Hi, const double* Hs,
                        const double* A_flow, double* u_3D_b, double* v_3D_b, double* D_3D_b, double* du_dz_3D_a, double* dv_dz_3D_a);
 
+/* ---- applied velocities --------------------------------------------------------- */
+/* Replaces set_ice_velocities_to_{SIA,SSA,SIASSA,DIVA}_results( mesh, ice, ...) (src/UFEMISM/ice_dynamics/conservation_of_momentum/
+ * conservation_of_momentum_main.f90:311-511), the fan-out of the solver results into ice%u_3D_b, ice%v_3D_b and the 3-D strain rates that
+ * solve_stress_balance does right after the solve (:113-152).  approximation = C%choice_stress_balance_approximation, hybrid_scheme =
+ * C%choice_hybrid_SIASSA_scheme ('add' | 'add_SIA_reduced', only read for SIA/SSA).  The solver results are the ones on the device: for SIA/SSA
+ * call ufe_b200_solve_SIA first (with du_dz_3D_a, dv_dz_3D_a if the strain rates are wanted), then ufe_b200_solve_SSA.  Afterwards the device's
+ * u_3D_b, v_3D_b ARE ice%u_3D_b, ice%v_3D_b, so ufe_b200_calc_secondary_velocities( h, NULL, NULL, ...) and ufe_b200_calc_vertical_velocities
+ * continue from them as calc_secondary_velocities / calc_vertical_velocities do in the reference (:167-170).  NULL outputs are skipped; the
+ * horizontal strain rates need the solve to have run with cfg->write_diagnostics = 1. */
+enum { UFE_APPROX_SSA = 0, UFE_APPROX_DIVA = 1, UFE_APPROX_SIA = 2, UFE_APPROX_SIASSA = 3 };
+enum { UFE_HYBRID_ADD = 0, UFE_HYBRID_ADD_SIA_REDUCED = 1 };
+typedef struct ufe_b200_ice_velocities {
+  double *u_3D_b, *v_3D_b;                                   /* (ti1:ti2, nz) */
+  double *du_dx_3D, *du_dy_3D, *du_dz_3D, *dv_dx_3D, *dv_dy_3D, *dv_dz_3D, *dw_dx_3D, *dw_dy_3D;   /* (vi1:vi2, nz) */
+} ufe_b200_ice_velocities;
+int ufe_b200_set_ice_velocities(ufe_b200_handle h, int approximation, int hybrid_scheme, const ufe_b200_ice_velocities* out);
+
 /* ---- secondary velocities ------------------------------------------------------------ */
 /* Outputs of calc_secondary_velocities( mesh, ice) (src/UFEMISM/ice_dynamics/conservation_of_momentum/conservation_of_momentum_main.f90:177-246):
  * the ice%... members of the same names; b-grid fields (ti1:ti2), a-grid fields (vi1:vi2[,nz]).  NULL pointers are skipped. */

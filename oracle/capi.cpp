@@ -286,3 +286,14 @@ extern "C" void orc_calc_and_apply_spill_over_flux(void* h, const ufe_b200_masks
   MaskSet M; std::memcpy(&M, masks, sizeof(M));
   calc_and_apply_spill_over_flux(o->mv, M, Hi_eff, u_vav_b, v_vav_b, dt, Hi_new, Qspill);
 }
+
+extern "C" int orc_set_ice_velocities(void* h, int approximation, int scheme, const double* u_3D_b, const double* v_3D_b, const double* u_b,
+                                      const double* v_b, const double* du_dx_a, const double* du_dy_a, const double* dv_dx_a,
+                                      const double* dv_dy_a, const double* du_dz_3D, const double* dv_dz_3D, const ufe_b200_ice_velocities* out) {
+  auto* o = static_cast<OracleMesh*>(h);
+  SolverResults R;
+  R.u_3D_b = u_3D_b; R.v_3D_b = v_3D_b; R.u_b = u_b; R.v_b = v_b; R.du_dx_a = du_dx_a; R.du_dy_a = du_dy_a; R.dv_dx_a = dv_dx_a; R.dv_dy_a = dv_dy_a;
+  R.du_dz_3D = du_dz_3D; R.dv_dz_3D = dv_dz_3D;
+  IceVelocities I{out->u_3D_b, out->v_3D_b, out->du_dx_3D, out->du_dy_3D, out->du_dz_3D, out->dv_dx_3D, out->dv_dy_3D, out->dv_dz_3D, out->dw_dx_3D, out->dw_dy_3D};
+  return set_ice_velocities(o->mv, approximation, scheme, R, I);
+}

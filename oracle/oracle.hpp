@@ -148,6 +148,18 @@ int calc_dHi_dt(const MeshView& mesh, const Config& C, ThicknessIO& io, double* 
 void calc_flux_divergence_matrix_upwind(const MeshView& mesh, const double* u_vav_b, const double* v_vav_b,
                                         const double* fraction_margin, Csr& M_divQ, std::vector<double>* u_perp = nullptr);
 
+// --- set_ice_velocities_to_{SIA,SSA,SIASSA,DIVA}_results (conservation_of_momentum_main.f90:311-511) -------
+// approximation: 0 SSA, 1 DIVA, 2 SIA, 3 SIA/SSA; scheme: 0 'add', 1 'add_SIA_reduced'.  Inputs: the solver objects' fields (NULL where the
+// approximation has none); outputs: ice%u_3D_b, v_3D_b (nTri,nz) and the eight 3-D strain rates (nV,nz), NULL = skipped.
+struct SolverResults {
+  const double *u_3D_b = nullptr, *v_3D_b = nullptr;               // SIA% or DIVA% (nTri,nz)
+  const double *u_b = nullptr, *v_b = nullptr;                     // SSA% (nTri)
+  const double *du_dx_a = nullptr, *du_dy_a = nullptr, *dv_dx_a = nullptr, *dv_dy_a = nullptr;   // SSA% / DIVA% (nV)
+  const double *du_dz_3D = nullptr, *dv_dz_3D = nullptr;           // SIA% / DIVA% (nV,nz)
+};
+struct IceVelocities { double *u_3D_b, *v_3D_b, *du_dx_3D, *du_dy_3D, *du_dz_3D, *dv_dx_3D, *dv_dy_3D, *dv_dz_3D, *dw_dx_3D, *dw_dy_3D; };
+int set_ice_velocities(const MeshView& mesh, int approximation, int scheme, const SolverResults& R, IceVelocities& I);
+
 // --- secondary velocities (conservation_of_momentum_main.f90:177-246): every pointer is an output the caller owns
 struct SecondaryVelocities {
   double *u_surf_b, *v_surf_b, *uabs_surf_b, *u_base_b, *v_base_b, *uabs_base_b, *u_vav_b, *v_vav_b, *uabs_vav_b;   // (nTri)

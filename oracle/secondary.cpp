@@ -1,5 +1,6 @@
 // TEST INFRASTRUCTURE ONLY (see oracle.hpp).
 // calc_secondary_velocities (src/UFEMISM/ice_dynamics/conservation_of_momentum/conservation_of_momentum_main.f90:177-246)
+#include <algorithm>
 #include <cmath>
 #include <vector>
 
@@ -153,3 +154,51 @@ void calc_vertical_velocities(const MeshView& mesh, const Operators& ops, const 
 }
 
 }  // namespace orc
+
+// ---------------------------------------------------------------------------------------------------
+// set_ice_velocities_to_SIA_results (conservation_of_momentum_main.f90:311-347), _SSA_ (:349-385), _SIASSA_ (:387-463), _DIVA_ (:465-511)
+// ---------------------------------------------------------------------------------------------------
+int orc::set_ice_velocities(const MeshView& mesh, int approximation, int scheme, const SolverResults& R, IceVelocities& I) {
+  const int nV = mesh.nV, nTri = mesh.nTri, nz = mesh.nz;
+  const double pi = 3.141592653589793238462643383279502884197;
+  auto zero_a = [&](double* d) { if (d) std::fill(d, d + (size_t)nV * nz, 0.0); };
+  auto layers = [&](double* d, const double* s2) { if (d) for (int k = 0; k < nz; ++k) for (int v = 0; v < nV; ++v) d[(size_t)k * nV + v] = s2[v]; };
+  auto copy_a = [&](double* d, const double* s3) { if (d) std::copy(s3, s3 + (size_t)nV * nz, d); };
+  switch (approximation) {
+    case 2:  // SIA
+      for (size_t j = 0; j < (size_t)nTri * nz; ++j) { I.u_3D_b[j] = R.u_3D_b[j]; I.v_3D_b[j] = R.v_3D_b[j]; }
+      copy_a(I.du_dz_3D, R.du_dz_3D); copy_a(I.dv_dz_3D, R.dv_dz_3D);
+      zero_a(I.du_dx_3D); zero_a(I.du_dy_3D); zero_a(I.dv_dx_3D); zero_a(I.dv_dy_3D);
+      break;
+    case 0:  // SSA
+      for (int k = 0; k < nz; ++k) for (int t = 0; t < nTri; ++t) { I.u_3D_b[(size_t)k * nTri + t] = R.u_b[t]; I.v_3D_b[(size_t)k * nTri + t] = R.v_b[t]; }
+      layers(I.du_dx_3D, R.du_dx_a); layers(I.du_dy_3D, R.du_dy_a); layers(I.dv_dx_3D, R.dv_dx_a); layers(I.dv_dy_3D, R.dv_dy_a);
+      zero_a(I.du_dz_3D); zero_a(I.dv_dz_3D);
+      break;
+    case 3:  // SIA/SSA
+      if (scheme != 0 && scheme != 1) return 1;  // crash('unknown choice_hybrid_SIASSA_scheme_config')
+      for (int t = 0; t < nTri; ++t) {
+        double w_sia_u = 1.0, w_sia_v = 1.0;
+        if (scheme == 1) {
+          w_sia_u = 1.0 - (2.0 / pi) * std::atan(std::pow(std::fabs(R.u_b[t]), 2.0) / std::pow(30.0, 2.0));
+          w_sia_v = 1.0 - (2.0 / pi) * std::atan(std::pow(std::fabs(R.v_b[t]), 2.0) / std::pow(30.0, 2.0));
+        }
+        for (int k = 0; k < nz; ++k) {
+          const size_t j = (size_t)k * nTri + t;
+          I.u_3D_b[j] = w_sia_u * R.u_3D_b[j] + R.u_b[t];
+          I.v_3D_b[j] = w_sia_v * R.v_3D_b[j] + R.v_b[t];
+        }
+      }
+      copy_a(I.du_dz_3D, R.du_dz_3D); copy_a(I.dv_dz_3D, R.dv_dz_3D);
+      layers(I.du_dx_3D, R.du_dx_a); layers(I.du_dy_3D, R.du_dy_a); layers(I.dv_dx_3D, R.dv_dx_a); layers(I.dv_dy_3D, R.dv_dy_a);
+      break;
+    case 1:  // DIVA
+      for (size_t j = 0; j < (size_t)nTri * nz; ++j) { I.u_3D_b[j] = R.u_3D_b[j]; I.v_3D_b[j] = R.v_3D_b[j]; }
+      layers(I.du_dx_3D, R.du_dx_a); layers(I.du_dy_3D, R.du_dy_a); layers(I.dv_dx_3D, R.dv_dx_a); layers(I.dv_dy_3D, R.dv_dy_a);
+      copy_a(I.du_dz_3D, R.du_dz_3D); copy_a(I.dv_dz_3D, R.dv_dz_3D);
+      break;
+    default: return 2;  // crash('unknown choice_stress_balance_approximation')
+  }
+  zero_a(I.dw_dx_3D); zero_a(I.dw_dy_3D);
+  return 0;
+}

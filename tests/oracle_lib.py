@@ -41,6 +41,7 @@ def lib():
         L.orc_Halfar_H.argtypes = [C.c_double] * 7
         L.orc_Schoof2006_icestream.argtypes = [C.c_double] * 7 + [dp, dp]
         L.orc_solve_SIA.argtypes = [C.c_void_p, C.POINTER(ub.Config), C.c_double] + [dp] * 8
+        L.orc_set_ice_velocities.argtypes = [C.c_void_p, C.c_int, C.c_int] + [dp] * 10 + [C.POINTER(ub.IceVelocities)]
         L.orc_calc_secondary_velocities.argtypes = [C.c_void_p, dp, dp, C.POINTER(ub.SecondaryVelocities)]
         L.orc_calc_vertical_velocities.argtypes = [C.c_void_p, C.POINTER(ub.Config), C.POINTER(ub.VerticalVelocityIO), dp, dp, dp, dp]
         PC = C.POINTER(ub.Config)
@@ -145,6 +146,11 @@ class OracleMesh:
         lib().orc_solve_SIA(self.h, C.byref(cfg), max_diffusivity, ub.dp(Hi), ub.dp(Hs), ub.dp(A_flow), *(ub.dp(out[k]) for k in
                             ("u_3D_b", "v_3D_b", "D_3D_b", "du_dz_3D_a", "dv_dz_3D_a")))
         return out
+
+    def set_ice_velocities(self, approximation, scheme, out, u_3D_b=None, v_3D_b=None, u_b=None, v_b=None, du_dx_a=None, du_dy_a=None,
+                           dv_dx_a=None, dv_dy_a=None, du_dz_3D=None, dv_dz_3D=None):
+        return lib().orc_set_ice_velocities(self.h, approximation, scheme, ub.dp(u_3D_b), ub.dp(v_3D_b), ub.dp(u_b), ub.dp(v_b), ub.dp(du_dx_a),
+                                            ub.dp(du_dy_a), ub.dp(dv_dx_a), ub.dp(dv_dy_a), ub.dp(du_dz_3D), ub.dp(dv_dz_3D), C.byref(out))
 
     def calc_secondary_velocities(self, u_3D_b, v_3D_b):
         self.calc_matrix_operators()

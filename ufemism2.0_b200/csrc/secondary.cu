@@ -3,6 +3,8 @@
 // Reference: src/UFEMISM/ice_dynamics/conservation_of_momentum/conservation_of_momentum_main.f90:177-246 -- one loop over triangles,
 // 2 map_b_a_3D + 6 map_b_a_2D SpMVs (the matrix re-read 2 nz + 6 times), two loops over vertices.  Here: one triangle kernel (a column read
 // of u_3D_b, v_3D_b) and one vertex kernel that gathers each neighbouring triangle once per layer for all outputs.
+#include <cstring>
+
 #include "mesh.cuh"
 #include "velocity.cuh"
 
@@ -245,6 +247,104 @@ extern "C" int ufe_b200_calc_secondary_velocities(ufe_b200_handle h, const doubl
   }
   UFE_CUDA(cudaStreamSynchronize(st));
   S.have_3D = true;
+  return 0;
+}
+
+// ---- set_ice_velocities_to_{SIA,SSA,SIASSA,DIVA}_results (conservation_of_momentum_main.f90:311-511) -------------------------------------
+namespace ufe { namespace {
+// ice%u_3D_b( ti,:) from the solver results, in place in the device's u_3D_b / v_3D_b:
+//   mode 0 (SSA)                  u_3D_b( ti,k) = SSA%u_b( ti)                                              (:361-364)
+//   mode 1 (SIA/SSA, 'add')       u_3D_b( ti,k) = SIA%u_3D_b( ti,k) + SSA%u_b( ti)                          (:405-408)
+//   mode 2 ('add_SIA_reduced')    u_3D_b( ti,k) = w_sia_u SIA%u_3D_b( ti,k) + SSA%u_b( ti),
+//                                 w_sia_u = 1 - (2/pi) atan( |u_b|^2 / 30^2), likewise v                     (:430-435)
+__global__ void k_set_velocities_b(int mode, int n, int off, size_t nb_ext, int nz, const double* __restrict__ u, const double* __restrict__ v,
+                                   double* __restrict__ u_3D, double* __restrict__ v_3D) {
+  const double pi = 3.141592653589793238462643383279502884197;   // parameters.f90:17
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const size_t i = off + r;
+    const double ub = u[i], vb = v[i];
+    double wu = 1.0, wv = 1.0;
+    if (mode == 0) { wu = 0.0; wv = 0.0; }
+    else if (mode == 2) {
+      wu = 1.0 - (2.0 / pi) * atan((fabs(ub) * fabs(ub)) / (30.0 * 30.0));
+      wv = 1.0 - (2.0 / pi) * atan((fabs(vb) * fabs(vb)) / (30.0 * 30.0));
+    }
+    for (int k = 0; k < nz; ++k) {
+      const size_t j = (size_t)k * nb_ext + i;
+      if (mode == 0) { u_3D[j] = ub; v_3D[j] = vb; }
+      else { u_3D[j] = wu * u_3D[j] + ub; v_3D[j] = wv * v_3D[j] + vb; }
+    }
+  }
+}
+// ice%du_dx_3D( vi,:) = SSA%du_dx_a( vi) and friends: one 2-D a-grid field into every layer
+__global__ void k_layers_from_2D(int n, int off, size_t na_ext, int nz, const double* __restrict__ a2d, double* __restrict__ a3d) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const double x = a2d[off + r];
+    for (int k = 0; k < nz; ++k) a3d[(size_t)k * na_ext + off + r] = x;
+  }
+}
+} }  // namespace ufe::<anon>
+
+extern "C" int ufe_b200_set_ice_velocities(ufe_b200_handle h, int approximation, int hybrid_scheme, const ufe_b200_ice_velocities* out) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && out, "ufe_b200_set_ice_velocities: NULL argument");
+  UFE_CHECK(approximation >= UFE_APPROX_SSA && approximation <= UFE_APPROX_SIASSA, "unknown choice_stress_balance_approximation %d", approximation);
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_CHECK(c->vel && c->vel->uploaded, "ufe_b200_set_ice_velocities: no solver results on the device");
+  Mesh& M = *c->mesh; Velocity& V = *c->vel;
+  cudaStream_t st = c->stream;
+  const int nz = M.nz, na = M.a.n_loc(), nb = M.b.n_loc();
+  const size_t na_ext = M.a.n_ext(), nb_ext = M.b.n_ext();
+  int mode = -1;   // what happens to the device's u_3D_b, v_3D_b
+  switch (approximation) {
+    case UFE_APPROX_SIA:  UFE_CHECK(V.last_approximation == UFE_APPROX_SIA, "set_ice_velocities_to_SIA_results: the last solve was not solve_SIA"); break;
+    case UFE_APPROX_DIVA: UFE_CHECK(V.last_approximation == UFE_APPROX_DIVA, "set_ice_velocities_to_DIVA_results: the last solve was not solve_DIVA"); break;
+    case UFE_APPROX_SSA:  UFE_CHECK(V.last_approximation == UFE_APPROX_SSA, "set_ice_velocities_to_SSA_results: the last solve was not solve_SSA"); mode = 0; break;
+    default:
+      UFE_CHECK(V.have_sia && V.last_approximation == UFE_APPROX_SSA, "set_ice_velocities_to_SIASSA_results: call ufe_b200_solve_SIA, then ufe_b200_solve_SSA");
+      UFE_CHECK(hybrid_scheme == UFE_HYBRID_ADD || hybrid_scheme == UFE_HYBRID_ADD_SIA_REDUCED, "unknown choice_hybrid_SIASSA_scheme_config %d", hybrid_scheme);
+      mode = hybrid_scheme == UFE_HYBRID_ADD ? 1 : 2;
+      V.have_sia = false;   // u_3D_b, v_3D_b now hold the hybrid velocities; the next hybrid step starts from a new solve_SIA
+  }
+  if (mode >= 0) {
+    UFE_LAUNCH(c, TC_TRI);
+    k_set_velocities_b<<<grid_for(c, nb, 128, 16), 128, 0, st>>>(mode, nb, M.b.off(), nb_ext, nz, V.u.p, V.v.p, V.u_3D.p, V.v_3D.p);
+    UFE_CUDA(cudaGetLastError());
+  }
+  auto d2h3 = [&](double* dst, const double* src, size_t n_ext, int off, int n_loc) {
+    return dst ? cudaMemcpy2DAsync(dst, sizeof(double) * n_loc, src + off, sizeof(double) * n_ext, sizeof(double) * n_loc, nz, cudaMemcpyDeviceToHost, st)
+               : cudaSuccess;
+  };
+  { UFE_REGION(c, TC_D2H); UFE_CUDA(d2h3(out->u_3D_b, V.u_3D.p, nb_ext, M.b.off(), nb)); UFE_CUDA(d2h3(out->v_3D_b, V.v_3D.p, nb_ext, M.b.off(), nb)); }
+  // horizontal strain rates: zero in the SIA, the solver's a-grid fields in every layer otherwise
+  double* const h2d_out[4] = {out->du_dx_3D, out->du_dy_3D, out->dv_dx_3D, out->dv_dy_3D};
+  const double* const src2d[4] = {V.du_dx.p, V.du_dy.p, V.dv_dx.p, V.dv_dy.p};
+  DBuf<double> layers;
+  for (int q = 0; q < 4; ++q) {
+    if (!h2d_out[q]) continue;
+    if (approximation == UFE_APPROX_SIA) { memset(h2d_out[q], 0, sizeof(double) * (size_t)na * nz); continue; }
+    UFE_CHECK(V.have_strain_2d, "ufe_b200_set_ice_velocities: the solve did not keep its strain rates (cfg->write_diagnostics = 0)");
+    UFE_TRY(layers.alloc(na_ext * nz));
+    { UFE_LAUNCH(c, TC_COLUMN); k_layers_from_2D<<<grid_for(c, na, 128, 16), 128, 0, st>>>(na, M.a.off(), na_ext, nz, src2d[q], layers.p); }
+    UFE_CUDA(cudaGetLastError());
+    UFE_REGION(c, TC_D2H);
+    UFE_CUDA(d2h3(h2d_out[q], layers.p, na_ext, M.a.off(), na));
+    UFE_CUDA(cudaStreamSynchronize(st));   // the scratch buffer is reused by the next field
+  }
+  // vertical shear: the SIA's (also in the hybrid), DIVA's own, zero in the SSA
+  if (out->du_dz_3D || out->dv_dz_3D) {
+    if (approximation == UFE_APPROX_SSA) {
+      if (out->du_dz_3D) memset(out->du_dz_3D, 0, sizeof(double) * (size_t)na * nz);
+      if (out->dv_dz_3D) memset(out->dv_dz_3D, 0, sizeof(double) * (size_t)na * nz);
+    } else {
+      UFE_CHECK(V.have_dudz_3d, "ufe_b200_set_ice_velocities: du_dz_3D is not on the device (give du_dz_3D_a, dv_dz_3D_a to ufe_b200_solve_SIA)");
+      UFE_REGION(c, TC_D2H);
+      UFE_CUDA(d2h3(out->du_dz_3D, V.du_dz_3D.p, na_ext, M.a.off(), na)); UFE_CUDA(d2h3(out->dv_dz_3D, V.dv_dz_3D.p, na_ext, M.a.off(), na));
+    }
+  }
+  if (out->dw_dx_3D) memset(out->dw_dx_3D, 0, sizeof(double) * (size_t)na * nz);   // all four routines neglect the gradients of w
+  if (out->dw_dy_3D) memset(out->dw_dy_3D, 0, sizeof(double) * (size_t)na * nz);
+  UFE_CUDA(cudaStreamSynchronize(st));
   return 0;
 }
 

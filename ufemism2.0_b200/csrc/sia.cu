@@ -113,5 +113,6 @@ extern "C" int ufe_b200_solve_SIA(ufe_b200_handle h, const ufe_b200_config* cfg,
   }
   UFE_CUDA(cudaStreamSynchronize(st));
   V.uploaded = true;   // Hi, Hs, A_flow, u_3D, v_3D are resident now
+  V.have_sia = true; V.last_approximation = UFE_APPROX_SIA; V.have_dudz_3d = du_dz_3D_a != nullptr;
   return 0;
 }

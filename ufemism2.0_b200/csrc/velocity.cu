@@ -926,6 +926,10 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
       UFE_CUDA(cudaMemsetAsync(V.u_base.p, 0, sizeof(double) * V.u_base.n, st)); UFE_CUDA(cudaMemsetAsync(V.v_base.p, 0, sizeof(double) * V.v_base.n, st));
       UFE_CUDA(cudaMemsetAsync(V.u_3D.p, 0, sizeof(double) * V.u_3D.n, st)); UFE_CUDA(cudaMemsetAsync(V.v_3D.p, 0, sizeof(double) * V.v_3D.n, st));
     }
+    // the solver object's strain rates stay at their initial zeros in the reference (allocate_SSA_solver / allocate_DIVA_solver)
+    for (DBuf<double>* b : {&V.du_dx, &V.du_dy, &V.dv_dx, &V.dv_dy}) UFE_CUDA(cudaMemsetAsync(b->p, 0, sizeof(double) * b->n, st));
+    if (DIVA) { UFE_CUDA(cudaMemsetAsync(V.du_dz_3D.p, 0, sizeof(double) * V.du_dz_3D.n, st)); UFE_CUDA(cudaMemsetAsync(V.dv_dz_3D.p, 0, sizeof(double) * V.dv_dz_3D.n, st)); V.have_dudz_3d = true; }
+    V.last_approximation = DIVA ? UFE_APPROX_DIVA : UFE_APPROX_SSA; V.have_strain_2d = true;
     UFE_CUDA(cudaStreamSynchronize(st));
     return 0;
   }
@@ -1055,6 +1059,9 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
   UFE_CUDA(cudaGetLastError());
   UFE_CUDA(cudaStreamSynchronize(st));
   *n_visc_its = it;
+  V.last_approximation = DIVA ? UFE_APPROX_DIVA : UFE_APPROX_SSA;
+  V.have_strain_2d = p.diagnostics != 0;
+  if (DIVA) { V.have_dudz_3d = true; V.have_sia = false; }   // DIVA%du_dz_3D_a is part of every viscosity iteration; u_3D_b is DIVA's now
   return 0;
 }
 

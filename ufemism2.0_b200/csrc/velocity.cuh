@@ -47,6 +47,9 @@ struct Velocity {
   DBuf<double> red, partials;
   DBuf<unsigned> counter;
   bool uploaded = false;
+  // what the last solves left on the device (read by ufe_b200_set_ice_velocities)
+  bool have_strain_2d = false, have_dudz_3d = false, have_sia = false;
+  int last_approximation = -1;   // UFE_APPROX_* of the last velocity solve (SIA: solve_SIA)
   int alloc(Ctx* c);
 };
 

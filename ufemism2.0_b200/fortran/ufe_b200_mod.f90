@@ -259,6 +259,17 @@ module ufe_b200_mod
       integer(c_int) :: ierr
     end function
 
+    ! set_ice_velocities_to_{SIA,SSA,SIASSA,DIVA}_results (conservation_of_momentum_main.f90:311-511); out = c_loc of a ufe_b200_ice_velocities
+    ! (c_loc's of ice%u_3D_b, v_3D_b, du_dx_3D, du_dy_3D, du_dz_3D, dv_dx_3D, dv_dy_3D, dv_dz_3D, dw_dx_3D, dw_dy_3D; c_null_ptr = skipped);
+    ! approximation: 0 'SSA', 1 'DIVA', 2 'SIA', 3 'SIA/SSA'; hybrid_scheme: 0 'add', 1 'add_SIA_reduced'
+    function c_ufe_b200_set_ice_velocities( h, approximation, hybrid_scheme, out) bind(C, name='ufe_b200_set_ice_velocities') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: approximation, hybrid_scheme
+      type(c_ptr), value :: out
+      integer(c_int) :: ierr
+    end function
+
     ! calc_secondary_velocities (conservation_of_momentum_main.f90:177-246); out = c_loc of a ufe_b200_secondary_velocities
     function c_ufe_b200_calc_secondary_velocities( h, u_3D_b, v_3D_b, out) bind(C, name='ufe_b200_calc_secondary_velocities') result( ierr)
       import :: c_int, c_ptr

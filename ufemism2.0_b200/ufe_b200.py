@@ -102,6 +102,26 @@ SECONDARY_FIELDS = ["u_surf_b", "v_surf_b", "uabs_surf_b", "u_base_b", "v_base_b
                     "u_surf", "v_surf", "u_base", "v_base", "u_vav", "v_vav", "uabs_surf", "uabs_base", "uabs_vav", "R_shear"]
 
 
+ICE_VELOCITY_FIELDS = ["u_3D_b", "v_3D_b", "du_dx_3D", "du_dy_3D", "du_dz_3D", "dv_dx_3D", "dv_dy_3D", "dv_dz_3D", "dw_dx_3D", "dw_dy_3D"]
+APPROX_SSA, APPROX_DIVA, APPROX_SIA, APPROX_SIASSA = 0, 1, 2, 3
+HYBRID_ADD, HYBRID_ADD_SIA_REDUCED = 0, 1
+
+
+class IceVelocities(C.Structure):
+    """outputs of set_ice_velocities_to_*_results: ice%u_3D_b, v_3D_b (ti1:ti2,nz) and the 3-D strain rates (vi1:vi2,nz)"""
+    _fields_ = [(n, c_dp) for n in ICE_VELOCITY_FIELDS]
+
+
+def alloc_ice_velocities(n_a, n_b, nz, fill=0.0):
+    s = IceVelocities()
+    arrs = {}
+    for n in ICE_VELOCITY_FIELDS:
+        a = np.full((n_b if n.endswith("_b") else n_a, nz), fill, order="F")
+        arrs[n] = a
+        setattr(s, n, dp(a))
+    return s, arrs
+
+
 class SecondaryVelocities(C.Structure):
     _fields_ = [(n, c_dp) for n in SECONDARY_FIELDS]
 
@@ -253,6 +273,7 @@ def lib():
                                    C.POINTER(ThicknessIO), c_dp] + [C.POINTER(C.c_int)] * 3
     L.ufe_b200_solve_SIA.argtypes = [H, C.POINTER(Config), C.c_double] + [c_dp] * 8
     L.ufe_b200_calc_secondary_velocities.argtypes = [H, c_dp, c_dp, C.POINTER(SecondaryVelocities)]
+    L.ufe_b200_set_ice_velocities.argtypes = [H, C.c_int, C.c_int, C.POINTER(IceVelocities)]
     L.ufe_b200_set_state_resident.argtypes = [H, C.c_int]
     PC = C.POINTER(Config)
     L.ufe_b200_determine_masks.argtypes = [H, PC, c_dp, c_dp, c_dp, C.POINTER(Masks)]
@@ -286,7 +307,7 @@ ABI_SYMBOLS = [
     "ufe_b200_set_mg_params", "ufe_b200_get_mg_info", "ufe_b200_mg_host_transfer", "ufe_b200_mg_host_transfer_get", "ufe_b200_mg_host_transfer_parts", "ufe_b200_mg_host_transfer_parts_get",
     "ufe_b200_solve_DIVA", "ufe_b200_solve_SSA", "ufe_b200_velocity_upload", "ufe_b200_velocity_solve_resident",
     "ufe_b200_velocity_download", "ufe_b200_thickness_upload", "ufe_b200_pc_step_resident", "ufe_b200_pc_step",
-    "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA", "ufe_b200_calc_secondary_velocities", "ufe_b200_calc_vertical_velocities", "ufe_b200_set_state_resident", "ufe_b200_determine_masks", "ufe_b200_calc_effective_thickness",
+    "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA", "ufe_b200_set_ice_velocities", "ufe_b200_calc_secondary_velocities", "ufe_b200_calc_vertical_velocities", "ufe_b200_set_state_resident", "ufe_b200_determine_masks", "ufe_b200_calc_effective_thickness",
                "ufe_b200_calc_grounded_fractions", "ufe_b200_calc_critical_timestep_adv", "ufe_b200_calc_critical_timestep_SIA", "ufe_b200_alter_params_defaults", "ufe_b200_geometry_resident", "ufe_b200_alter_ice_thickness",
                "ufe_b200_calc_and_apply_spill_over_flux",
     "ufe_b200_timing_enable", "ufe_b200_timing_get", "ufe_b200_timing_reset", "ufe_b200_timer_start", "ufe_b200_timer_stop",
