@@ -386,6 +386,17 @@ int ufe_b200_calc_grounded_fractions(ufe_b200_handle h, const ufe_b200_config* c
  * UFE_GF_BILIN_INTERP_TAF); choice < 0 switches the behaviour off again. */
 int ufe_b200_geometry_resident(ufe_b200_handle h, int choice, int nbins, const double* dHb, const double* bedrock_cdf, const double* bedrock_cdf_b);
 
+/* Replaces calc_pc_truncation_error( mesh, ice, pc) (time_stepping/predictor_corrector_scheme.f90:327-361; Robinson et al., 2020, Eq. 32) and the
+ * error assessment that follows it in run_ice_dynamics_model_pc (:254-279): tau_np1 = zeta_t |Hi_np1 - Hi_star_np1| / ((3 zeta_t + 3) dt_n);
+ * eta_np1 = max( C%pc_eta_min, tau_np1) over fully grounded vertices off the grounding line; n_tot = vertices with fraction_gr = 1, n_guilty =
+ * those of them with tau_np1 > C%pc_epsilon, whose pc%tau_n_guilty is incremented.  All fields (vi1:vi2); logical masks as 0/1; the three scalar
+ * results are global (the reference's MPI_ALLREDUCE MAX / SUM).  tau_np1 and tau_n_guilty may be NULL.  The time-step rule itself (Eq. 33 and
+ * the accept / retry decision, :59-76, 281-300) is scalar host logic and stays in the Fortran driver. */
+int ufe_b200_calc_pc_truncation_error(ufe_b200_handle h, double zeta_t, double dt_n, double pc_eta_min, double pc_epsilon, const double* Hi_np1,
+                                      const double* Hi_star_np1, const int32_t* mask_grounded_ice, const int32_t* mask_gl_gr,
+                                      const double* fraction_gr, double* tau_np1, int32_t* tau_n_guilty, double* eta_np1, int32_t* n_tot,
+                                      int32_t* n_guilty);
+
 /* Replace calc_critical_timestep_adv / _SIA( mesh, ice, dt_crit) (utilities/time_step_criteria.f90:80-141, 20-78); the result is the global
  * minimum (the reference's MPI_ALLREDUCE( MPI_MIN)).  u_vav_b, v_vav_b NULL = the velocities of the last device solve. */
 int ufe_b200_calc_critical_timestep_adv(ufe_b200_handle h, const ufe_b200_config* cfg, int do_grounded_only_adv_dt, const double* Hi,

@@ -297,3 +297,10 @@ extern "C" int orc_set_ice_velocities(void* h, int approximation, int scheme, co
   IceVelocities I{out->u_3D_b, out->v_3D_b, out->du_dx_3D, out->du_dy_3D, out->du_dz_3D, out->dv_dx_3D, out->dv_dy_3D, out->dv_dz_3D, out->dw_dx_3D, out->dw_dy_3D};
   return set_ice_velocities(o->mv, approximation, scheme, R, I);
 }
+
+extern "C" void orc_calc_pc_truncation_error(int nV, double zeta_t, double dt_n, double pc_eta_min, double pc_epsilon, const double* Hi_np1,
+                                             const double* Hi_star_np1, const int* mask_grounded_ice, const int* mask_gl_gr,
+                                             const double* fraction_gr, double* tau_np1, int* tau_n_guilty, double* eta_np1, int* n_tot, int* n_guilty) {
+  calc_pc_truncation_error(nV, zeta_t, dt_n, pc_eta_min, pc_epsilon, Hi_np1, Hi_star_np1, mask_grounded_ice, mask_gl_gr, fraction_gr, tau_np1,
+                           tau_n_guilty, eta_np1, n_tot, n_guilty);
+}

@@ -148,6 +148,11 @@ int calc_dHi_dt(const MeshView& mesh, const Config& C, ThicknessIO& io, double* 
 void calc_flux_divergence_matrix_upwind(const MeshView& mesh, const double* u_vav_b, const double* v_vav_b,
                                         const double* fraction_margin, Csr& M_divQ, std::vector<double>* u_perp = nullptr);
 
+// --- calc_pc_truncation_error + error assessment (time_stepping/predictor_corrector_scheme.f90:327-361, 254-279) ---------
+void calc_pc_truncation_error(int nV, double zeta_t, double dt_n, double pc_eta_min, double pc_epsilon, const double* Hi_np1, const double* Hi_star_np1,
+                              const int* mask_grounded_ice, const int* mask_gl_gr, const double* fraction_gr, double* tau_np1, int* tau_n_guilty,
+                              double* eta_np1, int* n_tot, int* n_guilty);
+
 // --- set_ice_velocities_to_{SIA,SSA,SIASSA,DIVA}_results (conservation_of_momentum_main.f90:311-511) -------
 // approximation: 0 SSA, 1 DIVA, 2 SIA, 3 SIA/SSA; scheme: 0 'add', 1 'add_SIA_reduced'.  Inputs: the solver objects' fields (NULL where the
 // approximation has none); outputs: ice%u_3D_b, v_3D_b (nTri,nz) and the eight 3-D strain rates (nV,nz), NULL = skipped.

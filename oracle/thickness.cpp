@@ -180,3 +180,25 @@ int calc_dHi_dt(const MeshView& mesh, const Config& C, ThicknessIO& io, double* 
 }
 
 }  // namespace orc
+
+// ---------------------------------------------------------------------------------------------------
+// calc_pc_truncation_error (predictor_corrector_scheme.f90:327-361; Robinson et al., 2020, Eq. 32) and the count of unstable
+// vertices that run_ice_dynamics_model_pc takes right after it (:254-279)
+// ---------------------------------------------------------------------------------------------------
+void orc::calc_pc_truncation_error(int nV, double zeta_t, double dt_n, double pc_eta_min, double pc_epsilon, const double* Hi_np1,
+                                   const double* Hi_star_np1, const int* mask_grounded_ice, const int* mask_gl_gr, const double* fraction_gr,
+                                   double* tau_np1, int* tau_n_guilty, double* eta_np1, int* n_tot, int* n_guilty) {
+  for (int vi = 0; vi < nV; ++vi)
+    tau_np1[vi] = zeta_t * std::fabs(Hi_np1[vi] - Hi_star_np1[vi]) / ((3.0 * zeta_t + 3.0) * dt_n);
+  double eta = pc_eta_min;
+  for (int vi = 0; vi < nV; ++vi)
+    if (mask_grounded_ice[vi] && !mask_gl_gr[vi] && fraction_gr[vi] == 1.0) eta = std::max(eta, tau_np1[vi]);
+  *eta_np1 = eta;
+  int tot = 0, guilty = 0;
+  for (int vi = 0; vi < nV; ++vi) {
+    if (fraction_gr[vi] < 1.0) continue;      // only fully grounded vertices
+    ++tot;
+    if (tau_np1[vi] > pc_epsilon) { ++guilty; if (tau_n_guilty) tau_n_guilty[vi] = tau_n_guilty[vi] + 1; }
+  }
+  *n_tot = tot; *n_guilty = guilty;
+}

@@ -300,6 +300,37 @@ __global__ void k_geo_dt_sia(GeoMesh m, int n, int off, int nb_ext, int nz, doub
   block_min_to(best, dtbits);
 }
 
+// ---- calc_pc_truncation_error + the guilty count of run_ice_dynamics_model_pc (predictor_corrector_scheme.f90:327-361, 254-279) ------------
+// counts[0] = n_tot, counts[1] = n_guilty; etabits = bits of the (positive) running maximum, initialised with C%pc_eta_min
+__global__ void k_pc_truncation_error(int n, int off, double zeta_t, double dt_n, double eps, const double* __restrict__ Hi_np1,
+                                      const double* __restrict__ Hi_star, const int* __restrict__ grounded, const int* __restrict__ gl_gr,
+                                      const double* __restrict__ fraction_gr, double* __restrict__ tau, int* __restrict__ guilty_rec,
+                                      unsigned long long* etabits, int* counts) {
+  double best = 0.0;
+  int ntot = 0, ngui = 0;
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const size_t i = off + r;
+    const double t = zeta_t * fabs(Hi_np1[i] - Hi_star[i]) / ((3.0 * zeta_t + 3.0) * dt_n);
+    tau[i] = t;
+    const bool full = fraction_gr[i] == 1.0;
+    if (grounded[i] && !gl_gr[i] && full) best = fmax(best, t);
+    if (full) {     // fraction_gr < 1: not considered (:262)
+      ++ntot;
+      if (t > eps) { ++ngui; if (guilty_rec) guilty_rec[i] = guilty_rec[i] + 1; }
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    best = fmax(best, __shfl_xor_sync(0xffffffffu, best, o));
+    ntot += __shfl_xor_sync(0xffffffffu, ntot, o);
+    ngui += __shfl_xor_sync(0xffffffffu, ngui, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (best > 0.0) atomicMax(etabits, (unsigned long long)__double_as_longlong(best));   // positive doubles: bit order = value order
+    if (ntot) atomicAdd(&counts[0], ntot);
+    if (ngui) atomicAdd(&counts[1], ngui);
+  }
+}
+
 // ---- alter_ice_thickness (ice_thickness_safeties.f90:26-288), after the two effective-thickness passes on Hi_new ------------------------------
 enum { MB_LAND = 1, MB_OCEAN = 2, MB_GROUNDED = 4, MB_FLOATING = 8, MB_GL_GR = 16, MB_GL_FL = 32, MB_CF_GR = 64, MB_CF_FL = 128 };
 struct AlterDev {
@@ -818,6 +849,57 @@ int ufe_b200_calc_critical_timestep_adv(ufe_b200_handle h, const ufe_b200_config
   }
   UFE_CUDA(cudaGetLastError());
   return finish_dt(c, G, cfg->dt_ice_max, dt_crit_adv);
+}
+
+int ufe_b200_calc_pc_truncation_error(ufe_b200_handle h, double zeta_t, double dt_n, double pc_eta_min, double pc_epsilon, const double* Hi_np1,
+                                      const double* Hi_star_np1, const int32_t* mask_grounded_ice, const int32_t* mask_gl_gr,
+                                      const double* fraction_gr, double* tau_np1, int32_t* tau_n_guilty, double* eta_np1, int32_t* n_tot,
+                                      int32_t* n_guilty) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && Hi_np1 && Hi_star_np1 && mask_grounded_ice && mask_gl_gr && fraction_gr && eta_np1 && n_tot && n_guilty,
+            "ufe_b200_calc_pc_truncation_error: NULL argument");
+  UFE_CHECK(dt_n > 0.0 && pc_eta_min > 0.0, "ufe_b200_calc_pc_truncation_error: dt_n and pc_eta_min must be positive");
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_TRY(ensure_geometry(c));
+  Mesh& M = *c->mesh; Geometry& G = *c->geo;
+  cudaStream_t st = c->stream;
+  const int na = M.a.n_loc();
+  auto up_i = [&](int* d, const int32_t* s) { return cudaMemcpyAsync(d + M.a.off(), s, sizeof(int) * na, cudaMemcpyHostToDevice, st); };
+  UFE_TRY(G.flag.alloc(2));
+  {
+    UFE_REGION(c, TC_H2D);
+    UFE_TRY(up_a(c, G.a[0].p, Hi_np1)); UFE_TRY(up_a(c, G.a[1].p, Hi_star_np1)); UFE_TRY(up_a(c, G.a[2].p, fraction_gr));
+    UFE_CUDA(up_i(G.ia[0].p, mask_grounded_ice)); UFE_CUDA(up_i(G.ia[1].p, mask_gl_gr));
+    if (tau_n_guilty) UFE_CUDA(up_i(G.ia[2].p, tau_n_guilty));
+    const unsigned long long init = (unsigned long long)__builtin_bit_cast(long long, pc_eta_min);
+    UFE_CUDA(cudaMemcpyAsync(G.dtbits.p, &init, sizeof(init), cudaMemcpyHostToDevice, st));
+    UFE_CUDA(cudaMemsetAsync(G.flag.p, 0, 2 * sizeof(int), st));
+  }
+  {
+    UFE_LAUNCH(c, TC_COLUMN);
+    k_pc_truncation_error<<<grid_for(c, na, 256), 256, 0, st>>>(na, M.a.off(), zeta_t, dt_n, pc_epsilon, G.a[0].p, G.a[1].p, G.ia[0].p, G.ia[1].p, G.a[2].p,
+                                                               G.a[5].p, tau_n_guilty ? G.ia[2].p : nullptr, G.dtbits.p, G.flag.p);
+  }
+  UFE_CUDA(cudaGetLastError());
+  unsigned long long bits = 0; int counts[2] = {0, 0};
+  {
+    UFE_REGION(c, TC_D2H);
+    UFE_TRY(down_a(c, tau_np1, G.a[5].p));
+    if (tau_n_guilty) UFE_CUDA(cudaMemcpyAsync(tau_n_guilty, G.ia[2].p + M.a.off(), sizeof(int) * na, cudaMemcpyDeviceToHost, st));
+    UFE_CUDA(cudaMemcpyAsync(&bits, G.dtbits.p, sizeof(bits), cudaMemcpyDeviceToHost, st));
+    UFE_CUDA(cudaMemcpyAsync(counts, G.flag.p, sizeof(counts), cudaMemcpyDeviceToHost, st));
+  }
+  UFE_CUDA(cudaStreamSynchronize(st));
+  double red[3] = {-__builtin_bit_cast(double, bits), (double)counts[0], (double)counts[1]};
+  if (c->nranks > 1) {   // MPI_ALLREDUCE MAX of eta (:353), SUM of the two counts (:276-277); the counts are exact in doubles
+    UFE_CUDA(cudaMemcpyAsync(G.a[7].p, red, sizeof(red), cudaMemcpyHostToDevice, st));
+    UFE_TRY(allreduce_min(c, G.a[7].p, 1));
+    UFE_TRY(allreduce_sum(c, G.a[7].p + 1, 2));
+    UFE_CUDA(cudaMemcpyAsync(red, G.a[7].p, sizeof(red), cudaMemcpyDeviceToHost, st));
+    UFE_CUDA(cudaStreamSynchronize(st));
+  }
+  *eta_np1 = -red[0]; *n_tot = (int32_t)red[1]; *n_guilty = (int32_t)red[2];
+  return 0;
 }
 
 int ufe_b200_calc_critical_timestep_SIA(ufe_b200_handle h, const ufe_b200_config* cfg, const double* Hi, const double* D_3D_b, double* dt_crit_SIA) {

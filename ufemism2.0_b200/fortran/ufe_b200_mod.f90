@@ -259,6 +259,19 @@ module ufe_b200_mod
       integer(c_int) :: ierr
     end function
 
+    ! calc_pc_truncation_error + the count of unstable vertices (time_stepping/predictor_corrector_scheme.f90:327-361, 254-279);
+    ! logical masks as integer(c_int32_t) 0/1 copies; tau_np1, tau_n_guilty may be c_null_ptr
+    function c_ufe_b200_calc_pc_truncation_error( h, zeta_t, dt_n, pc_eta_min, pc_epsilon, Hi_np1, Hi_star_np1, mask_grounded_ice, mask_gl_gr, &
+      fraction_gr, tau_np1, tau_n_guilty, eta_np1, n_tot, n_guilty) bind(C, name='ufe_b200_calc_pc_truncation_error') result( ierr)
+      import :: c_int, c_int32_t, c_double, c_ptr
+      type(c_ptr), value :: h
+      real(c_double), value :: zeta_t, dt_n, pc_eta_min, pc_epsilon
+      type(c_ptr), value :: Hi_np1, Hi_star_np1, mask_grounded_ice, mask_gl_gr, fraction_gr, tau_np1, tau_n_guilty
+      real(c_double), intent(out) :: eta_np1
+      integer(c_int32_t), intent(out) :: n_tot, n_guilty
+      integer(c_int) :: ierr
+    end function
+
     ! set_ice_velocities_to_{SIA,SSA,SIASSA,DIVA}_results (conservation_of_momentum_main.f90:311-511); out = c_loc of a ufe_b200_ice_velocities
     ! (c_loc's of ice%u_3D_b, v_3D_b, du_dx_3D, du_dy_3D, du_dz_3D, dv_dx_3D, dv_dy_3D, dv_dz_3D, dw_dx_3D, dw_dy_3D; c_null_ptr = skipped);
     ! approximation: 0 'SSA', 1 'DIVA', 2 'SIA', 3 'SIA/SSA'; hybrid_scheme: 0 'add', 1 'add_SIA_reduced'
