@@ -386,6 +386,15 @@ int ufe_b200_calc_grounded_fractions(ufe_b200_handle h, const ufe_b200_config* c
  * UFE_GF_BILIN_INTERP_TAF); choice < 0 switches the behaviour off again. */
 int ufe_b200_geometry_resident(ufe_b200_handle h, int choice, int nbins, const double* dHb, const double* bedrock_cdf, const double* bedrock_cdf_b);
 
+/* Replaces apply_grounded_fractions_to_bed_roughness( mesh, ice, bed_roughness, bed_roughness_applied) (basal_conditions/sliding_laws.f90:568-636),
+ * the preliminary A-grid scaling every sliding law applies to its bed-roughness field when C%do_subgrid_friction_on_A_grid is set: weight =
+ * fraction_gr ** max( 0, log10( max( 1, Hi)) - Hs_slope / 0.005) on grounding-line / grounded-calving-front vertices, 1 on other grounded ice, 0 on
+ * floating ice and open ocean.  Pass the result as the till_friction_angle / beta_sq / alpha_sq member of struct ufe_b200_ice_inputs; the sliding law decides
+ * which field it scales (:108, 151, 207, 263, 318, 372).  masks: mask_gl_gr, mask_cf_gr, mask_gl_fl, mask_grounded_ice, mask_floating_ice,
+ * mask_icefree_ocean are read.  All fields (vi1:vi2). */
+int ufe_b200_apply_grounded_fractions_to_bed_roughness(ufe_b200_handle h, const double* Hi, const double* Hs_slope, const double* fraction_gr,
+                                                       const ufe_b200_masks* masks, const double* bed_roughness, double* bed_roughness_applied);
+
 /* Replaces calc_pc_truncation_error( mesh, ice, pc) (time_stepping/predictor_corrector_scheme.f90:327-361; Robinson et al., 2020, Eq. 32) and the
  * error assessment that follows it in run_ice_dynamics_model_pc (:254-279): tau_np1 = zeta_t |Hi_np1 - Hi_star_np1| / ((3 zeta_t + 3) dt_n);
  * eta_np1 = max( C%pc_eta_min, tau_np1) over fully grounded vertices off the grounding line; n_tot = vertices with fraction_gr = 1, n_guilty =

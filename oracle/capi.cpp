@@ -304,3 +304,9 @@ extern "C" void orc_calc_pc_truncation_error(int nV, double zeta_t, double dt_n,
   calc_pc_truncation_error(nV, zeta_t, dt_n, pc_eta_min, pc_epsilon, Hi_np1, Hi_star_np1, mask_grounded_ice, mask_gl_gr, fraction_gr, tau_np1,
                            tau_n_guilty, eta_np1, n_tot, n_guilty);
 }
+
+extern "C" void orc_apply_grounded_fractions_to_bed_roughness(int nV, const double* Hi, const double* Hs_slope, const double* fraction_gr,
+                                                              const ufe_b200_masks* mk, const double* bed_roughness, double* applied) {
+  apply_grounded_fractions_to_bed_roughness(nV, Hi, Hs_slope, fraction_gr, mk->mask_gl_gr, mk->mask_cf_gr, mk->mask_gl_fl, mk->mask_grounded_ice,
+                                            mk->mask_floating_ice, mk->mask_icefree_ocean, bed_roughness, applied);
+}

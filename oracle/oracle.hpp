@@ -148,6 +148,11 @@ int calc_dHi_dt(const MeshView& mesh, const Config& C, ThicknessIO& io, double* 
 void calc_flux_divergence_matrix_upwind(const MeshView& mesh, const double* u_vav_b, const double* v_vav_b,
                                         const double* fraction_margin, Csr& M_divQ, std::vector<double>* u_perp = nullptr);
 
+// --- apply_grounded_fractions_to_bed_roughness (basal_conditions/sliding_laws.f90:568-636), do_subgrid_friction_on_A_grid = .true. ----------
+void apply_grounded_fractions_to_bed_roughness(int nV, const double* Hi, const double* Hs_slope, const double* fraction_gr, const int* mask_gl_gr,
+                                               const int* mask_cf_gr, const int* mask_gl_fl, const int* mask_grounded_ice, const int* mask_floating_ice,
+                                               const int* mask_icefree_ocean, const double* bed_roughness, double* bed_roughness_applied);
+
 // --- calc_pc_truncation_error + error assessment (time_stepping/predictor_corrector_scheme.f90:327-361, 254-279) ---------
 void calc_pc_truncation_error(int nV, double zeta_t, double dt_n, double pc_eta_min, double pc_epsilon, const double* Hi_np1, const double* Hi_star_np1,
                               const int* mask_grounded_ice, const int* mask_gl_gr, const double* fraction_gr, double* tau_np1, int* tau_n_guilty,

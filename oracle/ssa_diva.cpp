@@ -506,3 +506,26 @@ double Halfar_H(double A, double n, double H0, double R0, double x, double y, do
 }
 
 }  // namespace orc
+
+// ---------------------------------------------------------------------------------------------------
+// apply_grounded_fractions_to_bed_roughness (sliding_laws.f90:568-636) with C%do_subgrid_friction_on_A_grid = .true.
+// ---------------------------------------------------------------------------------------------------
+void orc::apply_grounded_fractions_to_bed_roughness(int nV, const double* Hi, const double* Hs_slope, const double* fraction_gr, const int* mask_gl_gr,
+                                                    const int* mask_cf_gr, const int* mask_gl_fl, const int* mask_grounded_ice,
+                                                    const int* mask_floating_ice, const int* mask_icefree_ocean, const double* bed_roughness,
+                                                    double* bed_roughness_applied) {
+  for (int vi = 0; vi < nV; ++vi) {
+    double weight_gr = 1.0;
+    const double exponent_hi = std::log10(std::max(1.0, Hi[vi]));
+    const double exponent_hs = Hs_slope[vi] / 0.005;
+    const double exponent_gr = std::max(0.0, exponent_hi - exponent_hs);
+    if (mask_gl_gr[vi]) weight_gr = std::pow(fraction_gr[vi], exponent_gr);
+    else if (mask_cf_gr[vi]) weight_gr = std::pow(fraction_gr[vi], exponent_gr);
+    else if (mask_gl_fl[vi]) weight_gr = std::pow(fraction_gr[vi], exponent_gr);
+    else if (mask_grounded_ice[vi]) weight_gr = 1.0;
+    else if (mask_floating_ice[vi]) weight_gr = 0.0;
+    else if (mask_icefree_ocean[vi]) weight_gr = 0.0;
+    weight_gr = std::min(1.0, std::max(0.0, weight_gr));
+    bed_roughness_applied[vi] = bed_roughness[vi] * weight_gr;
+  }
+}

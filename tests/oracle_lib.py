@@ -41,6 +41,7 @@ def lib():
         L.orc_Halfar_H.argtypes = [C.c_double] * 7
         L.orc_Schoof2006_icestream.argtypes = [C.c_double] * 7 + [dp, dp]
         L.orc_solve_SIA.argtypes = [C.c_void_p, C.POINTER(ub.Config), C.c_double] + [dp] * 8
+        L.orc_apply_grounded_fractions_to_bed_roughness.argtypes = [C.c_int, dp, dp, dp, C.POINTER(ub.Masks), dp, dp]
         L.orc_calc_pc_truncation_error.argtypes = [C.c_int] + [C.c_double] * 4 + [dp, dp, ip, ip, dp, dp, ip, C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.orc_set_ice_velocities.argtypes = [C.c_void_p, C.c_int, C.c_int] + [dp] * 10 + [C.POINTER(ub.IceVelocities)]
         L.orc_calc_secondary_velocities.argtypes = [C.c_void_p, dp, dp, C.POINTER(ub.SecondaryVelocities)]

@@ -300,6 +300,27 @@ __global__ void k_geo_dt_sia(GeoMesh m, int n, int off, int nb_ext, int nz, doub
   block_min_to(best, dtbits);
 }
 
+// mask bits packed by pack_mask_bits
+enum { MB_LAND = 1, MB_OCEAN = 2, MB_GROUNDED = 4, MB_FLOATING = 8, MB_GL_GR = 16, MB_GL_FL = 32, MB_CF_GR = 64, MB_CF_FL = 128 };
+
+// ---- apply_grounded_fractions_to_bed_roughness (sliding_laws.f90:592-631) -------------------------------------------------------------------
+__global__ void k_bed_roughness_weight(int n, int off, const int* __restrict__ bits, const double* __restrict__ Hi, const double* __restrict__ Hs_slope,
+                                       const double* __restrict__ fraction_gr, const double* __restrict__ rough, double* __restrict__ applied) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const size_t i = off + r;
+    const int mb = bits[i];
+    double w = 1.0;
+    const double exponent_hi = log10(fmax(1.0, Hi[i]));
+    const double exponent_hs = Hs_slope[i] / 0.005;
+    const double exponent_gr = fmax(0.0, exponent_hi - exponent_hs);
+    if (mb & (MB_GL_GR | MB_CF_GR | MB_GL_FL)) w = pow(fraction_gr[i], exponent_gr);
+    else if (mb & MB_GROUNDED) w = 1.0;
+    else if (mb & (MB_FLOATING | MB_OCEAN)) w = 0.0;
+    w = fmin(1.0, fmax(0.0, w));
+    applied[i] = rough[i] * w;
+  }
+}
+
 // ---- calc_pc_truncation_error + the guilty count of run_ice_dynamics_model_pc (predictor_corrector_scheme.f90:327-361, 254-279) ------------
 // counts[0] = n_tot, counts[1] = n_guilty; etabits = bits of the (positive) running maximum, initialised with C%pc_eta_min
 __global__ void k_pc_truncation_error(int n, int off, double zeta_t, double dt_n, double eps, const double* __restrict__ Hi_np1,
@@ -332,7 +353,6 @@ __global__ void k_pc_truncation_error(int n, int off, double zeta_t, double dt_n
 }
 
 // ---- alter_ice_thickness (ice_thickness_safeties.f90:26-288), after the two effective-thickness passes on Hi_new ------------------------------
-enum { MB_LAND = 1, MB_OCEAN = 2, MB_GROUNDED = 4, MB_FLOATING = 8, MB_GL_GR = 16, MB_GL_FL = 32, MB_CF_GR = 64, MB_CF_FL = 128 };
 struct AlterDev {
   ufe_b200_alter_params p;
   double rw_over_ri, fixiness, limitness;
@@ -849,6 +869,29 @@ int ufe_b200_calc_critical_timestep_adv(ufe_b200_handle h, const ufe_b200_config
   }
   UFE_CUDA(cudaGetLastError());
   return finish_dt(c, G, cfg->dt_ice_max, dt_crit_adv);
+}
+
+int ufe_b200_apply_grounded_fractions_to_bed_roughness(ufe_b200_handle h, const double* Hi, const double* Hs_slope, const double* fraction_gr,
+                                                       const ufe_b200_masks* masks, const double* bed_roughness, double* bed_roughness_applied) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c && Hi && Hs_slope && fraction_gr && masks && bed_roughness && bed_roughness_applied,
+            "ufe_b200_apply_grounded_fractions_to_bed_roughness: NULL argument");
+  UFE_CUDA(cudaSetDevice(c->device));
+  UFE_TRY(ensure_geometry(c));
+  Mesh& M = *c->mesh; Geometry& G = *c->geo;
+  {
+    UFE_REGION(c, TC_H2D);
+    UFE_TRY(up_a(c, G.a[0].p, Hi)); UFE_TRY(up_a(c, G.a[1].p, Hs_slope)); UFE_TRY(up_a(c, G.a[2].p, fraction_gr)); UFE_TRY(up_a(c, G.a[3].p, bed_roughness));
+    UFE_TRY(pack_mask_bits(c, G, masks, MB_OCEAN | MB_GROUNDED | MB_FLOATING | MB_GL_GR | MB_GL_FL | MB_CF_GR));
+  }
+  {
+    UFE_LAUNCH(c, TC_COLUMN);
+    k_bed_roughness_weight<<<grid_for(c, M.a.n_loc(), 256), 256, 0, c->stream>>>(M.a.n_loc(), M.a.off(), G.ia[2].p, G.a[0].p, G.a[1].p, G.a[2].p, G.a[3].p, G.a[5].p);
+  }
+  UFE_CUDA(cudaGetLastError());
+  { UFE_REGION(c, TC_D2H); UFE_TRY(down_a(c, bed_roughness_applied, G.a[5].p)); }
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
 }
 
 int ufe_b200_calc_pc_truncation_error(ufe_b200_handle h, double zeta_t, double dt_n, double pc_eta_min, double pc_epsilon, const double* Hi_np1,

@@ -259,6 +259,14 @@ module ufe_b200_mod
       integer(c_int) :: ierr
     end function
 
+    ! apply_grounded_fractions_to_bed_roughness (basal_conditions/sliding_laws.f90:568-636); masks = c_loc of a ufe_b200_masks
+    function c_ufe_b200_apply_grounded_fractions_to_bed_roughness( h, Hi, Hs_slope, fraction_gr, masks, bed_roughness, bed_roughness_applied) &
+      bind(C, name='ufe_b200_apply_grounded_fractions_to_bed_roughness') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h, Hi, Hs_slope, fraction_gr, masks, bed_roughness, bed_roughness_applied
+      integer(c_int) :: ierr
+    end function
+
     ! calc_pc_truncation_error + the count of unstable vertices (time_stepping/predictor_corrector_scheme.f90:327-361, 254-279);
     ! logical masks as integer(c_int32_t) 0/1 copies; tau_np1, tau_n_guilty may be c_null_ptr
     function c_ufe_b200_calc_pc_truncation_error( h, zeta_t, dt_n, pc_eta_min, pc_epsilon, Hi_np1, Hi_star_np1, mask_grounded_ice, mask_gl_gr, &
