@@ -47,3 +47,63 @@ def test_oracle_diva_follows_the_reference_checksum_log():
         assert rc == 0 and nv == 1
         seq.append((f["u_vav_b"].min(), f["u_vav_b"].max()))
     check_extremes(seq, rows)
+
+
+# ---- ISMIP-HOM experiment A, L = 160 km, DIVA without sliding, periodic borders (integrated_test_ISMIP_HOM_small) -----------------------------------
+# reference name -> member of the velocity state; compared on the mean of |.| (2 %) and, where listed, on the maximum (2 %)
+HOM_FIELDS = {"DIVA%du_dz_3D_a": "du_dz_3D_a", "DIVA%eta_3D_a": "eta_3D_a", "DIVA%eta_3D_b": "eta_3D_b", "DIVA%eta_vav_a": "eta_vav_a", "DIVA%N_a": "N_a",
+              "DIVA%N_b": "N_b", "DIVA%F1_3D_b": "F1_3D_b", "DIVA%F2_3D_b": "F2_3D_b", "DIVA%beta_eff_a": "beta_eff_a", "DIVA%beta_eff_b": "beta_eff_b",
+              "DIVA%tau_bx_b": "tau_bx_b", "DIVA%u_3D_b": "u_3D_b", "DIVA%v_3D_b": "v_3D_b", "DIVA%u_vav_b": "u_vav_b", "DIVA%v_vav_b": "v_vav_b",
+              "du_dx_a": "du_dx_a", "du_dy_a": "du_dy_a"}
+HOM_MAXIMA = ["DIVA%du_dz_3D_a", "DIVA%F1_3D_b", "DIVA%F2_3D_b", "DIVA%beta_eff_a", "DIVA%beta_eff_b", "DIVA%tau_bx_b", "DIVA%u_3D_b", "DIVA%u_vav_b"]
+
+
+def ismip_hom_reference():
+    return json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden.json")))["ismip_hom_A_160_DIVA"]
+
+
+def check_ismip_hom_sequence(seq, nTri, g):
+    """seq[k] = (sum, min, max) of u_b after relaxed viscosity iteration k + 1: all 48 iterations of the reference's solve"""
+    rows = np.array(g["u_b_relaxed"])
+    assert len(seq) == len(rows) == 48
+    for k, (s, mn, mx) in enumerate(seq):
+        assert abs(s / nTri - rows[k, 0] / g["nTri"]) <= 0.02 * rows[k, 0] / g["nTri"], (k + 1, s / nTri, rows[k, 0] / g["nTri"])
+        assert abs(mx - rows[k, 3]) <= 0.01 * rows[k, 3], (k + 1, mx, rows[k, 3])
+        if k >= 4:
+            assert abs(mn - rows[k, 2]) <= 0.04 * rows[k, 2], (k + 1, mn, rows[k, 2])
+
+
+def check_ismip_hom_fields(f, m, g):
+    for ref_name, name in HOM_FIELDS.items():
+        a, r = f[name], g["last"][ref_name]
+        n_ref = (g["nV"] if name.endswith("_a") else g["nTri"]) * (m.nz if a.ndim == 2 else 1)
+        mean, mean_ref = np.abs(a).sum() / a.size, r[1] / n_ref
+        assert abs(mean - mean_ref) <= 0.02 * mean_ref, (name, mean, mean_ref)
+        if ref_name in HOM_MAXIMA:
+            assert abs(a.max() - r[3]) <= 0.02 * r[3], (name, a.max(), r[3])
+    assert not f["u_base_b"].any() and not f["basal_friction_coefficient_b"].any()      # no sliding: the log holds zeros too
+    assert g["last"]["DIVA%u_base_b"] == [0.0] * 4 and g["last"]["DIVA%basal_friction_coefficient_b"] == [0.0] * 4
+
+
+def test_oracle_ismip_hom_a_follows_the_reference_checksum_log():
+    """All 48 viscosity iterations of the reference's ISMIP-HOM A solve, then every named DIVA field of its last iteration: means within 2 % on a mesh of
+    our generator with the reference's triangle count.  The surface velocity maximum (the experiment's headline number) is 106.7 against 106.9 m/yr."""
+    g = ismip_hom_reference()
+    w = wl.ismip_hom_a()
+    m = w.mesh
+    assert abs(m.nTri - g["nTri"]) <= 0.02 * g["nTri"] and abs(m.nV - g["nV"]) <= 0.02 * g["nV"]
+    o = ol.OracleMesh(m)
+    st, f = ub.alloc_velocity_state(m.nV, m.nTri, m.nz)
+    cfg = w.cfg
+    cfg.visc_it_nit = 0
+    seq = []
+    for k in range(48):
+        rc, nv, na = o.solve_velocity(cfg, 1, w.ice_inputs(), st)
+        assert rc == 0 and nv == 1
+        seq.append((f["u_vav_b"].sum(), f["u_vav_b"].min(), f["u_vav_b"].max()))
+    check_ismip_hom_sequence(seq, m.nTri, g)
+    check_ismip_hom_fields(f, m, g)
+    # the reference stopped here because the iteration had converged (visc_it_norm_dUV_tol = 5e-7); so has this one
+    du = f["u_vav_b"] - f["u_b_prev"]; dv = f["v_vav_b"] - f["v_b_prev"]
+    su = f["u_vav_b"] + f["u_b_prev"]; sv = f["v_vav_b"] + f["v_b_prev"]
+    assert 2.0 * (du @ du + dv @ dv) / (su @ su + sv @ sv) < 2e-6

@@ -162,3 +162,25 @@ def ssa_icestream(h, nz=12, seed=20261104, jitter=0.2):
                                   (ub.BC_ZERO, ub.BC_ZERO), (ub.BC_INFINITE_SSA_ICESTREAM, ub.BC_ZERO)]):   # north, east, south, west
         cfg.BC_u[k] = bu; cfg.BC_v[k] = bv
     return Workload(mesh, cfg, f, approximation=0, name="SSA_icestream")
+
+
+def ismip_hom_a(L=160e3, h=6737.0, approximation=1, nz=12, seed=20261104, jitter=0.2):
+    """ISMIP-HOM experiment A as the reference's integrated test runs it (automated_testing/UFEMISM/integrated_test_ISMIP_HOM_small/
+    all_ISMIP_HOM_config_files/config_ISMIP_HOM_A_*_DIVA.cfg): a 1000 m slab on a 0.5 degree slope over a doubly sinusoidal bed
+    (idealised_geometries.f90:243-267), domain +-L, no sliding, all four borders 'periodic_ISMIP-HOM' for u and v."""
+    mesh = uh.HostMesh.synthetic(-L, L, -L, L, h, jitter=jitter, seed=seed, nz=nz)
+    x, y = mesh.V[:, 0], mesh.V[:, 1]
+    Hs = 2000.0 - x * np.tan(0.5 * np.pi / 180.0)
+    Hb = Hs - 1000.0 + 500.0 * np.sin(x * 2.0 * np.pi / L) * np.sin(y * 2.0 * np.pi / L)
+    Hi = Hs - Hb
+    f = _common_fields(mesh, Hi, Hb, np.full(mesh.nV, -10000.0), A_uniform=1e-16)
+    f["SMB"] = np.zeros(mesh.nV)
+    cfg = ub.default_config()
+    cfg.visc_it_norm_dUV_tol = 5e-7; cfg.visc_it_nit = 5000; cfg.visc_it_relax = 0.4; cfg.visc_eff_min = 1e4; cfg.vel_max = 5000.0
+    cfg.stress_balance_PETSc_rtol = 1e-6; cfg.stress_balance_PETSc_abstol = 1e-4
+    cfg.Glens_flow_law_exponent = 3.0; cfg.Glens_flow_law_epsilon_sq_0 = 1e-12; cfg.uniform_Glens_flow_factor = 1e-16
+    cfg.choice_sliding_law = ub.SLID_NO_SLIDING
+    cfg.refgeo_idealised_ISMIP_HOM_L = L
+    for k in range(4):
+        cfg.BC_u[k] = ub.BC_PERIODIC_ISMIP_HOM; cfg.BC_v[k] = ub.BC_PERIODIC_ISMIP_HOM
+    return Workload(mesh, cfg, f, approximation=approximation, name="ISMIP-HOM A")
