@@ -108,6 +108,42 @@ def _worker(rank, world, port, q):
         full = np.zeros((nc.value, 2))
         np.add.at(full, agg, res)
         np.testing.assert_allclose(t.numpy(), full, rtol=1e-13, atol=1e-13)
+        # copy boundary conditions ('infinite_SSA_icestream' / 'periodic_ISMIP-HOM'): a copy row reads the previous solution around a point that
+        # usually lies in another rank's block, so every rank writes its own slice into a zero global vector and one all-reduce completes it
+        # (velocity.cu: copy_bc_rhs); the load vector of the owned copy rows then equals the single-process assembly
+        t1, t2 = uh.partition_list(m.nTri, rank, world)
+        up = 100.0 * rng.standard_normal(m.nTri); vp = 100.0 * rng.standard_normal(m.nTri)
+        glob = np.zeros(2 * m.nTri)
+        glob[t1 - 1:t2] = up[t1 - 1:t2]; glob[m.nTri + t1 - 1:m.nTri + t2] = vp[t1 - 1:t2]
+        tg = torch.from_numpy(glob)
+        dist.all_reduce(tg, op=dist.ReduceOp.SUM)
+        assert np.array_equal(tg.numpy(), np.concatenate([up, vp]))
+        cfg = wl.scaling_config(); cfg.visc_it_relax = 0.3; cfg.refgeo_idealised_ISMIP_HOM_L = 1.0e6
+        for k, (bu, bv) in enumerate([(2, 2), (3, 2), (0, 0), (3, 1)]):
+            cfg.BC_u[k] = bu; cfg.BC_v[k] = bv
+        coef = [1e10 * (1 + 0.1 * rng.random(m.nTri))] + [rng.standard_normal(m.nTri) for _ in range(5)]
+        bb = o.assemble(cfg, *coef, u_b_prev=up, v_b_prev=vp)[3]
+        side = {1: 0, 2: 0, 3: 1, 4: 1, 5: 2, 6: 2, 7: 3, 8: 3}
+        n_copy = n_remote = 0
+        for ti in range(t1, t2 + 1):
+            if m.TriBI[ti - 1] == 0:
+                continue
+            for uv in range(2):
+                choice = (cfg.BC_u if uv == 0 else cfg.BC_v)[side[int(m.TriBI[ti - 1])]]
+                if choice < 2:
+                    continue
+                tj, wt = o.find_ti_copy(choice, 1.0e6, ti)
+                src = tg.numpy()[uv * m.nTri:(uv + 1) * m.nTri]
+                fixed = 0.0
+                for n_ in range(len(tj)):
+                    if tj[n_]:
+                        fixed = fixed + wt[n_] * src[tj[n_] - 1]
+                val_ = 0.3 * fixed + 0.7 * src[ti - 1]
+                assert abs(val_ - bb[2 * (ti - 1) + uv]) <= 1e-12 * max(1.0, abs(val_))
+                n_copy += 1
+                n_remote += int(((tj[tj > 0] < t1) | (tj[tj > 0] > t2)).any())
+        assert n_copy > 20 and n_remote > 0
+        checked += 1
         dist.barrier()
         dist.destroy_process_group()
         q.put((rank, "ok", checked))
@@ -129,7 +165,7 @@ def test_two_ranks_over_gloo():
         p.join(timeout=60)
     for rank, status, info in results:
         assert status == "ok", f"rank {rank}: {info}"
-        assert info == 4
+        assert info == 5
 
 
 @pytest.mark.parametrize("nranks", [2, 4, 8])
