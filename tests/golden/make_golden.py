@@ -64,11 +64,13 @@ if os.path.exists(ref):
             S["u_b_limited"].append(_nums(l))
     json.dump(S, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "ssa_icestream_small.json"), "w"))   # compact: 520 x 3 rows
 
-# Output of the reference itself: ISMIP-HOM experiment A, L = 160 km, DIVA, no sliding, 'periodic_ISMIP-HOM' borders (integrated_test_ISMIP_HOM_small):
-# u_b after each of the 48 relaxed viscosity iterations, and the statistics of every named DIVA field the last iteration logged.
-ref = "/root/reference/automated_testing/UFEMISM/integrated_test_ISMIP_HOM_small/reference/checksum_logfile_A_160_DIVA.txt"
-if os.path.exists(ref):
-    S = {"source": "automated_testing/UFEMISM/integrated_test_ISMIP_HOM_small/reference/checksum_logfile_A_160_DIVA.txt",
+# Output of the reference itself: ISMIP-HOM experiment A, L = 160 / 80 / 40 km, DIVA, no sliding, 'periodic_ISMIP-HOM' borders (integrated_test_ISMIP_HOM_small):
+# u_b after each of the 48-50 relaxed viscosity iterations, and the statistics of every named DIVA field the last iteration logged.
+for _L in (160, 80, 40):
+    ref = "/root/reference/automated_testing/UFEMISM/integrated_test_ISMIP_HOM_small/reference/checksum_logfile_A_%d_DIVA.txt" % _L
+    if not os.path.exists(ref):
+        continue
+    S = {"source": "automated_testing/UFEMISM/integrated_test_ISMIP_HOM_small/reference/checksum_logfile_A_%d_DIVA.txt" % _L,
          "columns": ["sum", "sum_abs", "min", "max"], "u_b_relaxed": [], "last": {}}
     for l in open(ref):
         if l.startswith(" mask_grounded_ice:") and "nV" not in S:
@@ -81,7 +83,7 @@ if os.path.exists(ref):
                 S["u_b_relaxed"].append(_nums(l))
             if not (name in ("u_b", "v_b") and "apply_velocity_limits]" in l):
                 S["last"][name] = _nums(l)          # later lines overwrite earlier ones: the last viscosity iteration stays
-    G["ismip_hom_A_160_DIVA"] = S
+    G["ismip_hom_A_%d_DIVA" % _L] = S
 
 json.dump(G, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden.json"), "w"), indent=1)
 print("wrote golden.json")

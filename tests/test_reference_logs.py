@@ -5,6 +5,7 @@ import json
 import os
 
 import numpy as np
+import pytest
 
 import oracle_lib as ol
 import ufe_b200 as ub
@@ -58,14 +59,14 @@ HOM_FIELDS = {"DIVA%du_dz_3D_a": "du_dz_3D_a", "DIVA%eta_3D_a": "eta_3D_a", "DIV
 HOM_MAXIMA = ["DIVA%du_dz_3D_a", "DIVA%F1_3D_b", "DIVA%F2_3D_b", "DIVA%beta_eff_a", "DIVA%beta_eff_b", "DIVA%tau_bx_b", "DIVA%u_3D_b", "DIVA%u_vav_b"]
 
 
-def ismip_hom_reference():
-    return json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden.json")))["ismip_hom_A_160_DIVA"]
+def ismip_hom_reference(L_km=160):
+    return json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden.json")))["ismip_hom_A_%d_DIVA" % L_km]
 
 
 def check_ismip_hom_sequence(seq, nTri, g):
     """seq[k] = (sum, min, max) of u_b after relaxed viscosity iteration k + 1: all 48 iterations of the reference's solve"""
     rows = np.array(g["u_b_relaxed"])
-    assert len(seq) == len(rows) == 48
+    assert len(seq) == len(rows) >= 48
     for k, (s, mn, mx) in enumerate(seq):
         assert abs(s / nTri - rows[k, 0] / g["nTri"]) <= 0.02 * rows[k, 0] / g["nTri"], (k + 1, s / nTri, rows[k, 0] / g["nTri"])
         assert abs(mx - rows[k, 3]) <= 0.01 * rows[k, 3], (k + 1, mx, rows[k, 3])
@@ -85,11 +86,12 @@ def check_ismip_hom_fields(f, m, g):
     assert g["last"]["DIVA%u_base_b"] == [0.0] * 4 and g["last"]["DIVA%basal_friction_coefficient_b"] == [0.0] * 4
 
 
-def test_oracle_ismip_hom_a_follows_the_reference_checksum_log():
-    """All 48 viscosity iterations of the reference's ISMIP-HOM A solve, then every named DIVA field of its last iteration: means within 2 % on a mesh of
+@pytest.mark.parametrize("L_km", [160, 80, 40])
+def test_oracle_ismip_hom_a_follows_the_reference_checksum_log(L_km):
+    """All 48-50 viscosity iterations of the reference's ISMIP-HOM A solve, then every named DIVA field of its last iteration: means within 2 % on a mesh of
     our generator with the reference's triangle count.  The surface velocity maximum (the experiment's headline number) is 106.7 against 106.9 m/yr."""
-    g = ismip_hom_reference()
-    w = wl.ismip_hom_a()
+    g = ismip_hom_reference(L_km)
+    w = wl.ismip_hom_a(L=L_km * 1e3, h=6737.0 * L_km / 160.0)       # the reference scales its mesh with L (resolution L / 20)
     m = w.mesh
     assert abs(m.nTri - g["nTri"]) <= 0.02 * g["nTri"] and abs(m.nV - g["nV"]) <= 0.02 * g["nV"]
     o = ol.OracleMesh(m)
@@ -97,7 +99,7 @@ def test_oracle_ismip_hom_a_follows_the_reference_checksum_log():
     cfg = w.cfg
     cfg.visc_it_nit = 0
     seq = []
-    for k in range(48):
+    for k in range(len(g["u_b_relaxed"])):
         rc, nv, na = o.solve_velocity(cfg, 1, w.ice_inputs(), st)
         assert rc == 0 and nv == 1
         seq.append((f["u_vav_b"].sum(), f["u_vav_b"].min(), f["u_vav_b"].max()))
