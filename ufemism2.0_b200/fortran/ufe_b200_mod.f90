@@ -19,6 +19,7 @@ module ufe_b200_mod
   use model_configuration, only: C
   use CSR_sparse_matrix_type, only: type_sparse_matrix_CSR_dp
   use mesh_types, only: type_mesh
+  use ice_model_types, only: type_ice_model, type_ice_pc
 
   implicit none
 
@@ -28,6 +29,7 @@ module ufe_b200_mod
   public :: solve_matrix_equation_CSR_B200
   public :: ufe_b200_upload_mesh, ufe_b200_destroy_mesh
   public :: ufe_b200_fill_config, ufe_b200_config
+  public :: set_ice_velocities_B200, calc_pc_truncation_error_B200
 
   type(c_ptr), save :: handle = c_null_ptr
 
@@ -395,6 +397,62 @@ contains
     ! Called from the mesh finaliser and before update_mesh -> remap_velocity_solver (UFEMISM_main_model.f90:1211)
     if (c_associated( handle)) call check( c_ufe_b200_mesh_destroy( handle), 'ufe_b200_destroy_mesh')
   end subroutine ufe_b200_destroy_mesh
+
+  subroutine set_ice_velocities_B200( mesh, ice)
+    ! Drop-in for the set_ice_velocities_to_{SIA,SSA,SIASSA,DIVA}_results call that follows the solve in solve_stress_balance
+    ! (src/UFEMISM/ice_dynamics/conservation_of_momentum/conservation_of_momentum_main.f90:113-152): the solver results are on the device,
+    ! the applied velocities and strain rates land in the ice model's own arrays.
+    type(type_mesh),              intent(in   ) :: mesh
+    type(type_ice_model), target, intent(inout) :: ice
+    character(len=1024), parameter :: routine_name = 'set_ice_velocities_B200'
+    type(c_ptr), target :: out(10)
+    integer(c_int) :: approximation, scheme
+    call init_routine( routine_name)
+    select case (C%choice_stress_balance_approximation)
+    case ('SSA');     approximation = 0
+    case ('DIVA');    approximation = 1
+    case ('SIA');     approximation = 2
+    case ('SIA/SSA'); approximation = 3
+    case default
+      call crash('unknown choice_stress_balance_approximation "' // trim( C%choice_stress_balance_approximation) // '"!')
+    end select
+    scheme = 0
+    if (approximation == 3) then
+      select case (C%choice_hybrid_SIASSA_scheme)
+      case ('add');             scheme = 0
+      case ('add_SIA_reduced'); scheme = 1
+      case default
+        call crash('unknown choice_hybrid_SIASSA_scheme_config "' // trim( C%choice_hybrid_SIASSA_scheme) // '"!')
+      end select
+    end if
+    ! member order of ufe_b200_ice_velocities (include/ufe_b200.h)
+    out = [c_loc( ice%u_3D_b), c_loc( ice%v_3D_b), c_loc( ice%du_dx_3D), c_loc( ice%du_dy_3D), c_loc( ice%du_dz_3D), &
+           c_loc( ice%dv_dx_3D), c_loc( ice%dv_dy_3D), c_loc( ice%dv_dz_3D), c_loc( ice%dw_dx_3D), c_loc( ice%dw_dy_3D)]
+    call check( c_ufe_b200_set_ice_velocities( handle, approximation, scheme, c_loc( out)), routine_name)
+    call finalise_routine( routine_name)
+  end subroutine set_ice_velocities_B200
+
+  subroutine calc_pc_truncation_error_B200( mesh, ice, pc, n_tot, n_guilty)
+    ! Drop-in for calc_pc_truncation_error( mesh, ice, pc) plus the loop that counts the unstable vertices in run_ice_dynamics_model_pc
+    ! (src/UFEMISM/ice_dynamics/time_stepping/predictor_corrector_scheme.f90:327-361, 254-279); n_tot, n_guilty are already summed over the ranks.
+    type(type_mesh),              intent(in   ) :: mesh
+    type(type_ice_model), target, intent(in   ) :: ice
+    type(type_ice_pc),    target, intent(inout) :: pc
+    integer,                      intent(  out) :: n_tot, n_guilty
+    character(len=1024), parameter :: routine_name = 'calc_pc_truncation_error_B200'
+    integer(c_int32_t), dimension(mesh%vi1:mesh%vi2), target :: mask_grounded_ice, mask_gl_gr
+    integer(c_int32_t) :: nt, ng
+    real(c_double) :: eta
+    call init_routine( routine_name)
+    mask_grounded_ice = merge( 1_c_int32_t, 0_c_int32_t, ice%mask_grounded_ice( mesh%vi1:mesh%vi2))
+    mask_gl_gr        = merge( 1_c_int32_t, 0_c_int32_t, ice%mask_gl_gr(        mesh%vi1:mesh%vi2))
+    call check( c_ufe_b200_calc_pc_truncation_error( handle, pc%zeta_t, pc%dt_n, C%pc_eta_min, C%pc_epsilon, c_loc( pc%Hi_np1), &
+      c_loc( pc%Hi_star_np1), c_loc( mask_grounded_ice), c_loc( mask_gl_gr), c_loc( ice%fraction_gr), c_loc( pc%tau_np1), &
+      c_loc( pc%tau_n_guilty), eta, nt, ng), routine_name)
+    pc%eta_np1 = eta
+    n_tot = int( nt); n_guilty = int( ng)
+    call finalise_routine( routine_name)
+  end subroutine calc_pc_truncation_error_B200
 
   subroutine ufe_b200_fill_config( cfg)
     ! Copy the C% scalars the path reads into the plain struct that crosses the ABI
