@@ -36,6 +36,12 @@ if os.path.exists(ref):
     # output of the reference itself: (sum, sum|.|, min, max) of u_b after each of the first 20 relaxed DIVA viscosity iterations of the first solve
     rows = [l for l in txt if l.startswith(" u_b:") and "/solve_DIVA_infinite_slab/relax_viscosity_iterations]" in l][:20]
     G["mismip_mod_small"]["u_b_relaxed"] = [[float(x.replace("-.", "-0.")) for x in re.findall(r"=\s*(-?[0-9]*\.[0-9]+E[+-][0-9]+)", l)] for l in rows]
+    # the first solve as a whole: number of viscosity iterations until convergence, the converged DIVA%u_vav_b and the driving stress
+    first = next(i for i, l in enumerate(txt) if l.startswith(" DIVA%u_vav_b:"))
+    num = lambda l: [float(x.replace("-.", "-0.")) for x in re.findall(r"=\s*(-?[0-9]*\.[0-9]+E[+-][0-9]+)", l)]
+    G["mismip_mod_small"]["n_visc_its_first_solve"] = sum(1 for l in txt[:first] if l.startswith(" u_b:") and "relax_viscosity_iterations]" in l)
+    G["mismip_mod_small"]["u_vav_b_converged"] = num(txt[first])
+    G["mismip_mod_small"]["tau_dx_b"] = num(next(l for l in txt if l.startswith(" tau_dx_b:")))
 
 # Output of the reference itself: the checksum log of integrated_test_SSA_icestream_small (16 km, SSA, BC 'infinite_SSA_icestream').  Its first
 # stress-balance solve logs (sum, sum|.|, min, max) of u_b / v_b after every relaxed viscosity iteration: 520 iterations, all kept.

@@ -71,3 +71,25 @@ def test_gpu_ismip_hom_a_follows_the_reference_checksum_log():
         check_ismip_hom_fields(f, m, g)
     finally:
         ctx.close()
+
+
+def test_gpu_diva_converges_like_the_reference():
+    """The whole first solve of integrated_test_MISMIP_mod_small on the device: the reference's 26 viscosity iterations and its converged maximum."""
+    import json
+    import os
+    g = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden.json")))["mismip_mod_small"]
+    w = mismip_mod_small_workload()
+    m = w.mesh
+    ctx = ub.Context(device=0)
+    try:
+        ctx.mesh_create(m)
+        ctx.calc_matrix_operators()
+        st, f = ub.alloc_velocity_state(m.nV, m.nTri, m.nz)
+        ice = w.ice_inputs()
+        nv, na = C.c_int(), C.c_int()
+        ub.check(ub.lib().ufe_b200_solve_DIVA(ctx.h, C.byref(w.cfg), C.byref(ice), C.byref(st), C.byref(nv), C.byref(na), None, None, None))
+    finally:
+        ctx.close()
+    assert abs(nv.value - g["n_visc_its_first_solve"]) <= 1, nv.value
+    assert abs(f["u_vav_b"].max() - g["u_vav_b_converged"][3]) <= 0.02 * g["u_vav_b_converged"][3]
+    assert abs(f["tau_dx_b"].max() - g["tau_dx_b"][3]) <= 0.03 * g["tau_dx_b"][3]

@@ -50,6 +50,21 @@ def test_oracle_diva_follows_the_reference_checksum_log():
     check_extremes(seq, rows)
 
 
+def test_oracle_diva_converges_like_the_reference():
+    """The whole first solve of integrated_test_MISMIP_mod_small: the reference needed 26 viscosity iterations (visc_it_norm_dUV_tol = 5e-5) and ended at
+    max( DIVA%u_vav_b) = 718.98 m/yr; its driving stress peaks at 488.7 Pa."""
+    g = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden.json")))["mismip_mod_small"]
+    assert g["n_visc_its_first_solve"] == 26 and abs(g["u_vav_b_converged"][3] - 718.979) < 1e-3
+    w = mismip_mod_small_workload()
+    m = w.mesh
+    o = ol.OracleMesh(m)
+    st, f = ub.alloc_velocity_state(m.nV, m.nTri, m.nz)
+    rc, n_visc, n_axb = o.solve_velocity(w.cfg, 1, w.ice_inputs(), st)
+    assert rc == 0 and abs(n_visc - g["n_visc_its_first_solve"]) <= 1, n_visc
+    assert abs(f["u_vav_b"].max() - g["u_vav_b_converged"][3]) <= 0.02 * g["u_vav_b_converged"][3]
+    assert abs(f["tau_dx_b"].max() - g["tau_dx_b"][3]) <= 0.03 * g["tau_dx_b"][3] and abs(f["tau_dx_b"].min() - g["tau_dx_b"][2]) <= 0.03 * abs(g["tau_dx_b"][2])
+
+
 # ---- ISMIP-HOM experiment A, L = 160 km, DIVA without sliding, periodic borders (integrated_test_ISMIP_HOM_small) -----------------------------------
 # reference name -> member of the velocity state; compared on the mean of |.| (2 %) and, where listed, on the maximum (2 %)
 HOM_FIELDS = {"DIVA%du_dz_3D_a": "du_dz_3D_a", "DIVA%eta_3D_a": "eta_3D_a", "DIVA%eta_3D_b": "eta_3D_b", "DIVA%eta_vav_a": "eta_vav_a", "DIVA%N_a": "N_a",
