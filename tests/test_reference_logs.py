@@ -19,6 +19,7 @@ def mismip_mod_small_workload():
     # calc_pore_water_pressure_Martin2011 + effective pressure (basal_hydrology_main.f90:227-266; Hb_min = 0, Hb_max = 1000 in the test's config)
     lam = np.clip(1.0 - (f["Hb"] - f["SL"] - 0.0) / (1000.0 - 0.0), 0.0, 1.0)
     f["effective_pressure"] = np.maximum(0.0, wl.ICE_DENSITY * wl.GRAV * f["Hi"] * (1.0 - 0.96 * lam))
+    w.cfg.Hi_min = 0.0                          # the small test's config.cfg (the 8 km scaling file has 0.1)
     return w
 
 

@@ -39,7 +39,7 @@ def scaling_config(cfg=None):
     c.choice_ice_integration_method = ub.INTEGRATION_SEMI_IMPLICIT; c.dHi_semiimplicit_fs = 1.5
     c.dHi_PETSc_rtol = 1e-8; c.dHi_PETSc_abstol = 1e-4
     c.dt_ice_min = 0.2; c.dt_ice_max = 10.0
-    c.uniform_Glens_flow_factor = 1e-16
+    c.uniform_Glens_flow_factor = 1e-16; c.Hi_min = 0.1
     for k in range(4):
         c.BC_u[k] = ub.BC_INFINITE; c.BC_v[k] = ub.BC_INFINITE; c.BC_H[k] = ub.BC_ZERO
     return c
