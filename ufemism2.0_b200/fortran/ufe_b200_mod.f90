@@ -156,6 +156,175 @@ module ufe_b200_mod
       integer(c_int) :: ierr
     end function
 
+    ! solve_DIVA_infinite_slab / solve_SSA on the model's arrays (DIVA_solver_infinite_slab.f90:52, SSA_main.f90:88); ice, state = c_loc of
+    ! ufe_b200_ice_inputs / ufe_b200_velocity_state filled with c_loc of the model arrays; BC_prescr_* = c_null_ptr when absent
+    function c_ufe_b200_solve_DIVA( h, cfg, ice, state, n_visc_its, n_Axb_its, BC_prescr_mask_b, BC_prescr_u_b, BC_prescr_v_b) &
+      bind(C, name='ufe_b200_solve_DIVA') result( ierr)
+      import :: c_int, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      type(c_ptr), value :: ice, state
+      integer(c_int), intent(out) :: n_visc_its, n_Axb_its
+      type(c_ptr), value :: BC_prescr_mask_b, BC_prescr_u_b, BC_prescr_v_b
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_solve_SSA( h, cfg, ice, state, n_visc_its, n_Axb_its, BC_prescr_mask_b, BC_prescr_u_b, BC_prescr_v_b) &
+      bind(C, name='ufe_b200_solve_SSA') result( ierr)
+      import :: c_int, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      type(c_ptr), value :: ice, state
+      integer(c_int), intent(out) :: n_visc_its, n_Axb_its
+      type(c_ptr), value :: BC_prescr_mask_b, BC_prescr_u_b, BC_prescr_v_b
+      integer(c_int) :: ierr
+    end function
+
+    ! the same solve on device-resident fields: upload once, solve, download what the host needs
+    function c_ufe_b200_velocity_upload( h, ice, state) bind(C, name='ufe_b200_velocity_upload') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h, ice, state
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_velocity_solve_resident( h, cfg, approximation, n_visc_its, n_Axb_its) bind(C, name='ufe_b200_velocity_solve_resident') result( ierr)
+      import :: c_int, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      integer(c_int), value :: approximation          ! 0 SSA, 1 DIVA
+      integer(c_int), intent(out) :: n_visc_its, n_Axb_its
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_velocity_download( h, state) bind(C, name='ufe_b200_velocity_download') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h, state
+      integer(c_int) :: ierr
+    end function
+
+    ! calc_dHi_dt (conservation_of_mass_main.f90:27); io = c_loc of a ufe_b200_thickness_io; finish = 0 leaves the spill-over / final update to
+    ! ufe_b200_dHi_dt_finish after the host ran calc_and_apply_spill_over_flux itself
+    function c_ufe_b200_calc_dHi_dt( h, cfg, io, dt, finish, n_Axb_its) bind(C, name='ufe_b200_calc_dHi_dt') result( ierr)
+      import :: c_int, c_double, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      type(c_ptr), value :: io
+      real(c_double), intent(inout) :: dt
+      integer(c_int), value :: finish
+      integer(c_int), intent(out) :: n_Axb_its
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_dHi_dt_finish( h, Hi, Hi_tplusdt, dt, AMB, dHi_dt) bind(C, name='ufe_b200_dHi_dt_finish') result( ierr)
+      import :: c_int, c_double, c_ptr
+      type(c_ptr), value :: h
+      real(c_double), intent(in) :: Hi(*)
+      real(c_double), intent(inout) :: Hi_tplusdt(*)
+      real(c_double), value :: dt
+      real(c_double), intent(inout) :: AMB(*), dHi_dt(*)
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_thickness_upload( h, io) bind(C, name='ufe_b200_thickness_upload') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h, io
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_thickness_download( h, Hi, dHi_dt, divQ) bind(C, name='ufe_b200_thickness_download') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h, Hi, dHi_dt, divQ       ! c_loc of the (vi1:vi2) arrays, c_null_ptr = skipped
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_pc_step_resident( h, cfg, approximation, dt, n_visc_its, n_Axb_its_velocity, n_Axb_its_thickness) &
+      bind(C, name='ufe_b200_pc_step_resident') result( ierr)
+      import :: c_int, c_double, c_ptr, ufe_b200_config
+      type(c_ptr), value :: h
+      type(ufe_b200_config), intent(in) :: cfg
+      integer(c_int), value :: approximation
+      real(c_double), value :: dt
+      integer(c_int), intent(out) :: n_visc_its, n_Axb_its_velocity, n_Axb_its_thickness
+      integer(c_int) :: ierr
+    end function
+
+    ! SpMV seam: multiply_CSR_matrix_with_vector_{1D,2D}_wrapper (CSR_matrix_vector_multiplication.f90:24,112) and the 16 operator wrappers
+    ! (mesh_disc_apply_operators.f90:18-431)
+    function c_ufe_b200_csr_register( h, id, m_glob, n_glob, m_loc, i1, n_loc, j1, ptr, ind, val) bind(C, name='ufe_b200_csr_register') result( ierr)
+      import :: c_int, c_int32_t, c_double, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: id, m_glob, n_glob, m_loc, i1, n_loc, j1
+      integer(c_int32_t), intent(in) :: ptr(*), ind(*)
+      real(c_double), intent(in) :: val(*)
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_csr_update_values( h, id, val) bind(C, name='ufe_b200_csr_update_values') result( ierr)
+      import :: c_int, c_double, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: id
+      real(c_double), intent(in) :: val(*)
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_spmv( h, id, xx, yy, ncols) bind(C, name='ufe_b200_spmv') result( ierr)
+      import :: c_int, c_double, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: id
+      real(c_double), intent(in) :: xx(*)
+      real(c_double), intent(inout) :: yy(*)
+      integer(c_int), value :: ncols
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_csr_release( h, id) bind(C, name='ufe_b200_csr_release') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: id
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_apply_operator( h, op, d_in, d_out, ncols) bind(C, name='ufe_b200_apply_operator') result( ierr)
+      import :: c_int, c_double, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: op                     ! UFE_OP_* in the order of calc_all_matrix_operators_mesh
+      real(c_double), intent(in) :: d_in(*)
+      real(c_double), intent(inout) :: d_out(*)
+      integer(c_int), value :: ncols                  ! 1 (_2D) or mesh%nz (_3D)
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_set_operator( h, op, m_loc, ptr, ind, val) bind(C, name='ufe_b200_set_operator') result( ierr)
+      import :: c_int, c_int32_t, c_double, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: op, m_loc
+      integer(c_int32_t), intent(in) :: ptr(*), ind(*)
+      real(c_double), intent(in) :: val(*)
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_get_operator_size( h, op, m_loc, nnz_loc) bind(C, name='ufe_b200_get_operator_size') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: op
+      integer(c_int), intent(out) :: m_loc, nnz_loc
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_get_operator( h, op, ptr, ind, val) bind(C, name='ufe_b200_get_operator') result( ierr)
+      import :: c_int, c_int32_t, c_double, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: op
+      integer(c_int32_t), intent(inout) :: ptr(*), ind(*)
+      real(c_double), intent(inout) :: val(*)
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_mesh_ranges( h, out6) bind(C, name='ufe_b200_mesh_ranges') result( ierr)
+      import :: c_int, c_int32_t, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int32_t), intent(out) :: out6(6)      ! vi1, vi2, ti1, ti2, ei1, ei2: must equal mesh%vi1 ... mesh%ei2
+      integer(c_int) :: ierr
+    end function
+    function c_ufe_b200_kernel_launches( h) bind(C, name='ufe_b200_kernel_launches') result( n)
+      import :: c_long_long, c_ptr
+      type(c_ptr), value :: h
+      integer(c_long_long) :: n
+    end function
+    subroutine c_ufe_b200_config_defaults( cfg) bind(C, name='ufe_b200_config_defaults')
+      import :: ufe_b200_config
+      type(ufe_b200_config), intent(out) :: cfg
+    end subroutine
+    subroutine c_ufe_b200_alter_params_defaults( prm) bind(C, name='ufe_b200_alter_params_defaults')
+      import :: c_ptr
+      type(c_ptr), value :: prm                       ! c_loc of a ufe_b200_alter_params
+    end subroutine
+
     ! one predictor-corrector step through host arrays (device phases of run_ice_dynamics_model_pc, predictor_corrector_scheme.f90:118-233)
     function c_ufe_b200_pc_step( h, cfg, approximation, dt, dt_prev, ice, state, io, dHi_dt_nm1, n_visc_its, n_Axb_its_velocity, &
       n_Axb_its_thickness) bind(C, name='ufe_b200_pc_step') result( ierr)
