@@ -78,3 +78,27 @@ def test_ctypes_config_follows_the_header_order_and_size():
             size += width * (int(dim.group(1)) if dim else 1)
     assert [n for n, _ in ub.Config._fields_] == c_members
     assert C.sizeof(ub.Config) == (size + 7) // 8 * 8            # doubles first, then 32-bit integers: no padding except at the end
+
+
+def _struct_members(hdr, name):
+    body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (name, name), hdr, flags=re.S).group(1)
+    out = []
+    for decl in body.split(";"):
+        decl = re.sub(r"^(const\s+)?(double|int32_t)\s*\*?", "", decl.strip())
+        out += [n.replace("*", "").strip() for n in decl.split(",") if n.strip()]
+    return out
+
+
+def test_pointer_tables_of_the_wrappers_follow_the_struct_member_order():
+    """The Fortran wrappers hand structs of pointers over as arrays of c_loc's: their order must be the member order of the C struct."""
+    import ufe_b200 as ub
+    _, hdr = header_prototypes()
+    _, src = shim_bindings()
+    tables = {"ice_in": "ufe_b200_ice_inputs", "state": "ufe_b200_velocity_state", "out": "ufe_b200_ice_velocities"}
+    rename = {"basal_friction_coefficient": "basal_friction_coefficient_a"}            # ice%basal_friction_coefficient is the a-grid field
+    for var, struct in tables.items():
+        m = re.search(r"\n\s*%s = \[(.*?)\]" % var, src, flags=re.S)
+        names = [re.search(r"%?(\w+)\s*\)$", item.strip()).group(1) for item in m.group(1).split(",")]
+        names = [rename.get(n, n) for n in names]
+        assert names == _struct_members(hdr, struct), (var, names, _struct_members(hdr, struct))
+    assert _struct_members(hdr, "ufe_b200_velocity_state") == ub.VELOCITY_FIELDS and _struct_members(hdr, "ufe_b200_ice_velocities") == ub.ICE_VELOCITY_FIELDS

@@ -19,7 +19,8 @@ module ufe_b200_mod
   use model_configuration, only: C
   use CSR_sparse_matrix_type, only: type_sparse_matrix_CSR_dp
   use mesh_types, only: type_mesh
-  use ice_model_types, only: type_ice_model, type_ice_pc
+  use ice_model_types, only: type_ice_model, type_ice_pc, type_ice_velocity_solver_DIVA
+  use bed_roughness_model_types, only: type_bed_roughness_model
 
   implicit none
 
@@ -29,7 +30,7 @@ module ufe_b200_mod
   public :: solve_matrix_equation_CSR_B200
   public :: ufe_b200_upload_mesh, ufe_b200_destroy_mesh
   public :: ufe_b200_fill_config, ufe_b200_config
-  public :: set_ice_velocities_B200, calc_pc_truncation_error_B200
+  public :: solve_DIVA_infinite_slab_B200, set_ice_velocities_B200, calc_pc_truncation_error_B200
 
   type(c_ptr), save :: handle = c_null_ptr
 
@@ -566,6 +567,53 @@ contains
     ! Called from the mesh finaliser and before update_mesh -> remap_velocity_solver (UFEMISM_main_model.f90:1211)
     if (c_associated( handle)) call check( c_ufe_b200_mesh_destroy( handle), 'ufe_b200_destroy_mesh')
   end subroutine ufe_b200_destroy_mesh
+
+  subroutine solve_DIVA_infinite_slab_B200( mesh, ice, bed_roughness, DIVA, n_visc_its, n_Axb_its, &
+    BC_prescr_mask_b, BC_prescr_u_b, BC_prescr_v_b)
+    ! Drop-in for solve_DIVA_infinite_slab (src/UFEMISM/ice_dynamics/conservation_of_momentum/SSA_DIVA/DIVA_solver_infinite_slab.f90:52-53): same
+    ! arguments, same meaning; the fields of the solver object are filled exactly as the reference fills them, so the checksum() calls that follow
+    ! (:225-226) and restart output keep working.  ice%A_flow must be up to date (calc_ice_rheology_Glen stays on the host).
+    type(type_mesh),                                   intent(in   ) :: mesh
+    type(type_ice_model),                      target, intent(inout) :: ice
+    type(type_bed_roughness_model),            target, intent(in   ) :: bed_roughness
+    type(type_ice_velocity_solver_DIVA),       target, intent(inout) :: DIVA
+    integer,                                           intent(  out) :: n_visc_its, n_Axb_its
+    integer,  dimension(mesh%ti1:mesh%ti2), optional, target, intent(in) :: BC_prescr_mask_b
+    real(dp), dimension(mesh%ti1:mesh%ti2), optional, target, intent(in) :: BC_prescr_u_b, BC_prescr_v_b
+    character(len=1024), parameter :: routine_name = 'solve_DIVA_infinite_slab_B200'
+    type(ufe_b200_config) :: cfg
+    type(c_ptr), target :: ice_in(10), state(33)
+    integer(c_int32_t), dimension(mesh%vi1:mesh%vi2), target :: mask_grounded_ice, mask_icefree_land
+    type(c_ptr) :: bm, bu, bv
+    integer(c_int) :: nv, na
+    call init_routine( routine_name)
+    if (present( BC_prescr_mask_b) .or. present( BC_prescr_u_b) .or. present( BC_prescr_v_b)) then
+      if (.not. (present( BC_prescr_mask_b) .and. present( BC_prescr_u_b) .and. present( BC_prescr_v_b))) then
+        call crash('need to provide prescribed u,v fields and mask!')
+      end if
+      bm = c_loc( BC_prescr_mask_b); bu = c_loc( BC_prescr_u_b); bv = c_loc( BC_prescr_v_b)
+    else
+      bm = c_null_ptr; bu = c_null_ptr; bv = c_null_ptr
+    end if
+    call ufe_b200_fill_config( cfg)
+    mask_grounded_ice = merge( 1_c_int32_t, 0_c_int32_t, ice%mask_grounded_ice( mesh%vi1:mesh%vi2))
+    mask_icefree_land = merge( 1_c_int32_t, 0_c_int32_t, ice%mask_icefree_land( mesh%vi1:mesh%vi2))
+    ! member order of ufe_b200_ice_inputs (include/ufe_b200.h)
+    ice_in = [c_loc( ice%Hi), c_loc( ice%Hs), c_loc( ice%A_flow), c_loc( ice%fraction_gr_b), c_loc( bed_roughness%till_friction_angle), &
+              c_loc( bed_roughness%beta_sq), c_loc( bed_roughness%alpha_sq), c_loc( ice%effective_pressure), c_loc( mask_grounded_ice), &
+              c_loc( mask_icefree_land)]
+    ! member order of ufe_b200_velocity_state (include/ufe_b200.h)
+    state = [c_loc( DIVA%u_vav_b), c_loc( DIVA%v_vav_b), c_loc( DIVA%u_base_b), c_loc( DIVA%v_base_b), c_loc( DIVA%tau_bx_b), c_loc( DIVA%tau_by_b), &
+             c_loc( DIVA%eta_3D_b), c_loc( DIVA%u_b_prev), c_loc( DIVA%v_b_prev), c_loc( DIVA%tau_dx_b), c_loc( DIVA%tau_dy_b), &
+             c_loc( DIVA%u_3D_b), c_loc( DIVA%v_3D_b), c_loc( DIVA%du_dx_a), c_loc( DIVA%du_dy_a), c_loc( DIVA%dv_dx_a), c_loc( DIVA%dv_dy_a), &
+             c_loc( DIVA%du_dz_3D_a), c_loc( DIVA%dv_dz_3D_a), c_loc( DIVA%eta_3D_a), c_loc( DIVA%eta_vav_a), c_loc( DIVA%N_a), &
+             c_loc( DIVA%N_b), c_loc( DIVA%dN_dx_b), c_loc( DIVA%dN_dy_b), c_loc( DIVA%F1_3D_a), c_loc( DIVA%F2_3D_a), &
+             c_loc( DIVA%F1_3D_b), c_loc( DIVA%F2_3D_b), c_loc( ice%basal_friction_coefficient), c_loc( DIVA%basal_friction_coefficient_b), &
+             c_loc( DIVA%beta_eff_a), c_loc( DIVA%beta_eff_b)]
+    call check( c_ufe_b200_solve_DIVA( handle, cfg, c_loc( ice_in), c_loc( state), nv, na, bm, bu, bv), routine_name)
+    n_visc_its = int( nv); n_Axb_its = int( na)
+    call finalise_routine( routine_name)
+  end subroutine solve_DIVA_infinite_slab_B200
 
   subroutine set_ice_velocities_B200( mesh, ice)
     ! Drop-in for the set_ice_velocities_to_{SIA,SSA,SIASSA,DIVA}_results call that follows the solve in solve_stress_balance
