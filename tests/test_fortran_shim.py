@@ -94,11 +94,12 @@ def test_pointer_tables_of_the_wrappers_follow_the_struct_member_order():
     import ufe_b200 as ub
     _, hdr = header_prototypes()
     _, src = shim_bindings()
-    tables = {"ice_in": "ufe_b200_ice_inputs", "state": "ufe_b200_velocity_state", "out": "ufe_b200_ice_velocities"}
-    rename = {"basal_friction_coefficient": "basal_friction_coefficient_a"}            # ice%basal_friction_coefficient is the a-grid field
+    tables = {"ice_in": "ufe_b200_ice_inputs", "state": "ufe_b200_velocity_state", "out": "ufe_b200_ice_velocities", "io": "ufe_b200_thickness_io"}
+    rename = {"basal_friction_coefficient": "basal_friction_coefficient_a",            # ice%basal_friction_coefficient is the a-grid field
+              "noice": "mask_noice", "bm": "BC_prescr_mask", "bh": "BC_prescr_Hi"}       # 0/1 copy of the logical mask; optional arguments
     for var, struct in tables.items():
         m = re.search(r"\n\s*%s = \[(.*?)\]" % var, src, flags=re.S)
-        names = [re.search(r"%?(\w+)\s*\)$", item.strip()).group(1) for item in m.group(1).split(",")]
+        names = [re.search(r"%?(\w+)\s*\)?$", item.strip()).group(1) for item in m.group(1).split(",")]
         names = [rename.get(n, n) for n in names]
         assert names == _struct_members(hdr, struct), (var, names, _struct_members(hdr, struct))
     assert _struct_members(hdr, "ufe_b200_velocity_state") == ub.VELOCITY_FIELDS and _struct_members(hdr, "ufe_b200_ice_velocities") == ub.ICE_VELOCITY_FIELDS

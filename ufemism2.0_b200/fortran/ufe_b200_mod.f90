@@ -30,7 +30,7 @@ module ufe_b200_mod
   public :: solve_matrix_equation_CSR_B200
   public :: ufe_b200_upload_mesh, ufe_b200_destroy_mesh
   public :: ufe_b200_fill_config, ufe_b200_config
-  public :: solve_DIVA_infinite_slab_B200, set_ice_velocities_B200, calc_pc_truncation_error_B200
+  public :: solve_DIVA_infinite_slab_B200, calc_dHi_dt_B200, set_ice_velocities_B200, calc_pc_truncation_error_B200
 
   type(c_ptr), save :: handle = c_null_ptr
 
@@ -614,6 +614,47 @@ contains
     n_visc_its = int( nv); n_Axb_its = int( na)
     call finalise_routine( routine_name)
   end subroutine solve_DIVA_infinite_slab_B200
+
+  subroutine calc_dHi_dt_B200( mesh, ice, Hi, Hb, SL, u_vav_b, v_vav_b, SMB, BMB, LMB, AMB, fraction_margin, mask_noice, dt, dHi_dt, Hi_tplusdt, &
+    divQ, dHi_dt_target, BC_prescr_mask, BC_prescr_Hi)
+    ! Drop-in for calc_dHi_dt (src/UFEMISM/ice_dynamics/conservation_of_mass/conservation_of_mass_main.f90:27-28): same arguments, same meaning
+    ! (explicit or semi-implicit by C%choice_ice_integration_method, thickness BCs, mask_noice, flux-limited dt, the warning on negative thickness
+    ! stays with the caller's checksum).
+    type(type_mesh),                                intent(in   ) :: mesh
+    type(type_ice_model),                           intent(inout) :: ice
+    real(dp), dimension(mesh%vi1:mesh%vi2), target, intent(in   ) :: Hi, Hb, SL
+    real(dp), dimension(mesh%ti1:mesh%ti2), target, intent(in   ) :: u_vav_b, v_vav_b
+    real(dp), dimension(mesh%vi1:mesh%vi2), target, intent(in   ) :: SMB, BMB, LMB
+    real(dp), dimension(mesh%vi1:mesh%vi2), target, intent(inout) :: AMB
+    real(dp), dimension(mesh%vi1:mesh%vi2), target, intent(in   ) :: fraction_margin
+    logical,  dimension(mesh%vi1:mesh%vi2),         intent(in   ) :: mask_noice
+    real(dp),                                       intent(inout) :: dt
+    real(dp), dimension(mesh%vi1:mesh%vi2), target, intent(  out) :: dHi_dt, Hi_tplusdt, divQ
+    real(dp), dimension(mesh%vi1:mesh%vi2), target, intent(in   ) :: dHi_dt_target
+    integer,  dimension(mesh%vi1:mesh%vi2), target, intent(in   ), optional :: BC_prescr_mask
+    real(dp), dimension(mesh%vi1:mesh%vi2), target, intent(in   ), optional :: BC_prescr_Hi
+    character(len=1024), parameter :: routine_name = 'calc_dHi_dt_B200'
+    type(ufe_b200_config) :: cfg
+    type(c_ptr), target :: io(17)
+    integer(c_int32_t), dimension(mesh%vi1:mesh%vi2), target :: noice
+    type(c_ptr) :: bm, bh
+    integer(c_int) :: its
+    real(c_double) :: dt_c
+    call init_routine( routine_name)
+    bm = c_null_ptr; bh = c_null_ptr
+    if (present( BC_prescr_mask) .and. present( BC_prescr_Hi)) then
+      bm = c_loc( BC_prescr_mask); bh = c_loc( BC_prescr_Hi)
+    end if
+    call ufe_b200_fill_config( cfg)
+    noice = merge( 1_c_int32_t, 0_c_int32_t, mask_noice)
+    ! member order of ufe_b200_thickness_io (include/ufe_b200.h)
+    io = [c_loc( Hi), c_loc( Hb), c_loc( SL), c_loc( u_vav_b), c_loc( v_vav_b), c_loc( SMB), c_loc( BMB), c_loc( LMB), c_loc( fraction_margin), &
+          c_loc( noice), c_loc( dHi_dt_target), bm, bh, c_loc( AMB), c_loc( dHi_dt), c_loc( Hi_tplusdt), c_loc( divQ)]
+    dt_c = dt
+    call check( c_ufe_b200_calc_dHi_dt( handle, cfg, c_loc( io), dt_c, 1_c_int, its), routine_name)
+    dt = dt_c
+    call finalise_routine( routine_name)
+  end subroutine calc_dHi_dt_B200
 
   subroutine set_ice_velocities_B200( mesh, ice)
     ! Drop-in for the set_ice_velocities_to_{SIA,SSA,SIASSA,DIVA}_results call that follows the solve in solve_stress_balance
