@@ -42,6 +42,8 @@ if os.path.exists(ref):
     G["mismip_mod_small"]["n_visc_its_first_solve"] = sum(1 for l in txt[:first] if l.startswith(" u_b:") and "relax_viscosity_iterations]" in l)
     G["mismip_mod_small"]["u_vav_b_converged"] = num(txt[first])
     G["mismip_mod_small"]["tau_dx_b"] = num(next(l for l in txt if l.startswith(" tau_dx_b:")))
+    # the first thickness step that sees velocities (dt = 0.1 yr, right after that solve): flux divergence of the uniform 100 m slab
+    G["mismip_mod_small"]["divQ_after_first_solve"] = num(next(l for l in txt[first:] if l.startswith(" divQ:")))
 
 # Output of the reference itself: the checksum log of integrated_test_SSA_icestream_small (16 km, SSA, BC 'infinite_SSA_icestream').  Its first
 # stress-balance solve logs (sum, sum|.|, min, max) of u_b / v_b after every relaxed viscosity iteration: 520 iterations, all kept.

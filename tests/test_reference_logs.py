@@ -66,6 +66,30 @@ def test_oracle_diva_converges_like_the_reference():
     assert abs(f["tau_dx_b"].max() - g["tau_dx_b"][3]) <= 0.03 * g["tau_dx_b"][3] and abs(f["tau_dx_b"].min() - g["tau_dx_b"][2]) <= 0.03 * abs(g["tau_dx_b"][2])
 
 
+def test_oracle_flux_divergence_against_the_reference_log():
+    """calc_ice_flux_divergence_matrix_upwind + divQ of the first thickness step that sees velocities (conservation_of_mass_utilities.f90:23-135): the strongest
+    convergence sits on the ice-free vertices just beyond the calving front and is the same on both meshes; the maximum depends on how the front is
+    resolved and is not compared."""
+    import bench
+    g = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden.json")))["mismip_mod_small"]
+    ref = g["divQ_after_first_solve"]
+    w = mismip_mod_small_workload()
+    m, f = w.mesh, w.f
+    f["mask_noice"] = (np.hypot(m.V[:, 0], m.V[:, 1]) > 900e3).astype(np.int32)        # choice_mask_noice_config = 'MISMIP_mod' (masks_mod.f90:419-428)
+    o = ol.OracleMesh(m)
+    st, s = ub.alloc_velocity_state(m.nV, m.nTri, m.nz)
+    rc, n_visc, n_axb = o.solve_velocity(w.cfg, 1, w.ice_inputs(), st)
+    assert rc == 0
+    out = {k: np.zeros(m.nV) for k in ("AMB", "dHi_dt", "Hi_tplusdt", "divQ")}
+    io, keep = bench.thickness_io(w, slice(None), f["Hi"], s["u_vav_b"], s["v_vav_b"], out)
+    rc, dt, its = o.calc_dHi_dt(w.cfg, io, 0.1)
+    assert rc == 0 and dt == 0.1
+    assert abs(out["divQ"].min() - ref[2]) <= 0.02 * abs(ref[2]), (out["divQ"].min(), ref[2])
+    assert abs(np.abs(out["divQ"]).sum() / m.nV - ref[1] / g["nV"]) <= 0.05 * ref[1] / g["nV"]
+    # no ice may appear where mask_noice holds: the flux that arrives there is taken out again
+    assert not out["Hi_tplusdt"][f["mask_noice"] == 1].any() and abs(out["Hi_tplusdt"].max() - 100.03) < 1e-3          # the log: max = 0.10002999991886E+03
+
+
 # ---- ISMIP-HOM experiment A, L = 160 km, DIVA without sliding, periodic borders (integrated_test_ISMIP_HOM_small) -----------------------------------
 # reference name -> member of the velocity state; compared on the mean of |.| (2 %) and, where listed, on the maximum (2 %)
 HOM_FIELDS = {"DIVA%du_dz_3D_a": "du_dz_3D_a", "DIVA%eta_3D_a": "eta_3D_a", "DIVA%eta_3D_b": "eta_3D_b", "DIVA%eta_vav_a": "eta_vav_a", "DIVA%N_a": "N_a",
