@@ -19,7 +19,7 @@ module ufe_b200_mod
   use model_configuration, only: C
   use CSR_sparse_matrix_type, only: type_sparse_matrix_CSR_dp
   use mesh_types, only: type_mesh
-  use ice_model_types, only: type_ice_model, type_ice_pc, type_ice_velocity_solver_DIVA
+  use ice_model_types, only: type_ice_model, type_ice_pc, type_ice_velocity_solver_DIVA, type_ice_velocity_solver_SSA
   use bed_roughness_model_types, only: type_bed_roughness_model
 
   implicit none
@@ -30,7 +30,7 @@ module ufe_b200_mod
   public :: solve_matrix_equation_CSR_B200
   public :: ufe_b200_upload_mesh, ufe_b200_destroy_mesh
   public :: ufe_b200_fill_config, ufe_b200_config
-  public :: solve_DIVA_infinite_slab_B200, calc_dHi_dt_B200, set_ice_velocities_B200, calc_pc_truncation_error_B200
+  public :: solve_DIVA_infinite_slab_B200, solve_SSA_B200, calc_dHi_dt_B200, set_ice_velocities_B200, calc_pc_truncation_error_B200
 
   type(c_ptr), save :: handle = c_null_ptr
 
@@ -614,6 +614,51 @@ contains
     n_visc_its = int( nv); n_Axb_its = int( na)
     call finalise_routine( routine_name)
   end subroutine solve_DIVA_infinite_slab_B200
+
+  subroutine solve_SSA_B200( mesh, ice, bed_roughness, SSA, n_visc_its, n_Axb_its, BC_prescr_mask_b, BC_prescr_u_b, BC_prescr_v_b)
+    ! Drop-in for solve_SSA (src/UFEMISM/ice_dynamics/conservation_of_momentum/SSA_DIVA/SSA_main.f90:88-89): same arguments, same meaning.
+    ! The SSA solver object has no 3-D fields: those members of ufe_b200_velocity_state stay c_null_ptr and are skipped by the library.
+    type(type_mesh),                                   intent(in   ) :: mesh
+    type(type_ice_model),                      target, intent(inout) :: ice
+    type(type_bed_roughness_model),            target, intent(in   ) :: bed_roughness
+    type(type_ice_velocity_solver_SSA),        target, intent(inout) :: SSA
+    integer,                                           intent(  out) :: n_visc_its, n_Axb_its
+    integer,  dimension(mesh%ti1:mesh%ti2), optional, target, intent(in) :: BC_prescr_mask_b
+    real(dp), dimension(mesh%ti1:mesh%ti2), optional, target, intent(in) :: BC_prescr_u_b, BC_prescr_v_b
+    character(len=1024), parameter :: routine_name = 'solve_SSA_B200'
+    type(ufe_b200_config) :: cfg
+    type(c_ptr), target :: ice_in_ssa(10), state_ssa(33)
+    integer(c_int32_t), dimension(mesh%vi1:mesh%vi2), target :: mask_grounded_ice, mask_icefree_land
+    type(c_ptr) :: bm, bu, bv
+    integer(c_int) :: nv, na
+    call init_routine( routine_name)
+    if (present( BC_prescr_mask_b) .or. present( BC_prescr_u_b) .or. present( BC_prescr_v_b)) then
+      if (.not. (present( BC_prescr_mask_b) .and. present( BC_prescr_u_b) .and. present( BC_prescr_v_b))) then
+        call crash('need to provide prescribed u,v fields and mask!')
+      end if
+      bm = c_loc( BC_prescr_mask_b); bu = c_loc( BC_prescr_u_b); bv = c_loc( BC_prescr_v_b)
+    else
+      bm = c_null_ptr; bu = c_null_ptr; bv = c_null_ptr
+    end if
+    call ufe_b200_fill_config( cfg)
+    cfg%stress_balance_PETSc_rtol = SSA%PETSc_rtol; cfg%stress_balance_PETSc_abstol = SSA%PETSc_abstol   ! SSA_main.f90:224
+    mask_grounded_ice = merge( 1_c_int32_t, 0_c_int32_t, ice%mask_grounded_ice( mesh%vi1:mesh%vi2))
+    mask_icefree_land = merge( 1_c_int32_t, 0_c_int32_t, ice%mask_icefree_land( mesh%vi1:mesh%vi2))
+    ice_in_ssa = [c_loc( ice%Hi), c_loc( ice%Hs), c_loc( ice%A_flow), c_loc( ice%fraction_gr_b), c_loc( bed_roughness%till_friction_angle), &
+                  c_loc( bed_roughness%beta_sq), c_loc( bed_roughness%alpha_sq), c_loc( ice%effective_pressure), c_loc( mask_grounded_ice), &
+                  c_loc( mask_icefree_land)]
+    ! member order of ufe_b200_velocity_state; SSA%u_b, v_b travel as u_vav_b, v_vav_b, SSA%eta_a as eta_vav_a
+    state_ssa = [c_loc( SSA%u_b), c_loc( SSA%v_b), c_null_ptr, c_null_ptr, c_null_ptr, c_null_ptr, &
+                 c_null_ptr, c_loc( SSA%u_b_prev), c_loc( SSA%v_b_prev), c_loc( SSA%tau_dx_b), c_loc( SSA%tau_dy_b), &
+                 c_null_ptr, c_null_ptr, c_loc( SSA%du_dx_a), c_loc( SSA%du_dy_a), c_loc( SSA%dv_dx_a), c_loc( SSA%dv_dy_a), &
+                 c_null_ptr, c_null_ptr, c_null_ptr, c_loc( SSA%eta_a), c_loc( SSA%N_a), &
+                 c_loc( SSA%N_b), c_loc( SSA%dN_dx_b), c_loc( SSA%dN_dy_b), c_null_ptr, c_null_ptr, &
+                 c_null_ptr, c_null_ptr, c_loc( ice%basal_friction_coefficient), c_loc( SSA%basal_friction_coefficient_b), &
+                 c_null_ptr, c_null_ptr]
+    call check( c_ufe_b200_solve_SSA( handle, cfg, c_loc( ice_in_ssa), c_loc( state_ssa), nv, na, bm, bu, bv), routine_name)
+    n_visc_its = int( nv); n_Axb_its = int( na)
+    call finalise_routine( routine_name)
+  end subroutine solve_SSA_B200
 
   subroutine calc_dHi_dt_B200( mesh, ice, Hi, Hb, SL, u_vav_b, v_vav_b, SMB, BMB, LMB, AMB, fraction_margin, mask_noice, dt, dHi_dt, Hi_tplusdt, &
     divQ, dHi_dt_target, BC_prescr_mask, BC_prescr_Hi)
