@@ -161,3 +161,16 @@ def test_oracle_follows_the_reference_checksum_log():
         assert rc == 0 and nv == 1
         seq.append((f["u_vav_b"].sum(), f["u_vav_b"].max()))
     check_against_reference_log(seq, m.nTri)
+
+
+def test_find_ti_copy_on_a_graded_mesh():
+    """the greedy walk of find_containing_vertex (start vertex 5) on the x-graded MISMIP+ mesh, where the resolution changes along the way"""
+    w = wl.mismip_plus(8.0e3)
+    m = w.mesh
+    o = ol.OracleMesh(m)
+    border = np.where(m.TriBI > 0)[0] + 1
+    for ti in border[::7]:
+        tj, wt = o.find_ti_copy(ub.BC_INFINITE_SSA_ICESTREAM, 0.0, int(ti))
+        tj_ref, w_ref = brute_force_copy(m, ub.BC_INFINITE_SSA_ICESTREAM, 0.0, int(ti))
+        n = len(tj_ref)
+        assert np.array_equal(tj[:n], tj_ref) and np.allclose(wt[:n], w_ref, rtol=1e-12)
