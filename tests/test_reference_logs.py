@@ -75,7 +75,7 @@ def test_oracle_flux_divergence_against_the_reference_log():
     ref = g["divQ_after_first_solve"]
     w = mismip_mod_small_workload()
     m, f = w.mesh, w.f
-    f["mask_noice"] = (np.hypot(m.V[:, 0], m.V[:, 1]) > 900e3).astype(np.int32)        # choice_mask_noice_config = 'MISMIP_mod' (masks_mod.f90:419-428)
+    f["mask_noice"] = wl.mask_noice(m, "MISMIP_mod")                                   # choice_mask_noice_config = 'MISMIP_mod' (masks_mod.f90:419-428)
     o = ol.OracleMesh(m)
     st, s = ub.alloc_velocity_state(m.nV, m.nTri, m.nz)
     rc, n_visc, n_axb = o.solve_velocity(w.cfg, 1, w.ice_inputs(), st)

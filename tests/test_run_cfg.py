@@ -34,7 +34,7 @@ def test_formatting_round_trips_every_number_of_a_reference_log():
 GEOMETRIES = {
     "MISMIP_mod": ("xmin_ANT_config = -1000e3\nxmax_ANT_config = 1000e3\nrefgeo_idealised_MISMIP_mod_Hi_init_config = 100.0\n"
                    "choice_basal_hydrology_model_config = 'Martin2011'\nslid_ZI_phi_fric_uniform_config = 10.0\nmaximum_resolution_uniform_config = 100e3\n"
-                   "choice_stress_balance_approximation_config = 'DIVA'\n"),
+                   "choice_stress_balance_approximation_config = 'DIVA'\nchoice_mask_noice_config = 'MISMIP_mod'\n"),
     "SSA_icestream": ("xmin_ANT_config = -400e3\nxmax_ANT_config = 400e3\nmaximum_resolution_uniform_config = 64e3\n"
                       "choice_stress_balance_approximation_config = 'SSA'\nchoice_sliding_law_config = 'idealised'\n"
                       "choice_idealised_sliding_law_config = 'SSA_icestream'\nBC_u_west_config = 'infinite_SSA_icestream'\n"),
@@ -54,7 +54,9 @@ def test_workload_of_the_experiment_a_config_names(geo):
     m, f = w.mesh, w.f
     assert w.cfg is setup.cfg and w.approximation == setup.approximation
     assert abs(m.xmax - float(setup.values["xmax_ANT"])) < 1e-6 and m.nV > 100 and np.isfinite(f["Hi"]).all() and f["Hi"].max() > 0
+    assert (f["mask_noice"].sum() > 0) == (geo == "MISMIP_mod")
     if geo == "MISMIP_mod":
+        assert not f["Hi"][f["mask_noice"] == 1].any()                  # the initial slab ends where the mask begins (r = 900 km)
         assert set(np.unique(f["Hi"])) == {0.0, 100.0} and f["effective_pressure"].max() < 0.2 * wl_overburden(f)   # Martin2011 pore water almost floats the ice
     if geo == "ISMIP-HOM_A":
         assert abs(f["Hi"].mean() - 1000.0) < 20.0 and list(w.cfg.BC_u) == [0, 0, 0, 2]

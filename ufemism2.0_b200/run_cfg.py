@@ -68,6 +68,10 @@ def workload_from_setup(setup, resolution=None, region="ANT"):
                       R0=float(v.get("refgeo_idealised_Halfar_R0", 500e3)), A=setup.cfg.uniform_Glens_flow_factor)
     else:
         raise cn.ConfigError(f'idealised geometry "{geo}" is not one of MISMIP_mod, SSA_icestream, ISMIP-HOM_A, Halfar')
+    try:
+        w.f["mask_noice"] = wl.mask_noice(w.mesh, v.get("choice_mask_noice", "none"))
+    except ValueError as e:
+        raise cn.ConfigError(str(e)) from e
     w.cfg = setup.cfg
     w.approximation = setup.approximation
     return w

@@ -29,6 +29,18 @@ def masks_from_geometry(Hi, Hb, SL):
     )
 
 
+def mask_noice(mesh, choice):
+    """calc_mask_noice (src/UFEMISM/ice_dynamics/utilities/masks_mod.f90:385-450) for the idealised choices: where no ice is allowed"""
+    x, y = mesh.V[:, 0], mesh.V[:, 1]
+    if choice == "none":
+        return np.zeros(mesh.nV, np.int32)
+    if choice == "MISMIP_mod":
+        return (np.hypot(x, y) > 900e3).astype(np.int32)         # kill all ice when r > 900 km
+    if choice == "MISMIP+":
+        return (x > 640e3).astype(np.int32)                      # kill all ice when x > 640 km
+    raise ValueError(f'unknown choice_mask_noice "{choice}"')
+
+
 def scaling_config(cfg=None):
     """config_MISMIP_8km_spinup_for_scaling.cfg :236-326 (DIVA, Zoet-Iverson, semi-implicit)."""
     c = cfg or ub.default_config()
