@@ -93,5 +93,35 @@ for _L in (160, 80, 40):
                 S["last"][name] = _nums(l)          # later lines overwrite earlier ones: the last viscosity iteration stays
     G["ismip_hom_A_%d_DIVA" % _L] = S
 
+# Output of the reference itself: the Halfar dome run of integrated_test_Halfar_dome_small (100 yr, SIA, predictor-corrector time stepping).  Every
+# predictor-corrector iteration logs the corrected thickness and the truncation error: 58 iterations, all kept.  (A three-digit exponent is printed without
+# its E: 0.76841014953792-234.)
+def _nums3(line):
+    return [float(re.sub(r"(\d)([+-]\d{3})$", r"\1E\2", x).replace("-.", "-0.")) for x in re.findall(r"=\s*(-?[0-9]*\.[0-9]+(?:E[+-][0-9]+|[+-][0-9]{3}))", line)]
+
+
+ref = "/root/reference/automated_testing/UFEMISM/integrated_test_Halfar_dome_small/reference/checksum_logfile_Halfar_40km_grid.txt"
+if os.path.exists(ref):
+    S = {"source": "automated_testing/UFEMISM/integrated_test_Halfar_dome_small/reference/checksum_logfile_Halfar_40km_grid.txt",
+         "columns": ["sum", "sum_abs", "min", "max"], "Hi_np1": [], "Hi_star_np1": [], "tau_np1": [], "divQ": []}
+    for l in open(ref):
+        if l.startswith(" fraction_gr:") and "nV" not in S:
+            S["nV"] = int(round(_nums3(l)[0]))                              # fraction_gr = 1 on every vertex
+        elif l.startswith(" fraction_gr_b:") and "nTri" not in S:
+            S["nTri"] = int(round(_nums3(l)[0]))
+        elif l.startswith(" ice%Hi:") and "Hi_initial" not in S:
+            S["Hi_initial"] = _nums3(l)
+        elif l.startswith(" region%ice%pc%Hi_np1:"):
+            S["Hi_np1"].append(_nums3(l))
+        elif l.startswith(" region%ice%pc%Hi_star_np1:"):
+            S["Hi_star_np1"].append(_nums3(l))
+        elif l.startswith(" pc%tau_np1:"):
+            S["tau_np1"].append(_nums3(l))
+        elif l.startswith(" divQ:"):
+            S["divQ"].append(_nums3(l))
+        elif l.startswith(" region%ice%Hs:"):
+            S["Hs_final"] = _nums3(l)
+    json.dump(S, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "halfar_40km.json"), "w"))
+
 json.dump(G, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden.json"), "w"), indent=1)
 print("wrote golden.json")
