@@ -44,6 +44,26 @@ if os.path.exists(ref):
     G["mismip_mod_small"]["tau_dx_b"] = num(next(l for l in txt if l.startswith(" tau_dx_b:")))
     # the first thickness step that sees velocities (dt = 0.1 yr, right after that solve): flux divergence of the uniform 100 m slab
     G["mismip_mod_small"]["divQ_after_first_solve"] = num(next(l for l in txt[first:] if l.startswith(" divQ:")))
+    # the whole 100-year run: per predictor-corrector iteration the number of viscosity iterations of its stress-balance solve, the converged
+    # DIVA%u_vav_b, the corrected thickness and the truncation error; first and last grounded fractions and mask counts
+    T = {"n_visc_its": [], "u_vav_b": [], "Hi_np1": [], "tau_np1": [], "fraction_gr_b": [], "fraction_gr": [], "mask_grounded_ice": [], "mask_floating_ice": []}
+    cnt = 0
+    for l in txt:
+        if l.startswith(" u_b:") and "relax_viscosity_iterations]" in l:
+            cnt += 1
+        elif l.startswith(" DIVA%u_vav_b:"):
+            T["n_visc_its"].append(cnt); cnt = 0; T["u_vav_b"].append(num(l))
+        elif l.startswith(" region%ice%pc%Hi_np1:"):
+            T["Hi_np1"].append(num(l))
+        elif l.startswith(" pc%tau_np1:"):
+            T["tau_np1"].append(num(l))
+        elif l.startswith(" fraction_gr_b:") or l.startswith(" fraction_gr:"):
+            T[l.split(":")[0].strip()].append(num(l)[0])
+        elif l.startswith(" mask_grounded_ice:") or l.startswith(" mask_floating_ice:"):
+            T[l.split(":")[0].strip()].append(int(re.search(r"sum = (\d+)", l).group(1)))
+    for k in ("fraction_gr_b", "fraction_gr", "mask_grounded_ice", "mask_floating_ice"):
+        T[k] = [T[k][0], T[k][-1]]
+    G["mismip_mod_small"]["time_loop"] = T
 
 # Output of the reference itself: the checksum log of integrated_test_SSA_icestream_small (16 km, SSA, BC 'infinite_SSA_icestream').  Its first
 # stress-balance solve logs (sum, sum|.|, min, max) of u_b / v_b after every relaxed viscosity iteration: 520 iterations, all kept.

@@ -61,7 +61,14 @@ class HalfarRun:
         self.eta_n = self.eta_np1 = PC_EPSILON
         self.guilty = np.zeros(nV, np.int32)
         self.frac_gr = np.ones(nV)                                      # Hb = 0, SL = -10 m: everything is grounded (the log: fraction_gr = 1 throughout)
-        self.log = []                                                   # per PC iteration: (t, dt, max Hi_np1, max tau, eta)
+        self.log = []                                                   # per PC iteration: (t, dt, max Hi_np1, max tau, eta, max u_vav_b)
+
+    # hooks for experiments with floating ice and sliding (tests/test_reference_mismip_mod_log.py); the Halfar dome needs none of them
+    def begin_action(self):
+        """what run_model_region does at every action time before the ice dynamics (UFEMISM_main_model.f90:118: run_basal_hydrology_model)"""
+
+    def update_fractions(self, Hi, mk):
+        """calc_grounded_fractions for the geometry the thickness step and the truncation error see"""
 
     def calc_dHi_dt(self, Hi, fraction_margin, dt):
         w, f = self.w, self.w.f
@@ -88,25 +95,28 @@ class HalfarRun:
         dt = max(min(dt, DT_MAX, PC_MAX_INCREASE * self.dt_n), DT_MIN)
         mk = o.determine_masks(cfg, self.Hi, Hb, SL)
         dt = min(dt, o.calc_critical_timestep_adv(cfg, 0, self.Hi, mk["mask_floating_ice"], self.u, self.v))
+        self.update_fractions(self.Hi, mk)
         fm = o.calc_effective_thickness(cfg, self.Hi, Hb, SL)[1]
-        d_nm1 = self.dHi_dt.copy()
+        d_nm1 = np.where(f["mask_noice"] == 1, 0.0, self.dHi_dt)
+        self.Hi_prev[f["mask_noice"] == 1] = 0.0
         self.eta_n = self.eta_np1
         for _ in range(PC_NIT_MAX):
             z = dt / self.dt_n
-            d_n = self.calc_dHi_dt(self.Hi, fm, dt)                                                   # on region%ice%Hi, see the module docstring
+            d_n = np.where(f["mask_noice"] == 1, 0.0, self.calc_dHi_dt(self.Hi, fm, dt))              # on region%ice%Hi, see the module docstring
             Hi_star = np.maximum(0.0, self.Hi_prev + dt * ((1 + z / 2) * d_n - (z / 2) * d_nm1))      # Eq. 30
             d_n = ((Hi_star - self.Hi_prev) / dt + (z / 2) * d_nm1) / (1 + z / 2)
             self.solve_stress_balance(Hi_star)
             mk = o.determine_masks(cfg, self.Hi_prev, Hb, SL)
+            self.update_fractions(self.Hi_prev, mk)
             fm_c = o.calc_effective_thickness(cfg, self.Hi_prev, Hb, SL)[1]
-            d_s = self.calc_dHi_dt(self.Hi_prev, fm_c, dt)
+            d_s = np.where(f["mask_noice"] == 1, 0.0, self.calc_dHi_dt(self.Hi_prev, fm_c, dt))
             Hi_np1 = np.maximum(0.0, self.Hi_prev + (dt / 2) * (d_n + d_s))                           # Eq. 31
             self.Hi = self.Hi_prev.copy()
             tau = np.zeros(self.m.nV); eta = C.c_double(); nt, ng = C.c_int(), C.c_int()
             ol.lib().orc_calc_pc_truncation_error(self.m.nV, z, self.dt_n, PC_ETA_MIN, PC_EPSILON, ub.dp(Hi_np1), ub.dp(Hi_star), ub.ip(mk["mask_grounded_ice"]),
                                                   ub.ip(mk["mask_gl_gr"]), ub.dp(self.frac_gr), ub.dp(tau), ub.ip(self.guilty), C.byref(eta), C.byref(nt), C.byref(ng))
             self.eta_np1 = eta.value
-            self.log.append((self.t_prev, dt, Hi_np1.max(), tau.max(), eta.value))
+            self.log.append((self.t_prev, dt, Hi_np1.max(), tau.max(), eta.value, self.u.max()))
             if self.eta_np1 < PC_EPSILON:
                 break
             if 100.0 * ng.value / max(nt.value, 1) < PC_GUILTY_MAX:
@@ -122,6 +132,7 @@ class HalfarRun:
     def run(self, t_end=T_END):
         time, t_thermo = 0.0, 0.0
         while time <= t_end:
+            self.begin_action()
             if time == self.t_next:
                 self.pc()
             wt_prev = (self.t_next - time) / (self.t_next - self.t_prev)
