@@ -72,6 +72,12 @@ class HalfarRun:
     def update_fractions(self, Hi, mk):
         """calc_grounded_fractions for the geometry the thickness step and the truncation error see"""
 
+    def truncation_error(self, z, Hi_np1, Hi_star, mk):
+        tau = np.zeros(self.m.nV); eta = C.c_double(); nt, ng = C.c_int(), C.c_int()
+        ol.lib().orc_calc_pc_truncation_error(self.m.nV, z, self.dt_n, PC_ETA_MIN, PC_EPSILON, ub.dp(Hi_np1), ub.dp(Hi_star), ub.ip(mk["mask_grounded_ice"]),
+                                              ub.ip(mk["mask_gl_gr"]), ub.dp(self.frac_gr), ub.dp(tau), ub.ip(self.guilty), C.byref(eta), C.byref(nt), C.byref(ng))
+        return tau, eta.value, nt.value, ng.value
+
     def calc_dHi_dt(self, Hi, fraction_margin, dt):
         w, f = self.w, self.w.f
         f["fraction_margin"] = fraction_margin
@@ -116,14 +122,12 @@ class HalfarRun:
             d_s = np.where(f["mask_noice"] == 1, 0.0, self.calc_dHi_dt(self.Hi_prev, fm_c, dt))
             Hi_np1 = np.maximum(0.0, self.Hi_prev + (dt / 2) * (d_n + d_s))                           # Eq. 31
             self.Hi = self.Hi_prev.copy()
-            tau = np.zeros(self.m.nV); eta = C.c_double(); nt, ng = C.c_int(), C.c_int()
-            ol.lib().orc_calc_pc_truncation_error(self.m.nV, z, self.dt_n, PC_ETA_MIN, PC_EPSILON, ub.dp(Hi_np1), ub.dp(Hi_star), ub.ip(mk["mask_grounded_ice"]),
-                                                  ub.ip(mk["mask_gl_gr"]), ub.dp(self.frac_gr), ub.dp(tau), ub.ip(self.guilty), C.byref(eta), C.byref(nt), C.byref(ng))
-            self.eta_np1 = eta.value
-            self.log.append((self.t_prev, dt, Hi_np1.max(), tau.max(), eta.value, self.u.max()))
+            tau, eta, nt, ng = self.truncation_error(z, Hi_np1, Hi_star, mk)
+            self.eta_np1 = eta
+            self.log.append((self.t_prev, dt, Hi_np1.max(), tau.max(), eta, self.u.max()))
             if self.eta_np1 < PC_EPSILON:
                 break
-            if 100.0 * ng.value / max(nt.value, 1) < PC_GUILTY_MAX:
+            if 100.0 * ng / max(nt, 1) < PC_GUILTY_MAX:
                 self.eta_np1 = 0.95 * PC_EPSILON
                 break
             dt *= 0.8
