@@ -1,6 +1,5 @@
 """The .cfg-driven run setup: UFEMISM's `&CONFIG` namelist read into ufe_b200_config (cfg_namelist.py, the twin of ufe_b200_fill_config in the Fortran
 shim).  With the reference tree present (build container) the reference's own config files must give exactly the configurations the workloads use."""
-import ctypes as C
 import os
 
 import pytest

@@ -13,7 +13,6 @@ import os
 
 import numpy as np
 
-import oracle_lib as ol
 import ufe_b200 as ub
 import workloads as wl
 from test_reference_halfar_log import HalfarRun
