@@ -45,9 +45,9 @@ class DeviceBackend:
                                                          ub.dp(cdf), ub.dp(cdf_b), ub.dp(fr), ub.dp(frb)))
         return fr, frb
 
-    def calc_critical_timestep_adv(self, cfg, grounded_only, Hi, mask_floating_ice, u, v):
+    def calc_critical_timestep_adv(self, cfg, grounded_only, Hi, mask_floating_ice, u_vav_b, v_vav_b):
         dt = C.c_double()
-        ub.check(self.L.ufe_b200_calc_critical_timestep_adv(self.ctx.h, C.byref(cfg), grounded_only, ub.dp(Hi), ub.ip(mask_floating_ice), ub.dp(u), ub.dp(v), C.byref(dt)))
+        ub.check(self.L.ufe_b200_calc_critical_timestep_adv(self.ctx.h, C.byref(cfg), grounded_only, ub.dp(Hi), ub.ip(mask_floating_ice), ub.dp(u_vav_b), ub.dp(v_vav_b), C.byref(dt)))
         return dt.value
 
     def calc_dHi_dt(self, cfg, io, dt):
@@ -62,10 +62,10 @@ class DeviceBackend:
                                            *(ub.dp(r[k]) for k in ("u_3D_b", "v_3D_b", "D_3D_b", "du_dz_3D_a", "dv_dz_3D_a"))))
         return r
 
-    def solve_velocity(self, cfg, approximation, ice, st):
+    def solve_velocity(self, cfg, approximation, ice, state):
         nv, na = C.c_int(), C.c_int()
         fn = self.L.ufe_b200_solve_DIVA if approximation == 1 else self.L.ufe_b200_solve_SSA
-        rc = fn(self.ctx.h, C.byref(cfg), C.byref(ice), C.byref(st), C.byref(nv), C.byref(na), None, None, None)
+        rc = fn(self.ctx.h, C.byref(cfg), C.byref(ice), C.byref(state), C.byref(nv), C.byref(na), None, None, None)
         return rc, nv.value, na.value
 
 

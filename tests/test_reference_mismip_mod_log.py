@@ -124,3 +124,27 @@ def test_oracle_diva_time_loop_follows_the_reference_mismip_mod_log():
     assert T["mask_grounded_ice"][1] > T["mask_grounded_ice"][0] and T["mask_floating_ice"][1] < T["mask_floating_ice"][0]
     assert run.masks["mask_grounded_ice"].sum() > run.first["grounded"] and run.masks["mask_floating_ice"].sum() < run.first["floating"]
     assert 1.02 < run.frac_gr_b.sum() / run.first["fraction_gr_b"] < 1.15
+
+
+def test_device_backend_of_the_time_loops_covers_every_call():
+    """scripts/gpu_time_loop.py swaps the loops' backend for the C ABI: every method the loops call on it must exist there, with the oracle binding's arguments"""
+    import ast
+    import importlib.util
+    import inspect
+    import oracle_lib as ol
+    here = os.path.dirname(os.path.abspath(__file__))
+    called = set()
+    for name in ("test_reference_halfar_log.py", "test_reference_mismip_mod_log.py"):
+        for n in ast.walk(ast.parse(open(os.path.join(here, name)).read())):
+            if isinstance(n, ast.Call) and isinstance(n.func, ast.Attribute) and isinstance(n.func.value, (ast.Name, ast.Attribute)):
+                v = n.func.value
+                if (isinstance(v, ast.Name) and v.id == "o") or (isinstance(v, ast.Attribute) and v.attr == "o"):
+                    called.add(n.func.attr)
+    assert {"determine_masks", "calc_effective_thickness", "calc_grounded_fractions", "calc_critical_timestep_adv", "calc_dHi_dt", "solve_SIA", "solve_velocity"} <= called
+    spec = importlib.util.spec_from_file_location("gpu_time_loop", os.path.join(os.path.dirname(here), "scripts", "gpu_time_loop.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    for name in sorted(called):
+        dev, orc = getattr(mod.DeviceBackend, name), getattr(ol.OracleMesh, name)
+        a, b = list(inspect.signature(dev).parameters), list(inspect.signature(orc).parameters)
+        assert a == b[:len(a)] and all(inspect.signature(orc).parameters[p].default is not inspect.Parameter.empty for p in b[len(a):]), (name, a, b)
