@@ -148,3 +148,44 @@ def test_device_backend_of_the_time_loops_covers_every_call():
         dev, orc = getattr(mod.DeviceBackend, name), getattr(ol.OracleMesh, name)
         a, b = list(inspect.signature(dev).parameters), list(inspect.signature(orc).parameters)
         assert a == b[:len(a)] and all(inspect.signature(orc).parameters[p].default is not inspect.Parameter.empty for p in b[len(a):]), (name, a, b)
+
+
+def test_one_call_step_model_reproduces_the_loop():
+    """CPU model of what timestep.cu does per call with ufe_b200_pc_reference_loop switched on (lagged thickness for the predictor, applied rate for the next
+    Eq. 30, the interpolation weight of the last action time), driven the way scripts/gpu_time_loop.py::one_call_mismip_mod drives the device: one call per
+    predictor-corrector step with the known time-step sequence.  It must land on the loop model's end state; without the switch it does not."""
+    def workload():
+        w = mismip_mod_small_workload()
+        w.f["mask_noice"] = wl.mask_noice(w.mesh, "MISMIP_mod")
+        return w
+    loop = MismipModRun(workload())
+    loop.run()
+    log = np.array(loop.log)
+
+    def one_call_run(reference_loop):
+        r = MismipModRun(workload())
+        f, cfg, o = r.w.f, r.w.cfg, r.o
+        Hb, SL, noice = f["Hb"], f["SL"], f["mask_noice"] == 1
+        Hi_n, Hi_lag, d_nm1, dt_n = r.Hi.copy(), r.Hi.copy(), np.zeros(r.m.nV), None
+        for t, dt in log[:, :2]:
+            last = max(t, np.ceil(t + dt) - 1.0)
+            wgt = (last - t) / dt if reference_loop else 0.0
+            r.Hi = Hi_lag; r.begin_action()                                    # the host: effective pressure of the thickness at the last action time
+            z = dt / (dt_n if dt_n else dt)
+            H_pred = Hi_lag if reference_loop else Hi_n
+            d_n = np.where(noice, 0.0, r.calc_dHi_dt(H_pred, o.calc_effective_thickness(cfg, H_pred, Hb, SL)[1], dt))
+            Hi_star = np.maximum(0.0, Hi_n + dt * ((1 + z / 2) * d_n - (z / 2) * d_nm1))
+            r.solve_stress_balance(Hi_star)
+            d_s = np.where(noice, 0.0, r.calc_dHi_dt(Hi_n, o.calc_effective_thickness(cfg, Hi_n, Hb, SL)[1], dt))
+            h = np.maximum(0.0, Hi_n + (dt / 2) * (d_n + d_s))
+            d_nm1 = (h - Hi_n) / dt if reference_loop else d_n
+            Hi_lag = (1.0 - wgt) * Hi_n + wgt * h
+            Hi_n, dt_n = h, dt
+        return Hi_n, r.u.max()
+
+    Hi_ref, u_ref = one_call_run(True)
+    rel = np.linalg.norm(Hi_ref - loop.Hi_next) / np.linalg.norm(loop.Hi_next)
+    assert rel < 1e-6 and abs(u_ref / loop.u.max() - 1.0) < 1e-5, (rel, u_ref, loop.u.max())
+    Hi_plain, u_plain = one_call_run(False)
+    rel_plain = np.linalg.norm(Hi_plain - loop.Hi_next) / np.linalg.norm(loop.Hi_next)
+    assert 1e-3 < rel_plain < 2e-2, rel_plain

@@ -18,6 +18,10 @@ struct PcState {
   DBuf<double> dHdt_n, dHdt_nm1, Hi_prev;
   double dt_n = 0.0;
   bool started = false;
+  // ufe_b200_pc_reference_loop: the two places where the reference's loop departs from Eq. 30 as printed (see the entry's comment in the header)
+  bool reference_loop = false, lag_valid = false;
+  double w_lag = 0.0;
+  DBuf<double> Hi_lag, Hi_save;
 };
 static PcState* g_pc = nullptr;   // one per process (one rank <-> one GPU)
 
@@ -42,14 +46,20 @@ __global__ void k_pc_predict(int n, int off, double dt, double zeta, double rho_
 __global__ void k_pc_correct(int n, int off, double dt, double rho_ratio, const int* __restrict__ mask_noice,
                              const double* __restrict__ dHdt_n, double* __restrict__ dHdt_nm1, const double* __restrict__ dHdt_star,
                              const double* __restrict__ Hb, const double* __restrict__ SL, double* __restrict__ Hi,
-                             double* __restrict__ Hi_vel, double* __restrict__ Hs_vel) {
+                             double* __restrict__ Hi_vel, double* __restrict__ Hs_vel, double* __restrict__ Hi_lag, double w_lag) {
   for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
     const size_t i = off + r;
     double ds = dHdt_star[i];
     if (mask_noice[i]) ds = 0.0;
-    const double h = fmax(0.0, Hi[i] + (dt / 2.0) * (dHdt_n[i] + ds));
+    const double h_old = Hi[i];
+    const double h = fmax(0.0, h_old + (dt / 2.0) * (dHdt_n[i] + ds));
     Hi[i] = h;
-    dHdt_nm1[i] = dHdt_n[i];
+    if (Hi_lag) {   // reference loop: region%ice%Hi as interpolated at the last action time, and the applied rate for the next Eq. 30
+      Hi_lag[i] = (1.0 - w_lag) * h_old + w_lag * h;               // ice_dynamics_main.f90:115-121
+      dHdt_nm1[i] = (h - h_old) / dt;                              // ice_dynamics_main.f90:140 -> predictor_corrector_scheme.f90:113
+    } else {
+      dHdt_nm1[i] = dHdt_n[i];
+    }
     Hi_vel[i] = h;
     Hs_vel[i] = h + fmax(SL[i] - rho_ratio * h, Hb[i]);
   }
@@ -71,10 +81,20 @@ static int pc_step_core(Ctx* c, const ufe_b200_config* cfg, int approximation, d
   double dt_p = dt, dt_c = dt;
   const bool dynamic = geometry_dynamic(c);
   // effective thickness / margin fraction of the current geometry (:107; the same values serve the corrector, :211)
+  const bool lagged = P.reference_loop;
+  if (lagged) {   // the predictor works on region%ice%Hi, which the reference leaves at the thickness of the last action time (:129 against :143)
+    if (P.Hi_lag.n < na) { UFE_TRY(P.Hi_lag.alloc(na)); UFE_TRY(P.Hi_save.alloc(na)); P.lag_valid = false; }
+    if (!P.lag_valid) { UFE_CUDA(cudaMemcpyAsync(P.Hi_lag.p, T.Hi.p, sizeof(double) * na, cudaMemcpyDeviceToDevice, st)); P.lag_valid = true; }
+    UFE_CUDA(cudaMemcpyAsync(P.Hi_save.p, T.Hi.p, sizeof(double) * na, cudaMemcpyDeviceToDevice, st));
+    UFE_CUDA(cudaMemcpyAsync(T.Hi.p, P.Hi_lag.p, sizeof(double) * na, cudaMemcpyDeviceToDevice, st));
+  }
   if (dynamic) UFE_TRY(geometry_for_thickness(c, cfg, T.Hi.p, T.Hb.p, T.SL.p, T.fraction_margin.p));
   // predictor: dHi_dt( Hi_n, u_n) (:129)
   UFE_TRY(halo_exchange(c, M.b, V.u.p)); UFE_TRY(halo_exchange(c, M.b, V.v.p));
   UFE_TRY(thickness_step(c, cfg, V.u.p, V.v.p, &dt_p, 1, &its_p));
+  if (lagged) {
+    UFE_CUDA(cudaMemcpyAsync(T.Hi.p, P.Hi_save.p, sizeof(double) * na, cudaMemcpyDeviceToDevice, st));
+  }
   UFE_CUDA(cudaMemcpyAsync(P.dHdt_n.p, T.dHi_dt.p, sizeof(double) * na, cudaMemcpyDeviceToDevice, st));
   { UFE_LAUNCH(c, TC_THICKNESS); k_pc_predict<<<grid, 128, 0, st>>>(n, M.a.off(), dt, zeta, rho_ratio, T.mask_noice.p, T.Hi.p, P.dHdt_n.p, P.dHdt_nm1.p, T.Hb.p, T.SL.p, V.Hi.p, V.Hs.p); }
   // velocities for the predicted geometry (:186)
@@ -95,9 +115,11 @@ static int pc_step_core(Ctx* c, const ufe_b200_config* cfg, int approximation, d
   UFE_TRY(velocity_solve(c, cfg, approximation, n_visc_its, n_Axb_its_velocity));
   UFE_TRY(after_velocity());
   // corrector: dHi_dt( Hi_n, u_np1) (:214)
+  if (lagged && dynamic) UFE_TRY(geometry_for_thickness(c, cfg, T.Hi.p, T.Hb.p, T.SL.p, T.fraction_margin.p));   // (:211) on Hi_prev, which now differs
   UFE_TRY(halo_exchange(c, M.b, V.u.p)); UFE_TRY(halo_exchange(c, M.b, V.v.p));
   UFE_TRY(thickness_step(c, cfg, V.u.p, V.v.p, &dt_c, 1, &its_c));
-  { UFE_LAUNCH(c, TC_THICKNESS); k_pc_correct<<<grid, 128, 0, st>>>(n, M.a.off(), dt, rho_ratio, T.mask_noice.p, P.dHdt_n.p, P.dHdt_nm1.p, T.dHi_dt.p, T.Hb.p, T.SL.p, T.Hi.p, V.Hi.p, V.Hs.p); }
+  { UFE_LAUNCH(c, TC_THICKNESS); k_pc_correct<<<grid, 128, 0, st>>>(n, M.a.off(), dt, rho_ratio, T.mask_noice.p, P.dHdt_n.p, P.dHdt_nm1.p, T.dHi_dt.p, T.Hb.p, T.SL.p, T.Hi.p, V.Hi.p, V.Hs.p,
+                                                              lagged ? P.Hi_lag.p : nullptr, P.w_lag); }
   UFE_CUDA(cudaGetLastError());
   *n_Axb_its_thickness = its_p + its_c;
   return 0;
@@ -141,7 +163,7 @@ int ufe_b200_thickness_upload(ufe_b200_handle h, const ufe_b200_thickness_io* io
     T.have_bc = true;
   } else T.have_bc = false;
   UFE_CUDA(cudaStreamSynchronize(c->stream));
-  if (g_pc) g_pc->started = false;
+  if (g_pc) { g_pc->started = false; g_pc->lag_valid = false; }
   return 0;
 }
 
@@ -241,6 +263,18 @@ int ufe_b200_pc_step(ufe_b200_handle h, const ufe_b200_config* cfg, int approxim
   UFE_CUDA(cudaStreamSynchronize(main_st));
   UFE_CUDA(cudaStreamSynchronize(c->copy_stream));
   P.dt_n = dt;
+  return 0;
+}
+
+int ufe_b200_pc_reference_loop(ufe_b200_handle h, int on, double wt_next_of_last_action) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c, "NULL handle");
+  UFE_CHECK(wt_next_of_last_action >= 0.0 && wt_next_of_last_action <= 1.0, "ufe_b200_pc_reference_loop: the interpolation weight must lie in [0, 1] (got %g)",
+            wt_next_of_last_action);
+  if (!g_pc) g_pc = new PcState();
+  if (!on) g_pc->lag_valid = false;
+  g_pc->reference_loop = on != 0;
+  g_pc->w_lag = wt_next_of_last_action;
   return 0;
 }
 

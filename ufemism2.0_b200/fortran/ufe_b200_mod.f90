@@ -431,6 +431,15 @@ module ufe_b200_mod
       integer(c_int) :: ierr
     end function
 
+    ! region%ice%Hi apart from Hi_prev, region%ice%dHi_dt as pc%dHi_dt_Hi_nm1_u_nm1 (ice_dynamics_main.f90:115-140); wt_next of the last action time
+    function c_ufe_b200_pc_reference_loop( h, on, wt_next_of_last_action) bind(C, name='ufe_b200_pc_reference_loop') result( ierr)
+      import :: c_int, c_ptr, c_double
+      type(c_ptr), value :: h
+      integer(c_int), value :: on
+      real(c_double), value :: wt_next_of_last_action
+      integer(c_int) :: ierr
+    end function
+
     ! apply_grounded_fractions_to_bed_roughness (basal_conditions/sliding_laws.f90:568-636); masks = c_loc of a ufe_b200_masks
     function c_ufe_b200_apply_grounded_fractions_to_bed_roughness( h, Hi, Hs_slope, fraction_gr, masks, bed_roughness, bed_roughness_applied) &
       bind(C, name='ufe_b200_apply_grounded_fractions_to_bed_roughness') result( ierr)
