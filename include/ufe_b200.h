@@ -309,11 +309,11 @@ int ufe_b200_set_state_resident(ufe_b200_handle h, int on);
  * Robinson et al. (2020), Eq. 30 as printed (both visible in the checksum log of integrated_test_Halfar_dome_small; tests/test_reference_halfar_log.py):
  *   - the predictor's calc_dHi_dt (and the effective thickness before it) sees region%ice%Hi, which run_ice_dynamics_model left at the thickness
  *     interpolated at the last action time (src/UFEMISM/ice_dynamics/ice_dynamics_main.f90:115-121), while Eq. 30 / 31 add to Hi_prev
- *     (time_stepping/predictor_corrector_scheme.f90:129 against :143).  The library keeps that field on the device: after a step n -> n+1 it is
+ *     (time_stepping/predictor_corrector_scheme.f90:129 against :140).  The library keeps that field on the device: after a step n -> n+1 it is
  *     (1 - w) Hi_n + w Hi_np1 with w = wt_next_of_last_action, the interpolation weight of the last action time before t_np1 (0 when no other sub-model
  *     acted in between); before the first step it equals the uploaded Hi;
  *   - pc%dHi_dt_Hi_nm1_u_nm1 is region%ice%dHi_dt, the applied rate (Hi_np1 - Hi_n) / dt of the previous step (ice_dynamics_main.f90:140 ->
- *     predictor_corrector_scheme.f90:113), not the previous predictor rate; ufe_b200_pc_step then returns that rate in dHi_dt_nm1.
+ *     predictor_corrector_scheme.f90:109), not the previous predictor rate; ufe_b200_pc_step then returns that rate in dHi_dt_nm1.
  * on = 0 (default): one thickness, previous predictor rate.  Callable before every step to set w.  Written at the end of round 1: compiled, not yet run on a GPU. */
 int ufe_b200_pc_reference_loop(ufe_b200_handle h, int on, double wt_next_of_last_action);
 

@@ -56,7 +56,7 @@ __global__ void k_pc_correct(int n, int off, double dt, double rho_ratio, const 
     Hi[i] = h;
     if (Hi_lag) {   // reference loop: region%ice%Hi as interpolated at the last action time, and the applied rate for the next Eq. 30
       Hi_lag[i] = (1.0 - w_lag) * h_old + w_lag * h;               // ice_dynamics_main.f90:115-121
-      dHdt_nm1[i] = (h - h_old) / dt;                              // ice_dynamics_main.f90:140 -> predictor_corrector_scheme.f90:113
+      dHdt_nm1[i] = (h - h_old) / dt;                              // ice_dynamics_main.f90:140 -> predictor_corrector_scheme.f90:109
     } else {
       dHdt_nm1[i] = dHdt_n[i];
     }
@@ -82,7 +82,7 @@ static int pc_step_core(Ctx* c, const ufe_b200_config* cfg, int approximation, d
   const bool dynamic = geometry_dynamic(c);
   // effective thickness / margin fraction of the current geometry (:107; the same values serve the corrector, :211)
   const bool lagged = P.reference_loop;
-  if (lagged) {   // the predictor works on region%ice%Hi, which the reference leaves at the thickness of the last action time (:129 against :143)
+  if (lagged) {   // the predictor works on region%ice%Hi, which the reference leaves at the thickness of the last action time (:129 against :140)
     if (P.Hi_lag.n < na) { UFE_TRY(P.Hi_lag.alloc(na)); UFE_TRY(P.Hi_save.alloc(na)); P.lag_valid = false; }
     if (!P.lag_valid) { UFE_CUDA(cudaMemcpyAsync(P.Hi_lag.p, T.Hi.p, sizeof(double) * na, cudaMemcpyDeviceToDevice, st)); P.lag_valid = true; }
     UFE_CUDA(cudaMemcpyAsync(P.Hi_save.p, T.Hi.p, sizeof(double) * na, cudaMemcpyDeviceToDevice, st));
