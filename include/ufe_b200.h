@@ -314,7 +314,8 @@ int ufe_b200_set_state_resident(ufe_b200_handle h, int on);
  *     acted in between); before the first step it equals the uploaded Hi;
  *   - pc%dHi_dt_Hi_nm1_u_nm1 is region%ice%dHi_dt, the applied rate (Hi_np1 - Hi_n) / dt of the previous step (ice_dynamics_main.f90:140 ->
  *     predictor_corrector_scheme.f90:109), not the previous predictor rate; ufe_b200_pc_step then returns that rate in dHi_dt_nm1.
- * on = 0 (default): one thickness, previous predictor rate.  Callable before every step to set w.  Written at the end of round 1: compiled, not yet run on a GPU. */
+ * on = 0 (default): one thickness, previous predictor rate.  Callable before every step to set w.  The switch belongs to the resident time-step state, of which
+ * there is one per process (one rank <-> one GPU); ufe_b200_thickness_upload re-initialises the lagged thickness from the uploaded Hi.  Written at the end of round 1: compiled, not yet run on a GPU. */
 int ufe_b200_pc_reference_loop(ufe_b200_handle h, int on, double wt_next_of_last_action);
 
 /* ---- SIA (config 4) ------------------------------------------------------------------------------ */
