@@ -12,7 +12,9 @@ import json
 import os
 
 import numpy as np
+import pytest
 
+import oracle_lib as ol
 import ufe_b200 as ub
 import workloads as wl
 from test_reference_halfar_log import HalfarRun
@@ -42,8 +44,9 @@ def bedrock_cdfs(m):
 
 
 class MismipModRun(HalfarRun):
-    def __init__(self, w):
+    def __init__(self, w, ksp=ol.KSP_BICGSTAB_JACOBI):
         super().__init__(w)
+        self.ksp = ksp
         m = self.m
         self.cdf, self.cdf_b = bedrock_cdfs(m)
         self.dHb = np.zeros(m.nV)
@@ -78,19 +81,20 @@ class MismipModRun(HalfarRun):
         f["mask_grounded_ice"], f["mask_icefree_land"] = mk["mask_grounded_ice"], mk["mask_icefree_land"]
         f["fraction_gr_b"] = self.grounded_fractions(Hi, mk)[1]
         f["Hi"], f["Hs"] = Hi, wl.ice_surface_elevation(Hi, f["Hb"], f["SL"])
-        rc, nv, na = self.o.solve_velocity(w.cfg, 1, w.ice_inputs(), self.st)
+        rc, nv, na = self.o.solve_velocity(w.cfg, 1, w.ice_inputs(), self.st, **({} if self.ksp == ol.KSP_BICGSTAB_JACOBI else {"ksp": self.ksp}))
         assert rc == 0
         self.n_visc.append(nv)
         self.u, self.v = self.state["u_vav_b"].copy(), self.state["v_vav_b"].copy()
 
 
-def test_oracle_diva_time_loop_follows_the_reference_mismip_mod_log():
+@pytest.mark.parametrize("ksp", [ol.KSP_BICGSTAB_JACOBI, ol.KSP_GMRES_ILU0])      # the device's Krylov method, and PETSc's default (GMRES(30) + ILU(0))
+def test_oracle_diva_time_loop_follows_the_reference_mismip_mod_log(ksp):
     g = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden.json")))["mismip_mod_small"]
     T = g["time_loop"]
     ref_u, ref_H, ref_nv = np.array(T["u_vav_b"]), np.array(T["Hi_np1"]), T["n_visc_its"]
     w = mismip_mod_small_workload()
     w.f["mask_noice"] = wl.mask_noice(w.mesh, "MISMIP_mod")
-    run = MismipModRun(w)
+    run = MismipModRun(w, ksp)
     # the initial sub-grid state.  The log's mesh is refined at the grounding line (220 grounded of 1022 vertices), ours is uniform, so counts do not compare;
     # the log's relation does (sum of fraction_gr = 218.3 for 220 grounded vertices: the grounding line cuts its cells about in half), and so does the area:
     # a 100 m slab floats where Hb < -100 rho_i / rho_w, i.e. beyond r = 448.5 km on the cone
