@@ -1,0 +1,34 @@
+"""The CPU legs of bench.py (`cpu_baseline`, `--impl reference`): the bounded sample runs the oracle through the same predictor-corrector call sequence the
+GPU arm times, and the reference arm prints one JSON line with the contract's keys.  (The GPU arm needs a GPU; its line is checked on the box.)"""
+import json
+import os
+import subprocess
+import sys
+
+import bench
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_cpu_sample_runs_the_step_and_scales_to_the_full_workload():
+    r = bench.run_cpu_sample(3000, 4005450, steps=1, warmup=0)
+    assert r["kind"] == "port" and r["unit"] == "velocity solves/s" and r["cores"] >= 1
+    assert 2000 < r["n_vertices_sample"] < 4500 and r["ms_per_step_sample"] > 0.0
+    # value = sample rate scaled linearly in vertices to the full workload
+    assert abs(r["value"] - (1e3 / r["ms_per_step_sample"]) * r["n_vertices_sample"] / 4005450) < 1e-12 * r["value"] + 1e-15
+    assert "viscosity its" in r["sample"] and "Krylov its" in r["sample"]
+
+
+def test_reference_arm_prints_the_contract_line():
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0", "--cpu-nv", "3000"],
+                       capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = [l for l in p.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    j = json.loads(lines[0])
+    for k in ("impl", "metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline", "dtype", "data", "config",
+              "cpu_baseline", "e2e", "gpu_launches"):
+        assert k in j, k
+    assert j["impl"] == "reference" and j["gpu_launches"] == 0 and j["dtype"] == "f64" and j["data"] == "synthetic" and j["vs_baseline"] is None
+    assert j["e2e"] == {"value": j["value"], "unit": j["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert j["cpu_baseline"]["value"] == j["value"] and j["cpu_baseline"]["kind"] == "port" and "workload" in j["config"]
