@@ -32,3 +32,11 @@ def test_reference_arm_prints_the_contract_line():
     assert j["impl"] == "reference" and j["gpu_launches"] == 0 and j["dtype"] == "f64" and j["data"] == "synthetic" and j["vs_baseline"] is None
     assert j["e2e"] == {"value": j["value"], "unit": j["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert j["cpu_baseline"]["value"] == j["value"] and j["cpu_baseline"]["kind"] == "port" and "workload" in j["config"]
+
+
+def test_reference_arm_other_ranks_exit_without_work():
+    """under torchrun (N > 1) rank 0 alone runs and prints the reference arm; the other ranks exit 0 silently, without waiting for a rendezvous"""
+    env = dict(os.environ, RANK="1", LOCAL_RANK="1", WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT="29533")
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0", "--cpu-nv", "3000"],
+                       capture_output=True, text=True, timeout=120, env=env)
+    assert p.returncode == 0 and p.stdout.strip() == "", (p.returncode, p.stdout[-500:], p.stderr[-500:])
