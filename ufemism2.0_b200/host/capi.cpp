@@ -24,6 +24,21 @@ void* ufe_host_mesh_dummy5(double xmin, double xmax, double ymin, double ymax) {
   return m;
 }
 
+// A mesh whose primary data (mesh_types.f90:56-68) the caller already holds -- e.g. one of the reference's own NetCDF meshes -- in the Fortran
+// layout; the secondary data follow from calc_secondary exactly as for a generated mesh (calc_all_secondary_mesh_data, mesh_secondary.f90:31-70).
+void* ufe_host_mesh_from_primary(int nV, int nTri, int nC_mem, int nz, int zeta_kind, double zeta_R, double xmin, double xmax, double ymin,
+                                 double ymax, const double* V, const int* nC, const int* C, const int* niTri, const int* iTri,
+                                 const int* VBI, const int* Tri, const double* Tricc, const int* TriC) {
+  auto* m = new HostMesh();
+  m->nV = nV; m->nTri = nTri; m->nC_mem = nC_mem; m->nz = nz;
+  m->xmin = xmin; m->xmax = xmax; m->ymin = ymin; m->ymax = ymax;
+  m->V.assign(V, V + (size_t)nV * 2); m->nC.assign(nC, nC + nV); m->C.assign(C, C + (size_t)nV * nC_mem);
+  m->niTri.assign(niTri, niTri + nV); m->iTri.assign(iTri, iTri + (size_t)nV * nC_mem); m->VBI.assign(VBI, VBI + nV);
+  m->Tri.assign(Tri, Tri + (size_t)nTri * 3); m->Tricc.assign(Tricc, Tricc + (size_t)nTri * 2); m->TriC.assign(TriC, TriC + (size_t)nTri * 3);
+  if (!ufe::calc_secondary(*m, zeta_kind, zeta_R)) { std::string e = m->last_error; *m = HostMesh(); m->last_error = e.empty() ? "failed" : e; }
+  return m;
+}
+
 void ufe_host_mesh_free(void* h) { delete static_cast<HostMesh*>(h); }
 
 const char* ufe_host_mesh_error(void* h) { return static_cast<HostMesh*>(h)->last_error.c_str(); }

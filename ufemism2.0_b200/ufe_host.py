@@ -23,6 +23,8 @@ def lib():
         L.ufe_host_mesh_synth.argtypes = [C.c_double] * 6 + [C.c_ulonglong] + [C.c_double] * 3 + [C.c_int] * 3 + [C.c_double]
         L.ufe_host_mesh_dummy5.restype = C.c_void_p
         L.ufe_host_mesh_dummy5.argtypes = [C.c_double] * 4
+        L.ufe_host_mesh_from_primary.restype = C.c_void_p
+        L.ufe_host_mesh_from_primary.argtypes = [C.c_int] * 5 + [C.c_double] * 5 + [C.c_void_p] * 9
         L.ufe_host_mesh_free.argtypes = [C.c_void_p]
         L.ufe_host_mesh_error.restype = C.c_char_p
         L.ufe_host_mesh_error.argtypes = [C.c_void_p]
@@ -86,6 +88,17 @@ class HostMesh:
     @classmethod
     def dummy5(cls, xmin=-1.0, xmax=1.0, ymin=-1.0, ymax=1.0):
         return cls(lib().ufe_host_mesh_dummy5(xmin, xmax, ymin, ymax))
+
+    @classmethod
+    def from_primary(cls, V, nC, C_, niTri, iTri, VBI, Tri, Tricc, TriC, xmin, xmax, ymin, ymax, nz=12, zeta_kind=0, zeta_R=10.0):
+        """A mesh from primary data the caller holds (Fortran shapes: V (nV,2), C (nV,nC_mem), Tri (nTri,3), ...; 1-based indices)."""
+        f64 = lambda a: np.asfortranarray(a, dtype=np.float64)
+        i32 = lambda a: np.asfortranarray(a, dtype=np.int32)
+        V, Tricc = f64(V), f64(Tricc)
+        nC, C_, niTri, iTri, VBI, Tri, TriC = (i32(a) for a in (nC, C_, niTri, iTri, VBI, Tri, TriC))
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        return cls(lib().ufe_host_mesh_from_primary(V.shape[0], Tri.shape[0], C_.shape[1], nz, zeta_kind, zeta_R, xmin, xmax, ymin, ymax,
+                                                    p(V), p(nC), p(C_), p(niTri), p(iTri), p(VBI), p(Tri), p(Tricc), p(TriC)))
 
     def halos(self, rank, nranks):
         out = (C.c_int * 36)()
