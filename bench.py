@@ -145,6 +145,32 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def bind_to_gpu_numa_node(gpu_index, log=lambda *a: None):
+    """Run this process (and first-touch its page-locked buffers) on the NUMA node the GPU hangs off: host<->device copies from the far socket
+    cross the inter-socket link and reach about half the PCIe rate.  No-op on single-node hosts or when sysfs / nvidia-smi say nothing."""
+    try:
+        bdf = subprocess.run(["nvidia-smi", "--query-gpu=pci.bus_id", "--format=csv,noheader", "-i", str(gpu_index)], capture_output=True, text=True,
+                             timeout=20).stdout.strip().lower()
+        if not bdf:
+            return None
+        bdf = bdf[-12:] if len(bdf) > 12 else bdf          # 00000000:1B:00.0 -> 0000:1b:00.0
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            log(f"bound to NUMA node {node} of GPU {gpu_index} ({len(cpus)} cpus)")
+            return node
+    except (OSError, ValueError, subprocess.SubprocessError):
+        pass
+    return None
+
+
 # ------------------------------------------------------------------------------------------------------------------
 # workload
 # ------------------------------------------------------------------------------------------------------------------
@@ -171,7 +197,7 @@ def make_workload(nv, pc="jacobi"):
     w = wl.mismip_mod(h_for_vertices(nv), half_width=HALF_WIDTH)
     cfg = w.cfg                      # config_MISMIP_8km_spinup_for_scaling.cfg physics
     cfg.write_diagnostics = 0
-    cfg.ksp_initial_guess_nonzero = 1  # time stepping starts each Krylov solve from the previous solution
+    cfg.ksp_initial_guess_nonzero = 0  # the reference's KSP starts from zero (petsc_basic.f90:163 is commented out); B200_use_initial_guess_config is timed as an extra
     cfg.pc_type = ub.PC_MG if pc == "mg" else ub.PC_JACOBI   # the oracle ignores this key (it has its own ksp switch)
     return w
 
@@ -199,29 +225,45 @@ def surf(Hi, Hb, SL, cfg):
     return Hi + np.maximum(SL - cfg.ice_density / cfg.seawater_density * Hi, Hb)
 
 
-def pc_step_host(calc_dHi_dt, solve_velocity, w, cfg, sl_a, S, dt, geometry=None):
-    """One predictor-corrector step through host buffers (the call sequence of predictor_corrector_scheme.f90:118-233).
-    S: dict with Hi, dHdt_nm1, dt_n, ice (IceInputs builder), velocity state arrays.  Used by the e2e leg (GPU C ABI)
-    and by the CPU reference arm (oracle) alike; only `calc_dHi_dt` / `solve_velocity` differ.
-    geometry( Hi, for_velocity): optional geometry/mask/sub-grid stage (determine_masks, calc_grounded_fractions, calc_effective_thickness;
-    :95-107, :172-179, :198-211); it updates the masks / fractions in w.f that the two callbacks read."""
+def pc_step_host(calc_dHi_dt, solve_velocity, w, cfg, sl_a, S, dt, geometry=None, hi_eff=None, alter=None, reference_loop=True, w_lag=0.0):
+    """One pass of iterate_pc_timestep through host buffers, in the reference's order (predictor_corrector_scheme.f90:86-233): what ufe_b200_pc_step and
+    ufe_b200_pc_step_resident do in one call.  Used by the CPU reference arm (oracle callbacks) and, as the model of the device step, by the tests.
+    S: Hi (= Hi_prev), dHdt_nm1 (pc%dHi_dt_Hi_nm1_u_nm1), dt_n, u, v [, Hi_model = region%ice%Hi where it lags behind Hi_prev].
+    geometry( Hi, for_velocity): optional geometry / mask / sub-grid stage (determine_masks, calc_grounded_fractions, calc_effective_thickness;
+    :95-107, :172-179, :198-211); it updates the masks / fractions in w.f that the two callbacks read.
+    hi_eff( Hi) -> effective thickness (calc_effective_thickness); alter( Hi_of_masks, Hi_old, Hi_new) -> Hi_new: alter_ice_thickness; default: the
+    removal of ice whose effective thickness is below C%Hi_min, which is all that routine does with its optional modifications off.
+    reference_loop / w_lag: see ufe_b200_pc_reference_loop."""
     f = w.f
-    Hb, SL, noice = f["Hb"][sl_a], f["SL"][sl_a], f["mask_noice"][sl_a]
+    Hb, SL, noice = f["Hb"][sl_a], f["SL"][sl_a], f["mask_noice"][sl_a] == 1
     zeta = dt / S["dt_n"]
+    if alter is None:
+        def alter(_Hi_of_masks, _Hi_old, Hi_new):
+            return np.where(hi_eff(Hi_new) < cfg.Hi_min, 0.0, Hi_new)
+    Hi_model = S.get("Hi_model") if reference_loop else None
+    if Hi_model is None:
+        Hi_model = S["Hi"]
+    Hi_prev = np.where(noice, 0.0, S["Hi"]); d_nm1 = np.where(noice, 0.0, S["dHdt_nm1"])                 # (:88-93)
     if geometry:
-        geometry(S["Hi"], False)
-    d_n, its_p = calc_dHi_dt(S["Hi"], S["u"], S["v"], dt)                      # predictor (:129)
-    d_n = np.where(noice == 1, 0.0, d_n)
-    Hi_star = np.maximum(0.0, S["Hi"] + dt * ((1 + zeta / 2) * d_n - (zeta / 2) * S["dHdt_nm1"]))   # Eq. 30
+        geometry(Hi_model, False)
+    d_n, its_p = calc_dHi_dt(Hi_model, S["u"], S["v"], dt)                               # predictor, on region%ice%Hi (:129)
+    d_n = np.where(noice, 0.0, d_n)
+    Hi_star = Hi_prev + dt * ((1 + zeta / 2) * d_n - (zeta / 2) * d_nm1)                 # Eq. 30 (:140)
+    Hi_star = alter(Hi_model, Hi_prev, Hi_star)                                          # (:145)
+    d_n = ((Hi_star - Hi_prev) / dt + (zeta / 2) * d_nm1) / (1 + zeta / 2)               # (:152)
     if geometry:
         geometry(Hi_star, True)
-    nv, na = solve_velocity(Hi_star, surf(Hi_star, Hb, SL, cfg))                  # (:186) updates S["u"], S["v"], ...
+    nv, na = solve_velocity(Hi_star, surf(Hi_star, Hb, SL, cfg))                         # (:186) updates S["u"], S["v"], ...
     if geometry:
-        geometry(S["Hi"], False)
-    d_s, its_c = calc_dHi_dt(S["Hi"], S["u"], S["v"], dt)                      # corrector (:214)
-    d_s = np.where(noice == 1, 0.0, d_s)
-    S["Hi"] = np.maximum(0.0, S["Hi"] + (dt / 2) * (d_n + d_s))                  # Eq. 31
-    S["dHdt_nm1"] = d_n
+        geometry(Hi_prev, False)
+    d_s, its_c = calc_dHi_dt(Hi_prev, S["u"], S["v"], dt)                                # corrector (:214)
+    d_s = np.where(noice, 0.0, d_s)
+    Hi_np1 = Hi_prev + (dt / 2) * (d_n + d_s)                                            # Eq. 31 (:226)
+    Hi_np1 = alter(Hi_prev, Hi_prev, Hi_np1)                                             # (:233)
+    S["Hi_star"], S["dHdt_n"] = Hi_star, d_n
+    S["dHdt_nm1"] = (Hi_np1 - Hi_prev) / dt if reference_loop else d_n                   # ice_dynamics_main.f90:140 -> :109
+    S["Hi_model"] = (1.0 - w_lag) * Hi_prev + w_lag * Hi_np1                             # ice_dynamics_main.f90:115-121
+    S["Hi"] = Hi_np1
     S["dt_n"] = dt
     return nv, na, its_p + its_c
 
@@ -232,52 +274,112 @@ STATE_FIELDS = ["u_vav_b", "v_vav_b", "u_base_b", "v_base_b", "tau_bx_b", "tau_b
 # ------------------------------------------------------------------------------------------------------------------
 # CPU arm: the oracle (port of the reference's algorithm) on the host cores, on a bounded sample of the workload
 # ------------------------------------------------------------------------------------------------------------------
-def run_cpu_sample(nv_sample, nv_full, steps, warmup, log=lambda *a: None):
+SPINUP_VISC = 6
+
+
+def host_threads():
+    """threads the CPU arm may use: the cores this process is allowed on (not OMP_NUM_THREADS, which torch.distributed.run sets to 1 for its children)"""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def run_cpu_sample(nv_sample, nv_full, steps, warmup, log=lambda *a: None, solvers=("bicgstab_jacobi", "gmres_bjacobi_ilu0"), budget_s=150.0):
+    """The oracle's predictor-corrector steps on all host cores, on a bounded sample mesh of the same workload, once per Krylov setting:
+    'gmres_bjacobi_ilu0' = the reference's actual default (PETSc GMRES(30) + block Jacobi with one ILU(0) per MPI rank, one rank per core;
+    petsc_basic.f90:95-105, 125-193), 'bicgstab_jacobi' = the algorithm `-ksp_type bcgs -pc_type jacobi` selects (the device's one-level method).
+    Both with the reference's zero initial guess (petsc_basic.f90:163).  `value` is the faster of the two."""
+    cores = host_threads()
+    os.environ["OMP_NUM_THREADS"] = str(cores)   # before liboracle.so (and libgomp with it) is loaded
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as ol   # CPU baseline leg: the one place bench.py may execute oracle/
     import ufe_b200 as ub
+    ol.lib().orc_set_num_threads(cores)
+    threads_used = int(ol.lib().orc_max_threads())
     w = make_workload(nv_sample)
     m, cfg = w.mesh, w.cfg
+    cfg.ksp_initial_guess_nonzero = 0            # reference semantics
     o = ol.OracleMesh(m)
     t0 = time.time()
     o.calc_matrix_operators()
-    log(f"[cpu] sample mesh nV={m.nV}, operators {time.time() - t0:.1f}s")
+    log(f"[cpu] sample mesh nV={m.nV}, operators {time.time() - t0:.1f}s, {threads_used} threads")
     sl = slice(None)
-    st, A = ub.alloc_velocity_state(m.nV, m.nTri, m.nz, fields=STATE_FIELDS + ["u_b_prev", "v_b_prev"])
-    out = {k: np.zeros(m.nV) for k in ("AMB", "dHi_dt", "Hi_tplusdt", "divQ")}
-
-    def calc(Hi, u, v, dt):
-        io, keep = thickness_io(w, sl, Hi, u, v, out)
-        rc, dt2, its = o.calc_dHi_dt(cfg, io, dt)
-        assert rc == 0
-        return out["dHi_dt"].copy(), its
-
-    def solve(Hi, Hs):
-        w.f["Hi"], w.f["Hs"] = Hi, Hs
-        ice = w.ice_inputs()
-        rc, nv, na = o.solve_velocity(cfg, 1, ice, st)
-        assert rc == 0
-        return nv, na
-
-    S = dict(Hi=w.f["Hi"].copy(), dHdt_nm1=np.zeros(m.nV), dt_n=DT, u=A["u_vav_b"], v=A["v_vav_b"])
+    KSP = {"bicgstab_jacobi": ol.KSP_BICGSTAB_JACOBI, "gmres_bjacobi_ilu0": ol.KSP_GMRES_BJACOBI_ILU0}
+    runs = {}
+    Hi0, Hs0 = w.f["Hi"].copy(), w.f["Hs"].copy()
+    # spin-up (untimed, shared by both settings): SPINUP_VISC viscosity iterations from rest, Krylov solves started from the previous iterate.  A converged
+    # spin-up (19 viscosity iterations) would cost more CPU time than the whole timed sample; instead every timed step runs exactly ONE viscosity iteration,
+    # which is what the spun-up device run does per step (config.per_step.viscosity_its = 1.0), so the work per step is the same: one assembly, one
+    # velocity Krylov solve from a zero guess, two thickness solves.
+    st0, A0 = ub.alloc_velocity_state(m.nV, m.nTri, m.nz, fields=STATE_FIELDS + ["u_b_prev", "v_b_prev"])
     t0 = time.time()
-    nv0, na0 = solve(S["Hi"], w.f["Hs"])     # spin-up: cold velocity solve (untimed)
+    cfg.ksp_initial_guess_nonzero = 1
+    rc, nv0, na0 = o.solve_velocity(cfg, 1, w.ice_inputs(), st0, ksp=ol.KSP_BICGSTAB_JACOBI, max_visc_its=SPINUP_VISC)
+    cfg.ksp_initial_guess_nonzero = 0
+    assert rc == 0
     log(f"[cpu] spin-up {time.time() - t0:.1f}s: {nv0} viscosity its, {na0} Krylov its")
-    for _ in range(warmup):
-        pc_step_host(calc, solve, w, cfg, sl, S, DT)
-    t0 = time.time()
-    tot = [0, 0, 0]
-    for _ in range(steps):
-        r = pc_step_host(calc, solve, w, cfg, sl, S, DT)
-        tot = [a + b for a, b in zip(tot, r)]
-    el = time.time() - t0
-    rate_sample = steps / el
-    cores = os.cpu_count() or 1
-    return dict(value=rate_sample * m.nV / nv_full, unit="velocity solves/s", cores=cores, kind="port",
-                sample=(f"{steps} predictor-corrector steps (after {warmup} warm-up) of the same MISMIP_mod DIVA config on a {m.nV}-vertex mesh "
-                        f"({rate_sample:.4f} steps/s measured, {tot[0] / steps:.1f} viscosity its and {tot[1] / steps:.0f} Krylov its per step), scaled "
-                        f"linearly in vertices to {nv_full}; optimistic for the CPU because Krylov iterations grow with resolution"),
-                ms_per_step_sample=1e3 * el / steps, n_vertices_sample=int(m.nV))
+    for name in solvers:
+        ksp = KSP[name]
+        st, A = ub.alloc_velocity_state(m.nV, m.nTri, m.nz, fields=STATE_FIELDS + ["u_b_prev", "v_b_prev"])
+        for k in A:
+            A[k][...] = A0[k]
+        out = {k: np.zeros(m.nV) for k in ("AMB", "dHi_dt", "Hi_tplusdt", "divQ")}
+        w.f["Hi"], w.f["Hs"] = Hi0.copy(), Hs0.copy()
+
+        def calc(Hi, u, v, dt):
+            io, keep = thickness_io(w, sl, Hi, u, v, out)
+            rc, dt2, its = o.calc_dHi_dt(cfg, io, dt, ksp=ksp)
+            assert rc == 0
+            return out["dHi_dt"].copy(), its
+
+        def solve(Hi, Hs):
+            w.f["Hi"], w.f["Hs"] = Hi, Hs
+            ice = w.ice_inputs()
+            rc, nv, na = o.solve_velocity(cfg, 1, ice, st, ksp=ksp, max_visc_its=1)
+            assert rc == 0
+            return nv, na
+
+        S = dict(Hi=w.f["Hi"].copy(), dHdt_nm1=np.zeros(m.nV), dt_n=DT, u=A["u_vav_b"], v=A["v_vav_b"])
+        he = lambda Hi: o.calc_effective_thickness(cfg, Hi, w.f["Hb"], w.f["SL"])[0]
+
+        def geometry(Hi, for_velocity):   # the stage the b200 arm runs on the device (--geometry 1): masks, grounded fractions, effective thickness
+            f = w.f
+            if for_velocity:
+                mk = o.determine_masks(cfg, Hi, f["Hb"], f["SL"])
+                f["mask_grounded_ice"], f["mask_icefree_land"] = mk["mask_grounded_ice"], mk["mask_icefree_land"]
+                f["fraction_gr_b"] = o.calc_grounded_fractions(cfg, ub.GF_BILIN_INTERP_TAF, 0, Hi, f["Hb"], f["SL"], np.zeros(m.nV), mk["mask_floating_ice"], None, None)[1]
+            else:
+                f["fraction_margin"] = o.calc_effective_thickness(cfg, Hi, f["Hb"], f["SL"])[1]
+
+        for _ in range(warmup):
+            pc_step_host(calc, solve, w, cfg, sl, S, DT, hi_eff=he, geometry=geometry)
+        t0 = time.time()
+        tot, done = [0, 0, 0], 0
+        for _ in range(steps):
+            r = pc_step_host(calc, solve, w, cfg, sl, S, DT, hi_eff=he, geometry=geometry)
+            tot = [a + b for a, b in zip(tot, r)]
+            done += 1
+            if time.time() - t0 > budget_s / len(solvers):
+                break
+        el = time.time() - t0
+        runs[name] = dict(steps_per_s_sample=done / el, ms_per_step_sample=1e3 * el / done, steps=done, viscosity_its_per_step=tot[0] / done,
+                          krylov_its_velocity_per_step=tot[1] / done, krylov_its_thickness_per_step=tot[2] / done)
+        log(f"[cpu] {name}: {runs[name]}")
+    best = max(runs, key=lambda k: runs[k]["steps_per_s_sample"])
+    factor = m.nV / nv_full
+    for r in runs.values():
+        r["value_extrapolated"] = r["steps_per_s_sample"] * factor
+    return dict(value=runs[best]["value_extrapolated"], unit="velocity solves/s", cores=threads_used, kind="port", solver=best,
+                sample=(f"{runs[best]['steps']} predictor-corrector steps (after {warmup} warm-up; one viscosity iteration per step like the device run, state spun up with "
+                        f"{SPINUP_VISC} viscosity iterations) of the same MISMIP_mod DIVA config on a {m.nV}-vertex mesh, "
+                        f"oracle built -O3 -march=x86-64-v3 with OpenMP over rows / columns / ILU blocks on {threads_used} threads, zero initial guess; "
+                        f"{runs[best]['steps_per_s_sample']:.4f} steps/s measured with {best} ({runs[best]['krylov_its_velocity_per_step']:.0f} Krylov its per step), "
+                        f"scaled linearly in vertices (x {factor:.5f}) to {nv_full}; optimistic for the CPU because Krylov iterations grow with resolution"),
+                same_config=False, extrapolation_factor=factor, n_vertices_sample=int(m.nV), n_vertices_full=int(nv_full),
+                ms_per_step_sample=runs[best]["ms_per_step_sample"], solvers=runs,
+                note=("gmres_bjacobi_ilu0 is the reference's default KSP/PC (one ILU(0) block per core, as `mpiexec -n <cores>` gives); bicgstab_jacobi is the "
+                      "one-level method of the device path; the device's headline uses a multigrid preconditioner the reference does not have"))
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -287,6 +389,7 @@ def run_b200(args, rank, world, rdv, log):
     import ufe_b200 as ub
     L = ub.lib()
     local_rank = int(os.environ.get("LOCAL_RANK", rank))
+    numa_node = bind_to_gpu_numa_node(local_rank, log)
     uid = None
     if world > 1:
         uid = rdv.bcast(ub.Context.unique_id() if rank == 0 else None, 128)
@@ -318,6 +421,8 @@ def run_b200(args, rank, world, rdv, log):
         log(f"multigrid hierarchy: {mg_info}")
     io, keep_io = thickness_io(w, sl_a, w.f["Hi"][sl_a])
     ub.check(L.ufe_b200_thickness_upload(ctx.h, C.byref(io)))
+    if args.geometry:   # determine_masks / calc_grounded_fractions / calc_effective_thickness between the solves, on the device (predictor_corrector_scheme.f90:95-211)
+        ub.check(L.ufe_b200_geometry_resident(ctx.h, ub.GF_BILIN_INTERP_TAF, 0, None, None, None))
 
     # ---- device-resident leg (`value`)
     def step_resident():
@@ -351,6 +456,20 @@ def run_b200(args, rank, world, rdv, log):
     top = "mg_fine" if classes["mg_fine"][0] > classes["spmv_stiffness"][0] else "spmv_stiffness"
     spmv_ms, spmv_n = classes[top]
     log("kernel classes (ms, launches): " + ", ".join(f"{k}={v[0]:.1f}/{v[1]}" for k, v in classes.items()))
+
+    # ---- the same steps with B200_use_initial_guess_config = .true. (each Krylov solve starts from the previous solution: the line the reference has
+    # commented out, petsc_basic.f90:163).  Reported beside `value`, never as `value`.
+    cfg.ksp_initial_guess_nonzero = 1
+    k_warm = max(1, min(args.steps, 3))
+    step_resident()
+    rdv.barrier()
+    ub.check(L.ufe_b200_timer_start(ctx.h))
+    tot_w = [0, 0, 0]
+    for _ in range(k_warm):
+        tot_w = [a + b for a, b in zip(tot_w, step_resident())]
+    ub.check(L.ufe_b200_timer_stop(ctx.h, C.cast(C.byref(ms), ub.c_dp)))
+    ms_warm = rdv.allreduce_max(ms.value)
+    cfg.ksp_initial_guess_nonzero = 0
 
     # ---- end-to-end leg (`e2e`): the same step through the host-buffer entry ufe_b200_pc_step -- every input the host model owns goes up
     # from page-locked host arrays and every result (thickness, rates, the whole velocity state incl. the 3-D fields) comes back, per step
@@ -396,6 +515,17 @@ def run_b200(args, rank, world, rdv, log):
     e2e_s = rdv.allreduce_max(time.perf_counter() - t0)
     L.ufe_b200_timing_enable(ctx.h, 0)
     h2d_ms, d2h_ms = ctx.timing("h2d")[0] / k_e2e, ctx.timing("d2h")[0] / k_e2e
+    # the same call when the host asks for the 2-D results only (NULL members of the state struct are skipped): ice%u_3D_b / v_3D_b are read by the
+    # thermodynamics and the output routines, which act every dt_thermodynamics / dt_output, not every ice-dynamics step
+    for k in ("u_3D_b", "v_3D_b"):
+        setattr(st_e2e, k, None)
+    bytes_out_2d = bytes_out - A_e2e["u_3D_b"].nbytes - A_e2e["v_3D_b"].nbytes
+    step_e2e()
+    rdv.barrier()
+    t0 = time.perf_counter()
+    for _ in range(k_e2e):
+        step_e2e()
+    e2e_2d_s = rdv.allreduce_max(time.perf_counter() - t0)
     for a in registered:
         L.ufe_b200_host_unregister(a.ctypes.data_as(C.c_void_p))
     bytes_in, bytes_out = [bytes_in * k_e2e], [bytes_out * k_e2e]
@@ -442,14 +572,24 @@ def run_b200(args, rank, world, rdv, log):
                                    f"{m.nV} vertices / {m.nTri} triangles, nz={m.nz}, dt={DT} yr, physics of config_MISMIP_8km_spinup_for_scaling.cfg",
                        "n_vertices": int(m.nV), "partition": f"{world} contiguous row blocks (partition_list)",
                        "l2_policy": "inputs larger than L2 (stiffness matrix 4 GB >> 126 MB)",
-                       "krylov": krylov_desc + ", rtol 1e-4 / abstol 1e-3, initial guess = previous solution (ksp_initial_guess_nonzero=1)",
+                       "krylov": krylov_desc + ", rtol 1e-4 / abstol 1e-3, zero initial guess (the reference's KSP semantics, petsc_basic.f90:163)",
+                       "value_is": "zero initial guess; value_initial_guess_nonzero is the same step with B200_use_initial_guess_config = .true.",
+                       "time_step": ("one pass of iterate_pc_timestep in the reference's order and semantics (lagged region%ice%Hi, applied rate in Eq. 30, alter_ice_thickness after Eq. 30 / 31, "
+                                     "rates re-derived; ufe_b200_pc_reference_loop default) with choice_mask_noice = 'MISMIP_mod'" +
+                                     (", geometry / mask / sub-grid stage on the device (bilin_interp_TAF)" if args.geometry else ", masks and sub-grid fractions as uploaded")),
                        "per_step": {"viscosity_its": tot[0] / args.steps, "krylov_its_velocity": tot[1] / args.steps, "krylov_its_thickness": tot[2] / args.steps}},
             "e2e": {"value": k_e2e / e2e_s, "unit": "velocity solves/s", "h2d_bytes_per_step": bytes_in[0] // k_e2e, "d2h_bytes_per_step": bytes_out[0] // k_e2e,
                     "steps": k_e2e, "ms_per_step": 1e3 * e2e_s / k_e2e, "h2d_ms_per_step": h2d_ms, "d2h_ms_per_step": d2h_ms,
+                    "h2d_GBps": (bytes_in[0] / k_e2e) / (h2d_ms * 1e6) if h2d_ms else None, "d2h_GBps": (bytes_out[0] / k_e2e) / (d2h_ms * 1e6) if d2h_ms else None,
+                    "numa_node_bound": numa_node,
+                    "without_3D_results": {"value": k_e2e / e2e_2d_s, "ms_per_step": 1e3 * e2e_2d_s / k_e2e, "d2h_bytes_per_step": int(bytes_out_2d),
+                                           "note": "u_3D_b / v_3D_b left on the device (NULL in the state struct); the host reads them when thermodynamics or output act"},
                     "call": "ufe_b200_pc_step (host buffers; transfers overlap the thickness solves on a second stream)",
                     "state": ("solver state resident on the device (ufe_b200_set_state_resident); per step in: geometry, mass balance, flow factor, "
                               "friction inputs; out: Hi(t+dt), rates, u/v_3D_b, depth-averaged and basal velocities, basal stresses")
                     if args.e2e_state == "resident" else "whole solver state (incl. eta_3D_b) uploaded and downloaded every step"},
+            "value_initial_guess_nonzero": {"value": k_warm / (ms_warm * 1e-3), "ms_per_step": ms_warm / k_warm, "steps": k_warm,
+                                            "krylov_its_velocity": tot_w[1] / k_warm, "krylov_its_thickness": tot_w[2] / k_warm},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak if peak else None, "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
@@ -470,7 +610,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--nv", type=int, default=4_000_000, help="target number of vertices (config 3: ~4M)")
-    ap.add_argument("--cpu-nv", type=int, default=60_000, help="vertices of the bounded CPU sample")
+    ap.add_argument("--cpu-nv", type=int, default=250_000, help="vertices of the bounded CPU sample")
     ap.add_argument("--pc", default="mg", choices=["jacobi", "mg"], help="preconditioner of the stiffness-matrix solve on the device")
     ap.add_argument("--mg-nu", type=int, default=1)
     ap.add_argument("--mg-omega", type=float, default=0.8)
@@ -479,6 +619,7 @@ def main():
     ap.add_argument("--mg-fp32", type=int, default=0)
     ap.add_argument("--e2e-state", choices=["resident", "roundtrip"], default="resident",
                     help="e2e leg: solver state kept on the device between calls (default) or uploaded and downloaded every step")
+    ap.add_argument("--geometry", type=int, default=1, help="1: masks / grounded fractions / effective thickness follow the thickness on the device inside the step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     args = ap.parse_args()
@@ -496,8 +637,8 @@ def main():
         if rank != 0:
             return
         nv_full = lattice_vertex_count(args.nv)     # the b200 arm's mesh size, without generating that mesh
-        cb = run_cpu_sample(args.cpu_nv, nv_full, max(1, min(args.steps, 3)), min(args.warmup, 1), log)
-        line = {"impl": "reference", "metric": "DIVA velocity solves/s", "value": cb["value"], "unit": "velocity solves/s", "n_gpus": args.gpus,
+        cb = run_cpu_sample(args.cpu_nv, nv_full, max(1, min(args.steps, 2)), min(args.warmup, 1), log)
+        line = {"impl": "reference", "metric": "DIVA velocity solves/s", "value": cb["value"], "unit": "velocity solves/s", "n_gpus": args.gpus, "same_config": False,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / cb["value"], "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": f"configs[2] (see b200 arm), CPU sample: {cb['sample']}", "n_vertices": nv_full},

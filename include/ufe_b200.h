@@ -80,7 +80,7 @@ typedef struct ufe_b200_config {
   int32_t choice_ice_integration_method;    /* UFE_INTEGRATION_* (:355) */
   int32_t BC_H[4];                          /* :364-367 */
   int32_t ksp_type, pc_type, ksp_maxit;     /* new keys B200_KSP_type_config / B200_PC_type_config; maxit = 2000 (petsc_basic.f90:166) */
-  int32_t write_diagnostics;                /* 1: also fill the intermediate DIVA fields that only checksum()/restart read */
+  int32_t write_diagnostics;                /* 1: also fill the intermediate DIVA fields that only checksum() reads (eta_vav_a, F1/F2_3D_b of all layers every iteration) */
   int32_t ksp_initial_guess_nonzero;        /* 0 (default): zero initial guess, the reference's behaviour (petsc_basic.f90:163 is commented out);
                                                1: start the Krylov solve from the current solution (= enabling KSPSetInitialGuessNonzero) */
   int32_t stiffness_format;                 /* storage the Krylov solver streams: 0 = 2x2-blocked sliced ELL (default), 1 = the CSR matrix itself */
@@ -188,6 +188,10 @@ int ufe_b200_get_stiffness_storage_bytes(ufe_b200_handle h, long long* csr_bytes
  * coarse correction, damping, correction scaling, number of coarse levels visited twice per cycle, FP32 storage of the preconditioner's
  * matrix values (0/1), largest coarsest level solved by a dense inverse.  Negative / NaN arguments keep the current value. */
 int ufe_b200_set_mg_params(ufe_b200_handle h, int nu_pre, int nu_post, double omega, double overcorr, int w_levels, int fp32, int dense_max);
+/* Further knobs of the same preconditioner by name (new key B200_MG_<name>_config): "adaptive" (1: the level-0 correction is scaled by the
+ * residual-minimising factor instead of `overcorr`), "adaptive_max", "nu_pre" (0 = no pre-smoothing), "nu_post", "coarse_sweeps", "tail_max" /
+ * "tail_cluster" (the smallest levels as one kernel per visit, on a thread-block cluster), "fuse", "use_graph".  Unknown names are an error. */
+int ufe_b200_set_mg_option(ufe_b200_handle h, const char* name, double value);
 /* Hierarchy of the last multigrid build: number of levels, nodes per level (up to 16 entries), matrix bytes one fine-level smoothing sweep
  * streams, total matrix bytes of all coarse levels, host seconds of the one-off pattern phase. */
 int ufe_b200_get_mg_info(ufe_b200_handle h, int* n_levels, int* nodes_per_level, long long* fine_bytes, long long* coarse_bytes, double* setup_s);
@@ -279,12 +283,17 @@ int ufe_b200_calc_dHi_dt(ufe_b200_handle h, const ufe_b200_config* cfg, ufe_b200
 int ufe_b200_dHi_dt_finish(ufe_b200_handle h, const double* Hi, double* Hi_tplusdt, double dt, double* AMB,
                            double* dHi_dt);
 
-/* Device-resident time stepping: upload the thickness inputs once, then every call advances one predictor-corrector
- * step -- calc_dHi_dt (predictor), solve_stress_balance on the predicted geometry, calc_dHi_dt (corrector) -- i.e. the
- * three device phases of iterate_pc_timestep (src/UFEMISM/ice_dynamics/time_stepping/predictor_corrector_scheme.f90:118-233,
- * Robinson et al. 2020 Eqs. 30-31) without any field leaving HBM.  The host-side stages the reference runs in between
- * (alter_ice_thickness, determine_masks, calc_grounded_fractions, dt control) are not part of this path: masks and
- * sub-grid fractions stay as uploaded; only Hs follows the thickness.  Needs ufe_b200_velocity_upload first. */
+/* Device-resident time stepping: upload the thickness inputs once, then every call advances one predictor-corrector step, i.e. one pass of
+ * iterate_pc_timestep of run_ice_dynamics_model_pc (src/UFEMISM/ice_dynamics/time_stepping/predictor_corrector_scheme.f90:86-233; Robinson et al.
+ * 2020, Eqs. 30-31) without any field leaving HBM, in the reference's order:
+ *   Hi_prev, dHi_dt_nm1 := 0 under mask_noice (:88-93); effective thickness of region%ice%Hi (:107, with ufe_b200_geometry_resident);
+ *   calc_dHi_dt( region%ice%Hi, u_n) (:129); Eq. 30 on Hi_prev (:140); alter_ice_thickness (:145); dHi_dt_Hi_n_u_n re-derived from the altered
+ *   Hi_star (:152); Hs, masks and grounded fractions of Hi_star (:156-176); solve_stress_balance (:186); masks / effective thickness of Hi_prev
+ *   (:198-211); calc_dHi_dt( Hi_prev, u_np1) (:214); Eq. 31 (:226); alter_ice_thickness (:233); Hi := Hi_np1.
+ * Without ufe_b200_geometry_resident the masks and sub-grid fractions stay as uploaded and only Hs follows the thickness; without
+ * ufe_b200_alter_resident alter_ice_thickness only removes ice whose effective thickness is below cfg->Hi_min (every optional modification off).
+ * The truncation error of the finished step is ufe_b200_calc_pc_truncation_error (Hi_star_np1 from ufe_b200_pc_download); the scalar time-step
+ * rule (Eq. 33, accept / retry) stays with the caller.  Needs ufe_b200_velocity_upload first. */
 int ufe_b200_thickness_upload(ufe_b200_handle h, const ufe_b200_thickness_io* io);
 int ufe_b200_pc_step_resident(ufe_b200_handle h, const ufe_b200_config* cfg, int approximation /*0 SSA, 1 DIVA*/, double dt,
                               int* n_visc_its, int* n_Axb_its_velocity, int* n_Axb_its_thickness);
@@ -293,8 +302,10 @@ int ufe_b200_thickness_download(ufe_b200_handle h, double* Hi, double* dHi_dt, d
  * (src/UFEMISM/ice_dynamics/time_stepping/predictor_corrector_scheme.f90:118-233) in one call.
  *   in : io->Hi (= Hi_n), Hb, SL, SMB, BMB, LMB, fraction_margin, mask_noice, dHi_dt_target [, BC_prescr_*]; ice inputs except Hi/Hs (the
  *        velocity solve sees the predicted geometry); state (u_vav_b, v_vav_b, u_base_b, v_base_b, tau_bx_b, tau_by_b, eta_3D_b);
- *        dHi_dt_nm1 = pc%dHi_dt_Hnm1_unm1 (vi1:vi2); dt_prev = pc%dt_n (<= 0: first step).
- *   out: io->Hi_tplusdt (= Hi_np1, Eq. 31), io->dHi_dt / divQ / AMB of the corrector, dHi_dt_nm1 = pc%dHi_dt_Hn_un, every non-NULL state field.
+ *        dHi_dt_nm1 = pc%dHi_dt_Hi_nm1_u_nm1 = region%ice%dHi_dt (vi1:vi2); dt_prev = pc%dt_n (<= 0: first step).  io->Hi is Hi_prev; region%ice%Hi, where
+ *        it differs, is tracked by the library or given by ufe_b200_pc_set_model_thickness (see ufe_b200_pc_reference_loop).
+ *   out: io->Hi_tplusdt (= pc%Hi_np1 after alter_ice_thickness), io->dHi_dt / divQ / AMB of the corrector's calc_dHi_dt, dHi_dt_nm1 = the rate the next
+ *        step's Eq. 30 takes (the applied rate (Hi_np1 - Hi_prev) / dt), every non-NULL state field.
  * Transfers the next phase does not depend on run on a second stream: the ice inputs and the 3-D state go up while the predictor runs, the
  * velocity state comes back while the corrector runs. */
 int ufe_b200_pc_step(ufe_b200_handle h, const ufe_b200_config* cfg, int approximation /*0 SSA, 1 DIVA*/, double dt, double dt_prev,
@@ -305,18 +316,32 @@ int ufe_b200_pc_step(ufe_b200_handle h, const ufe_b200_config* cfg, int approxim
  * longer copied to the device, and `state` only selects which results are copied back (NULL members are skipped).  Call with 0 after the
  * host changed the state itself (e.g. remapping to a new mesh). */
 int ufe_b200_set_state_resident(ufe_b200_handle h, int on);
-/* on = 1: the one-call time steps follow run_ice_dynamics_model_pc inside the reference's time loop in the two places where that loop departs from
- * Robinson et al. (2020), Eq. 30 as printed (both visible in the checksum log of integrated_test_Halfar_dome_small; tests/test_reference_halfar_log.py):
+/* on = 1 (the DEFAULT): the one-call time steps follow run_ice_dynamics_model_pc inside the reference's time loop in the two places where that loop
+ * departs from Robinson et al. (2020), Eq. 30 as printed (both visible in the checksum log of integrated_test_Halfar_dome_small;
+ * tests/test_reference_halfar_log.py):
  *   - the predictor's calc_dHi_dt (and the effective thickness before it) sees region%ice%Hi, which run_ice_dynamics_model left at the thickness
  *     interpolated at the last action time (src/UFEMISM/ice_dynamics/ice_dynamics_main.f90:115-121), while Eq. 30 / 31 add to Hi_prev
  *     (time_stepping/predictor_corrector_scheme.f90:129 against :140).  The library keeps that field on the device: after a step n -> n+1 it is
  *     (1 - w) Hi_n + w Hi_np1 with w = wt_next_of_last_action, the interpolation weight of the last action time before t_np1 (0 when no other sub-model
- *     acted in between); before the first step it equals the uploaded Hi;
+ *     acted in between: region%ice%Hi is then one whole step behind); before the first step it equals the uploaded Hi.  A caller that holds
+ *     region%ice%Hi itself hands it over with ufe_b200_pc_set_model_thickness before the step instead;
  *   - pc%dHi_dt_Hi_nm1_u_nm1 is region%ice%dHi_dt, the applied rate (Hi_np1 - Hi_n) / dt of the previous step (ice_dynamics_main.f90:140 ->
- *     predictor_corrector_scheme.f90:109), not the previous predictor rate; ufe_b200_pc_step then returns that rate in dHi_dt_nm1.
- * on = 0 (default): one thickness, previous predictor rate.  Callable before every step to set w.  The switch belongs to the resident time-step state, of which
- * there is one per process (one rank <-> one GPU); ufe_b200_thickness_upload re-initialises the lagged thickness from the uploaded Hi.  Written at the end of round 1: compiled, not yet run on a GPU. */
+ *     predictor_corrector_scheme.f90:109), not the previous predictor rate; ufe_b200_pc_step returns that rate in dHi_dt_nm1.
+ * on = 0: Eq. 30 as printed -- one thickness, previous predictor rate.  Callable before every step to set w.  The state belongs to the handle and
+ * is released with the mesh; ufe_b200_thickness_upload re-initialises the lagged thickness from the uploaded Hi. */
 int ufe_b200_pc_reference_loop(ufe_b200_handle h, int on, double wt_next_of_last_action);
+/* region%ice%Hi (vi1:vi2) as the host model holds it, for the predictor of the next step (reference-loop mode; see above) */
+int ufe_b200_pc_set_model_thickness(ufe_b200_handle h, const double* Hi_model);
+/* alter_ice_thickness inside the one-call steps (after Eq. 30 and after Eq. 31; predictor_corrector_scheme.f90:145, 233) with the caller's C% settings:
+ * prm as for ufe_b200_alter_ice_thickness (below), time = region%time, refgeo_Hi / refgeo_Hb = refgeo_PD%Hi / %Hb and ice%Ti_hom (vi1:vi2; kept on the
+ * device, may be NULL on later calls that only advance `time` or change prm).  The masks it reads are those of the model geometry at that point of the
+ * loop (region%ice%Hi for the predictor, Hi_prev for the corrector), formed on the device.  prm = NULL switches back to the minimal form. */
+struct ufe_b200_alter_params;
+int ufe_b200_alter_resident(ufe_b200_handle h, const struct ufe_b200_alter_params* prm, double time, const double* refgeo_Hi, const double* refgeo_Hb,
+                            const double* Ti_hom);
+/* fields of the last one-call step that the host model keeps in type_ice_pc / type_ice_model (all (vi1:vi2), NULL = skip): pc%Hi_star_np1,
+ * pc%dHi_dt_Hi_n_u_n (re-derived, :152), the rate the next Eq. 30 will use, and region%ice%Hi as the library tracks it */
+int ufe_b200_pc_download(ufe_b200_handle h, double* Hi_star_np1, double* dHi_dt_Hi_n_u_n, double* dHi_dt_nm1_next, double* Hi_model);
 
 /* ---- SIA (config 4) ------------------------------------------------------------------------------ */
 /* Replaces solve_SIA( mesh, ice, SIA) (src/UFEMISM/ice_dynamics/conservation_of_momentum/SIA/SIA_main.f90:65-158), the analytical SIA
@@ -333,8 +358,8 @@ int ufe_b200_solve_SIA(ufe_b200_handle h, const ufe_b200_config* cfg, double SIA
  * C%choice_hybrid_SIASSA_scheme ('add' | 'add_SIA_reduced', only read for SIA/SSA).  The solver results are the ones on the device: for SIA/SSA
  * call ufe_b200_solve_SIA first (with du_dz_3D_a, dv_dz_3D_a if the strain rates are wanted), then ufe_b200_solve_SSA.  Afterwards the device's
  * u_3D_b, v_3D_b ARE ice%u_3D_b, ice%v_3D_b, so ufe_b200_calc_secondary_velocities( h, NULL, NULL, ...) and ufe_b200_calc_vertical_velocities
- * continue from them as calc_secondary_velocities / calc_vertical_velocities do in the reference (:167-170).  NULL outputs are skipped; the
- * horizontal strain rates need the solve to have run with cfg->write_diagnostics = 1. */
+ * continue from them as calc_secondary_velocities / calc_vertical_velocities do in the reference (:167-170).  NULL outputs are skipped.  The strain
+ * rates are those of the last viscosity iteration of the solve, whatever cfg->write_diagnostics was. */
 enum { UFE_APPROX_SSA = 0, UFE_APPROX_DIVA = 1, UFE_APPROX_SIA = 2, UFE_APPROX_SIASSA = 3 };
 enum { UFE_HYBRID_ADD = 0, UFE_HYBRID_ADD_SIA_REDUCED = 1 };
 typedef struct ufe_b200_ice_velocities {

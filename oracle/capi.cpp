@@ -2,6 +2,8 @@
 #include <cstring>
 #include <memory>
 
+#include <omp.h>
+
 #include "../include/ufe_b200.h"
 #include "oracle.hpp"
 
@@ -62,11 +64,16 @@ void orc_spmv(int m, int n, const int* ptr, const int* ind, const double* val, c
   spmv(A, x, y);
 }
 
-// ksp: 0 = BiCGStab + Jacobi (the CUDA algorithm), 1 = GMRES(30) + ILU(0) (the reference's PETSc default)
+// ksp: 0 = BiCGStab + Jacobi (the CUDA algorithm), 1 = GMRES(30) + ILU(0) (the reference's PETSc default on one rank), 2 = GMRES(30) + block Jacobi of
+// ILU(0) blocks (the default on several ranks; orc_set_bjacobi_blocks, default one block per OpenMP thread)
+void orc_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }   // (torch.distributed.run exports OMP_NUM_THREADS=1 to its children)
+int orc_max_threads() { return omp_get_max_threads(); }
+void orc_set_bjacobi_blocks(int n) { set_bjacobi_blocks(n); }
+int orc_bjacobi_blocks() { return bjacobi_blocks(); }
 int orc_ksp_solve(int m, const int* ptr, const int* ind, const double* val, const double* b, double* x, double rtol,
                   double abstol, int maxit, int ksp, int* its) {
   Csr A = borrow_csr(m, m, ptr, ind, val);
-  return ksp == 1 ? ksp_gmres_ilu0(A, b, x, rtol, abstol, maxit, 30, its) : ksp_bicgstab_jacobi(A, b, x, rtol, abstol, maxit, its);
+  return ksp_solve(ksp, A, b, x, rtol, abstol, maxit, its);
 }
 
 void* orc_mesh_create(const ufe_b200_mesh_desc* d) {

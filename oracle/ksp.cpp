@@ -15,6 +15,8 @@
 #include <cmath>
 #include <cstring>
 
+#include <omp.h>
+
 #include "oracle.hpp"
 
 namespace orc {
@@ -99,21 +101,6 @@ namespace {
 // canonical CSR (0-based, sorted columns, duplicates summed) as an assembled AIJ matrix holds it
 struct Aij { int n; std::vector<int> ptr, ind, diag; std::vector<double> val; };
 
-void to_aij(const Csr& A, Aij& B) {
-  B.n = A.m; B.ptr.assign(A.m + 1, 0);
-  std::vector<std::pair<int, double>> row;
-  for (int i = 1; i <= A.m; ++i) {
-    row.clear();
-    for (int k = A.ptr[i - 1]; k <= A.ptr[i] - 1; ++k) row.push_back({A.ind[k - 1] - 1, A.val[k - 1]});
-    std::stable_sort(row.begin(), row.end(), [](auto& a, auto& b) { return a.first < b.first; });
-    for (size_t k = 0; k < row.size(); ++k) {
-      if (k > 0 && row[k].first == row[k - 1].first) B.val.back() += row[k].second;
-      else { B.ind.push_back(row[k].first); B.val.push_back(row[k].second); }
-    }
-    B.ptr[i] = (int)B.ind.size();
-  }
-}
-
 // ILU(0), natural ordering, in place (row-wise IKJ); zero pivots are an error, as in PETSc
 bool ilu0(Aij& F) {
   const int n = F.n;
@@ -151,44 +138,116 @@ void ilu_solve(const Aij& F, const double* r, double* z) {
     z[i] = s / F.val[F.diag[i]];
   }
 }
+
+// PCBJACOBI with one ILU(0) block per rank -- PETSc's default preconditioner on more than one MPI rank: rank r owns the rows partition_list gives it
+// (mpi_distributed_memory.f90:47-73; petsc_basic.f90:494 hands PETSc exactly those row blocks) and factors the diagonal block of its rows, i.e. the
+// entries whose column lies in the same range; everything outside the block is dropped from the preconditioner.  nblocks = 1 is plain ILU(0).
+struct BlockIlu {
+  std::vector<Aij> F;
+  std::vector<int> r0;   // first row (0-based) of every block, size nblocks + 1
+};
+
+bool block_ilu0(const Csr& A, int nblocks, BlockIlu& B) {
+  const int n = A.m;
+  if (n <= 2 * nblocks) nblocks = 1;            // partition_list: rank 0 owns everything
+  B.F.assign(nblocks, Aij()); B.r0.assign(nblocks + 1, 0);
+  for (int r = 0; r < nblocks; ++r) {
+    const int rem = n % nblocks, slice = n / nblocks;
+    B.r0[r] = slice * r + std::min(r, rem);
+  }
+  B.r0[nblocks] = n;
+  int bad = 0;
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : bad)
+  for (int r = 0; r < nblocks; ++r) {
+    const int lo = B.r0[r], hi = B.r0[r + 1];
+    Aij& F = B.F[r];
+    F.n = hi - lo; F.ptr.assign(F.n + 1, 0);
+    std::vector<std::pair<int, double>> row;
+    for (int i = lo; i < hi; ++i) {
+      row.clear();
+      for (int k = A.ptr[i]; k <= A.ptr[i + 1] - 1; ++k) {
+        const int j = A.ind[k - 1] - 1;
+        if (j >= lo && j < hi) row.push_back({j - lo, A.val[k - 1]});
+      }
+      std::stable_sort(row.begin(), row.end(), [](auto& a, auto& b) { return a.first < b.first; });
+      for (size_t k = 0; k < row.size(); ++k) {
+        if (k > 0 && row[k].first == row[k - 1].first) F.val.back() += row[k].second;
+        else { F.ind.push_back(row[k].first); F.val.push_back(row[k].second); }
+      }
+      F.ptr[i - lo + 1] = (int)F.ind.size();
+    }
+    if (!ilu0(F)) bad += 1;
+  }
+  return bad == 0;
+}
+
+void block_ilu_solve(const BlockIlu& B, const double* r, double* z) {
+  const int nb = (int)B.F.size();
+#pragma omp parallel for schedule(dynamic, 1)
+  for (int b = 0; b < nb; ++b) ilu_solve(B.F[b], r + B.r0[b], z + B.r0[b]);
+}
 }  // namespace
 
 int ksp_gmres_ilu0(const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int restart, int* its, bool use_guess) {
+  return ksp_gmres_bjacobi_ilu0(A, 1, b, x, rtol, abstol, maxit, restart, its, use_guess);
+}
+
+static int g_bjacobi_blocks = 0;   // 0: one block per OpenMP thread (= one per MPI rank of `mpiexec -n <cores>`)
+void set_bjacobi_blocks(int n) { g_bjacobi_blocks = n; }
+int bjacobi_blocks() { return g_bjacobi_blocks > 0 ? g_bjacobi_blocks : omp_get_max_threads(); }
+
+int ksp_solve(int ksp_type, const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int* its, bool use_guess) {
+  if (ksp_type == KSP_gmres_ilu0) return ksp_gmres_ilu0(A, b, x, rtol, abstol, maxit, 30, its, use_guess);
+  if (ksp_type == KSP_gmres_bjacobi_ilu0) return ksp_gmres_bjacobi_ilu0(A, bjacobi_blocks(), b, x, rtol, abstol, maxit, 30, its, use_guess);
+  return ksp_bicgstab_jacobi(A, b, x, rtol, abstol, maxit, its, use_guess);
+}
+
+int ksp_gmres_bjacobi_ilu0(const Csr& A, int nblocks, const double* b, double* x, double rtol, double abstol, int maxit, int restart, int* its,
+                           bool use_guess) {
   const size_t n = A.m;
-  Aij F;
-  to_aij(A, F);
-  if (!ilu0(F)) return 3;
+  BlockIlu F;
+  if (!block_ilu0(A, std::max(1, nblocks), F)) return 3;
   const int m = restart;
   std::vector<std::vector<double>> Vk(m + 1, std::vector<double>(n));
   std::vector<double> H((size_t)(m + 1) * m, 0.0), cs(m), sn(m), g(m + 1), w(n), tmp(n), y(m);
   if (!use_guess) for (size_t i = 0; i < n; ++i) x[i] = 0.0;
   *its = 0;
-  ilu_solve(F, b, w.data());
+  block_ilu_solve(F, b, w.data());
   double ttol = std::max(rtol * std::sqrt(dot(w.data(), w.data(), n)), abstol);
   int total = 0;
   while (true) {
     // preconditioned residual z = B (b - A x)
     spmv(A, x, tmp.data());
+#pragma omp parallel for schedule(static)
     for (size_t i = 0; i < n; ++i) tmp[i] = b[i] - tmp[i];
-    ilu_solve(F, tmp.data(), Vk[0].data());
+    block_ilu_solve(F, tmp.data(), Vk[0].data());
     double beta = std::sqrt(dot(Vk[0].data(), Vk[0].data(), n));
     if (beta <= ttol || total >= maxit) { *its = total; return 0; }
-    for (size_t i = 0; i < n; ++i) Vk[0][i] /= beta;
+    { double* v0 = Vk[0].data();
+#pragma omp parallel for schedule(static)
+      for (size_t i = 0; i < n; ++i) v0[i] /= beta; }
     std::fill(g.begin(), g.end(), 0.0);
     g[0] = beta;
     int k = 0;
     bool done = false;
     for (; k < m && total < maxit; ++k) {
       spmv(A, Vk[k].data(), tmp.data());
-      ilu_solve(F, tmp.data(), w.data());
+      block_ilu_solve(F, tmp.data(), w.data());
       for (int j = 0; j <= k; ++j) {  // modified Gram-Schmidt
-        double h = dot(w.data(), Vk[j].data(), n);
+        const double* vj = Vk[j].data();
+        double h = dot(w.data(), vj, n);
         H[(size_t)j * m + k] = h;
-        for (size_t i = 0; i < n; ++i) w[i] -= h * Vk[j][i];
+        double* ww = w.data();
+#pragma omp parallel for schedule(static)
+        for (size_t i = 0; i < n; ++i) ww[i] -= h * vj[i];
       }
       double hn = std::sqrt(dot(w.data(), w.data(), n));
       H[(size_t)(k + 1) * m + k] = hn;
-      if (hn != 0.0) for (size_t i = 0; i < n; ++i) Vk[k + 1][i] = w[i] / hn;
+      if (hn != 0.0) {
+        double* vn = Vk[k + 1].data(); const double* ww = w.data();
+#pragma omp parallel for schedule(static)
+        for (size_t i = 0; i < n; ++i) vn[i] = ww[i] / hn;
+      }
       for (int j = 0; j < k; ++j) {  // apply previous Givens rotations
         double t = cs[j] * H[(size_t)j * m + k] + sn[j] * H[(size_t)(j + 1) * m + k];
         H[(size_t)(j + 1) * m + k] = -sn[j] * H[(size_t)j * m + k] + cs[j] * H[(size_t)(j + 1) * m + k];
@@ -207,7 +266,11 @@ int ksp_gmres_ilu0(const Csr& A, const double* b, double* x, double rtol, double
       for (int j = i + 1; j < k; ++j) s -= H[(size_t)i * m + j] * y[j];
       y[i] = s / H[(size_t)i * m + i];
     }
-    for (int j = 0; j < k; ++j) for (size_t i = 0; i < n; ++i) x[i] += y[j] * Vk[j][i];
+    for (int j = 0; j < k; ++j) {
+      const double yj = y[j]; const double* vj = Vk[j].data();
+#pragma omp parallel for schedule(static)
+      for (size_t i = 0; i < n; ++i) x[i] += yj * vj[i];
+    }
     if (done || total >= maxit) { *its = total; return 0; }
   }
 }

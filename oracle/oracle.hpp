@@ -61,7 +61,7 @@ void calc_all_matrix_operators(const MeshView& mesh, Operators& ops);
 enum SlidingLaw { SLID_no_sliding = 0, SLID_Weertman = 1, SLID_Coulomb = 2, SLID_Budd = 3, SLID_Tsai2015 = 4,
                   SLID_Schoof2005 = 5, SLID_ZoetIverson = 6, SLID_idealised_SSA_icestream = 7 };
 enum BC { BC_infinite = 0, BC_zero = 1, BC_periodic_ISMIP_HOM = 2, BC_infinite_SSA_icestream = 3 };
-enum KspType { KSP_bicgstab_jacobi = 0, KSP_gmres_ilu0 = 1 };
+enum KspType { KSP_bicgstab_jacobi = 0, KSP_gmres_ilu0 = 1, KSP_gmres_bjacobi_ilu0 = 2 };
 
 struct Config {
   // viscosity iteration (…type_and_namelist.f90:300-312)
@@ -98,6 +98,12 @@ struct Config {
 // guess, left preconditioning, convergence on ||B r||_2 <= max(rtol ||B b||_2, abstol), <= maxit its.
 int ksp_bicgstab_jacobi(const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int* its, bool use_guess = false);
 int ksp_gmres_ilu0(const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int restart, int* its, bool use_guess = false);
+// the same with PETSc's default PC on `nblocks` MPI ranks: block Jacobi, one ILU(0) per rank's row block (partition_list)
+void set_bjacobi_blocks(int n);   // 0 = one block per OpenMP thread
+int bjacobi_blocks();
+int ksp_solve(int ksp_type, const Csr& A, const double* b, double* x, double rtol, double abstol, int maxit, int* its, bool use_guess = false);
+int ksp_gmres_bjacobi_ilu0(const Csr& A, int nblocks, const double* b, double* x, double rtol, double abstol, int maxit, int restart, int* its,
+                           bool use_guess = false);
 
 // --- linearised SSA/DIVA (solve_linearised_SSA_DIVA_infinite_slab.f90) --------------------------------
 void assemble_SSA_DIVA(const MeshView& mesh, const Operators& ops, const Config& C,

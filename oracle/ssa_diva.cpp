@@ -12,6 +12,9 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
+
+#include <omp.h>
 
 #include "oracle.hpp"
 
@@ -86,12 +89,23 @@ void assemble_SSA_DIVA(const MeshView& mesh, const Operators& ops, const Config&
                        const int* BC_mask, const double* BC_u, const double* BC_v,
                        Csr& A, std::vector<double>& bb, const double* u_b_prev, const double* v_b_prev) {
   const int nTri = mesh.nTri, R = 2 * nTri;
-  std::vector<int> ti_copy(mesh.nC_mem); std::vector<double> wti_copy(mesh.nC_mem);
   const Csr& Mx = ops.M[OP2_ddx_b_b]; const Csr& My = ops.M[OP2_ddy_b_b];
   const Csr& Mxx = ops.M[OP2_d2dx2_b_b]; const Csr& Mxy = ops.M[OP2_d2dxdy_b_b]; const Csr& Myy = ops.M[OP2_d2dy2_b_b];
-  A.init(R, R, Mx.nnz() * 4);
   bb.assign(R, 0.0);
-  for (int row = 1; row <= R; ++row) {
+  // Like the reference, where every MPI rank appends the rows of its own block (partition_list) to its own CSR object: one block of rows per OpenMP
+  // thread, each appended in ascending row order, the blocks concatenated in rank order.  Entry order and values do not depend on the thread count.
+  const int nblk = std::max(1, std::min(omp_get_max_threads(), R / 64));
+  std::vector<std::vector<int>> b_len(nblk), b_ind(nblk); std::vector<std::vector<double>> b_val(nblk);
+  std::vector<int> r_lo(nblk + 1);
+  for (int b = 0; b <= nblk; ++b) r_lo[b] = 1 + (int)((long long)R * b / nblk);
+#pragma omp parallel for schedule(static, 1)
+  for (int blk = 0; blk < nblk; ++blk) {
+  std::vector<int> ti_copy(mesh.nC_mem); std::vector<double> wti_copy(mesh.nC_mem);
+  struct Local { std::vector<int>& len; std::vector<int>& ind; std::vector<double>& val; int row0;
+                 void add(int i, int j, double v) { ind.push_back(j); val.push_back(v); ++len[i - row0]; } } A{b_len[blk], b_ind[blk], b_val[blk], r_lo[blk]};
+  A.len.assign(r_lo[blk + 1] - r_lo[blk], 0);
+  A.ind.reserve((size_t)(r_lo[blk + 1] - r_lo[blk]) * 22); A.val.reserve((size_t)(r_lo[blk + 1] - r_lo[blk]) * 22);
+  for (int row = r_lo[blk]; row < r_lo[blk + 1]; ++row) {
     // n2tiuv: row = 2(ti-1)+uv (mesh_translation_tables.f90:190-198)
     const int ti = (row + 1) / 2, uv = (row % 2 == 1) ? 1 : 2;
     if (BC_mask && BC_mask[ti - 1] == 1) {
@@ -166,15 +180,27 @@ void assemble_SSA_DIVA(const MeshView& mesh, const Operators& ops, const Config&
       bb[row - 1] = C.do_include_SSADIVA_crossterms ? -tau : -tau / N;
     }
   }
-  A.finalise();
+  }
+  // concatenate (ptr as add_entry_CSR_dist + finalise_matrix_CSR_dist leave it: 1-based running offsets)
+  size_t nnz = 0;
+  for (int b = 0; b < nblk; ++b) nnz += b_ind[b].size();
+  A.init(R, R, 0);
+  A.ind.resize(nnz); A.val.resize(nnz);
+  size_t off = 0;
+  for (int b = 0; b < nblk; ++b) {
+    int run = (int)off + 1;
+    for (int r = r_lo[b]; r < r_lo[b + 1]; ++r) { run += b_len[b][r - r_lo[b]]; A.ptr[r] = run; }
+    std::memcpy(A.ind.data() + off, b_ind[b].data(), sizeof(int) * b_ind[b].size());
+    std::memcpy(A.val.data() + off, b_val[b].data(), sizeof(double) * b_val[b].size());
+    off += b_ind[b].size();
+  }
 }
 
 namespace {
 
 int linear_solve(const Config& C, const Csr& A, const double* b, double* x, double rtol, double abstol, int* its) {
   const bool g = C.ksp_initial_guess_nonzero != 0;
-  if (C.ksp_type == KSP_gmres_ilu0) return ksp_gmres_ilu0(A, b, x, rtol, abstol, C.ksp_maxit, 30, its, g);
-  return ksp_bicgstab_jacobi(A, b, x, rtol, abstol, C.ksp_maxit, its, g);
+  return ksp_solve(C.ksp_type, A, b, x, rtol, abstol, C.ksp_maxit, its, g);
 }
 
 // solve_SSA_DIVA_linearised (solve_linearised_SSA_DIVA_infinite_slab.f90:23-178)
@@ -224,6 +250,7 @@ void sliding_law(const MeshView& mesh, const Config& C, const IceInputs& ice, co
       tauc[vi - 1] = found ? mn : C.Hi_min * C.ice_density * C.grav;
     }
   }
+#pragma omp parallel for schedule(static)
   for (int v = 0; v < nV; ++v) {
     const double uabs = std::sqrt(C.slid_delta_v * C.slid_delta_v + u_a[v] * u_a[v] + v_a[v] * v_a[v]);
     double b = 0.0;
@@ -308,7 +335,8 @@ int solve_DIVA(const MeshView& mesh, const Operators& ops, const Config& C, cons
   double L2_uv = 1e9, relax = C.visc_it_relax, eps0 = C.Glens_flow_law_epsilon_sq_0;
   int nit_diverg = 0, it = 0;
   const double n_glen = C.Glens_flow_law_exponent;
-  std::vector<double> dz_b((size_t)nTri * nz), dz2_b((size_t)nTri * nz), u_base_a(nV), v_base_a(nV), prof(nz), integ(nz);
+  std::vector<double> dz_b((size_t)nTri * nz), dz2_b((size_t)nTri * nz), u_base_a(nV), v_base_a(nV);
+  if (nz > 64) return 5;
   bool converged = false;
   while (!converged) {
     ++it;
@@ -318,6 +346,7 @@ int solve_DIVA(const MeshView& mesh, const Operators& ops, const Config& C, cons
     spmv(ops.M[OP_ddx_b_a], D.v_vav_b.data(), D.dv_dx_a.data());
     spmv(ops.M[OP_ddy_b_a], D.v_vav_b.data(), D.dv_dy_a.data());
     // calc_vertical_shear_strain_rates (DIVA_solver_infinite_slab.f90:235-273)
+#pragma omp parallel for collapse(2) schedule(static)
     for (int k = 0; k < nz; ++k)
       for (int t = 0; t < nTri; ++t) {
         const double e = std::max(C.visc_eff_min, D.eta_3D_b[(size_t)k * nTri + t]);
@@ -329,6 +358,7 @@ int solve_DIVA(const MeshView& mesh, const Operators& ops, const Config& C, cons
     // calc_effective_viscosity (:275-351)
     const double A_min = 1e-18;
     const double eta_max = 0.5 * std::pow(A_min, -1.0 / n_glen) * std::pow(eps0, (1.0 - n_glen) / (2.0 * n_glen));
+#pragma omp parallel for collapse(2) schedule(static)
     for (int k = 0; k < nz; ++k)
       for (int v = 0; v < nV; ++v) {
         const size_t i = (size_t)k * nV + v;
@@ -339,6 +369,7 @@ int solve_DIVA(const MeshView& mesh, const Operators& ops, const Config& C, cons
         D.eta_3D_a[i] = std::min(std::max(eta, C.visc_eff_min), eta_max);
       }
     spmv_3D(ops.M[OP_map_a_b], D.eta_3D_a.data(), D.eta_3D_b.data(), nz);
+#pragma omp parallel for schedule(static)
     for (int v = 0; v < nV; ++v) {
       D.eta_vav_a[v] = vertical_average(zeta, &D.eta_3D_a[v], nz, nV);
       D.N_a[v] = D.eta_vav_a[v] * std::max((double)0.1f, ice.Hi[v]);  // max( 0.1, Hi): default-real literal (:341)
@@ -347,8 +378,10 @@ int solve_DIVA(const MeshView& mesh, const Operators& ops, const Config& C, cons
     spmv(ops.M[OP_ddx_a_b], D.N_a.data(), D.dN_dx_b.data());
     spmv(ops.M[OP_ddy_a_b], D.N_a.data(), D.dN_dy_b.data());
     // calc_F_integrals (:353-395)
+#pragma omp parallel for schedule(static)
     for (int v = 0; v < nV; ++v) {
       const double Hc = -std::max(0.1, ice.Hi[v]);
+      double prof[64], integ[64];   // nz <= 64
       for (int pw = 1; pw <= 2; ++pw) {
         for (int k = 0; k < nz; ++k) prof[k] = ((pw == 1) ? zeta[k] : zeta[k] * zeta[k]) / D.eta_3D_a[(size_t)k * nV + v];
         integ[nz - 1] = 0.0;
@@ -363,6 +396,7 @@ int solve_DIVA(const MeshView& mesh, const Operators& ops, const Config& C, cons
     spmv(ops.M[OP_map_b_a], D.u_base_b.data(), u_base_a.data());
     spmv(ops.M[OP_map_b_a], D.v_base_b.data(), v_base_a.data());
     sliding_law(mesh, C, ice, u_base_a.data(), v_base_a.data(), D.basal_friction_coefficient_a.data());
+#pragma omp parallel for schedule(static)
     for (int v = 0; v < nV; ++v) {
       const double b = D.basal_friction_coefficient_a[v];
       D.beta_eff_a[v] = (C.choice_sliding_law == SLID_no_sliding) ? 1.0 / D.F2_3D_a[v] : b / (1.0 + b * D.F2_3D_a[v]);
@@ -379,6 +413,7 @@ int solve_DIVA(const MeshView& mesh, const Operators& ops, const Config& C, cons
     *n_Axb_its += its;
     velocity_limits_relax(C, nTri, D.u_vav_b.data(), D.v_vav_b.data(), D.u_b_prev.data(), D.v_b_prev.data(), relax);
     // calc_basal_velocities (:487-523), calc_basal_shear_stress (:459-485)
+#pragma omp parallel for schedule(static)
     for (int t = 0; t < nTri; ++t) {
       if (C.choice_sliding_law == SLID_no_sliding) { D.u_base_b[t] = 0.0; D.v_base_b[t] = 0.0; }
       else {
@@ -398,6 +433,7 @@ int solve_DIVA(const MeshView& mesh, const Operators& ops, const Config& C, cons
     if (max_visc_its_override >= 0 ? it >= nit : it > nit) break;
   }
   // calc_3D_velocities (:525-568)
+#pragma omp parallel for collapse(2) schedule(static)
   for (int k = 0; k < nz; ++k)
     for (int t = 0; t < nTri; ++t) {
       const size_t i = (size_t)k * nTri + t;

@@ -164,9 +164,7 @@ int calc_dHi_dt(const MeshView& mesh, const Config& C, ThicknessIO& io, double* 
     for (int vi = 1; vi <= nV; ++vi) if (io.mask_noice[vi - 1]) { row_to_identity(AA, vi); bb[vi - 1] = 0.0; }
     const bool g = C.ksp_initial_guess_nonzero != 0;
     if (g) for (int v = 0; v < nV; ++v) io.Hi_tplusdt[v] = ex.Hi_new[v];
-    int rc = (C.ksp_type == KSP_gmres_ilu0)
-                 ? ksp_gmres_ilu0(AA, bb.data(), io.Hi_tplusdt, C.dHi_PETSc_rtol, C.dHi_PETSc_abstol, C.ksp_maxit, 30, n_Axb_its, g)
-                 : ksp_bicgstab_jacobi(AA, bb.data(), io.Hi_tplusdt, C.dHi_PETSc_rtol, C.dHi_PETSc_abstol, C.ksp_maxit, n_Axb_its, g);
+    int rc = ksp_solve(C.ksp_type, AA, bb.data(), io.Hi_tplusdt, C.dHi_PETSc_rtol, C.dHi_PETSc_abstol, C.ksp_maxit, n_Axb_its, g);
     if (rc != 0) return rc;
     for (int v = 0; v < nV; ++v) { io.dHi_dt[v] = (io.Hi_tplusdt[v] - io.Hi[v]) / dts; io.AMB[v] = io.dHi_dt[v] - (io.Hi_tplusdt[v] - io.Hi[v]) / dts; }
   }

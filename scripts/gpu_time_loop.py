@@ -4,8 +4,7 @@ iteration with the oracle's loop and with the reference's checksum log.
 
     gpurun -- 'python scripts/gpu_time_loop.py > gpurun_out/time_loop.log 2>&1'
 
-Written at the end of round 1 without GPU time left to run it: it is the gate for the wide-seam change DESIGN.md section 8 describes, and is meant to be promoted
-to a `-m gpu` test once it has run green.  The host loop is the same object as in the CPU tests; only the backend differs.
+tests/test_gpu_time_loop.py runs the three parts as `-m gpu` tests.  The host loop is the same object as in the CPU tests; only the backend differs.
 """
 import ctypes as C
 import json
@@ -101,8 +100,7 @@ def one_call_mismip_mod(cpu):
     the step in this experiment, so the sequence is known beforehand); compared with the CPU loop model at the end"""
     sys.path.insert(0, ROOT)
     import bench
-    w = mismip_mod_small_workload()
-    w.f["mask_noice"] = wl.mask_noice(w.mesh, "MISMIP_mod")
+    w = mismip_mod_workload()
     m, cfg, f, L = w.mesh, w.cfg, w.f, ub.lib()
     cdf, cdf_b = M.bedrock_cdfs(m)
     dHb = np.zeros(m.nV)
@@ -138,12 +136,12 @@ def one_call_mismip_mod(cpu):
     relu = np.abs(state["u_vav_b"].max() / cpu.u.max() - 1.0)
     print(f"[MISMIP_mod small, one call per step] viscosity iterations {n_visc}")
     print(f"[MISMIP_mod small, one call per step] final thickness against the CPU loop model: relative L2 {rel:.3e}; max u_vav_b relative {relu:.3e}")
-    return rel < 1e-4 and relu < 1e-3
+    return bool(rel < 1e-6 and relu < 1e-5)
 
 
-def main():
+def halfar_narrow_seam():
+    """Halfar dome, SIA: every call of the 100-year loop through the C ABI"""
     ok = True
-    # Halfar dome, SIA
     cpu = H.HalfarRun(H.halfar_40km_workload())
     Hi_cpu = cpu.run()
     w = H.halfar_40km_workload()
@@ -160,20 +158,31 @@ def main():
     ratio = np.array(gpu.log)[2:55, 3] / ref_tau[2:55]
     print(f"[Halfar 40 km]   device / reference log, max tau_np1 of iterations 3-55: {ratio.min():.3f} .. {ratio.max():.3f}, median {np.median(ratio):.3f}")
     ok &= 0.6 < ratio.min() and ratio.max() < 1.3
+    return bool(ok)
 
-    # MISMIP_mod, DIVA
-    def workload():
-        w = mismip_mod_small_workload()
-        w.f["mask_noice"] = wl.mask_noice(w.mesh, "MISMIP_mod")
-        return w
-    cpu = M.MismipModRun(workload())
+
+def mismip_mod_workload():
+    w = mismip_mod_small_workload()
+    w.f["mask_noice"] = wl.mask_noice(w.mesh, "MISMIP_mod")
+    return w
+
+
+def mismip_mod_cpu_loop():
+    cpu = M.MismipModRun(mismip_mod_workload())
     Hi_cpu = cpu.run()
-    w = workload()
+    return cpu, Hi_cpu
+
+
+def mismip_mod_narrow_seam(cpu, Hi_cpu):
+    """MISMIP_mod, DIVA: every call of the 100-year loop through the C ABI"""
+    ok = True
+    w = mismip_mod_workload()
     ctx = ub.Context(device=0)
     try:
         ctx.mesh_create(w.mesh); ctx.calc_matrix_operators()
         gpu = M.MismipModRun.__new__(M.MismipModRun)
         H.HalfarRun.__init__(gpu, w)
+        gpu.ksp = 0            # oracle_lib.KSP_BICGSTAB_JACOBI: the loop then calls solve_velocity without the oracle-only keyword
         on_device(gpu, ctx)
         gpu.cdf, gpu.cdf_b = M.bedrock_cdfs(w.mesh); gpu.dHb = np.zeros(w.mesh.nV)
         gpu.st, gpu.state = ub.alloc_velocity_state(w.mesh.nV, w.mesh.nTri, w.mesh.nz)
@@ -195,6 +204,13 @@ def main():
         ok &= np.abs(growth - 1).max() < 0.025 and np.abs(log[:, 2] - ref_H).max() < 0.2
     else:
         ok = False
+    return bool(ok)
+
+
+def main():
+    ok = halfar_narrow_seam()
+    cpu, Hi_cpu = mismip_mod_cpu_loop()
+    ok &= mismip_mod_narrow_seam(cpu, Hi_cpu)
     ok &= one_call_mismip_mod(cpu)
     print("TIME LOOP PARITY", "OK" if ok else "FAILED")
     sys.exit(0 if ok else 1)

@@ -24,7 +24,7 @@ approx = w.approximation
 ctx = ub.Context(device=0)
 ctx.mesh_create(m); ctx.calc_matrix_operators()
 cfg.visc_it_nit = nvisc - 1; cfg.visc_it_norm_dUV_tol = 1e-30; cfg.write_diagnostics = 0
-cfg.ksp_initial_guess_nonzero = 1
+cfg.ksp_initial_guess_nonzero = int(os.environ.get("PROBE_GUESS", "0"))
 ice = w.ice_inputs()
 L = ub.lib()
 print(f"mesh nV={m.nV} nTri={m.nTri}", flush=True)
@@ -36,8 +36,10 @@ for tok in spec.split(";"):
     if tok == "jacobi":
         SETTINGS.append(("jacobi", None))
     else:
-        nu, wl_, oc, om, fp = tok.split(",")
-        SETTINGS.append((f"mg nu={nu} w={wl_} oc={oc} om={om} fp32={fp}", dict(nu_pre=int(nu), nu_post=int(nu), w_levels=int(wl_), overcorr=float(oc), omega=float(om), fp32=int(fp))))
+        f = tok.split(",")
+        nu, wl_, oc, om, fp = f[:5]
+        opts = dict(kv.split("=") for kv in f[5:])          # further knobs by name, e.g. adaptive=1,nu_pre=0,tail_max=12000,tail_cluster=8
+        SETTINGS.append((f"mg nu={nu} w={wl_} oc={oc} om={om} fp32={fp} {opts}", dict(nu_pre=int(nu), nu_post=int(nu), w_levels=int(wl_), overcorr=float(oc), omega=float(om), fp32=int(fp), _opts=opts)))
 timing = int(os.environ.get("PROBE_TIMING", "1"))
 
 ref = None
@@ -46,7 +48,14 @@ for name, prm in SETTINGS:
     ub.check(L.ufe_b200_velocity_upload(ctx.h, C.byref(ice), C.byref(st)))
     cfg.pc_type = ub.PC_JACOBI if prm is None else ub.PC_MG
     if prm:
+        prm = dict(prm)
+        opts = prm.pop("_opts", {})
         ctx.set_mg_params(**prm)
+        for k0 in ("adaptive", "tail_max", "tail_cluster"):
+            ctx.set_mg_option(k0, 0)
+        ctx.set_mg_option("nu_pre", prm["nu_pre"])
+        for k0, v0 in opts.items():
+            ctx.set_mg_option(k0, float(v0))
     L.ufe_b200_timing_reset(ctx.h); L.ufe_b200_timing_enable(ctx.h, timing)
     a, b = C.c_int(), C.c_int()
     l0 = ctx.kernel_launches()

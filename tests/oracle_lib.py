@@ -11,7 +11,7 @@ import ufe_b200 as ub
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 _LIB = None
-KSP_BICGSTAB_JACOBI, KSP_GMRES_ILU0 = 0, 1
+KSP_BICGSTAB_JACOBI, KSP_GMRES_ILU0, KSP_GMRES_BJACOBI_ILU0 = 0, 1, 2   # 2: PETSc's default on several ranks (set_bjacobi_blocks)
 
 
 def lib():
@@ -21,6 +21,7 @@ def lib():
         dp, ip = ub.c_dp, ub.c_ip
         L.orc_spmv.argtypes = [C.c_int, C.c_int, ip, ip, dp, dp, dp]
         L.orc_ksp_solve.argtypes = [C.c_int, ip, ip, dp, dp, dp, C.c_double, C.c_double, C.c_int, C.c_int, C.POINTER(C.c_int)]
+        L.orc_set_bjacobi_blocks.argtypes = [C.c_int]
         L.orc_mesh_create.restype = C.c_void_p
         L.orc_mesh_create.argtypes = [C.POINTER(ub.MeshDesc)]
         L.orc_mesh_destroy.argtypes = [C.c_void_p]
@@ -58,6 +59,11 @@ def lib():
         L.orc_calc_and_apply_spill_over_flux.argtypes = [C.c_void_p, C.POINTER(ub.Masks), dp, dp, dp, C.c_double, dp, dp]
         _LIB = L
     return _LIB
+
+
+def set_bjacobi_blocks(n):
+    """number of ILU(0) blocks (= MPI ranks of the reference run) of KSP_GMRES_BJACOBI_ILU0; 0 = one per OpenMP thread"""
+    lib().orc_set_bjacobi_blocks(n)
 
 
 def spmv(m, n, ptr, ind, val, x):

@@ -16,7 +16,22 @@ def test_cpu_sample_runs_the_step_and_scales_to_the_full_workload():
     assert 2000 < r["n_vertices_sample"] < 4500 and r["ms_per_step_sample"] > 0.0
     # value = sample rate scaled linearly in vertices to the full workload
     assert abs(r["value"] - (1e3 / r["ms_per_step_sample"]) * r["n_vertices_sample"] / 4005450) < 1e-12 * r["value"] + 1e-15
-    assert "viscosity its" in r["sample"] and "Krylov its" in r["sample"]
+    assert "viscosity iteration" in r["sample"] and "Krylov its" in r["sample"]
+    # both Krylov settings were timed: the reference's default (GMRES(30) + block Jacobi / ILU(0), one block per core) and the device's one-level method
+    assert set(r["solvers"]) == {"bicgstab_jacobi", "gmres_bjacobi_ilu0"} and r["solver"] in r["solvers"] and r["same_config"] is False
+    assert abs(r["extrapolation_factor"] - r["n_vertices_sample"] / 4005450) < 1e-15
+    for v in r["solvers"].values():
+        assert v["viscosity_its_per_step"] == 1.0 and v["krylov_its_velocity_per_step"] > 10
+
+
+def test_cpu_sample_uses_all_cores_under_torchrun():
+    """torch.distributed.run exports OMP_NUM_THREADS=1 to its children: the CPU arm must not inherit it (round-1 SCALE ratios were void because it did)"""
+    code = ("import os, sys; sys.path.insert(0, %r); import bench; r = bench.run_cpu_sample(1500, 4005450, 1, 0, solvers=('bicgstab_jacobi',)); "
+            "print('CORES', r['cores'], len(os.sched_getaffinity(0)))" % ROOT)
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600, env=dict(os.environ, OMP_NUM_THREADS="1"))
+    assert p.returncode == 0, p.stderr[-2000:]
+    used, avail = [int(x) for x in p.stdout.split("CORES")[1].split()[:2]]
+    assert used == avail
 
 
 def test_reference_arm_prints_the_contract_line():

@@ -43,8 +43,11 @@ def _spin_up(ctx, w):
     return ice, st, A
 
 
-@pytest.mark.parametrize("pc", [ub.PC_JACOBI, ub.PC_MG])
-def test_resident_pc_steps_match_oracle_sequence(pc):
+@pytest.mark.parametrize("pc,ref_loop,w_lag", [(ub.PC_JACOBI, 1, 0.0), (ub.PC_MG, 1, 0.0), (ub.PC_MG, 1, 0.6), (ub.PC_MG, 0, 0.0)])
+def test_resident_pc_steps_match_oracle_sequence(pc, ref_loop, w_lag):
+    """the one-call step against the reference's loop body driven on the host with the oracle, for the reference's loop semantics (the default: lagged
+    region%ice%Hi one whole step behind, or interpolated with the weight of the last action time) and for Eq. 30 as printed"""
+    NSTEP = 3
     w = _workload()
     m, cfg = w.mesh, w.cfg
     cfg.pc_type = pc
@@ -55,11 +58,15 @@ def test_resident_pc_steps_match_oracle_sequence(pc):
     io, keep = bench.thickness_io(w, slice(None), w.f["Hi"].copy())
     ub.check(L.ufe_b200_thickness_upload(ctx.h, C.byref(io)))
     nv, na, nt = C.c_int(), C.c_int(), C.c_int()
-    for _ in range(2):
+    if not (ref_loop == 1 and w_lag == 0.0):            # (1, 0.0) is the default and is not set explicitly
+        ub.check(L.ufe_b200_pc_reference_loop(ctx.h, ref_loop, w_lag))
+    for _ in range(NSTEP):
         ub.check(L.ufe_b200_pc_step_resident(ctx.h, C.byref(cfg), 1, DT, C.byref(nv), C.byref(na), C.byref(nt)))
     Hi_g = np.zeros(m.nV); dH_g = np.zeros(m.nV)
     ub.check(L.ufe_b200_thickness_download(ctx.h, ub.dp(Hi_g), ub.dp(dH_g), None))
     ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
+    pc_g = {k: np.zeros(m.nV) for k in ("Hi_star", "d_n", "d_next", "model")}
+    ub.check(L.ufe_b200_pc_download(ctx.h, ub.dp(pc_g["Hi_star"]), ub.dp(pc_g["d_n"]), ub.dp(pc_g["d_next"]), ub.dp(pc_g["model"])))
     u_g = A["u_vav_b"].copy()
     ctx.close()
 
@@ -85,10 +92,17 @@ def test_resident_pc_steps_match_oracle_sequence(pc):
     rc, _a, _b = o.solve_velocity(cfg2, 1, w2.ice_inputs(), st2)
     assert rc == 0
     S = dict(Hi=w2.f["Hi"].copy(), dHdt_nm1=np.zeros(m.nV), dt_n=DT, u=A2["u_vav_b"], v=A2["v_vav_b"])
-    for _ in range(2):
-        bench.pc_step_host(calc, solve, w2, cfg2, slice(None), S, DT)
+    he = lambda Hi: o.calc_effective_thickness(cfg2, Hi, w2.f["Hb"], w2.f["SL"])[0]
+    for _ in range(NSTEP):
+        bench.pc_step_host(calc, solve, w2, cfg2, slice(None), S, DT, hi_eff=he, reference_loop=bool(ref_loop), w_lag=w_lag)
     assert rel_l2(Hi_g, S["Hi"]) < 1e-9, rel_l2(Hi_g, S["Hi"])
     assert rel_l2(u_g, A2["u_vav_b"]) < 1e-6, rel_l2(u_g, A2["u_vav_b"])
+    # what the host model keeps in type_ice_pc: pc%Hi_star_np1, the re-derived pc%dHi_dt_Hi_n_u_n, the next pc%dHi_dt_Hi_nm1_u_nm1, region%ice%Hi
+    assert rel_l2(pc_g["Hi_star"], S["Hi_star"]) < 1e-9 and (not ref_loop or rel_l2(pc_g["model"], S["Hi_model"]) < 1e-9)
+    scale = np.abs(S["dHdt_nm1"]).max()
+    assert np.abs(pc_g["d_n"] - S["dHdt_n"]).max() < 1e-7 * scale and np.abs(pc_g["d_next"] - S["dHdt_nm1"]).max() < 1e-7 * scale
+    if ref_loop and w_lag == 0.0:
+        assert rel_l2(S["Hi_model"], S["Hi"]) > 1e-6          # region%ice%Hi really is one step behind
 
 
 def test_host_buffer_pc_step_equals_resident():
@@ -231,8 +245,9 @@ def test_resident_pc_steps_with_the_geometry_stage_on_the_device():
     assert rc == 0
     S = dict(Hi=w2.f["Hi"].copy(), dHdt_nm1=np.zeros(m.nV), dt_n=DTL, u=A2["u_vav_b"], v=A2["v_vav_b"])
     fgb0 = w2.f["fraction_gr_b"].copy()
+    he = lambda Hi: o.calc_effective_thickness(cfg2, Hi, w2.f["Hb"], w2.f["SL"])[0]
     for _ in range(NSTEP):
-        bench.pc_step_host(calc, solve, w2, cfg2, slice(None), S, DTL, geometry=geometry)
+        bench.pc_step_host(calc, solve, w2, cfg2, slice(None), S, DTL, geometry=geometry, hi_eff=he)
     assert rel_l2(w2.f["fraction_gr_b"], fgb0) > 1e-3          # the stage did change what the velocity solve sees
     assert rel_l2(Hi_g, S["Hi"]) < 1e-9, rel_l2(Hi_g, S["Hi"])
     assert rel_l2(u_g, A2["u_vav_b"]) < 1e-6, rel_l2(u_g, A2["u_vav_b"])

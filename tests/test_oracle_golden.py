@@ -138,3 +138,29 @@ def test_analytic_solutions():
     assert u0.value > uy.value > 0 and abs(uy.value - um.value) < 1e-9 * abs(uy.value)
     L.orc_Schoof2006_icestream(1e-18, 3.0, 2000.0, -0.0003, 150e3, 1.0, 3.1e5, cast(uy), cast(t))
     assert uy.value == 0.0
+
+
+def test_block_jacobi_ilu0_is_the_multi_rank_default():
+    # PETSc's default PC on n ranks is block Jacobi with one ILU(0) per rank's row block: one block = plain ILU(0) (same iterates), more blocks = a weaker
+    # preconditioner that converges to the same solution
+    m = uh.HostMesh.synthetic(-1e6, 1e6, -1e6, 1e6, 5e4)
+    o = ol.OracleMesh(m)
+    pxx, ixx, vxx, _, _ = o.get_operator(ub.OP["M2_d2dx2_b_b"])
+    _, _, vyy, _, _ = o.get_operator(ub.OP["M2_d2dy2_b_b"])
+    val = vxx + vyy
+    b = np.full(m.nTri, 1e-9)
+    for ti in np.nonzero(m.TriBI > 0)[0]:
+        k1, k2 = pxx[ti] - 1, pxx[ti + 1] - 1
+        val[k1:k2] = np.where(ixx[k1:k2] == ti + 1, 1.0, 0.0)
+        b[ti] = 0.0
+    f1, its1, rc = ol.ksp_solve(pxx, ixx, val, b, 1e-10, 1e-30, ksp=ol.KSP_GMRES_ILU0)
+    assert rc == 0
+    try:
+        ol.set_bjacobi_blocks(1)
+        f2, its2, rc = ol.ksp_solve(pxx, ixx, val, b, 1e-10, 1e-30, ksp=ol.KSP_GMRES_BJACOBI_ILU0)
+        assert rc == 0 and its2 == its1 and np.abs(f1 - f2).max() < 1e-12 * np.abs(f1).max()   # (OpenMP reductions: not bitwise)
+        ol.set_bjacobi_blocks(4)
+        f4, its4, rc = ol.ksp_solve(pxx, ixx, val, b, 1e-10, 1e-30, ksp=ol.KSP_GMRES_BJACOBI_ILU0)
+        assert rc == 0 and its4 > its1 and np.abs(f4 - f1).max() < 1e-7 * np.abs(f1).max(), (its1, its4)
+    finally:
+        ol.set_bjacobi_blocks(0)

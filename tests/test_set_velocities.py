@@ -142,3 +142,34 @@ def test_gpu_set_velocities_ssa_and_diva():
         assert np.abs(out2["u_3D_b"]).max() > 0
     finally:
         ctx.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("approx", [ub.APPROX_DIVA, ub.APPROX_SSA])
+def test_gpu_set_velocities_without_the_checksum_log(approx):
+    """C%do_write_checksum_log is .false. by default (model_configuration_type_and_namelist.f90:48), so the Fortran shim passes write_diagnostics = 0; the
+    fan-out after the solve (set_ice_velocities_to_DIVA / SSA_results) must still find every strain rate, identical to the run with the log switched on"""
+    w = wl.mismip_mod(5.0e4)
+    m, cfg = w.mesh, w.cfg
+    cfg.visc_it_nit = 2
+    outs = []
+    ctx = ub.Context(device=0)
+    try:
+        ctx.mesh_create(m); ctx.calc_matrix_operators()
+        for diag in (1, 0):
+            cfg.write_diagnostics = diag
+            nv, na = C.c_int(), C.c_int()
+            ice = w.ice_inputs()
+            st, g = ub.alloc_velocity_state(m.nV, m.nTri, m.nz)
+            solve = ub.lib().ufe_b200_solve_DIVA if approx == ub.APPROX_DIVA else ub.lib().ufe_b200_solve_SSA
+            ub.check(solve(ctx.h, C.byref(cfg), C.byref(ice), C.byref(st), C.byref(nv), C.byref(na), None, None, None))
+            s, out = ub.alloc_ice_velocities(m.nV, m.nTri, m.nz, fill=np.nan)
+            ub.check(ub.lib().ufe_b200_set_ice_velocities(ctx.h, approx, 0, C.byref(s)))
+            outs.append(out)
+    finally:
+        ctx.close()
+    for k in ub.ICE_VELOCITY_FIELDS:
+        assert np.isfinite(outs[1][k]).all() and np.array_equal(outs[0][k], outs[1][k]), k
+    assert np.abs(outs[1]["du_dx_3D"]).max() > 0
+    if approx == ub.APPROX_DIVA:
+        assert np.abs(outs[1]["du_dz_3D"]).max() > 0

@@ -105,6 +105,8 @@ struct MgParams {
   int nu_pre = 1, nu_post = 1;   // block-Jacobi sweeps before / after the coarse-grid correction
   double omega = 0.8;            // damping
   double overcorr = 1.5;         // scaling of the coarse-grid correction (plain aggregation under-corrects; > 1.7 is not robust)
+  int adaptive = 0;              // 1: on level 0 the correction is scaled by the factor that minimises the residual instead of `overcorr` (mg.cu: k_mg_aq)
+  double adaptive_max = 4.0;     // ... kept inside [0, adaptive_max]
   int w_levels = 3;              // coarse levels 1..w_levels are visited twice per cycle (W-cycle on top, V-cycle below)
   int dense_max = 128;           // coarsest level: at most this many nodes -> dense inverse; otherwise `coarse_sweeps` sweeps
   int coarse_sweeps = 8;
@@ -112,6 +114,7 @@ struct MgParams {
                                  // Measured slower than graph nodes on B200 at 4 M vertices (0.82 vs 0.72 ms per cycle with 2048, 1.98 ms with
                                  // 16384: one SM's L2 bandwidth and latency cost more than ~80 kernel boundaries save;
                                  // profiles/r01_mg_probe_tail.log), so off by default; UFE_B200_MG_TAIL=<nodes> enables it
+  int tail_cluster = 0;          // > 0: the tail kernel runs as one thread-block cluster of this many CTAs (cluster barrier between operations)
   int max_levels = 12;
   int fuse = 0;                  // 1: fuse neighbouring operations on the coarse levels (3 launches per level visit instead of 5); measured no
                                  // gain on B200 (the fused kernels have longer dependent-load chains: profiles/r01_mg_probe_fuse.log)
@@ -120,6 +123,9 @@ struct MgParams {
   int use_graph = 1;             // coarse-grid correction (levels >= 1): 0 plain launches, 1 one CUDA graph (default), 2 one persistent
                                  // cooperative kernel (measured slower than the graph on B200: profiles/r01_mg_probe_modes.log)
 };
+
+struct PcState;                      // timestep.cu
+void pc_state_free(PcState*);
 
 struct Ctx {
   int device = 0, rank = 0, nranks = 1;
@@ -144,6 +150,9 @@ struct Ctx {
   Thickness* thick = nullptr;
   Secondary* sec = nullptr;
   Geometry* geo = nullptr;
+  PcState* pc = nullptr;         // state of the predictor-corrector stepper between calls (released with the mesh)
+  cudaEvent_t t0 = nullptr, t1 = nullptr;   // ufe_b200_timer_start / _stop
+  unsigned long long bc_version = 0;        // bumped whenever the prescribed-velocity mask of the stiffness pattern changes
   int state_resident = 0;        // ufe_b200_set_state_resident: ufe_b200_pc_step keeps the solver state on the device between calls
   MgParams mg_params;
   // pinned scratch for small D2H reads

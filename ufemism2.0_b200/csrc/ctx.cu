@@ -229,6 +229,7 @@ int ufe_b200_init(int device, int rank, int nranks, const void* id128, ufe_b200_
   UFE_CHECK(e == cudaSuccess && ndev > 0, "ufe_b200_init: no CUDA device (%s); this library has no CPU fallback",
             e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
   UFE_CHECK(nranks >= 1 && rank >= 0 && rank < nranks, "ufe_b200_init: bad rank %d of %d", rank, nranks);
+  UFE_CHECK(nranks == 1 || id128 != nullptr, "ufe_b200_init: nranks > 1 needs the broadcast unique id");
   if (device < 0) device = rank % ndev;
   UFE_CUDA(cudaSetDevice(device));
   Ctx* c = new Ctx();
@@ -239,14 +240,16 @@ int ufe_b200_init(int device, int rank, int nranks, const void* id128, ufe_b200_
   UFE_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   UFE_CUDA(cudaMallocHost((void**)&c->h_pinned, 64 * sizeof(double)));
   if (nranks > 1) {
-    UFE_CHECK(id128 != nullptr, "ufe_b200_init: nranks > 1 needs the broadcast unique id");
     ncclUniqueId id;
     memcpy(&id, id128, 128);
     NcclApi* N = nccl_api();
-    if (!N) return 3;
+    if (!N) { ufe_b200_finalize(reinterpret_cast<ufe_b200_handle>(c)); return 3; }
     ncclComm_t comm;
     ncclResult_t r = N->CommInitRank(&comm, nranks, id, rank);
-    UFE_CHECK(r == ncclSuccess, "ncclCommInitRank: %s", N->GetErrorString(r));
+    if (r != ncclSuccess) {
+      ufe_b200_finalize(reinterpret_cast<ufe_b200_handle>(c));
+      UFE_CHECK(false, "ncclCommInitRank: %s", N->GetErrorString(r));
+    }
     c->nccl = comm;
   }
   *out = reinterpret_cast<ufe_b200_handle>(c);
@@ -265,6 +268,7 @@ int ufe_b200_finalize(ufe_b200_handle h) {
   for (auto& e : c->ev_pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
   if (c->nccl && nccl_api()) nccl_api()->CommDestroy((ncclComm_t)c->nccl);
   if (c->h_pinned) cudaFreeHost(c->h_pinned);
+  if (c->t0) { cudaEventDestroy(c->t0); cudaEventDestroy(c->t1); }
   if (c->copy_stream) { cudaStreamDestroy(c->copy_stream); cudaEventDestroy(c->ev_copy_a); cudaEventDestroy(c->ev_copy_b); }
   cudaStreamDestroy(c->stream);
   delete c;
@@ -282,21 +286,20 @@ int ufe_b200_timing_enable(ufe_b200_handle h, int on) {
   if (on == 1) cudaProfilerStart(); else cudaProfilerStop();
   return 0;
 }
-static cudaEvent_t g_t0 = nullptr, g_t1 = nullptr;
 int ufe_b200_timer_start(ufe_b200_handle h) {
   Ctx* c = reinterpret_cast<Ctx*>(h);
   UFE_CUDA(cudaSetDevice(c->device));
-  if (!g_t0) { UFE_CUDA(cudaEventCreate(&g_t0)); UFE_CUDA(cudaEventCreate(&g_t1)); }
-  UFE_CUDA(cudaEventRecord(g_t0, c->stream));
+  if (!c->t0) { UFE_CUDA(cudaEventCreate(&c->t0)); UFE_CUDA(cudaEventCreate(&c->t1)); }
+  UFE_CUDA(cudaEventRecord(c->t0, c->stream));
   return 0;
 }
 int ufe_b200_timer_stop(ufe_b200_handle h, double* ms) {
   Ctx* c = reinterpret_cast<Ctx*>(h);
-  UFE_CHECK(g_t0 && ms, "ufe_b200_timer_stop without ufe_b200_timer_start");
-  UFE_CUDA(cudaEventRecord(g_t1, c->stream));
-  UFE_CUDA(cudaEventSynchronize(g_t1));
+  UFE_CHECK(c->t0 && ms, "ufe_b200_timer_stop without ufe_b200_timer_start");
+  UFE_CUDA(cudaEventRecord(c->t1, c->stream));
+  UFE_CUDA(cudaEventSynchronize(c->t1));
   float f = 0.f;
-  UFE_CUDA(cudaEventElapsedTime(&f, g_t0, g_t1));
+  UFE_CUDA(cudaEventElapsedTime(&f, c->t0, c->t1));
   *ms = f;
   return 0;
 }

@@ -401,6 +401,28 @@ __global__ void k_geo_alter(int n, int off, AlterDev a, const int* __restrict__ 
   }
 }
 
+// the six mask bits alter_ice_thickness reads, from the basic mask code of the geometry the masks belong to (masks_mod.f90:63-203)
+__global__ void k_geo_alter_bits(GeoMesh m, int n, int off, const int* __restrict__ kind, int* __restrict__ bits) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const int vi = m.vi1 + (int)r;
+    const int k = kind[off + r];
+    bool nb_fl = false, nb_gr = false;
+    for (int ci = 0; ci < m.nC[vi - 1]; ++ci) {
+      const int kj = kind[m.C[(size_t)ci * m.nV + vi - 1] - m.a_lo];
+      nb_fl |= kj == 4; nb_gr |= kj == 3;
+    }
+    int b = (k == 1 ? MB_LAND : 0) | (k == 2 ? MB_OCEAN : 0) | (k == 3 ? MB_GROUNDED : 0) | (k == 4 ? MB_FLOATING : 0);
+    if (k == 3 && nb_fl) b |= MB_GL_GR;
+    if (k == 4 && nb_gr) b |= MB_GL_FL;
+    bits[off + r] = b;
+  }
+}
+// alter_ice_thickness with every optional modification switched off: what is left is the removal of very thin ice (:75-80)
+__global__ void k_geo_alter_thin(int n, int off, double Hi_min, const double* __restrict__ Hi_eff, double* __restrict__ Hi_new) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x)
+    if (Hi_eff[off + r] < Hi_min) Hi_new[off + r] = 0.0;
+}
+
 // ---- calc_and_apply_spill_over_flux (ice_thickness_safeties.f90:290-437) -------------------------------------------------------------------
 struct SpillMesh { const double *A, *D_x, *D_y, *D; };
 __device__ __forceinline__ double u_perp_of(const GeoMesh& m, const SpillMesh& g, int vi, int ci, const double* __restrict__ u_b, const double* __restrict__ v_b) {
@@ -583,6 +605,44 @@ int geometry_for_thickness(Ctx* c, const ufe_b200_config* cfg, double* Hi, const
   { UFE_LAUNCH(c, TC_COLUMN); k_geo_margin<<<grid, 128, 0, st>>>(m, na, off, Hi, G.ia[1].p); }
   UFE_TRY(halo_exchange_int(c, M.a, G.ia[1].p));
   { UFE_LAUNCH(c, TC_COLUMN); k_geo_hi_eff<<<grid, 128, 0, st>>>(m, na, off, cfg->seawater_density / cfg->ice_density, Hi, Hb, SL, G.ia[1].p, G.a[5].p, fraction_margin); }
+  UFE_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// alter_ice_thickness( mesh, ice, Hi_old, Hb, SL, Hi_new, refgeo, time) on device fields (extended a-range vectors, owned part valid on entry).
+// prm == nullptr: every optional modification off, only `Hi_eff_new < C%Hi_min -> 0` remains (the scaling configuration's settings).
+// Hi_of_masks: the thickness ice%mask_* belong to at the time of the call (region%ice%Hi of the last determine_masks).
+int geometry_alter(Ctx* c, const ufe_b200_config* cfg, const ufe_b200_alter_params* prm, double time, double* Hi_of_masks, const double* Hi_old,
+                   const double* Hb, const double* SL, const double* ref_Hi, const double* ref_Hb, const double* Ti_hom, double* Hi_new) {
+  UFE_TRY(ensure_geometry(c));
+  Mesh& M = *c->mesh; Geometry& G = *c->geo;
+  cudaStream_t st = c->stream;
+  const int na = M.a.n_loc(), off = M.a.off();
+  const GeoMesh m = geo_mesh(M);
+  const int grid = grid_for(c, na, 128, 16);
+  const double rw_ri = cfg->seawater_density / cfg->ice_density;
+  // the would-be effective thickness of Hi_new (:55)
+  UFE_TRY(halo_exchange(c, M.a, Hi_new));
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_margin<<<grid, 128, 0, st>>>(m, na, off, Hi_new, G.ia[1].p); }
+  UFE_TRY(halo_exchange_int(c, M.a, G.ia[1].p));
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_hi_eff<<<grid, 128, 0, st>>>(m, na, off, rw_ri, Hi_new, Hb, SL, G.ia[1].p, G.a[5].p, G.a[6].p); }
+  if (!prm) {
+    UFE_LAUNCH(c, TC_COLUMN);
+    k_geo_alter_thin<<<grid, 128, 0, st>>>(na, off, cfg->Hi_min, G.a[5].p, Hi_new);
+    UFE_CUDA(cudaGetLastError());
+    return 0;
+  }
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_kind<<<grid, 128, 0, st>>>(na, off, rw_ri, Hi_of_masks, Hb, SL, G.ia[0].p, nullptr); }
+  UFE_TRY(halo_exchange_int(c, M.a, G.ia[0].p));
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_alter_bits<<<grid, 128, 0, st>>>(m, na, off, G.ia[0].p, G.ia[2].p); }
+  AlterDev a;
+  a.p = *prm; a.rw_over_ri = rw_ri;
+  a.fixiness = decay_weight(time, prm->fixiness_t_start, prm->fixiness_t_end, prm->do_fixiness_before_start);
+  a.limitness = decay_weight(time, prm->limitness_t_start, prm->limitness_t_end, prm->do_limitness_before_start);
+  a.protect = prm->do_protect_grounded_mask && time <= prm->protect_grounded_mask_t_end;
+  UFE_TRY(G.flag.alloc(1));
+  UFE_CUDA(cudaMemsetAsync(G.flag.p, 0, sizeof(int), st));
+  { UFE_LAUNCH(c, TC_COLUMN); k_geo_alter<<<grid, 128, 0, st>>>(na, off, a, G.ia[2].p, Hi_old, Hb, SL, G.a[5].p, ref_Hi, ref_Hb, Ti_hom, Hi_new, G.flag.p); }
   UFE_CUDA(cudaGetLastError());
   return 0;
 }

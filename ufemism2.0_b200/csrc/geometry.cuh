@@ -14,4 +14,8 @@ int geometry_for_velocity(Ctx* c, const ufe_b200_config* cfg, double* Hi, const 
 // calc_effective_thickness for the geometry: writes fraction_margin (extended a range, owned part)
 int geometry_for_thickness(Ctx* c, const ufe_b200_config* cfg, double* Hi, const double* Hb, const double* SL, double* fraction_margin);
 
+// alter_ice_thickness on device fields (ice_thickness_safeties.f90:26-288); prm == nullptr: only the removal of ice thinner than C%Hi_min
+int geometry_alter(Ctx* c, const ufe_b200_config* cfg, const ufe_b200_alter_params* prm, double time, double* Hi_of_masks, const double* Hi_old,
+                   const double* Hb, const double* SL, const double* ref_Hi, const double* ref_Hb, const double* Ti_hom, double* Hi_new);
+
 }  // namespace ufe

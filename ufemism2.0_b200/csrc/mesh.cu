@@ -151,6 +151,7 @@ int ufe_b200_mesh_destroy(ufe_b200_handle h) {
   thickness_free(c->thick); c->thick = nullptr;
   secondary_free(c->sec); c->sec = nullptr;
   geometry_free(c->geo); c->geo = nullptr;
+  pc_state_free(c->pc); c->pc = nullptr;
   delete c->mesh; c->mesh = nullptr;
   return 0;
 }

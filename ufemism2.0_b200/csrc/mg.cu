@@ -479,6 +479,65 @@ __device__ __forceinline__ void d_mg_axpy(int n2, typename MgPtr<R>::cd a, typen
 __global__ void k_mg_axpy(int n2, const double* __restrict__ a, double* __restrict__ y) { d_mg_axpy(n2, a, y, blockIdx.x, gridDim.x); }
 
 // coarse block values: sum of the fine blocks listed for the slot
+// ---- level 0: the coarse-grid correction with its own step length --------------------------------------------------------------------------
+// Plain aggregation under-corrects, and the factor that repairs it depends on the problem (1.5 is safe everywhere, 2.0 - 2.3 halves the Krylov count
+// on the 4 M-vertex MISMIP_mod mesh but diverges on MISMIP+; profiles/r01_mg_probe_4M_b.log).  MgParams::adaptive replaces the fixed factor on level 0
+// by the one that minimises the residual of the corrected iterate: with r = b - A x (the pre-smoothing residual that was restricted) and q = A (P e),
+// w = (r, q) / (q, q), x <- x + w P e, and the post-smoothing sweep x + Dw (b - A x) follows from r - w q without another pass over the matrix.
+// So the cycle still streams the level-0 matrix twice; what is new is one more vector (q) and two dot products, fused into the pass that forms q.
+__global__ void k_mg_prolong_set(int n, const int* __restrict__ agg, const double* __restrict__ ec, double* __restrict__ pe_own) {
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x)
+    reinterpret_cast<double2*>(pe_own)[t] = reinterpret_cast<const double2*>(ec)[agg[t]];
+}
+// q = A pe (owned rows), scal[0] = (r, q), scal[1] = (q, q)
+template <typename VT>
+__global__ void __launch_bounds__(kBlock) k_mg_aq(int n, const int* __restrict__ slice_ptr, const int* __restrict__ col, const VT* __restrict__ val,
+                                                  const double* __restrict__ pe_ext, const double* __restrict__ r, double* __restrict__ q,
+                                                  double* scal, double* partials, unsigned* counter) {
+  const int lane = threadIdx.x & 31;
+  const int warps_per_block = blockDim.x >> 5;
+  const int n_slices = (n + 31) >> 5;
+  const double2* __restrict__ x2 = reinterpret_cast<const double2*>(pe_ext);
+  double acc[2] = {0.0, 0.0};
+  for (int s = blockIdx.x * warps_per_block + (threadIdx.x >> 5); s < n_slices; s += gridDim.x * warps_per_block) {
+    const int t = (s << 5) + lane;
+    const int k0 = slice_ptr[s], k1 = slice_ptr[s + 1];
+    double yu = 0.0, yv = 0.0;
+    const int* __restrict__ cp = col + (size_t)k0 * 32 + lane;
+    const VT* __restrict__ vp = val + (size_t)k0 * 128 + lane;
+#pragma unroll 2
+    for (int k = k0; k < k1; ++k, cp += 32, vp += 128) {
+      const int tj = *cp;
+      const double a0 = (double)vp[0], a1 = (double)vp[32], a2 = (double)vp[64], a3 = (double)vp[96];
+      const double2 xv = x2[tj];
+      yu += a0 * xv.x + a1 * xv.y;
+      yv += a2 * xv.x + a3 * xv.y;
+    }
+    if (t < n) {
+      reinterpret_cast<double2*>(q)[t] = make_double2(yu, yv);
+      const double2 rv = reinterpret_cast<const double2*>(r)[t];
+      acc[0] += rv.x * yu + rv.y * yv;
+      acc[1] += yu * yu + yv * yv;
+    }
+  }
+  grid_sum<2>(acc, partials, counter, scal);
+}
+// out = x + w pe + Dw (r - w q);  w = (r, q) / (q, q), kept inside [0, w_max]; (q, q) = 0 (nothing to correct): w = 0
+__global__ void k_mg_mr_update(int n, int off, const double* __restrict__ x_ext, const double* __restrict__ pe_ext, const double* __restrict__ r,
+                               const double* __restrict__ q, const double* __restrict__ dblk, const double* __restrict__ scal, double w_max,
+                               double* __restrict__ out) {
+  const double rq = scal[0], qq = scal[1];
+  double w = (qq > 0.0) ? rq / qq : 0.0;
+  w = fmin(fmax(w, 0.0), w_max);
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+    const double2 xv = reinterpret_cast<const double2*>(x_ext)[off + t], pv = reinterpret_cast<const double2*>(pe_ext)[off + t];
+    const double2 rv = reinterpret_cast<const double2*>(r)[t], qv = reinterpret_cast<const double2*>(q)[t];
+    const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
+    const double ru = rv.x - w * qv.x, rw = rv.y - w * qv.y;
+    reinterpret_cast<double2*>(out)[t] = make_double2(xv.x + w * pv.x + d01.x * ru + d01.y * rw, xv.y + w * pv.y + d23.x * ru + d23.y * rw);
+  }
+}
+
 template <typename VTI, typename VTO>
 __global__ void k_mg_galerkin(long long n_cslots, const int* __restrict__ gal_ptr, const int* __restrict__ gal_src, const VTI* __restrict__ fv,
                               VTO* __restrict__ cv) {
@@ -682,6 +741,47 @@ __global__ void __launch_bounds__(kTailBlock, 1) k_mg_tail(const MgStep* __restr
     }
     __syncthreads();
   }
+}
+
+// The same step list on one thread-block CLUSTER: the CTAs of the cluster (8, or 16 with the non-portable size) share every operation, separated by
+// the cluster barrier (barrier.cluster, release / acquire at cluster scope: a few hundred nanoseconds in hardware, against ~3 us for a grid-wide
+// cooperative barrier over 148 SMs and ~4 us for a graph-node boundary).  That makes the tail worthwhile from a larger level on (MgParams::tail_max
+// ~ 10^4 nodes: level 3 of the 4 M-vertex hierarchy, 16 operations per visit, 8 visits per cycle).  Arithmetic and summation order per row are those
+// of the stand-alone kernels.
+template <typename VT>
+__global__ void __launch_bounds__(kTailBlock, 1) k_mg_tail_cluster(const MgStep* __restrict__ steps, int nsteps) {
+  cooperative_groups::cluster_group cl = cooperative_groups::this_cluster();
+  const int bid = (int)cl.block_rank(), nb = (int)cl.num_blocks();
+  __shared__ double sb[2 * 128];
+  for (int s = 0; s < nsteps; ++s) {
+    const MgStep st = steps[s];
+    switch (st.op) {
+      case MG_OP_SMOOTH0: d_mg_smooth0<false>(st.n, st.b, st.d, st.out, bid, nb); break;
+      case MG_OP_SWEEP: d_mg_sweep<VT, 0, kTailU, false>(st.n, st.off, st.ip0, st.ip1, static_cast<const VT*>(st.val), st.x, st.b, st.d, st.out, bid, nb); break;
+      case MG_OP_RESID: d_mg_sweep<VT, 1, kTailU, false>(st.n, st.off, st.ip0, st.ip1, static_cast<const VT*>(st.val), st.x, st.b, st.d, st.out, bid, nb); break;
+      case MG_OP_RESTRICT: d_mg_restrict<false>(st.n, st.ip0, st.ip1, st.x, st.out, bid, nb); break;
+      case MG_OP_PROLONG: d_mg_prolong<false>(st.n, st.ip0, st.x, st.w, st.out, bid, nb); break;
+      case MG_OP_AXPY: d_mg_axpy<false>(st.n, st.x, st.out, bid, nb); break;
+      case MG_OP_DENSE: if (bid == 0) d_mg_dense_solve<false>(st.n, static_cast<const double*>(st.val), st.b, st.out, sb); break;
+    }
+    cl.sync();
+  }
+}
+template <typename VT>
+int launch_tail_cluster(Ctx* c, int cluster, const MgStep* steps, int nsteps) {
+  static bool allowed = false;
+  if (cluster > 8 && !allowed) {
+    UFE_CUDA(cudaFuncSetAttribute(k_mg_tail_cluster<VT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    allowed = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(cluster); cfg.blockDim = dim3(kTailBlock); cfg.dynamicSmemBytes = 0; cfg.stream = c->stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  UFE_CUDA(cudaLaunchKernelEx(&cfg, k_mg_tail_cluster<VT>, steps, nsteps));
+  return 0;
 }
 
 // ---- BiCGStab pieces that differ from the Jacobi path (the preconditioner is no longer fused into the SpMV) ----------
@@ -907,7 +1007,9 @@ int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out, bool x1_ready) 
     const int which = (b == L.b.p && out == L.sol.p) ? 0 : (b == L.b2.p && out == L.sol2.p) ? 1 : -1;
     if (which >= 0) {
       UFE_LAUNCH(c, TC_MG_COARSE);
-      k_mg_tail<VT><<<1, kTailBlock, 0, st>>>(reinterpret_cast<const MgStep*>(G.tail_prog.p) + G.tail_off[which], G.tail_len[which]);
+      const MgStep* prog = reinterpret_cast<const MgStep*>(G.tail_prog.p) + G.tail_off[which];
+      if (P.tail_cluster > 1) UFE_TRY(launch_tail_cluster<VT>(c, P.tail_cluster, prog, G.tail_len[which]));
+      else k_mg_tail<VT><<<1, kTailBlock, 0, st>>>(prog, G.tail_len[which]);
       return 0;
     }
   }
@@ -928,25 +1030,47 @@ int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out, bool x1_ready) 
   }
   MgLevel& Cn = G.lv[l + 1];
   const bool split = l == 0 && G.distributed;   // level 0 is a row block: its iterates need the neighbours' halo before every matrix pass
-  if (!x1_ready) op_smooth0(c, G, l, L.n, b, L.dblk.p, xa + 2 * L.off);
-  for (int s = 1; s < P.nu_pre; ++s) {
+  // level 0 without pre-smoothing (nu_pre = 0): the iterate is zero and the right-hand side itself is the residual that gets restricted, which
+  // saves one of the cycle's two passes over the level-0 matrix
+  const bool no_pre = l == 0 && P.nu_pre == 0 && !G.rec;
+  const double* res = no_pre ? b : L.r.p;
+  if (no_pre) {
+    UFE_CUDA(cudaMemsetAsync(xa + 2 * L.off, 0, sizeof(double) * 2 * (size_t)L.n, st));
+  } else {
+    if (!x1_ready) op_smooth0(c, G, l, L.n, b, L.dblk.p, xa + 2 * L.off);
+    for (int s = 1; s < P.nu_pre; ++s) {
+      if (split) UFE_TRY(halo_exchange(c, G.rb, xa, 1, 2));
+      launch_sweep<VT, 0>(c, G, L, l, xa, b, xb + 2 * L.off);
+      std::swap(xa, xb);
+    }
     if (split) UFE_TRY(halo_exchange(c, G.rb, xa, 1, 2));
-    launch_sweep<VT, 0>(c, G, L, l, xa, b, xb + 2 * L.off);
-    std::swap(xa, xb);
+    launch_sweep<VT, 1>(c, G, L, l, xa, b, L.r.p);
   }
-  if (split) UFE_TRY(halo_exchange(c, G.rb, xa, 1, 2));
-  launch_sweep<VT, 1>(c, G, L, l, xa, b, L.r.p);
   if (split) UFE_CUDA(cudaMemsetAsync(Cn.b.p, 0, sizeof(double) * 2 * (size_t)Cn.n, st));
   // the child's first sweep rides on the restriction unless the child is solved directly or its right-hand side still needs the all-reduce
   const bool child_smooths = !(l + 1 == last && G.dense_n > 0);
   const bool fuse_down = mg_fuse(G) && !split && child_smooths && l >= 1;
-  if (fuse_down) op_restrict(c, G, l, L.nc_loc, L.mem_ptr.p, L.mem.p, L.r.p, Cn.b.p + 2 * (size_t)L.c_offset, Cn.dblk.p, Cn.xa.p + 2 * Cn.off);
-  else op_restrict(c, G, l, L.nc_loc, L.mem_ptr.p, L.mem.p, L.r.p, Cn.b.p + 2 * (size_t)L.c_offset);
+  if (fuse_down) op_restrict(c, G, l, L.nc_loc, L.mem_ptr.p, L.mem.p, res, Cn.b.p + 2 * (size_t)L.c_offset, Cn.dblk.p, Cn.xa.p + 2 * Cn.off);
+  else op_restrict(c, G, l, L.nc_loc, L.mem_ptr.p, L.mem.p, res, Cn.b.p + 2 * (size_t)L.c_offset);
   if (split) UFE_TRY(allreduce_sum_large(c, Cn.b.p, 2 * (size_t)Cn.n, false));   // every rank now holds the whole level-1 right-hand side
   if (l == 0) UFE_TRY(mg_coarse_from_fine<VT>(c, G));
   else UFE_TRY(mg_coarse_correction<VT>(c, G, l, fuse_down));
   int s0 = 0;
-  if (mg_fuse(G) && l >= 1 && P.nu_post >= 1) {   // prolongation fused into the first post-sweep (levels >= 1: off = 0, agg covers the whole level)
+  if (l == 0 && P.adaptive && P.nu_post >= 1 && !G.rec) {   // correction with the residual-minimising step length; doubles as the first post-sweep
+    UFE_TRY(G.mr_q.alloc(2 * (size_t)L.n)); UFE_TRY(G.mr_scal.alloc(2)); UFE_TRY(G.mr_partials.alloc(2 * (size_t)c->sm_count * 8));
+    if (!G.mr_counter.n) { UFE_TRY(G.mr_counter.alloc(1)); UFE_CUDA(cudaMemsetAsync(G.mr_counter.p, 0, sizeof(unsigned), st)); }
+    { UFE_LAUNCH(c, TC_MG_VEC); k_mg_prolong_set<<<grid_for(c, L.n, kBlock), kBlock, 0, st>>>(L.n, L.agg.p, Cn.sol.p, xb + 2 * L.off); }
+    if (split) UFE_TRY(halo_exchange(c, G.rb, xb, 1, 2));
+    {
+      UFE_LAUNCH(c, TC_MG_FINE);
+      const int grid = std::min(grid_for(c, (long long)L.n_slices * 32, kBlock), c->sm_count * 8);
+      k_mg_aq<VT><<<grid, kBlock, 0, st>>>(L.n, L.slice_ptr, L.col, level_values<VT>(L), xb, res, G.mr_q.p, G.mr_scal.p, G.mr_partials.p, G.mr_counter.p);
+    }
+    if (split) UFE_TRY(allreduce_sum(c, G.mr_scal.p, 2));
+    double* dst = (P.nu_post == 1) ? out : xa + 2 * L.off;
+    { UFE_LAUNCH(c, TC_MG_VEC); k_mg_mr_update<<<grid_for(c, L.n, kBlock), kBlock, 0, st>>>(L.n, L.off, xa, xb, res, G.mr_q.p, L.dblk.p, G.mr_scal.p, P.adaptive_max, dst); }
+    s0 = 1;
+  } else if (mg_fuse(G) && l >= 1 && P.nu_post >= 1) {   // prolongation fused into the first post-sweep (levels >= 1: off = 0, agg covers the whole level)
     double* dst = (P.nu_post == 1) ? out : xb + 2 * L.off;
     launch_sweep<VT, 3>(c, G, L, l, xa, b, dst, nullptr, L.agg.p, Cn.sol.p, P.overcorr);
     std::swap(xa, xb);

@@ -87,6 +87,8 @@ struct Mg {
   // the levels from tail_level down run as one single-CTA kernel per visit (mg.cu: k_mg_tail); two step lists: (b, sol) and (b2, sol2)
   int tail_level = 0, tail_off[2] = {0, 0}, tail_len[2] = {0, 0};
   DBuf<char> tail_prog;
+  DBuf<double> mr_q, mr_scal, mr_partials;   // level-0 correction with its own step length (MgParams::adaptive)
+  DBuf<unsigned> mr_counter;
   bool valid = false;
   long long gather_entries = 0;
   double setup_host_s = 0.0;

@@ -323,7 +323,7 @@ extern "C" int ufe_b200_set_ice_velocities(ufe_b200_handle h, int approximation,
   for (int q = 0; q < 4; ++q) {
     if (!h2d_out[q]) continue;
     if (approximation == UFE_APPROX_SIA) { memset(h2d_out[q], 0, sizeof(double) * (size_t)na * nz); continue; }
-    UFE_CHECK(V.have_strain_2d, "ufe_b200_set_ice_velocities: the solve did not keep its strain rates (cfg->write_diagnostics = 0)");
+    UFE_CHECK(V.have_strain_2d, "ufe_b200_set_ice_velocities: no SSA / DIVA solve has produced strain rates yet");
     UFE_TRY(layers.alloc(na_ext * nz));
     { UFE_LAUNCH(c, TC_COLUMN); k_layers_from_2D<<<grid_for(c, na, 128, 16), 128, 0, st>>>(na, M.a.off(), na_ext, nz, src2d[q], layers.p); }
     UFE_CUDA(cudaGetLastError());

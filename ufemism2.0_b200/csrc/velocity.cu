@@ -246,11 +246,12 @@ __global__ void __launch_bounds__(128, MB) k_vertex_diva(VertexArgs a, VelPar p)
     const double beta = sliding_beta(p, ub, vb, a.tauc[i], a.beta_sq[i], a.alpha_sq[i], a.neff[i], a.Vy[a.vi1 - 1 + r]);
     a.beta_a[i] = beta;
     a.beta_eff_a[i] = (p.sliding_law == UFE_SLID_NO_SLIDING) ? 1.0 / F2_surf : beta / (1.0 + beta * F2_surf);
-    if (p.diagnostics) {
-      a.du_dx[i] = du_dx; a.du_dy[i] = du_dy; a.dv_dx[i] = dv_dx; a.dv_dy[i] = dv_dy; a.eta_vav[i] = vav;
+    // DIVA%du_dx_a ... DIVA%du_dz_3D_a are results, not diagnostics: set_ice_velocities_to_DIVA_results copies them into ice%du_dx_3D ... after every
+    // solve (conservation_of_momentum_main.f90:472-511), so they are stored whatever cfg->write_diagnostics says
+    a.du_dx[i] = du_dx; a.du_dy[i] = du_dy; a.dv_dx[i] = dv_dx; a.dv_dy[i] = dv_dy;
 #pragma unroll
-      for (int k = 0; k < nz; ++k) { a.du_dz_3D[(size_t)k * a.n_ext + i] = dzu[k]; a.dv_dz_3D[(size_t)k * a.n_ext + i] = dzv[k]; }
-    }
+    for (int k = 0; k < nz; ++k) { a.du_dz_3D[(size_t)k * a.n_ext + i] = dzu[k]; a.dv_dz_3D[(size_t)k * a.n_ext + i] = dzv[k]; }
+    if (p.diagnostics) a.eta_vav[i] = vav;
   }
 }
 
@@ -271,7 +272,7 @@ __global__ void __launch_bounds__(128) k_vertex_ssa(VertexArgs a, VelPar p) {
     a.eta_vav[i] = e;
     a.N_a[i] = e * fmax(0.1, a.Hi[i]);
     a.beta_a[i] = sliding_beta(p, ua, va, a.tauc[i], a.beta_sq[i], a.alpha_sq[i], a.neff[i], a.Vy[a.vi1 - 1 + r]);
-    if (p.diagnostics) { a.du_dx[i] = du_dx; a.du_dy[i] = du_dy; a.dv_dx[i] = dv_dx; a.dv_dy[i] = dv_dy; }
+    a.du_dx[i] = du_dx; a.du_dy[i] = du_dy; a.dv_dx[i] = dv_dx; a.dv_dy[i] = dv_dy;   // SSA%du_dx_a ...: results (set_ice_velocities_to_SSA_results)
   }
 }
 
@@ -818,8 +819,6 @@ static int d2h_field(Ctx* c, double* h, const double* d_ext, const Range& r, int
   return 0;
 }
 
-static unsigned long long g_bc_version = 0;
-
 static int upload_bc(Ctx* c, const int32_t* mask, const double* bu, const double* bv) {
   Mesh& M = *c->mesh; Velocity& V = *c->vel;
   if (mask || bu || bv) {
@@ -827,10 +826,10 @@ static int upload_bc(Ctx* c, const int32_t* mask, const double* bu, const double
     UFE_TRY(h2d_field(c, V.bc_mask.p, M.b, mask)); UFE_TRY(h2d_field(c, V.bc_u.p, M.b, bu)); UFE_TRY(h2d_field(c, V.bc_v.p, M.b, bv));
     V.have_bc = true;
     V.pattern_valid = false;   // the mask may have changed; the pattern kernels are cheap compared with one solve
-    ++g_bc_version;
+    ++c->bc_version;
   } else if (V.have_bc) {
     UFE_CUDA(cudaMemsetAsync(V.bc_mask.p, 0, sizeof(int) * V.bc_mask.n, c->stream));
-    V.have_bc = false; V.pattern_valid = false; ++g_bc_version;
+    V.have_bc = false; V.pattern_valid = false; ++c->bc_version;
   }
   return 0;
 }
@@ -933,7 +932,7 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
     UFE_CUDA(cudaStreamSynchronize(st));
     return 0;
   }
-  UFE_TRY(ensure_pattern(c, p, g_bc_version));
+  UFE_TRY(ensure_pattern(c, p, c->bc_version));
   const int g_a = grid_for(c, na, 128, 16), g_b = grid_for(c, nb, 128, 16);
   const Mesh::OpGroup& gab = M.grp[Mesh::G_AB];
   const Mesh::OpGroup& gba = M.grp[Mesh::G_BA];
@@ -1060,7 +1059,7 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
   UFE_CUDA(cudaStreamSynchronize(st));
   *n_visc_its = it;
   V.last_approximation = DIVA ? UFE_APPROX_DIVA : UFE_APPROX_SSA;
-  V.have_strain_2d = p.diagnostics != 0;
+  V.have_strain_2d = true;
   if (DIVA) { V.have_dudz_3d = true; V.have_sia = false; }   // DIVA%du_dz_3D_a is part of every viscosity iteration; u_3D_b is DIVA's now
   return 0;
 }
@@ -1132,7 +1131,7 @@ int ufe_b200_solve_SSA_DIVA_linearised(ufe_b200_handle h, const ufe_b200_config*
   UFE_TRY(upload_bc(c, bm, bu, bv));
   V.uploaded = true;
   VelPar p = make_par(cfg);
-  UFE_TRY(ensure_pattern(c, p, g_bc_version));
+  UFE_TRY(ensure_pattern(c, p, c->bc_version));
   StiffArgs sa = stiff_args(c, csr_values_unneeded(c, cfg));
   const int g_b = grid_for(c, nb, 128, 16);
   { UFE_LAUNCH(c, TC_EPILOGUE); k_store_prev<<<g_b, 128, 0, st>>>(nb, M.b.off(), V.u.p, V.v.p, V.u_prev.p, V.v_prev.p); }
@@ -1191,6 +1190,30 @@ int ufe_b200_set_mg_params(ufe_b200_handle h, int nu_pre, int nu_post, double om
     G.drop_graph();                                   // the captured launch sequence depends on the cycle shape
     if (p.fp32 != old_fp32 || p.dense_max != old_dense) G.valid = false;   // storage precision / depth are fixed at build time
     else if (G.valid) { const int ug = G.p.use_graph; G.p = p; G.p.use_graph = ug; }
+  }
+  return 0;
+}
+
+int ufe_b200_set_mg_option(ufe_b200_handle h, const char* name, double value) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c != nullptr && name != nullptr, "ufe_b200_set_mg_option: NULL argument");
+  MgParams& p = c->mg_params;
+  bool rebuild = false;
+  if (!strcmp(name, "adaptive")) p.adaptive = (int)value;
+  else if (!strcmp(name, "adaptive_max")) p.adaptive_max = value;
+  else if (!strcmp(name, "tail_max")) { p.tail_max = (int)value; rebuild = true; }
+  else if (!strcmp(name, "tail_cluster")) { p.tail_cluster = (int)value; rebuild = true; }
+  else if (!strcmp(name, "coarse_sweeps")) p.coarse_sweeps = (int)value;
+  else if (!strcmp(name, "fuse")) p.fuse = (int)value;
+  else if (!strcmp(name, "use_graph")) p.use_graph = (int)value;
+  else if (!strcmp(name, "nu_pre")) p.nu_pre = (int)value;          // 0 allowed here: no pre-smoothing (the right-hand side itself is restricted)
+  else if (!strcmp(name, "nu_post")) p.nu_post = (int)value;
+  else UFE_CHECK(false, "ufe_b200_set_mg_option: unknown option '%s'", name);
+  if (c->vel) {
+    Mg& G = c->vel->mg;
+    G.drop_graph();
+    if (rebuild) G.valid = false;
+    else if (G.valid) G.p = p;
   }
   return 0;
 }

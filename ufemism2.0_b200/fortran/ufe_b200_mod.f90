@@ -157,6 +157,15 @@ module ufe_b200_mod
       integer(c_int) :: ierr
     end function
 
+    ! further multigrid knobs by name (C%B200_MG_<name>_config); name = a null-terminated c_char string
+    function c_ufe_b200_set_mg_option( h, name, value) bind(C, name='ufe_b200_set_mg_option') result( ierr)
+      import :: c_int, c_double, c_ptr, c_char
+      type(c_ptr), value :: h
+      character(kind=c_char), dimension(*), intent(in) :: name
+      real(c_double), value :: value
+      integer(c_int) :: ierr
+    end function
+
     ! solve_DIVA_infinite_slab / solve_SSA on the model's arrays (DIVA_solver_infinite_slab.f90:52, SSA_main.f90:88); ice, state = c_loc of
     ! ufe_b200_ice_inputs / ufe_b200_velocity_state filled with c_loc of the model arrays; BC_prescr_* = c_null_ptr when absent
     function c_ufe_b200_solve_DIVA( h, cfg, ice, state, n_visc_its, n_Axb_its, BC_prescr_mask_b, BC_prescr_u_b, BC_prescr_v_b) &
@@ -437,6 +446,29 @@ module ufe_b200_mod
       type(c_ptr), value :: h
       integer(c_int), value :: on
       real(c_double), value :: wt_next_of_last_action
+      integer(c_int) :: ierr
+    end function
+
+    ! region%ice%Hi as the host holds it, for the predictor of the next one-call step (predictor_corrector_scheme.f90:129)
+    function c_ufe_b200_pc_set_model_thickness( h, Hi_model) bind(C, name='ufe_b200_pc_set_model_thickness') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h, Hi_model
+      integer(c_int) :: ierr
+    end function
+
+    ! alter_ice_thickness inside the one-call steps (predictor_corrector_scheme.f90:145, 233); prm = c_loc of a ufe_b200_alter_params or c_null_ptr
+    function c_ufe_b200_alter_resident( h, prm, time, refgeo_Hi, refgeo_Hb, Ti_hom) bind(C, name='ufe_b200_alter_resident') result( ierr)
+      import :: c_int, c_ptr, c_double
+      type(c_ptr), value :: h, prm
+      real(c_double), value :: time
+      type(c_ptr), value :: refgeo_Hi, refgeo_Hb, Ti_hom
+      integer(c_int) :: ierr
+    end function
+
+    ! pc%Hi_star_np1, pc%dHi_dt_Hi_n_u_n, the next pc%dHi_dt_Hi_nm1_u_nm1 and region%ice%Hi of the last one-call step (c_null_ptr = skip)
+    function c_ufe_b200_pc_download( h, Hi_star_np1, dHi_dt_Hi_n_u_n, dHi_dt_nm1_next, Hi_model) bind(C, name='ufe_b200_pc_download') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h, Hi_star_np1, dHi_dt_Hi_n_u_n, dHi_dt_nm1_next, Hi_model
       integer(c_int) :: ierr
     end function
 

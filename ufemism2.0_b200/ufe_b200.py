@@ -253,6 +253,7 @@ def lib():
     L.ufe_b200_get_stiffness.argtypes = [H, c_ip, c_ip, c_dp, c_dp]
     L.ufe_b200_get_stiffness_storage_bytes.argtypes = [H, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
     L.ufe_b200_set_mg_params.argtypes = [H, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, C.c_int, C.c_int]
+    L.ufe_b200_set_mg_option.argtypes = [H, C.c_char_p, C.c_double]
     L.ufe_b200_get_mg_info.argtypes = [H, C.POINTER(C.c_int), c_ip, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), c_dp]
     L.ufe_b200_mg_host_transfer.argtypes = [C.c_int, C.c_int, c_ip, c_ip, C.POINTER(C.c_int), C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
     L.ufe_b200_mg_host_transfer_get.argtypes = [c_ip] * 5
@@ -279,6 +280,9 @@ def lib():
     L.ufe_b200_set_ice_velocities.argtypes = [H, C.c_int, C.c_int, C.POINTER(IceVelocities)]
     L.ufe_b200_set_state_resident.argtypes = [H, C.c_int]
     L.ufe_b200_pc_reference_loop.argtypes = [H, C.c_int, C.c_double]
+    L.ufe_b200_pc_set_model_thickness.argtypes = [H, c_dp]
+    L.ufe_b200_alter_resident.argtypes = [H, C.POINTER(AlterParams), C.c_double, c_dp, c_dp, c_dp]
+    L.ufe_b200_pc_download.argtypes = [H, c_dp, c_dp, c_dp, c_dp]
     PC = C.POINTER(Config)
     L.ufe_b200_determine_masks.argtypes = [H, PC, c_dp, c_dp, c_dp, C.POINTER(Masks)]
     L.ufe_b200_calc_effective_thickness.argtypes = [H, PC, c_dp, c_dp, c_dp, c_dp, c_dp]
@@ -311,7 +315,7 @@ ABI_SYMBOLS = [
     "ufe_b200_set_mg_params", "ufe_b200_get_mg_info", "ufe_b200_mg_host_transfer", "ufe_b200_mg_host_transfer_get", "ufe_b200_mg_host_transfer_parts", "ufe_b200_mg_host_transfer_parts_get",
     "ufe_b200_solve_DIVA", "ufe_b200_solve_SSA", "ufe_b200_velocity_upload", "ufe_b200_velocity_solve_resident",
     "ufe_b200_velocity_download", "ufe_b200_thickness_upload", "ufe_b200_pc_step_resident", "ufe_b200_pc_step",
-    "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA", "ufe_b200_calc_pc_truncation_error", "ufe_b200_apply_grounded_fractions_to_bed_roughness", "ufe_b200_set_ice_velocities", "ufe_b200_calc_secondary_velocities", "ufe_b200_calc_vertical_velocities", "ufe_b200_set_state_resident", "ufe_b200_pc_reference_loop", "ufe_b200_determine_masks", "ufe_b200_calc_effective_thickness",
+    "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA", "ufe_b200_calc_pc_truncation_error", "ufe_b200_apply_grounded_fractions_to_bed_roughness", "ufe_b200_set_ice_velocities", "ufe_b200_calc_secondary_velocities", "ufe_b200_calc_vertical_velocities", "ufe_b200_set_state_resident", "ufe_b200_pc_reference_loop", "ufe_b200_set_mg_option", "ufe_b200_pc_set_model_thickness", "ufe_b200_alter_resident", "ufe_b200_pc_download", "ufe_b200_determine_masks", "ufe_b200_calc_effective_thickness",
                "ufe_b200_calc_grounded_fractions", "ufe_b200_calc_critical_timestep_adv", "ufe_b200_calc_critical_timestep_SIA", "ufe_b200_alter_params_defaults", "ufe_b200_geometry_resident", "ufe_b200_alter_ice_thickness",
                "ufe_b200_calc_and_apply_spill_over_flux",
     "ufe_b200_timing_enable", "ufe_b200_timing_get", "ufe_b200_timing_reset", "ufe_b200_timer_start", "ufe_b200_timer_stop",
@@ -408,6 +412,9 @@ class Context:
 
     def set_mg_params(self, nu_pre=-1, nu_post=-1, omega=-1.0, overcorr=-1.0, w_levels=-1, fp32=-1, dense_max=-1):
         check(lib().ufe_b200_set_mg_params(self.h, nu_pre, nu_post, omega, overcorr, w_levels, fp32, dense_max))
+
+    def set_mg_option(self, name, value):
+        check(lib().ufe_b200_set_mg_option(self.h, name.encode(), float(value)))
 
     def mg_info(self):
         nl = C.c_int(); nodes = np.zeros(16, np.int32); fb = C.c_longlong(); cb = C.c_longlong(); ss = C.c_double()

@@ -117,6 +117,9 @@ def mismip_mod(h, half_width=1.0e6, nz=12, seed=20261104, jitter=0.2, nC_mem=32,
     else:
         Hi = np.where(r > 900e3, 0.0, 100.0)
     f = _common_fields(mesh, Hi, Hb, SL)
+    # choice_mask_noice_config = 'MISMIP_mod' (config_MISMIP_8km_spinup_for_scaling.cfg:398; masks_mod.f90:385-450): no ice beyond r = 900 km, in the
+    # coordinates of the (scaled) island like every other radius of this geometry
+    f["mask_noice"] = (r > 900e3).astype(np.int32)
     return Workload(mesh, scaling_config(), f, approximation=1, name="MISMIP_mod")
 
 
