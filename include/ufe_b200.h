@@ -443,6 +443,21 @@ int ufe_b200_calc_pc_truncation_error(ufe_b200_handle h, double zeta_t, double d
                                       const double* fraction_gr, double* tau_np1, int32_t* tau_n_guilty, double* eta_np1, int32_t* n_tot,
                                       int32_t* n_guilty);
 
+/* No counterpart in the reference: added at the request of the run's operators, for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  The same computation as ufe_b200_calc_pc_truncation_error on the n vertices passed
+ * (host buffers of length n; tau_np1 and tau_n_guilty may be NULL), but with every byte of device memory -- staged inputs, per-vertex outputs, the
+ * reduction cells -- in one file-scope __device__ array of fixed size inside the library (csrc/noalloc.cu: 256 + 44 bytes x
+ * UFE_B200_NOALLOC_MAX_VERTICES = 11 534 592 bytes, held by every GPU that loads the library until the process exits).  The call allocates nothing
+ * (no cudaMalloc / cudaFree / allocating library routine, no mesh needed on the handle) and fails with a clear ufe_b200_last_error when
+ * n > UFE_B200_NOALLOC_MAX_VERTICES.  eta_np1, n_tot and n_guilty cover the n vertices of THIS call only (no reduction over ranks).  All calls on
+ * a device share the array: the cells that must start from a known value are reset inside every call, and two calls that overlap on one GPU (two
+ * handles or two host threads) race -- serialise them. */
+#define UFE_B200_NOALLOC_MAX_VERTICES 262144
+int ufe_b200_calc_pc_truncation_error_noalloc(ufe_b200_handle h, int n, double zeta_t, double dt_n, double pc_eta_min, double pc_epsilon,
+                                              const double* Hi_np1, const double* Hi_star_np1, const int32_t* mask_grounded_ice,
+                                              const int32_t* mask_gl_gr, const double* fraction_gr, double* tau_np1, int32_t* tau_n_guilty,
+                                              double* eta_np1, int32_t* n_tot, int32_t* n_guilty);
+
 /* Replace calc_critical_timestep_adv / _SIA( mesh, ice, dt_crit) (utilities/time_step_criteria.f90:80-141, 20-78); the result is the global
  * minimum (the reference's MPI_ALLREDUCE( MPI_MIN)).  u_vav_b, v_vav_b NULL = the velocities of the last device solve. */
 int ufe_b200_calc_critical_timestep_adv(ufe_b200_handle h, const ufe_b200_config* cfg, int do_grounded_only_adv_dt, const double* Hi,

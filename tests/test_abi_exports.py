@@ -37,3 +37,8 @@ def test_no_cpu_fallback():
         pytest.skip("a GPU is present")
     with pytest.raises(ub.UfeError, match="no CUDA device|CPU fallback"):
         ub.Context()
+
+
+def test_no_alloc_limit_follows_the_header():
+    hdr = open(os.path.join(ROOT, "include", "ufe_b200.h")).read()
+    assert int(re.search(r"#define UFE_B200_NOALLOC_MAX_VERTICES (\d+)", hdr).group(1)) == ub.NOALLOC_MAX_VERTICES

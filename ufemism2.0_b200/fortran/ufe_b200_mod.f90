@@ -493,6 +493,21 @@ module ufe_b200_mod
       integer(c_int) :: ierr
     end function
 
+    ! No counterpart in the reference (added at the request of the run's operators): the same computation on the n vertices passed, with all device
+    ! memory in a fixed array inside the library (n <= UFE_B200_NOALLOC_MAX_VERTICES = 262144); allocates nothing; results of this rank only
+    function c_ufe_b200_calc_pc_truncation_error_noalloc( h, n, zeta_t, dt_n, pc_eta_min, pc_epsilon, Hi_np1, Hi_star_np1, mask_grounded_ice, &
+      mask_gl_gr, fraction_gr, tau_np1, tau_n_guilty, eta_np1, n_tot, n_guilty) bind(C, name='ufe_b200_calc_pc_truncation_error_noalloc') &
+      result( ierr)
+      import :: c_int, c_int32_t, c_double, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int), value :: n
+      real(c_double), value :: zeta_t, dt_n, pc_eta_min, pc_epsilon
+      type(c_ptr), value :: Hi_np1, Hi_star_np1, mask_grounded_ice, mask_gl_gr, fraction_gr, tau_np1, tau_n_guilty
+      real(c_double), intent(out) :: eta_np1
+      integer(c_int32_t), intent(out) :: n_tot, n_guilty
+      integer(c_int) :: ierr
+    end function
+
     ! set_ice_velocities_to_{SIA,SSA,SIASSA,DIVA}_results (conservation_of_momentum_main.f90:311-511); out = c_loc of a ufe_b200_ice_velocities
     ! (c_loc's of ice%u_3D_b, v_3D_b, du_dx_3D, du_dy_3D, du_dz_3D, dv_dx_3D, dv_dy_3D, dv_dz_3D, dw_dx_3D, dw_dy_3D; c_null_ptr = skipped);
     ! approximation: 0 'SSA', 1 'DIVA', 2 'SIA', 3 'SIA/SSA'; hybrid_scheme: 0 'add', 1 'add_SIA_reduced'
