@@ -191,11 +191,29 @@ def lattice_vertex_count(nv):
     return ncol * (ny + 1)
 
 
-def make_workload(nv, pc="jacobi"):
+# BASELINE.json's configs as bench workloads.  The driver's line is "antarctica" (configs[2]); the others are run by hand (logs under profiles/).
+CONFIGS = {
+    "antarctica": dict(index=2, nv=4_000_000, approximation=1,
+                       text="DIVA + ice_thickness predictor-corrector time stepping on a synthetic Antarctica-scale MISMIP_mod mesh"),
+    "mismip8km": dict(index=0, nv=0, approximation=1,
+                      text="MISMIP_mod island of config_MISMIP_8km_spinup_for_scaling.cfg (domain +-1000 km) at a uniform 8 km: the latency-bound regime"),
+    "mismipplus_ssa": dict(index=1, nv=500_000, approximation=0,
+                           text="MISMIP+ bed (800 x 80 km), SSA, Schoof2005 sliding, resolution graded towards the grounding line"),
+    "sweep": dict(index=4, nv=4_000_000, approximation=1,
+                  text="Krylov solve of the DIVA system of the first viscosity iteration, zero initial guess, rtol 1e-7, on the mesh generator of configs[2]"),
+}
+
+
+def make_workload(nv, pc="jacobi", config="antarctica"):
     import ufe_b200 as ub
     import workloads as wl
-    w = wl.mismip_mod(h_for_vertices(nv), half_width=HALF_WIDTH)
-    cfg = w.cfg                      # config_MISMIP_8km_spinup_for_scaling.cfg physics
+    if config == "mismip8km":
+        w = wl.mismip_mod(8.0e3, half_width=1.0e6)
+    elif config == "mismipplus_ssa":
+        w = wl.mismip_plus(float(np.sqrt(800e3 * 80e3 / (nv * np.sqrt(3.0) / 2.0))))
+    else:
+        w = wl.mismip_mod(h_for_vertices(nv), half_width=HALF_WIDTH)
+    cfg = w.cfg                      # config_MISMIP_8km_spinup_for_scaling.cfg physics; MISMIP+: Schoof2005 sliding, rtol 1e-7
     cfg.write_diagnostics = 0
     cfg.ksp_initial_guess_nonzero = 0  # the reference's KSP starts from zero (petsc_basic.f90:163 is commented out); B200_use_initial_guess_config is timed as an extra
     cfg.pc_type = ub.PC_MG if pc == "mg" else ub.PC_JACOBI   # the oracle ignores this key (it has its own ksp switch)
@@ -395,8 +413,11 @@ def run_b200(args, rank, world, rdv, log):
         uid = rdv.bcast(ub.Context.unique_id() if rank == 0 else None, 128)
     ctx = ub.Context(device=local_rank, rank=rank, nranks=world, unique_id=uid)
     t0 = time.time()
-    w = make_workload(args.nv, args.pc)
+    conf = CONFIGS[args.config]
+    approx = conf["approximation"]
+    w = make_workload(args.nv, args.pc, args.config)
     m, cfg = w.mesh, w.cfg
+    dt = DT
     if args.pc == "mg":
         ctx.set_mg_params(nu_pre=args.mg_nu, nu_post=args.mg_nu, omega=args.mg_omega, overcorr=args.mg_overcorr, w_levels=args.mg_w_levels, fp32=args.mg_fp32)
     log(f"mesh nV={m.nV} nTri={m.nTri} nE={m.nE} generated in {time.time() - t0:.1f}s")
@@ -414,8 +435,14 @@ def run_b200(args, rank, world, rdv, log):
     # ---- spin-up (untimed): cold DIVA solve to the converged velocity of the initial geometry
     t0 = time.time()
     ub.check(L.ufe_b200_velocity_upload(ctx.h, C.byref(ice), C.byref(st)))
-    ub.check(L.ufe_b200_velocity_solve_resident(ctx.h, C.byref(cfg), 1, C.byref(nv_), C.byref(na_)))
+    ub.check(L.ufe_b200_velocity_solve_resident(ctx.h, C.byref(cfg), approx, C.byref(nv_), C.byref(na_)))
     log(f"spin-up: {nv_.value} viscosity its, {na_.value} Krylov its in {time.time() - t0:.1f}s")
+    if args.config == "mismipplus_ssa":
+        # 0.25 of the advective limit of the finest triangles (the reference's calc_critical_timestep_adv has 0.5 built in), from the spun-up velocities
+        ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
+        speed = rdv.allreduce_max(float(np.hypot(A["u_vav_b"], A["v_vav_b"]).max()))
+        dt = 0.25 * float(np.sqrt(m.TriA.min() * 4.0 / np.sqrt(3.0))) / max(speed, 1.0)
+        log(f"MISMIP+: max speed {speed:.1f} m/yr, dt = {dt:.4f} yr")
     mg_info = ctx.mg_info() if args.pc == "mg" else None
     if mg_info:
         log(f"multigrid hierarchy: {mg_info}")
@@ -426,7 +453,7 @@ def run_b200(args, rank, world, rdv, log):
 
     # ---- device-resident leg (`value`)
     def step_resident():
-        ub.check(L.ufe_b200_pc_step_resident(ctx.h, C.byref(cfg), 1, DT, C.byref(nv_), C.byref(na_), C.byref(nt_)))
+        ub.check(L.ufe_b200_pc_step_resident(ctx.h, C.byref(cfg), approx, dt, C.byref(nv_), C.byref(na_), C.byref(nt_)))
         return nv_.value, na_.value, nt_.value
 
     for _ in range(args.warmup):
@@ -438,12 +465,23 @@ def run_b200(args, rank, world, rdv, log):
     L.ufe_b200_timing_enable(ctx.h, 1)
     launches0 = ctx.kernel_launches()
     rdv.barrier()
-    ub.check(L.ufe_b200_timer_start(ctx.h))
     tot = [0, 0, 0]
-    for _ in range(args.steps):
-        tot = [a + b for a, b in zip(tot, step_resident())]
     ms = C.c_double()
-    ub.check(L.ufe_b200_timer_stop(ctx.h, C.cast(C.byref(ms), ub.c_dp)))
+    flush_l2 = m.nV < 400_000        # stiffness matrix (~1 kB / vertex) not well above the 126 MB L2: write a 512 MB buffer between the timed steps
+    if flush_l2:
+        ms_sum = 0.0
+        for _ in range(args.steps):
+            ub.check(L.ufe_b200_l2_flush(ctx.h))
+            ub.check(L.ufe_b200_timer_start(ctx.h))
+            tot = [a + b for a, b in zip(tot, step_resident())]
+            ub.check(L.ufe_b200_timer_stop(ctx.h, C.cast(C.byref(ms), ub.c_dp)))
+            ms_sum += ms.value
+        ms.value = ms_sum
+    else:
+        ub.check(L.ufe_b200_timer_start(ctx.h))
+        for _ in range(args.steps):
+            tot = [a + b for a, b in zip(tot, step_resident())]
+        ub.check(L.ufe_b200_timer_stop(ctx.h, C.cast(C.byref(ms), ub.c_dp)))
     rdv.barrier()
     ms_total = rdv.allreduce_max(ms.value)
     launches = ctx.kernel_launches() - launches0
@@ -500,7 +538,7 @@ def run_b200(args, rank, world, rdv, log):
     bytes_out = sum(a.nbytes for a in A_e2e.values()) + sum(a.nbytes for a in out.values()) + dH_nm1.nbytes
 
     def step_e2e():
-        ub.check(L.ufe_b200_pc_step(ctx.h, C.byref(cfg), 1, DT, DT, C.byref(ice), C.byref(st_e2e), C.byref(io2), ub.dp(dH_nm1),
+        ub.check(L.ufe_b200_pc_step(ctx.h, C.byref(cfg), approx, dt, dt, C.byref(ice), C.byref(st_e2e), C.byref(io2), ub.dp(dH_nm1),
                                     C.byref(nv_), C.byref(na_), C.byref(nt_)))
         keep_io["Hi"][:] = out["Hi_tplusdt"]      # the host model accepts the step: Hi_n := Hi_np1
 
@@ -565,13 +603,16 @@ def run_b200(args, rank, world, rdv, log):
         avg_ms = spmv_ms / max(spmv_n, 1)
         achieved = B_spmv / (avg_ms * 1e-3) / 1e9 if spmv_n else 0.0
         res = {
-            "metric": "DIVA velocity solves/s", "value": args.steps / (ms_total * 1e-3), "unit": "velocity solves/s", "n_gpus": world,
+            "metric": ("DIVA" if approx == 1 else "SSA") + " velocity solves/s", "value": args.steps / (ms_total * 1e-3), "unit": "velocity solves/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"configs[2]: DIVA + ice_thickness predictor-corrector time stepping on a synthetic Antarctica-scale MISMIP_mod mesh, "
-                                   f"{m.nV} vertices / {m.nTri} triangles, nz={m.nz}, dt={DT} yr, physics of config_MISMIP_8km_spinup_for_scaling.cfg",
+            "config": {"workload": f"configs[{conf['index']}]: {conf['text']}, "
+                                   f"{m.nV} vertices / {m.nTri} triangles, nz={m.nz}, dt={dt:.4g} yr, " +
+                                   ("physics of config_MISMIP_8km_spinup_for_scaling.cfg" if approx == 1 else "SSA"),
+                       "name": args.config,
                        "n_vertices": int(m.nV), "partition": f"{world} contiguous row blocks (partition_list)",
-                       "l2_policy": "inputs larger than L2 (stiffness matrix 4 GB >> 126 MB)",
+                       "l2_policy": ("L2 flushed between the timed steps (512 MB written by ufe_b200_l2_flush; each step timed by its own event pair)" if flush_l2
+                                     else f"inputs larger than L2 (stiffness matrix {blk_b.value / 1e9:.2f} GB >> 126 MB)"),
                        "krylov": krylov_desc + ", rtol 1e-4 / abstol 1e-3, zero initial guess (the reference's KSP semantics, petsc_basic.f90:163)",
                        "value_is": "zero initial guess; value_initial_guess_nonzero is the same step with B200_use_initial_guess_config = .true.",
                        "time_step": ("one pass of iterate_pc_timestep in the reference's order and semantics (lagged region%ice%Hi, applied rate in Eq. 30, alter_ice_thickness after Eq. 30 / 31, "
@@ -603,13 +644,103 @@ def run_b200(args, rank, world, rdv, log):
     return res
 
 
+def run_sweep(args, rank, world, rdv, log):
+    """configs[4]: the Krylov solve of the DIVA system of the FIRST viscosity iteration (velocities zero, viscosity from the
+    initial strain-rate guess), zero initial guess, rtol 1e-7, on the mesh generator of configs[2] at --nv vertices, row blocks over `world` GPUs.
+    One step = upload the zero state (untimed), then ufe_b200_velocity_solve_resident with visc_it_nit = 1 (timed: assembly of the first iteration,
+    preconditioner set-up, the Krylov solve, epilogue)."""
+    import ufe_b200 as ub
+    L = ub.lib()
+    local_rank = int(os.environ.get("LOCAL_RANK", rank))
+    bind_to_gpu_numa_node(local_rank, log)
+    uid = rdv.bcast(ub.Context.unique_id() if rank == 0 else None, 128) if world > 1 else None
+    ctx = ub.Context(device=local_rank, rank=rank, nranks=world, unique_id=uid)
+    w = make_workload(args.nv, args.pc, "sweep")
+    m, cfg = w.mesh, w.cfg
+    cfg.visc_it_nit = 1
+    cfg.stress_balance_PETSc_rtol, cfg.stress_balance_PETSc_abstol = 1e-7, 1e-30
+    cfg.ksp_initial_guess_nonzero = 0
+    if args.pc == "mg":
+        ctx.set_mg_params(nu_pre=args.mg_nu, nu_post=args.mg_nu, omega=args.mg_omega, overcorr=args.mg_overcorr, w_levels=args.mg_w_levels, fp32=args.mg_fp32)
+    ctx.mesh_create(m)
+    ctx.calc_matrix_operators()
+    vr, tr = (ctx.vi1, ctx.vi2), (ctx.ti1, ctx.ti2)
+    na, nb = vr[1] - vr[0] + 1, tr[1] - tr[0] + 1
+    ice = w.ice_inputs(vr, tr)
+    st, A = ub.alloc_velocity_state(na, nb, m.nz, fields=STATE_FIELDS + ["u_b_prev", "v_b_prev"])
+    nv_, na_ = C.c_int(), C.c_int()
+    ms = C.c_double()
+
+    def step(timed):
+        ub.check(L.ufe_b200_velocity_upload(ctx.h, C.byref(ice), C.byref(st)))          # zero velocities again: the same system every step
+        if timed:
+            ub.check(L.ufe_b200_timer_start(ctx.h))
+        ub.check(L.ufe_b200_velocity_solve_resident(ctx.h, C.byref(cfg), 1, C.byref(nv_), C.byref(na_)))
+        if timed:
+            ub.check(L.ufe_b200_timer_stop(ctx.h, C.cast(C.byref(ms), ub.c_dp)))
+        return ms.value, na_.value
+
+    for _ in range(args.warmup):
+        step(False)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    L.ufe_b200_timing_reset(ctx.h)
+    L.ufe_b200_timing_enable(ctx.h, 1)
+    launches0 = ctx.kernel_launches()
+    rdv.barrier()
+    ms_sum, its = 0.0, 0
+    for _ in range(args.steps):
+        t, k = step(True)
+        ms_sum += t; its += k
+    rdv.barrier()
+    ms_total = rdv.allreduce_max(ms_sum)
+    launches = ctx.kernel_launches() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    L.ufe_b200_timing_enable(ctx.h, 0)
+    classes = {c: ctx.timing(c) for c in ("spmv_stiffness", "mg_fine", "mg_vec", "mg_coarse", "mg_setup", "krylov_vec", "assembly", "column", "tri", "epilogue")}
+    krylov_ms = sum(classes[c][0] for c in ("spmv_stiffness", "mg_fine", "mg_vec", "mg_coarse", "krylov_vec"))
+    res = None
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        csr_b, blk_b = C.c_longlong(), C.c_longlong()
+        ub.check(L.ufe_b200_get_stiffness_storage_bytes(ctx.h, C.byref(csr_b), C.byref(blk_b)))
+        top = "mg_fine" if classes["mg_fine"][0] > classes["spmv_stiffness"][0] else "spmv_stiffness"
+        B_spmv = csr_b.value + 16 * 2 * nb + (8 * 2 * nb if top == "mg_fine" else 0)
+        t_ms, t_n = classes[top]
+        avg_ms = t_ms / max(t_n, 1)
+        achieved = B_spmv / (avg_ms * 1e-3) / 1e9 if t_n else 0.0
+        res = {"metric": "DIVA Krylov solves/s", "value": args.steps / (ms_total * 1e-3), "unit": "linear solves/s", "n_gpus": world, "steps": args.steps,
+               "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+               "data": "synthetic",
+               "config": {"workload": f"configs[4]: {CONFIGS['sweep']['text']}, {m.nV} vertices / {m.nTri} triangles, nz={m.nz}", "name": "sweep",
+                          "n_vertices": int(m.nV), "partition": f"{world} contiguous row blocks (partition_list)",
+                          "l2_policy": f"inputs larger than L2 (stiffness matrix {blk_b.value / 1e9:.2f} GB per rank)",
+                          "krylov": ("BiCGStab + aggregation multigrid" if args.pc == "mg" else "BiCGStab + Jacobi") + ", rtol 1e-7, zero initial guess",
+                          "per_step": {"krylov_its": its / args.steps, "krylov_ms": krylov_ms / args.steps,
+                                       "ms_per_krylov_it": krylov_ms / max(its, 1)}},
+               "e2e": None, "gpu_launches": int(launches),
+               "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None,
+                            "avg_launch_ms": avg_ms, "launches": t_n, "algorithmic_bytes_per_launch": B_spmv, "traffic": None},
+               "kernel_classes_ms": {k: v[0] for k, v in classes.items()}, "clocks": clocks}
+    ctx.close()
+    return res
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--nv", type=int, default=4_000_000, help="target number of vertices (config 3: ~4M)")
+    ap.add_argument("--config", default="antarctica", choices=sorted(CONFIGS), help="BASELINE.json config: antarctica = configs[2] (the driver's line), "
+                    "mismip8km = configs[0], mismipplus_ssa = configs[1], sweep = configs[4] (one mesh size per call: --nv)")
+    ap.add_argument("--nv", type=int, default=0, help="target number of vertices (0: the config's own, ~4M for configs[2])")
     ap.add_argument("--cpu-nv", type=int, default=250_000, help="vertices of the bounded CPU sample")
     ap.add_argument("--pc", default="mg", choices=["jacobi", "mg"], help="preconditioner of the stiffness-matrix solve on the device")
     ap.add_argument("--mg-nu", type=int, default=1)
@@ -626,6 +757,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    args.nv = args.nv or CONFIGS[args.config]["nv"]
 
     def log(*a):
         if args.verbose or os.environ.get("UFE_BENCH_VERBOSE"):
@@ -649,9 +781,14 @@ def main():
         return
 
     rdv = Rendezvous(rank, world)
+    if args.config == "sweep":
+        res = run_sweep(args, rank, world, rdv, log)
+        if rank == 0:
+            print(json.dumps(res), flush=True)
+        return
     res = run_b200(args, rank, world, rdv, log)
     if rank == 0:
-        if not args.no_cpu_baseline and world == 1:
+        if not args.no_cpu_baseline and world == 1 and args.config == "antarctica":
             res["cpu_baseline"] = run_cpu_sample(args.cpu_nv, res["config"]["n_vertices"], 2, 1, log)
         print(json.dumps(res), flush=True)
 

@@ -29,8 +29,8 @@ extern "C" {
 typedef struct ufe_b200_ctx* ufe_b200_handle;
 
 /* ---- enumerations ---------------------------------------------------------------------------- */
-enum { UFE_KSP_BICGSTAB = 0, UFE_KSP_CG = 1 };                       /* north_star (b) */
-enum { UFE_PC_JACOBI = 0, UFE_PC_NONE = 1, UFE_PC_BJACOBI2 = 2, UFE_PC_NEUMANN = 3,
+enum { UFE_KSP_BICGSTAB = 0 };   /* the only Krylov method: neither matrix of the path is symmetric, so north_star (b)'s CG has no use here */
+enum { UFE_PC_JACOBI = 0, UFE_PC_NONE = 1,   /* values 2 and 3 are unassigned */
        UFE_PC_MG = 4 };   /* aggregation multigrid, stiffness-matrix solve only (new key B200_PC_type_config = 'multigrid') */
 enum { UFE_BC_INFINITE = 0, UFE_BC_ZERO = 1,                          /* C%BC_{u,v,H}_{north,east,south,west} */
        UFE_BC_PERIODIC_ISMIP_HOM = 2, UFE_BC_INFINITE_SSA_ICESTREAM = 3 }; /* BC_u / BC_v only: the copy rows of
@@ -260,6 +260,19 @@ int ufe_b200_velocity_upload(ufe_b200_handle h, const ufe_b200_ice_inputs* ice, 
 int ufe_b200_velocity_solve_resident(ufe_b200_handle h, const ufe_b200_config* cfg, int approximation /*0 SSA, 1 DIVA*/,
                                      int* n_visc_its, int* n_Axb_its);
 int ufe_b200_velocity_download(ufe_b200_handle h, ufe_b200_velocity_state* st);
+
+/* Replaces remap_DIVA_solver( mesh_old, mesh_new, DIVA) / remap_SSA_solver( mesh_old, mesh_new, SSA)
+ * (src/UFEMISM/ice_dynamics/conservation_of_momentum/SSA_DIVA/DIVA_main.f90:115-222, SSA_main.f90:247-311; called from remap_velocity_solver after
+ * update_mesh, UFEMISM_main_model.f90:1211) for a solver state that lives on the device: the fields the viscosity iteration re-uses (DIVA: u_vav_b,
+ * v_vav_b, tau_bx_b, tau_by_b, eta_3D_b, u_3D_b, v_3D_b; SSA: u_b, v_b) go  map_b_a( mesh_old) -> Atlas map -> set_border_vertices_to_interior_mean
+ * (apply_maps.f90:531-583, mesh_utilities.f90:1648-1757) -> map_a_b( mesh_new)  from the state of h_old into the state of h_new; everything else of
+ * the solver object starts from zero (reallocate_bounds / reallocate_clean).  h_old: the handle of the old mesh with its velocity state; h_new: a second
+ * handle of the same rank / GPU on which ufe_b200_mesh_create + ufe_b200_calc_matrix_operators have run for the new mesh.  The map is the rank's rows
+ * (new vertices vi1:vi2) of type_map%M as CSR (1-based offsets relative to map_ptr[0], 1-based global columns = vertices of the old mesh); building it
+ * (create_map_from_mesh_to_mesh_*, line tracing through both meshes) is mesh generation and stays on the host.  Afterwards: ufe_b200_velocity_upload(
+ * h_new, ice, NULL) for the inputs on the new mesh, ufe_b200_finalize( h_old) -- the state is NOT copied back to the host in between. */
+int ufe_b200_remap_velocity_solver(ufe_b200_handle h_old, ufe_b200_handle h_new, int approximation /*0 SSA, 1 DIVA*/, int m_loc,
+                                   const int32_t* map_ptr, const int32_t* map_ind, const double* map_val);
 
 /* ---- wide seam: ice thickness -------------------------------------------------------------------- */
 /* Replaces calc_dHi_dt( mesh, ice, Hi, Hb, SL, u_vav_b, v_vav_b, SMB, BMB, LMB, AMB, fraction_margin, mask_noice, dt,
@@ -504,6 +517,8 @@ int ufe_b200_timing_enable(ufe_b200_handle h, int on);
  * returns the elapsed device time in milliseconds */
 int ufe_b200_timer_start(ufe_b200_handle h);
 int ufe_b200_timer_stop(ufe_b200_handle h, double* ms);
+/* writes a 512 MB device buffer (4 x L2) on the library's stream: bench.py calls it between the timed iterations of workloads smaller than L2 */
+int ufe_b200_l2_flush(ufe_b200_handle h);
 /* page-lock / unlock a host buffer the caller passes repeatedly (cudaHostRegister), so H2D/D2H copies run at full rate */
 int ufe_b200_host_register(void* ptr, size_t bytes);
 int ufe_b200_host_unregister(void* ptr);

@@ -34,6 +34,8 @@ def run(ctx, w, pc, steps):
     ub.check(L.ufe_b200_velocity_upload(ctx.h, C.byref(ice), C.byref(st)))
     ub.check(L.ufe_b200_velocity_solve_resident(ctx.h, C.byref(cfg), 1, C.byref(nv), C.byref(na)))
     its = [(nv.value, na.value)]
+    ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
+    u0 = A["u_vav_b"].copy()          # the first stress-balance solve, before any thickness step
     io, keep = bench.thickness_io(w, sa, w.f["Hi"][sa])
     ub.check(L.ufe_b200_thickness_upload(ctx.h, C.byref(io)))
     for _ in range(steps):
@@ -42,7 +44,7 @@ def run(ctx, w, pc, steps):
     Hi = np.zeros(vr[1] - vr[0] + 1)
     ub.check(L.ufe_b200_thickness_download(ctx.h, ub.dp(Hi), None, None))
     ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
-    return dict(u=A["u_vav_b"].copy(), v=A["v_vav_b"].copy(), u3=A["u_3D_b"].copy(), Hi=Hi, vr=vr, tr=tr, its=its)
+    return dict(u=A["u_vav_b"].copy(), v=A["v_vav_b"].copy(), u3=A["u_3D_b"].copy(), Hi=Hi, vr=vr, tr=tr, its=its, u0=u0)
 
 
 def rel(a, b):
@@ -70,6 +72,14 @@ for pc, name in CASES:
     sa = slice(multi["vr"][0] - 1, multi["vr"][1]); sb = slice(multi["tr"][0] - 1, multi["tr"][1])
     errs = dict(u=rel(multi["u"], single["u"][sb]), v=rel(multi["v"], single["v"][sb]), u_3D=rel(multi["u3"], single["u3"][sb, :]),
                 Hi=rel(multi["Hi"], single["Hi"][sa]))
+    # and against the CPU oracle (the reference's algorithm restated): rank 0 solves the first stress balance of the whole mesh with it
+    if rank == 0 and os.environ.get("PARITY_ORACLE", "1") == "1":
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_lib as ol
+        wo = workload()
+        st_o, A_o = ub.alloc_velocity_state(wo.mesh.nV, wo.mesh.nTri, wo.mesh.nz)
+        rc, nv_o, na_o = ol.OracleMesh(wo.mesh).solve_velocity(wo.cfg, 1, wo.ice_inputs(), st_o)
+        errs["u_first_solve_vs_oracle"] = rel(multi["u0"], A_o["u_vav_b"][sb]) if rc == 0 else 1.0
     worst = rdv.allreduce_max(max(errs.values()))
     good = worst < 1e-6
     ok = ok and good

@@ -8,7 +8,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 # measurement / introspection helpers of bench.py and the tests; a Fortran host has no use for them
 TOOLING = {"ufe_b200_get_mg_info", "ufe_b200_get_stiffness", "ufe_b200_get_stiffness_size", "ufe_b200_get_stiffness_storage_bytes", "ufe_b200_host_register",
-           "ufe_b200_host_unregister", "ufe_b200_mg_host_transfer", "ufe_b200_mg_host_transfer_get", "ufe_b200_mg_host_transfer_parts",
+           "ufe_b200_host_unregister", "ufe_b200_l2_flush", "ufe_b200_mg_host_transfer", "ufe_b200_mg_host_transfer_get", "ufe_b200_mg_host_transfer_parts",
            "ufe_b200_mg_host_transfer_parts_get", "ufe_b200_timer_start", "ufe_b200_timer_stop", "ufe_b200_timing_enable", "ufe_b200_timing_get",
            "ufe_b200_timing_reset"}
 

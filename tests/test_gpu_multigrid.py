@@ -101,6 +101,23 @@ def test_multigrid_with_initial_guess_and_config_tolerance(setup):
     assert rel_l2(gm["u_vav_b"], gj["u_vav_b"]) < 5e-3       # two preconditioners at rtol 1e-4
 
 
+def test_merged_reductions_of_the_multi_rank_recurrence(setup, monkeypatch):
+    """k_ksmg_dot5 / k_ksmg_update_xr5 (two all-reduces per iteration, the default on several ranks), forced on one rank: same solution as the
+    direct sums at the configuration's tolerance and at a tight one, with about the same iteration count"""
+    w, ctx, o = setup
+    m = w.mesh
+    co = _coefficients(m, seed=6)
+    cfg = wl.scaling_config()
+    cfg.pc_type = ub.PC_MG
+    for rtol, tol in ((1e-4, 2e-4), (1e-10, 1e-8)):
+        monkeypatch.setenv("UFE_B200_KSP_MERGED", "0")
+        u0, v0, its0 = _linearised(ctx, cfg, m, *co, rtol, 1e-30)
+        monkeypatch.setenv("UFE_B200_KSP_MERGED", "1")
+        u1, v1, its1 = _linearised(ctx, cfg, m, *co, rtol, 1e-30)
+        assert rel_l2(u1, u0) < tol and rel_l2(v1, v0) < tol, (rtol, rel_l2(u1, u0), rel_l2(v1, v0))
+        assert abs(its1 - its0) <= max(2, its0 // 5), (rtol, its0, its1)
+
+
 def test_multigrid_is_deterministic(setup):
     w, ctx, o = setup
     m = w.mesh

@@ -170,7 +170,7 @@ def run_setup(values):
     c.ksp_type = int(values.get("B200_KSP_type", ub.KSP_BICGSTAB))
     pc = values.get("B200_PC_type", ub.PC_JACOBI)
     c.pc_type = _choice(_PC, pc, "B200_PC_type") if isinstance(pc, str) else int(pc)
-    if c.ksp_type not in (ub.KSP_BICGSTAB, ub.KSP_CG) or c.pc_type not in (ub.PC_JACOBI, ub.PC_NONE, ub.PC_MG):
+    if c.ksp_type != ub.KSP_BICGSTAB or c.pc_type not in (ub.PC_JACOBI, ub.PC_NONE, ub.PC_MG):
         raise ConfigError(f"unknown B200_KSP_type / B200_PC_type {c.ksp_type} / {c.pc_type}")
     c.ksp_initial_guess_nonzero = 1 if values.get("B200_use_initial_guess", False) else 0
     c.stiffness_format = int(values.get("B200_stiffness_format", 0))

@@ -84,6 +84,14 @@ struct DevCsr {
   DBuf<double> val_buf;
   int vec_width = 4;   // lanes per row of the vector-per-row kernel (1,2,4,8,16,32)
   bool valid = false;
+  // Sliced-ELL copy (slices of 32 rows, entries of a slice stored column-major so that a warp with one row per lane reads val/ind in full
+  // 256 B / 128 B segments; csr.cu: csr_sell_build / csr_sell_refresh).  Built on demand for matrices that are multiplied many times (Krylov
+  // solves, registered matrices, mesh operators); empty otherwise.  sell_slice[s] = first slot of slice s (a multiple of 32).
+  DBuf<int> sell_slice, sell_ind;
+  DBuf<double> sell_val;
+  const int* sell_src_ptr = nullptr;   // the ptr array the pattern was built from (a rebuilt CSR pattern invalidates the copy)
+  long long sell_src_nnz = -1;
+  bool has_sell() const { return sell_val.p != nullptr && sell_src_ptr == ptr && sell_src_nnz == nnz; }
 };
 
 // ---- timing classes ----------------------------------------------------------------------------------
@@ -130,6 +138,7 @@ void pc_state_free(PcState*);
 struct Ctx {
   int device = 0, rank = 0, nranks = 1;
   cudaStream_t stream = nullptr;
+  DBuf<unsigned char> l2_flush;         // ufe_b200_l2_flush: a buffer larger than L2, written between timed iterations of small workloads
   cudaStream_t copy_stream = nullptr;   // host<->device transfers that overlap compute (ufe_b200_pc_step)
   cudaEvent_t ev_copy_a = nullptr, ev_copy_b = nullptr;
   void* nccl = nullptr;             // ncclComm_t when nranks > 1

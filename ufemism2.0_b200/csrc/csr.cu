@@ -108,6 +108,79 @@ int csr_upload(Ctx* c, DevCsr& A, int m_glob, int n_glob, int m_loc, int i1, int
   return 0;
 }
 
+// ---- sliced-ELL copy (DevCsr::sell_*) --------------------------------------------------------------------------------------------------------
+// width of every slice of 32 rows = its longest row
+__global__ void k_sell_width(int m, int nslices, const int* __restrict__ ptr, int* __restrict__ width) {
+  for (long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x; s < nslices; s += (long long)gridDim.x * blockDim.x) {
+    int w = 0;
+    const int r1 = (int)s * 32, r2 = min(m, r1 + 32);
+    for (int r = r1; r < r2; ++r) w = max(w, ptr[r + 1] - ptr[r]);
+    width[s] = w;
+  }
+}
+// one thread per (slice, lane): entry k of row r sits at slice[s] + 32 k + lane; padding = value 0 at a column of the same row
+template <bool PATTERN>
+__global__ void k_sell_fill(int m, int nslices, const int* __restrict__ ptr, const int* __restrict__ ind, const double* __restrict__ val,
+                            const int* __restrict__ slice, int* __restrict__ sind, double* __restrict__ sval) {
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < (long long)nslices * 32; t += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)t, s = r >> 5, b = slice[s], w = (slice[s + 1] - b) >> 5;
+    const int k1 = r < m ? ptr[r] : 0, len = r < m ? ptr[r + 1] - k1 : 0;
+    const int pad = len > 0 ? ind[k1 + len - 1] : 0;
+    for (int k = 0; k < w; ++k) {
+      const size_t slot = (size_t)b + (size_t)k * 32 + (r & 31);
+      sval[slot] = k < len ? val[k1 + k] : 0.0;
+      if (PATTERN) sind[slot] = k < len ? ind[k1 + k] : pad;
+    }
+  }
+}
+
+// UFE_B200_CSR_KERNEL=vector keeps the vector-per-row kernels everywhere (the comparison of profiles/r02_spmv_probe_*.log)
+static bool sell_disabled() {
+  static const bool off = [] { const char* e = getenv("UFE_B200_CSR_KERNEL"); return e && !strcmp(e, "vector"); }();
+  return off;
+}
+
+int csr_sell_build(Ctx* c, DevCsr& A) {
+  if (A.m_loc == 0 || sell_disabled()) return 0;
+  const int nslices = (A.m_loc + 31) / 32;
+  DBuf<int> width;
+  UFE_TRY(width.alloc(nslices));
+  {
+    UFE_LAUNCH(c, TC_OPERATOR_SPMV);
+    k_sell_width<<<grid_for(c, nslices, kBlock), kBlock, 0, c->stream>>>(A.m_loc, nslices, A.ptr, width.p);
+  }
+  UFE_CUDA(cudaGetLastError());
+  std::vector<int> w(nslices), sl((size_t)nslices + 1);     // once per pattern: the prefix sum runs on the host
+  UFE_CUDA(cudaMemcpyAsync(w.data(), width.p, sizeof(int) * nslices, cudaMemcpyDeviceToHost, c->stream));
+  UFE_CUDA(cudaStreamSynchronize(c->stream));
+  long long slots = 0;
+  for (int s = 0; s < nslices; ++s) { sl[s] = (int)slots; slots += 32LL * w[s]; }
+  UFE_CHECK(slots < (1LL << 31), "sliced-ELL copy: %lld slots do not fit 32-bit offsets", slots);
+  sl[nslices] = (int)slots;
+  UFE_TRY(A.sell_slice.alloc((size_t)nslices + 1)); UFE_TRY(A.sell_ind.alloc((size_t)std::max(slots, 1LL))); UFE_TRY(A.sell_val.alloc((size_t)std::max(slots, 1LL)));
+  UFE_CUDA(cudaMemcpyAsync(A.sell_slice.p, sl.data(), sizeof(int) * sl.size(), cudaMemcpyHostToDevice, c->stream));
+  {
+    UFE_LAUNCH(c, TC_OPERATOR_SPMV);
+    k_sell_fill<true><<<grid_for(c, (long long)nslices * 32, kBlock), kBlock, 0, c->stream>>>(A.m_loc, nslices, A.ptr, A.ind, A.val, A.sell_slice.p,
+                                                                                            A.sell_ind.p, A.sell_val.p);
+  }
+  UFE_CUDA(cudaGetLastError());
+  UFE_CUDA(cudaStreamSynchronize(c->stream));   // sl goes out of scope
+  A.sell_src_ptr = A.ptr; A.sell_src_nnz = A.nnz;
+  return 0;
+}
+
+int csr_sell_refresh(Ctx* c, DevCsr& A) {
+  if (!A.has_sell()) return csr_sell_build(c, A);
+  if (A.m_loc == 0) return 0;
+  const int nslices = (A.m_loc + 31) / 32;
+  UFE_LAUNCH(c, TC_OPERATOR_SPMV);
+  k_sell_fill<false><<<grid_for(c, (long long)nslices * 32, kBlock), kBlock, 0, c->stream>>>(A.m_loc, nslices, A.ptr, A.ind, A.val, A.sell_slice.p,
+                                                                                           nullptr, A.sell_val.p);
+  UFE_CUDA(cudaGetLastError());
+  return 0;
+}
+
 template <int W>
 static void launch_spmv_plain(Ctx* c, const DevCsr& A, const double* x_ext, double* y, int tc) {
   CsrOp<W> op{A.ptr, A.ind, A.val};
@@ -118,6 +191,14 @@ static void launch_spmv_plain(Ctx* c, const DevCsr& A, const double* x_ext, doub
 
 int csr_spmv(Ctx* c, const DevCsr& A, const double* x_ext, double* y, int tc) {
   if (A.m_loc == 0) return 0;
+  if (A.has_sell()) {
+    SellOp op{A.sell_slice.p, A.sell_ind.p, A.sell_val.p};
+    UFE_LAUNCH(c, tc);
+    k_spmv_fused<SellOp, 0><<<grid_for(c, A.m_loc, kBlock), kBlock, 0, c->stream>>>(op, A.m_loc, 0, 0, x_ext, nullptr, y, nullptr, nullptr, nullptr,
+                                                                                 nullptr, nullptr);
+    UFE_CUDA(cudaGetLastError());
+    return 0;
+  }
   switch (A.vec_width) {
     case 2: launch_spmv_plain<2>(c, A, x_ext, y, tc); break;
     case 4: launch_spmv_plain<4>(c, A, x_ext, y, tc); break;
@@ -144,9 +225,51 @@ __global__ void k_spmv_multicol(int m, int n_ext, int ncols, const int* __restri
   }
 }
 
+// the same product on the sliced-ELL copy: one row per thread, the row's entries read once per chunk of NC columns (coalesced, see SellOp), NC
+// accumulators and NC independent gathers per entry in flight; blockIdx.y = column chunk
+template <int NC>
+__global__ void __launch_bounds__(kBlock) k_sell_multicol(int m, int n_ext, int ncols, const int* __restrict__ slice, const int* __restrict__ ind,
+                                                          const double* __restrict__ val, const double* __restrict__ x, double* __restrict__ y) {
+  const int c0 = blockIdx.y * NC, nc = min(NC, ncols - c0);
+  const double* __restrict__ xc = x + (size_t)c0 * n_ext;
+  for (long long rr = (long long)blockIdx.x * blockDim.x + threadIdx.x; rr < m; rr += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)rr, s = r >> 5, b = slice[s], w = (slice[s + 1] - b) >> 5;
+    const int* __restrict__ ip = ind + b + (r & 31);
+    const double* __restrict__ vp = val + b + (r & 31);
+    double acc[NC];
+#pragma unroll
+    for (int q = 0; q < NC; ++q) acc[q] = 0.0;
+    for (int k = 0; k < w; ++k) {
+      const int j = ip[k * 32];
+      const double v = vp[k * 32];
+#pragma unroll
+      for (int q = 0; q < NC; ++q)
+        if (q < nc) acc[q] += v * xc[(size_t)q * n_ext + j];
+    }
+#pragma unroll
+    for (int q = 0; q < NC; ++q)
+      if (q < nc) y[(size_t)(c0 + q) * m + r] = acc[q];
+  }
+}
+
+template <int NC>
+static void launch_sell_multicol(Ctx* c, const DevCsr& A, const double* x_ext, double* y, int ncols) {
+  dim3 grid(grid_for(c, A.m_loc, kBlock), (ncols + NC - 1) / NC);
+  k_sell_multicol<NC><<<grid, kBlock, 0, c->stream>>>(A.m_loc, A.cols.n_ext(), ncols, A.sell_slice.p, A.sell_ind.p, A.sell_val.p, x_ext, y);
+}
+
 int csr_spmv_multicol(Ctx* c, const DevCsr& A, const double* x_ext, double* y, int ncols, int tc) {
   if (ncols == 1) return csr_spmv(c, A, x_ext, y, tc);
   if (A.m_loc == 0) return 0;
+  if (A.has_sell()) {
+    UFE_LAUNCH(c, tc);
+    if (ncols <= 4) launch_sell_multicol<4>(c, A, x_ext, y, ncols);
+    else if (ncols <= 8) launch_sell_multicol<8>(c, A, x_ext, y, ncols);
+    else if (ncols <= 12 || (ncols > 16 && ncols <= 24)) launch_sell_multicol<12>(c, A, x_ext, y, ncols);
+    else launch_sell_multicol<16>(c, A, x_ext, y, ncols);
+    UFE_CUDA(cudaGetLastError());
+    return 0;
+  }
   UFE_LAUNCH(c, tc);
   k_spmv_multicol<<<grid_for(c, A.m_loc, kBlock), kBlock, 0, c->stream>>>(A.m_loc, A.cols.n_ext(), ncols, A.ptr, A.ind,
                                                                          A.val, x_ext, y);
@@ -162,13 +285,18 @@ int csr_make_dinv(Ctx* c, const DevCsr& A, double* dinv, int pc_type) {
   return 0;
 }
 
-int csr_ksp_solve(Ctx* c, const DevCsr& A, const double* d_b, double* d_x_ext, const KrylovParams& kp, int tc, int* its) {
+int csr_ksp_solve(Ctx* c, DevCsr& A, const double* d_b, double* d_x_ext, const KrylovParams& kp, int tc, int* its) {
   UFE_CHECK(kp.ksp_type == UFE_KSP_BICGSTAB, "only BiCGStab is available for general (non-symmetric) matrices");
   UFE_CHECK(kp.pc_type == UFE_PC_JACOBI || kp.pc_type == UFE_PC_NONE, "generic CSR solve supports pc = jacobi | none");
   if (!c->krylov) c->krylov = new Krylov();
   UFE_TRY(c->krylov->dinv.alloc(A.m_loc));
   UFE_TRY(csr_make_dinv(c, A, c->krylov->dinv.p, kp.pc_type));
   const double* dinv = c->krylov->dinv.p;
+  // A Krylov solve multiplies with A at least twice per iteration: one pass that (re)fills the sliced-ELL copy pays off from the first iterations on.
+  if (!sell_disabled() && A.m_loc > 0) {
+    UFE_TRY(csr_sell_refresh(c, A));
+    return bicgstab_solve(c, SellOp{A.sell_slice.p, A.sell_ind.p, A.sell_val.p}, A.cols, d_b, dinv, d_x_ext, kp, tc, its);
+  }
   switch (A.vec_width) {
     case 2: return bicgstab_solve(c, CsrOp<2>{A.ptr, A.ind, A.val}, A.cols, d_b, dinv, d_x_ext, kp, tc, its);
     case 4: return bicgstab_solve(c, CsrOp<4>{A.ptr, A.ind, A.val}, A.cols, d_b, dinv, d_x_ext, kp, tc, its);
@@ -214,6 +342,7 @@ int ufe_b200_csr_register(ufe_b200_handle h, int id, int m_glob, int n_glob, int
   if (it != c->csr.end()) { delete it->second; c->csr.erase(it); }
   DevCsr* A = new DevCsr();
   int rc = csr_upload(c, *A, m_glob, n_glob, m_loc, i1, n_loc, j1, ptr, ind, val, false);
+  if (!rc) rc = csr_sell_build(c, *A);      // registered matrices are multiplied repeatedly (the SpMV seam)
   if (rc) { delete A; return rc; }
   c->csr[id] = A;
   return 0;
@@ -225,6 +354,7 @@ int ufe_b200_csr_update_values(ufe_b200_handle h, int id, const double* val) {
   UFE_CHECK(it != c->csr.end(), "ufe_b200_csr_update_values: matrix %d is not registered", id);
   UFE_CUDA(cudaSetDevice(c->device));
   UFE_CUDA(cudaMemcpyAsync(it->second->val, val, sizeof(double) * it->second->nnz, cudaMemcpyHostToDevice, c->stream));
+  UFE_TRY(csr_sell_refresh(c, *it->second));
   UFE_CUDA(cudaStreamSynchronize(c->stream));
   return 0;
 }

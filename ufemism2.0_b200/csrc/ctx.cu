@@ -303,6 +303,15 @@ int ufe_b200_timer_stop(ufe_b200_handle h, double* ms) {
   *ms = f;
   return 0;
 }
+int ufe_b200_l2_flush(ufe_b200_handle h) {
+  Ctx* c = reinterpret_cast<Ctx*>(h);
+  UFE_CHECK(c, "ufe_b200_l2_flush: NULL handle");
+  UFE_CUDA(cudaSetDevice(c->device));
+  constexpr size_t kBytes = size_t(512) << 20;    // 4 x the 126 MB L2 of a B200
+  if (!c->l2_flush.p) UFE_TRY(c->l2_flush.alloc(kBytes));
+  UFE_CUDA(cudaMemsetAsync(c->l2_flush.p, 0, kBytes, c->stream));
+  return 0;
+}
 int ufe_b200_host_register(void* ptr, size_t bytes) {
   cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterDefault);
   if (e != cudaSuccess) {

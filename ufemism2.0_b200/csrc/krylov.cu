@@ -8,7 +8,7 @@ int Krylov::ensure(Ctx* c, int m_loc, int n_ext) {
   UFE_TRY(R.alloc(m_loc)); UFE_TRY(RP.alloc(m_loc)); UFE_TRY(V.alloc(m_loc)); UFE_TRY(T.alloc(m_loc));
   UFE_TRY(P.alloc(n_ext)); UFE_TRY(S.alloc(n_ext));
   grid = c->sm_count * 8;
-  UFE_TRY(partials.alloc((size_t)4 * grid));
+  UFE_TRY(partials.alloc((size_t)8 * grid));
   if (!scal.p) {
     UFE_TRY(scal.alloc(KS_COUNT)); UFE_TRY(counter.alloc(4)); UFE_TRY(flags.alloc(KF_COUNT));
     UFE_CUDA(cudaMemsetAsync(counter.p, 0, 4 * sizeof(unsigned), c->stream));

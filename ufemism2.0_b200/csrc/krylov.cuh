@@ -17,7 +17,7 @@
 namespace ufe {
 
 // device scalars; two parity banks of 8 doubles + persistent slots
-enum { KS_RHO = 0, KS_RR = 1, KS_D1 = 2, KS_ST = 3, KS_TT = 4, KS_BANK = 8, KS_RR0 = 16, KS_RINIT = 17, KS_RTOL = 18, KS_ABSTOL = 19, KS_COUNT = 24 };
+enum { KS_RHO = 0, KS_RR = 1, KS_D1 = 2, KS_ST = 3, KS_TT = 4, KS_SS = 5, KS_SRP = 6, KS_TRP = 7 /* 5-7: merged reduction of mg.cu */, KS_BANK = 8, KS_RR0 = 16, KS_RINIT = 17, KS_RTOL = 18, KS_ABSTOL = 19, KS_COUNT = 24 };
 enum { KF_DONE = 0, KF_ITS = 1, KF_REASON = 2, KF_COUNT = 4 };
 
 struct Krylov {
@@ -105,6 +105,31 @@ struct CsrOp {
 #pragma unroll
     for (int o = W / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o, W);
     return s;
+  }
+};
+
+// the same matrix as a sliced-ELL copy (DevCsr::sell_*): one row per thread, a warp = one slice of 32 rows whose entries are stored column-major,
+// so every val / ind load of the warp is one full 256 B / 128 B segment and each thread keeps several independent loads in flight
+// (north_star (b): "coalesced, vectorised loads"; the vector-per-row kernel above has one entry per thread in flight, which is what holds it at
+// ~0.4 of the copy bandwidth).  Padding slots hold val = 0 and a column of the same row.
+struct SellOp {
+  static constexpr int W = 1;
+  const int* __restrict__ slice;
+  const int* __restrict__ ind;
+  const double* __restrict__ val;
+  __device__ __forceinline__ double row(int r, int, const double* __restrict__ x) const {
+    const int s = r >> 5, b = slice[s], w = (slice[s + 1] - b) >> 5;
+    const int* __restrict__ ip = ind + b + (r & 31);
+    const double* __restrict__ vp = val + b + (r & 31);
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int k = 0;
+    for (; k + 3 < w; k += 4) {
+      const int j0 = ip[k * 32], j1 = ip[(k + 1) * 32], j2 = ip[(k + 2) * 32], j3 = ip[(k + 3) * 32];
+      const double v0 = vp[k * 32], v1 = vp[(k + 1) * 32], v2 = vp[(k + 2) * 32], v3 = vp[(k + 3) * 32];
+      s0 += v0 * x[j0]; s1 += v1 * x[j1]; s2 += v2 * x[j2]; s3 += v3 * x[j3];
+    }
+    for (; k < w; ++k) s0 += vp[k * 32] * x[ip[k * 32]];
+    return (s0 + s1) + (s2 + s3);
   }
 };
 

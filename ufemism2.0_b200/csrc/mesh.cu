@@ -216,7 +216,8 @@ int ufe_b200_apply_operator(ufe_b200_handle h, int op, const double* d_in, doubl
   UFE_CHECK(c && c->mesh && op >= 0 && op < UFE_OP_COUNT && c->mesh->op[op].valid, "ufe_b200_apply_operator: operator %d not available", op);
   UFE_CHECK(ncols >= 1, "ufe_b200_apply_operator: ncols must be >= 1");
   UFE_CUDA(cudaSetDevice(c->device));
-  const DevCsr& A = c->mesh->op[op];
+  DevCsr& A = c->mesh->op[op];
+  if (!A.has_sell()) UFE_TRY(csr_sell_build(c, A));     // first product with this operator: the sliced-ELL copy every later one streams
   const int n_loc = A.cols.n_loc(), n_ext = A.cols.n_ext();
   DBuf<double> x, y;
   UFE_TRY(x.alloc((size_t)n_ext * ncols)); UFE_TRY(y.alloc((size_t)A.m_loc * ncols));

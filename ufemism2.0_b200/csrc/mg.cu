@@ -829,6 +829,43 @@ __global__ void k_ksmg_dot2(int m, int iter, const double* __restrict__ s, const
   grid_sum<2>(acc, partials, counter, scal + (iter & 1) * KS_BANK + KS_ST);
 }
 
+// Several ranks: every separate reduction is one more ncclAllReduce on the critical path, so the second half of the iteration carries all five
+// inner products of S and T at once -- ST = (s, t), TT = (t, t), SS = (s, s), SRP = (s, r~), TRP = (t, r~) (adjacent slots KS_ST..KS_TRP) --
+// and the update forms the next RHO = (r, r~) = SRP - omega TRP and RR = (r, r) = SS - 2 omega ST + omega^2 TT from them instead of reducing again:
+// two all-reduces per iteration instead of three.  The expansion of RR loses log10( SS / RR) digits to cancellation -- one or two per iteration at
+// the contraction rates of this preconditioner -- which is why the single-rank path keeps the direct sums.
+__global__ void k_ksmg_dot5(int m, int iter, const double* __restrict__ s, const double* __restrict__ t, const double* __restrict__ rp, double* scal,
+                            double* partials, unsigned* counter, const int* flags) {
+  if (flags[KF_DONE]) return;
+  double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x) {
+    const double sv = s[i], tv = t[i], rv = rp[i];
+    acc[0] += sv * tv; acc[1] += tv * tv; acc[2] += sv * sv; acc[3] += sv * rv; acc[4] += tv * rv;
+  }
+  grid_sum<5>(acc, partials, counter, scal + (iter & 1) * KS_BANK + KS_ST);
+}
+// x += alpha P + omega S;  R = S - omega T;  RHO, RR of the next iteration from the five inner products (no reduction)
+__global__ void k_ksmg_update_xr5(int m, int iter, double* __restrict__ x_own, const double* __restrict__ P_own, const double* __restrict__ S_own,
+                                  const double* __restrict__ T, double* __restrict__ R, double* scal, const int* flags) {
+  if (flags[KF_DONE]) return;
+  const int p = iter & 1;
+  const double* cur = scal + p * KS_BANK;
+  const double alpha = cur[KS_RHO] / cur[KS_D1];
+  const double omega = (cur[KS_TT] == 0.0) ? 0.0 : cur[KS_ST] / cur[KS_TT];
+  const bool bad = !(isfinite(alpha) && isfinite(omega));
+  if (blockIdx.x == 0 && threadIdx.x == 0) {          // the other bank: nobody reads it during this kernel
+    double* nxt = scal + (1 - p) * KS_BANK;
+    nxt[KS_RHO] = bad ? nan("") : cur[KS_SRP] - omega * cur[KS_TRP];
+    nxt[KS_RR] = bad ? nan("") : fmax(0.0, cur[KS_SS] - 2.0 * omega * cur[KS_ST] + omega * omega * cur[KS_TT]);
+  }
+  if (bad) return;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x) {
+    const double s = S_own[i];
+    x_own[i] += alpha * P_own[i] + omega * s;
+    R[i] = s - omega * T[i];
+  }
+}
+
 // =====================================================================================================================
 // host: cycle
 // =====================================================================================================================
@@ -1256,6 +1293,9 @@ int bicgstab_solve_mg(Ctx* c, Mg& G, const BlkLauncher& A, const Range& rr, cons
   int* h_flags = reinterpret_cast<int*>(c->h_pinned);
   const bool monitor = getenv("UFE_B200_KSP_MONITOR") != nullptr;   // like -ksp_monitor: preconditioned residual norm per iteration
   const int restart_every = 40;
+  // several ranks: merged reductions (k_ksmg_dot5); UFE_B200_KSP_MERGED=0/1 overrides (1 on one rank is how the tests compare the two recurrences)
+  const char* merged_env = getenv("UFE_B200_KSP_MERGED");
+  const bool merged = merged_env ? atoi(merged_env) != 0 : c->nranks > 1;
   int total_its = 0, use_guess = kp.use_guess, breakdowns = 0;
   for (int attempt = 0;; ++attempt) {
     const int maxit = std::min(kp.maxit - total_its, restart_every);
@@ -1295,13 +1335,19 @@ int bicgstab_solve_mg(Ctx* c, Mg& G, const BlkLauncher& A, const Range& rr, cons
         UFE_TRY(halo_exchange(c, rr, K.S.p));
         spmv_plain(K.S.p, K.W1.p);
         UFE_TRY(mg_apply(c, G, K.W1.p, K.T.p));
-        { UFE_LAUNCH(c, TC_KRYLOV_VEC); k_ksmg_dot2<<<gv, kBlock, 0, st>>>(m, iter, S_own, K.T.p, K.scal.p, K.partials.p, K.counter.p + 2, K.flags.p); }
-        UFE_TRY(allreduce_sum(c, K.scal.p + p * KS_BANK + KS_ST, 2));
-        {
-          UFE_LAUNCH(c, TC_KRYLOV_VEC);
-          k_ks_update_xr<<<gv, kBlock, 0, st>>>(m, iter, x_own, P_own, S_own, K.T.p, K.R.p, K.RP.p, K.scal.p, K.partials.p, K.counter.p + 3, K.flags.p);
+        if (merged) {
+          { UFE_LAUNCH(c, TC_KRYLOV_VEC); k_ksmg_dot5<<<gv, kBlock, 0, st>>>(m, iter, S_own, K.T.p, K.RP.p, K.scal.p, K.partials.p, K.counter.p + 2, K.flags.p); }
+          UFE_TRY(allreduce_sum(c, K.scal.p + p * KS_BANK + KS_ST, 5));
+          { UFE_LAUNCH(c, TC_KRYLOV_VEC); k_ksmg_update_xr5<<<gv, kBlock, 0, st>>>(m, iter, x_own, P_own, S_own, K.T.p, K.R.p, K.scal.p, K.flags.p); }
+        } else {
+          { UFE_LAUNCH(c, TC_KRYLOV_VEC); k_ksmg_dot2<<<gv, kBlock, 0, st>>>(m, iter, S_own, K.T.p, K.scal.p, K.partials.p, K.counter.p + 2, K.flags.p); }
+          UFE_TRY(allreduce_sum(c, K.scal.p + p * KS_BANK + KS_ST, 2));
+          {
+            UFE_LAUNCH(c, TC_KRYLOV_VEC);
+            k_ks_update_xr<<<gv, kBlock, 0, st>>>(m, iter, x_own, P_own, S_own, K.T.p, K.R.p, K.RP.p, K.scal.p, K.partials.p, K.counter.p + 3, K.flags.p);
+          }
+          UFE_TRY(allreduce_sum(c, K.scal.p + (1 - p) * KS_BANK + KS_RHO, 2));
         }
-        UFE_TRY(allreduce_sum(c, K.scal.p + (1 - p) * KS_BANK + KS_RHO, 2));
       }
       if (iter >= maxit) {
         UFE_LAUNCH(c, TC_KRYLOV_VEC);

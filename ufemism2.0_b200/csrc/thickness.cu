@@ -287,6 +287,7 @@ static int ensure_th_pattern(Ctx* c) {
   UFE_TRY(T.M.ind_buf.alloc(nnz)); UFE_TRY(T.M.val_buf.alloc(nnz)); UFE_TRY(T.Mval0.alloc(nnz));
   T.M.ind = T.M.ind_buf.p; T.M.val = T.M.val_buf.p;
   T.M.m_loc = n; T.M.nnz = nnz; T.M.rows = M.a; T.M.cols = M.a; T.M.vec_width = 8; T.M.valid = true;
+  T.M.sell_src_ptr = nullptr;   // a new pattern: the sliced-ELL copy of the previous one is void
   { UFE_LAUNCH(c, TC_THICKNESS); k_th_fill_ind<<<grid, 128, 0, c->stream>>>(mv, T.M.ptr, T.M.ind); }
   UFE_CUDA(cudaGetLastError());
   T.pattern = true;

@@ -508,6 +508,17 @@ module ufe_b200_mod
       integer(c_int) :: ierr
     end function
 
+    ! remap_DIVA_solver / remap_SSA_solver (DIVA_main.f90:115-222, SSA_main.f90:247-311) on a device-resident solver state: h_old holds the old mesh
+    ! and state, h_new the new mesh; map_ptr / map_ind / map_val = c_loc of the rank's rows of the Atlas map (type_map%M) as CSR
+    function c_ufe_b200_remap_velocity_solver( h_old, h_new, approximation, m_loc, map_ptr, map_ind, map_val) &
+      bind(C, name='ufe_b200_remap_velocity_solver') result( ierr)
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h_old, h_new
+      integer(c_int), value :: approximation, m_loc
+      type(c_ptr), value :: map_ptr, map_ind, map_val
+      integer(c_int) :: ierr
+    end function
+
     ! set_ice_velocities_to_{SIA,SSA,SIASSA,DIVA}_results (conservation_of_momentum_main.f90:311-511); out = c_loc of a ufe_b200_ice_velocities
     ! (c_loc's of ice%u_3D_b, v_3D_b, du_dx_3D, du_dy_3D, du_dz_3D, dv_dx_3D, dv_dy_3D, dv_dz_3D, dw_dx_3D, dw_dy_3D; c_null_ptr = skipped);
     ! approximation: 0 'SSA', 1 'DIVA', 2 'SIA', 3 'SIA/SSA'; hybrid_scheme: 0 'add', 1 'add_SIA_reduced'

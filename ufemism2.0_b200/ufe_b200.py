@@ -16,8 +16,8 @@ c_dp = C.POINTER(C.c_double)
 c_ip = C.POINTER(C.c_int32)
 
 # enumerations of include/ufe_b200.h
-KSP_BICGSTAB, KSP_CG = 0, 1
-PC_JACOBI, PC_NONE, PC_BJACOBI2, PC_NEUMANN, PC_MG = 0, 1, 2, 3, 4
+KSP_BICGSTAB = 0
+PC_JACOBI, PC_NONE, PC_MG = 0, 1, 4
 BC_INFINITE, BC_ZERO, BC_PERIODIC_ISMIP_HOM, BC_INFINITE_SSA_ICESTREAM = 0, 1, 2, 3
 (SLID_NO_SLIDING, SLID_WEERTMAN, SLID_COULOMB, SLID_BUDD, SLID_TSAI2015, SLID_SCHOOF2005, SLID_ZOET_IVERSON,
  SLID_IDEALISED_SSA_ICESTREAM) = range(8)
@@ -279,6 +279,7 @@ def lib():
                                                     C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     L.ufe_b200_calc_pc_truncation_error_noalloc.argtypes = [H, C.c_int] + [C.c_double] * 4 + [c_dp, c_dp, c_ip, c_ip, c_dp, c_dp, c_ip, C.POINTER(C.c_double),
                                                             C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    L.ufe_b200_remap_velocity_solver.argtypes = [H, H, C.c_int, C.c_int, c_ip, c_ip, c_dp]
     L.ufe_b200_set_ice_velocities.argtypes = [H, C.c_int, C.c_int, C.POINTER(IceVelocities)]
     L.ufe_b200_set_state_resident.argtypes = [H, C.c_int]
     L.ufe_b200_pc_reference_loop.argtypes = [H, C.c_int, C.c_double]
@@ -301,6 +302,7 @@ def lib():
     L.ufe_b200_timing_get.argtypes = [H, C.c_char_p, c_dp, C.POINTER(C.c_longlong)]
     L.ufe_b200_timing_reset.argtypes = [H]
     L.ufe_b200_timer_start.argtypes = [H]
+    L.ufe_b200_l2_flush.argtypes = [H]
     L.ufe_b200_timer_stop.argtypes = [H, c_dp]
     L.ufe_b200_host_register.argtypes = [C.c_void_p, C.c_size_t]
     L.ufe_b200_host_unregister.argtypes = [C.c_void_p]
@@ -317,10 +319,10 @@ ABI_SYMBOLS = [
     "ufe_b200_set_mg_params", "ufe_b200_get_mg_info", "ufe_b200_mg_host_transfer", "ufe_b200_mg_host_transfer_get", "ufe_b200_mg_host_transfer_parts", "ufe_b200_mg_host_transfer_parts_get",
     "ufe_b200_solve_DIVA", "ufe_b200_solve_SSA", "ufe_b200_velocity_upload", "ufe_b200_velocity_solve_resident",
     "ufe_b200_velocity_download", "ufe_b200_thickness_upload", "ufe_b200_pc_step_resident", "ufe_b200_pc_step",
-    "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA", "ufe_b200_calc_pc_truncation_error", "ufe_b200_calc_pc_truncation_error_noalloc", "ufe_b200_apply_grounded_fractions_to_bed_roughness", "ufe_b200_set_ice_velocities", "ufe_b200_calc_secondary_velocities", "ufe_b200_calc_vertical_velocities", "ufe_b200_set_state_resident", "ufe_b200_pc_reference_loop", "ufe_b200_set_mg_option", "ufe_b200_pc_set_model_thickness", "ufe_b200_alter_resident", "ufe_b200_pc_download", "ufe_b200_determine_masks", "ufe_b200_calc_effective_thickness",
+    "ufe_b200_thickness_download", "ufe_b200_calc_dHi_dt", "ufe_b200_dHi_dt_finish", "ufe_b200_solve_SIA", "ufe_b200_calc_pc_truncation_error", "ufe_b200_calc_pc_truncation_error_noalloc", "ufe_b200_apply_grounded_fractions_to_bed_roughness", "ufe_b200_set_ice_velocities", "ufe_b200_remap_velocity_solver", "ufe_b200_calc_secondary_velocities", "ufe_b200_calc_vertical_velocities", "ufe_b200_set_state_resident", "ufe_b200_pc_reference_loop", "ufe_b200_set_mg_option", "ufe_b200_pc_set_model_thickness", "ufe_b200_alter_resident", "ufe_b200_pc_download", "ufe_b200_determine_masks", "ufe_b200_calc_effective_thickness",
                "ufe_b200_calc_grounded_fractions", "ufe_b200_calc_critical_timestep_adv", "ufe_b200_calc_critical_timestep_SIA", "ufe_b200_alter_params_defaults", "ufe_b200_geometry_resident", "ufe_b200_alter_ice_thickness",
                "ufe_b200_calc_and_apply_spill_over_flux",
-    "ufe_b200_timing_enable", "ufe_b200_timing_get", "ufe_b200_timing_reset", "ufe_b200_timer_start", "ufe_b200_timer_stop",
+    "ufe_b200_timing_enable", "ufe_b200_timing_get", "ufe_b200_timing_reset", "ufe_b200_timer_start", "ufe_b200_timer_stop", "ufe_b200_l2_flush",
     "ufe_b200_host_register", "ufe_b200_host_unregister"]
 
 
