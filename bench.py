@@ -588,11 +588,11 @@ def run_b200(args, rank, world, rdv, log):
             B_streamed = (mg_info["fine_bytes"] if mg_info else blk_b.value) + 8 * rows_loc * 5
         kernel_name = ("k_mg_sweep level 0 (stiffness-matrix pass fused with block-Jacobi update / residual inside the multigrid cycle)" if top == "mg_fine"
                        else "k_spmv_blk (stiffness-matrix SpMV with fused Jacobi + dot products inside BiCGStab)")
-        # roofline.traffic: DRAM bytes per launch of that kernel from the committed `ncu --set full` capture (profiles/r01_ncu_traffic.json), valid
+        # roofline.traffic: DRAM bytes per launch of that kernel from the committed `ncu --set full` capture (profiles/r02_ncu_traffic.json), valid
         # for the mesh the capture was taken on (one rank, same triangle count); null otherwise
         traffic, traffic_src = None, None
         try:
-            cap = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))["k_mg_sweep_level0" if top == "mg_fine" else "k_spmv_blk"]
+            cap = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")))["k_mg_sweep_level0" if top == "mg_fine" else "k_spmv_blk"]
             if world == 1 and cap.get("n_triangles") == int(m.nTri) and "dram_bytes_read" in cap:
                 traffic, traffic_src = int(cap["dram_bytes_read"]) + int(cap["dram_bytes_write"]), cap["report"]
         except (OSError, KeyError, ValueError):

@@ -42,3 +42,23 @@ for cls in ["spmv_stiffness", "krylov_vec", "assembly", "column", "tri", "epilog
     print(f"  {cls:16s} {ms:10.2f} ms  {n:7d} launches{extra}")
 ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
 print("speed max", np.hypot(arrs["u_vav_b"], arrs["v_vav_b"]).max())
+
+# the variants of the two gather kernels of the viscosity iteration (velocity.cu), each from the same zero state: kernel time per launch and the result
+if os.environ.get("PROBE_VARIANTS", "1") == "1":
+    ref = None
+    for name, env in (("interleaved copies + shared-memory columns (default)", {}), ("reference-layout gathers", {"UFE_B200_INTERLEAVE": "0"}),
+                      ("local-memory columns", {"UFE_B200_VERTEX_SMEM": "0"}), ("round-1 kernels", {"UFE_B200_INTERLEAVE": "0", "UFE_B200_VERTEX_SMEM": "0"})):
+        for k in ("UFE_B200_INTERLEAVE", "UFE_B200_VERTEX_SMEM"):
+            os.environ.pop(k, None)
+        os.environ.update(env)
+        for a_ in arrs.values():
+            a_[...] = 0.0
+        ub.check(L.ufe_b200_velocity_upload(ctx.h, C.byref(ice), C.byref(st)))
+        L.ufe_b200_timing_reset(ctx.h)
+        ub.check(L.ufe_b200_velocity_solve_resident(ctx.h, C.byref(cfg), 1, C.byref(a), C.byref(b)))
+        ub.check(L.ufe_b200_velocity_download(ctx.h, C.byref(st)))
+        u = arrs["u_vav_b"].copy()
+        ref = u if ref is None else ref
+        col, asm = ctx.timing("column"), ctx.timing("assembly")
+        print(f"{name:55s}: column {col[0] / a.value:.3f} ms / viscosity iteration ({col[1]} launches), assembly {asm[0] / a.value:.3f} ms ({asm[1]} launches), "
+              f"{a.value} visc its, {b.value} Krylov its, rel diff of u vs first variant {np.linalg.norm(u - ref) / np.linalg.norm(ref):.2e}")

@@ -172,13 +172,33 @@ __global__ void k_driving_stress(int n, int off, const int* __restrict__ ptr, co
 }
 
 // ---- a-grid (vertex) kernels --------------------------------------------------------------------------------
+// out( i,k) [i-major, k fastest] = in( k,i) [the reference's layout]  (RECIP: zeta_k / max( floor, in)) over a whole extended range, through a
+// shared-memory tile so that both the reads and the writes are full segments
+template <bool RECIP>
+__global__ void __launch_bounds__(128) k_layers_interleave(int n_ext, int nz, const double* __restrict__ in, const double* __restrict__ zeta, double floor_,
+                                                           double* __restrict__ out) {
+  extern __shared__ double tile[];   // [128][nz + 1] (odd pitch for nz = 12: no bank conflicts on the column-wise fill)
+  const int pitch = nz + 1;
+  for (long long base = (long long)blockIdx.x * 128; base < n_ext; base += (long long)gridDim.x * 128) {
+    const int cnt = (int)min((long long)128, n_ext - base);
+    if ((int)threadIdx.x < cnt)
+      for (int k = 0; k < nz; ++k) {
+        const double v = in[(size_t)k * n_ext + base + threadIdx.x];
+        tile[threadIdx.x * pitch + k] = RECIP ? zeta[k] / fmax(floor_, v) : v;
+      }
+    __syncthreads();
+    for (int t = threadIdx.x; t < cnt * nz; t += 128) out[(size_t)base * nz + t] = tile[(t / nz) * pitch + t % nz];
+    __syncthreads();
+  }
+}
+
 struct VertexArgs {
   int n, off, n_ext, nb_ext, nz, vi1, nV;
   const int* ptr; const int* ind;                      // b->a pattern (M_map_b_a = M_ddx_b_a = M_ddy_b_a)
   const double* w_map; const double* w_ddx; const double* w_ddy;
   const double* zeta; const double* Vy;
   const double* u; const double* v; const double* u_base; const double* v_base; const double* tau_bx; const double* tau_by;
-  const double* eta_3D_b;
+  const double* eta_3D_b; const double* rzT;     // rzT != nullptr: the interleaved zeta / eta copy is gathered instead of eta_3D_b
   const double* Hi; const double* A_flow; const double* A_flow_vav;
   const double* tauc; const double* beta_sq; const double* alpha_sq; const double* neff;
   double* du_dx; double* du_dy; double* dv_dx; double* dv_dy; double* du_dz_3D; double* dv_dz_3D;
@@ -192,10 +212,21 @@ struct VertexArgs {
 // registers per thread); NZ = 0: run-time nz, the arrays are local memory (128 registers + 784 B of stack).  Same operations, same order.
 // Measured at 4 M vertices: 6.4 ms for NZ = 12 against 5.8 ms for NZ = 0 -- the kernel is bound by the latency of the triangle-column
 // gathers, and the register version runs fewer warps per SM; so NZ = 0 is what runs (UFE_B200_VERTEX_NZ12 selects the other for profiling).
-template <int NZ, int MB = 6>
+// SMEM: the three per-column arrays live in shared memory ([k][thread], conflict-free) instead of local memory: the ncu capture of round 2
+// (profiles/r02_step_kernels_4M_ncu.md) showed 864 B of stack per thread going through L1 to DRAM -- 4.1 GB written and 6.3 GB read per launch
+// against 2.6 GB of algorithmic traffic.
+template <bool SMEM, int CAP>
+struct ColumnArray {
+  double loc[SMEM ? 1 : CAP];
+  double* sh;
+  __device__ __forceinline__ double& operator[](int k) { return SMEM ? sh[k * 128] : loc[k]; }
+};
+template <int NZ, int MB = 6, bool SMEM = false>
 __global__ void __launch_bounds__(128, MB) k_vertex_diva(VertexArgs a, VelPar p) {
   constexpr int kCap = NZ > 0 ? NZ : kMaxNz;
-  double dzu[kCap], dzv[kCap], eta[kCap];
+  extern __shared__ double s_col[];   // SMEM: [3][nz][128]
+  ColumnArray<SMEM, kCap> dzu, dzv, eta;
+  if (SMEM) { dzu.sh = s_col + threadIdx.x; dzv.sh = dzu.sh + a.nz * 128; eta.sh = dzv.sh + a.nz * 128; }
   for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < a.n; r += (long long)gridDim.x * blockDim.x) {
     const size_t i = a.off + r;
     const int nz = NZ > 0 ? NZ : a.nz;
@@ -209,11 +240,21 @@ __global__ void __launch_bounds__(128, MB) k_vertex_diva(VertexArgs a, VelPar p)
       du_dx += wx * uj; du_dy += wy * uj; dv_dx += wx * vj; dv_dy += wy * vj;
       ub += wm * a.u_base[tj]; vb += wm * a.v_base[tj];
       const double tbx = a.tau_bx[tj], tby = a.tau_by[tj];
+      if (a.rzT) {
+        const double* __restrict__ rz = a.rzT + (size_t)tj * nz;     // zeta_k / eta of this triangle's column: contiguous
 #pragma unroll
-      for (int k = 0; k < nz; ++k) {
-        const double e = fmax(p.visc_eff_min, a.eta_3D_b[(size_t)k * a.nb_ext + tj]);
-        dzu[k] += wm * (tbx * a.zeta[k] / e);
-        dzv[k] += wm * (tby * a.zeta[k] / e);
+        for (int k = 0; k < nz; ++k) {
+          const double q_k = rz[k];
+          dzu[k] += wm * (tbx * q_k);
+          dzv[k] += wm * (tby * q_k);
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < nz; ++k) {
+          const double e = fmax(p.visc_eff_min, a.eta_3D_b[(size_t)k * a.nb_ext + tj]);
+          dzu[k] += wm * (tbx * a.zeta[k] / e);
+          dzv[k] += wm * (tby * a.zeta[k] / e);
+        }
       }
     }
     const double hs = du_dx * du_dx + dv_dy * dv_dy + du_dx * dv_dy + 0.25 * (du_dy + dv_dx) * (du_dy + dv_dx);
@@ -510,6 +551,7 @@ struct TriArgs {
   const int* ptr; const int* ind;                // a->b pattern (M_map_a_b = M_ddx_a_b = M_ddy_a_b), 3 entries per row
   const double* w_map; const double* w_ddx; const double* w_ddy;
   const double* N_a; const double* beta_a; const double* beta_eff_a; const double* eta_3D_a; const double* F1_3D_a; const double* F2_3D_a;
+  const double* etaT;                            // != nullptr: layer-interleaved copy of eta_3D_a
   const double* fraction_gr_b; const double* tau_dx; const double* tau_dy;
   double* N_b; double* dN_dx_b; double* dN_dy_b; double* beta_b; double* beta_eff_b; double* eta_3D_b; double* F1_3D_b; double* F2_3D_b;
 };
@@ -535,7 +577,7 @@ __global__ void __launch_bounds__(128) k_tri_assemble(TriArgs t, StiffArgs s, Ve
         const bool need_f = (k == 0) || t.final_pass || p.diagnostics;
         for (int q = q1; q < q2; ++q) {
           const size_t j = (size_t)k * t.na_ext + t.ind[q];
-          e += t.w_map[q] * t.eta_3D_a[j];
+          e += t.w_map[q] * (t.etaT ? t.etaT[(size_t)t.ind[q] * t.nz + k] : t.eta_3D_a[j]);
           if (need_f) { f2 += t.w_map[q] * t.F2_3D_a[j]; f1 += t.w_map[q] * t.F1_3D_a[j]; }
         }
         t.eta_3D_b[(size_t)k * t.nb_ext + i] = e;
@@ -975,6 +1017,15 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
   ta.N_b = V.N_b.p; ta.dN_dx_b = V.dN_dx_b.p; ta.dN_dy_b = V.dN_dy_b.p; ta.beta_b = V.beta_b.p; ta.beta_eff_b = V.beta_eff_b.p;
   ta.eta_3D_b = V.eta_3D_b.p; ta.F1_3D_b = V.F1_3D_b.p; ta.F2_3D_b = V.F2_3D_b.p;
   StiffArgs sa = stiff_args(c, csr_values_unneeded(c, cfg));
+  // layer-interleaved work copies of the two gathered 3-D fields (UFE_B200_INTERLEAVE=0: gather the reference layout directly, as before)
+  const bool interleave_on = !(getenv("UFE_B200_INTERLEAVE") && atoi(getenv("UFE_B200_INTERLEAVE")) == 0);   // read per solve: scripts/perf_probe.py toggles it
+  const bool interleave = DIVA && interleave_on;
+  const size_t tile_bytes = sizeof(double) * 128 * (size_t)(nz + 1);
+  va.rzT = nullptr; ta.etaT = nullptr;
+  if (interleave) {
+    UFE_TRY(V.rzT_b.alloc((size_t)M.b.n_ext() * nz)); UFE_TRY(V.etaT_a.alloc((size_t)M.a.n_ext() * nz));
+    va.rzT = V.rzT_b.p; ta.etaT = V.etaT_a.p;
+  }
 
   // adaptive relaxation (DIVA_solver_infinite_slab.f90:121-131)
   double L2_uv = 1e9, relax = cfg->visc_it_relax, eps0 = cfg->Glens_flow_law_epsilon_sq_0;
@@ -991,6 +1042,10 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
       UFE_TRY(halo_exchange(c, M.b, V.u_base.p)); UFE_TRY(halo_exchange(c, M.b, V.v_base.p));
       UFE_TRY(halo_exchange(c, M.b, V.tau_bx.p)); UFE_TRY(halo_exchange(c, M.b, V.tau_by.p));
       UFE_TRY(halo_exchange(c, M.b, V.eta_3D_b.p, nz));
+      if (interleave) {
+        UFE_LAUNCH(c, TC_COLUMN);
+        k_layers_interleave<true><<<grid_for(c, M.b.n_ext(), 128), 128, tile_bytes, st>>>(M.b.n_ext(), nz, V.eta_3D_b.p, M.zeta.p, p.visc_eff_min, V.rzT_b.p);
+      }
     }
     {
       UFE_LAUNCH(c, TC_COLUMN);
@@ -1000,7 +1055,17 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
         // registers capped for 6 resident blocks per SM (80 registers): the kernel is bound by gather latency, more warps beat fewer spills
         // (column class per step at 4 M vertices: 6.5 ms with 4 blocks / 128 registers, 5.25 ms with 6, 5.4 ms with 8)
         static const int mb = getenv("UFE_B200_VERTEX_MB") ? atoi(getenv("UFE_B200_VERTEX_MB")) : 6;
-        if (mb >= 8) k_vertex_diva<0, 8><<<g_a, 128, 0, st>>>(va, p);
+        const bool col_smem = !(getenv("UFE_B200_VERTEX_SMEM") && atoi(getenv("UFE_B200_VERTEX_SMEM")) == 0);
+        const size_t col_bytes = sizeof(double) * 3 * 128 * (size_t)nz;    // 36 KB at nz = 12: 4 blocks per SM leave ~100 KB of L1 for the gathers
+        if (col_smem) {
+          static bool attr_set = false;
+          if (!attr_set) {
+            UFE_CUDA(cudaFuncSetAttribute(k_vertex_diva<0, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * 3 * 128 * kMaxNz)));
+            attr_set = true;
+          }
+          k_vertex_diva<0, 4, true><<<g_a, 128, col_bytes, st>>>(va, p);
+        }
+        else if (mb >= 8) k_vertex_diva<0, 8><<<g_a, 128, 0, st>>>(va, p);
         else if (mb >= 6) k_vertex_diva<0, 6><<<g_a, 128, 0, st>>>(va, p);
         else k_vertex_diva<0, 4><<<g_a, 128, 0, st>>>(va, p);
       }
@@ -1009,6 +1074,10 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
     if (DIVA) {
       UFE_TRY(halo_exchange(c, M.a, V.beta_eff_a.p)); UFE_TRY(halo_exchange(c, M.a, V.eta_3D_a.p, nz));
       UFE_TRY(halo_exchange(c, M.a, V.F2_3D_a.p, nz)); UFE_TRY(halo_exchange(c, M.a, V.F1_3D_a.p, nz));
+      if (interleave) {
+        UFE_LAUNCH(c, TC_ASSEMBLY);
+        k_layers_interleave<false><<<grid_for(c, M.a.n_ext(), 128), 128, tile_bytes, st>>>(M.a.n_ext(), nz, V.eta_3D_a.p, M.zeta.p, 0.0, V.etaT_a.p);
+      }
     }
     {
       UFE_LAUNCH(c, TC_ASSEMBLY);
@@ -1204,6 +1273,9 @@ int ufe_b200_set_mg_option(ufe_b200_handle h, const char* name, double value) {
   else if (!strcmp(name, "tail_max")) { p.tail_max = (int)value; rebuild = true; }
   else if (!strcmp(name, "tail_cluster")) { p.tail_cluster = (int)value; rebuild = true; }
   else if (!strcmp(name, "coarse_sweeps")) p.coarse_sweeps = (int)value;
+  else if (!strcmp(name, "max_levels")) { p.max_levels = (int)value; rebuild = true; }     // a shorter hierarchy ends in coarse_sweeps sweeps
+  else if (!strcmp(name, "dense_max")) { p.dense_max = (int)value; rebuild = true; }
+  else if (!strcmp(name, "w_levels")) p.w_levels = (int)value;
   else if (!strcmp(name, "fuse")) p.fuse = (int)value;
   else if (!strcmp(name, "use_graph")) p.use_graph = (int)value;
   else if (!strcmp(name, "nu_pre")) p.nu_pre = (int)value;          // 0 allowed here: no pre-smoothing (the right-hand side itself is restricted)

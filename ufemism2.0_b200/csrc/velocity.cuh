@@ -23,6 +23,10 @@ struct Velocity {
   DBuf<double> N_b, dN_dx_b, dN_dy_b, beta_b, beta_eff_b, F1_3D_b, F2_3D_b;
   // --- state on the a-grid
   DBuf<double> du_dx, du_dy, dv_dx, dv_dy, du_dz_3D, dv_dz_3D, eta_3D_a, eta_vav, N_a, F1_3D_a, F2_3D_a, beta_a, beta_eff_a;
+  // --- layer-interleaved work copies ([i][k] instead of the reference's [k][i]) of the two 3-D fields the kernels GATHER through the mesh operators:
+  // a neighbour's column is then one 8 nz-byte segment instead of nz sectors (velocity.cu: k_layers_interleave)
+  DBuf<double> rzT_b;          // zeta_k / max( visc_eff_min, eta_3D_b( ti,k)): what k_vertex_diva sums into du_dz / dv_dz
+  DBuf<double> etaT_a;         // eta_3D_a( vi,k) for the a->b mapping in k_tri_assemble
   // --- prescribed velocities
   DBuf<int> bc_mask;
   DBuf<double> bc_u, bc_v;
