@@ -313,6 +313,7 @@ def run_cpu_sample(nv_sample, nv_full, steps, warmup, log=lambda *a: None, solve
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as ol   # CPU baseline leg: the one place bench.py may execute oracle/
     import ufe_b200 as ub
+    threads_before = int(ol.lib().orc_max_threads())
     ol.lib().orc_set_num_threads(cores)
     threads_used = int(ol.lib().orc_max_threads())
     w = make_workload(nv_sample)
@@ -388,6 +389,7 @@ def run_cpu_sample(nv_sample, nv_full, steps, warmup, log=lambda *a: None, solve
     factor = m.nV / nv_full
     for r in runs.values():
         r["value_extrapolated"] = r["steps_per_s_sample"] * factor
+    ol.lib().orc_set_num_threads(threads_before)     # a caller that lives on (the test-suite) keeps its own thread count
     return dict(value=runs[best]["value_extrapolated"], unit="velocity solves/s", cores=threads_used, kind="port", solver=best,
                 sample=(f"{runs[best]['steps']} predictor-corrector steps (after {warmup} warm-up; one viscosity iteration per step like the device run, state spun up with "
                         f"{SPINUP_VISC} viscosity iterations) of the same MISMIP_mod DIVA config on a {m.nV}-vertex mesh, "
@@ -420,6 +422,8 @@ def run_b200(args, rank, world, rdv, log):
     dt = DT
     if args.pc == "mg":
         ctx.set_mg_params(nu_pre=args.mg_nu, nu_post=args.mg_nu, omega=args.mg_omega, overcorr=args.mg_overcorr, w_levels=args.mg_w_levels, fp32=args.mg_fp32)
+        if args.mg_stop_nodes > 0:
+            ctx.set_mg_option("stop_nodes", args.mg_stop_nodes); ctx.set_mg_option("coarse_sweeps", args.mg_coarse_sweeps)
     log(f"mesh nV={m.nV} nTri={m.nTri} nE={m.nE} generated in {time.time() - t0:.1f}s")
     t0 = time.time()
     ctx.mesh_create(m)
@@ -598,7 +602,8 @@ def run_b200(args, rank, world, rdv, log):
         except (OSError, KeyError, ValueError):
             pass
         krylov_desc = ("BiCGStab + aggregation multigrid (%d levels %s, %d+%d block-Jacobi sweeps, omega %.2f, %s matrix storage in the preconditioner)"
-                       % (mg_info["levels"], mg_info["nodes"], args.mg_nu, args.mg_nu, args.mg_omega, "FP32" if args.mg_fp32 else "FP64")
+                       % (mg_info["levels"], str(mg_info["nodes"]) + (f", {args.mg_coarse_sweeps} sweeps on the coarsest" if args.mg_stop_nodes > 0 else ", dense solve on the coarsest"),
+                          args.mg_nu, args.mg_nu, args.mg_omega, "FP32" if args.mg_fp32 else "FP64")
                        if mg_info else "BiCGStab + Jacobi")
         avg_ms = spmv_ms / max(spmv_n, 1)
         achieved = B_spmv / (avg_ms * 1e-3) / 1e9 if spmv_n else 0.0
@@ -662,6 +667,8 @@ def run_sweep(args, rank, world, rdv, log):
     cfg.ksp_initial_guess_nonzero = 0
     if args.pc == "mg":
         ctx.set_mg_params(nu_pre=args.mg_nu, nu_post=args.mg_nu, omega=args.mg_omega, overcorr=args.mg_overcorr, w_levels=args.mg_w_levels, fp32=args.mg_fp32)
+        if args.mg_stop_nodes > 0:
+            ctx.set_mg_option("stop_nodes", args.mg_stop_nodes); ctx.set_mg_option("coarse_sweeps", args.mg_coarse_sweeps)
     ctx.mesh_create(m)
     ctx.calc_matrix_operators()
     vr, tr = (ctx.vi1, ctx.vi2), (ctx.ti1, ctx.ti2)
@@ -748,6 +755,9 @@ def main():
     ap.add_argument("--mg-overcorr", type=float, default=1.5)
     ap.add_argument("--mg-w-levels", type=int, default=3)
     ap.add_argument("--mg-fp32", type=int, default=0)
+    ap.add_argument("--mg-stop-nodes", type=int, default=-1, help="stop coarsening at the first level with at most this many nodes and run --mg-coarse-sweeps "
+                    "sweeps there (ufe_b200_set_mg_option); -1: 2000 for the MISMIP_mod meshes of configs[2] / [4], 0 (library default: coarsen down to the dense solve) otherwise")
+    ap.add_argument("--mg-coarse-sweeps", type=int, default=24)
     ap.add_argument("--e2e-state", choices=["resident", "roundtrip"], default="resident",
                     help="e2e leg: solver state kept on the device between calls (default) or uploaded and downloaded every step")
     ap.add_argument("--geometry", type=int, default=1, help="1: masks / grounded fractions / effective thickness follow the thickness on the device inside the step")
@@ -758,6 +768,10 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     args.nv = args.nv or CONFIGS[args.config]["nv"]
+    if args.mg_stop_nodes < 0:
+        # measured on the 4 M-vertex MISMIP_mod mesh (profiles/r02_mg_probe_stop_4M.log): 46 Krylov iterations against 63 and 17 % less solve time than
+        # the full hierarchy; the graded MISMIP+ mesh and the 72 k-vertex mesh prefer the library default (r02_mg_probe_stop_{mplus,72k}.log)
+        args.mg_stop_nodes = 2000 if args.config in ("antarctica", "sweep") else 0
 
     def log(*a):
         if args.verbose or os.environ.get("UFE_BENCH_VERBOSE"):

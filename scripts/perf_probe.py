@@ -46,9 +46,10 @@ print("speed max", np.hypot(arrs["u_vav_b"], arrs["v_vav_b"]).max())
 # the variants of the two gather kernels of the viscosity iteration (velocity.cu), each from the same zero state: kernel time per launch and the result
 if os.environ.get("PROBE_VARIANTS", "1") == "1":
     ref = None
-    for name, env in (("interleaved copies + shared-memory columns (default)", {}), ("reference-layout gathers", {"UFE_B200_INTERLEAVE": "0"}),
-                      ("local-memory columns", {"UFE_B200_VERTEX_SMEM": "0"}), ("round-1 kernels", {"UFE_B200_INTERLEAVE": "0", "UFE_B200_VERTEX_SMEM": "0"})):
-        for k in ("UFE_B200_INTERLEAVE", "UFE_B200_VERTEX_SMEM"):
+    for name, env in (("interleaved zeta/eta copy + shared-memory columns (default)", {}), ("+ interleaved eta_3D_a copy for the assembly", {"UFE_B200_INTERLEAVE_A": "1"}),
+                      ("reference-layout gathers", {"UFE_B200_INTERLEAVE": "0"}), ("local-memory columns", {"UFE_B200_VERTEX_SMEM": "0"}),
+                      ("round-1 kernels", {"UFE_B200_INTERLEAVE": "0", "UFE_B200_VERTEX_SMEM": "0"})):
+        for k in ("UFE_B200_INTERLEAVE", "UFE_B200_INTERLEAVE_A", "UFE_B200_VERTEX_SMEM"):
             os.environ.pop(k, None)
         os.environ.update(env)
         for a_ in arrs.values():

@@ -46,15 +46,19 @@ for name in ("map_a_b", "ddx_a_a", "ddx_b_a", "ddx_b_b", "M2_d2dx2_b_b"):
             want = val[k] @ x[ind[k] - 1, :]
             got = y[r]
             assert np.allclose(got, want, rtol=1e-12, atol=1e-12 * np.abs(val[k]).sum() * np.abs(x).max()), (name, r)
-        L.ufe_b200_timing_reset(ctx.h)
-        L.ufe_b200_timing_enable(ctx.h, 1)
-        for _ in range(5):
-            ctx.spmv(1, x, rows, ncols)
-        L.ufe_b200_timing_enable(ctx.h, 0)
-        ms, n = ctx.timing("operator_spmv")
         B = 12 * nnz + 4 * (rows + 1) + 8 * ncols * (rows + cols)
-        gbs = B / (ms / n * 1e-3) / 1e9
-        print(f"{name:14s} ncols={ncols:2d} rows={rows} nnz/row={nnz / rows:.1f}: {ms / n:.3f} ms/launch ({n} launches), {B / 1e9:.3f} GB algorithmic -> "
-              f"{gbs:.0f} GB/s = {gbs / peak:.2f} of peak")
+        for variant in (("", "1"),) if ncols == 1 else (("reference-layout x (default)", "0"), ("column-interleaved x", "1")):
+            os.environ["UFE_B200_MULTICOL_INTERLEAVE"] = variant[1]
+            ctx.spmv(1, x, rows, ncols)
+            L.ufe_b200_timing_reset(ctx.h)
+            L.ufe_b200_timing_enable(ctx.h, 1)
+            reps = 5
+            for _ in range(reps):
+                ctx.spmv(1, x, rows, ncols)
+            L.ufe_b200_timing_enable(ctx.h, 0)
+            ms, n = ctx.timing("operator_spmv")
+            gbs = B / (ms / reps * 1e-3) / 1e9
+            print(f"{name:14s} ncols={ncols:2d} rows={rows} nnz/row={nnz / rows:.1f} {variant[0]:28s}: {ms / reps:.3f} ms/product ({n // reps} launches each), "
+                  f"{B / 1e9:.3f} GB algorithmic -> {gbs:.0f} GB/s = {gbs / peak:.2f} of peak")
     L.ufe_b200_csr_release(ctx.h, 1)
 ctx.close()

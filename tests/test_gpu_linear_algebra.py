@@ -93,9 +93,12 @@ def test_apply_operators_2D_and_3D(ctx, mesh_ops):
     for name in ("map_a_b", "map_b_a", "ddx_a_b"):
         optr, oind, oval, mm, nn = o.get_operator(ub.OP[name])
         X = np.asfortranarray(rng.standard_normal((nn, m.nz)))
-        Y = ctx.apply_operator(ub.OP[name], X, mm, ncols=m.nz)
         Yo = o.apply_operator(ub.OP[name], X, ncols=m.nz)
-        assert np.abs(Y - Yo).max() < 1e-12 * np.abs(Yo).max(), name
+        for interleave in ("0", "1"):      # k_sell_multicol on the reference layout (default) / k_sell_multicol_T on the column-interleaved copy
+            os.environ["UFE_B200_MULTICOL_INTERLEAVE"] = interleave
+            Y = ctx.apply_operator(ub.OP[name], X, mm, ncols=m.nz)
+            assert np.abs(Y - Yo).max() < 1e-12 * np.abs(Yo).max(), (name, interleave)
+        os.environ.pop("UFE_B200_MULTICOL_INTERLEAVE")
 
 
 def test_ksp_on_stiffness_matrix(ctx, mesh_ops):

@@ -68,6 +68,29 @@ def test_stiffness_pattern_bit_exact(setup, variant):
         assert np.abs(u[bc[0] == 1] - bc[1][bc[0] == 1]).max() < 1e-9
 
 
+def test_same_prescribed_mask_keeps_the_pattern_and_new_values_or_mask_take_effect(setup):
+    """upload_bc (velocity.cu): the pattern depends on the mask only; new prescribed values with the same mask must reach the load vector without a pattern
+    rebuild (fewer launches than the first call), a different mask must rebuild it"""
+    w, ctx, o = setup
+    m = w.mesh
+    cfg = wl.scaling_config()
+    rng = np.random.default_rng(12)
+    co = (1e10 * (1 + 0.1 * rng.random(m.nTri)), 1e3 * rng.standard_normal(m.nTri), 1e3 * rng.standard_normal(m.nTri), 1e3 * rng.random(m.nTri),
+          1e4 * rng.standard_normal(m.nTri), 1e4 * rng.standard_normal(m.nTri))
+    mask1 = (rng.random(m.nTri) < 0.05).astype(np.int32); mask2 = (rng.random(m.nTri) < 0.08).astype(np.int32)
+    launches = []
+    for mask, scale in ((mask1, 10.0), (mask1, -3.0), (mask2, 5.0)):
+        bc = (mask, scale * np.ones(m.nTri), 2.0 * scale * np.ones(m.nTri))
+        l0 = ctx.kernel_launches()
+        u, v, its = _linearised(ctx, cfg, m, *co, 1e-12, 1e-30, bc)
+        launches.append((ctx.kernel_launches() - l0) / max(its, 1))
+        ptr, ind, val, bb = ctx.get_stiffness()
+        optr, oind, oval, obb = o.assemble(cfg, *co, *bc)
+        assert np.array_equal(ptr, optr) and np.array_equal(ind, oind)
+        assert np.abs(bb - obb).max() <= 1e-13 * np.abs(obb).max()
+        assert np.abs(u[mask == 1] - scale).max() < 1e-9 and np.abs(v[mask == 1] - 2.0 * scale).max() < 1e-9
+
+
 # field -> tolerance (relative L2) after a fixed number of viscosity iterations at tight KSP tolerance
 _FIELDS = ["u_vav_b", "v_vav_b", "u_base_b", "v_base_b", "tau_bx_b", "tau_by_b", "eta_3D_b", "u_b_prev", "v_b_prev", "tau_dx_b", "tau_dy_b",
            "u_3D_b", "v_3D_b", "du_dx_a", "du_dy_a", "dv_dx_a", "dv_dy_a", "du_dz_3D_a", "dv_dz_3D_a", "eta_3D_a", "eta_vav_a", "N_a", "N_b",

@@ -118,6 +118,7 @@ struct MgParams {
   int w_levels = 3;              // coarse levels 1..w_levels are visited twice per cycle (W-cycle on top, V-cycle below)
   int dense_max = 128;           // coarsest level: at most this many nodes -> dense inverse; otherwise `coarse_sweeps` sweeps
   int coarse_sweeps = 8;
+  int stop_nodes = 0;            // > 0: coarsening stops at the first level with at most this many nodes; above dense_max that level is solved by `coarse_sweeps` sweeps
   int tail_max = 0;              // > 0: levels from the first one with <= tail_max nodes down run as one single-CTA kernel per visit (k_mg_tail).
                                  // Measured slower than graph nodes on B200 at 4 M vertices (0.82 vs 0.72 ms per cycle with 2048, 1.98 ms with
                                  // 16384: one SM's L2 bandwidth and latency cost more than ~80 kernel boundaries save;
@@ -138,6 +139,7 @@ void pc_state_free(PcState*);
 struct Ctx {
   int device = 0, rank = 0, nranks = 1;
   cudaStream_t stream = nullptr;
+  DBuf<double> xT;                      // column-interleaved copy of the right-hand sides of a multi-column product (csr.cu)
   DBuf<unsigned char> l2_flush;         // ufe_b200_l2_flush: a buffer larger than L2, written between timed iterations of small workloads
   cudaStream_t copy_stream = nullptr;   // host<->device transfers that overlap compute (ufe_b200_pc_step)
   cudaEvent_t ev_copy_a = nullptr, ev_copy_b = nullptr;

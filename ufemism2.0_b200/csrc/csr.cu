@@ -252,6 +252,52 @@ __global__ void __launch_bounds__(kBlock) k_sell_multicol(int m, int n_ext, int 
   }
 }
 
+// [k][i] -> [i][k] through a shared-memory tile (reads and writes in full segments)
+__global__ void __launch_bounds__(128) k_interleave_columns(int n, int ncols, const double* __restrict__ in, double* __restrict__ out) {
+  extern __shared__ double tile[];   // [128][ncols + 1]
+  const int pitch = ncols + 1;
+  for (long long base = (long long)blockIdx.x * 128; base < n; base += (long long)gridDim.x * 128) {
+    const int cnt = (int)min((long long)128, n - base);
+    if ((int)threadIdx.x < cnt)
+      for (int k = 0; k < ncols; ++k) tile[threadIdx.x * pitch + k] = in[(size_t)k * n + base + threadIdx.x];
+    __syncthreads();
+    for (int t = threadIdx.x; t < cnt * ncols; t += 128) out[(size_t)base * ncols + t] = tile[(t / ncols) * pitch + t % ncols];
+    __syncthreads();
+  }
+}
+// the multi-column product on a column-interleaved copy xT[j][c] of the right-hand sides: the NC values an entry needs are one contiguous segment
+// (8 NC bytes) instead of NC sectors 8 n_ext bytes apart -- the ncu capture of k_sell_multicol showed the product bound by exactly those sector-sized
+// gathers (DRAM traffic = algorithmic bytes at 20 % of the bandwidth, profiles/r02_generic_spmv_4M_ncu.md)
+template <int NC>
+__global__ void __launch_bounds__(kBlock) k_sell_multicol_T(int m, int ncols, const int* __restrict__ slice, const int* __restrict__ ind,
+                                                            const double* __restrict__ val, const double* __restrict__ xT, double* __restrict__ y) {
+  const int c0 = blockIdx.y * NC, nc = min(NC, ncols - c0);
+  for (long long rr = (long long)blockIdx.x * blockDim.x + threadIdx.x; rr < m; rr += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)rr, s = r >> 5, b = slice[s], w = (slice[s + 1] - b) >> 5;
+    const int* __restrict__ ip = ind + b + (r & 31);
+    const double* __restrict__ vp = val + b + (r & 31);
+    double acc[NC];
+#pragma unroll
+    for (int q = 0; q < NC; ++q) acc[q] = 0.0;
+    for (int k = 0; k < w; ++k) {
+      const double* __restrict__ xr = xT + (size_t)ip[k * 32] * ncols + c0;
+      const double v = vp[k * 32];
+#pragma unroll
+      for (int q = 0; q < NC; ++q)
+        if (q < nc) acc[q] += v * xr[q];
+    }
+#pragma unroll
+    for (int q = 0; q < NC; ++q)
+      if (q < nc) y[(size_t)(c0 + q) * m + r] = acc[q];
+  }
+}
+
+template <int NC>
+static void launch_sell_multicol_T(Ctx* c, const DevCsr& A, const double* xT, double* y, int ncols) {
+  dim3 grid(grid_for(c, A.m_loc, kBlock), (ncols + NC - 1) / NC);
+  k_sell_multicol_T<NC><<<grid, kBlock, 0, c->stream>>>(A.m_loc, ncols, A.sell_slice.p, A.sell_ind.p, A.sell_val.p, xT, y);
+}
+
 template <int NC>
 static void launch_sell_multicol(Ctx* c, const DevCsr& A, const double* x_ext, double* y, int ncols) {
   dim3 grid(grid_for(c, A.m_loc, kBlock), (ncols + NC - 1) / NC);
@@ -261,6 +307,24 @@ static void launch_sell_multicol(Ctx* c, const DevCsr& A, const double* x_ext, d
 int csr_spmv_multicol(Ctx* c, const DevCsr& A, const double* x_ext, double* y, int ncols, int tc) {
   if (ncols == 1) return csr_spmv(c, A, x_ext, y, tc);
   if (A.m_loc == 0) return 0;
+  // Measured on the operators of the 4 M-vertex mesh (profiles/r02_spmv_probe_sell_v2.log): the interleaved copy does not pay -- 0.94 / 1.01 / 1.14 ms
+  // against 0.90 / 0.85 / 0.93 ms for map_a_b / ddx_a_a / ddx_b_a with 12 columns -- so the product is bound by the dependent index -> value chain,
+  // not by the sectors; the path stays selectable (UFE_B200_MULTICOL_INTERLEAVE=1) and tested.
+  if (A.has_sell() && ncols >= 4 && ncols <= 40 && getenv("UFE_B200_MULTICOL_INTERLEAVE") && atoi(getenv("UFE_B200_MULTICOL_INTERLEAVE")) == 1) {
+    const int n_ext = A.cols.n_ext();
+    UFE_TRY(c->xT.alloc((size_t)n_ext * ncols));
+    {
+      UFE_LAUNCH(c, tc);
+      k_interleave_columns<<<grid_for(c, n_ext, 128), 128, sizeof(double) * 128 * (size_t)(ncols + 1), c->stream>>>(n_ext, ncols, x_ext, c->xT.p);
+    }
+    UFE_LAUNCH(c, tc);
+    if (ncols <= 4) launch_sell_multicol_T<4>(c, A, c->xT.p, y, ncols);
+    else if (ncols <= 8) launch_sell_multicol_T<8>(c, A, c->xT.p, y, ncols);
+    else if (ncols <= 12 || (ncols > 16 && ncols <= 24)) launch_sell_multicol_T<12>(c, A, c->xT.p, y, ncols);
+    else launch_sell_multicol_T<16>(c, A, c->xT.p, y, ncols);
+    UFE_CUDA(cudaGetLastError());
+    return 0;
+  }
   if (A.has_sell()) {
     UFE_LAUNCH(c, tc);
     if (ncols <= 4) launch_sell_multicol<4>(c, A, x_ext, y, ncols);

@@ -1190,7 +1190,7 @@ int mg_build(Ctx* c, Mg& G, const BlkMat& B, const Range& rb) {
   }
   while (true) {
     MgLevel& L = G.lv.back();
-    const bool small = L.n <= G.p.dense_max && !(G.distributed && G.lv.size() == 1);   // a split level 0 is never the coarsest
+    const bool small = (L.n <= G.p.dense_max || L.n <= G.p.stop_nodes) && !(G.distributed && G.lv.size() == 1);   // a split level 0 is never the coarsest
     if (small || (int)G.lv.size() >= G.p.max_levels) break;
     HostTransfer T;
     const bool split = G.distributed && G.lv.size() == 1;

@@ -866,12 +866,20 @@ static int upload_bc(Ctx* c, const int32_t* mask, const double* bu, const double
   if (mask || bu || bv) {
     UFE_CHECK(mask && bu && bv, "need to provide prescribed u,v fields and mask!");  // DIVA_solver_infinite_slab.f90:104-107
     UFE_TRY(h2d_field(c, V.bc_mask.p, M.b, mask)); UFE_TRY(h2d_field(c, V.bc_u.p, M.b, bu)); UFE_TRY(h2d_field(c, V.bc_v.p, M.b, bv));
+    // The sparsity pattern (and the multigrid hierarchy on it) depends on the mask only, not on the prescribed values: a caller that passes the same
+    // mask every time step keeps its pattern.  With several ranks every rank would have to take the same decision (the multigrid set-up holds
+    // collectives), so there the pattern is rebuilt whenever a mask is passed.
+    const size_t nb = (size_t)M.b.n_loc();
+    const bool same = c->nranks == 1 && V.have_bc && V.bc_mask_host.size() == nb && memcmp(V.bc_mask_host.data(), mask, nb * sizeof(int32_t)) == 0;
     V.have_bc = true;
-    V.pattern_valid = false;   // the mask may have changed; the pattern kernels are cheap compared with one solve
-    ++c->bc_version;
+    if (!same) {
+      V.bc_mask_host.assign(mask, mask + nb);
+      V.pattern_valid = false;
+      ++c->bc_version;
+    }
   } else if (V.have_bc) {
     UFE_CUDA(cudaMemsetAsync(V.bc_mask.p, 0, sizeof(int) * V.bc_mask.n, c->stream));
-    V.have_bc = false; V.pattern_valid = false; ++c->bc_version;
+    V.have_bc = false; V.pattern_valid = false; ++c->bc_version; V.bc_mask_host.clear();
   }
   return 0;
 }
@@ -1018,14 +1026,15 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
   ta.eta_3D_b = V.eta_3D_b.p; ta.F1_3D_b = V.F1_3D_b.p; ta.F2_3D_b = V.F2_3D_b.p;
   StiffArgs sa = stiff_args(c, csr_values_unneeded(c, cfg));
   // layer-interleaved work copies of the two gathered 3-D fields (UFE_B200_INTERLEAVE=0: gather the reference layout directly, as before)
-  const bool interleave_on = !(getenv("UFE_B200_INTERLEAVE") && atoi(getenv("UFE_B200_INTERLEAVE")) == 0);   // read per solve: scripts/perf_probe.py toggles it
-  const bool interleave = DIVA && interleave_on;
+  // Measured at 4 M vertices (profiles/r02_perf_probe_variants_4M.log): the b-grid copy takes the column class from 6.1 to 3.7 ms per viscosity
+  // iteration; the a-grid copy does nothing for k_tri_assemble (6.96 against 6.88 ms: its time is the operator rows and the 40 values it writes per
+  // triangle, not the 36 eta gathers), so it is off unless UFE_B200_INTERLEAVE_A=1.  Read per solve: scripts/perf_probe.py toggles them.
+  const bool interleave = DIVA && !(getenv("UFE_B200_INTERLEAVE") && atoi(getenv("UFE_B200_INTERLEAVE")) == 0);
+  const bool interleave_a = DIVA && getenv("UFE_B200_INTERLEAVE_A") && atoi(getenv("UFE_B200_INTERLEAVE_A")) == 1;
   const size_t tile_bytes = sizeof(double) * 128 * (size_t)(nz + 1);
   va.rzT = nullptr; ta.etaT = nullptr;
-  if (interleave) {
-    UFE_TRY(V.rzT_b.alloc((size_t)M.b.n_ext() * nz)); UFE_TRY(V.etaT_a.alloc((size_t)M.a.n_ext() * nz));
-    va.rzT = V.rzT_b.p; ta.etaT = V.etaT_a.p;
-  }
+  if (interleave) { UFE_TRY(V.rzT_b.alloc((size_t)M.b.n_ext() * nz)); va.rzT = V.rzT_b.p; }
+  if (interleave_a) { UFE_TRY(V.etaT_a.alloc((size_t)M.a.n_ext() * nz)); ta.etaT = V.etaT_a.p; }
 
   // adaptive relaxation (DIVA_solver_infinite_slab.f90:121-131)
   double L2_uv = 1e9, relax = cfg->visc_it_relax, eps0 = cfg->Glens_flow_law_epsilon_sq_0;
@@ -1074,7 +1083,7 @@ int velocity_solve(Ctx* c, const ufe_b200_config* cfg, int approximation, int* n
     if (DIVA) {
       UFE_TRY(halo_exchange(c, M.a, V.beta_eff_a.p)); UFE_TRY(halo_exchange(c, M.a, V.eta_3D_a.p, nz));
       UFE_TRY(halo_exchange(c, M.a, V.F2_3D_a.p, nz)); UFE_TRY(halo_exchange(c, M.a, V.F1_3D_a.p, nz));
-      if (interleave) {
+      if (interleave_a) {
         UFE_LAUNCH(c, TC_ASSEMBLY);
         k_layers_interleave<false><<<grid_for(c, M.a.n_ext(), 128), 128, tile_bytes, st>>>(M.a.n_ext(), nz, V.eta_3D_a.p, M.zeta.p, 0.0, V.etaT_a.p);
       }
@@ -1275,6 +1284,7 @@ int ufe_b200_set_mg_option(ufe_b200_handle h, const char* name, double value) {
   else if (!strcmp(name, "coarse_sweeps")) p.coarse_sweeps = (int)value;
   else if (!strcmp(name, "max_levels")) { p.max_levels = (int)value; rebuild = true; }     // a shorter hierarchy ends in coarse_sweeps sweeps
   else if (!strcmp(name, "dense_max")) { p.dense_max = (int)value; rebuild = true; }
+  else if (!strcmp(name, "stop_nodes")) { p.stop_nodes = (int)value; rebuild = true; }
   else if (!strcmp(name, "w_levels")) p.w_levels = (int)value;
   else if (!strcmp(name, "fuse")) p.fuse = (int)value;
   else if (!strcmp(name, "use_graph")) p.use_graph = (int)value;

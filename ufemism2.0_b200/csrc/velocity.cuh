@@ -31,6 +31,7 @@ struct Velocity {
   DBuf<int> bc_mask;
   DBuf<double> bc_u, bc_v;
   bool have_bc = false;
+  std::vector<int32_t> bc_mask_host;   // the mask the current pattern was built for (velocity.cu: upload_bc)
   // --- linear system: stiffness matrix on a pattern built once per (mesh, BC) (K3 of SURVEY 2e)
   DevCsr A;
   DBuf<int> row_kind;          // per matrix row: 0 free, 1 identity (prescribed / 'zero'), 2 'infinite'
