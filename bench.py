@@ -424,6 +424,7 @@ def run_b200(args, rank, world, rdv, log):
         ctx.set_mg_params(nu_pre=args.mg_nu, nu_post=args.mg_nu, omega=args.mg_omega, overcorr=args.mg_overcorr, w_levels=args.mg_w_levels, fp32=args.mg_fp32)
         if args.mg_stop_nodes > 0:
             ctx.set_mg_option("stop_nodes", args.mg_stop_nodes); ctx.set_mg_option("coarse_sweeps", args.mg_coarse_sweeps)
+            ctx.set_mg_option("coarsest_cluster", args.mg_coarsest_cluster)
     log(f"mesh nV={m.nV} nTri={m.nTri} nE={m.nE} generated in {time.time() - t0:.1f}s")
     t0 = time.time()
     ctx.mesh_create(m)
@@ -602,7 +603,7 @@ def run_b200(args, rank, world, rdv, log):
         except (OSError, KeyError, ValueError):
             pass
         krylov_desc = ("BiCGStab + aggregation multigrid (%d levels %s, %d+%d block-Jacobi sweeps, omega %.2f, %s matrix storage in the preconditioner)"
-                       % (mg_info["levels"], str(mg_info["nodes"]) + (f", {args.mg_coarse_sweeps} sweeps on the coarsest" if args.mg_stop_nodes > 0 else ", dense solve on the coarsest"),
+                       % (mg_info["levels"], str(mg_info["nodes"]) + (f", {args.mg_coarse_sweeps} sweeps on the coarsest" + (f" in one {args.mg_coarsest_cluster}-CTA cluster kernel per visit" if args.mg_coarsest_cluster > 1 else "") if args.mg_stop_nodes > 0 else ", dense solve on the coarsest"),
                           args.mg_nu, args.mg_nu, args.mg_omega, "FP32" if args.mg_fp32 else "FP64")
                        if mg_info else "BiCGStab + Jacobi")
         avg_ms = spmv_ms / max(spmv_n, 1)
@@ -669,6 +670,7 @@ def run_sweep(args, rank, world, rdv, log):
         ctx.set_mg_params(nu_pre=args.mg_nu, nu_post=args.mg_nu, omega=args.mg_omega, overcorr=args.mg_overcorr, w_levels=args.mg_w_levels, fp32=args.mg_fp32)
         if args.mg_stop_nodes > 0:
             ctx.set_mg_option("stop_nodes", args.mg_stop_nodes); ctx.set_mg_option("coarse_sweeps", args.mg_coarse_sweeps)
+            ctx.set_mg_option("coarsest_cluster", args.mg_coarsest_cluster)
     ctx.mesh_create(m)
     ctx.calc_matrix_operators()
     vr, tr = (ctx.vi1, ctx.vi2), (ctx.ti1, ctx.ti2)
@@ -757,7 +759,9 @@ def main():
     ap.add_argument("--mg-fp32", type=int, default=0)
     ap.add_argument("--mg-stop-nodes", type=int, default=-1, help="stop coarsening at the first level with at most this many nodes and run --mg-coarse-sweeps "
                     "sweeps there (ufe_b200_set_mg_option); -1: 2000 for the MISMIP_mod meshes of configs[2] / [4], 0 (library default: coarsen down to the dense solve) otherwise")
-    ap.add_argument("--mg-coarse-sweeps", type=int, default=24)
+    ap.add_argument("--mg-coarse-sweeps", type=int, default=32)
+    ap.add_argument("--mg-coarsest-cluster", type=int, default=-1, help="> 1: the sweeps on the coarsest level as one thread-block-cluster kernel of this many CTAs "
+                    "(-1: 16 whenever --mg-stop-nodes is in effect)")
     ap.add_argument("--e2e-state", choices=["resident", "roundtrip"], default="resident",
                     help="e2e leg: solver state kept on the device between calls (default) or uploaded and downloaded every step")
     ap.add_argument("--geometry", type=int, default=1, help="1: masks / grounded fractions / effective thickness follow the thickness on the device inside the step")
@@ -772,6 +776,10 @@ def main():
         # measured on the 4 M-vertex MISMIP_mod mesh (profiles/r02_mg_probe_stop_4M.log): 46 Krylov iterations against 63 and 17 % less solve time than
         # the full hierarchy; the graded MISMIP+ mesh and the 72 k-vertex mesh prefer the library default (r02_mg_probe_stop_{mplus,72k}.log)
         args.mg_stop_nodes = 2000 if args.config in ("antarctica", "sweep") else 0
+    if args.mg_coarsest_cluster < 0:
+        # 4 M vertices (profiles/r02_mg_probe_coarsest_cluster_4M.log, r02_bench_4_cluster16_cs32.log): 32 sweeps in one 16-CTA cluster kernel per visit cost
+        # what 24 sweeps cost as graph nodes and save 2 more Krylov iterations per step (150.0 against 165.6 ms per step)
+        args.mg_coarsest_cluster = 16 if args.mg_stop_nodes > 0 else 0
 
     def log(*a):
         if args.verbose or os.environ.get("UFE_BENCH_VERBOSE"):

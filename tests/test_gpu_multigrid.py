@@ -118,6 +118,28 @@ def test_merged_reductions_of_the_multi_rank_recurrence(setup, monkeypatch):
         assert abs(its1 - its0) <= max(2, its0 // 5), (rtol, its0, its1)
 
 
+@pytest.mark.parametrize("cluster", [8, 16])
+def test_coarsest_level_sweeps_as_one_cluster_kernel(setup, cluster):
+    """k_mg_coarsest_cluster (matrix slices in shared memory, iterate exchanged through L2 + cluster barrier) against the same sweeps as graph nodes"""
+    w, ctx, o = setup
+    m = w.mesh
+    co = _coefficients(m, seed=7)
+    cfg = wl.scaling_config()
+    cfg.pc_type = ub.PC_MG
+    try:
+        ctx.set_mg_option("stop_nodes", 4000); ctx.set_mg_option("coarse_sweeps", 12)
+        ctx.set_mg_option("coarsest_cluster", 0)
+        u0, v0, its0 = _linearised(ctx, cfg, m, *co, 1e-10, 1e-30)
+        info = ctx.mg_info()
+        assert 128 < info["nodes"][-1] <= 4000, info        # the hierarchy ends in a level that is swept, not solved directly
+        ctx.set_mg_option("coarsest_cluster", cluster)
+        u1, v1, its1 = _linearised(ctx, cfg, m, *co, 1e-10, 1e-30)
+        assert abs(its1 - its0) <= 1, (its0, its1)
+        assert rel_l2(u1, u0) < 1e-8 and rel_l2(v1, v0) < 1e-8, (rel_l2(u1, u0), rel_l2(v1, v0))
+    finally:
+        ctx.set_mg_option("coarsest_cluster", 0); ctx.set_mg_option("stop_nodes", 0); ctx.set_mg_option("coarse_sweeps", 8)
+
+
 def test_multigrid_is_deterministic(setup):
     w, ctx, o = setup
     m = w.mesh

@@ -784,6 +784,101 @@ int launch_tail_cluster(Ctx* c, int cluster, const MgStep* steps, int nsteps) {
   return 0;
 }
 
+// ---- the sweeps on the coarsest level as ONE thread-block-cluster kernel per visit --------------------------------------------------------------
+// A hierarchy that stops at ~10^3 nodes (MgParams::stop_nodes) solves that level with `coarse_sweeps` damped block-Jacobi sweeps.  As graph nodes
+// each sweep costs ~3 us although it moves only ~0.5 MB: two dependent L2 round trips (column index -> iterate) plus a kernel boundary, 8 visits x 24
+// sweeps per cycle.  Here every CTA of the cluster first copies the matrix slices of its rows into shared memory (the whole level is ~0.6 MB: 16 CTAs
+// hold it), then runs all sweeps: columns and values come from shared memory, only the iterate is gathered from L2 (ld.global.cg: never from a stale
+// L1 line), written back and published to the other CTAs by the cluster barrier (barrier.cluster, release / acquire at cluster scope).  Same row
+// arithmetic and summation order as k_mg_smooth0 / k_mg_sweep<MODE 0>.
+constexpr int kCoarsestBlock = 256;
+template <typename VT>
+__global__ void __launch_bounds__(kCoarsestBlock, 1) k_mg_coarsest_cluster(int n, const int* __restrict__ slice_ptr, const int* __restrict__ col,
+                                                                           const VT* __restrict__ val, const double* __restrict__ dblk,
+                                                                           const double* __restrict__ b, double* xa, double* xb, double* out, int nsweeps) {
+  cooperative_groups::cluster_group cl = cooperative_groups::this_cluster();
+  const int rank = (int)cl.block_rank(), C = (int)cl.num_blocks();
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  const int n_slices = (n + 31) >> 5;
+  const int per = (n_slices + C - 1) / C;
+  const int s0 = min(n_slices, rank * per), s1 = min(n_slices, s0 + per);
+  const int k_lo = slice_ptr[s0], k_hi = slice_ptr[s1];
+  VT* s_val = reinterpret_cast<VT*>(s_raw);                                            // [slot][4][32]
+  int* s_col = reinterpret_cast<int*>(s_raw + sizeof(VT) * 128 * (size_t)(k_hi - k_lo));   // [slot][32]
+  for (int i = threadIdx.x; i < (k_hi - k_lo) * 128; i += blockDim.x) s_val[i] = val[(size_t)k_lo * 128 + i];
+  for (int i = threadIdx.x; i < (k_hi - k_lo) * 32; i += blockDim.x) s_col[i] = col[(size_t)k_lo * 32 + i];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  // first sweep from a zero iterate: x = Dw b
+  for (int s = s0 + warp; s < s1; s += nwarps) {
+    const int t = (s << 5) + lane;
+    if (t < n) {
+      const double2 bv = reinterpret_cast<const double2*>(b)[t];
+      const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
+      reinterpret_cast<double2*>(xa)[t] = make_double2(d01.x * bv.x + d01.y * bv.y, d23.x * bv.x + d23.y * bv.y);
+    }
+  }
+  cl.sync();        // also orders the shared-memory copies (it is a superset of __syncthreads)
+  double* src = xa; double* dst = xb;
+  for (int sw = 0; sw < nsweeps; ++sw) {
+    if (sw == nsweeps - 1) dst = out;
+    const double2* x2 = reinterpret_cast<const double2*>(src);
+    for (int s = s0 + warp; s < s1; s += nwarps) {
+      const int t = (s << 5) + lane;
+      const int k0 = slice_ptr[s] - k_lo, k1 = slice_ptr[s + 1] - k_lo;
+      double yu = 0.0, yv = 0.0;
+      constexpr int U = 8;
+      for (int k = k0; k < k1; k += U) {
+        double2 xv[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (k + u < k1) xv[u] = __ldcg(x2 + s_col[(k + u) * 32 + lane]);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (k + u < k1) {
+            const VT* vp = s_val + (size_t)(k + u) * 128 + lane;
+            yu += (double)vp[0] * xv[u].x + (double)vp[32] * xv[u].y;
+            yv += (double)vp[64] * xv[u].x + (double)vp[96] * xv[u].y;
+          }
+      }
+      if (t < n) {
+        const double2 bv = reinterpret_cast<const double2*>(b)[t];
+        const double ru = bv.x - yu, rv = bv.y - yv;
+        const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
+        const double2 xo = __ldcg(x2 + t);
+        reinterpret_cast<double2*>(dst)[t] = make_double2(xo.x + d01.x * ru + d01.y * rv, xo.y + d23.x * ru + d23.y * rv);
+      }
+    }
+    cl.sync();
+    double* tmp = src; src = dst; dst = (tmp == out) ? xb : tmp;
+  }
+}
+// shared memory a cluster of C CTAs needs for level L (the largest share of slots of any CTA), or 0 if the level has no slices
+template <typename VT>
+size_t coarsest_cluster_smem(const std::vector<int>& slice_ptr_host, int n, int C) {
+  const int n_slices = (n + 31) >> 5, per = (n_slices + C - 1) / C;
+  int worst = 0;
+  for (int r = 0; r < C; ++r) {
+    const int s0 = std::min(n_slices, r * per), s1 = std::min(n_slices, s0 + per);
+    worst = std::max(worst, slice_ptr_host[s1] - slice_ptr_host[s0]);
+  }
+  return (size_t)worst * (128 * sizeof(VT) + 32 * sizeof(int));
+}
+template <typename VT>
+int launch_coarsest_cluster(Ctx* c, int cluster, size_t smem, const MgLevel& L, const VT* val, const double* b, double* xa, double* xb, double* out, int nsweeps) {
+  static size_t smem_set = 0;
+  static bool nonportable = false;
+  if (smem > smem_set) { UFE_CUDA(cudaFuncSetAttribute(k_mg_coarsest_cluster<VT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); smem_set = smem; }
+  if (cluster > 8 && !nonportable) { UFE_CUDA(cudaFuncSetAttribute(k_mg_coarsest_cluster<VT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1)); nonportable = true; }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(cluster); cfg.blockDim = dim3(kCoarsestBlock); cfg.dynamicSmemBytes = smem; cfg.stream = c->stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  UFE_CUDA(cudaLaunchKernelEx(&cfg, k_mg_coarsest_cluster<VT>, L.n, L.slice_ptr, L.col, val, (const double*)L.dblk.p, b, xa, xb, out, nsweeps));
+  return 0;
+}
+
 // ---- BiCGStab pieces that differ from the Jacobi path (the preconditioner is no longer fused into the SpMV) ----------
 
 // Bb = M^-1 b, Br = M^-1 (b - A x0) (Br == Bb and x zeroed when there is no initial guess)
@@ -1057,6 +1152,11 @@ int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out, bool x1_ready) 
       op_dense(c, G, b, out);
       return 0;
     }
+    if (P.coarsest_cluster > 1 && !G.rec && G.coarsest_smem > 0 && P.coarse_sweeps >= 1 && L.off == 0) {   // all sweeps of this visit in one cluster kernel
+      UFE_LAUNCH(c, TC_MG_COARSE);
+      UFE_TRY(launch_coarsest_cluster<VT>(c, P.coarsest_cluster, G.coarsest_smem, L, level_values<VT>(L), b, xa, xb, out, P.coarse_sweeps));
+      return 0;
+    }
     op_smooth0(c, G, l, L.n, b, L.dblk.p, xa + 2 * L.off);
     for (int s = 0; s < P.coarse_sweeps; ++s) {
       double* dst = (s == P.coarse_sweeps - 1) ? out : xb + 2 * L.off;
@@ -1244,6 +1344,12 @@ int mg_build(Ctx* c, Mg& G, const BlkMat& B, const Range& rb) {
     G.dense_n = 2 * Lc.n;
     UFE_TRY(G.dense_w.alloc((size_t)G.dense_n * 2 * G.dense_n));
     UFE_TRY(G.dense_inv.alloc((size_t)G.dense_n * G.dense_n));
+  }
+  // the sweeps of a coarsest level that is not solved directly: one cluster kernel per visit if every CTA's share of the matrix fits its shared memory
+  G.coarsest_smem = 0;
+  if (G.p.coarsest_cluster > 1 && G.dense_n == 0 && G.lv.size() > 1 && (int)H.slice_ptr.size() == Lc.n_slices + 1) {
+    const size_t need = G.p.fp32 ? coarsest_cluster_smem<float>(H.slice_ptr, Lc.n, G.p.coarsest_cluster) : coarsest_cluster_smem<double>(H.slice_ptr, Lc.n, G.p.coarsest_cluster);
+    if (need > 0 && need <= 200 * 1024) G.coarsest_smem = need;
   }
   UFE_CUDA(cudaStreamSynchronize(c->stream));
   G.setup_host_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
