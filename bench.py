@@ -424,7 +424,7 @@ def run_b200(args, rank, world, rdv, log):
         ctx.set_mg_params(nu_pre=args.mg_nu, nu_post=args.mg_nu, omega=args.mg_omega, overcorr=args.mg_overcorr, w_levels=args.mg_w_levels, fp32=args.mg_fp32)
         if args.mg_stop_nodes > 0:
             ctx.set_mg_option("stop_nodes", args.mg_stop_nodes); ctx.set_mg_option("coarse_sweeps", args.mg_coarse_sweeps)
-            ctx.set_mg_option("coarsest_cluster", args.mg_coarsest_cluster)
+            ctx.set_mg_option("coarsest_cluster", args.mg_coarsest_cluster); ctx.set_mg_option("coarsest_dsmem", args.mg_coarsest_dsmem)
     log(f"mesh nV={m.nV} nTri={m.nTri} nE={m.nE} generated in {time.time() - t0:.1f}s")
     t0 = time.time()
     ctx.mesh_create(m)
@@ -670,7 +670,7 @@ def run_sweep(args, rank, world, rdv, log):
         ctx.set_mg_params(nu_pre=args.mg_nu, nu_post=args.mg_nu, omega=args.mg_omega, overcorr=args.mg_overcorr, w_levels=args.mg_w_levels, fp32=args.mg_fp32)
         if args.mg_stop_nodes > 0:
             ctx.set_mg_option("stop_nodes", args.mg_stop_nodes); ctx.set_mg_option("coarse_sweeps", args.mg_coarse_sweeps)
-            ctx.set_mg_option("coarsest_cluster", args.mg_coarsest_cluster)
+            ctx.set_mg_option("coarsest_cluster", args.mg_coarsest_cluster); ctx.set_mg_option("coarsest_dsmem", args.mg_coarsest_dsmem)
     ctx.mesh_create(m)
     ctx.calc_matrix_operators()
     vr, tr = (ctx.vi1, ctx.vi2), (ctx.ti1, ctx.ti2)
@@ -757,6 +757,7 @@ def main():
     ap.add_argument("--mg-overcorr", type=float, default=1.5)
     ap.add_argument("--mg-w-levels", type=int, default=3)
     ap.add_argument("--mg-fp32", type=int, default=0)
+    ap.add_argument("--mg-coarsest-dsmem", type=int, default=0, help="iterate of the coarsest-level cluster kernel in distributed shared memory (1) or through L2 (0)")
     ap.add_argument("--mg-stop-nodes", type=int, default=-1, help="stop coarsening at the first level with at most this many nodes and run --mg-coarse-sweeps "
                     "sweeps there (ufe_b200_set_mg_option); -1: 2000 for the MISMIP_mod meshes of configs[2] / [4], 0 (library default: coarsen down to the dense solve) otherwise")
     ap.add_argument("--mg-coarse-sweeps", type=int, default=32)

@@ -11,7 +11,7 @@ if [ "$PARITY_ONLY" = "1" ]; then
 else
   bash scripts/multi_gpu_check.sh $N $O/r02_multi_gpu_check_${N}gpu.log; echo "multi-GPU check rc=$?"
 fi
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29550 bench.py --gpus $N --steps 5 --warmup 3 \
+[ "${SKIP_BENCH:-0}" = "1" ] || timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29550 bench.py --gpus $N --steps 5 --warmup 3 \
   > $O/r02_bench_${N}gpu.log 2> $O/r02_bench_${N}gpu.err; echo "bench rc=$?"
 tail -c 600 $O/r02_multi_gpu_*_${N}gpu.log
 ls -la $O

@@ -118,8 +118,9 @@ def test_merged_reductions_of_the_multi_rank_recurrence(setup, monkeypatch):
         assert abs(its1 - its0) <= max(2, its0 // 5), (rtol, its0, its1)
 
 
+@pytest.mark.parametrize("dsmem", [0, 1])
 @pytest.mark.parametrize("cluster", [8, 16])
-def test_coarsest_level_sweeps_as_one_cluster_kernel(setup, cluster):
+def test_coarsest_level_sweeps_as_one_cluster_kernel(setup, cluster, dsmem):
     """k_mg_coarsest_cluster (matrix slices in shared memory, iterate exchanged through L2 + cluster barrier) against the same sweeps as graph nodes"""
     w, ctx, o = setup
     m = w.mesh
@@ -132,12 +133,12 @@ def test_coarsest_level_sweeps_as_one_cluster_kernel(setup, cluster):
         u0, v0, its0 = _linearised(ctx, cfg, m, *co, 1e-10, 1e-30)
         info = ctx.mg_info()
         assert 128 < info["nodes"][-1] <= 4000, info        # the hierarchy ends in a level that is swept, not solved directly
-        ctx.set_mg_option("coarsest_cluster", cluster)
+        ctx.set_mg_option("coarsest_cluster", cluster); ctx.set_mg_option("coarsest_dsmem", dsmem)
         u1, v1, its1 = _linearised(ctx, cfg, m, *co, 1e-10, 1e-30)
         assert abs(its1 - its0) <= 1, (its0, its1)
         assert rel_l2(u1, u0) < 1e-8 and rel_l2(v1, v0) < 1e-8, (rel_l2(u1, u0), rel_l2(v1, v0))
     finally:
-        ctx.set_mg_option("coarsest_cluster", 0); ctx.set_mg_option("stop_nodes", 0); ctx.set_mg_option("coarse_sweeps", 8)
+        ctx.set_mg_option("coarsest_cluster", 0); ctx.set_mg_option("coarsest_dsmem", 0); ctx.set_mg_option("stop_nodes", 0); ctx.set_mg_option("coarse_sweeps", 8)
 
 
 def test_multigrid_is_deterministic(setup):

@@ -792,7 +792,10 @@ int launch_tail_cluster(Ctx* c, int cluster, const MgStep* steps, int nsteps) {
 // L1 line), written back and published to the other CTAs by the cluster barrier (barrier.cluster, release / acquire at cluster scope).  Same row
 // arithmetic and summation order as k_mg_smooth0 / k_mg_sweep<MODE 0>.
 constexpr int kCoarsestBlock = 256;
-template <typename VT>
+// DS = true: the iterate lives in every CTA's shared memory (two buffers of n double2); a CTA writes the new values of its rows into the next buffer of
+// ALL CTAs through distributed shared memory (cluster.map_shared_rank) and the gathers of the next sweep are local shared-memory reads -- no L2 round
+// trip left inside a sweep.  DS = false: the iterate is exchanged through L2 (ld.global.cg / st.global + cluster barrier).
+template <typename VT, bool DS>
 __global__ void __launch_bounds__(kCoarsestBlock, 1) k_mg_coarsest_cluster(int n, const int* __restrict__ slice_ptr, const int* __restrict__ col,
                                                                            const VT* __restrict__ val, const double* __restrict__ dblk,
                                                                            const double* __restrict__ b, double* xa, double* xb, double* out, int nsweeps) {
@@ -803,25 +806,37 @@ __global__ void __launch_bounds__(kCoarsestBlock, 1) k_mg_coarsest_cluster(int n
   const int per = (n_slices + C - 1) / C;
   const int s0 = min(n_slices, rank * per), s1 = min(n_slices, s0 + per);
   const int k_lo = slice_ptr[s0], k_hi = slice_ptr[s1];
-  VT* s_val = reinterpret_cast<VT*>(s_raw);                                            // [slot][4][32]
-  int* s_col = reinterpret_cast<int*>(s_raw + sizeof(VT) * 128 * (size_t)(k_hi - k_lo));   // [slot][32]
+  // layout: [iterate buffers: 2 x n_slices * 32 double2 (DS only)] [values: slot x 4 x 32] [columns: slot x 32]; the iterate region has the same
+  // size in every CTA, so the same offset addresses it in every peer
+  const size_t xbytes = DS ? sizeof(double2) * 2 * (size_t)n_slices * 32 : 0;
+  double2* s_x = reinterpret_cast<double2*>(s_raw);
+  VT* s_val = reinterpret_cast<VT*>(s_raw + xbytes);
+  int* s_col = reinterpret_cast<int*>(s_raw + xbytes + sizeof(VT) * 128 * (size_t)(k_hi - k_lo));
   for (int i = threadIdx.x; i < (k_hi - k_lo) * 128; i += blockDim.x) s_val[i] = val[(size_t)k_lo * 128 + i];
   for (int i = threadIdx.x; i < (k_hi - k_lo) * 32; i += blockDim.x) s_col[i] = col[(size_t)k_lo * 32 + i];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int nx = n_slices * 32;
+  auto publish = [&](int buf, int t, double2 v) {     // DS: node t of buffer `buf` in every CTA of the cluster
+    for (int r = 0; r < C; ++r) cl.map_shared_rank(s_x, r)[buf * nx + t] = v;
+  };
   // first sweep from a zero iterate: x = Dw b
   for (int s = s0 + warp; s < s1; s += nwarps) {
     const int t = (s << 5) + lane;
+    double2 v = make_double2(0.0, 0.0);
     if (t < n) {
       const double2 bv = reinterpret_cast<const double2*>(b)[t];
       const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
-      reinterpret_cast<double2*>(xa)[t] = make_double2(d01.x * bv.x + d01.y * bv.y, d23.x * bv.x + d23.y * bv.y);
+      v = make_double2(d01.x * bv.x + d01.y * bv.y, d23.x * bv.x + d23.y * bv.y);
+      if (!DS) reinterpret_cast<double2*>(xa)[t] = v;
     }
+    if (DS) publish(0, t, v);       // padding rows of the last slice hold zeros (their columns may be read, their values are zero)
   }
   cl.sync();        // also orders the shared-memory copies (it is a superset of __syncthreads)
   double* src = xa; double* dst = xb;
   for (int sw = 0; sw < nsweeps; ++sw) {
-    if (sw == nsweeps - 1) dst = out;
-    const double2* x2 = reinterpret_cast<const double2*>(src);
+    const bool last = sw == nsweeps - 1;
+    if (last) dst = out;
+    const double2* x2 = DS ? s_x + (sw & 1) * nx : reinterpret_cast<const double2*>(src);
     for (int s = s0 + warp; s < s1; s += nwarps) {
       const int t = (s << 5) + lane;
       const int k0 = slice_ptr[s] - k_lo, k1 = slice_ptr[s + 1] - k_lo;
@@ -831,7 +846,7 @@ __global__ void __launch_bounds__(kCoarsestBlock, 1) k_mg_coarsest_cluster(int n
         double2 xv[U];
 #pragma unroll
         for (int u = 0; u < U; ++u)
-          if (k + u < k1) xv[u] = __ldcg(x2 + s_col[(k + u) * 32 + lane]);
+          if (k + u < k1) xv[u] = DS ? x2[s_col[(k + u) * 32 + lane]] : __ldcg(x2 + s_col[(k + u) * 32 + lane]);
 #pragma unroll
         for (int u = 0; u < U; ++u)
           if (k + u < k1) {
@@ -840,15 +855,18 @@ __global__ void __launch_bounds__(kCoarsestBlock, 1) k_mg_coarsest_cluster(int n
             yv += (double)vp[64] * xv[u].x + (double)vp[96] * xv[u].y;
           }
       }
+      double2 v = make_double2(0.0, 0.0);
       if (t < n) {
         const double2 bv = reinterpret_cast<const double2*>(b)[t];
         const double ru = bv.x - yu, rv = bv.y - yv;
         const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
-        const double2 xo = __ldcg(x2 + t);
-        reinterpret_cast<double2*>(dst)[t] = make_double2(xo.x + d01.x * ru + d01.y * rv, xo.y + d23.x * ru + d23.y * rv);
+        const double2 xo = DS ? x2[t] : __ldcg(x2 + t);
+        v = make_double2(xo.x + d01.x * ru + d01.y * rv, xo.y + d23.x * ru + d23.y * rv);
+        if (!DS || last) reinterpret_cast<double2*>(dst)[t] = v;
       }
+      if (DS && !last) publish((sw + 1) & 1, t, v);
     }
-    cl.sync();
+    cl.sync();      // (after the last sweep: no CTA may exit while a peer could still write into its shared memory)
     double* tmp = src; src = dst; dst = (tmp == out) ? xb : tmp;
   }
 }
@@ -863,19 +881,21 @@ size_t coarsest_cluster_smem(const std::vector<int>& slice_ptr_host, int n, int 
   }
   return (size_t)worst * (128 * sizeof(VT) + 32 * sizeof(int));
 }
-template <typename VT>
+inline size_t coarsest_cluster_xbytes(int n) { return sizeof(double2) * 2 * (size_t)((n + 31) / 32) * 32; }
+template <typename VT, bool DS>
 int launch_coarsest_cluster(Ctx* c, int cluster, size_t smem, const MgLevel& L, const VT* val, const double* b, double* xa, double* xb, double* out, int nsweeps) {
   static size_t smem_set = 0;
   static bool nonportable = false;
-  if (smem > smem_set) { UFE_CUDA(cudaFuncSetAttribute(k_mg_coarsest_cluster<VT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); smem_set = smem; }
-  if (cluster > 8 && !nonportable) { UFE_CUDA(cudaFuncSetAttribute(k_mg_coarsest_cluster<VT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1)); nonportable = true; }
+  if (DS) smem += coarsest_cluster_xbytes(L.n);
+  if (smem > smem_set) { UFE_CUDA(cudaFuncSetAttribute(k_mg_coarsest_cluster<VT, DS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); smem_set = smem; }
+  if (cluster > 8 && !nonportable) { UFE_CUDA(cudaFuncSetAttribute(k_mg_coarsest_cluster<VT, DS>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1)); nonportable = true; }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(cluster); cfg.blockDim = dim3(kCoarsestBlock); cfg.dynamicSmemBytes = smem; cfg.stream = c->stream;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  UFE_CUDA(cudaLaunchKernelEx(&cfg, k_mg_coarsest_cluster<VT>, L.n, L.slice_ptr, L.col, val, (const double*)L.dblk.p, b, xa, xb, out, nsweeps));
+  UFE_CUDA(cudaLaunchKernelEx(&cfg, k_mg_coarsest_cluster<VT, DS>, L.n, L.slice_ptr, L.col, val, (const double*)L.dblk.p, b, xa, xb, out, nsweeps));
   return 0;
 }
 
@@ -1154,7 +1174,10 @@ int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out, bool x1_ready) 
     }
     if (P.coarsest_cluster > 1 && !G.rec && G.coarsest_smem > 0 && P.coarse_sweeps >= 1 && L.off == 0) {   // all sweeps of this visit in one cluster kernel
       UFE_LAUNCH(c, TC_MG_COARSE);
-      UFE_TRY(launch_coarsest_cluster<VT>(c, P.coarsest_cluster, G.coarsest_smem, L, level_values<VT>(L), b, xa, xb, out, P.coarse_sweeps));
+      if (P.coarsest_dsmem && G.coarsest_smem + coarsest_cluster_xbytes(L.n) <= 200 * 1024)
+        UFE_TRY((launch_coarsest_cluster<VT, true>(c, P.coarsest_cluster, G.coarsest_smem, L, level_values<VT>(L), b, xa, xb, out, P.coarse_sweeps)));
+      else
+        UFE_TRY((launch_coarsest_cluster<VT, false>(c, P.coarsest_cluster, G.coarsest_smem, L, level_values<VT>(L), b, xa, xb, out, P.coarse_sweeps)));
       return 0;
     }
     op_smooth0(c, G, l, L.n, b, L.dblk.p, xa + 2 * L.off);
