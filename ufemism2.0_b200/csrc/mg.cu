@@ -883,14 +883,14 @@ size_t coarsest_cluster_smem(const std::vector<int>& slice_ptr_host, int n, int 
 }
 inline size_t coarsest_cluster_xbytes(int n) { return sizeof(double2) * 2 * (size_t)((n + 31) / 32) * 32; }
 template <typename VT, bool DS>
-int launch_coarsest_cluster(Ctx* c, int cluster, size_t smem, const MgLevel& L, const VT* val, const double* b, double* xa, double* xb, double* out, int nsweeps) {
+int launch_coarsest_cluster(Ctx* c, int cluster, int threads, size_t smem, const MgLevel& L, const VT* val, const double* b, double* xa, double* xb, double* out, int nsweeps) {
   static size_t smem_set = 0;
   static bool nonportable = false;
   if (DS) smem += coarsest_cluster_xbytes(L.n);
   if (smem > smem_set) { UFE_CUDA(cudaFuncSetAttribute(k_mg_coarsest_cluster<VT, DS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); smem_set = smem; }
   if (cluster > 8 && !nonportable) { UFE_CUDA(cudaFuncSetAttribute(k_mg_coarsest_cluster<VT, DS>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1)); nonportable = true; }
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(cluster); cfg.blockDim = dim3(kCoarsestBlock); cfg.dynamicSmemBytes = smem; cfg.stream = c->stream;
+  cfg.gridDim = dim3(cluster); cfg.blockDim = dim3(std::min(kCoarsestBlock, std::max(32, (threads / 32) * 32))); cfg.dynamicSmemBytes = smem; cfg.stream = c->stream;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
@@ -1175,9 +1175,9 @@ int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out, bool x1_ready) 
     if (P.coarsest_cluster > 1 && !G.rec && G.coarsest_smem > 0 && P.coarse_sweeps >= 1 && L.off == 0) {   // all sweeps of this visit in one cluster kernel
       UFE_LAUNCH(c, TC_MG_COARSE);
       if (P.coarsest_dsmem && G.coarsest_smem + coarsest_cluster_xbytes(L.n) <= 200 * 1024)
-        UFE_TRY((launch_coarsest_cluster<VT, true>(c, P.coarsest_cluster, G.coarsest_smem, L, level_values<VT>(L), b, xa, xb, out, P.coarse_sweeps)));
+        UFE_TRY((launch_coarsest_cluster<VT, true>(c, P.coarsest_cluster, P.coarsest_threads, G.coarsest_smem, L, level_values<VT>(L), b, xa, xb, out, P.coarse_sweeps)));
       else
-        UFE_TRY((launch_coarsest_cluster<VT, false>(c, P.coarsest_cluster, G.coarsest_smem, L, level_values<VT>(L), b, xa, xb, out, P.coarse_sweeps)));
+        UFE_TRY((launch_coarsest_cluster<VT, false>(c, P.coarsest_cluster, P.coarsest_threads, G.coarsest_smem, L, level_values<VT>(L), b, xa, xb, out, P.coarse_sweeps)));
       return 0;
     }
     op_smooth0(c, G, l, L.n, b, L.dblk.p, xa + 2 * L.off);

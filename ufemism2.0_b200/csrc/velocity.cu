@@ -1287,6 +1287,7 @@ int ufe_b200_set_mg_option(ufe_b200_handle h, const char* name, double value) {
   else if (!strcmp(name, "stop_nodes")) { p.stop_nodes = (int)value; rebuild = true; }
   else if (!strcmp(name, "coarsest_cluster")) { p.coarsest_cluster = (int)value; rebuild = true; }
   else if (!strcmp(name, "coarsest_dsmem")) p.coarsest_dsmem = (int)value;
+  else if (!strcmp(name, "coarsest_threads")) p.coarsest_threads = (int)value;
   else if (!strcmp(name, "w_levels")) p.w_levels = (int)value;
   else if (!strcmp(name, "fuse")) p.fuse = (int)value;
   else if (!strcmp(name, "use_graph")) p.use_graph = (int)value;
