@@ -425,6 +425,7 @@ def run_b200(args, rank, world, rdv, log):
         if args.mg_stop_nodes > 0:
             ctx.set_mg_option("stop_nodes", args.mg_stop_nodes); ctx.set_mg_option("coarse_sweeps", args.mg_coarse_sweeps)
             ctx.set_mg_option("coarsest_cluster", args.mg_coarsest_cluster); ctx.set_mg_option("coarsest_dsmem", args.mg_coarsest_dsmem)
+            ctx.set_mg_option("coarsest_cheb", args.mg_coarsest_cheb); ctx.set_mg_option("cheb_ratio", args.mg_cheb_ratio)
     log(f"mesh nV={m.nV} nTri={m.nTri} nE={m.nE} generated in {time.time() - t0:.1f}s")
     t0 = time.time()
     ctx.mesh_create(m)
@@ -603,7 +604,7 @@ def run_b200(args, rank, world, rdv, log):
         except (OSError, KeyError, ValueError):
             pass
         krylov_desc = ("BiCGStab + aggregation multigrid (%d levels %s, %d+%d block-Jacobi sweeps, omega %.2f, %s matrix storage in the preconditioner)"
-                       % (mg_info["levels"], str(mg_info["nodes"]) + (f", {args.mg_coarse_sweeps} sweeps on the coarsest" + (f" in one {args.mg_coarsest_cluster}-CTA cluster kernel per visit" if args.mg_coarsest_cluster > 1 else "") if args.mg_stop_nodes > 0 else ", dense solve on the coarsest"),
+                       % (mg_info["levels"], str(mg_info["nodes"]) + (f", {args.mg_coarse_sweeps} " + ("Chebyshev steps" if args.mg_coarsest_cheb else "sweeps") + " on the coarsest" + (f" in one {args.mg_coarsest_cluster}-CTA cluster kernel per visit" if args.mg_coarsest_cluster > 1 else "") if args.mg_stop_nodes > 0 else ", dense solve on the coarsest"),
                           args.mg_nu, args.mg_nu, args.mg_omega, "FP32" if args.mg_fp32 else "FP64")
                        if mg_info else "BiCGStab + Jacobi")
         avg_ms = spmv_ms / max(spmv_n, 1)
@@ -671,6 +672,7 @@ def run_sweep(args, rank, world, rdv, log):
         if args.mg_stop_nodes > 0:
             ctx.set_mg_option("stop_nodes", args.mg_stop_nodes); ctx.set_mg_option("coarse_sweeps", args.mg_coarse_sweeps)
             ctx.set_mg_option("coarsest_cluster", args.mg_coarsest_cluster); ctx.set_mg_option("coarsest_dsmem", args.mg_coarsest_dsmem)
+            ctx.set_mg_option("coarsest_cheb", args.mg_coarsest_cheb); ctx.set_mg_option("cheb_ratio", args.mg_cheb_ratio)
     ctx.mesh_create(m)
     ctx.calc_matrix_operators()
     vr, tr = (ctx.vi1, ctx.vi2), (ctx.ti1, ctx.ti2)
@@ -757,10 +759,12 @@ def main():
     ap.add_argument("--mg-overcorr", type=float, default=1.5)
     ap.add_argument("--mg-w-levels", type=int, default=3)
     ap.add_argument("--mg-fp32", type=int, default=0)
+    ap.add_argument("--mg-coarsest-cheb", type=int, default=1, help="1: the corrections on the coarsest level are Chebyshev steps (k_mg_coarsest_cluster) instead of stationary sweeps")
+    ap.add_argument("--mg-cheb-ratio", type=float, default=30.0)
     ap.add_argument("--mg-coarsest-dsmem", type=int, default=0, help="iterate of the coarsest-level cluster kernel in distributed shared memory (1) or through L2 (0)")
     ap.add_argument("--mg-stop-nodes", type=int, default=-1, help="stop coarsening at the first level with at most this many nodes and run --mg-coarse-sweeps "
                     "sweeps there (ufe_b200_set_mg_option); -1: 2000 for the MISMIP_mod meshes of configs[2] / [4], 0 (library default: coarsen down to the dense solve) otherwise")
-    ap.add_argument("--mg-coarse-sweeps", type=int, default=32)
+    ap.add_argument("--mg-coarse-sweeps", type=int, default=-1, help="corrections on the coarsest level after the first one (-1: 8 Chebyshev steps, or 32 stationary sweeps with --mg-coarsest-cheb 0)")
     ap.add_argument("--mg-coarsest-cluster", type=int, default=-1, help="> 1: the sweeps on the coarsest level as one thread-block-cluster kernel of this many CTAs "
                     "(-1: 16 whenever --mg-stop-nodes is in effect)")
     ap.add_argument("--e2e-state", choices=["resident", "roundtrip"], default="resident",
@@ -781,6 +785,13 @@ def main():
         # 4 M vertices (profiles/r02_mg_probe_coarsest_cluster_4M.log, r02_bench_4_cluster16_cs32.log): 32 sweeps in one 16-CTA cluster kernel per visit cost
         # what 24 sweeps cost as graph nodes and save 2 more Krylov iterations per step (150.0 against 165.6 ms per step)
         args.mg_coarsest_cluster = 16 if args.mg_stop_nodes > 0 else 0
+    if args.mg_coarsest_cluster <= 1:
+        args.mg_coarsest_cheb = 0          # the Chebyshev steps live in the cluster kernel
+    if args.mg_coarse_sweeps < 0:
+        # 8 Chebyshev steps for [lmax / 30, lmax] do what 32 stationary sweeps do (42-43 Krylov iterations in the cold probe either way,
+        # profiles/r02_mg_probe_cheb_4M.log) at 0.70 instead of 1.11 ms per cycle: the same step time on one GPU (150.0 ms, r02_bench_6_cheb8.log),
+        # less of the replicated coarse graph on several
+        args.mg_coarse_sweeps = 8 if args.mg_coarsest_cheb else 32
 
     def log(*a):
         if args.verbose or os.environ.get("UFE_BENCH_VERBOSE"):

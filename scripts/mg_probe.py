@@ -53,7 +53,7 @@ for name, prm in SETTINGS:
         ctx.set_mg_params(**prm)
         for k0 in ("adaptive", "tail_max", "tail_cluster"):
             ctx.set_mg_option(k0, 0)
-        ctx.set_mg_option("max_levels", 12); ctx.set_mg_option("coarse_sweeps", 8); ctx.set_mg_option("stop_nodes", 0); ctx.set_mg_option("coarsest_cluster", 0); ctx.set_mg_option("coarsest_dsmem", 0); ctx.set_mg_option("coarsest_threads", 256)
+        ctx.set_mg_option("max_levels", 12); ctx.set_mg_option("coarse_sweeps", 8); ctx.set_mg_option("stop_nodes", 0); ctx.set_mg_option("coarsest_cluster", 0); ctx.set_mg_option("coarsest_dsmem", 0); ctx.set_mg_option("coarsest_threads", 256); ctx.set_mg_option("coarsest_cheb", 0); ctx.set_mg_option("cheb_ratio", 30.0)
         ctx.set_mg_option("nu_pre", prm["nu_pre"])
         for k0, v0 in opts.items():
             ctx.set_mg_option(k0, float(v0))

@@ -141,6 +141,29 @@ def test_coarsest_level_sweeps_as_one_cluster_kernel(setup, cluster, dsmem):
         ctx.set_mg_option("coarsest_cluster", 0); ctx.set_mg_option("coarsest_dsmem", 0); ctx.set_mg_option("stop_nodes", 0); ctx.set_mg_option("coarse_sweeps", 8)
 
 
+def test_chebyshev_steps_on_the_coarsest_level(setup):
+    """coarsest_cheb: the corrections of k_mg_coarsest_cluster as Chebyshev steps for [lmax / ratio, lmax] of Dw A (lmax from k_mg_lmax_bound); a fixed
+    polynomial preconditioner, so the solve must land on the same solution, with no more iterations than twice as many stationary sweeps need"""
+    w, ctx, o = setup
+    m = w.mesh
+    co = _coefficients(m, seed=8)
+    cfg = wl.scaling_config()
+    cfg.pc_type = ub.PC_MG
+    try:
+        ctx.set_mg_option("stop_nodes", 4000); ctx.set_mg_option("coarsest_cluster", 16)
+        ctx.set_mg_option("coarse_sweeps", 24); ctx.set_mg_option("coarsest_cheb", 0)
+        u0, v0, its0 = _linearised(ctx, cfg, m, *co, 1e-10, 1e-30)
+        ctx.set_mg_option("coarse_sweeps", 12); ctx.set_mg_option("coarsest_cheb", 1)
+        u1, v1, its1 = _linearised(ctx, cfg, m, *co, 1e-10, 1e-30)
+        ub2 = _linearised(ctx, cfg, m, *co, 1e-10, 1e-30)
+        assert rel_l2(u1, u0) < 1e-8 and rel_l2(v1, v0) < 1e-8, (rel_l2(u1, u0), rel_l2(v1, v0))
+        assert 0 < its1 <= its0 + max(3, its0 // 4), (its0, its1)
+        assert ub2[2] == its1 and np.array_equal(ub2[0], u1)          # deterministic
+    finally:
+        for k, v in (("coarsest_cheb", 0), ("coarsest_cluster", 0), ("stop_nodes", 0), ("coarse_sweeps", 8)):
+            ctx.set_mg_option(k, v)
+
+
 def test_multigrid_is_deterministic(setup):
     w, ctx, o = setup
     m = w.mesh

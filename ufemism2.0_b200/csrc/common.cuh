@@ -119,6 +119,8 @@ struct MgParams {
   int dense_max = 128;           // coarsest level: at most this many nodes -> dense inverse; otherwise `coarse_sweeps` sweeps
   int coarse_sweeps = 8;
   int coarsest_cluster = 0;      // > 1: the sweeps on the coarsest level run as one kernel of this many CTAs in one thread-block cluster (mg.cu: k_mg_coarsest_cluster)
+  int coarsest_cheb = 0;         // 1: the `coarse_sweeps` corrections of that kernel are Chebyshev steps for [lmax / cheb_ratio, lmax] of Dw A instead of stationary sweeps
+  double cheb_ratio = 30.0;
   int coarsest_threads = 256;    // threads per CTA of that kernel (a multiple of 32, at most 256)
   int coarsest_dsmem = 0;        // ... with the iterate exchanged through L2 (0) or held in distributed shared memory (1); measured equal (2 us per sweep either way)
   int stop_nodes = 0;            // > 0: coarsening stops at the first level with at most this many nodes; above dense_max that level is solved by `coarse_sweeps` sweeps

@@ -791,6 +791,28 @@ int launch_tail_cluster(Ctx* c, int cluster, const MgStep* steps, int nsteps) {
 // hold it), then runs all sweeps: columns and values come from shared memory, only the iterate is gathered from L2 (ld.global.cg: never from a stale
 // L1 line), written back and published to the other CTAs by the cluster barrier (barrier.cluster, release / acquire at cluster scope).  Same row
 // arithmetic and summation order as k_mg_smooth0 / k_mg_sweep<MODE 0>.
+// upper bound of the spectral radius of Dw A on one level: the largest absolute row sum of the 2x2 blocks Dw_i A_ij (infinity norm), as the bits of a
+// positive double through atomicMax.  Input of the Chebyshev variant of k_mg_coarsest_cluster; one pass per numeric set-up.
+template <typename VT>
+__global__ void k_mg_lmax_bound(int n, const int* __restrict__ slice_ptr, const int* __restrict__ col, const VT* __restrict__ val, const double* __restrict__ dblk,
+                                unsigned long long* out_bits) {
+  double worst = 0.0;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+    const int s = t >> 5, lane = t & 31;
+    const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
+    double r0 = 0.0, r1 = 0.0;
+    for (int k = slice_ptr[s]; k < slice_ptr[s + 1]; ++k) {
+      const VT* p = val + (size_t)k * 128 + lane;
+      const double a0 = (double)p[0], a1 = (double)p[32], a2 = (double)p[64], a3 = (double)p[96];
+      r0 += fabs(d01.x * a0 + d01.y * a2) + fabs(d01.x * a1 + d01.y * a3);
+      r1 += fabs(d23.x * a0 + d23.y * a2) + fabs(d23.x * a1 + d23.y * a3);
+    }
+    worst = fmax(worst, fmax(r0, r1));
+  }
+  for (int o = 16; o > 0; o >>= 1) worst = fmax(worst, __shfl_xor_sync(0xffffffffu, worst, o));
+  if ((threadIdx.x & 31) == 0 && worst > 0.0) atomicMax(out_bits, (unsigned long long)__double_as_longlong(worst));
+}
+
 constexpr int kCoarsestBlock = 256;
 // DS = true: the iterate lives in every CTA's shared memory (two buffers of n double2); a CTA writes the new values of its rows into the next buffer of
 // ALL CTAs through distributed shared memory (cluster.map_shared_rank) and the gathers of the next sweep are local shared-memory reads -- no L2 round
@@ -798,7 +820,20 @@ constexpr int kCoarsestBlock = 256;
 template <typename VT, bool DS>
 __global__ void __launch_bounds__(kCoarsestBlock, 1) k_mg_coarsest_cluster(int n, const int* __restrict__ slice_ptr, const int* __restrict__ col,
                                                                            const VT* __restrict__ val, const double* __restrict__ dblk,
-                                                                           const double* __restrict__ b, double* xa, double* xb, double* out, int nsweeps) {
+                                                                           const double* __restrict__ b, double* xa, double* xb, double* out, int nsweeps,
+                                                                           const double* __restrict__ lmax, double cheb_ratio) {
+  // lmax != nullptr: the nsweeps corrections are Chebyshev steps for the eigenvalue interval [lmax / cheb_ratio, lmax] of Dw A instead of stationary
+  // sweeps: x_{k+1} = x_k + d_k, d_k = rho_k rho_{k-1} d_{k-1} + (2 rho_k / delta) Dw (b - A x_k) -- a fixed polynomial of Dw A, i.e. still a linear,
+  // iteration-independent preconditioner, which damps the whole interval by ((sqrt(kappa) - 1) / (sqrt(kappa) + 1))^k where a stationary sweep needs
+  // (1 - 1 / kappa)^k.  d_k of a thread's own rows stays in registers.
+  const bool cheb = lmax != nullptr;
+  double theta = 1.0, delta = 1.0, sigma = 1.0, rho_old = 1.0;
+  if (cheb) {
+    const double hi = 1.05 * fmax(*lmax, 1e-300), lo = hi / cheb_ratio;
+    theta = 0.5 * (hi + lo); delta = 0.5 * (hi - lo); sigma = theta / delta; rho_old = 1.0 / sigma;
+  }
+  constexpr int kMaxOwn = 4;      // slices a warp may own (launch_coarsest_cluster checks it)
+  double2 dk[kMaxOwn];
   cooperative_groups::cluster_group cl = cooperative_groups::this_cluster();
   const int rank = (int)cl.block_rank(), C = (int)cl.num_blocks();
   extern __shared__ __align__(16) unsigned char s_raw[];
@@ -819,17 +854,22 @@ __global__ void __launch_bounds__(kCoarsestBlock, 1) k_mg_coarsest_cluster(int n
   auto publish = [&](int buf, int t, double2 v) {     // DS: node t of buffer `buf` in every CTA of the cluster
     for (int r = 0; r < C; ++r) cl.map_shared_rank(s_x, r)[buf * nx + t] = v;
   };
-  // first sweep from a zero iterate: x = Dw b
-  for (int s = s0 + warp; s < s1; s += nwarps) {
-    const int t = (s << 5) + lane;
-    double2 v = make_double2(0.0, 0.0);
-    if (t < n) {
-      const double2 bv = reinterpret_cast<const double2*>(b)[t];
-      const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
-      v = make_double2(d01.x * bv.x + d01.y * bv.y, d23.x * bv.x + d23.y * bv.y);
-      if (!DS) reinterpret_cast<double2*>(xa)[t] = v;
+  // first sweep from a zero iterate: x = Dw b  (Chebyshev: x = d_0 = Dw b / theta)
+  {
+    int own = 0;
+    for (int s = s0 + warp; s < s1; s += nwarps, ++own) {
+      const int t = (s << 5) + lane;
+      double2 v = make_double2(0.0, 0.0);
+      if (t < n) {
+        const double2 bv = reinterpret_cast<const double2*>(b)[t];
+        const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
+        v = make_double2(d01.x * bv.x + d01.y * bv.y, d23.x * bv.x + d23.y * bv.y);
+        if (cheb) { v.x /= theta; v.y /= theta; }
+        if (!DS) reinterpret_cast<double2*>(xa)[t] = v;
+      }
+      if (own < kMaxOwn) dk[own] = v;
+      if (DS) publish(0, t, v);       // padding rows of the last slice hold zeros (their columns may be read, their values are zero)
     }
-    if (DS) publish(0, t, v);       // padding rows of the last slice hold zeros (their columns may be read, their values are zero)
   }
   cl.sync();        // also orders the shared-memory copies (it is a superset of __syncthreads)
   double* src = xa; double* dst = xb;
@@ -837,7 +877,10 @@ __global__ void __launch_bounds__(kCoarsestBlock, 1) k_mg_coarsest_cluster(int n
     const bool last = sw == nsweeps - 1;
     if (last) dst = out;
     const double2* x2 = DS ? s_x + (sw & 1) * nx : reinterpret_cast<const double2*>(src);
-    for (int s = s0 + warp; s < s1; s += nwarps) {
+    const double rho = 1.0 / (2.0 * sigma - rho_old);        // Chebyshev coefficients of this step (the same in every thread)
+    const double c_d = rho * rho_old, c_z = 2.0 * rho / delta;
+    int own = 0;
+    for (int s = s0 + warp; s < s1; s += nwarps, ++own) {
       const int t = (s << 5) + lane;
       const int k0 = slice_ptr[s] - k_lo, k1 = slice_ptr[s + 1] - k_lo;
       double yu = 0.0, yv = 0.0;
@@ -861,11 +904,19 @@ __global__ void __launch_bounds__(kCoarsestBlock, 1) k_mg_coarsest_cluster(int n
         const double ru = bv.x - yu, rv = bv.y - yv;
         const double2 d01 = reinterpret_cast<const double2*>(dblk)[2 * t], d23 = reinterpret_cast<const double2*>(dblk)[2 * t + 1];
         const double2 xo = DS ? x2[t] : __ldcg(x2 + t);
-        v = make_double2(xo.x + d01.x * ru + d01.y * rv, xo.y + d23.x * ru + d23.y * rv);
+        if (cheb) {
+          const double2 dprev = dk[own < kMaxOwn ? own : 0];
+          const double2 dn = make_double2(c_d * dprev.x + c_z * (d01.x * ru + d01.y * rv), c_d * dprev.y + c_z * (d23.x * ru + d23.y * rv));
+          if (own < kMaxOwn) dk[own] = dn;
+          v = make_double2(xo.x + dn.x, xo.y + dn.y);
+        } else {
+          v = make_double2(xo.x + d01.x * ru + d01.y * rv, xo.y + d23.x * ru + d23.y * rv);
+        }
         if (!DS || last) reinterpret_cast<double2*>(dst)[t] = v;
       }
       if (DS && !last) publish((sw + 1) & 1, t, v);
     }
+    rho_old = rho;
     cl.sync();      // (after the last sweep: no CTA may exit while a peer could still write into its shared memory)
     double* tmp = src; src = dst; dst = (tmp == out) ? xb : tmp;
   }
@@ -883,7 +934,8 @@ size_t coarsest_cluster_smem(const std::vector<int>& slice_ptr_host, int n, int 
 }
 inline size_t coarsest_cluster_xbytes(int n) { return sizeof(double2) * 2 * (size_t)((n + 31) / 32) * 32; }
 template <typename VT, bool DS>
-int launch_coarsest_cluster(Ctx* c, int cluster, int threads, size_t smem, const MgLevel& L, const VT* val, const double* b, double* xa, double* xb, double* out, int nsweeps) {
+int launch_coarsest_cluster(Ctx* c, int cluster, int threads, size_t smem, const MgLevel& L, const VT* val, const double* b, double* xa, double* xb, double* out, int nsweeps,
+                            const double* lmax, double cheb_ratio) {
   static size_t smem_set = 0;
   static bool nonportable = false;
   if (DS) smem += coarsest_cluster_xbytes(L.n);
@@ -895,7 +947,7 @@ int launch_coarsest_cluster(Ctx* c, int cluster, int threads, size_t smem, const
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  UFE_CUDA(cudaLaunchKernelEx(&cfg, k_mg_coarsest_cluster<VT, DS>, L.n, L.slice_ptr, L.col, val, (const double*)L.dblk.p, b, xa, xb, out, nsweeps));
+  UFE_CUDA(cudaLaunchKernelEx(&cfg, k_mg_coarsest_cluster<VT, DS>, L.n, L.slice_ptr, L.col, val, (const double*)L.dblk.p, b, xa, xb, out, nsweeps, lmax, cheb_ratio));
   return 0;
 }
 
@@ -1174,10 +1226,13 @@ int mg_cycle(Ctx* c, Mg& G, int l, const double* b, double* out, bool x1_ready) 
     }
     if (P.coarsest_cluster > 1 && !G.rec && G.coarsest_smem > 0 && P.coarse_sweeps >= 1 && L.off == 0) {   // all sweeps of this visit in one cluster kernel
       UFE_LAUNCH(c, TC_MG_COARSE);
+      // Chebyshev steps need d_k of every own row in registers: at most 4 slices per warp
+      const int per = ((L.n_slices + P.coarsest_cluster - 1) / P.coarsest_cluster), warps = std::max(1, std::min(kCoarsestBlock, P.coarsest_threads) / 32);
+      const double* lmax = (P.coarsest_cheb && (per + warps - 1) / warps <= 4) ? reinterpret_cast<const double*>(G.lmax_bits.p) : nullptr;
       if (P.coarsest_dsmem && G.coarsest_smem + coarsest_cluster_xbytes(L.n) <= 200 * 1024)
-        UFE_TRY((launch_coarsest_cluster<VT, true>(c, P.coarsest_cluster, P.coarsest_threads, G.coarsest_smem, L, level_values<VT>(L), b, xa, xb, out, P.coarse_sweeps)));
+        UFE_TRY((launch_coarsest_cluster<VT, true>(c, P.coarsest_cluster, P.coarsest_threads, G.coarsest_smem, L, level_values<VT>(L), b, xa, xb, out, P.coarse_sweeps, lmax, P.cheb_ratio)));
       else
-        UFE_TRY((launch_coarsest_cluster<VT, false>(c, P.coarsest_cluster, P.coarsest_threads, G.coarsest_smem, L, level_values<VT>(L), b, xa, xb, out, P.coarse_sweeps)));
+        UFE_TRY((launch_coarsest_cluster<VT, false>(c, P.coarsest_cluster, P.coarsest_threads, G.coarsest_smem, L, level_values<VT>(L), b, xa, xb, out, P.coarse_sweeps, lmax, P.cheb_ratio)));
       return 0;
     }
     op_smooth0(c, G, l, L.n, b, L.dblk.p, xa + 2 * L.off);
@@ -1267,6 +1322,13 @@ int mg_numeric(Ctx* c, Mg& G) {
       VT* cv = const_cast<VT*>(level_values<VT>(G.lv[1]));
       UFE_TRY(allreduce_sum_large(c, cv, (size_t)G.lv[1].n_slots * 4, sizeof(VT) == 4));
     }
+  }
+  if (G.p.coarsest_cheb && G.dense_n == 0 && nl > 1) {      // spectral bound of Dw A on the coarsest level for the Chebyshev steps
+    MgLevel& L = G.lv[nl - 1];
+    UFE_TRY(G.lmax_bits.alloc(1));
+    UFE_CUDA(cudaMemsetAsync(G.lmax_bits.p, 0, sizeof(unsigned long long), st));
+    UFE_LAUNCH(c, TC_MG_SETUP);
+    k_mg_lmax_bound<VT><<<grid_for(c, L.n, kBlock), kBlock, 0, st>>>(L.n, L.slice_ptr, L.col, level_values<VT>(L), L.dblk.p, G.lmax_bits.p);
   }
   if (G.dense_n > 0) {
     MgLevel& L = G.lv[nl - 1];

@@ -71,6 +71,7 @@ struct Mg {
     graph_exec = nullptr; graph = nullptr; graph_launches = 0; program_n = 0; tail_len[0] = tail_len[1] = 0;
   }
   std::vector<MgLevel> lv;
+  DBuf<unsigned long long> lmax_bits;     // bits of the bound of the spectral radius of Dw A on the coarsest level (Chebyshev steps)
   size_t coarsest_smem = 0;               // shared memory per CTA of k_mg_coarsest_cluster for the last level (0: does not fit / not wanted)
   DBuf<double> dense_w, dense_inv;        // Gauss-Jordan workspace [N][2N], inverse (column-major) [N][N]
   int dense_n = 0;                        // unknowns of the dense coarsest solve (0: smoothing only)

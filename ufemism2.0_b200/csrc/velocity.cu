@@ -1288,6 +1288,8 @@ int ufe_b200_set_mg_option(ufe_b200_handle h, const char* name, double value) {
   else if (!strcmp(name, "coarsest_cluster")) { p.coarsest_cluster = (int)value; rebuild = true; }
   else if (!strcmp(name, "coarsest_dsmem")) p.coarsest_dsmem = (int)value;
   else if (!strcmp(name, "coarsest_threads")) p.coarsest_threads = (int)value;
+  else if (!strcmp(name, "coarsest_cheb")) p.coarsest_cheb = (int)value;
+  else if (!strcmp(name, "cheb_ratio")) p.cheb_ratio = value;
   else if (!strcmp(name, "w_levels")) p.w_levels = (int)value;
   else if (!strcmp(name, "fuse")) p.fuse = (int)value;
   else if (!strcmp(name, "use_graph")) p.use_graph = (int)value;
