@@ -28,7 +28,7 @@ module ufe_b200_mod
 
   public :: ufe_b200_initialise, ufe_b200_finalise
   public :: solve_matrix_equation_CSR_B200
-  public :: ufe_b200_upload_mesh, ufe_b200_destroy_mesh
+  public :: ufe_b200_upload_mesh, ufe_b200_destroy_mesh, remap_velocity_solver_B200
   public :: ufe_b200_fill_config, ufe_b200_config
   public :: solve_DIVA_infinite_slab_B200, solve_SSA_B200, calc_dHi_dt_B200, set_ice_velocities_B200, calc_pc_truncation_error_B200
 
@@ -634,6 +634,35 @@ contains
     ! Called from the mesh finaliser and before update_mesh -> remap_velocity_solver (UFEMISM_main_model.f90:1211)
     if (c_associated( handle)) call check( c_ufe_b200_mesh_destroy( handle), 'ufe_b200_destroy_mesh')
   end subroutine ufe_b200_destroy_mesh
+
+  subroutine remap_velocity_solver_B200( mesh_new, approximation, M_map)
+    ! Drop-in for the remap_DIVA_solver / remap_SSA_solver branch of remap_velocity_solver (called after update_mesh, UFEMISM_main_model.f90:1211;
+    ! DIVA_main.f90:115-222, SSA_main.f90:247-311) when the solver state lives on the device: a second handle takes the new mesh, the re-used
+    ! fields go old b-grid -> old a-grid -> Atlas map -> border fix -> new b-grid on the device, the old handle is released and the new one
+    ! becomes the module's handle.  M_map = the rank's rows (mesh_new%vi1:vi2) of the map from mesh_old's to mesh_new's vertices as a finalised
+    ! type_sparse_matrix_CSR_dp (mat_petsc2CSR( map%M, M_map), petsc_basic.f90:366; the map itself is still made by create_map_from_mesh_to_mesh_*).
+    ! approximation: 0 'SSA', 1 'DIVA'.
+    type(type_mesh),                 target, intent(in) :: mesh_new
+    integer,                                 intent(in) :: approximation
+    type(type_sparse_matrix_CSR_dp), target, intent(in) :: M_map
+    character(len=1024), parameter :: routine_name = 'remap_velocity_solver_B200'
+    character(kind=c_char) :: id128(128)
+    type(c_ptr) :: handle_old
+    integer :: ierr
+    call init_routine( routine_name)
+    handle_old = handle
+    id128 = c_null_char
+    if (par%n > 1) then
+      if (par%primary) call check( c_ufe_b200_get_unique_id( id128), routine_name)
+      call MPI_BCAST( id128, 128, MPI_BYTE, 0, MPI_COMM_WORLD, ierr)
+    end if
+    call check( c_ufe_b200_init( -1_c_int, int( par%i, c_int), int( par%n, c_int), id128, handle), routine_name)
+    call ufe_b200_upload_mesh( mesh_new)      ! on the new handle: ufe_b200_mesh_create + ufe_b200_calc_matrix_operators
+    call check( c_ufe_b200_remap_velocity_solver( handle_old, handle, int( approximation, c_int), int( M_map%m_loc, c_int), &
+      c_loc( M_map%ptr( M_map%i1)), c_loc( M_map%ind), c_loc( M_map%val)), routine_name)   ! ptr( i1: i2+1): 1-based offsets into the local ind / val
+    call check( c_ufe_b200_finalize( handle_old), routine_name)
+    call finalise_routine( routine_name)
+  end subroutine remap_velocity_solver_B200
 
   subroutine solve_DIVA_infinite_slab_B200( mesh, ice, bed_roughness, DIVA, n_visc_its, n_Axb_its, &
     BC_prescr_mask_b, BC_prescr_u_b, BC_prescr_v_b)
