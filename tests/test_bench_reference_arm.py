@@ -55,3 +55,15 @@ def test_reference_arm_other_ranks_exit_without_work():
     p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0", "--cpu-nv", "3000"],
                        capture_output=True, text=True, timeout=120, env=env)
     assert p.returncode == 0 and p.stdout.strip() == "", (p.returncode, p.stdout[-500:], p.stderr[-500:])
+
+
+def test_every_bench_config_builds_its_workload():
+    """bench.py --config: the workloads of the other BASELINE configs (mesh + fields + physics), without a GPU"""
+    import bench
+    w = bench.make_workload(0, "mg", "mismip8km")
+    assert 60_000 < w.mesh.nV < 90_000 and w.approximation == 1 and w.f["mask_noice"].sum() > 0          # +-1000 km at 8 km, MISMIP_mod no-ice mask
+    w = bench.make_workload(20_000, "mg", "mismipplus_ssa")
+    assert w.approximation == 0 and abs(w.mesh.xmax - 800e3) < 1.0 and w.cfg.stress_balance_PETSc_rtol == 1e-7
+    w = bench.make_workload(20_000, "mg", "sweep")
+    assert w.approximation == 1 and w.cfg.ksp_initial_guess_nonzero == 0
+    assert set(bench.CONFIGS) == {"antarctica", "mismip8km", "mismipplus_ssa", "sweep"} and sorted(c["index"] for c in bench.CONFIGS.values()) == [0, 1, 2, 4]
