@@ -79,3 +79,18 @@ def test_laplace_solve_reproduces_the_reference_component_test(res):
         ok, err = rm.checksum_close(rm.checksum(f), ref["f_ex"], 1e-10)
         assert ok, (ksp, err, its)
         assert np.abs(f - f_ex).max() <= 1e-10 * np.abs(f_ex).max()
+
+
+def test_hdf5_reader_refuses_what_it_does_not_understand(tmp_path):
+    """tests/golden/h5lite.py reads exactly the HDF5 features the reference's files use; anything else must raise instead of returning wrong data"""
+    import sys
+    sys.path.insert(0, rm.GOLD)
+    import h5lite
+    bad = tmp_path / "not_hdf5.nc"
+    bad.write_bytes(b"CDF\x01" + bytes(60))                           # a classic (non-HDF5) NetCDF header
+    with pytest.raises(h5lite.H5Unsupported, match="not an HDF5 file"):
+        h5lite.File(str(bad))
+    v0 = tmp_path / "superblock_v0.h5"
+    v0.write_bytes(b"\x89HDF\r\n\x1a\n" + bytes([0]) + bytes(87))     # HDF5 signature, superblock version 0
+    with pytest.raises(h5lite.H5Unsupported, match="superblock version 0"):
+        h5lite.File(str(v0))
