@@ -162,3 +162,50 @@ def test_split_rows_assemble_the_global_galerkin_product(nparts):
         P[2 * t, 2 * agg[t]] = 1.0; P[2 * t + 1, 2 * agg[t] + 1] = 1.0
     Ac = dense_from_ell(nc.value, 0, csp, ccol, cval, nc.value)
     np.testing.assert_allclose(Ac, P.T @ A @ P, rtol=1e-12, atol=1e-12)
+
+
+def test_chebyshev_steps_model_of_the_coarsest_level_kernel():
+    """numpy model of k_mg_coarsest_cluster's Chebyshev mode (mg.cu): x_0 = 0, d_0 = Dw b / theta, x_{k+1} = x_k + d_k,
+    d_k = rho_k rho_{k-1} d_{k-1} + (2 rho_k / delta) Dw (b - A x_k) on [lmax / ratio, lmax], lmax = 1.05 x the infinity-norm bound of Dw A.
+    The map b -> x is linear (a fixed polynomial of Dw A: a valid stationary preconditioner), and 8 steps leave about the error of 32 damped
+    Jacobi sweeps (and much less than 8 of them) on a diagonally dominant, slightly non-symmetric matrix."""
+    rng = np.random.default_rng(21)
+    n = 400
+    # a 2-D Laplacian-like matrix with a weak shift and a non-symmetric perturbation (what the coarse SSA operators look like after Jacobi scaling)
+    g = int(np.sqrt(n)); A = np.zeros((n, n))
+    for i in range(g):
+        for j in range(g):
+            r = i * g + j
+            A[r, r] = 4.0 + 0.02
+            for di, dj in ((1, 0), (-1, 0), (0, 1), (0, -1)):
+                ii, jj = i + di, j + dj
+                if 0 <= ii < g and 0 <= jj < g:
+                    A[r, ii * g + jj] = -1.0 + 0.05 * rng.standard_normal()
+    Dw = 0.8 / np.diag(A)
+
+    def cheb(b, steps, ratio=30.0):
+        hi = 1.05 * np.abs(Dw[:, None] * A).sum(axis=1).max(); lo = hi / ratio
+        theta, delta = 0.5 * (hi + lo), 0.5 * (hi - lo)
+        sigma = theta / delta; rho_old = 1.0 / sigma
+        d = Dw * b / theta; x = d.copy()
+        for _ in range(steps):
+            rho = 1.0 / (2.0 * sigma - rho_old)
+            d = rho * rho_old * d + (2.0 * rho / delta) * (Dw * (b - A @ x))
+            x = x + d
+            rho_old = rho
+        return x
+
+    def jacobi(b, sweeps):
+        x = Dw * b
+        for _ in range(sweeps):
+            x = x + Dw * (b - A @ x)
+        return x
+
+    b1, b2 = rng.standard_normal(n), rng.standard_normal(n)
+    np.testing.assert_allclose(cheb(2.0 * b1 - 3.0 * b2, 8), 2.0 * cheb(b1, 8) - 3.0 * cheb(b2, 8), rtol=1e-12, atol=1e-12)   # linear in b
+    x_ex = np.linalg.solve(A, b1)
+    e_c = np.linalg.norm(cheb(b1, 8) - x_ex) / np.linalg.norm(x_ex)
+    e_j = np.linalg.norm(jacobi(b1, 32) - x_ex) / np.linalg.norm(x_ex)
+    e_j8 = np.linalg.norm(jacobi(b1, 8) - x_ex) / np.linalg.norm(x_ex)
+    assert e_c < 1.1 * e_j < 1.0 and e_c < 0.85 * e_j8, (e_c, e_j, e_j8)      # 8 steps do what 32 sweeps do (the device probe says the same)
+    assert np.linalg.norm(cheb(b1, 16) - x_ex) < np.linalg.norm(cheb(b1, 8) - x_ex)        # more steps, smaller error
